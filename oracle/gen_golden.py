@@ -1,0 +1,151 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz by running the UNMODIFIED reference
+(imported from /root/reference through oracle/ref_shim.py) on seeded inputs.
+
+Run in the build container:   python -m oracle.gen_golden
+The fixtures are small, are committed, and travel to the GPU box where /root/reference does
+not exist.  Every array in them is an output of the reference's own code
+(DLRM_Net / nn.EmbeddingBag / interact_features / RWSAdagrad / torch.optim.SGD / sharders).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+# (name, seed, ln_emb, D, ln_bot, ln_top, B, L, fixed_L, optimizer)
+CASES = [
+    # C1: tiny CPU run of BASELINE.json configs[0] (README.md:141; defaults dlrm_s_pytorch.py:1181-1185)
+    ("c1_tiny_sgd", 123, [4, 3, 2], 2, [4, 3, 2], [8, 4, 2, 1], 2, 10, False, "sgd"),
+    ("c1_tiny_rws", 123, [4, 3, 2], 2, [4, 3, 2], [8, 4, 2, 1], 2, 10, False, "rwsadagrad"),
+    # C2-like: Kaggle MLP shape and 26 tables, rows capped so the fixture stays small
+    ("c2_kaggle_small_rws", 123,
+     [1460, 583, 1000, 1000, 305, 24, 1000, 633, 3, 1000, 1000, 1000, 1000, 27, 1000, 1000, 10,
+      1000, 1000, 4, 1000, 18, 15, 1000, 105, 1000],
+     16, [13, 512, 256, 64, 16], [367, 512, 256, 1], 128, 1, True, "rwsadagrad"),
+    # C3-like: multi-hot pooling, dim 64, variable bag length incl. duplicates across bags
+    ("c3_multihot_sgd", 727, [500, 400, 300, 200], 64, [16, 32, 64], [74, 32, 1], 64, 20, False, "sgd"),
+    # C4-like: dim 128, L=1, skewed tiny tables next to larger ones (hot rows)
+    ("c4_terabyte_small_rws", 123, [3000, 39, 17, 7, 20, 3, 7000, 1500, 63, 4, 10, 2208],
+     128, [13, 64, 128], [206, 64, 1], 256, 1, True, "rwsadagrad"),
+]
+
+
+def run_case(ns, name, seed, ln_emb, D, ln_bot, ln_top, B, L, fixed_L, opt):
+    np.random.seed(seed)
+    torch.manual_seed(seed)
+    ln_emb = np.array(ln_emb)
+    ln_bot = np.array(ln_bot)
+    ln_top = np.array(ln_top)
+    m = ns.dlrm.DLRM_Net(D, ln_emb, ln_bot, ln_top, arch_interaction_op="dot",
+                         sigmoid_bot=-1, sigmoid_top=ln_top.size - 2)
+    out = {}
+    for k, E in enumerate(m.emb_l):
+        out["W0_%d" % k] = E.weight.detach().numpy().copy()
+    for pre, mlp in (("bot", m.bot_l), ("top", m.top_l)):
+        j = 0
+        for layer in mlp:
+            if isinstance(layer, torch.nn.Linear):
+                out["%s_W_%d" % (pre, j)] = layer.weight.detach().numpy().copy()
+                out["%s_b_%d" % (pre, j)] = layer.bias.detach().numpy().copy()
+                j += 1
+    # inputs from the reference's own generators (dlrm_data_pytorch.py:1165-1228, 1095-1106)
+    X, lS_o, lS_i = ns.dp.generate_dist_input_batch(
+        int(ln_bot[0]), ln_emb, B, L, fixed_L, "uniform", 0, 1, -1, 1)
+    Tgt = ns.dp.generate_random_output_batch(B, 1, True)
+    out["X"] = X.numpy()
+    out["target"] = Tgt.numpy()
+    for k in range(len(ln_emb)):
+        out["off_%d" % k] = lS_o[k].numpy().astype(np.int64)
+        out["idx_%d" % k] = lS_i[k].numpy().astype(np.int64)
+
+    if opt == "sgd":
+        optim = torch.optim.SGD(m.parameters(), lr=0.1)
+    else:
+        optim = ns.rwsadagrad.RWSAdagrad(m.parameters(), lr=0.1)
+
+    # forward pieces, exactly the calls sequential_forward makes (dlrm_s_pytorch.py:732-770)
+    x = m.apply_mlp(X, m.bot_l)
+    ly = m.apply_emb(lS_o, lS_i)
+    for t in ly:
+        t.retain_grad()
+    x.retain_grad()
+    z = m.interact_features(x, ly)
+    z.retain_grad()
+    p = m.apply_mlp(z, m.top_l)
+    loss = m.loss_fn(p, Tgt)
+    optim.zero_grad()
+    loss.backward()
+    out["x_bot"] = x.detach().numpy()
+    out["pooled"] = np.stack([t.detach().numpy() for t in ly], axis=1)        # [B,T,D]
+    out["interact"] = z.detach().numpy()
+    out["pred"] = p.detach().numpy()
+    out["loss"] = np.array(loss.item(), dtype=np.float32)
+    out["d_interact"] = z.grad.numpy().copy()
+    out["d_x_bot"] = x.grad.numpy().copy()
+    out["d_pooled"] = np.stack([t.grad.numpy() for t in ly], axis=1)          # [B,T,D]
+    for k, E in enumerate(m.emb_l):
+        g = E.weight.grad
+        assert g.is_sparse
+        out["graw_idx_%d" % k] = g._indices().numpy().copy()[0]               # uncoalesced
+        gc = g.coalesce()
+        out["gco_idx_%d" % k] = gc._indices().numpy().copy()[0]
+        out["gco_val_%d" % k] = gc._values().numpy().copy()
+    optim.step()
+    for k, E in enumerate(m.emb_l):
+        out["W1_%d" % k] = E.weight.detach().numpy().copy()
+        if opt == "rwsadagrad":
+            out["mom1_%d" % k] = optim.state[E.weight]["momentum"].numpy().copy()
+    # a second step on the same batch exercises non-zero accumulator state
+    p2 = m(X, lS_o, lS_i)
+    loss2 = m.loss_fn(p2, Tgt)
+    optim.zero_grad()
+    loss2.backward()
+    optim.step()
+    out["loss2"] = np.array(loss2.item(), dtype=np.float32)
+    for k, E in enumerate(m.emb_l):
+        out["W2_%d" % k] = E.weight.detach().numpy().copy()
+        if opt == "rwsadagrad":
+            out["mom2_%d" % k] = optim.state[E.weight]["momentum"].numpy().copy()
+    out["meta_ln_emb"] = ln_emb
+    out["meta_ln_bot"] = ln_bot
+    out["meta_ln_top"] = ln_top
+    out["meta_misc"] = np.array([D, B, L, int(fixed_L), seed])
+    out["meta_opt"] = np.array(opt)
+    out["meta_lr"] = np.array(0.1)
+    return out
+
+
+def sharder_golden(ns):
+    kaggle = [1460, 583, 10131227, 2202608, 305, 24, 12517, 633, 3, 93145, 5683, 8351593, 3194, 27,
+              14992, 5461306, 10, 5652, 2173, 4, 7046547, 18, 15, 286181, 105, 142572]
+    tera = [39884406, 39043, 17289, 7420, 20263, 3, 7120, 1543, 63, 38532951, 2953546, 403346, 10,
+            2208, 11938, 155, 4, 976, 14, 39979771, 25641295, 39664984, 585935, 12972, 108, 36]
+    out = {"kaggle": np.array(kaggle), "terabyte": np.array(tera)}
+    for nm, Es in (("kaggle", kaggle), ("terabyte", tera), ("bench", [1000000] * 8)):
+        for W in (1, 2, 3, 4, 8):
+            for alg in ("naive", "naive_chunk", "greedy", "hardcode"):
+                out["%s_%s_%d" % (nm, alg, W)] = np.array(ns.sharders.shard(np.array(Es), W, alg))
+    return out
+
+
+def main():
+    sys.path.insert(0, ROOT)
+    from oracle.ref_shim import load_reference
+    ns = load_reference()
+    os.makedirs(GOLDEN, exist_ok=True)
+    for case in CASES:
+        out = run_case(ns, *case)
+        path = os.path.join(GOLDEN, case[0] + ".npz")
+        np.savez_compressed(path, **out)
+        print("wrote", path, os.path.getsize(path), "bytes; loss", out["loss"], out["loss2"])
+    sh = sharder_golden(ns)
+    np.savez_compressed(os.path.join(GOLDEN, "sharders.npz"), **sh)
+    print("wrote sharders.npz")
+
+
+if __name__ == "__main__":
+    main()
