@@ -1,0 +1,83 @@
+// Layout kernels either side of the model-parallel exchange.  sm_100a.
+//
+// Replaces the torch.cat / split / .contiguous() copies of All2All_Req / All2All_Wait
+// (extend_distributed.py:424, 460, 482-487, 494-495) and the torch.cat of interact_features
+// (dlrm_s_pytorch.py:629-637): the send side needs no packing at all because the lookup kernel already
+// writes [B, T_r, D], which IS the concatenation over destination ranks of [B/W, T_r, D]; the receive
+// side is one pass that drops every source rank's [lb, T_p, D] chunk into its feature slots of the
+// [lb, 1+T, D] interaction input (rank-major table order, as the reference's cat produces), and the
+// backward is the mirror image.  Pure copy: 2 * lb*T*D*4 bytes of HBM traffic.
+#include "common.cuh"
+
+namespace dlrmx {
+
+constexpr int kMaxRanks = 64;
+struct RankSplit {
+    int W;
+    int first_table[kMaxRanks + 1];  // exclusive prefix of tables per rank
+};
+
+// dir 0: recv chunks -> feature block ; dir 1: feature-block gradient -> send chunks
+template <int VEC>
+__global__ void __launch_bounds__(256)
+a2a_layout_kernel(float* __restrict__ chunks, float* __restrict__ block, int64_t bsb, int feat_off,
+                  RankSplit rs, int lb, int D, int dir) {
+    const int T = rs.first_table[rs.W];
+    const int dv = D / VEC;
+    const int64_t total = (int64_t)lb * T * dv;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        const int d = (int)(e % dv);
+        const int64_t r = e / dv;
+        const int t = (int)(r % T);
+        const int b = (int)(r / T);
+        int p = 0;
+        while (t >= rs.first_table[p + 1]) ++p;
+        const int tp = rs.first_table[p + 1] - rs.first_table[p];
+        // chunk p starts at lb*first_table[p]*D and is [lb, tp, D]
+        float* c = chunks + ((int64_t)lb * rs.first_table[p] + (int64_t)b * tp + (t - rs.first_table[p])) * D + d * VEC;
+        float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * D + d * VEC;
+        RowVec<VEC> v;
+        if (dir == 0) { v.load(c); v.store(f); }
+        else          { v.load(f); v.store(c); }
+    }
+}
+
+static int a2a_layout(float* chunks, float* block, int64_t bsb, int feat_off, int W, const int* tpr, int lb,
+                      int D, int dir, dlrmx_stream_t stream) {
+    DLRMX_REQUIRE(W >= 1 && W <= kMaxRanks, "a2a layout: W=%d out of range", W);
+    DLRMX_REQUIRE(lb >= 0 && D >= 1, "a2a layout: bad sizes");
+    RankSplit rs;
+    rs.W = W;
+    rs.first_table[0] = 0;
+    for (int p = 0; p < W; ++p) {
+        DLRMX_REQUIRE(tpr[p] >= 0, "a2a layout: negative table count");
+        rs.first_table[p + 1] = rs.first_table[p] + tpr[p];
+    }
+    const int T = rs.first_table[W];
+    if (lb == 0 || T == 0) return DLRMX_OK;
+    const bool vec = (D % 4 == 0) && (bsb % 4 == 0) && (((uintptr_t)chunks | (uintptr_t)block) & 15) == 0;
+    const int64_t total = (int64_t)lb * T * (vec ? D / 4 : D);
+    int64_t nblk = ceil_div(total, 256);
+    if (nblk > (int64_t)kSMs * 16) nblk = (int64_t)kSMs * 16;
+    const unsigned blocks = (unsigned)nblk;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (vec) a2a_layout_kernel<4><<<blocks, 256, 0, st>>>(chunks, block, bsb, feat_off, rs, lb, D, dir);
+    else     a2a_layout_kernel<1><<<blocks, 256, 0, st>>>(chunks, block, bsb, feat_off, rs, lb, D, dir);
+    return check_launch(dir == 0 ? "a2a_unpack" : "a2a_pack_grad");
+}
+
+}  // namespace dlrmx
+
+extern "C" {
+int dlrmx_a2a_unpack(const float* recv, int W, const int* host_tables_per_rank, int lb, int D, float* dst,
+                     int64_t dst_stride_b, int feat_off, dlrmx_stream_t stream) {
+    return dlrmx::a2a_layout(const_cast<float*>(recv), dst, dst_stride_b, feat_off, W, host_tables_per_rank, lb, D, 0,
+                             stream);
+}
+int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+                        const int* host_tables_per_rank, int lb, int D, float* send, dlrmx_stream_t stream) {
+    return dlrmx::a2a_layout(send, const_cast<float*>(dfeat), dfeat_stride_b, feat_off, W, host_tables_per_rank, lb, D,
+                             1, stream);
+}
+}

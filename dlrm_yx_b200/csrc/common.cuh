@@ -1,0 +1,113 @@
+// Shared helpers for libdlrmx (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <atomic>
+
+#include "../../include/dlrmx.h"
+
+namespace dlrmx {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<int64_t> g_launches;
+
+inline int check_launch(const char* what) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return DLRMX_E_CUDA;
+    }
+    return DLRMX_OK;
+}
+
+#define DLRMX_REQUIRE(cond, ...)           \
+    do {                                   \
+        if (!(cond)) {                     \
+            dlrmx::set_error(__VA_ARGS__); \
+            return DLRMX_E_ARG;            \
+        }                                  \
+    } while (0)
+
+constexpr int kSMs = 148;  // B200
+
+// Experiment knobs (dlrmx_set_tunable); 0 = default.
+enum { DLRMX_TUNE_FWD_K = 0, DLRMX_TUNE_BWD_K = 1, DLRMX_TUNE_COUNT = 8 };
+int get_tunable(int which);
+
+__host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---- vector access ---------------------------------------------------------------------------
+// Rows of the big tables are read exactly once per step: keep them out of L1 and mark them
+// evict-first in L2 so the pooled outputs / gradients (re-read by the next kernel) stay resident.
+template <int VEC>
+struct RowVec;
+
+template <>
+struct RowVec<4> {
+    float4 v;
+    __device__ __forceinline__ void zero() { v = make_float4(0.f, 0.f, 0.f, 0.f); }
+    __device__ __forceinline__ void load_stream(const float* p) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "l"(p));
+    }
+    __device__ __forceinline__ void load(const float* p) { v = *reinterpret_cast<const float4*>(p); }
+    __device__ __forceinline__ void load_ro(const float* p) { v = __ldg(reinterpret_cast<const float4*>(p)); }
+    __device__ __forceinline__ void load_unaligned(const float* p) { v = make_float4(p[0], p[1], p[2], p[3]); }
+    __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = v; }
+    __device__ __forceinline__ void add(const RowVec& o) {
+        v.x = __fadd_rn(v.x, o.v.x); v.y = __fadd_rn(v.y, o.v.y);
+        v.z = __fadd_rn(v.z, o.v.z); v.w = __fadd_rn(v.w, o.v.w);
+    }
+    __device__ __forceinline__ void add_scaled(const RowVec& o, float w) {  // acc + (row*w), two roundings
+        v.x = __fadd_rn(v.x, __fmul_rn(o.v.x, w)); v.y = __fadd_rn(v.y, __fmul_rn(o.v.y, w));
+        v.z = __fadd_rn(v.z, __fmul_rn(o.v.z, w)); v.w = __fadd_rn(v.w, __fmul_rn(o.v.w, w));
+    }
+    __device__ __forceinline__ float sumsq() const {
+        return __fadd_rn(__fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y)),
+                         __fadd_rn(__fmul_rn(v.z, v.z), __fmul_rn(v.w, v.w)));
+    }
+    template <typename F>
+    __device__ __forceinline__ void map(const RowVec& g, F f) {  // v = f(v, g) elementwise
+        v.x = f(v.x, g.v.x); v.y = f(v.y, g.v.y); v.z = f(v.z, g.v.z); v.w = f(v.w, g.v.w);
+    }
+};
+
+template <>
+struct RowVec<1> {
+    float v;
+    __device__ __forceinline__ void zero() { v = 0.f; }
+    __device__ __forceinline__ void load_stream(const float* p) { v = __ldg(p); }
+    __device__ __forceinline__ void load(const float* p) { v = *p; }
+    __device__ __forceinline__ void load_ro(const float* p) { v = __ldg(p); }
+    __device__ __forceinline__ void load_unaligned(const float* p) { v = *p; }
+    __device__ __forceinline__ void store(float* p) const { *p = v; }
+    __device__ __forceinline__ void add(const RowVec& o) { v = __fadd_rn(v, o.v); }
+    __device__ __forceinline__ void add_scaled(const RowVec& o, float w) { v = __fadd_rn(v, __fmul_rn(o.v, w)); }
+    __device__ __forceinline__ float sumsq() const { return __fmul_rn(v, v); }
+    template <typename F>
+    __device__ __forceinline__ void map(const RowVec& g, F f) { v = f(v, g.v); }
+};
+
+// Lane geometry for a row of D floats: groups of G lanes (power of two <= 32), each lane owning CH
+// vectors of VEC floats at columns (lane + c*G)*VEC.
+struct RowGeom {
+    int vec, g, ch;
+};
+inline bool row_geometry(int D, RowGeom* out) {
+    if (D <= 0) return false;
+    int vec = (D % 4 == 0) ? 4 : 1;
+    int nv = D / vec;
+    int g = 1;
+    while (g < nv && g < 32) g <<= 1;
+    int ch = (nv + g - 1) / g;
+    if (ch > 4) return false;
+    if (ch == 3) ch = 4;
+    out->vec = vec; out->g = g; out->ch = ch;
+    return true;
+}
+
+}  // namespace dlrmx

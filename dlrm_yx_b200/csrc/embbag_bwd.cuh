@@ -1,0 +1,94 @@
+// Backward step 3: segmented reduce of pooled-row gradients over runs of equal (sorted) row ids, with
+// the sparse optimizer update fused into the same pass.  sm_100a.
+//
+// Replaces EmbeddingBag.backward (sparse COO grad, one [D] entry per looked-up index) followed by
+// torch.optim.SGD.step on sparse grads (dlrm_s_pytorch.py:1640, 1933) or RWSAdagrad.step's sparse
+// branch (optim/rwsadagrad.py:97-113: coalesce, mom[r] += mean_d(g^2), W[r] -= clr*g/(sqrt(mom[r])+eps)).
+//
+// Work decomposition is by SORTED POSITION, not by row: a group of G = D/4 lanes owns one segment of
+// 32 consecutive sorted positions, whatever runs they contain.  That keeps the load balanced under the
+// Criteo skew (3-row tables with ~11 K duplicates per row next to 40 M-row tables with none):
+//   * runs that start and end inside the segment are reduced in registers and the table row is
+//     updated on the spot (read W row, read accumulator, write both) -- the common case;
+//   * a run that crosses a segment boundary leaves per-segment partial sums (head/tail partials) and is
+//     finished by `bwd_fixup_kernel`: the segment where the run STARTS adds the partials of the
+//     following segments in ascending order and applies the update.  Fixed order -> deterministic.
+// Within a batch of K positions the K gradient rows and the W rows of the runs ending there are all
+// issued before any is consumed (K 16-B loads in flight per lane); run boundaries come from comparing
+// adjacent keys (group-uniform broadcast loads, no run-offset array needed).
+// HBM-bound: algorithmic bytes = T*B*D*4 (pooled-row gradients, re-reads hit L2) + N*8 (key, bag)
+//            + 2*U*D*4 (table rows RMW) [+ 2*U*4 accumulators].
+#pragma once
+#include "common.cuh"
+
+namespace dlrmx {
+
+constexpr int kSeg = 32;  // sorted positions per group
+
+struct BwdParams {
+    int optimizer;
+    float* const* tables;
+    float* const* moms;
+    const int64_t* row_base;
+    int B, D;
+    const float* grad;
+    int64_t stride_b, stride_t;
+    const uint32_t* skey;
+    const int32_t* sbag;
+    int64_t N, nseg;
+    float lr, eps;
+    float* head_partial;  // [nseg, D]
+    float* tail_partial;  // [nseg, D]
+};
+
+template <int G>
+__device__ __forceinline__ unsigned group_mask() {
+    if constexpr (G == 32) {
+        return 0xffffffffu;
+    } else {
+        return ((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1));
+    }
+}
+
+// One table row: w <- optimizer(w, acc).  `w` was loaded by the caller (prefetched), m_old likewise.
+template <int VEC, int G, int CH>
+__device__ __forceinline__ void apply_row(const BwdParams& P, float* wp, float* mp, float m_old,
+                                          RowVec<VEC> (&w)[CH], const RowVec<VEC> (&acc)[CH], int col0) {
+    if (P.optimizer == DLRMX_OPT_SGD) {
+        const float a = -P.lr;
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+            if (CH == 1 || col0 + c * G * VEC < P.D) {
+                w[c].map(acc[c], [a](float wv, float gv) { return __fmaf_rn(a, gv, wv); });
+                w[c].store(wp + c * G * VEC);
+            }
+    } else {
+        float ss = 0.f;
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+            if (col0 + c * G * VEC < P.D) ss = __fadd_rn(ss, acc[c].sumsq());
+        const unsigned m = group_mask<G>();
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) ss = __fadd_rn(ss, __shfl_xor_sync(m, ss, o));
+        const float mom = __fadd_rn(m_old, __fdiv_rn(ss, (float)P.D));
+        const float stdv = __fadd_rn(__fsqrt_rn(mom), P.eps);
+        const float a = -P.lr;
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+            if (CH == 1 || col0 + c * G * VEC < P.D) {
+                w[c].map(acc[c], [a, stdv](float wv, float gv) { return __fmaf_rn(a, __fdiv_rn(gv, stdv), wv); });
+                w[c].store(wp + c * G * VEC);
+            }
+        if ((threadIdx.x & (G - 1)) == 0) *mp = mom;
+    }
+}
+
+template <int VEC, int G, int CH>
+__device__ __forceinline__ void store_partial(float* base, int64_t seg, int D, int col0,
+                                              const RowVec<VEC> (&acc)[CH]) {
+    float* p = base + seg * D + col0;
+#pragma unroll
+    for (int c = 0; c < CH; ++c)
+        if (CH == 1 || col0 + c * G * VEC < D) acc[c].store(p + c * G * VEC);
+}
+}  // namespace dlrmx

@@ -1,0 +1,219 @@
+"""Thin tensor-level wrappers over the C ABI (include/dlrmx.h).  PyTorch is plumbing here: device
+memory, the current stream and autograd hooks; all arithmetic is in libdlrmx.so.  Nothing in this
+module has a CPU path -- CPU tensors raise.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.DlrmxError("dlrm_yx_b200 kernels need CUDA tensors (no CPU fallback); got a %s tensor"
+                                  % t.device)
+
+
+class TableSet:
+    """A group of embedding tables that are looked up / updated together by one kernel launch.
+
+    Holds the device-side pointer arrays the C ABI takes: table base pointers, row counts, the exclusive
+    row prefix (global row ids for the sorted backward) and, for RWSAdagrad, accumulator pointers.
+    Tables stay ordinary [rows_t, D] fp32 tensors (state_dict / checkpoint compatible:
+    SURVEY.md section 5) -- the arrays are rebuilt whenever a tensor's storage moves.
+    """
+
+    def __init__(self, weights, moms=None):
+        self.weights = list(weights)
+        self.moms = None if moms is None else list(moms)
+        self._key = None
+        self.refresh()
+
+    def refresh(self):
+        ws = self.weights
+        key = tuple(w.data_ptr() for w in ws) + tuple(() if self.moms is None else (m.data_ptr() for m in self.moms))
+        if key == self._key:
+            return
+        _need_cuda(*ws)
+        D = ws[0].shape[1]
+        for w in ws:
+            if w.dtype != torch.float32 or w.dim() != 2 or w.shape[1] != D or not w.is_contiguous():
+                raise _lib.DlrmxError("tables must be contiguous fp32 [rows, D] with a common D")
+        dev = ws[0].device
+        self.device, self.D, self.T = dev, D, len(ws)
+        rows = [int(w.shape[0]) for w in ws]
+        base = [0]
+        for r in rows:
+            base.append(base[-1] + r)
+        self.total_rows = base[-1]
+        self.rows = rows
+        self.table_ptrs = torch.tensor([w.data_ptr() for w in ws], dtype=torch.int64, device=dev)
+        self.table_rows = torch.tensor(rows, dtype=torch.int64, device=dev)
+        self.row_base = torch.tensor(base, dtype=torch.int64, device=dev)
+        self.mom_ptrs = None
+        if self.moms is not None:
+            _need_cuda(*self.moms)
+            self.mom_ptrs = torch.tensor([m.data_ptr() for m in self.moms], dtype=torch.int64, device=dev)
+        self._key = key
+
+
+def _idx_suffix(indices, offsets):
+    if indices.dtype != offsets.dtype or indices.dtype not in (torch.int32, torch.int64):
+        raise _lib.DlrmxError("indices and offsets must both be int32 or both int64")
+    return "i32" if indices.dtype == torch.int32 else "i64"
+
+
+def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_t=None,
+                   per_sample_weights=None, err_flag=None, validate=True):
+    """Pooled rows of every bag (t, b).  Default output layout [B, T, D] (the batched module's,
+    dlrm_s_pytorch.py:589-591); pass out/stride_b/stride_t to write elsewhere (e.g. features 1.. of the
+    [B, 1+T, D] interaction input)."""
+    tables.refresh()
+    _need_cuda(indices, offsets, per_sample_weights, out)
+    indices = indices.contiguous()
+    offsets = offsets.contiguous()
+    T, D = tables.T, tables.D
+    if offsets.numel() < T * B:
+        raise _lib.DlrmxError("offsets has %d entries, need at least T*B = %d" % (offsets.numel(), T * B))
+    if out is None:
+        out = torch.empty((B, T, D), dtype=torch.float32, device=tables.device)
+        stride_b, stride_t = T * D, D
+    fn = getattr(_lib.load(), "dlrmx_embbag_fwd_" + _idx_suffix(indices, offsets))
+    rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0,
+            indices.data_ptr(), offsets.data_ptr(), indices.numel(), T, B, D, _ptr(per_sample_weights),
+            out.data_ptr(), stride_b, stride_t, _ptr(err_flag), _stream())
+    _lib.check(rc, "dlrmx_embbag_fwd")
+    return out
+
+
+def bwd_sort(tables, indices, offsets, B):
+    """(sorted_key uint32-as-int32 tensor [N], sorted_bag int32 [N]): global row ids of all looked-up
+    indices, stably sorted, with the bag each one came from."""
+    tables.refresh()
+    _need_cuda(indices, offsets)
+    indices = indices.contiguous()
+    offsets = offsets.contiguous()
+    N = indices.numel()
+    lib = _lib.load()
+    dev = tables.device
+    skey = torch.empty(N, dtype=torch.int32, device=dev)   # bit pattern is uint32
+    sbag = torch.empty(N, dtype=torch.int32, device=dev)
+    wsb = lib.dlrmx_bwd_sort_workspace_bytes(N, tables.T * B)
+    ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=dev)
+    fn = getattr(lib, "dlrmx_bwd_sort_" + _idx_suffix(indices, offsets))
+    rc = fn(indices.data_ptr(), offsets.data_ptr(), N, tables.T, B, tables.row_base.data_ptr(),
+            tables.total_rows, skey.data_ptr(), sbag.data_ptr(), ws.data_ptr(), wsb, _stream())
+    _lib.check(rc, "dlrmx_bwd_sort")
+    return skey, sbag
+
+
+def bwd_segments(skey):
+    """(unique_key [N], run_off [N+1], num_unique [1]) on device; only the first num_unique(+1) entries
+    are meaningful."""
+    _need_cuda(skey)
+    N = skey.numel()
+    lib = _lib.load()
+    dev = skey.device
+    uniq = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+    run_off = torch.empty(N + 1, dtype=torch.int32, device=dev)
+    nuniq = torch.empty(1, dtype=torch.int32, device=dev)
+    wsb = lib.dlrmx_bwd_segments_workspace_bytes(N)
+    ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=dev)
+    rc = lib.dlrmx_bwd_segments(skey.data_ptr(), N, uniq.data_ptr(), run_off.data_ptr(), nuniq.data_ptr(),
+                                ws.data_ptr(), wsb, _stream())
+    _lib.check(rc, "dlrmx_bwd_segments")
+    return uniq, run_off, nuniq
+
+
+def bwd_update(tables, optimizer, grad, stride_b, stride_t, B, skey, sbag, lr, eps=0.0):
+    """Fused segmented reduce + sparse optimizer update of the touched table rows (in place)."""
+    tables.refresh()
+    _need_cuda(grad, skey, sbag)
+    N = skey.numel()
+    lib = _lib.load()
+    if optimizer == _lib.OPT_RWSADAGRAD and tables.mom_ptrs is None:
+        raise _lib.DlrmxError("RWSAdagrad update needs row-wise accumulators (TableSet(moms=...))")
+    wsb = lib.dlrmx_bwd_update_workspace_bytes(N, tables.D)
+    ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=tables.device)
+    rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(), _ptr(tables.mom_ptrs),
+                              tables.row_base.data_ptr(), tables.T, B, tables.D, grad.data_ptr(), stride_b,
+                              stride_t, skey.data_ptr(), sbag.data_ptr(), N, float(lr), float(eps),
+                              ws.data_ptr(), wsb, _stream())
+    _lib.check(rc, "dlrmx_bwd_update")
+
+
+def bwd_coalesce(grad, stride_b, stride_t, B, D, sbag, run_off, nuniq, max_unique=None):
+    """Coalesced gradient rows [N, D] (first num_unique valid) for the non-fused parity seam."""
+    _need_cuda(grad, sbag, run_off, nuniq)
+    N = sbag.numel()
+    gsum = torch.empty((max(N, 1), D), dtype=torch.float32, device=grad.device)
+    rc = _lib.load().dlrmx_bwd_coalesce(B, D, grad.data_ptr(), stride_b, stride_t, sbag.data_ptr(),
+                                        run_off.data_ptr(), nuniq.data_ptr(), N, gsum.data_ptr(), _stream())
+    _lib.check(rc, "dlrmx_bwd_coalesce")
+    return gsum
+
+
+def tri_count(F, itself=False):
+    return F * (F + 1) // 2 if itself else F * (F - 1) // 2
+
+
+def interact_dot_fwd(feat, itself=False, out=None):
+    """feat [B, F, D] (sample stride may exceed F*D) -> [B, D + F(F-1)/2]."""
+    _need_cuda(feat, out)
+    B, F, D = feat.shape
+    if feat.stride(2) != 1 or feat.stride(1) != D:
+        raise _lib.DlrmxError("feat must be [B, F, D] with contiguous F x D blocks")
+    if out is None:
+        out = torch.empty((B, D + tri_count(F, itself)), dtype=torch.float32, device=feat.device)
+    rc = _lib.load().dlrmx_interact_dot_fwd(feat.data_ptr(), feat.stride(0), B, F, D, int(itself),
+                                            out.data_ptr(), out.stride(0), _stream())
+    _lib.check(rc, "dlrmx_interact_dot_fwd")
+    return out
+
+
+def interact_dot_bwd(feat, dout, itself=False, dfeat=None):
+    _need_cuda(feat, dout, dfeat)
+    B, F, D = feat.shape
+    if dout.stride(1) != 1:
+        dout = dout.contiguous()
+    if dfeat is None:
+        dfeat = torch.empty((B, F, D), dtype=torch.float32, device=feat.device)
+    rc = _lib.load().dlrmx_interact_dot_bwd(feat.data_ptr(), feat.stride(0), B, F, D, int(itself),
+                                            dout.data_ptr(), dout.stride(0), dfeat.data_ptr(),
+                                            dfeat.stride(0), _stream())
+    _lib.check(rc, "dlrmx_interact_dot_bwd")
+    return dfeat
+
+
+def _int_array(values):
+    return (ctypes.c_int * len(values))(*[int(v) for v in values])
+
+
+def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):
+    """recv = concat_p [lb, T_p, D]  ->  dst[:, feat_off + t, :] (rank-major table order)."""
+    _need_cuda(recv, dst)
+    rc = _lib.load().dlrmx_a2a_unpack(recv.data_ptr(), len(tables_per_rank), _int_array(tables_per_rank), lb, D,
+                                      dst.data_ptr(), dst.stride(0), feat_off, _stream())
+    _lib.check(rc, "dlrmx_a2a_unpack")
+    return dst
+
+
+def a2a_pack_grad(dfeat, feat_off, tables_per_rank, lb, D, send=None):
+    _need_cuda(dfeat, send)
+    T = sum(int(t) for t in tables_per_rank)
+    if send is None:
+        send = torch.empty(lb * T * D, dtype=torch.float32, device=dfeat.device)
+    rc = _lib.load().dlrmx_a2a_pack_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
+                                         _int_array(tables_per_rank), lb, D, send.data_ptr(), _stream())
+    _lib.check(rc, "dlrmx_a2a_pack_grad")
+    return send

@@ -1,0 +1,173 @@
+/*
+ * dlrmx.h -- C ABI of libdlrmx.so, the B200 (sm_100a) sparse hot path for DLRM.
+ *
+ * This is the drop-in boundary.  The reference's only native interface for this
+ * path is the torch op of yx_modfs:
+ *     TORCH_LIBRARY(batched_forward, m) { m.def("forward", &batched_embedding_forward_cuda); }
+ *         -- yx_modfs/batched_forward.cpp:4-13, kernel yx_modfs/table_batched_embeddings_cuda_yx.cu:251-389
+ * and everything else on the path is reached through Python call sites of dlrm_s_pytorch.py /
+ * optim/rwsadagrad.py / extend_distributed.py.  Every entry point below names the reference
+ * interface it replaces.  The Python host layer (dlrm_yx_b200/*.py) binds these with ctypes and
+ * re-creates the reference-facing names (torch.ops.batched_forward.forward, nn.EmbeddingBag-like
+ * module, TableBatchedEmbeddingBags, interact_features, RWSAdagrad, alltoall).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all data pointers are DEVICE pointers unless named host_*;
+ *   - `stream` is a cudaStream_t passed as void*; every call is stream-ordered and non-blocking,
+ *     never switches device, never allocates (workspace sizes are queried and passed in);
+ *   - return 0 on success, a negative DLRMX_E_* code on failure; dlrmx_last_error() gives the text;
+ *   - "bag" (t,b) = lookup b of table t, bag id = t*B + b (table-major, the packed layout of
+ *     dlrm_data_pytorch.py:748-753);  offsets[bag] is the first index position of the bag, its end
+ *     is offsets[bag+1] for bag+1 < T*B and N (the index count) for the last bag -- which is both the
+ *     nn.EmbeddingBag rule (dlrm_s_pytorch.py:571-577) and the T*B+1 packed rule;
+ *   - pooled rows / their gradients are addressed as  base + b*stride_b + t*stride_t  (in floats),
+ *     so the same kernels write [B,T,D], [T,B,D] or straight into the [B,1+T,D] interaction input.
+ */
+#ifndef DLRMX_H_
+#define DLRMX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLRMX_VERSION 100
+
+#define DLRMX_OK 0
+#define DLRMX_E_ARG (-1)      /* bad argument (shape / alignment / unsupported D) */
+#define DLRMX_E_CUDA (-2)     /* CUDA runtime error at launch */
+#define DLRMX_E_WORKSPACE (-3)/* workspace too small */
+
+typedef void* dlrmx_stream_t;
+
+/* Sparse optimizers fused into the backward (dlrm_s_pytorch.py:1639-1666). */
+#define DLRMX_OPT_SGD 0        /* torch.optim.SGD on sparse grads: W[r] += -lr * g[r]            */
+#define DLRMX_OPT_RWSADAGRAD 1 /* optim/rwsadagrad.py:95-113: row-wise accumulator                */
+
+int dlrmx_version(void);
+const char* dlrmx_last_error(void);
+/* Number of kernels launched by this library since load (bench.py's gpu_launches claim). */
+int64_t dlrmx_launch_count(void);
+/* Experiment knobs for kernel-variant sweeps (0 = default): which 0 = forward bags-in-lockstep K
+ * (4 or 8), 1 = backward positions-in-flight.  Not part of the reference-facing surface. */
+int dlrmx_set_tunable(int which, int value);
+
+/* ---------------------------------------------------------------------------------------------
+ * Forward: table-batched embedding-bag sum pooling.
+ * Replaces nn.EmbeddingBag(mode="sum").forward as called by DLRM_Net.apply_emb
+ * (dlrm_s_pytorch.py:526-587), TableBatchedEmbeddingBags.forward (dlrm_s_pytorch.py:589-591) and
+ * batched_embedding_forward_cuda (yx_modfs/table_batched_embeddings_cuda_yx.cu:317-389).
+ *   tables      [T] device array of row-major fp32 table base pointers ([rows_t, D] each, 16-B aligned
+ *               when D % 4 == 0)
+ *   table_rows  [T] device int64 row counts, or NULL to skip index validation
+ *   indices     [N] row ids local to their table; offsets [>= T*B] bag starts (see conventions)
+ *   psw         [N] per-sample weights (dlrm_s_pytorch.py:544-547) or NULL
+ *   out         pooled rows, fp32, written for every bag (empty bag -> zeros)
+ *   err_flag    device int, or NULL; bit 0 is set if an index is outside [0, rows_t)
+ * Sum order: sequential in index order, plain fp32 adds (bit-exact with ATen's EmbeddingBag).
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows,
+                         const int32_t* indices, const int32_t* offsets, int64_t N,
+                         int T, int B, int D, const float* psw,
+                         float* out, int64_t stride_b, int64_t stride_t,
+                         int* err_flag, dlrmx_stream_t stream);
+int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows,
+                         const int64_t* indices, const int64_t* offsets, int64_t N,
+                         int T, int B, int D, const float* psw,
+                         float* out, int64_t stride_b, int64_t stride_t,
+                         int* err_flag, dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Backward, step 1: sort the looked-up rows.
+ * Replaces what EmbeddingBag backward + grad.coalesce() do implicitly (sparse COO gradient with
+ * one entry per looked-up index, then sort + merge: optim/rwsadagrad.py:98); no [N,D] gradient
+ * expansion is ever materialised.
+ *   key[p]  = table_row_base[t(p)] + indices[p]   (global row id, uint32: sum of rows < 2^32)
+ *   bag[p]  = t(p)*B + b(p)
+ * sorted by key with an LSD radix sort (8-bit digits, only ceil(log2(total_rows)/8) passes), STABLE
+ * in p -- identical to torch.sort(stable=True) on the keys.
+ *   table_row_base  [T+1] device int64 exclusive prefix of the table row counts
+ *   total_rows      host copy of table_row_base[T]
+ *   sorted_key [N] uint32, sorted_bag [N] int32: outputs
+ * ------------------------------------------------------------------------------------------- */
+size_t dlrmx_bwd_sort_workspace_bytes(int64_t N, int64_t total_bags);
+int dlrmx_bwd_sort_i32(const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
+                       const int64_t* table_row_base, int64_t total_rows,
+                       uint32_t* sorted_key, int32_t* sorted_bag,
+                       void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+int dlrmx_bwd_sort_i64(const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
+                       const int64_t* table_row_base, int64_t total_rows,
+                       uint32_t* sorted_key, int32_t* sorted_bag,
+                       void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+
+/* Backward, step 2 (only needed by the non-fused "parity seam" and the tests): run-length
+ * structure of the sorted keys.
+ *   unique_key [N] (first num_unique valid), run_off [N+1] (first num_unique+1 valid; run u covers
+ *   sorted positions [run_off[u], run_off[u+1])), num_unique: device int32[1].
+ * These integer arrays are the bit-exact contract against sort/unique_consecutive. */
+size_t dlrmx_bwd_segments_workspace_bytes(int64_t N);
+int dlrmx_bwd_segments(const uint32_t* sorted_key, int64_t N,
+                       uint32_t* unique_key, int32_t* run_off, int32_t* num_unique,
+                       void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Backward, step 3 (fused): segmented reduce of the pooled-row gradients over each run of equal
+ * keys + the sparse optimizer update of that table row, one pass.
+ * Replaces EmbeddingBag.backward + torch.optim.SGD.step (dlrm_s_pytorch.py:1640, 1933) and
+ * RWSAdagrad.step's sparse branch (optim/rwsadagrad.py:97-113).
+ *   grad        gradient of the pooled rows, addressed like `out` of the forward
+ *   psw         per-sample weights [N] indexed by ORIGINAL position -- not supported when fused: NULL
+ *   moms        [T] device array of row-wise accumulator pointers ([rows_t] fp32), RWSADAGRAD only
+ *   lr          SGD: lr.  RWSADAGRAD: clr = lr / (1 + (step-1)*lr_decay), computed by the caller
+ * Deterministic: each run is summed in sorted (stable) order; runs longer than one 32-position
+ * segment are reduced per segment and the segment partials added in ascending order.
+ * ------------------------------------------------------------------------------------------- */
+size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D);
+int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms,
+                     const int64_t* table_row_base, int T, int B, int D,
+                     const float* grad, int64_t stride_b, int64_t stride_t,
+                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N,
+                     float lr, float eps,
+                     void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+
+/* Non-fused variant: emits the coalesced gradient rows  gsum[u,:] = sum over run u  ([num_unique, D],
+ * row stride D) so that the reference's own optimizers can consume a coalesced sparse COO gradient
+ * ("parity seam").  Needs run_off/num_unique from dlrmx_bwd_segments. */
+int dlrmx_bwd_coalesce(int B, int D, const float* grad, int64_t stride_b, int64_t stride_t,
+                       const int32_t* sorted_bag, const int32_t* run_off,
+                       const int32_t* num_unique, int64_t N, float* gsum, dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Dot / cat feature interaction.  Replaces DLRM_Net.interact_features (dlrm_s_pytorch.py:627-673):
+ *   feat   [B, F, D] fp32 (feature 0 = bottom-MLP output x, features 1.. = pooled embeddings), row
+ *          stride feat_stride_b floats -- the forward kernel above writes pooled rows straight into it;
+ *   out    [B, out_stride] fp32:  out[b, 0:D] = x[b];  out[b, D + k] = <feat[b,li[k]], feat[b,lj[k]]>
+ *          with (li,lj) = tril_indices(F, F, itself ? 0 : -1) in row-major order (dlrm_s_pytorch.py:646-656).
+ * Backward: dfeat[b,i,:] = sum_j (dZ[i,j] + dZ[j,i]) feat[b,j,:]  (+ dout[b,0:D] on feature 0).
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_interact_dot_fwd(const float* feat, int64_t feat_stride_b, int B, int F, int D, int itself,
+                           float* out, int64_t out_stride, dlrmx_stream_t stream);
+int dlrmx_interact_dot_bwd(const float* feat, int64_t feat_stride_b, int B, int F, int D, int itself,
+                           const float* dout, int64_t dout_stride,
+                           float* dfeat, int64_t dfeat_stride_b, dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Model-parallel exchange helpers.  Replaces the cat / split / contiguous copies around
+ * dist.all_to_all_single in extend_distributed.py:405-508 (All2All_Req / All2All_Wait).
+ * a2a_unpack: recv buffer = concat over source ranks p of [lb, T_p, D]  ->  dst [lb, F, D] features
+ *             feat_off + (rank-major table order), i.e. straight into the interaction input.
+ * a2a_pack_grad: the transpose, dfeat [lb, F, D] -> send buffer concat over p of [lb, T_p, D].
+ *   tables_per_rank: HOST int array [W].
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_a2a_unpack(const float* recv, int W, const int* host_tables_per_rank, int lb, int D,
+                     float* dst, int64_t dst_stride_b, int feat_off, dlrmx_stream_t stream);
+int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+                        const int* host_tables_per_rank, int lb, int D,
+                        float* send, dlrmx_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLRMX_H_ */

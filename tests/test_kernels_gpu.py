@@ -1,0 +1,235 @@
+"""GPU parity tests of the raw kernels (through the C ABI) against the numpy oracle.
+
+Bars: pooled forward outputs, sort order, unique rows and run offsets are BIT-EXACT; gradients, updated
+rows, accumulators and interactions within rtol 1e-5 / atol 1e-6 (summation order differs), as stated
+in SURVEY.md 8c.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_np as O
+
+pytestmark = pytest.mark.gpu
+
+
+def cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+def make_case(rng, rows, D, B, max_len, fixed_len=None, empty_frac=0.0, hot=False):
+    """Random packed lookups: returns (Ws, indices int64, offsets int64 [T*B+1])."""
+    T = len(rows)
+    Ws = [rng.uniform(-1, 1, size=(r, D)).astype(np.float32) for r in rows]
+    idx, off = [], [0]
+    for t in range(T):
+        for b in range(B):
+            if fixed_len is not None:
+                L = fixed_len
+            else:
+                L = int(rng.integers(0, max_len + 1))
+                if rng.random() < empty_frac:
+                    L = 0
+            if hot:
+                ids = np.minimum(rng.zipf(1.3, size=L) - 1, rows[t] - 1)
+            else:
+                ids = rng.integers(0, rows[t], size=L)
+            idx.extend(ids.tolist())
+            off.append(len(idx))
+    return Ws, np.array(idx, dtype=np.int64), np.array(off, dtype=np.int64)
+
+
+def to_dev(Ws, idx, off, dev, dtype):
+    from dlrm_yx_b200 import ops
+    tw = [torch.from_numpy(w.copy()).to(dev) for w in Ws]
+    ts = ops.TableSet(tw)
+    return ts, torch.from_numpy(idx).to(dev).to(dtype), torch.from_numpy(off).to(dev).to(dtype)
+
+
+@pytest.mark.parametrize("D", [128, 64, 16, 2, 3, 256, 96, 8])
+@pytest.mark.parametrize("dtype", [torch.int32, torch.int64])
+def test_forward_bit_exact(D, dtype):
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(D * 7 + 1)
+    rows = [50, 3, 1, 200, 17]
+    B = 37
+    Ws, idx, off = make_case(rng, rows, D, B, max_len=9, empty_frac=0.2)
+    ts, di, do = to_dev(Ws, idx, off, dev, dtype)
+    out = ops.embbag_forward(ts, di, do, B)
+    ref = O.embbag_fwd_batched(Ws, idx, off, B)
+    assert np.array_equal(out.cpu().numpy(), ref)
+    # same lookups without the trailing sentinel (nn.EmbeddingBag offsets rule: last bag runs to N)
+    out2 = ops.embbag_forward(ts, di, do[:-1].contiguous(), B)
+    assert np.array_equal(out2.cpu().numpy(), ref)
+
+
+def test_forward_one_index_per_bag_and_strided_output():
+    """Criteo layout (L=1, offsets = arange) written straight into a [B, 1+T, D] interaction buffer."""
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(5)
+    rows, D, B = [1000, 7, 333, 4], 128, 300
+    Ws, idx, off = make_case(rng, rows, D, B, max_len=1, fixed_len=1)
+    ts, di, do = to_dev(Ws, idx, off, dev, torch.int32)
+    T = len(rows)
+    feat = torch.full((B, 1 + T, D), -7.0, device=dev)
+    ops.embbag_forward(ts, di, do, B, out=feat[:, 1:, :], stride_b=(1 + T) * D, stride_t=D)
+    ref = O.embbag_fwd_batched(Ws, idx, off, B)
+    got = feat.cpu().numpy()
+    assert np.array_equal(got[:, 1:, :], ref)
+    assert np.all(got[:, 0, :] == -7.0)
+
+
+def test_forward_long_bags_and_weights():
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(11)
+    rows, D, B = [5000, 4000], 64, 33
+    Ws, idx, off = make_case(rng, rows, D, B, max_len=100, fixed_len=100)
+    ts, di, do = to_dev(Ws, idx, off, dev, torch.int64)
+    out = ops.embbag_forward(ts, di, do, B)
+    assert np.array_equal(out.cpu().numpy(), O.embbag_fwd_batched(Ws, idx, off, B))
+    psw = rng.uniform(0.5, 1.5, size=idx.size).astype(np.float32)
+    outw = ops.embbag_forward(ts, di, do, B, per_sample_weights=torch.from_numpy(psw).to(dev))
+    lS_o, lS_i = O.unpack_batched(idx, off, len(rows), B)
+    base = 0
+    refw = []
+    for t in range(len(rows)):
+        n = lS_i[t].size
+        refw.append(O.embbag_fwd_table(Ws[t], lS_i[t], lS_o[t], psw[base:base + n]))
+        base += n
+    assert np.array_equal(outw.cpu().numpy(), np.stack(refw, axis=1))
+
+
+def test_forward_flags_out_of_range_index():
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    Ws = [np.ones((4, 8), np.float32)]
+    ts, di, do = to_dev(Ws, np.array([1, 9, 2], np.int64), np.array([0, 1, 2, 3], np.int64), dev, torch.int64)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    out = ops.embbag_forward(ts, di, do, 3, err_flag=flag)
+    assert int(flag.item()) == 1
+    assert np.array_equal(out.cpu().numpy()[:, 0, 0], np.array([1, 0, 1], np.float32))
+
+
+@pytest.mark.parametrize("rows,B,max_len,hot", [
+    ([50, 3, 1, 200, 17], 61, 9, False),
+    ([300000, 5, 70000], 700, 6, True),       # > 2 radix passes, hot rows, several tiles
+    ([3], 5000, 1, False),                    # one tiny table: runs of thousands of duplicates
+    ([20000000, 40000000], 257, 3, False),    # 26-bit keys: 4 passes
+])
+@pytest.mark.parametrize("dtype", [torch.int32, torch.int64])
+def test_sort_and_segments_bit_exact(rows, B, max_len, hot, dtype):
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(len(rows) * 13 + B)
+    T = len(rows)
+    idx, off = [], [0]
+    for t in range(T):
+        for b in range(B):
+            L = int(rng.integers(0, max_len + 1))
+            ids = np.minimum(rng.zipf(1.2, size=L) - 1, rows[t] - 1) if hot else rng.integers(0, rows[t], size=L)
+            idx.extend(ids.tolist())
+            off.append(len(idx))
+    idx, off = np.array(idx, np.int64), np.array(off, np.int64)
+    base = np.concatenate([[0], np.cumsum(rows)])
+    art = O.sort_artifacts(idx, off, T, B, base[:-1])
+
+    class FakeTables:  # sort needs only the row prefix, not the tables themselves
+        pass
+    ts = FakeTables()
+    ts.T, ts.device, ts.total_rows = T, dev, int(base[-1])
+    ts.row_base = torch.from_numpy(base.astype(np.int64)).to(dev)
+    ts.refresh = lambda: None
+    skey, sbag = ops.bwd_sort(ts, torch.from_numpy(idx).to(dev).to(dtype), torch.from_numpy(off).to(dev).to(dtype), B)
+    got_key = skey.cpu().numpy().view(np.uint32).astype(np.int64)
+    assert np.array_equal(got_key, art["sorted_key"])
+    assert np.array_equal(sbag.cpu().numpy().astype(np.int64), art["sorted_bag"])
+    uniq, run_off, nu = ops.bwd_segments(skey)
+    U = int(nu.item())
+    assert U == art["unique"].size
+    assert np.array_equal(uniq.cpu().numpy().view(np.uint32)[:U].astype(np.int64), art["unique"])
+    assert np.array_equal(run_off.cpu().numpy()[:U + 1].astype(np.int64), art["run_off"])
+
+
+@pytest.mark.parametrize("D", [128, 64, 16, 2])
+@pytest.mark.parametrize("opt", ["sgd", "rwsadagrad"])
+def test_fused_backward_update(D, opt):
+    from dlrm_yx_b200 import ops, _lib
+    dev = cuda()
+    rng = np.random.default_rng(D + (0 if opt == "sgd" else 100))
+    rows, B = [400, 3, 1, 90, 2000], 257      # tiny tables -> runs crossing many 32-position segments
+    T = len(rows)
+    Ws, idx, off = make_case(rng, rows, D, B, max_len=4, empty_frac=0.1)
+    moms_np = [rng.uniform(0, 0.5, size=r).astype(np.float32) for r in rows]
+    tw = [torch.from_numpy(w.copy()).to(dev) for w in Ws]
+    tm = [torch.from_numpy(m.copy()).to(dev) for m in moms_np]
+    ts = ops.TableSet(tw, moms=tm)
+    di, do = torch.from_numpy(idx).to(dev).to(torch.int32), torch.from_numpy(off).to(dev).to(torch.int32)
+    grad = rng.normal(size=(B, T, D)).astype(np.float32)
+    dg = torch.from_numpy(grad).to(dev)
+    skey, sbag = ops.bwd_sort(ts, di, do, B)
+    lr, eps = 0.1, 1e-10
+    ops.bwd_update(ts, _lib.OPT_SGD if opt == "sgd" else _lib.OPT_RWSADAGRAD, dg, T * D, D, B, skey, sbag, lr, eps)
+
+    base = np.concatenate([[0], np.cumsum(rows)])
+    art = O.sort_artifacts(idx, off, T, B, base[:-1])
+    g = O.embbag_bwd_coalesced(O.go_rows(grad), art, D)
+    Wcat = np.concatenate(Ws, axis=0)
+    mom = np.concatenate(moms_np)
+    if opt == "sgd":
+        O.sgd_update(Wcat, art["unique"], g, lr)
+    else:
+        O.rwsadagrad_update(Wcat, mom, art["unique"], g, lr, eps)
+    got = np.concatenate([w.cpu().numpy() for w in tw], axis=0)
+    np.testing.assert_allclose(got, Wcat, rtol=1e-5, atol=1e-6)
+    untouched = np.ones(Wcat.shape[0], bool)
+    untouched[art["unique"]] = False
+    assert np.array_equal(got[untouched], np.concatenate(Ws, axis=0)[untouched])   # untouched rows bit-identical
+    if opt == "rwsadagrad":
+        np.testing.assert_allclose(np.concatenate([m.cpu().numpy() for m in tm]), mom, rtol=1e-5, atol=1e-7)
+
+    # non-fused parity seam: coalesced gradient rows
+    uniq, run_off, nu = ops.bwd_segments(skey)
+    gs = ops.bwd_coalesce(dg, T * D, D, B, D, sbag, run_off, nu)
+    U = int(nu.item())
+    np.testing.assert_allclose(gs.cpu().numpy()[:U], g, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (4, 2), (2, 8), (33, 32)])
+@pytest.mark.parametrize("itself", [False, True])
+def test_interaction_fwd_bwd(F, D, itself):
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(F * 100 + D)
+    B = 19
+    feat = rng.normal(size=(B, F, D)).astype(np.float32)
+    df = torch.from_numpy(feat).to(dev)
+    out = ops.interact_dot_fwd(df, itself)
+    ref = O.interact_dot(feat[:, 0, :], feat[:, 1:, :], itself)
+    np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=1e-5, atol=1e-5)
+    dR = rng.normal(size=ref.shape).astype(np.float32)
+    dfeat = ops.interact_dot_bwd(df, torch.from_numpy(dR).to(dev), itself)
+    dx, demb = O.interact_dot_bwd(feat[:, 0, :], feat[:, 1:, :], dR, itself)
+    np.testing.assert_allclose(dfeat.cpu().numpy(), np.concatenate([dx[:, None, :], demb], axis=1),
+                               rtol=1e-5, atol=2e-5)
+
+
+@pytest.mark.parametrize("D", [128, 6])
+def test_a2a_layout_roundtrip(D):
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(3)
+    tpr, lb = [1, 2, 6, 5], 13
+    T = sum(tpr)
+    chunks = [rng.normal(size=(lb, t, D)).astype(np.float32) for t in tpr]
+    recv = torch.from_numpy(np.concatenate([c.reshape(-1) for c in chunks])).to(dev)
+    feat = torch.zeros((lb, 1 + T, D), device=dev)
+    ops.a2a_unpack(recv, tpr, lb, D, feat, 1)
+    ref = np.concatenate(chunks, axis=1)
+    assert np.array_equal(feat.cpu().numpy()[:, 1:, :], ref)
+    send = ops.a2a_pack_grad(feat, 1, tpr, lb, D)
+    assert np.array_equal(send.cpu().numpy(), recv.cpu().numpy())
