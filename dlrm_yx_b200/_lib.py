@@ -37,6 +37,8 @@ SIGNATURES = {
                                  c_void_p]),
     "dlrmx_bwd_coalesce": (c_int, [c_int, c_int, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_void_p, c_void_p]),
+    "dlrmx_rows_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float,
+                                  c_float, c_void_p]),
     "dlrmx_interact_dot_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64,
                                        c_void_p]),
     "dlrmx_interact_dot_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64,

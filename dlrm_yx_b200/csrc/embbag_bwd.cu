@@ -184,6 +184,50 @@ bwd_coalesce_kernel(int B, int D, const float* __restrict__ grad, int64_t stride
         if (CH == 1 || col0 + c * G * VEC < D) acc[c].store(o + c * G * VEC);
 }
 
+
+// Non-fused optimizer on an already coalesced gradient (unique rows + summed gradient rows): the GPU
+// form of torch.optim.SGD / RWSAdagrad.step's sparse branch (optim/rwsadagrad.py:97-113) for ONE table.
+// The reference refuses rwsadagrad on GPU (dlrm_s_pytorch.py:1636-1637); this is what it would run.
+template <int VEC, int G, int CH>
+__global__ void __launch_bounds__(256)
+rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom,
+                   const int64_t* __restrict__ rows, const float* __restrict__ gsum, int64_t U, int D,
+                   float lr, float eps) {
+    const int gl = threadIdx.x & (G - 1);
+    const int64_t u = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+    if (u >= U) return;
+    const int col0 = gl * VEC;
+    const int64_t row = rows[u];
+    BwdParams P;
+    P.optimizer = optimizer; P.D = D; P.lr = lr; P.eps = eps;
+    RowVec<VEC> g[CH], w[CH];
+    float* wp = W + row * D + col0;
+    const float* gp = gsum + u * D + col0;
+#pragma unroll
+    for (int c = 0; c < CH; ++c)
+        if (CH == 1 || col0 + c * G * VEC < D) {
+            g[c].load_ro(gp + c * G * VEC);
+            w[c].load(wp + c * G * VEC);
+        } else {
+            g[c].zero();
+        }
+    float* mp = nullptr;
+    float mo = 0.f;
+    if (optimizer == DLRMX_OPT_RWSADAGRAD) {
+        mp = mom + row;
+        mo = *mp;
+    }
+    apply_row<VEC, G, CH>(P, wp, mp, mo, w, g, col0);
+}
+
+template <int VEC, int G, int CH>
+static int launch_rows_update(int optimizer, float* W, float* mom, const int64_t* rows, const float* gsum,
+                              int64_t U, int D, float lr, float eps, cudaStream_t st) {
+    const unsigned blocks = (unsigned)ceil_div(U * G, 256);
+    rows_update_kernel<VEC, G, CH><<<blocks, 256, 0, st>>>(optimizer, W, mom, rows, gsum, U, D, lr, eps);
+    return check_launch("rows_update");
+}
+
 template <int VEC, int G, int CH>
 static int launch_update(const BwdParams& P, cudaStream_t st) {
     const int threads = 256;
@@ -289,6 +333,24 @@ int dlrmx_bwd_coalesce(int B, int D, const float* grad, int64_t stride_b, int64_
     launch_coalesce<V, G_, C>(B, D, grad, stride_b, stride_t, sorted_bag, run_off, num_unique, N, gsum, st)
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_COAL);
     set_error("bwd_coalesce: no kernel for D=%d", D);
+    return DLRMX_E_ARG;
+}
+
+int dlrmx_rows_update(int optimizer, float* table, float* mom, const int64_t* rows, const float* gsum,
+                      int64_t U, int D, float lr, float eps, dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || optimizer == DLRMX_OPT_RWSADAGRAD, "rows_update: bad optimizer %d", optimizer);
+    DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || mom != nullptr, "rows_update: rwsadagrad needs the accumulator");
+    RowGeom g;
+    DLRMX_REQUIRE(row_geometry(D, &g), "rows_update: unsupported D=%d", D);
+    DLRMX_REQUIRE(U >= 0 && U < (1ll << 31), "rows_update: bad U");
+    if (g.vec == 4)
+        DLRMX_REQUIRE((((uintptr_t)table | (uintptr_t)gsum) & 15) == 0, "rows_update: table/gsum must be 16-B aligned");
+    if (U == 0) return DLRMX_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+#define DLRMX_CALL_ROWS(V, G_, C) launch_rows_update<V, G_, C>(optimizer, table, mom, rows, gsum, U, D, lr, eps, st)
+    DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_ROWS);
+    set_error("rows_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;
 }
 }

@@ -1,0 +1,289 @@
+"""Host-side mirror of the reference model's hot-path interface (DLRM_Net, dlrm_s_pytorch.py:226-824) with
+the sparse path running on libdlrmx: same method names, argument meaning and error behaviour for
+`create_mlp / create_emb / create_emb_batched / apply_mlp / apply_emb / apply_emb_batched /
+interact_features / forward / sequential_forward / distributed_forward / distribute_batched_emb_data`.
+
+What is deliberately NOT here: `parallel_forward` (single-process multi-GPU, SURVEY.md 2.1 out of scope),
+QR/MD embeddings, quantised inference, the fbgemm path.
+
+Two ways through the sparse arch:
+  * modular (default, reads like the reference): per-table `EmbeddingBagSum` or one
+    `TableBatchedEmbeddingBags`, then `interact_features`;
+  * `fuse_sparse_arch=True` with `batched_emb=True` and dot interaction: lookup writes pooled rows straight
+    into the [B, 1+T, D] interaction input, one interaction kernel, and in backward one interaction kernel
+    whose output gradient feeds the fused sort/reduce/update in place -- no cat / split / contiguous copies.
+    In the multi-process form the exchange is completed by one unpack kernel into the same block.
+"""
+import sys
+
+import numpy as np
+import torch
+from torch import nn
+from torch.autograd.profiler import record_function
+
+from . import _lib, embedding, interaction, ops, sharders
+from . import extend_distributed as ext_dist
+
+
+class _SparseArchLocal(torch.autograd.Function):
+    """Single-GPU fused lookup + dot interaction.  forward(x [B,D]) -> R [B, D + F(F-1)/2]."""
+
+    @staticmethod
+    def forward(ctx, x, weights, emb, indices, offsets, itself):
+        B, D = x.shape
+        T = emb.T
+        feat = torch.empty((B, 1 + T, D), dtype=torch.float32, device=x.device)
+        ops.embbag_forward(emb.table_set(), indices, offsets, B, out=feat[:, 1:, :],
+                           stride_b=(1 + T) * D, stride_t=D)
+        feat[:, 0, :].copy_(x)
+        ctx.emb, ctx.itself = emb, bool(itself)
+        ctx.save_for_backward(feat, indices, offsets)
+        return ops.interact_dot_fwd(feat, ctx.itself)
+
+    @staticmethod
+    def backward(ctx, dR):
+        feat, indices, offsets = ctx.saved_tensors
+        B, F, D = feat.shape
+        dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
+        ctx.emb.fused_backward(dfeat[:, 1:, :], indices, offsets, B, stride_b=F * D, stride_t=D)
+        return dfeat[:, 0, :], None, None, None, None, None
+
+
+class _ExchangeInteract(torch.autograd.Function):
+    """Multi-process: completes the all-to-all into the feature block, then dot interaction.
+    backward packs the block gradient and starts the transposed exchange (completed by the request's
+    own backward, so it overlaps with the bottom-MLP backward exactly as in the reference)."""
+
+    @staticmethod
+    def forward(ctx, x, recv, itself):
+        lb, D = x.shape
+        T = ext_dist.myreq.a2a_info.global_table_num
+        feat = torch.empty((lb, 1 + T, D), dtype=torch.float32, device=x.device)
+        ctx.info = ext_dist.complete_into(recv, feat, 1)
+        feat[:, 0, :].copy_(x)
+        ctx.itself = bool(itself)
+        ctx.save_for_backward(feat)
+        return ops.interact_dot_fwd(feat, ctx.itself)
+
+    @staticmethod
+    def backward(ctx, dR):
+        (feat,) = ctx.saved_tensors
+        dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
+        send = ext_dist.start_backward_from(ctx.info, dfeat, 1)
+        return dfeat[:, 0, :], send, None
+
+
+class DLRM_Net(nn.Module):
+    def create_mlp(self, ln, sigmoid_layer):
+        """Linear + ReLU stack, Sigmoid after layer `sigmoid_layer`; weights N(0, sqrt(2/(m+n))), biases
+        N(0, sqrt(1/m)) drawn from numpy's global RNG in layer order (dlrm_s_pytorch.py:227-265)."""
+        layers = []
+        for i in range(ln.size - 1):
+            n, m = int(ln[i]), int(ln[i + 1])
+            LL = nn.Linear(n, m, bias=True)
+            W = np.random.normal(0.0, np.sqrt(2 / (m + n)), size=(m, n)).astype(np.float32)
+            bt = np.random.normal(0.0, np.sqrt(1 / m), size=m).astype(np.float32)
+            LL.weight.data = torch.tensor(W, requires_grad=True)
+            LL.bias.data = torch.tensor(bt, requires_grad=True)
+            layers.append(LL)
+            layers.append(nn.Sigmoid() if i == sigmoid_layer else nn.ReLU())
+        return nn.Sequential(*layers)
+
+    def create_emb(self, m, ln, weighted_pooling=None):
+        """One EmbeddingBagSum per (local) table, weights U(+-sqrt(1/n)) from numpy in table order
+        (dlrm_s_pytorch.py:267-318)."""
+        emb_l = nn.ModuleList()
+        v_W_l = []
+        for i in range(ln.size):
+            if ext_dist.my_size > 1 and i not in self.local_emb_indices:
+                continue
+            n = int(ln[i])
+            a = np.sqrt(1 / n)
+            W = np.random.uniform(low=-a, high=a, size=(n, m)).astype(np.float32)
+            emb_l.append(embedding.EmbeddingBagSum(n, m, _weight=torch.tensor(W)))
+            v_W_l.append(None if weighted_pooling is None else torch.ones(n, dtype=torch.float32))
+        return emb_l, v_W_l
+
+    def create_emb_batched(self, D, Es, weighted_pooling=None, learning_rate=0.1):
+        """dlrm_s_pytorch.py:321-334: one table-batched module over the local tables, optimizer fused."""
+        assert weighted_pooling is None, "Weighted pooling not supported yet!"
+        self.Es = Es[self.local_emb_indices] if ext_dist.my_size > 1 else Es
+        T = len(self.Es)
+        return embedding.TableBatchedEmbeddingBags(
+            T, self.Es, D, optimizer=self.emb_optimizer, learning_rate=learning_rate,
+            eps=self.emb_eps, stochastic_rounding=False, init=self.emb_init), [None] * T
+
+    def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, arch_interaction_op=None,
+                 arch_interaction_itself=False, sigmoid_bot=-1, sigmoid_top=-1, sync_dense_params=True,
+                 loss_threshold=0.0, ndevices=-1, weighted_pooling=None, loss_function="bce",
+                 batched_emb=False, sharder="naive", allocation=None,
+                 # additions (keyword-only in spirit): the fused optimizer of the batched module
+                 emb_optimizer=embedding.Optimizer.SGD, emb_learning_rate=0.1, emb_eps=None, emb_init="auto",
+                 fuse_sparse_arch=False):
+        super().__init__()
+        if None in (m_spa, ln_emb, ln_bot, ln_top, arch_interaction_op):
+            return
+        if ndevices > 1:
+            sys.exit("single-process multi-GPU (parallel_forward) is not supported: launch one process per GPU")
+        self.m_spa, self.ln_emb, self.ln_bot, self.ln_top = m_spa, np.asarray(ln_emb), np.asarray(ln_bot), np.asarray(ln_top)
+        self.ndevices = ndevices
+        self.arch_interaction_op = arch_interaction_op
+        self.arch_interaction_itself = arch_interaction_itself
+        self.sync_dense_params = sync_dense_params
+        self.loss_threshold = loss_threshold
+        self.loss_function = loss_function
+        self.weighted_pooling = ("learned" if weighted_pooling not in (None, "fixed") else weighted_pooling)
+        self.batched_emb = batched_emb
+        self.fbgemm_emb = False
+        self.sharder = sharder
+        self.emb_optimizer, self.emb_eps, self.emb_init = emb_optimizer, emb_eps, emb_init
+        self.fuse_sparse_arch = bool(fuse_sparse_arch)
+        if self.fuse_sparse_arch and not (batched_emb and arch_interaction_op == "dot"):
+            raise ValueError("fuse_sparse_arch needs batched_emb=True and arch_interaction_op='dot'")
+        self.device_indices = [0]
+
+        if ext_dist.my_size > 1:       # table-wise model parallel (dlrm_s_pytorch.py:444-468)
+            n_emb = len(self.ln_emb)
+            if n_emb < ext_dist.my_size:
+                sys.exit("only (%d) sparse features for (%d) devices, table partitions will fail"
+                         % (n_emb, ext_dist.my_size))
+            self.n_global_emb = n_emb
+            if sharder == "input":
+                self.device_indices = list(map(int, allocation.split(",")))
+            else:
+                self.device_indices = sharders.shard(self.ln_emb, ext_dist.my_size, sharder)
+            self.n_emb_per_rank = [0] * ext_dist.my_size
+            for i in range(n_emb):
+                self.n_emb_per_rank[self.device_indices[i]] += m_spa // int(self.ln_bot[-1])
+            self.local_emb_indices = [i for i, j in enumerate(self.device_indices) if j == ext_dist.my_local_rank]
+        if batched_emb:
+            self.emb_l, w_list = self.create_emb_batched(m_spa, self.ln_emb, weighted_pooling=weighted_pooling,
+                                                         learning_rate=emb_learning_rate)
+        else:
+            self.emb_l, w_list = self.create_emb(m_spa, self.ln_emb, weighted_pooling=weighted_pooling)
+        if self.weighted_pooling == "learned":
+            self.v_W_l = nn.ParameterList([nn.Parameter(w) for w in w_list])
+        else:
+            self.v_W_l = w_list
+        self.bot_l = self.create_mlp(self.ln_bot, sigmoid_bot)
+        self.top_l = self.create_mlp(self.ln_top, sigmoid_top)
+        if loss_function == "mse":
+            self.loss_fn = torch.nn.MSELoss(reduction="mean")
+        elif loss_function == "bce":
+            self.loss_fn = torch.nn.BCELoss(reduction="mean")
+        else:
+            sys.exit("ERROR: --loss-function=" + loss_function + " is not supported")
+
+    def apply_mlp(self, x, layers):
+        return layers(x)
+
+    def apply_emb(self, lS_o, lS_i):
+        """List of T pooled tensors [B, D] (dlrm_s_pytorch.py:526-587)."""
+        ly = []
+        for k, sparse_index_group_batch in enumerate(lS_i):
+            sparse_offset_group_batch = lS_o[k]
+            if self.v_W_l[k] is not None:
+                per_sample_weights = self.v_W_l[k].gather(0, sparse_index_group_batch)
+            else:
+                per_sample_weights = None
+            V = self.emb_l[k](sparse_index_group_batch, sparse_offset_group_batch,
+                              per_sample_weights=per_sample_weights)
+            ly.append(V)
+        d = int(self.ln_bot[-1])
+        out = []
+        for y in ly:
+            if y.shape[1] == d:
+                out.append(y)
+            else:
+                out.extend(y.split(d, dim=1))
+        return out
+
+    def apply_emb_batched(self, lS_o, lS_i, device_ids=None):
+        """lS_i / lS_o: one-element lists holding the packed indices / offsets (dlrm_s_pytorch.py:589-591;
+        one module on one device here, so no parallel_apply threads)."""
+        mods = self.emb_l if isinstance(self.emb_l, nn.ModuleList) else [self.emb_l]
+        return [m(i, o) for m, i, o in zip(mods, lS_i, lS_o)]
+
+    def interact_features(self, x, ly):
+        return interaction.interact_features(x, ly, self.arch_interaction_op, self.arch_interaction_itself,
+                                             batched=self.batched_emb)
+
+    def forward(self, dense_x, lS_o, lS_i):
+        if ext_dist.my_size > 1:
+            return self.distributed_forward(dense_x, lS_o, lS_i)
+        return self.sequential_forward(dense_x, lS_o, lS_i)
+
+    def _clamp(self, p):
+        if 0.0 < self.loss_threshold < 1.0:
+            return torch.clamp(p, min=self.loss_threshold, max=(1.0 - self.loss_threshold))
+        return p
+
+    def _batched_module(self):
+        return self.emb_l[0] if isinstance(self.emb_l, nn.ModuleList) else self.emb_l
+
+    def sequential_forward(self, dense_x, lS_o, lS_i):
+        if not isinstance(self.emb_l, nn.ModuleList):
+            self.emb_l = nn.ModuleList([self.emb_l])
+        with record_function("module::forward_pass::bottom_mlp"):
+            x = self.apply_mlp(dense_x, self.bot_l)
+        if self.fuse_sparse_arch:
+            with record_function("module::forward_pass::embedding_lookup"):
+                emb = self._batched_module()
+                z = _SparseArchLocal.apply(x, emb.embedding_weights, emb, lS_i, lS_o, self.arch_interaction_itself)
+        else:
+            with record_function("module::forward_pass::embedding_lookup"):
+                if self.batched_emb:
+                    ly = self.apply_emb_batched([lS_o], [lS_i])
+                else:
+                    ly = self.apply_emb(lS_o, lS_i)
+            with record_function("module::forward_pass::interaction"):
+                z = self.interact_features(x, ly)
+        with record_function("module::forward_pass::top_mlp"):
+            p = self.apply_mlp(z, self.top_l)
+        return self._clamp(p)
+
+    def distributed_forward(self, dense_x, lS_o, lS_i):
+        """Local tables x full global batch -> all-to-all (overlapped with the bottom MLP) -> local batch x
+        all tables -> interaction -> top MLP (dlrm_s_pytorch.py:686-730)."""
+        if not isinstance(self.emb_l, nn.ModuleList):
+            self.emb_l = nn.ModuleList([self.emb_l])
+        with record_function("module::forward_pass::embedding_lookup"):
+            if self.batched_emb:
+                ly = self.apply_emb_batched([lS_o], [lS_i])
+            else:
+                ly = self.apply_emb(lS_o, lS_i)
+            if len(self.emb_l) != len(ly):
+                sys.exit("ERROR: corrupted intermediate result in distributed_forward call")
+            a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank, self.batched_emb)
+        with record_function("module::forward_pass::bottom_mlp"):
+            x = self.apply_mlp(dense_x, self.bot_l)
+            if self.fuse_sparse_arch:
+                recv = a2a_req.tensor[0]
+            else:
+                ly = list(a2a_req.wait())
+        with record_function("module::forward_pass::interaction"):
+            if self.fuse_sparse_arch:
+                z = _ExchangeInteract.apply(x, recv, self.arch_interaction_itself)
+            else:
+                z = self.interact_features(x, ly)
+        with record_function("module::forward_pass::top_mlp"):
+            p = self.apply_mlp(z, self.top_l)
+        return self._clamp(p)
+
+    def distribute_batched_emb_data(self, batch_size, lS_o, lS_i):
+        """Packed global batch (all T tables) -> this rank's packed batch (local tables, offsets re-based),
+        dlrm_s_pytorch.py:772-802 (distributed branch).  Unlike the reference it does not assume a fixed
+        number of indices per lookup: each table's index range comes from its own offsets."""
+        B = batch_size
+        if ext_dist.my_size <= 1:
+            return [lS_o], [lS_i]
+        o_parts, i_parts, run = [], [], 0
+        bounds = lS_o[::B].tolist() if lS_o.numel() % B == 1 else None
+        for k in self.local_emb_indices:
+            o = lS_o[k * B:(k + 1) * B + 1]
+            lo, hi = (bounds[k], bounds[k + 1]) if bounds else (int(o[0]), int(o[-1]))
+            i_parts.append(lS_i[lo:hi])
+            rel = o - lo + run
+            o_parts.append(rel if not o_parts else rel[1:])
+            run += hi - lo
+        return [torch.cat(o_parts, dim=0)], [torch.cat(i_parts, dim=0)]

@@ -1,0 +1,240 @@
+"""Model-parallel exchange of pooled embeddings with the reference's surface (extend_distributed.py):
+module globals `my_size / my_rank / my_local_rank / my_local_size`, `init_distributed`, `get_my_slice`,
+`get_split_lengths`, `alltoall(inputs, per_rank_table_splits, batched_emb) -> Request`, `Request.wait()`,
+`all_gather`, `barrier`, `DDP`.
+
+One process per GPU; transport is NCCL all-to-all over NVLink (torch.distributed plumbing).  What changes
+against the reference (extend_distributed.py:405-508):
+  * the batched lookup already writes [B, T_r, D], which IS the send buffer (concatenation over destination
+    ranks of [B/W, T_r, D]) -- no torch.cat / flatten copy before the send;
+  * `complete_into(recv, feat, feat_off)` (used by dlrm_net.s fast path) drops every source rank's chunk
+    straight into the [B/W, 1+T, D] interaction input with ONE kernel (dlrmx_a2a_unpack) instead of W views
+    + a cat, and the backward packs the feature-block gradient with dlrmx_a2a_pack_grad;
+  * only the NCCL/Gloo all_to_all_single path exists (the scatter / scatter_list fallbacks for backends
+    without all-to-all are out of scope).
+Autograd behaviour is the reference's: forward batch-scatter / table-gather, backward the exact transpose,
+asynchronous in both directions, one request outstanding (the global `myreq`).
+"""
+import os
+
+import torch
+import torch.distributed as dist
+from torch.autograd import Function
+from torch.nn.parallel import DistributedDataParallel as DDP  # noqa: F401  (re-export, as the reference does)
+
+from . import ops
+
+my_size = -1
+my_rank = -1
+my_local_rank = -1
+my_local_size = -1
+myreq = None
+
+
+def _env_int(names, default=-1):
+    for n in names:
+        v = os.environ.get(n)
+        if v is not None and int(v) >= 0:
+            return int(v)
+    return default
+
+
+def get_my_slice(n):
+    """Contiguous slice of n items owned by this rank; the first n % W ranks own one more
+    (extend_distributed.py:47-55)."""
+    base, extra = divmod(n, my_size)
+    lo = my_rank * base + min(my_rank, extra)
+    return slice(lo, lo + base + (1 if my_rank < extra else 0), 1)
+
+
+def get_split_lengths(n):
+    """(my length, per-rank lengths or None when n divides evenly) -- extend_distributed.py:58-66."""
+    base, extra = divmod(n, my_size)
+    if extra == 0:
+        return base, None
+    splits = [base + (1 if r < extra else 0) for r in range(my_size)]
+    return splits[my_rank], splits
+
+
+def init_distributed(rank=-1, local_rank=-1, size=-1, use_gpu=False, backend=""):
+    """Rank discovery from the launcher environment (torchrun / MPI variables) and process-group
+    creation: NCCL on GPU, Gloo otherwise (extend_distributed.py:81-207)."""
+    global my_size, my_rank, my_local_rank, my_local_size, myreq
+    if rank == -1:
+        rank = _env_int(["PMI_RANK", "OMPI_COMM_WORLD_RANK", "MV2_COMM_WORLD_RANK", "RANK"], -1)
+    if size == -1:
+        size = _env_int(["PMI_SIZE", "OMPI_COMM_WORLD_SIZE", "MV2_COMM_WORLD_SIZE", "WORLD_SIZE"], -1)
+    if local_rank == -1:
+        local_rank = _env_int(["MPI_LOCALRANKID", "OMPI_COMM_WORLD_LOCAL_RANK", "MV2_COMM_WORLD_LOCAL_RANK",
+                               "LOCAL_RANK"], 0)
+    local_size = _env_int(["MPI_LOCALNRANKS", "OMPI_COMM_WORLD_LOCAL_SIZE", "MV2_COMM_WORLD_LOCAL_SIZE",
+                           "LOCAL_WORLD_SIZE"], 1)
+    if not backend:
+        backend = "nccl" if use_gpu else "gloo"
+    if size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        os.environ["RANK"], os.environ["WORLD_SIZE"] = str(rank), str(size)
+        if use_gpu:
+            if local_size != torch.cuda.device_count() and local_size > torch.cuda.device_count():
+                raise RuntimeError("%d local ranks but %d GPUs" % (local_size, torch.cuda.device_count()))
+            torch.cuda.set_device(local_rank)
+        if not dist.is_initialized():
+            dist.init_process_group(backend, rank=rank, world_size=size)
+        my_rank, my_size = dist.get_rank(), dist.get_world_size()
+        my_local_rank, my_local_size = local_rank, local_size
+    else:
+        my_rank, my_size, my_local_rank, my_local_size = 0, 1, 0, 1
+    myreq = Request()
+
+
+class All2AllInfo(object):
+    pass
+
+
+class Request(object):
+    """The one in-flight exchange (extend_distributed.py:210-220)."""
+
+    def __init__(self):
+        self.req = None
+        self.tensor = None
+        self.a2a_info = None
+
+    def wait(self):
+        """Tuple of W tensors: [B/W, T_p*D] (or [B/W, T_p, D] when batched)."""
+        ret = _A2AWait.apply(*self.tensor)
+        self.req = None
+        self.tensor = None
+        return ret
+
+
+def _split_sizes(info):
+    """Element counts per peer: forward receives lb*T_p*D from rank p and sends B_p*T_r*D to it."""
+    recv = [info.local_batch_num * t * info.emb_dim for t in info.tables_per_rank]
+    if info.global_batch_partition_slices:
+        send = [b * info.local_table_num * info.emb_dim for b in info.global_batch_partition_slices]
+    else:
+        send = None
+    return send, recv
+
+
+class _A2AReq(Function):
+    @staticmethod
+    def forward(ctx, info, *inputs):
+        global myreq
+        send_split, recv_split = _split_sizes(info)
+        if info.batched_emb:
+            send = inputs[0].contiguous().view(-1)                  # [B, T_r, D] already is the send layout
+        else:
+            send = torch.cat(inputs, dim=1).view(-1)                # T_r x [B, D] -> [B, T_r*D]
+        recv = send.new_empty([info.global_table_num * info.local_batch_num * info.emb_dim])
+        myreq.req = dist.all_to_all_single(recv, send, recv_split, send_split, async_op=True)
+        myreq.tensor = (recv,)
+        info.send_split, info.recv_split = send_split, recv_split
+        myreq.a2a_info = info
+        ctx.info = info
+        return myreq.tensor
+
+    @staticmethod
+    def backward(ctx, *unused):
+        global myreq
+        info = ctx.info
+        myreq.req.wait()
+        myreq.req = None
+        g = myreq.tensor
+        myreq.tensor = None
+        if info.batched_emb:
+            grads = [g.view(info.batch_size, -1, info.emb_dim)]
+        else:
+            grads = [c.contiguous() for c in g.view(info.batch_size, -1).split(info.emb_dim, dim=1)]
+        return (None, *grads)
+
+
+def _issue_backward(info, send):
+    global myreq
+    recv = send.new_empty([info.batch_size * info.local_table_num * info.emb_dim])
+    myreq.req = dist.all_to_all_single(recv, send, info.send_split, info.recv_split, async_op=True)
+    myreq.tensor = recv
+
+
+class _A2AWait(Function):
+    @staticmethod
+    def forward(ctx, recv):
+        global myreq
+        info = myreq.a2a_info
+        ctx.info = info
+        myreq.req.wait()
+        myreq.req = None
+        myreq.tensor = None
+        chunks = recv.split(info.recv_split)
+        if info.batched_emb:
+            return tuple(c.view(info.local_batch_num, -1, info.emb_dim) for c in chunks)
+        return tuple(c.view(info.local_batch_num, -1) for c in chunks)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        send = torch.cat([g.contiguous().view(-1) for g in grads])
+        _issue_backward(ctx.info, send)
+        return (send,)
+
+
+def complete_into(recv, feat, feat_off=1):
+    """Low-level half of the fast path (no autograd): waits for the forward exchange and writes every
+    source rank's [lb, T_p, D] chunk into feat[:, feat_off + t, :] (rank-major table order) with one
+    kernel.  Returns the exchange descriptor needed by `start_backward_from`."""
+    global myreq
+    info = myreq.a2a_info
+    myreq.req.wait()
+    myreq.req = None
+    myreq.tensor = None
+    ops.a2a_unpack(recv, info.tables_per_rank, info.local_batch_num, info.emb_dim, feat, feat_off)
+    return info
+
+
+def start_backward_from(info, dfeat, feat_off=1):
+    """Packs dfeat[:, feat_off:, :] into per-destination chunks (one kernel) and starts the transposed
+    exchange; `_A2AReq.backward` completes it.  Returns the send buffer (kept alive by the caller)."""
+    send = ops.a2a_pack_grad(dfeat, feat_off, info.tables_per_rank, info.local_batch_num, info.emb_dim)
+    _issue_backward(info, send)
+    return send
+
+
+def alltoall(inputs, per_rank_table_splits, batched_emb=False):
+    """inputs: this rank's pooled embeddings for the FULL global batch -- a list of T_r tensors [B, D], or
+    one [B, T_r, D] tensor when `batched_emb`; per_rank_table_splits[p] = tables held by rank p.
+    Starts the exchange and returns the global Request (extend_distributed.py:601-639)."""
+    global myreq
+    info = All2AllInfo()
+    if batched_emb:
+        info.batch_size, info.local_table_num, info.emb_dim = inputs[0].size()
+    else:
+        info.batch_size, info.emb_dim = inputs[0].size()
+        info.local_table_num = len(inputs)
+    info.local_batch_num, info.global_batch_partition_slices = get_split_lengths(info.batch_size)
+    info.tables_per_rank = (list(per_rank_table_splits) if per_rank_table_splits
+                            else [info.local_table_num] * my_size)
+    info.global_table_wise_partition_slices = per_rank_table_splits
+    info.global_table_num = sum(info.tables_per_rank)
+    info.batched_emb = batched_emb
+    _A2AReq.apply(info, *inputs)
+    return myreq
+
+
+def all_gather(input, lengths=None, dim=0):
+    """Concatenation of every rank's tensor along `dim` (extend_distributed.py:642-645); `lengths[p]` gives
+    rank p's extent when they differ."""
+    if my_size <= 1:
+        return input
+    if dim != 0:
+        return all_gather(input.transpose(0, dim).contiguous(), lengths, 0).transpose(0, dim)
+    if lengths is None:
+        parts = [torch.empty_like(input) for _ in range(my_size)]
+    else:
+        parts = [input.new_empty((int(n),) + tuple(input.shape[1:])) for n in lengths]
+    dist.all_gather(parts, input.contiguous())
+    return torch.cat(parts, dim=0)
+
+
+def barrier():
+    if my_size > 1:
+        dist.barrier()

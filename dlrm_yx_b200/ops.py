@@ -217,3 +217,14 @@ def a2a_pack_grad(dfeat, feat_off, tables_per_rank, lb, D, send=None):
                                          _int_array(tables_per_rank), lb, D, send.data_ptr(), _stream())
     _lib.check(rc, "dlrmx_a2a_pack_grad")
     return send
+
+
+def rows_update(optimizer, weight, mom, rows, gsum, lr, eps=0.0):
+    """Non-fused sparse optimizer step of one table: rows int64 [U] unique, gsum [U, D] coalesced."""
+    _need_cuda(weight, mom, rows, gsum)
+    if rows.dtype != torch.int64 or not rows.is_contiguous() or not gsum.is_contiguous():
+        raise _lib.DlrmxError("rows_update: rows must be contiguous int64, gsum contiguous fp32")
+    U, D = gsum.shape
+    rc = _lib.load().dlrmx_rows_update(optimizer, weight.data_ptr(), _ptr(mom), rows.data_ptr(), gsum.data_ptr(),
+                                       U, D, float(lr), float(eps), _stream())
+    _lib.check(rc, "dlrmx_rows_update")

@@ -139,6 +139,13 @@ int dlrmx_bwd_coalesce(int B, int D, const float* grad, int64_t stride_b, int64_
                        const int32_t* sorted_bag, const int32_t* run_off,
                        const int32_t* num_unique, int64_t N, float* gsum, dlrmx_stream_t stream);
 
+/* Non-fused sparse optimizer step of ONE table on an already coalesced gradient (the GPU form of
+ * torch.optim.SGD on a sparse grad, dlrm_s_pytorch.py:1640/1933, and of RWSAdagrad.step's sparse
+ * branch, optim/rwsadagrad.py:97-113 -- which the reference refuses to run on GPU,
+ * dlrm_s_pytorch.py:1636-1637).  rows [U] int64 unique row ids, gsum [U, D] summed gradient rows. */
+int dlrmx_rows_update(int optimizer, float* table, float* mom, const int64_t* rows, const float* gsum,
+                      int64_t U, int D, float lr, float eps, dlrmx_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Dot / cat feature interaction.  Replaces DLRM_Net.interact_features (dlrm_s_pytorch.py:627-673):
  *   feat   [B, F, D] fp32 (feature 0 = bottom-MLP output x, features 1.. = pooled embeddings), row
