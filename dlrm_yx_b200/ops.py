@@ -13,6 +13,34 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+# Optional per-kernel timing (bench.py): when PROFILE is a dict, every wrapper brackets its launch(es) with
+# CUDA events on the launching stream and appends (start, end) under the kernel's name.
+PROFILE = None
+
+
+class _timed:
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.s = torch.cuda.Event(enable_timing=True)
+            self.e = torch.cuda.Event(enable_timing=True)
+            self.s.record()
+
+    def __exit__(self, *a):
+        if PROFILE is not None:
+            self.e.record()
+            PROFILE.setdefault(self.name, []).append((self.s, self.e))
+        return False
+
+
+def profile_summary():
+    """{name: (calls, mean ms)} of the events collected so far (synchronises)."""
+    torch.cuda.synchronize()
+    return {k: (len(v), sum(s.elapsed_time(e) for s, e in v) / len(v)) for k, v in (PROFILE or {}).items()}
+
+
 def _ptr(t):
     return 0 if t is None else t.data_ptr()
 
@@ -89,10 +117,11 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
         out = torch.empty((B, T, D), dtype=torch.float32, device=tables.device)
         stride_b, stride_t = T * D, D
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_" + _idx_suffix(indices, offsets))
-    rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0,
-            indices.data_ptr(), offsets.data_ptr(), indices.numel(), T, B, D, _ptr(per_sample_weights),
-            out.data_ptr(), stride_b, stride_t, _ptr(err_flag), _stream())
-    _lib.check(rc, "dlrmx_embbag_fwd")
+    with _timed("embbag_fwd"):
+        rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0,
+                indices.data_ptr(), offsets.data_ptr(), indices.numel(), T, B, D, _ptr(per_sample_weights),
+                out.data_ptr(), stride_b, stride_t, _ptr(err_flag), _stream())
+        _lib.check(rc, "dlrmx_embbag_fwd")
     return out
 
 
@@ -111,9 +140,10 @@ def bwd_sort(tables, indices, offsets, B):
     wsb = lib.dlrmx_bwd_sort_workspace_bytes(N, tables.T * B)
     ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=dev)
     fn = getattr(lib, "dlrmx_bwd_sort_" + _idx_suffix(indices, offsets))
-    rc = fn(indices.data_ptr(), offsets.data_ptr(), N, tables.T, B, tables.row_base.data_ptr(),
-            tables.total_rows, skey.data_ptr(), sbag.data_ptr(), ws.data_ptr(), wsb, _stream())
-    _lib.check(rc, "dlrmx_bwd_sort")
+    with _timed("bwd_sort"):
+        rc = fn(indices.data_ptr(), offsets.data_ptr(), N, tables.T, B, tables.row_base.data_ptr(),
+                tables.total_rows, skey.data_ptr(), sbag.data_ptr(), ws.data_ptr(), wsb, _stream())
+        _lib.check(rc, "dlrmx_bwd_sort")
     return skey, sbag
 
 
@@ -145,11 +175,12 @@ def bwd_update(tables, optimizer, grad, stride_b, stride_t, B, skey, sbag, lr, e
         raise _lib.DlrmxError("RWSAdagrad update needs row-wise accumulators (TableSet(moms=...))")
     wsb = lib.dlrmx_bwd_update_workspace_bytes(N, tables.D)
     ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=tables.device)
-    rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(), _ptr(tables.mom_ptrs),
-                              tables.row_base.data_ptr(), tables.T, B, tables.D, grad.data_ptr(), stride_b,
-                              stride_t, skey.data_ptr(), sbag.data_ptr(), N, float(lr), float(eps),
-                              ws.data_ptr(), wsb, _stream())
-    _lib.check(rc, "dlrmx_bwd_update")
+    with _timed("bwd_update"):
+        rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(), _ptr(tables.mom_ptrs),
+                                  tables.row_base.data_ptr(), tables.T, B, tables.D, grad.data_ptr(), stride_b,
+                                  stride_t, skey.data_ptr(), sbag.data_ptr(), N, float(lr), float(eps),
+                                  ws.data_ptr(), wsb, _stream())
+        _lib.check(rc, "dlrmx_bwd_update")
 
 
 def bwd_coalesce(grad, stride_b, stride_t, B, D, sbag, run_off, nuniq, max_unique=None):
@@ -175,9 +206,10 @@ def interact_dot_fwd(feat, itself=False, out=None):
         raise _lib.DlrmxError("feat must be [B, F, D] with contiguous F x D blocks")
     if out is None:
         out = torch.empty((B, D + tri_count(F, itself)), dtype=torch.float32, device=feat.device)
-    rc = _lib.load().dlrmx_interact_dot_fwd(feat.data_ptr(), feat.stride(0), B, F, D, int(itself),
-                                            out.data_ptr(), out.stride(0), _stream())
-    _lib.check(rc, "dlrmx_interact_dot_fwd")
+    with _timed("interact_fwd"):
+        rc = _lib.load().dlrmx_interact_dot_fwd(feat.data_ptr(), feat.stride(0), B, F, D, int(itself),
+                                                out.data_ptr(), out.stride(0), _stream())
+        _lib.check(rc, "dlrmx_interact_dot_fwd")
     return out
 
 
@@ -188,10 +220,11 @@ def interact_dot_bwd(feat, dout, itself=False, dfeat=None):
         dout = dout.contiguous()
     if dfeat is None:
         dfeat = torch.empty((B, F, D), dtype=torch.float32, device=feat.device)
-    rc = _lib.load().dlrmx_interact_dot_bwd(feat.data_ptr(), feat.stride(0), B, F, D, int(itself),
-                                            dout.data_ptr(), dout.stride(0), dfeat.data_ptr(),
-                                            dfeat.stride(0), _stream())
-    _lib.check(rc, "dlrmx_interact_dot_bwd")
+    with _timed("interact_bwd"):
+        rc = _lib.load().dlrmx_interact_dot_bwd(feat.data_ptr(), feat.stride(0), B, F, D, int(itself),
+                                                dout.data_ptr(), dout.stride(0), dfeat.data_ptr(),
+                                                dfeat.stride(0), _stream())
+        _lib.check(rc, "dlrmx_interact_dot_bwd")
     return dfeat
 
 
@@ -202,9 +235,10 @@ def _int_array(values):
 def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):
     """recv = concat_p [lb, T_p, D]  ->  dst[:, feat_off + t, :] (rank-major table order)."""
     _need_cuda(recv, dst)
-    rc = _lib.load().dlrmx_a2a_unpack(recv.data_ptr(), len(tables_per_rank), _int_array(tables_per_rank), lb, D,
-                                      dst.data_ptr(), dst.stride(0), feat_off, _stream())
-    _lib.check(rc, "dlrmx_a2a_unpack")
+    with _timed("a2a_unpack"):
+        rc = _lib.load().dlrmx_a2a_unpack(recv.data_ptr(), len(tables_per_rank), _int_array(tables_per_rank), lb, D,
+                                          dst.data_ptr(), dst.stride(0), feat_off, _stream())
+        _lib.check(rc, "dlrmx_a2a_unpack")
     return dst
 
 
@@ -213,9 +247,10 @@ def a2a_pack_grad(dfeat, feat_off, tables_per_rank, lb, D, send=None):
     T = sum(int(t) for t in tables_per_rank)
     if send is None:
         send = torch.empty(lb * T * D, dtype=torch.float32, device=dfeat.device)
-    rc = _lib.load().dlrmx_a2a_pack_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
-                                         _int_array(tables_per_rank), lb, D, send.data_ptr(), _stream())
-    _lib.check(rc, "dlrmx_a2a_pack_grad")
+    with _timed("a2a_pack_grad"):
+        rc = _lib.load().dlrmx_a2a_pack_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
+                                             _int_array(tables_per_rank), lb, D, send.data_ptr(), _stream())
+        _lib.check(rc, "dlrmx_a2a_pack_grad")
     return send
 
 

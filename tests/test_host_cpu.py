@@ -1,0 +1,125 @@
+"""Host-side logic either side of the kernels, on CPU: sharders (bit-exact vs the reference's own output),
+packed layouts, batch slicing, and the model-parallel exchange run with 2 gloo processes (pure communication +
+autograd plumbing: no kernels are involved when `Request.wait()` is used)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from dlrm_yx_b200 import data, sharders
+from oracle import oracle_np as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_sharders_match_reference_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "sharders.npz"))
+    tables = {"kaggle": g["kaggle"], "terabyte": g["terabyte"], "bench": np.array([1000000] * 8)}
+    n = 0
+    for key in g.files:
+        if key in ("kaggle", "terabyte"):
+            continue
+        nm, rest = key.split("_", 1)
+        alg, W = rest.rsplit("_", 1)
+        assert sharders.shard(tables[nm], int(W), alg) == g[key].tolist(), key
+        assert O.shard(tables[nm].tolist(), int(W), alg) == g[key].tolist(), key
+        n += 1
+    assert n == 60
+    assert list(data.TERABYTE_ROWS) == g["terabyte"].tolist() and list(data.KAGGLE_ROWS) == g["kaggle"].tolist()
+
+
+def test_unknown_sharder_raises():
+    with pytest.raises(ValueError):
+        sharders.shard([1, 2, 3], 2, "nope")
+
+
+def test_traffic_sharder_balances_table_counts():
+    d = sharders.shard(data.TERABYTE_ROWS, 8, "traffic")
+    counts = [d.count(r) for r in range(8)]
+    assert max(counts) - min(counts) <= 1 and sorted(set(d)) == list(range(8))
+
+
+def test_get_splits():
+    assert sharders.get_splits(26, 8) == [4, 4, 3, 3, 3, 3, 3, 3]
+    assert sharders.get_splits(8, 4) == [2, 2, 2, 2]
+
+
+def test_pack_matches_oracle_and_roundtrips():
+    rng = np.random.default_rng(3)
+    X, lS_o, lS_i, tgt = data.random_batch([50, 7, 3, 1000], 16, 5, 4, fixed=False, rng=rng)
+    idx, off = data.pack(lS_o, lS_i)
+    oi, oo = O.pack_batched([o.numpy() for o in lS_o], [i.numpy() for i in lS_i])
+    assert np.array_equal(idx.numpy(), oi) and np.array_equal(off.numpy(), oo)
+    assert idx.dtype == torch.int32 and off.numel() == 4 * 16 + 1
+    bo, bi = O.unpack_batched(idx.numpy(), off.numpy(), 4, 16)
+    for k in range(4):
+        assert np.array_equal(bo[k], lS_o[k].numpy()) and np.array_equal(bi[k], lS_i[k].numpy())
+    li, lo = data.local_packed(lS_o, lS_i, [1, 3])
+    ri, ro = O.distribute_batched_local(idx.numpy(), off.numpy(), 4, 16, [1, 3])
+    assert np.array_equal(li.numpy(), ri) and np.array_equal(lo.numpy(), ro)
+
+
+def test_random_batch_distribution_rules():
+    rng = np.random.default_rng(1)
+    X, lS_o, lS_i, tgt = data.random_batch([1000, 3], 32, 10, 13, fixed=True, rng=rng)
+    assert X.shape == (32, 13) and X.dtype == torch.float32 and tgt.shape == (32, 1)
+    i0 = lS_i[0].view(32, 10).numpy()
+    assert np.all(np.diff(i0, axis=1) > 0)                       # sorted, distinct within a bag
+    assert lS_i[1].max() <= 2 and lS_o[1].numel() == 32           # a 3-row table cannot give 10 distinct ids
+    assert data.num_interactions(26, 128) == 479 and data.num_interactions(26, 16) == 367
+    assert data.num_interactions(8, 64) == 100 and data.num_interactions(3, 2) == 8
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _a2a_worker(rank, W, port, batched, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    from dlrm_yx_b200 import extend_distributed as ext
+    ext.init_distributed(rank=rank, local_rank=rank, size=W, use_gpu=False, backend="gloo")
+    B, D, tpr = 6, 4, [2, 1]
+    rng = np.random.default_rng(5)
+    pooled = [rng.normal(size=(B, t, D)).astype(np.float32) for t in tpr]      # every rank knows all (test only)
+    coef = [rng.normal(size=(B // W, sum(tpr), D)).astype(np.float32) for _ in range(W)]
+    mine = torch.from_numpy(pooled[rank].copy()).requires_grad_(True)
+    if batched:
+        req = ext.alltoall([mine], tpr, True)
+        outs = req.wait()
+        got = torch.cat([o.view(B // W, -1, D) for o in outs], dim=1)
+    else:
+        ins = [mine[:, t, :] for t in range(tpr[rank])]
+        req = ext.alltoall(ins, tpr, False)
+        outs = req.wait()
+        got = torch.cat(outs, dim=1).view(B // W, -1, D)
+    (got * torch.from_numpy(coef[rank])).sum().backward()
+    np.savez(os.path.join(out_dir, "r%d_%d.npz" % (rank, int(batched))), out=got.detach().numpy(),
+             grad=mine.grad.numpy(), slice=np.array([ext.get_my_slice(B).start, ext.get_my_slice(B).stop]))
+    ext.barrier()
+    torch.distributed.destroy_process_group()
+
+
+@pytest.mark.parametrize("batched", [False, True])
+def test_alltoall_two_ranks_gloo(tmp_path, batched):
+    W, B, D, tpr = 2, 6, 4, [2, 1]
+    port = _free_port()
+    mp.spawn(_a2a_worker, args=(W, port, batched, str(tmp_path)), nprocs=W, join=True)
+    rng = np.random.default_rng(5)
+    pooled = [rng.normal(size=(B, t, D)).astype(np.float32) for t in tpr]
+    coef = [rng.normal(size=(B // W, sum(tpr), D)).astype(np.float32) for _ in range(W)]
+    want = O.alltoall_fwd(pooled, W)
+    want_grad = O.alltoall_bwd(coef, tpr, W)
+    for r in range(W):
+        got = np.load(os.path.join(str(tmp_path), "r%d_%d.npz" % (r, int(batched))))
+        assert np.array_equal(got["out"], want[r])
+        assert np.array_equal(got["grad"], want_grad[r])
+        assert got["slice"].tolist() == [r * 3, r * 3 + 3]

@@ -1,0 +1,202 @@
+"""GPU parity of the reference-facing host layer (modules, optimizers, DLRM_Net mirror, torch op) against the
+golden vectors produced by the UNMODIFIED reference (tests/golden/, oracle/gen_golden.py) and the oracle.
+
+Bars: pooled forward outputs and coalesced row ids bit-exact; losses, gradients, updated rows and
+accumulators rtol 1e-5 / atol 1e-6 (fp32 MLPs, TF32 off -- the reference's precision).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_np as O
+
+pytestmark = pytest.mark.gpu
+RT, AT = 1e-5, 1e-6
+CASES = ["c1_tiny_sgd", "c1_tiny_rws", "c2_kaggle_small_rws", "c3_multihot_sgd", "c4_terabyte_small_rws"]
+
+
+@pytest.fixture(autouse=True)
+def _fp32():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+
+
+def load(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    return g, len(g["meta_ln_emb"]), int(g["meta_misc"][0]), int(g["meta_misc"][1])
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def load_mlps(m, g):
+    with torch.no_grad():
+        for pre, mlp in (("bot", m.bot_l), ("top", m.top_l)):
+            j = 0
+            for layer in mlp:
+                if isinstance(layer, torch.nn.Linear):
+                    layer.weight.copy_(cu(g["%s_W_%d" % (pre, j)]))
+                    layer.bias.copy_(cu(g["%s_b_%d" % (pre, j)]))
+                    j += 1
+
+
+def build_net(g, T, D, batched, fuse=False, opt="sgd", lr=0.1):
+    from dlrm_yx_b200 import dlrm_net, embedding
+    np.random.seed(int(g["meta_misc"][4]))
+    kind = embedding.Optimizer.SGD if opt == "sgd" else embedding.Optimizer.EXACT_ROWWISE_ADAGRAD
+    m = dlrm_net.DLRM_Net(D, g["meta_ln_emb"], g["meta_ln_bot"], g["meta_ln_top"], arch_interaction_op="dot",
+                          sigmoid_bot=-1, sigmoid_top=len(g["meta_ln_top"]) - 2, batched_emb=batched,
+                          emb_optimizer=kind, emb_learning_rate=lr, fuse_sparse_arch=fuse)
+    return m.cuda()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_seeded_construction_reproduces_reference_weights(golden_dir, name):
+    """Same numpy seed -> same tables and MLP weights as the reference's DLRM_Net (draw order is part of parity)."""
+    g, T, D, B = load(golden_dir, name)
+    m = build_net(g, T, D, batched=False)
+    for k in range(T):
+        assert np.array_equal(m.emb_l[k].weight.detach().cpu().numpy(), g["W0_%d" % k])
+    assert np.array_equal(m.bot_l[0].weight.detach().cpu().numpy(), g["bot_W_0"])
+    assert np.array_equal(m.top_l[0].bias.detach().cpu().numpy(), g["top_b_0"])
+    mb = build_net(g, T, D, batched=True)
+    for k, w in enumerate(mb.emb_l.split_weights()):
+        assert np.array_equal(w.cpu().numpy(), g["W0_%d" % k])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_embedding_bag_module_forward_and_coalesced_grad(golden_dir, name):
+    from dlrm_yx_b200 import embedding
+    g, T, D, B = load(golden_dir, name)
+    for k in range(T):
+        E = embedding.EmbeddingBagSum(int(g["meta_ln_emb"][k]), D, _weight=cu(g["W0_%d" % k]))
+        out = E(cu(g["idx_%d" % k]), cu(g["off_%d" % k]))
+        assert np.array_equal(out.detach().cpu().numpy(), g["pooled"][:, k, :])
+        out.backward(cu(g["d_pooled"][:, k, :]))
+        gr = E.weight.grad
+        assert gr.is_sparse and gr.is_coalesced()
+        assert np.array_equal(gr._indices()[0].cpu().numpy(), g["gco_idx_%d" % k])     # == reference coalesce()
+        np.testing.assert_allclose(gr._values().cpu().numpy(), g["gco_val_%d" % k], rtol=RT, atol=AT)
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("fused", [False, True])
+def test_per_table_model_two_train_steps(golden_dir, name, fused):
+    """apply_emb / interact_features / backward / optimizer.step, exactly the reference's call sequence."""
+    from dlrm_yx_b200 import rwsadagrad
+    g, T, D, B = load(golden_dir, name)
+    m = build_net(g, T, D, batched=False)
+    lr = float(g["meta_lr"])
+    if str(g["meta_opt"]) == "sgd":
+        opt = rwsadagrad.SparseSGD(m.parameters(), lr=lr)
+    else:
+        opt = rwsadagrad.RWSAdagrad(m.parameters(), lr=lr)
+    if fused:
+        opt.attach(*m.emb_l)
+    X, tgt = cu(g["X"]), cu(g["target"])
+    lS_o = [cu(g["off_%d" % k]) for k in range(T)]
+    lS_i = [cu(g["idx_%d" % k]) for k in range(T)]
+    x = m.apply_mlp(X, m.bot_l)
+    ly = m.apply_emb(lS_o, lS_i)
+    z = m.interact_features(x, ly)
+    p = m.apply_mlp(z, m.top_l)
+    np.testing.assert_allclose(x.detach().cpu().numpy(), g["x_bot"], rtol=RT, atol=AT)
+    assert np.array_equal(torch.stack(ly, 1).detach().cpu().numpy(), g["pooled"])
+    np.testing.assert_allclose(z.detach().cpu().numpy(), g["interact"], rtol=RT, atol=AT)
+    np.testing.assert_allclose(p.detach().cpu().numpy(), g["pred"], rtol=RT, atol=AT)
+    loss = m.loss_fn(p, tgt)
+    opt.zero_grad()
+    loss.backward()
+    opt.step()
+    np.testing.assert_allclose(loss.item(), float(g["loss"]), rtol=RT)
+    for k in range(T):
+        np.testing.assert_allclose(m.emb_l[k].weight.detach().cpu().numpy(), g["W1_%d" % k], rtol=RT, atol=AT)
+    loss2 = m.loss_fn(m(X, lS_o, lS_i), tgt)
+    opt.zero_grad()
+    loss2.backward()
+    opt.step()
+    np.testing.assert_allclose(loss2.item(), float(g["loss2"]), rtol=RT)
+    for k in range(T):
+        np.testing.assert_allclose(m.emb_l[k].weight.detach().cpu().numpy(), g["W2_%d" % k], rtol=RT, atol=AT)
+        if str(g["meta_opt"]) != "sgd":
+            np.testing.assert_allclose(opt.state[m.emb_l[k].weight]["momentum"].cpu().numpy(), g["mom2_%d" % k],
+                                       rtol=RT, atol=1e-9)
+
+
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("fuse", [False, True])
+def test_batched_model_two_train_steps(golden_dir, name, fuse):
+    """--batched-emb path: packed int32 inputs, ONE lookup launch, optimizer fused into backward."""
+    from dlrm_yx_b200 import data, rwsadagrad
+    g, T, D, B = load(golden_dir, name)
+    lr = float(g["meta_lr"])
+    sgd = str(g["meta_opt"]) == "sgd"
+    m = build_net(g, T, D, batched=True, fuse=fuse, opt="sgd" if sgd else "rws", lr=lr)
+    dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
+    opt = torch.optim.SGD(dense, lr=lr) if sgd else rwsadagrad.RWSAdagrad(dense, lr=lr)
+    idx, off = data.pack([torch.from_numpy(g["off_%d" % k]) for k in range(T)],
+                         [torch.from_numpy(g["idx_%d" % k]) for k in range(T)])
+    idx, off = idx.cuda(), off.cuda()
+    X, tgt = cu(g["X"]), cu(g["target"])
+    for step, (lk, wk) in enumerate((("loss", "W1_%d"), ("loss2", "W2_%d"))):
+        p = m(X, off, idx)
+        loss = m.loss_fn(p, tgt)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        assert m._batched_module().embedding_weights.grad is None
+        np.testing.assert_allclose(loss.item(), float(g[lk]), rtol=RT)
+        for k, w in enumerate(m._batched_module().split_weights()):
+            np.testing.assert_allclose(w.cpu().numpy(), g[wk % k], rtol=RT, atol=AT)
+    if not sgd:
+        for k, mom in enumerate(m._batched_module().split_momentum()):
+            np.testing.assert_allclose(mom.cpu().numpy(), g["mom2_%d" % k], rtol=RT, atol=1e-9)
+
+
+def test_cat_interaction_is_layout_only():
+    from dlrm_yx_b200 import interaction
+    x = torch.randn(5, 8, device="cuda")
+    ly = [torch.randn(5, 8, device="cuda") for _ in range(3)]
+    R = interaction.interact_features(x, ly, "cat")
+    assert np.array_equal(R.cpu().numpy(), O.interact_cat(x.cpu().numpy(), torch.stack(ly, 1).cpu().numpy()))
+
+
+def test_torch_op_batched_forward_single_device():
+    """torch.ops.batched_forward.forward with the calling convention of yx_modfs/dlrm.py:108-117 (offsets before
+    indices; int32; concatenated weights + table_offsets), more than one table per device."""
+    import dlrm_yx_b200.batched_forward  # noqa: F401  (registers the op, like the reference's import)
+    rng = np.random.default_rng(2)
+    rows, D, B, L = [40, 7, 300], 64, 33, 5
+    Ws = [rng.uniform(-1, 1, size=(r, D)).astype(np.float32) for r in rows]
+    idx = np.concatenate([rng.integers(0, r, size=B * L) for r in rows]).astype(np.int32)
+    off = (np.arange(len(rows) * B + 1) * L).astype(np.int32)
+    toff = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int32)
+    out = torch.ops.batched_forward.forward([cu(np.concatenate(Ws))], [cu(toff)], [cu(off)], [cu(idx)], L, 8, False)
+    assert tuple(out.shape) == (B, len(rows), D)
+    assert np.array_equal(out.cpu().numpy(), O.embbag_fwd_batched(Ws, idx, off, B))
+
+
+def test_rwsadagrad_steps_torch_embeddingbag_grads_too():
+    """The optimizer accepts the UNCOALESCED sparse grads torch's own nn.EmbeddingBag emits (reference layout)."""
+    from dlrm_yx_b200 import rwsadagrad
+    torch.manual_seed(0)
+    E = torch.nn.EmbeddingBag(50, 16, mode="sum", sparse=True).cuda()
+    W0 = E.weight.detach().cpu().numpy().copy()
+    idx = torch.randint(0, 50, (200,), device="cuda")
+    off = torch.arange(0, 200, 4, device="cuda")
+    go = torch.randn(50, 16, device="cuda")
+    opt = rwsadagrad.RWSAdagrad(E.parameters(), lr=0.05)
+    E(idx, off).backward(go)
+    opt.step()
+    pk_i, pk_o = O.pack_batched([off.cpu().numpy()], [idx.cpu().numpy()])
+    art = O.sort_artifacts(pk_i, pk_o, 1, 50, [0])
+    gs = O.embbag_bwd_coalesced(go.cpu().numpy(), art, 16)
+    mom = np.zeros(50, np.float32)
+    O.rwsadagrad_update(W0, mom, art["unique"], gs, 0.05)
+    np.testing.assert_allclose(E.weight.detach().cpu().numpy(), W0, rtol=RT, atol=AT)
+    np.testing.assert_allclose(opt.state[E.weight]["momentum"].cpu().numpy(), mom, rtol=RT, atol=1e-9)
