@@ -121,7 +121,7 @@ class DLRM_Net(nn.Module):
                  emb_optimizer=embedding.Optimizer.SGD, emb_learning_rate=0.1, emb_eps=None, emb_init="auto",
                  fuse_sparse_arch=False):
         super().__init__()
-        if None in (m_spa, ln_emb, ln_bot, ln_top, arch_interaction_op):
+        if any(a is None for a in (m_spa, ln_emb, ln_bot, ln_top, arch_interaction_op)):
             return
         if ndevices > 1:
             sys.exit("single-process multi-GPU (parallel_forward) is not supported: launch one process per GPU")

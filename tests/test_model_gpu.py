@@ -79,7 +79,8 @@ def test_embedding_bag_module_forward_and_coalesced_grad(golden_dir, name):
         assert np.array_equal(out.detach().cpu().numpy(), g["pooled"][:, k, :])
         out.backward(cu(g["d_pooled"][:, k, :]))
         gr = E.weight.grad
-        assert gr.is_sparse and gr.is_coalesced()
+        assert gr.is_sparse          # autograd's accumulation drops the is_coalesced flag; the DATA is coalesced:
+        assert gr._indices().shape[1] == gr.coalesce()._indices().shape[1]
         assert np.array_equal(gr._indices()[0].cpu().numpy(), g["gco_idx_%d" % k])     # == reference coalesce()
         np.testing.assert_allclose(gr._values().cpu().numpy(), g["gco_val_%d" % k], rtol=RT, atol=AT)
 
