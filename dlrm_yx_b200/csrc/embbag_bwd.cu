@@ -3,9 +3,24 @@
 
 namespace dlrmx {
 
+template <typename T, int G>
+__device__ __forceinline__ T bshfl64(unsigned mask, T v, int src) {
+    unsigned long long u = (unsigned long long)v;
+    unsigned lo = __shfl_sync(mask, (unsigned)u, src, G);
+    unsigned hi = __shfl_sync(mask, (unsigned)(u >> 32), src, G);
+    return (T)(((unsigned long long)hi << 32) | lo);
+}
+
+// One group of G lanes per segment of kSeg sorted positions, walked as kSeg/G sub-tiles.  Per sub-tile the
+// metadata is fetched LANE-PARALLEL with coalesced loads (lane i: key, bag, is-last-of-run, gradient pointer and,
+// for run ends, the table-row / accumulator pointers), so the key -> bag -> pointer chain costs one round of
+// memory latency per G positions; positions are then consumed K at a time with K gradient rows (and the table
+// rows of the runs ending there) in flight per lane.
 template <int VEC, int G, int CH, int K>
-__global__ void __launch_bounds__(256, 2) bwd_update_kernel(const BwdParams P) {
+__global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(const BwdParams P) {
     const int gl = threadIdx.x & (G - 1);
+    const unsigned gmask = group_mask<G>();
+    const int gshift = (threadIdx.x & 31) & ~(G - 1);
     const int64_t seg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
     if (seg >= P.nseg) return;
     const int64_t p0 = seg * kSeg, p1 = min(P.N, p0 + kSeg);
@@ -13,83 +28,111 @@ __global__ void __launch_bounds__(256, 2) bwd_update_kernel(const BwdParams P) {
     const uint32_t* __restrict__ skey = P.skey;
     const int32_t* __restrict__ sbag = P.sbag;
 
-    bool owned = !(p0 > 0 && skey[p0 - 1] == skey[p0]);  // does the first run start in this segment?
+    bool owned = true;                       // does the first run START in this segment?
+    if (p0 > 0) owned = skey[p0 - 1] != skey[p0];
     RowVec<VEC> acc[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c) acc[c].zero();
 
-    for (int64_t pb = p0; pb < p1; pb += K) {
-        uint32_t kk[K + 1];
-        kk[0] = skey[pb];
-#pragma unroll
-        for (int j = 1; j <= K; ++j) kk[j] = (pb + j < P.N) ? skey[pb + j] : ~kk[j - 1];
+#pragma unroll 1
+    for (int64_t pt = p0; pt < p1; pt += G) {
+        const int nvalid = (int)min((int64_t)G, p1 - pt);
+        // ---- lane-parallel metadata ---------------------------------------------------------------------
+        const int64_t p = pt + gl;
+        bool last = false;
+        const float* gptr = nullptr;
+        float* wptr = nullptr;
+        float* mptr = nullptr;
+        if (gl < nvalid) {
+            const uint32_t key = skey[p];
+            const uint32_t knext = (p + 1 < P.N) ? skey[p + 1] : ~key;
+            const int bag = sbag[p];
+            last = knext != key;
+            const int t = bag / P.B;
+            const int b = bag - t * P.B;
+            gptr = P.grad + (int64_t)b * P.stride_b + (int64_t)t * P.stride_t;    // row start; col0 added after broadcast
+            if (last) {
+                const int64_t row = (int64_t)key - P.row_base[t];
+                wptr = P.tables[t] + row * P.D;
+                if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mptr = P.moms[t] + row;
+            }
+        }
+        const unsigned lastmask = (__ballot_sync(gmask, last) >> gshift);
 
-        RowVec<VEC> g[K][CH], w[K][CH];
-        float* wp[K];
-        float* mp[K];
-        float mo[K];
-        bool valid[K], last[K];
+        for (int j0 = 0; j0 < nvalid; j0 += K) {
+            RowVec<VEC> g[K][CH], w[K][CH];
+            float* wp[K];
+            float* mp[K];
+            float mo[K];
+            bool v[K], l[K];
 #pragma unroll
-        for (int j = 0; j < K; ++j) {
-            valid[j] = pb + j < p1;
-            last[j] = valid[j] && kk[j + 1] != kk[j];
-            wp[j] = nullptr;
-            mp[j] = nullptr;
-            mo[j] = 0.f;
-            if (valid[j]) {
-                const int bag = sbag[pb + j];
-                const int t = bag / P.B;
-                const int b = bag - t * P.B;
-                const float* gp = P.grad + (int64_t)b * P.stride_b + (int64_t)t * P.stride_t + col0;
+            for (int j = 0; j < K; ++j) {
+                const int jj = j0 + j;
+                v[j] = jj < nvalid;
+                l[j] = v[j] && ((lastmask >> jj) & 1u);
+                wp[j] = nullptr;
+                mp[j] = nullptr;
+                mo[j] = 0.f;
+                const float* gp = bshfl64<const float*, G>(gmask, gptr, jj & (G - 1)) + col0;
+                if (v[j]) {
 #pragma unroll
-                for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
-                if (last[j]) {
-                    const int64_t row = (int64_t)kk[j] - P.row_base[t];
-                    wp[j] = P.tables[t] + row * P.D + col0;
+                    for (int c = 0; c < CH; ++c)
+                        if (CH == 1 || col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
+                }
+                if (l[j]) {
+                    wp[j] = bshfl64<float*, G>(gmask, wptr, jj & (G - 1)) + col0;
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
                         if (CH == 1 || col0 + c * G * VEC < P.D) w[j][c].load(wp[j] + c * G * VEC);
                     if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-                        mp[j] = P.moms[t] + row;
+                        mp[j] = bshfl64<float*, G>(gmask, mptr, jj & (G - 1));
                         mo[j] = *mp[j];
                     }
                 }
             }
-        }
 #pragma unroll
-        for (int j = 0; j < K; ++j) {
-            if (valid[j]) {
+            for (int j = 0; j < K; ++j) {
+                if (v[j]) {
 #pragma unroll
-                for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].add(g[j][c]);
-                if (last[j]) {
-                    if (owned) apply_row<VEC, G, CH>(P, wp[j], mp[j], mo[j], w[j], acc, col0);
-                    else store_partial<VEC, G, CH>(P.head_partial, seg, P.D, col0, acc);
+                    for (int c = 0; c < CH; ++c)
+                        if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].add(g[j][c]);
+                    if (l[j]) {
+                        if (owned) apply_row<VEC, G, CH>(P, wp[j], mp[j], mo[j], w[j], acc, col0);
+                        else store_partial<VEC, G, CH>(P.head_partial, seg, P.D, col0, acc);
 #pragma unroll
-                    for (int c = 0; c < CH; ++c) acc[c].zero();
-                    owned = true;
-                } else if (pb + j == p1 - 1) {  // the segment ends inside a run
-                    store_partial<VEC, G, CH>(owned ? P.tail_partial : P.head_partial, seg, P.D, col0, acc);
+                        for (int c = 0; c < CH; ++c) acc[c].zero();
+                        owned = true;
+                    } else if (pt + j0 + j == p1 - 1) {  // the segment ends inside a run
+                        store_partial<VEC, G, CH>(owned ? P.tail_partial : P.head_partial, seg, P.D, col0, acc);
+                    }
                 }
             }
         }
     }
 }
 
-// Finishes runs that cross segment boundaries; one group per segment, most exit immediately.
+// Finishes runs that cross segment boundaries.  One group per segment; only the segment where a crossing run
+// STARTS does work: it adds, in ascending order, the head partials of the following segments the run covers.
+// Which segments those are is found lane-parallel: lane i tests whether segment s+i lies entirely inside the run
+// (two key loads), a ballot gives the length of the covered stretch, and the partial rows are then fetched
+// KF at a time -- so a hot row spanning hundreds of segments costs a few memory latencies per G segments.
 template <int VEC, int G, int CH>
 __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
     constexpr int KF = 8;
     const int gl = threadIdx.x & (G - 1);
+    const unsigned gmask = group_mask<G>();
+    const int gshift = (threadIdx.x & 31) & ~(G - 1);
     const int64_t seg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
     if (seg >= P.nseg) return;
     const int64_t p0 = seg * kSeg, p1 = min(P.N, p0 + kSeg);
     const uint32_t* __restrict__ skey = P.skey;
     if (p1 >= P.N) return;
     const uint32_t key = skey[p1 - 1];
-    if (skey[p1] != key) return;                                     // no run crosses my end
-    if (skey[p0] == key && p0 > 0 && skey[p0 - 1] == key) return;     // I am a middle segment
+    const uint32_t kafter = skey[p1];
+    const uint32_t kfirst = skey[p0];
+    const uint32_t kbefore = skey[p0 > 0 ? p0 - 1 : 0];
+    if (kafter != key) return;                                        // no run crosses my end
+    if (kfirst == key && p0 > 0 && kbefore == key) return;            // I am a middle segment
     const int col0 = gl * VEC;
 
     RowVec<VEC> acc[CH];
@@ -100,31 +143,39 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
             if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].load(tp + c * G * VEC);
     }
     bool done = false;
-    for (int64_t s = seg + 1; !done; s += KF) {
-        RowVec<VEC> h[KF][CH];
-        bool cont[KF];
-#pragma unroll
-        for (int j = 0; j < KF; ++j) {
-            const int64_t sj = s + j;
-            cont[j] = false;
-            if (sj < P.nseg) {
-                const float* hp = P.head_partial + sj * P.D + col0;
-#pragma unroll
-                for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < P.D) h[j][c].load(hp + c * G * VEC);
-                const int64_t e = min(P.N, (sj + 1) * kSeg);
-                cont[j] = e < P.N && skey[e - 1] == key && skey[e] == key;
-            }
+    int64_t s = seg + 1;
+    while (!done) {
+        // lane i: is segment s+i entirely inside the run, with the run continuing past its end?
+        const int64_t sj = s + gl;
+        const int64_t e = min(P.N, (sj + 1) * kSeg);
+        bool full = false;
+        if (sj < P.nseg && e < P.N) {
+            const uint32_t a = skey[e - 1], bnext = skey[e];
+            full = (a == key) & (bnext == key);
         }
+        const unsigned fullmask = (__ballot_sync(gmask, full) >> gshift) & ((G == 32) ? 0xffffffffu : ((1u << G) - 1u));
+        const int nfull = (fullmask == ((G == 32) ? 0xffffffffu : ((1u << G) - 1u))) ? G : (__ffs(~fullmask) - 1);
+        done = nfull < G;
+        const int cnt = done ? nfull + 1 : G;      // the stretch ends with the segment holding the run's tail piece
+        for (int q0 = 0; q0 < cnt; q0 += KF) {
+            RowVec<VEC> h[KF][CH];
 #pragma unroll
-        for (int j = 0; j < KF; ++j) {
-            if (!done) {
+            for (int j = 0; j < KF; ++j)
+                if (q0 + j < cnt) {
+                    const float* hp = P.head_partial + (s + q0 + j) * P.D + col0;
 #pragma unroll
-                for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].add(h[j][c]);
-                if (!cont[j]) done = true;
-            }
+                    for (int c = 0; c < CH; ++c)
+                        if (CH == 1 || col0 + c * G * VEC < P.D) h[j][c].load(hp + c * G * VEC);
+                }
+#pragma unroll
+            for (int j = 0; j < KF; ++j)
+                if (q0 + j < cnt) {
+#pragma unroll
+                    for (int c = 0; c < CH; ++c)
+                        if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].add(h[j][c]);
+                }
         }
+        s += cnt;
     }
     const int bag = P.sbag[p1 - 1];
     const int t = bag / P.B;
@@ -232,10 +283,7 @@ template <int VEC, int G, int CH>
 static int launch_update(const BwdParams& P, cudaStream_t st) {
     const int threads = 256;
     const unsigned blocks = (unsigned)ceil_div(P.nseg * G, threads);
-    if (get_tunable(DLRMX_TUNE_BWD_K) == 8 && CH == 1)
-        bwd_update_kernel<VEC, G, CH, 8><<<blocks, threads, 0, st>>>(P);
-    else
-        bwd_update_kernel<VEC, G, CH, (CH == 1 ? 4 : 2)><<<blocks, threads, 0, st>>>(P);
+    bwd_update_kernel<VEC, G, CH, (CH == 1 ? 4 : 2)><<<blocks, threads, 0, st>>>(P);
     int rc = check_launch("bwd_update");
     if (rc) return rc;
     bwd_fixup_kernel<VEC, G, CH><<<blocks, threads, 0, st>>>(P);

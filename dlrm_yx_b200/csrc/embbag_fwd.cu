@@ -2,128 +2,188 @@
 //
 // Replaces nn.EmbeddingBag(mode="sum") as driven by DLRM_Net.apply_emb (dlrm_s_pytorch.py:526-587),
 // the batched module call of dlrm_s_pytorch.py:589-591 and the yx kernel
-// (yx_modfs/table_batched_embeddings_cuda_yx.cu:251-315).  Not a translation of the latter: that
-// kernel gives one 16-B load in flight per lane and 32-bit addressing; here
-//   * a group of G = D/4 lanes (a full warp at D=128) owns K consecutive bags and walks them in
-//     LOCKSTEP: round r issues the r-th row of all K bags before any of them is consumed, so every
-//     lane keeps K independent 16-B `ld.global.nc.L1::no_allocate` row loads in flight -- the
-//     memory-level parallelism a random 512-B gather needs to approach HBM bandwidth (Criteo has one
-//     index per bag, so unrolling along the bag would give exactly one load in flight);
-//   * offsets / indices of the K bags are read with group-uniform (broadcast) loads: one 32-B sector
-//     serves 8 bags, and they stay L1-resident across rounds;
+// (yx_modfs/table_batched_embeddings_cuda_yx.cu:251-315).  Not a translation of the latter (one 16-B load in
+// flight per lane, 32-bit addressing, a serial offsets -> index -> row dependent chain per bag).  Here:
+//   * a group of G = D/4 lanes (a full warp at D=128) owns a TILE of G consecutive bags.  The tile's metadata is
+//     fetched lane-parallel with coalesced loads -- lane i reads offsets[bag_i], offsets[bag_i+1], the table
+//     pointer / row count of its bag and the bag's FIRST index -- so the offsets -> index -> pointer chain is
+//     paid once per G bags (two memory latencies), not once per bag;
+//   * the tile is then walked in batches of K bags in LOCKSTEP: the metadata of the K bags is broadcast with
+//     warp shuffles, round r issues the r-th row of all K bags before any is consumed (K independent 16-B
+//     `ld.global.nc.L1::no_allocate` loads in flight per lane) and the indices of round r+1 are requested
+//     before the rows of round r are consumed (index stream prefetch, mostly L1 hits: 8 indices per sector);
 //   * each bag is summed sequentially in index order with plain fp32 adds -> bit-exact with ATen;
-//   * 64-bit row addressing, per-table base pointers, strided output so pooled rows land directly
-//     in the [B, 1+T, D] interaction input (no torch.cat afterwards).
+//   * 64-bit row addressing, per-table base pointers, strided output so pooled rows land directly in the
+//     [B, 1+T, D] interaction input (no torch.cat afterwards).
 // HBM-bound: algorithmic bytes = N*D*4 (rows) + N*ib + T*B*ob + T*B*D*4 (pooled rows).
 #include "common.cuh"
 
 namespace dlrmx {
 
-template <int VEC, int G, int CH, int K, typename IdxT>
-__global__ void __launch_bounds__(256, (K * CH >= 8) ? 2 : 3)
+template <int G>
+__device__ __forceinline__ unsigned fwd_group_mask() {
+    if constexpr (G == 32) {
+        return 0xffffffffu;
+    } else {
+        return ((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1));
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ T shfl64(unsigned mask, T v, int src, int width) {
+    static_assert(sizeof(T) == 8, "shfl64 moves 8-byte values");
+    unsigned long long u = (unsigned long long)v;
+    unsigned lo = __shfl_sync(mask, (unsigned)u, src, width);
+    unsigned hi = __shfl_sync(mask, (unsigned)(u >> 32), src, width);
+    return (T)(((unsigned long long)hi << 32) | lo);
+}
+__device__ __forceinline__ int64_t shfl_idx(unsigned mask, int64_t v, int src, int width) {
+    return shfl64<int64_t>(mask, v, src, width);
+}
+__device__ __forceinline__ int32_t shfl_idx(unsigned mask, int32_t v, int src, int width) {
+    return __shfl_sync(mask, v, src, width);
+}
+
+// K bags in lockstep x U consecutive rows of each bag in flight; FULL: a tile is G bags (short bags, e.g. the
+// one-index-per-bag Criteo layout), otherwise a tile is one batch of K bags (long bags: more groups, and the
+// memory-level parallelism comes from unrolling ALONG the bag -- loads are issued U at a time, the adds still
+// happen one by one in index order).
+template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
+__global__ void __launch_bounds__(256, (K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2))
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag) {
+    constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
+    constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
-    const int64_t group = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
-    const int64_t bag0 = group * K;
-    if (bag0 >= total_bags) return;
+    const unsigned gmask = fwd_group_mask<G>();
+    const int64_t tile = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+    const int64_t tile_bag0 = tile * TILE;
+    if (tile_bag0 >= total_bags) return;      // whole group leaves together
     const int col0 = gl * VEC;
 
-    IdxT start[K];
-    int len[K];
-    int tk[K];
-    int maxlen = 0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const int64_t bag = bag0 + k;
-        if (bag < total_bags) {
+    // ---- lane-parallel metadata of the tile: lane i (< TILE) describes bag tile_bag0 + i ---------------
+    IdxT my_s = 0, my_ix = -1;
+    int my_len = 0;
+    const float* my_base = nullptr;
+    int64_t my_rows = 0;
+    {
+        const int64_t bag = tile_bag0 + gl;
+        if (gl < TILE && bag < total_bags) {
             const IdxT s = offsets[bag];
             const IdxT e = (bag + 1 < total_bags) ? offsets[bag + 1] : (IdxT)N;
-            start[k] = s;
-            len[k] = (int)(e - s);
-            tk[k] = (int)(bag / B);
-        } else {
-            start[k] = 0;
-            len[k] = 0;
-            tk[k] = 0;
+            const int t = (int)(bag / B);
+            my_base = tables[t];
+            my_rows = (table_rows != nullptr) ? table_rows[t] : (int64_t)0x7fffffffffffffffll;
+            my_s = s;
+            my_len = (int)(e - s);
+            if (my_len > 0) my_ix = indices[s];
         }
-        maxlen = max(maxlen, len[k]);
     }
 
-    RowVec<VEC> acc[K][CH];
+#pragma unroll 1
+    for (int b0 = 0; b0 < TILE; b0 += KB) {
+        if (tile_bag0 + b0 >= total_bags) break;
+        IdxT start[KB], ix[KB][U];
+        int len[KB];
+        const float* base[KB];
+        int64_t nrows[KB];
+        int maxlen = 0;
 #pragma unroll
-    for (int k = 0; k < K; ++k)
+        for (int k = 0; k < KB; ++k) {
+            start[k] = shfl_idx(gmask, my_s, b0 + k, G);
+            ix[k][0] = shfl_idx(gmask, my_ix, b0 + k, G);
+            len[k] = __shfl_sync(gmask, my_len, b0 + k, G);
+            base[k] = shfl64<const float*>(gmask, my_base, b0 + k, G);
+            nrows[k] = shfl64<int64_t>(gmask, my_rows, b0 + k, G);
+            maxlen = max(maxlen, len[k]);
+        }
 #pragma unroll
-        for (int c = 0; c < CH; ++c) acc[k][c].zero();
+        for (int k = 0; k < KB; ++k)
+#pragma unroll
+            for (int u = 1; u < U; ++u) ix[k][u] = (u < len[k]) ? indices[start[k] + u] : (IdxT)-1;
 
-    for (int r = 0; r < maxlen; ++r) {
-        IdxT ix[K];
+        RowVec<VEC> acc[KB][CH];
 #pragma unroll
-        for (int k = 0; k < K; ++k) ix[k] = (r < len[k]) ? indices[start[k] + r] : (IdxT)-1;
+        for (int k = 0; k < KB; ++k)
+#pragma unroll
+            for (int c = 0; c < CH; ++c) acc[k][c].zero();
 
-        RowVec<VEC> row[K][CH];
+        for (int r = 0; r < maxlen; r += U) {
+            RowVec<VEC> row[KB][U][CH];
+            bool live[KB][U];
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            if (ix[k] >= 0) {
-                if (table_rows != nullptr && (int64_t)ix[k] >= table_rows[tk[k]]) {
-                    if (err_flag != nullptr && gl == 0) atomicOr(err_flag, 1);
-                    ix[k] = -1;
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int k = 0; k < KB; ++k) {
+                    live[k][u] = r + u < len[k];
+                    if (live[k][u] && ((int64_t)ix[k][u] < 0 || (int64_t)ix[k][u] >= nrows[k])) {   // bad index
+                        if (err_flag != nullptr && gl == 0) atomicOr(err_flag, 1);
+                        live[k][u] = false;
+                    }
+                    if (live[k][u]) {
+                        const float* p = base[k] + (int64_t)ix[k][u] * D + col0;
+#pragma unroll
+                        for (int c = 0; c < CH; ++c)
+                            if (CH == 1 || col0 + c * G * VEC < D) row[k][u][c].load_stream(p + c * G * VEC);
+                    }
                 }
-            } else if (r < len[k]) {  // negative index in the data
-                if (err_flag != nullptr && gl == 0) atomicOr(err_flag, 1);
-            }
-            if (ix[k] >= 0) {
-                const float* p = tables[tk[k]] + (int64_t)ix[k] * D + col0;
+            // request the next rounds' indices before this round's rows are consumed
+            IdxT nix[KB][U];
+#pragma unroll
+            for (int k = 0; k < KB; ++k)
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    nix[k][u] = (r + U + u < len[k]) ? indices[start[k] + r + U + u] : (IdxT)-1;
+#pragma unroll
+            for (int k = 0; k < KB; ++k)
+#pragma unroll
+                for (int u = 0; u < U; ++u)            // sequential in index order: bit-exact with ATen
+                    if (live[k][u]) {
+                        if (psw == nullptr) {
+#pragma unroll
+                            for (int c = 0; c < CH; ++c)
+                                if (CH == 1 || col0 + c * G * VEC < D) acc[k][c].add(row[k][u][c]);
+                        } else {
+                            const float w = __ldg(psw + start[k] + r + u);
+#pragma unroll
+                            for (int c = 0; c < CH; ++c)
+                                if (CH == 1 || col0 + c * G * VEC < D) acc[k][c].add_scaled(row[k][u][c], w);
+                        }
+                    }
+#pragma unroll
+            for (int k = 0; k < KB; ++k)
+#pragma unroll
+                for (int u = 0; u < U; ++u) ix[k][u] = nix[k][u];
+        }
+
+#pragma unroll
+        for (int k = 0; k < KB; ++k) {
+            const int64_t bag = tile_bag0 + b0 + k;
+            if (bag < total_bags) {
+                const int64_t t = bag / B;
+                const int64_t b = bag - t * B;
+                float* o = out + b * stride_b + t * stride_t + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < D) row[k][c].load_stream(p + c * G * VEC);
+                    if (col0 + c * G * VEC < D) acc[k][c].store(o + c * G * VEC);
             }
-        }
-        if (psw == nullptr) {
-#pragma unroll
-            for (int k = 0; k < K; ++k)
-                if (ix[k] >= 0) {
-#pragma unroll
-                    for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < D) acc[k][c].add(row[k][c]);
-                }
-        } else {
-#pragma unroll
-            for (int k = 0; k < K; ++k)
-                if (ix[k] >= 0) {
-                    const float w = __ldg(psw + start[k] + r);
-#pragma unroll
-                    for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < D) acc[k][c].add_scaled(row[k][c], w);
-                }
-        }
-    }
-
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        const int64_t bag = bag0 + k;
-        if (bag < total_bags) {
-            const int64_t b = bag - (int64_t)tk[k] * B;
-            float* o = out + b * stride_b + (int64_t)tk[k] * stride_t + col0;
-#pragma unroll
-            for (int c = 0; c < CH; ++c)
-                if (col0 + c * G * VEC < D) acc[k][c].store(o + c * G * VEC);
         }
     }
 }
 
-template <int VEC, int G, int CH, int K, typename IdxT>
+template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, cudaStream_t st) {
     const int64_t total_bags = (int64_t)T * B;
-    const int64_t groups = ceil_div(total_bags, K);
+    constexpr int TILE = FULL ? G : ((K < G) ? K : G);
+    const int64_t groups = ceil_div(total_bags, TILE);   // one group of G lanes per tile of TILE bags
     const int threads = 256;
     const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
-    embbag_fwd_kernel<VEC, G, CH, K, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
+    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
         tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag);
     return check_launch("embbag_fwd");
 }
@@ -141,13 +201,19 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
                       "embbag_fwd: out must be 16-B aligned with strides multiple of 4 when D%%4==0");
     if ((int64_t)T * B == 0) return DLRMX_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    // Short bags (<= 2 indices on average, e.g. Criteo's one per bag): tiles of G bags, K in lockstep.
+    // Long bags: K bags per group, U rows of each in flight.  FWD_K tunable: 8 -> K=8 (short) / U=8 (long).
+    const bool short_bags = N <= 2 * (int64_t)T * B;
+    const int tune = get_tunable(DLRMX_TUNE_FWD_K);
+#define DLRMX_FWD_ARGS tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b, stride_t, err_flag, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                  \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                   \
-        if (CH_ == 1 && get_tunable(DLRMX_TUNE_FWD_K) == 4)                                            \
-            return launch_fwd<VEC_, G_, CH_, 4, IdxT>(tables, table_rows, indices, offsets, N, T, B, D, psw, \
-                                                      out, stride_b, stride_t, err_flag, st);          \
-        return launch_fwd<VEC_, G_, CH_, 8 / CH_, IdxT>(tables, table_rows, indices, offsets, N, T, B, D, \
-                                                        psw, out, stride_b, stride_t, err_flag, st);   \
+        if (short_bags) {                                                                              \
+            if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 8, 1, true, IdxT>(DLRMX_FWD_ARGS); \
+            return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);       \
+        }                                                                                              \
+        if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS); \
+        return launch_fwd<VEC_, G_, CH_, 2, (CH_ == 1 ? 4 : 2), false, IdxT>(DLRMX_FWD_ARGS);          \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
     DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)

@@ -114,8 +114,7 @@ def main():
     uniq = [int(ops.bwd_segments(sk)[2].item()) for sk, _ in sorted_batches]
     U = sum(uniq) / len(uniq)
     for opt, name in ((_lib.OPT_SGD, "sgd"), (_lib.OPT_RWSADAGRAD, "rwsadagrad")):
-        for k in (4, 8):
-            _lib.set_tunable(_lib.TUNE_BWD_K, k)
+        for k in (4,):
 
             def u():
                 sk, sb = sorted_batches[it[0] % nbatch]
