@@ -53,6 +53,7 @@ OPT_SGD = 0
 OPT_RWSADAGRAD = 1
 TUNE_FWD_K = 0
 TUNE_BWD_K = 1
+TUNE_IX_CUDACORE = 2   # 1: force the CUDA-core interaction kernels (default: 3xTF32 tensor-core kernels)
 
 _lib = None
 

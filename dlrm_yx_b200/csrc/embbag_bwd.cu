@@ -115,10 +115,10 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
 // STARTS does work: it adds, in ascending order, the head partials of the following segments the run covers.
 // Which segments those are is found lane-parallel: lane i tests whether segment s+i lies entirely inside the run
 // (two key loads), a ballot gives the length of the covered stretch, and the partial rows are then fetched
-// KF at a time -- so a hot row spanning hundreds of segments costs a few memory latencies per G segments.
+// up to 32 at a time -- so a hot row spanning hundreds of segments costs a few memory latencies per G segments.
 template <int VEC, int G, int CH>
 __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
-    constexpr int KF = 8;
+    constexpr int KF = (CH == 1) ? 32 : 8;   // partial rows in flight: the chain walk is pure latency
     const int gl = threadIdx.x & (G - 1);
     const unsigned gmask = group_mask<G>();
     const int gshift = (threadIdx.x & 31) & ~(G - 1);

@@ -198,6 +198,13 @@ static int launch_ix_bwd(const float* feat, int64_t fsb, int B, int F, int D, in
     return check_launch("interact_dot_bwd");
 }
 
+// tensor-core (3xTF32) kernels of interact_mma.cu; return 1 when they took the shape
+int interact_fwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int itself, float* out, int64_t ostride,
+                     cudaStream_t st, int* rc);
+int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int itself, const float* dout,
+                     int64_t dstride, float* dfeat, int64_t dfsb, cudaStream_t st, int* rc);
+enum { DLRMX_TUNE_IX_CUDACORE = 2 };   // tunable 2 = 1 forces the CUDA-core kernels (tests compare both)
+
 }  // namespace dlrmx
 
 extern "C" {
@@ -208,6 +215,10 @@ int dlrmx_interact_dot_fwd(const float* feat, int64_t feat_stride_b, int B, int 
     DLRMX_REQUIRE(out_stride >= D + tri_count(F, itself), "interact_dot_fwd: out_stride too small");
     if (B == 0) return DLRMX_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (get_tunable(DLRMX_TUNE_IX_CUDACORE) == 0) {
+        int rc = 0;
+        if (interact_fwd_mma(feat, feat_stride_b, B, F, D, itself, out, out_stride, st, &rc)) return rc;
+    }
     const int nb = (F + 3) / 4, nblocks = nb * (nb + 1) / 2;
     if (D % 4 == 0) {
         DLRMX_REQUIRE(feat_stride_b % 4 == 0 && ((uintptr_t)feat & 15) == 0,
@@ -230,6 +241,11 @@ int dlrmx_interact_dot_bwd(const float* feat, int64_t feat_stride_b, int B, int 
     DLRMX_REQUIRE(B >= 0 && F >= 1 && D >= 1, "interact_dot_bwd: bad sizes");
     if (B == 0) return DLRMX_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (get_tunable(DLRMX_TUNE_IX_CUDACORE) == 0) {
+        int rc = 0;
+        if (interact_bwd_mma(feat, feat_stride_b, B, F, D, itself, dout, dout_stride, dfeat, dfeat_stride_b, st, &rc))
+            return rc;
+    }
     RowGeom g;
     DLRMX_REQUIRE(row_geometry(D, &g) && g.ch == 1, "interact_dot_bwd: unsupported D=%d (D%%4==0 and D<=128, or D<=32)", D);
     if (g.vec == 4)

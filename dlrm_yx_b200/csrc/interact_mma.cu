@@ -1,0 +1,342 @@
+// Dot feature interaction on the tensor cores, fp32-accurate (3xTF32 split).  sm_100a.
+//
+// Replaces DLRM_Net.interact_features('dot') (dlrm_s_pytorch.py:627-659: cat -> bmm(T, T^t) -> tril_indices gather
+// -> cat) and its autograd backward, for F <= 32 features and D % 8 == 0 (the Kaggle / benchmark / Terabyte shapes:
+// F = 27, 9, 27; D = 16, 64, 128).  Other shapes take the CUDA-core kernels of interact.cu.
+//
+// One CTA of 4 warps owns one sample at a time (persistent loop over samples):
+//   forward : the F x D feature block is staged into shared memory with 16-byte cp.async copies (all in flight
+//             at once -- that is the memory-level parallelism), row stride D+4 floats so that the mma fragment
+//             loads T[g + 8r][k0 + t + 4h] hit 32 distinct banks.  Z = T T^t is a 32x32x D contraction done as
+//             m16n8k8 TF32 mma tiles, lower-triangle tiles only (6 of 8).  Because A and B are the SAME matrix,
+//             the 8 values a lane loads per k-step serve as both its A and its B fragments.
+//             fp32 accuracy: x = hi + lo with hi = tf32(x), lo = tf32(x - hi) (round-half-away);  Z += a_lo*b_hi + a_hi*b_lo + a_hi*b_hi
+//             (the dropped lo*lo term is 2^-22 relative), accumulated in fp32 -- meets the 1e-5 / 1e-6 bar.
+//   backward: dT = (dZ + dZ^t) T is a 32 x D x 32 contraction: the symmetric coefficient block S is built in shared
+//             memory from dR[:, D:], its fragments (hi/lo) are kept in registers for the whole sample, T is staged
+//             with row stride D+8 (bank-conflict-free B fragments), the result goes straight from the accumulator
+//             fragments to global memory (full 32-byte sectors), with the pass-through dR[:, :D] added to feature 0.
+// HBM traffic is the algorithmic minimum: B*F*D*4 in + B*(D+nz)*4 out (forward).
+#include "common.cuh"
+
+namespace dlrmx {
+
+// x = hi + lo with hi = x rounded to TF32 (10 explicit mantissa bits, round-half-away: add half an ulp to the
+// magnitude, clear the 13 low bits) and lo = (x - hi) rounded the same way.  Written with integer ops because
+// `cvt.rna.tf32.f32` expands to a 4-instruction sequence with an Inf/NaN guard on sm_100; the tensor core ignores
+// the 13 low operand bits, so `lo` needs only the add.  4 instructions per split instead of 9.  Finite inputs only.
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi)) + 0x1000u;
+}
+
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// all but the most recent group have landed
+__device__ __forceinline__ void cp_async_wait_prev() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+__host__ __device__ inline int tri_count_mma(int F, int itself) { return itself ? F * (F + 1) / 2 : F * (F - 1) / 2; }
+
+constexpr int kMmaWarps = 4;
+
+// ---------------------------------------------------------------------------------------------------------
+// forward: one CTA (4 warps) per sample, persistent loop.  The contraction dimension D is split across the
+// warps (warp w takes k-steps w, w+4, ...): every warp owns all six lower-triangle tiles for its k-steps,
+// writes its partial triangle to shared memory, and the four partials are added in a fixed order with
+// round-to-nearest adds (short accumulation chains inside the tensor core, deterministic result).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kMmaWarps * 32)
+interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
+                        float* __restrict__ out, int64_t ostride) {
+    extern __shared__ __align__(16) float smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int DS = D + 4;          // fragment loads T[g + 8r][k0 + t + 4h]: banks 4g + t, all distinct
+    const int nz = tri_count_mma(F, itself);
+    const int nzp = (nz + 3) & ~3;
+    // two tile buffers [F][DS]: the next sample is copied in (cp.async) while this one is being contracted
+    float* zpart = smem + 2 * F * DS + warp * nzp;        // this warp's partial triangle
+    const int dv = D >> 2;
+    const bool two_m = F > 16;
+    int rowoff[4];                                        // rows >= F only feed discarded outputs: alias row F-1
+#pragma unroll
+    for (int r = 0; r < 4; ++r) rowoff[r] = min(g + 8 * r, F - 1) * DS;
+    // where each accumulator element goes in the lower-triangle vector (torch.tril_indices order), -1 = dropped;
+    // fixed per lane, so computed once instead of per sample
+    int zdst[2][4][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int i = 16 * m + g + 8 * (q >> 1), j = 8 * n + 2 * t + (q & 1);
+                const bool keep = (n <= 2 * m + 1) && i < F && (itself ? j <= i : j < i);
+                zdst[m][n][q] = keep ? (itself ? i * (i + 1) / 2 + j : i * (i - 1) / 2 + j) : -1;
+            }
+
+    auto stage = [&](int64_t bb, int which) {
+        if (bb < B) {
+            const float* src = feat + bb * fsb;
+            float* dstt = smem + which * F * DS;
+            for (int f = warp; f < F; f += kMmaWarps)
+                for (int k4 = lane; k4 < dv; k4 += 32)
+                    cp_async16(dstt + f * DS + 4 * k4, src + (int64_t)f * D + 4 * k4);
+        }
+        cp_async_commit();
+    };
+    int buf = 0;
+    stage(blockIdx.x, 0);
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x, buf ^= 1) {
+        stage(b + gridDim.x, buf ^ 1);       // that buffer's last readers finished before the previous barrier
+        cp_async_wait_prev();
+        __syncthreads();
+        const float* tile = smem + buf * F * DS;
+        float* o = out + b * ostride;
+        for (int k = threadIdx.x; k < D; k += kMmaWarps * 32) o[k] = tile[k];     // R[:, 0:D] = x
+
+        float c[2][4][4];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int n = 0; n < 4; ++n)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) c[m][n][q] = 0.f;
+
+        for (int k0 = 8 * warp; k0 < D; k0 += 8 * kMmaWarps) {
+            uint32_t hi[4][2], lo[4][2];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) split_tf32(tile[rowoff[r] + k0 + t + 4 * h], hi[r][h], lo[r][h]);
+#pragma unroll
+            for (int m = 0; m < 2; ++m) {
+                if (m == 1 && !two_m) break;
+                const uint32_t ah[4] = {hi[2 * m][0], hi[2 * m + 1][0], hi[2 * m][1], hi[2 * m + 1][1]};
+                const uint32_t al[4] = {lo[2 * m][0], lo[2 * m + 1][0], lo[2 * m][1], lo[2 * m + 1][1]};
+#pragma unroll
+                // lower-triangle tiles only (n <= 2m+1); term-major order keeps the dependent mmas apart
+#pragma unroll
+                for (int n = 0; n < 4; ++n)
+                    if (n <= 2 * m + 1) mma_tf32(c[m][n], al, hi[n][0], hi[n][1]);
+#pragma unroll
+                for (int n = 0; n < 4; ++n)
+                    if (n <= 2 * m + 1) mma_tf32(c[m][n], ah, lo[n][0], lo[n][1]);
+#pragma unroll
+                for (int n = 0; n < 4; ++n)
+                    if (n <= 2 * m + 1) mma_tf32(c[m][n], ah, hi[n][0], hi[n][1]);
+            }
+        }
+        // accumulator fragments -> this warp's partial lower-triangle vector
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int n = 0; n < 4; ++n) {
+                if (n > 2 * m + 1) continue;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (zdst[m][n][q] >= 0) zpart[zdst[m][n][q]] = c[m][n][q];
+            }
+        __syncthreads();
+        const float* z0 = smem + 2 * F * DS;
+        for (int q = threadIdx.x; q < nz; q += kMmaWarps * 32)
+            o[D + q] = __fadd_rn(__fadd_rn(z0[q], z0[nzp + q]), __fadd_rn(z0[2 * nzp + q], z0[3 * nzp + q]));
+        // no barrier here: the partials are rewritten only after the next iteration's barrier
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// backward:  dfeat[b, i, :] = sum_j S[i][j] * feat[b, j, :]  (+ dR[b, :D] on i = 0),  S = dZ + dZ^t
+// One CTA per sample; the D output columns are split across the 4 warps in 8-column tiles.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kMmaWarps * 32, 4)
+interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
+                        const float* __restrict__ dout, int64_t dstride, float* __restrict__ dfeat, int64_t dfsb) {
+    extern __shared__ __align__(16) float smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int DS = D + 8;          // B fragments T[k0 + t (+4)][n0 + g]: banks 8t + g, all distinct
+    constexpr int SS = 36;         // A fragments S[g (+8)][k0 + t (+4)]: banks 4g + t, all distinct
+    constexpr int NT = 4;          // 8-column output tiles per warp and pass
+    const int nz = tri_count_mma(F, itself);
+    const int nzp = (nz + 3) & ~3;
+    // two stages of { feature tile [F][DS], dR[b, D:] (+ zero slot at [nzp]) }: the next sample streams in via
+    // cp.async while this one is contracted; S [32][SS] is single (rebuilt between the two barriers)
+    const int stage_floats = F * DS + nzp + 4;
+    float* S = smem + 2 * stage_floats;
+    const int dv = D >> 2;
+    const bool two_m = F > 16;
+    const int ksteps = (F + 7) >> 3;
+
+    // S[i][j] = dZ[max][min] (off-diagonal), 2 dZ[i][i] (diagonal, `itself` only), 0 outside F x F.  Each thread
+    // fills the same 8 entries for every sample: source slot and scale are computed once.
+    int ssrc[8];
+    float sscale[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const int e = threadIdx.x + u * kMmaWarps * 32;
+        const int i = e >> 5, j = e & 31;
+        ssrc[u] = nzp;               // the zero slot
+        sscale[u] = 1.f;
+        if (i < F && j < F) {
+            if (i == j) {
+                if (itself) { ssrc[u] = i * (i + 1) / 2 + i; sscale[u] = 2.f; }
+            } else {
+                const int hi_ = max(i, j), lo_ = min(i, j);
+                ssrc[u] = itself ? hi_ * (hi_ + 1) / 2 + lo_ : hi_ * (hi_ - 1) / 2 + lo_;
+            }
+        }
+    }
+    if (threadIdx.x < 2) smem[threadIdx.x * stage_floats + F * DS + nzp] = 0.f;
+
+    auto stage = [&](int64_t bb, int which) {
+        if (bb < B) {
+            const float* src = feat + bb * fsb;
+            float* dstt = smem + which * stage_floats;
+            for (int f = warp; f < F; f += kMmaWarps)
+                for (int k4 = lane; k4 < dv; k4 += 32)
+                    cp_async16(dstt + f * DS + 4 * k4, src + (int64_t)f * D + 4 * k4);
+            const float* dz = dout + bb * dstride + D;         // rows of dR are only 4-byte aligned
+            for (int q = threadIdx.x; q < nz; q += kMmaWarps * 32) cp_async4(dstt + F * DS + q, dz + q);
+        }
+        cp_async_commit();
+    };
+    int buf = 0;
+    stage(blockIdx.x, 0);
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x, buf ^= 1) {
+        cp_async_wait_all();                 // this sample's stage has landed (the only group in flight)
+        __syncthreads();                     // ... and every warp is done contracting the previous sample,
+        stage(b + gridDim.x, buf ^ 1);       // so its stage can be refilled while this one is worked on
+        const float* tile = smem + buf * stage_floats;
+        const float* zbuf = tile + F * DS;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = threadIdx.x + u * kMmaWarps * 32;
+            S[(e >> 5) * SS + (e & 31)] = zbuf[ssrc[u]] * sscale[u];
+        }
+        __syncthreads();
+
+        float* dst = dfeat + b * dfsb;
+        const float* dx = dout + b * dstride;
+        for (int nb = 8 * NT * warp; nb < D; nb += 8 * NT * kMmaWarps) {      // NT column tiles per pass
+            float c[NT][2][4];
+#pragma unroll
+            for (int n = 0; n < NT; ++n)
+#pragma unroll
+                for (int m = 0; m < 2; ++m)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) c[n][m][q] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                if (ks >= ksteps) break;
+                uint32_t ah[2][4], al[2][4];                 // A fragments of S for this k-step, split once
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    const int r0 = 16 * m + g, k0 = 8 * ks + t;
+                    split_tf32(S[r0 * SS + k0], ah[m][0], al[m][0]);
+                    split_tf32(S[(r0 + 8) * SS + k0], ah[m][1], al[m][1]);
+                    split_tf32(S[r0 * SS + k0 + 4], ah[m][2], al[m][2]);
+                    split_tf32(S[(r0 + 8) * SS + k0 + 4], ah[m][3], al[m][3]);
+                }
+                const int j0 = 8 * ks + t, j1 = j0 + 4;      // feature rows >= F contribute zero
+                const bool ok0 = j0 < F, ok1 = j1 < F;
+#pragma unroll
+                for (int n = 0; n < NT; ++n) {
+                    const int n0 = nb + 8 * n;
+                    if (n0 >= D) break;
+                    uint32_t bh0, bl0, bh1, bl1;
+                    split_tf32(ok0 ? tile[j0 * DS + n0 + g] : 0.f, bh0, bl0);
+                    split_tf32(ok1 ? tile[j1 * DS + n0 + g] : 0.f, bh1, bl1);
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        if (m == 1 && !two_m) break;
+                        mma_tf32(c[n][m], al[m], bh0, bh1);
+                        mma_tf32(c[n][m], ah[m], bl0, bl1);
+                        mma_tf32(c[n][m], ah[m], bh0, bh1);
+                    }
+                }
+            }
+#pragma unroll
+            for (int n = 0; n < NT; ++n) {
+                const int n0 = nb + 8 * n;
+                if (n0 >= D) break;
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    if (m == 1 && !two_m) break;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int i = 16 * m + g + 8 * h;
+                        if (i < F) {
+                            float2 v = make_float2(c[n][m][2 * h], c[n][m][2 * h + 1]);
+                            const int col = n0 + 2 * t;
+                            if (i == 0) {          // dense pass-through: R[:, 0:D] = x
+                                v.x = __fadd_rn(v.x, __ldg(dx + col));
+                                v.y = __fadd_rn(v.y, __ldg(dx + col + 1));
+                            }
+                            *reinterpret_cast<float2*>(dst + (int64_t)i * D + col) = v;
+                        }
+                    }
+                }
+            }
+        }
+        // no barrier here: S and the other stage are only written after the next iteration's first barrier
+    }
+}
+
+static int mma_grid(int B) {
+    const int64_t cap = (int64_t)kSMs * 12;      // persistent: a few CTAs per SM, each loops over samples
+    return (int)(B < cap ? B : cap);
+}
+
+// Returns 1 if the shape is handled here (and launches), 0 if the caller should use the CUDA-core kernel.
+int interact_fwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int itself, float* out, int64_t ostride,
+                     cudaStream_t st, int* rc) {
+    if (F > 32 || F < 2 || D % 8 != 0 || D > 512 || fsb % 4 != 0 || ((uintptr_t)feat & 15) != 0) return 0;
+    const int nz = tri_count_mma(F, itself);
+    const size_t smem = (2 * (size_t)F * (D + 4) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4;
+    if (smem > 200 * 1024) return 0;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(interact_fwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_done = true;
+    }
+    interact_fwd_mma_kernel<<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, out, ostride);
+    *rc = check_launch("interact_dot_fwd(mma)");
+    return 1;
+}
+
+int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int itself, const float* dout,
+                     int64_t dstride, float* dfeat, int64_t dfsb, cudaStream_t st, int* rc) {
+    if (F > 32 || F < 2 || D % 8 != 0 || D > 512 || fsb % 4 != 0 || dfsb % 2 != 0 || ((uintptr_t)feat & 15) != 0 ||
+        ((uintptr_t)dfeat & 7) != 0)
+        return 0;
+    const int nz = tri_count_mma(F, itself);
+    const size_t smem = (2 * ((size_t)F * (D + 8) + ((nz + 3) & ~3) + 4) + 32 * 36) * 4;
+    if (smem > 200 * 1024) return 0;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(interact_bwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_done = true;
+    }
+    interact_bwd_mma_kernel<<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, dout, dstride, dfeat,
+                                                                      dfsb);
+    *rc = check_launch("interact_dot_bwd(mma)");
+    return 1;
+}
+
+}  // namespace dlrmx
