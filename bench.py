@@ -38,7 +38,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU mini-batch (default: the config's)")
     ap.add_argument("--global-batch", type=int, default=0, help="fix the GLOBAL batch (strong scaling)")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (debug only; marks the run)")
-    ap.add_argument("--mlp", default="tf32", choices=["tf32", "fp32", "bf16"])
+    ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
+                    help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
     ap.add_argument("--sharder", default="greedy")
     ap.add_argument("--optimizer", default="rwsadagrad", choices=["rwsadagrad", "sgd"])
     ap.add_argument("--nbatches", type=int, default=8, help="distinct synthetic batches cycled through")
@@ -162,6 +163,9 @@ def build_model(args, cfg, W):
     m = dlrm_net.DLRM_Net(D, np.array(cfg["rows"]), ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
                           sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True, sharder=args.sharder,
                           emb_optimizer=kind, emb_learning_rate=lr, emb_init="device").cuda()
+    if args.mlp == "fused-bf16":
+        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd")
+        return m, None
     dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
     if W > 1:
         from dlrm_yx_b200 import extend_distributed as ext
@@ -201,9 +205,13 @@ def run_ours(args):
         with autocast:
             p = m(X, off, idx)
         loss = m.loss_fn(p.float(), tgt)
-        opt.zero_grad(set_to_none=True)
-        loss.backward()
-        opt.step()
+        if opt is None:
+            loss.backward()
+            m.step_mlps()
+        else:
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
         return loss
 
     def sync():
@@ -340,7 +348,8 @@ def main():
             calls, ms = r["prof"][name]
             kern[name] = {"ms": round(ms, 4), "calls_per_step": calls / K, "algorithmic_MB": round(nbytes / 1e6, 1),
                           "GBps": round(nbytes / ms / 1e6, 1), "frac": round(nbytes / ms / 1e6 / peak, 4)}
-    for name in ("bwd_sort", "interact_fwd", "interact_bwd", "a2a_unpack", "a2a_pack_grad"):
+    for name in ("bwd_sort", "interact_fwd", "interact_bwd", "a2a_unpack", "a2a_pack_grad", "relu_bwd_bias_grad",
+                 "dense_opt"):
         if name in r["prof"]:
             kern[name] = {"ms": round(r["prof"][name][1], 4), "calls_per_step": r["prof"][name][0] / K}
     f = kern["embbag_fwd"]
@@ -348,7 +357,8 @@ def main():
         "metric": "DLRM train samples/sec", "value": Bg * K / (r["ms_dev"] / 1e3), "unit": "samples/s",
         "n_gpus": W, "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / K,
         "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
-        "dtype": "fp32 (embedding/interaction/optimizer fp32; MLP GEMMs %s)" % args.mlp, "data": "synthetic",
+        "dtype": "fp32 (embedding/interaction/sparse optimizer fp32; MLP GEMMs %s)"
+                 % {"fused-bf16": "bf16 in / fp32 accumulate"}.get(args.mlp, args.mlp), "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, W, Bg), "global_batch": Bg, "per_gpu_batch": lb,
                    "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder), "
                    "data-parallel MLPs (DDP), NCCL all-to-all" % (W, args.sharder),

@@ -1,0 +1,149 @@
+// Elementwise / reduction kernels around the MLP-tower GEMMs (create_mlp / apply_mlp, dlrm_s_pytorch.py:227-265,
+// 518-524) and the dense half of the optimizers (torch.optim.SGD, dlrm_s_pytorch.py:1640; RWSAdagrad.step dense
+// branch, optim/rwsadagrad.py:115-118).  sm_100a.
+//
+// The GEMMs themselves are plain library GEMMs on the tensor cores (bf16 in, fp32 accumulate, bias + ReLU in the
+// cuBLASLt epilogue); what PyTorch would add around them -- ReLU backward, bias-gradient reduction, dtype casts, 4
+// optimizer kernels per parameter tensor -- is fused here into two HBM-bound passes:
+//   relu_bwd_bias_grad : dz = dy * (y > 0) (bf16) and the column sums of dz (the bias gradient) in ONE read of dy, y:
+//                        algorithmic bytes 3 * B*N*2; column sums are per-row-chunk partials added later in a fixed
+//                        order (deterministic).
+//   dense_adagrad/sgd  : ONE launch over the flat parameter buffer of all layers: acc += g^2; p -= lr*g/(sqrt(acc)+eps)
+//                        (or p -= lr*g), refreshes the bf16 shadow the GEMMs read, and clears g for the next step:
+//                        20 bytes per parameter.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace dlrmx {
+
+constexpr int kRbThreads = 256;
+constexpr int kRbRowLanes = 8;                     // row lanes per CTA
+constexpr int kRbColVecs = kRbThreads / kRbRowLanes;  // 32 column vectors of 8 bf16 = 256 columns per CTA
+
+struct alignas(16) Bf16x8 {
+    __nv_bfloat162 v[4];
+};
+
+__global__ void __launch_bounds__(kRbThreads)
+relu_bwd_bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                          __nv_bfloat16* __restrict__ dz, float* __restrict__ db_partial, int B, int N,
+                          int rows_per_chunk, int relu) {
+    __shared__ float red[kRbRowLanes][kRbColVecs * 8 + 8];
+    const int cv = threadIdx.x % kRbColVecs, rl = threadIdx.x / kRbColVecs;
+    const int col = (blockIdx.x * kRbColVecs + cv) * 8;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(B, r0 + rows_per_chunk);
+    float s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = 0.f;
+    if (col < N) {
+#pragma unroll 4
+        for (int r = r0 + rl; r < r1; r += kRbRowLanes) {
+            const size_t off = (size_t)r * N + col;
+            Bf16x8 g = *reinterpret_cast<const Bf16x8*>(dy + off);
+            if (relu) {
+                const Bf16x8 a = *reinterpret_cast<const Bf16x8*>(y + off);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float2 av = __bfloat1622float2(a.v[i]);
+                    float2 gv = __bfloat1622float2(g.v[i]);
+                    gv.x = av.x > 0.f ? gv.x : 0.f;
+                    gv.y = av.y > 0.f ? gv.y : 0.f;
+                    g.v[i] = __float22bfloat162_rn(gv);
+                }
+                *reinterpret_cast<Bf16x8*>(dz + off) = g;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float2 gv = __bfloat1622float2(g.v[i]);
+                s[2 * i] += gv.x;
+                s[2 * i + 1] += gv.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[rl][cv * 8 + i] = s[i];
+    __syncthreads();
+    for (int c = threadIdx.x; c < kRbColVecs * 8; c += kRbThreads) {
+        const int gc = blockIdx.x * kRbColVecs * 8 + c;
+        if (gc < N) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < kRbRowLanes; ++q) t += red[q][c];
+            db_partial[(size_t)blockIdx.y * N + gc] = t;
+        }
+    }
+}
+
+// mode 0: SGD  p -= lr * g ;  mode 1: Adagrad  acc += g*g ; p -= lr * g / (sqrt(acc) + eps)
+__global__ void __launch_bounds__(256)
+dense_opt_kernel(int mode, float* __restrict__ p, float* __restrict__ acc, float* __restrict__ g,
+                 __nv_bfloat16* __restrict__ shadow, int64_t n, float lr, float eps, float gscale) {
+    const int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i4 >= n) return;
+    if (i4 + 4 <= n) {
+        float4 pv = *reinterpret_cast<float4*>(p + i4);
+        float4 gv = *reinterpret_cast<float4*>(g + i4);
+        gv.x *= gscale; gv.y *= gscale; gv.z *= gscale; gv.w *= gscale;
+        if (mode == 1) {
+            float4 av = *reinterpret_cast<float4*>(acc + i4);
+            av.x = __fmaf_rn(gv.x, gv.x, av.x); av.y = __fmaf_rn(gv.y, gv.y, av.y);
+            av.z = __fmaf_rn(gv.z, gv.z, av.z); av.w = __fmaf_rn(gv.w, gv.w, av.w);
+            *reinterpret_cast<float4*>(acc + i4) = av;
+            pv.x -= lr * __fdiv_rn(gv.x, __fsqrt_rn(av.x) + eps); pv.y -= lr * __fdiv_rn(gv.y, __fsqrt_rn(av.y) + eps);
+            pv.z -= lr * __fdiv_rn(gv.z, __fsqrt_rn(av.z) + eps); pv.w -= lr * __fdiv_rn(gv.w, __fsqrt_rn(av.w) + eps);
+        } else {
+            pv.x -= lr * gv.x; pv.y -= lr * gv.y; pv.z -= lr * gv.z; pv.w -= lr * gv.w;
+        }
+        *reinterpret_cast<float4*>(p + i4) = pv;
+        *reinterpret_cast<float4*>(g + i4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (shadow != nullptr) {
+            *reinterpret_cast<__nv_bfloat162*>(shadow + i4) = __floats2bfloat162_rn(pv.x, pv.y);
+            *reinterpret_cast<__nv_bfloat162*>(shadow + i4 + 2) = __floats2bfloat162_rn(pv.z, pv.w);
+        }
+    } else {
+        for (int64_t i = i4; i < n; ++i) {
+            const float gv = g[i] * gscale;
+            float pv = p[i];
+            if (mode == 1) {
+                const float av = __fmaf_rn(gv, gv, acc[i]);
+                acc[i] = av;
+                pv -= lr * __fdiv_rn(gv, __fsqrt_rn(av) + eps);
+            } else {
+                pv -= lr * gv;
+            }
+            p[i] = pv;
+            g[i] = 0.f;
+            if (shadow != nullptr) shadow[i] = __float2bfloat16_rn(pv);
+        }
+    }
+}
+
+}  // namespace dlrmx
+
+extern "C" {
+int dlrmx_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db_partial, int B, int N, int chunks,
+                             int relu, dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(B >= 0 && N > 0 && N % 8 == 0 && chunks >= 1, "relu_bwd_bias_grad: need N %% 8 == 0, chunks >= 1");
+    DLRMX_REQUIRE((((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dz) & 15) == 0, "relu_bwd_bias_grad: 16-B alignment");
+    const int rows_per_chunk = (int)ceil_div(B > 0 ? B : 1, chunks);
+    dim3 grid((unsigned)ceil_div(N, kRbColVecs * 8), (unsigned)chunks);
+    relu_bwd_bias_grad_kernel<<<grid, kRbThreads, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dz, db_partial, B, N, rows_per_chunk, relu);
+    return check_launch("relu_bwd_bias_grad");
+}
+
+int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
+                    float eps, float grad_scale, dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(mode == 0 || (mode == 1 && acc != nullptr), "dense_opt: mode 0 (sgd) or 1 (adagrad, needs acc)");
+    DLRMX_REQUIRE(n >= 0 && (((uintptr_t)params | (uintptr_t)grads | (uintptr_t)acc | (uintptr_t)shadow_bf16) & 15) == 0,
+                  "dense_opt: buffers must be 16-B aligned");
+    if (n == 0) return DLRMX_OK;
+    const unsigned blocks = (unsigned)ceil_div(ceil_div(n, 4), 256);
+    dense_opt_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(mode, params, acc, grads, (__nv_bfloat16*)shadow_bf16, n,
+                                                             lr, eps, grad_scale);
+    return check_launch("dense_opt");
+}
+}

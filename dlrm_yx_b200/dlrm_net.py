@@ -177,6 +177,20 @@ class DLRM_Net(nn.Module):
     def apply_mlp(self, x, layers):
         return layers(x)
 
+    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10):
+        """Replaces the two nn.Sequential towers by FusedMLP (bf16 tensor-core GEMMs with fused epilogues, flat
+        parameter buffers, one-kernel optimizer step).  After this, call `step_mlps()` instead of putting the tower
+        parameters into an outer optimizer."""
+        from . import mlp
+        self.bot_l = mlp.FusedMLP(self.bot_l, lr, optimizer, eps)
+        self.top_l = mlp.FusedMLP(self.top_l, lr, optimizer, eps)
+        return self
+
+    def step_mlps(self):
+        w = max(ext_dist.my_size, 1)
+        self.bot_l.step(w)
+        self.top_l.step(w)
+
     def apply_emb(self, lS_o, lS_i):
         """List of T pooled tensors [B, D] (dlrm_s_pytorch.py:526-587)."""
         ly = []

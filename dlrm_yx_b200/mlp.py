@@ -1,0 +1,150 @@
+"""MLP towers on the tensor cores, with the reference's construction (create_mlp, dlrm_s_pytorch.py:227-265) and
+call shape (apply_mlp: `layers(x)`, 518-524).
+
+`FusedMLP(sequential, ...)` takes over the Linear layers that create_mlp built (same numpy-initialised weights):
+  * all weights and biases of the tower live in ONE flat fp32 master buffer (+ one flat gradient buffer, one flat
+    Adagrad accumulator, one flat bf16 shadow that the GEMMs read);
+  * forward per layer = one tensor-core GEMM, bf16 operands, fp32 accumulate, bias + ReLU in the GEMM epilogue
+    (a plain library GEMM: cuBLASLt through torch);
+  * backward per layer = one fused pass dz = dy*(y>0) + bias-gradient partial sums (dlrmx_relu_bwd_bias_grad), then
+    the two GEMMs dW = dz^t x (fp32 out, written straight into the flat gradient buffer) and dx = dz W;
+  * `step()` = (all-reduce of the flat gradient buffer when data-parallel, the reference wraps the towers in DDP,
+    dlrm_s_pytorch.py:1626-1633) + ONE kernel for the whole tower (dlrmx_dense_opt): SGD, or the dense Adagrad branch
+    of RWSAdagrad (optim/rwsadagrad.py:115-118), which also refreshes the bf16 shadow and clears the gradients.
+Layers whose output width is not a multiple of 8 (the final 256 -> 1 sigmoid layer) run as ordinary fp32 torch ops on
+views of the same flat buffers.  Input widths are zero-padded to a multiple of 8 (13 -> 16, 479 -> 480).
+
+Precision: bf16 operands / fp32 accumulation -- looser than the reference's fp32 cuBLAS and stated as such by
+bench.py; parity tests use the unfused fp32 towers.
+"""
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+from torch import nn
+
+from . import _lib, ops
+
+
+def _ceil(x, m):
+    return (x + m - 1) // m * m
+
+
+class _Layer:
+    pass
+
+
+class _LinearAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, anchor, mlp, li):
+        L = mlp.layers[li]
+        hb = h if h.dtype == torch.bfloat16 else h.to(torch.bfloat16)
+        if hb.shape[1] != L.K_pad:
+            padded = hb.new_zeros((hb.shape[0], L.K_pad))
+            padded[:, :L.K].copy_(hb)
+            hb = padded
+        hb = hb.contiguous()
+        if L.act == "relu":
+            y = torch._addmm_activation(L.b_shadow, hb, L.w_shadow.t())
+        else:
+            y = torch.addmm(L.b_shadow, hb, L.w_shadow.t())
+        ctx.mlp, ctx.li = mlp, li
+        ctx.save_for_backward(hb, y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        hb, y = ctx.saved_tensors
+        L = ctx.mlp.layers[ctx.li]
+        dyb = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
+        dyb = dyb.contiguous()
+        dz, part = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"))
+        torch.sum(part, dim=0, out=L.gb)
+        L.gW.copy_(torch.mm(dz.t(), hb, out_dtype=torch.float32))
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.mm(dz, L.w_shadow)
+            if L.K_pad != L.K:
+                dx = dx[:, :L.K]
+        return dx, None, None, None
+
+
+class FusedMLP(nn.Module):
+    def __init__(self, sequential, lr, optimizer="adagrad", eps=1e-10, initial_accumulator_value=0.0):
+        super().__init__()
+        mods = list(sequential)
+        if len(mods) % 2 or not all(isinstance(m, nn.Linear) for m in mods[0::2]):
+            raise ValueError("FusedMLP expects the Linear/activation pairs that create_mlp builds")
+        self.lr, self.eps = float(lr), float(eps)
+        self.mode = {"sgd": 0, "adagrad": 1, "rwsadagrad": 1}[optimizer]
+        dev = mods[0].weight.device
+        if dev.type != "cuda":
+            raise _lib.DlrmxError("FusedMLP needs CUDA parameters (no CPU fallback)")
+        self.layers, off = [], 0
+        for lin, act in zip(mods[0::2], mods[1::2]):
+            L = _Layer()
+            L.N, L.K = lin.weight.shape
+            L.act = "relu" if isinstance(act, nn.ReLU) else ("sigmoid" if isinstance(act, nn.Sigmoid) else None)
+            if L.act is None:
+                raise ValueError("unsupported activation %r" % act)
+            L.fused = (L.N % 8 == 0) and L.act == "relu"
+            L.K_pad = _ceil(L.K, 8) if L.fused else L.K
+            L.w_off, off = off, _ceil(off + L.N * L.K_pad, 8)
+            L.b_off, off = off, _ceil(off + L.N, 8)
+            self.layers.append(L)
+        self.numel = off
+        master = torch.zeros(off, dtype=torch.float32, device=dev)
+        for L, lin in zip(self.layers, mods[0::2]):
+            master[L.w_off:L.w_off + L.N * L.K_pad].view(L.N, L.K_pad)[:, :L.K].copy_(lin.weight.data)
+            master[L.b_off:L.b_off + L.N].copy_(lin.bias.data)
+        self.master = nn.Parameter(master, requires_grad=False)       # state_dict: one flat fp32 tensor per tower
+        self.register_buffer("acc", torch.full_like(master, float(initial_accumulator_value)))
+        self.register_buffer("grad", torch.zeros_like(master), persistent=False)
+        self.register_buffer("shadow", master.to(torch.bfloat16), persistent=False)
+        self._anchor = torch.zeros(1, device=dev, requires_grad=True)  # makes every layer's backward run
+        self._bind()
+
+    def _bind(self):
+        for L in self.layers:
+            nW = L.N * L.K_pad
+            L.w_shadow = self.shadow[L.w_off:L.w_off + nW].view(L.N, L.K_pad)
+            L.b_shadow = self.shadow[L.b_off:L.b_off + L.N]
+            L.gW = self.grad[L.w_off:L.w_off + nW].view(L.N, L.K_pad)
+            L.gb = self.grad[L.b_off:L.b_off + L.N]
+            if not L.fused:     # plain fp32 torch layer on views of the flat buffers
+                L.w_leaf = self.master.data[L.w_off:L.w_off + nW].view(L.N, L.K_pad).requires_grad_()
+                L.b_leaf = self.master.data[L.b_off:L.b_off + L.N].requires_grad_()
+                L.w_leaf.grad, L.b_leaf.grad = L.gW, L.gb
+
+    def _apply(self, fn, *args, **kwargs):       # .to()/.cuda() re-allocate the flat buffers: re-create the views
+        out = super()._apply(fn, *args, **kwargs)
+        self._anchor = torch.zeros(1, device=self.master.device, requires_grad=True)
+        self._bind()
+        return out
+
+    def weight(self, i):
+        """fp32 [N, K] view of layer i's weight (checkpoint / inspection)."""
+        L = self.layers[i]
+        return self.master.data[L.w_off:L.w_off + L.N * L.K_pad].view(L.N, L.K_pad)[:, :L.K]
+
+    def bias(self, i):
+        L = self.layers[i]
+        return self.master.data[L.b_off:L.b_off + L.N]
+
+    def forward(self, x):
+        h = x
+        for i, L in enumerate(self.layers):
+            if L.fused:
+                h = _LinearAct.apply(h, self._anchor, self, i)
+            else:
+                z = F.linear(h.float(), L.w_leaf, L.b_leaf)
+                h = torch.sigmoid(z) if L.act == "sigmoid" else torch.relu(z)
+        return h if h.dtype == torch.float32 else h.float()
+
+    @torch.no_grad()
+    def step(self, world_size=1):
+        scale = 1.0
+        if world_size > 1:
+            dist.all_reduce(self.grad)
+            scale = 1.0 / world_size          # DDP averages the replicas' gradients
+        ops.dense_opt(self.mode, self.master.data, self.acc if self.mode == 1 else None, self.grad, self.shadow,
+                      self.lr, self.eps, scale)

@@ -263,3 +263,26 @@ def rows_update(optimizer, weight, mom, rows, gsum, lr, eps=0.0):
     rc = _lib.load().dlrmx_rows_update(optimizer, weight.data_ptr(), _ptr(mom), rows.data_ptr(), gsum.data_ptr(),
                                        U, D, float(lr), float(eps), _stream())
     _lib.check(rc, "dlrmx_rows_update")
+
+
+def relu_bwd_bias_grad(dy, y, relu=True, chunks=64):
+    """(dz bf16 [B,N], db_partial fp32 [chunks,N]): dz = dy * (y > 0) and per-chunk column sums of dz, one pass."""
+    _need_cuda(dy, y)
+    B, N = dy.shape
+    dz = torch.empty_like(dy) if relu else dy
+    part = torch.empty((chunks, N), dtype=torch.float32, device=dy.device)
+    with _timed("relu_bwd_bias_grad"):
+        rc = _lib.load().dlrmx_relu_bwd_bias_grad(dy.data_ptr(), y.data_ptr(), dz.data_ptr(), part.data_ptr(), B, N,
+                                                  chunks, int(relu), _stream())
+        _lib.check(rc, "dlrmx_relu_bwd_bias_grad")
+    return dz, part
+
+
+def dense_opt(mode, params, acc, grads, shadow, lr, eps=0.0, grad_scale=1.0):
+    """One launch over a flat fp32 parameter buffer: SGD (mode 0) or Adagrad (mode 1); refreshes the bf16 shadow and
+    clears the gradients."""
+    _need_cuda(params, acc, grads, shadow)
+    with _timed("dense_opt"):
+        rc = _lib.load().dlrmx_dense_opt(mode, params.data_ptr(), _ptr(acc), grads.data_ptr(), _ptr(shadow),
+                                         params.numel(), float(lr), float(eps), float(grad_scale), _stream())
+        _lib.check(rc, "dlrmx_dense_opt")

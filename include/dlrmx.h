@@ -161,6 +161,21 @@ int dlrmx_interact_dot_bwd(const float* feat, int64_t feat_stride_b, int B, int 
                            float* dfeat, int64_t dfeat_stride_b, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * MLP towers (create_mlp / apply_mlp, dlrm_s_pytorch.py:227-265, 518-524): fused passes around the
+ * tensor-core GEMMs, and the dense half of the optimizers.
+ * relu_bwd_bias_grad: dz = dy * (y > 0) (bf16 [B,N], skipped when relu == 0) and per-row-chunk column
+ *   sums of dz into db_partial [chunks, N] fp32 (the bias gradient is their sum over chunks).
+ * dense_opt: ONE launch over a flat parameter buffer: mode 0 = torch.optim.SGD (dlrm_s_pytorch.py:1640)
+ *   p -= lr*g ; mode 1 = Adagrad, the dense branch of RWSAdagrad.step (optim/rwsadagrad.py:115-118)
+ *   acc += g*g ; p -= lr * g / (sqrt(acc) + eps).  g is scaled by grad_scale first and cleared afterwards;
+ *   shadow_bf16 (optional) receives the bf16 copy of p that the GEMMs read.
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_relu_bwd_bias_grad(const void* dy_bf16, const void* y_bf16, void* dz_bf16, float* db_partial, int B,
+                             int N, int chunks, int relu, dlrmx_stream_t stream);
+int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
+                    float eps, float grad_scale, dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Model-parallel exchange helpers.  Replaces the cat / split / contiguous copies around
  * dist.all_to_all_single in extend_distributed.py:405-508 (All2All_Req / All2All_Wait).
  * a2a_unpack: recv buffer = concat over source ranks p of [lb, T_p, D]  ->  dst [lb, F, D] features

@@ -1,0 +1,138 @@
+"""FusedMLP (bf16 tensor-core towers) against the fp32 torch towers that create_mlp builds, and the fused dense
+optimizer kernel against the reference formulas.  bf16 operands with fp32 accumulation: outputs / gradients are
+compared as stated in the test docstring (the fp32 parity bars apply to the unfused towers, which the
+golden-vector tests use).  The optimizer kernel itself is fp32 and held to 1e-6."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _need_gpu():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+
+def make_tower(ln, sigmoid_layer):
+    from dlrm_yx_b200 import dlrm_net
+    np.random.seed(3)
+    return dlrm_net.DLRM_Net.create_mlp(None, np.array(ln), sigmoid_layer).cuda()
+
+
+def scale_close(a, b, tol):
+    """Relative Frobenius error.  (Max-abs is the wrong yardstick for gradients through ReLU: a pre-activation that
+    rounds across zero in bf16 flips its gate and moves single gradient entries by a full |dy*w|.)"""
+    a, b = a.float(), b.float()
+    err, ref = (a - b).norm().item(), b.norm().item()
+    assert err <= tol * ref + 1e-6, (err, ref)
+
+
+def emulate(fused, x, go):
+    """fp32 torch restatement of the tower WITH the bf16 roundings FusedMLP applies (operands and stored activations /
+    gradients rounded to bf16, products accumulated in fp32): isolates kernel / plumbing errors from rounding."""
+    bf = torch.bfloat16
+    saved, h = [], x
+    for i, L in enumerate(fused.layers):
+        if L.fused:
+            hb = h.to(bf).float()
+            y = torch.relu(hb @ fused.weight(i).to(bf).float().t() + fused.bias(i).to(bf).float()).to(bf).float()
+            saved.append((hb, y))
+            h = y
+        else:
+            hl = h.float().detach().requires_grad_()
+            W, b = fused.weight(i).clone().requires_grad_(), fused.bias(i).clone().requires_grad_()
+            h = torch.sigmoid(torch.nn.functional.linear(hl, W, b))
+            saved.append((hl, W, b))
+    out, grads, dy = h, [None] * len(fused.layers), go
+    for i in reversed(range(len(fused.layers))):
+        L = fused.layers[i]
+        if L.fused:
+            hb, y = saved[i]
+            dz = dy.to(bf).float() * (y > 0)
+            grads[i] = (dz.t() @ hb, dz.sum(0))
+            dy = (dz @ fused.weight(i).to(bf).float()).to(bf).float()
+        else:
+            hl, W, b = saved[i]
+            out.backward(dy)
+            grads[i], dy = (W.grad, b.grad), hl.grad
+    return out.detach(), dy, grads
+
+
+@pytest.mark.parametrize("ln,sig", [([13, 64, 32, 16], -1), ([479, 128, 64, 1], 2), ([16, 8], -1),
+                                    ([13, 512, 256, 128], -1)])
+def test_fused_mlp_matches_fp32_tower(ln, sig):
+    """Two bars: (1) against the same-rounding fp32 emulation: 5e-3 relative Frobenius error everywhere (what is left
+    is accumulation order and 1-ulp bf16 ties); (2) against the true fp32 tower create_mlp builds: forward 1e-2; the
+    gradients 0.15 -- a pre-activation that bf16 rounding moves across zero flips its ReLU gate and changes single
+    gradient entries by a full |dy*w|, so the fp32 gradient bar is a sanity bound, not a precision claim."""
+    from dlrm_yx_b200 import mlp
+    ref = make_tower(ln, sig)
+    fused = mlp.FusedMLP(make_tower(ln, sig), lr=0.1, optimizer="sgd")
+    B = 257
+    torch.manual_seed(0)
+    x = torch.rand(B, ln[0], device="cuda")
+    xr = x.clone().requires_grad_()
+    xf = x.clone().requires_grad_()
+    yr, yf = ref(xr), fused(xf)
+    go = torch.randn_like(yr)
+    ye, dxe, ge = emulate(fused, x, go)
+    yr.backward(go)
+    yf.backward(go)
+    scale_close(yf, ye, 5e-3)
+    scale_close(xf.grad, dxe, 5e-3)
+    scale_close(yf, yr, 1e-2)
+    scale_close(xf.grad, xr.grad, 0.15)
+    lins = [m for m in ref if isinstance(m, torch.nn.Linear)]
+    for i, lin in enumerate(lins):
+        L = fused.layers[i]
+        scale_close(L.gW[:, :L.K], ge[i][0], 5e-3)
+        scale_close(L.gb, ge[i][1], 5e-3)
+        scale_close(L.gW[:, :L.K], lin.weight.grad, 0.15)
+        scale_close(L.gb, lin.bias.grad, 0.15)
+        if L.K_pad != L.K:
+            assert float(L.gW[:, L.K:].abs().max()) == 0.0          # padded input columns never get gradient
+    # SGD step: master -= lr * grad, shadow refreshed, grads cleared
+    w0 = fused.weight(0).clone()
+    g0 = fused.layers[0].gW[:, :ln[0]].clone()
+    fused.step()
+    torch.testing.assert_close(fused.weight(0), w0 - 0.1 * g0, rtol=1e-6, atol=1e-7)
+    assert float(fused.grad.abs().max()) == 0.0
+    torch.testing.assert_close(fused.shadow.float(), fused.master.data.to(torch.bfloat16).float())
+
+
+def test_dense_adagrad_kernel_matches_reference_formula():
+    """optim/rwsadagrad.py:115-118: sum += g*g ; p -= clr * g / (sqrt(sum) + eps)."""
+    from dlrm_yx_b200 import ops
+    torch.manual_seed(1)
+    n = 100003
+    p = torch.randn(n, device="cuda")
+    acc = torch.rand(n, device="cuda")
+    g = torch.randn(n, device="cuda")
+    shadow = torch.empty(n, dtype=torch.bfloat16, device="cuda")
+    p0, a0, g0 = p.clone(), acc.clone(), g.clone()
+    ops.dense_opt(1, p, acc, g, shadow, lr=0.05, eps=1e-10, grad_scale=0.5)
+    gs = g0 * 0.5
+    a1 = a0 + gs * gs
+    p1 = p0 - 0.05 * gs / (a1.sqrt() + 1e-10)
+    torch.testing.assert_close(acc, a1, rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(p, p1, rtol=1e-6, atol=1e-7)
+    assert float(g.abs().max()) == 0.0
+    torch.testing.assert_close(shadow.float(), p.to(torch.bfloat16).float())
+
+
+def test_relu_bwd_bias_grad_kernel():
+    from dlrm_yx_b200 import ops
+    torch.manual_seed(2)
+    B, N = 1000, 264
+    y = torch.relu(torch.randn(B, N, device="cuda")).to(torch.bfloat16)
+    dy = torch.randn(B, N, device="cuda").to(torch.bfloat16)
+    dz, part = ops.relu_bwd_bias_grad(dy, y, relu=True, chunks=7)
+    want = dy.float() * (y.float() > 0)
+    assert torch.equal(dz.float(), want)
+    torch.testing.assert_close(part.sum(0), want.sum(0), rtol=1e-5, atol=1e-4)
+    dz2, part2 = ops.relu_bwd_bias_grad(dy, y, relu=False, chunks=3)
+    assert dz2 is dy
+    torch.testing.assert_close(part2.sum(0), dy.float().sum(0), rtol=1e-5, atol=1e-4)
