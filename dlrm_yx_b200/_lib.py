@@ -43,6 +43,10 @@ SIGNATURES = {
                                        c_void_p]),
     "dlrmx_interact_dot_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64,
                                        c_void_p, c_int64, c_void_p]),
+    "dlrmx_interact_dot_fwd_mixed": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                             c_int64, c_void_p]),
+    "dlrmx_interact_dot_bwd_mixed": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                             c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "dlrmx_relu_bwd_bias_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                          c_void_p]),
     "dlrmx_dense_opt": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,

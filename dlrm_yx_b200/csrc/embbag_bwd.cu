@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
     const int gshift = (threadIdx.x & 31) & ~(G - 1);
     const int64_t seg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
     if (seg >= P.nseg) return;
-    const int64_t p0 = seg * kSeg, p1 = min(P.N, p0 + kSeg);
+    const int64_t p0 = seg * P.seg_len, p1 = min(P.N, p0 + P.seg_len);
     const int col0 = gl * VEC;
     const uint32_t* __restrict__ skey = P.skey;
     const int32_t* __restrict__ sbag = P.sbag;
@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
     RowVec<VEC> acc[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c) acc[c].zero();
+    bool open = false;                       // does the position walked last belong to a run that is not finished?
 
 #pragma unroll 1
     for (int64_t pt = p0; pt < p1; pt += G) {
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
             float* mp[K];
             float mo[K];
             bool v[K], l[K];
+            // ---- stage 1: every load of the batch is issued before anything is consumed -------------------
 #pragma unroll
             for (int j = 0; j < K; ++j) {
                 const int jj = j0 + j;
@@ -90,25 +92,83 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
                     }
                 }
             }
+            // ---- stage 2: running sums in place, g[j] <- sum of the run up to position j (same order of
+            //      additions as a sequential walk: acc + g0 + g1 + ...) ---------------------------------------
 #pragma unroll
             for (int j = 0; j < K; ++j) {
                 if (v[j]) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].add(g[j][c]);
-                    if (l[j]) {
-                        if (owned) apply_row<VEC, G, CH>(P, wp[j], mp[j], mo[j], w[j], acc, col0);
-                        else store_partial<VEC, G, CH>(P.head_partial, seg, P.D, col0, acc);
+                        if (CH == 1 || col0 + c * G * VEC < P.D) {
+                            if (j == 0) g[0][c].add(acc[c]);
+                            else if (!l[j > 0 ? j - 1 : 0]) g[j][c].add(g[j > 0 ? j - 1 : 0][c]);
+                        }
+                }
+            }
+            // ---- stage 3: per-row step sizes for all run ends of the batch at once (the K butterflies, square
+            //      roots and divisions are independent -> they overlap instead of forming one long chain) ------
+            const unsigned ends = (lastmask >> j0) & ((1u << K) - 1u);
+            float a[K], mnew[K];
 #pragma unroll
-                        for (int c = 0; c < CH; ++c) acc[c].zero();
-                        owned = true;
-                    } else if (pt + j0 + j == p1 - 1) {  // the segment ends inside a run
-                        store_partial<VEC, G, CH>(owned ? P.tail_partial : P.head_partial, seg, P.D, col0, acc);
+            for (int j = 0; j < K; ++j) { a[j] = -P.lr; mnew[j] = 0.f; }
+            if (P.optimizer == DLRMX_OPT_RWSADAGRAD && ends != 0u) {
+                float ss[K];
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    ss[j] = 0.f;
+                    if (l[j]) {
+#pragma unroll
+                        for (int c = 0; c < CH; ++c)
+                            if (col0 + c * G * VEC < P.D) ss[j] = __fadd_rn(ss[j], g[j][c].sumsq());
                     }
+                }
+#pragma unroll
+                for (int o = G / 2; o > 0; o >>= 1) {
+#pragma unroll
+                    for (int j = 0; j < K; ++j) ss[j] = __fadd_rn(ss[j], __shfl_xor_sync(gmask, ss[j], o));
+                }
+#pragma unroll
+                for (int j = 0; j < K; ++j)
+                    if (l[j]) {
+                        mnew[j] = __fadd_rn(mo[j], row_mean(P, ss[j]));
+                        a[j] = __fdiv_rn(-P.lr, __fadd_rn(__fsqrt_rn(mnew[j]), P.eps));
+                    }
+            }
+            // ---- stage 4: apply / park the finished runs -----------------------------------------------------
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+                if (l[j]) {
+                    if (owned) {
+                        const float aj = a[j];
+#pragma unroll
+                        for (int c = 0; c < CH; ++c)
+                            if (CH == 1 || col0 + c * G * VEC < P.D) {
+                                w[j][c].map(g[j][c], [aj](float wv, float gv) { return __fmaf_rn(aj, gv, wv); });
+                                w[j][c].store(wp[j] + c * G * VEC);
+                            }
+                        if (P.optimizer == DLRMX_OPT_RWSADAGRAD && gl == 0) *mp[j] = mnew[j];
+                    } else {
+                        store_partial<VEC, G, CH>(P.head_partial, seg, P.D, col0, g[j]);
+                    }
+                    owned = true;
+                }
+            }
+            // ---- stage 5: carry the open run into the next batch ----------------------------------------------
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+                if (v[j]) {
+#pragma unroll
+                    for (int c = 0; c < CH; ++c) {
+                        acc[c] = g[j][c];
+                        if (l[j]) acc[c].zero();
+                    }
+                    open = !l[j];
                 }
             }
         }
     }
+    if (open)   // the segment ends inside a run
+        store_partial<VEC, G, CH>(owned ? P.tail_partial : P.head_partial, seg, P.D, col0, acc);
 }
 
 // Finishes runs that cross segment boundaries.  One group per segment; only the segment where a crossing run
@@ -124,7 +184,7 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
     const int gshift = (threadIdx.x & 31) & ~(G - 1);
     const int64_t seg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
     if (seg >= P.nseg) return;
-    const int64_t p0 = seg * kSeg, p1 = min(P.N, p0 + kSeg);
+    const int64_t p0 = seg * P.seg_len, p1 = min(P.N, p0 + P.seg_len);
     const uint32_t* __restrict__ skey = P.skey;
     if (p1 >= P.N) return;
     const uint32_t key = skey[p1 - 1];
@@ -147,7 +207,7 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
     while (!done) {
         // lane i: is segment s+i entirely inside the run, with the run continuing past its end?
         const int64_t sj = s + gl;
-        const int64_t e = min(P.N, (sj + 1) * kSeg);
+        const int64_t e = min(P.N, (sj + 1) * P.seg_len);
         bool full = false;
         if (sj < P.nseg && e < P.N) {
             const uint32_t a = skey[e - 1], bnext = skey[e];
@@ -250,7 +310,7 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
     const int col0 = gl * VEC;
     const int64_t row = rows[u];
     BwdParams P;
-    P.optimizer = optimizer; P.D = D; P.lr = lr; P.eps = eps;
+    P.optimizer = optimizer; P.D = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
     RowVec<VEC> g[CH], w[CH];
     float* wp = W + row * D + col0;
     const float* gp = gsum + u * D + col0;
@@ -323,8 +383,19 @@ static int launch_coalesce(int B, int D, const float* grad, int64_t sb, int64_t 
         }                                                                             \
     } while (0)
 
+// Sorted positions per group.  Longer segments mean fewer partial rows and shorter fix-up chains (the fix-up is pure
+// latency: 47 us at 32, 29 at 64, 17 at 128, 12 at 256 on the Terabyte shape) but fewer, longer warps in the main pass;
+// measured optimum on B200: 64 with the row-wise Adagrad math in the loop, 128 for SGD.  Small inputs keep 32 so the
+// grid still fills the 148 SMs.  Tunable 3 overrides (32/64/128/256).
+static int seg_len_for(int64_t N, int optimizer) {
+    const int t = get_tunable(DLRMX_TUNE_BWD_SEG);
+    if (t == 32 || t == 64 || t == 128 || t == 256) return t;
+    if (N < (int64_t)148 * 24 * 64 * 2) return kSeg;
+    return optimizer == DLRMX_OPT_SGD ? 128 : 64;
+}
+
 static size_t update_workspace_bytes(int64_t N, int D) {
-    const int64_t nseg = ceil_div(N > 0 ? N : 1, kSeg);
+    const int64_t nseg = ceil_div(N > 0 ? N : 1, kSeg);       // sized for the smallest segment length
     return align_up((size_t)nseg * D * 4, 256) * 2;
 }
 
@@ -354,12 +425,23 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     BwdParams P;
     P.optimizer = optimizer; P.tables = tables; P.moms = moms; P.row_base = table_row_base;
     P.B = B; P.D = D; P.grad = grad; P.stride_b = stride_b; P.stride_t = stride_t;
-    P.skey = sorted_key; P.sbag = sorted_bag; P.N = N; P.nseg = ceil_div(N, kSeg);
-    P.lr = lr; P.eps = eps;
+    P.skey = sorted_key; P.sbag = sorted_bag; P.N = N; P.seg_len = seg_len_for(N, optimizer); P.nseg = ceil_div(N, (int64_t)P.seg_len);
+    P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
     P.head_partial = (float*)workspace;
     P.tail_partial = (float*)((char*)workspace + align_up((size_t)P.nseg * D * 4, 256));
     cudaStream_t st = (cudaStream_t)stream;
 #define DLRMX_CALL_UPDATE(V, G_, C) launch_update<V, G_, C>(P, st)
+    // Wide rows (D = 128..512 with 16-B lanes): narrower groups with several column chunks per lane, so one warp
+    // walks 2 or 4 segments at once and the per-position scalar work (shuffles, pointers, sqrt, division) is shared.
+    if (g.vec == 4 && g.g == 32 && D % 128 == 0) {
+        const int tune = get_tunable(DLRMX_TUNE_BWD_K);
+        const int nv = D / 4;
+        if (tune == 8 && nv / 8 <= 4) return launch_update<4, 8, 4>(P, st);
+        if (tune == 16 && nv / 16 <= 4) {
+            if (nv / 16 == 2) return launch_update<4, 16, 2>(P, st);
+            if (nv / 16 == 4) return launch_update<4, 16, 4>(P, st);
+        }
+    }
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;

@@ -17,9 +17,23 @@
 //             with row stride D+8 (bank-conflict-free B fragments), the result goes straight from the accumulator
 //             fragments to global memory (full 32-byte sectors), with the pass-through dR[:, :D] added to feature 0.
 // HBM traffic is the algorithmic minimum: B*F*D*4 in + B*(D+nz)*4 out (forward).
+//
+// MIXED variants (template flag) serve the bf16 MLP towers: feature 0 (the bottom-MLP output) is read as bf16, the
+// result [x | tril] is written as bf16 with its row padded with zeros to the top MLP's K (a multiple of 8), dR is read
+// as bf16 and the feature-0 gradient is written as bf16; pooled embeddings and their gradients stay fp32.  Since the
+// consumer rounds to bf16 (2^-9) anyway, the products are single-pass TF32 (operands rounded to nearest, 2^-11) with
+// fp32 accumulation -- one mma per tile instead of three, which makes both kernels HBM-bound.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace dlrmx {
+
+__device__ __forceinline__ uint32_t round_tf32(float x) { return __float_as_uint(x) + 0x1000u; }   // low 13 bits ignored
+__device__ __forceinline__ void cp_async16_raw(void* smem_dst, const void* gsrc) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc));
+}
 
 // x = hi + lo with hi = x rounded to TF32 (10 explicit mantissa bits, round-half-away: add half an ulp to the
 // magnitude, clear the 13 low bits) and lo = (x - hi) rounded the same way.  Written with integer ops because
@@ -60,9 +74,10 @@ constexpr int kMmaWarps = 4;
 // writes its partial triangle to shared memory, and the four partials are added in a fixed order with
 // round-to-nearest adds (short accumulation chains inside the tensor core, deterministic result).
 // ---------------------------------------------------------------------------------------------------------
+template <bool MIXED>
 __global__ void __launch_bounds__(kMmaWarps * 32)
 interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
-                        float* __restrict__ out, int64_t ostride) {
+                        void* __restrict__ out_, int64_t ostride, const __nv_bfloat16* __restrict__ xb) {
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
@@ -71,6 +86,8 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     const int nzp = (nz + 3) & ~3;
     // two tile buffers [F][DS]: the next sample is copied in (cp.async) while this one is being contracted
     float* zpart = smem + 2 * F * DS + warp * nzp;        // this warp's partial triangle
+    // MIXED: the bf16 x row of each stage is parked behind the partials and converted at fragment-load time
+    __nv_bfloat16* xs_base = reinterpret_cast<__nv_bfloat16*>(smem + 2 * F * DS + kMmaWarps * nzp);
     const int dv = D >> 2;
     const bool two_m = F > 16;
     int rowoff[4];                                        // rows >= F only feed discarded outputs: alias row F-1
@@ -94,9 +111,13 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         if (bb < B) {
             const float* src = feat + bb * fsb;
             float* dstt = smem + which * F * DS;
-            for (int f = warp; f < F; f += kMmaWarps)
+            for (int f = warp + (MIXED ? 1 : 0); f < F; f += kMmaWarps)
                 for (int k4 = lane; k4 < dv; k4 += 32)
                     cp_async16(dstt + f * DS + 4 * k4, src + (int64_t)f * D + 4 * k4);
+            if (MIXED) {
+                for (int k8 = threadIdx.x; k8 < (D >> 3); k8 += kMmaWarps * 32)
+                    cp_async16_raw(xs_base + which * D + 8 * k8, xb + bb * D + 8 * k8);
+            }
         }
         cp_async_commit();
     };
@@ -107,8 +128,17 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         cp_async_wait_prev();
         __syncthreads();
         const float* tile = smem + buf * F * DS;
-        float* o = out + b * ostride;
-        for (int k = threadIdx.x; k < D; k += kMmaWarps * 32) o[k] = tile[k];     // R[:, 0:D] = x
+        const __nv_bfloat16* xs = xs_base + buf * D;
+        float* o = nullptr;
+        __nv_bfloat16* ob = nullptr;
+        if (MIXED) {
+            ob = reinterpret_cast<__nv_bfloat16*>(out_) + b * ostride;
+            for (int k = threadIdx.x; k < (D >> 1); k += kMmaWarps * 32)          // R[:, 0:D] = x
+                reinterpret_cast<__nv_bfloat162*>(ob)[k] = reinterpret_cast<const __nv_bfloat162*>(xs)[k];
+        } else {
+            o = reinterpret_cast<float*>(out_) + b * ostride;
+            for (int k = threadIdx.x; k < D; k += kMmaWarps * 32) o[k] = tile[k];     // R[:, 0:D] = x
+        }
 
         float c[2][4][4];
 #pragma unroll
@@ -123,20 +153,29 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
 #pragma unroll
             for (int r = 0; r < 4; ++r)
 #pragma unroll
-                for (int h = 0; h < 2; ++h) split_tf32(tile[rowoff[r] + k0 + t + 4 * h], hi[r][h], lo[r][h]);
+                for (int h = 0; h < 2; ++h) {
+                    float x = tile[rowoff[r] + k0 + t + 4 * h];
+                    if (MIXED) {
+                        if (r == 0 && g == 0) x = __bfloat162float(xs[k0 + t + 4 * h]);     // feature 0 arrives as bf16
+                        hi[r][h] = round_tf32(x);
+                    } else {
+                        split_tf32(x, hi[r][h], lo[r][h]);
+                    }
+                }
 #pragma unroll
             for (int m = 0; m < 2; ++m) {
                 if (m == 1 && !two_m) break;
                 const uint32_t ah[4] = {hi[2 * m][0], hi[2 * m + 1][0], hi[2 * m][1], hi[2 * m + 1][1]};
-                const uint32_t al[4] = {lo[2 * m][0], lo[2 * m + 1][0], lo[2 * m][1], lo[2 * m + 1][1]};
-#pragma unroll
                 // lower-triangle tiles only (n <= 2m+1); term-major order keeps the dependent mmas apart
+                if (!MIXED) {
+                    const uint32_t al[4] = {lo[2 * m][0], lo[2 * m + 1][0], lo[2 * m][1], lo[2 * m + 1][1]};
 #pragma unroll
-                for (int n = 0; n < 4; ++n)
-                    if (n <= 2 * m + 1) mma_tf32(c[m][n], al, hi[n][0], hi[n][1]);
+                    for (int n = 0; n < 4; ++n)
+                        if (n <= 2 * m + 1) mma_tf32(c[m][n], al, hi[n][0], hi[n][1]);
 #pragma unroll
-                for (int n = 0; n < 4; ++n)
-                    if (n <= 2 * m + 1) mma_tf32(c[m][n], ah, lo[n][0], lo[n][1]);
+                    for (int n = 0; n < 4; ++n)
+                        if (n <= 2 * m + 1) mma_tf32(c[m][n], ah, lo[n][0], lo[n][1]);
+                }
 #pragma unroll
                 for (int n = 0; n < 4; ++n)
                     if (n <= 2 * m + 1) mma_tf32(c[m][n], ah, hi[n][0], hi[n][1]);
@@ -154,8 +193,22 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
             }
         __syncthreads();
         const float* z0 = smem + 2 * F * DS;
-        for (int q = threadIdx.x; q < nz; q += kMmaWarps * 32)
-            o[D + q] = __fadd_rn(__fadd_rn(z0[q], z0[nzp + q]), __fadd_rn(z0[2 * nzp + q], z0[3 * nzp + q]));
+        if (MIXED) {       // bf16 pairs; the tail of the row up to ostride (the top MLP's padded K) is zero-filled
+            const int npair = (int)((ostride - D) >> 1);
+            for (int q2 = threadIdx.x; q2 < npair; q2 += kMmaWarps * 32) {
+                float v[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int q = 2 * q2 + e;
+                    v[e] = q < nz ? __fadd_rn(__fadd_rn(z0[q], z0[nzp + q]), __fadd_rn(z0[2 * nzp + q], z0[3 * nzp + q]))
+                                  : 0.f;
+                }
+                reinterpret_cast<__nv_bfloat162*>(ob + D)[q2] = __floats2bfloat162_rn(v[0], v[1]);
+            }
+        } else {
+            for (int q = threadIdx.x; q < nz; q += kMmaWarps * 32)
+                o[D + q] = __fadd_rn(__fadd_rn(z0[q], z0[nzp + q]), __fadd_rn(z0[2 * nzp + q], z0[3 * nzp + q]));
+        }
         // no barrier here: the partials are rewritten only after the next iteration's barrier
     }
 }
@@ -164,9 +217,11 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
 // backward:  dfeat[b, i, :] = sum_j S[i][j] * feat[b, j, :]  (+ dR[b, :D] on i = 0),  S = dZ + dZ^t
 // One CTA per sample; the D output columns are split across the 4 warps in 8-column tiles.
 // ---------------------------------------------------------------------------------------------------------
+template <bool MIXED>
 __global__ void __launch_bounds__(kMmaWarps * 32, 4)
 interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
-                        const float* __restrict__ dout, int64_t dstride, float* __restrict__ dfeat, int64_t dfsb) {
+                        const void* __restrict__ dout_, int64_t dstride, float* __restrict__ dfeat, int64_t dfsb,
+                        const __nv_bfloat16* __restrict__ xb, __nv_bfloat16* __restrict__ dxb) {
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
@@ -177,7 +232,11 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     const int nzp = (nz + 3) & ~3;
     // two stages of { feature tile [F][DS], dR[b, D:] (+ zero slot at [nzp]) }: the next sample streams in via
     // cp.async while this one is contracted; S [32][SS] is single (rebuilt between the two barriers)
-    const int stage_floats = F * DS + nzp + 4;
+    // MIXED: the stage holds the raw bf16 row dR[b, 0:D+nz] (16-byte chunks, zero slot behind it) and the bf16 x row
+    const int nchunk = (D + nz + 7) >> 3;
+    const int stage_floats = MIXED ? F * DS + 4 * nchunk + 4 + (D >> 1) : F * DS + nzp + 4;
+    const int zero_slot = MIXED ? 8 * nchunk : nzp;
+    const int zbase = MIXED ? D : 0;             // index of dZ[0] inside the staged row
     float* S = smem + 2 * stage_floats;
     const int dv = D >> 2;
     const bool two_m = F > 16;
@@ -191,28 +250,39 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     for (int u = 0; u < 8; ++u) {
         const int e = threadIdx.x + u * kMmaWarps * 32;
         const int i = e >> 5, j = e & 31;
-        ssrc[u] = nzp;               // the zero slot
+        ssrc[u] = zero_slot;
         sscale[u] = 1.f;
         if (i < F && j < F) {
             if (i == j) {
-                if (itself) { ssrc[u] = i * (i + 1) / 2 + i; sscale[u] = 2.f; }
+                if (itself) { ssrc[u] = zbase + i * (i + 1) / 2 + i; sscale[u] = 2.f; }
             } else {
                 const int hi_ = max(i, j), lo_ = min(i, j);
-                ssrc[u] = itself ? hi_ * (hi_ + 1) / 2 + lo_ : hi_ * (hi_ - 1) / 2 + lo_;
+                ssrc[u] = zbase + (itself ? hi_ * (hi_ + 1) / 2 + lo_ : hi_ * (hi_ - 1) / 2 + lo_);
             }
         }
     }
-    if (threadIdx.x < 2) smem[threadIdx.x * stage_floats + F * DS + nzp] = 0.f;
+    if (threadIdx.x < 2) smem[threadIdx.x * stage_floats + F * DS + (MIXED ? 4 * nchunk : nzp)] = 0.f;
+    const float* dout = reinterpret_cast<const float*>(dout_);
+    const __nv_bfloat16* doutb = reinterpret_cast<const __nv_bfloat16*>(dout_);
 
     auto stage = [&](int64_t bb, int which) {
         if (bb < B) {
             const float* src = feat + bb * fsb;
             float* dstt = smem + which * stage_floats;
-            for (int f = warp; f < F; f += kMmaWarps)
+            for (int f = warp + (MIXED ? 1 : 0); f < F; f += kMmaWarps)
                 for (int k4 = lane; k4 < dv; k4 += 32)
                     cp_async16(dstt + f * DS + 4 * k4, src + (int64_t)f * D + 4 * k4);
-            const float* dz = dout + bb * dstride + D;         // rows of dR are only 4-byte aligned
-            for (int q = threadIdx.x; q < nz; q += kMmaWarps * 32) cp_async4(dstt + F * DS + q, dz + q);
+            if (MIXED) {
+                __nv_bfloat16* zr = reinterpret_cast<__nv_bfloat16*>(dstt + F * DS);
+                for (int q = threadIdx.x; q < nchunk; q += kMmaWarps * 32)
+                    cp_async16_raw(zr + 8 * q, doutb + bb * dstride + 8 * q);
+                __nv_bfloat16* xr = zr + 8 * nchunk + 8;
+                for (int q = threadIdx.x; q < (D >> 3); q += kMmaWarps * 32)
+                    cp_async16_raw(xr + 8 * q, xb + bb * D + 8 * q);
+            } else {
+                const float* dz = dout + bb * dstride + D;         // rows of dR are only 4-byte aligned
+                for (int q = threadIdx.x; q < nz; q += kMmaWarps * 32) cp_async4(dstt + F * DS + q, dz + q);
+            }
         }
         cp_async_commit();
     };
@@ -224,10 +294,13 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         stage(b + gridDim.x, buf ^ 1);       // so its stage can be refilled while this one is worked on
         const float* tile = smem + buf * stage_floats;
         const float* zbuf = tile + F * DS;
+        const __nv_bfloat16* zraw = reinterpret_cast<const __nv_bfloat16*>(zbuf);
+        const __nv_bfloat16* xs = zraw + 8 * nchunk + 8;
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
             const int e = threadIdx.x + u * kMmaWarps * 32;
-            S[(e >> 5) * SS + (e & 31)] = zbuf[ssrc[u]] * sscale[u];
+            const float zv = MIXED ? __bfloat162float(zraw[ssrc[u]]) : zbuf[ssrc[u]];
+            S[(e >> 5) * SS + (e & 31)] = zv * sscale[u];
         }
         __syncthreads();
 
@@ -248,10 +321,17 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
 #pragma unroll
                 for (int m = 0; m < 2; ++m) {
                     const int r0 = 16 * m + g, k0 = 8 * ks + t;
-                    split_tf32(S[r0 * SS + k0], ah[m][0], al[m][0]);
-                    split_tf32(S[(r0 + 8) * SS + k0], ah[m][1], al[m][1]);
-                    split_tf32(S[r0 * SS + k0 + 4], ah[m][2], al[m][2]);
-                    split_tf32(S[(r0 + 8) * SS + k0 + 4], ah[m][3], al[m][3]);
+                    if (MIXED) {
+                        ah[m][0] = round_tf32(S[r0 * SS + k0]);
+                        ah[m][1] = round_tf32(S[(r0 + 8) * SS + k0]);
+                        ah[m][2] = round_tf32(S[r0 * SS + k0 + 4]);
+                        ah[m][3] = round_tf32(S[(r0 + 8) * SS + k0 + 4]);
+                    } else {
+                        split_tf32(S[r0 * SS + k0], ah[m][0], al[m][0]);
+                        split_tf32(S[(r0 + 8) * SS + k0], ah[m][1], al[m][1]);
+                        split_tf32(S[r0 * SS + k0 + 4], ah[m][2], al[m][2]);
+                        split_tf32(S[(r0 + 8) * SS + k0 + 4], ah[m][3], al[m][3]);
+                    }
                 }
                 const int j0 = 8 * ks + t, j1 = j0 + 4;      // feature rows >= F contribute zero
                 const bool ok0 = j0 < F, ok1 = j1 < F;
@@ -259,14 +339,23 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
                 for (int n = 0; n < NT; ++n) {
                     const int n0 = nb + 8 * n;
                     if (n0 >= D) break;
-                    uint32_t bh0, bl0, bh1, bl1;
-                    split_tf32(ok0 ? tile[j0 * DS + n0 + g] : 0.f, bh0, bl0);
-                    split_tf32(ok1 ? tile[j1 * DS + n0 + g] : 0.f, bh1, bl1);
+                    uint32_t bh0, bl0 = 0, bh1, bl1 = 0;
+                    if (MIXED) {
+                        float t0 = ok0 ? tile[j0 * DS + n0 + g] : 0.f;
+                        if (j0 == 0) t0 = __bfloat162float(xs[n0 + g]);          // feature 0 arrives as bf16
+                        bh0 = round_tf32(t0);
+                        bh1 = round_tf32(ok1 ? tile[j1 * DS + n0 + g] : 0.f);
+                    } else {
+                        split_tf32(ok0 ? tile[j0 * DS + n0 + g] : 0.f, bh0, bl0);
+                        split_tf32(ok1 ? tile[j1 * DS + n0 + g] : 0.f, bh1, bl1);
+                    }
 #pragma unroll
                     for (int m = 0; m < 2; ++m) {
                         if (m == 1 && !two_m) break;
-                        mma_tf32(c[n][m], al[m], bh0, bh1);
-                        mma_tf32(c[n][m], ah[m], bl0, bl1);
+                        if (!MIXED) {
+                            mma_tf32(c[n][m], al[m], bh0, bh1);
+                            mma_tf32(c[n][m], ah[m], bl0, bl1);
+                        }
                         mma_tf32(c[n][m], ah[m], bh0, bh1);
                     }
                 }
@@ -284,6 +373,16 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
                         if (i < F) {
                             float2 v = make_float2(c[n][m][2 * h], c[n][m][2 * h + 1]);
                             const int col = n0 + 2 * t;
+                            if (MIXED) {
+                                if (i == 0) {      // dense pass-through R[:, 0:D] = x; gradient of x leaves as bf16
+                                    v.x = __fadd_rn(v.x, __bfloat162float(zraw[col]));
+                                    v.y = __fadd_rn(v.y, __bfloat162float(zraw[col + 1]));
+                                    *reinterpret_cast<__nv_bfloat162*>(dxb + b * D + col) = __floats2bfloat162_rn(v.x, v.y);
+                                } else {
+                                    *reinterpret_cast<float2*>(dst + (int64_t)i * D + col) = v;
+                                }
+                                continue;
+                            }
                             if (i == 0) {          // dense pass-through: R[:, 0:D] = x
                                 v.x = __fadd_rn(v.x, __ldg(dx + col));
                                 v.y = __fadd_rn(v.y, __ldg(dx + col + 1));
@@ -303,26 +402,29 @@ static int mma_grid(int B) {
     return (int)(B < cap ? B : cap);
 }
 
+static bool mma_shape_ok(int F, int D) { return F <= 32 && F >= 2 && D % 8 == 0 && D <= 512; }
+
 // Returns 1 if the shape is handled here (and launches), 0 if the caller should use the CUDA-core kernel.
 int interact_fwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int itself, float* out, int64_t ostride,
                      cudaStream_t st, int* rc) {
-    if (F > 32 || F < 2 || D % 8 != 0 || D > 512 || fsb % 4 != 0 || ((uintptr_t)feat & 15) != 0) return 0;
+    if (!mma_shape_ok(F, D) || fsb % 4 != 0 || ((uintptr_t)feat & 15) != 0) return 0;
     const int nz = tri_count_mma(F, itself);
     const size_t smem = (2 * (size_t)F * (D + 4) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4;
     if (smem > 200 * 1024) return 0;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(interact_fwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_fwd_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
-    interact_fwd_mma_kernel<<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, out, ostride);
+    interact_fwd_mma_kernel<false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, out, ostride,
+                                                                              nullptr);
     *rc = check_launch("interact_dot_fwd(mma)");
     return 1;
 }
 
 int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int itself, const float* dout,
                      int64_t dstride, float* dfeat, int64_t dfsb, cudaStream_t st, int* rc) {
-    if (F > 32 || F < 2 || D % 8 != 0 || D > 512 || fsb % 4 != 0 || dfsb % 2 != 0 || ((uintptr_t)feat & 15) != 0 ||
+    if (!mma_shape_ok(F, D) || fsb % 4 != 0 || dfsb % 2 != 0 || ((uintptr_t)feat & 15) != 0 ||
         ((uintptr_t)dfeat & 7) != 0)
         return 0;
     const int nz = tri_count_mma(F, itself);
@@ -330,13 +432,61 @@ int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
     if (smem > 200 * 1024) return 0;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(interact_bwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_bwd_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
-    interact_bwd_mma_kernel<<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, dout, dstride, dfeat,
-                                                                      dfsb);
+    interact_bwd_mma_kernel<false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, dout, dstride,
+                                                                              dfeat, dfsb, nullptr, nullptr);
     *rc = check_launch("interact_dot_bwd(mma)");
     return 1;
+}
+
+// bf16-facing variants.  Return 0 on success, a negative code (message set) when the shape is not supported.
+int interact_fwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
+                       void* out_bf16, int64_t ostride, cudaStream_t st) {
+    const int nz = tri_count_mma(F, itself);
+    if (!mma_shape_ok(F, D) || fsb % 4 != 0 || ((uintptr_t)feat & 15) != 0 || ((uintptr_t)x_bf16 & 15) != 0 ||
+        ((uintptr_t)out_bf16 & 3) != 0 || ostride % 2 != 0 || ostride < D + nz) {
+        set_error("interact_dot_fwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, even "
+                  "out_stride >= D + nz (F=%d D=%d out_stride=%lld)", F, D, (long long)ostride);
+        return DLRMX_E_ARG;
+    }
+    const size_t smem = (2 * (size_t)F * (D + 4) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4 + 2 * (size_t)D * 2;
+    if (smem > 200 * 1024) { set_error("interact_dot_fwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(interact_fwd_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_done = true;
+    }
+    interact_fwd_mma_kernel<true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+        feat, fsb, B, F, D, itself, out_bf16, ostride, (const __nv_bfloat16*)x_bf16);
+    return check_launch("interact_dot_fwd_mixed");
+}
+
+int interact_bwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
+                       const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16,
+                       cudaStream_t st) {
+    const int nz = tri_count_mma(F, itself);
+    if (!mma_shape_ok(F, D) || fsb % 4 != 0 || dfsb % 2 != 0 || ((uintptr_t)feat & 15) != 0 ||
+        ((uintptr_t)dfeat & 7) != 0 || ((uintptr_t)x_bf16 & 15) != 0 || ((uintptr_t)dout_bf16 & 15) != 0 ||
+        ((uintptr_t)dx_bf16 & 3) != 0 || dstride % 8 != 0 || dstride < ((D + nz + 7) & ~7)) {
+        set_error("interact_dot_bwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, "
+                  "dout_stride %% 8 == 0 and >= D + nz rounded up to 8 (F=%d D=%d dout_stride=%lld)", F, D,
+                  (long long)dstride);
+        return DLRMX_E_ARG;
+    }
+    const int nchunk = (D + nz + 7) >> 3;
+    const size_t smem = (2 * ((size_t)F * (D + 8) + 4 * nchunk + 4 + (D >> 1)) + 32 * 36) * 4;
+    if (smem > 200 * 1024) { set_error("interact_dot_bwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(interact_bwd_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_done = true;
+    }
+    interact_bwd_mma_kernel<true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+        feat, fsb, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, (const __nv_bfloat16*)x_bf16,
+        (__nv_bfloat16*)dx_bf16);
+    return check_launch("interact_dot_bwd_mixed");
 }
 
 }  // namespace dlrmx

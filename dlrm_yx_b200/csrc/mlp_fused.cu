@@ -25,6 +25,14 @@ struct alignas(16) Bf16x8 {
     __nv_bfloat162 v[4];
 };
 
+__device__ __forceinline__ Bf16x8 ld_stream16(const __nv_bfloat16* p) {   // read-once data: do not pollute L1
+    Bf16x8 r;
+    uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "l"(p));
+    return r;
+}
+
 __global__ void __launch_bounds__(kRbThreads)
 relu_bwd_bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                           __nv_bfloat16* __restrict__ dz, float* __restrict__ db_partial, int B, int N,
@@ -37,27 +45,40 @@ relu_bwd_bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
 #pragma unroll
     for (int i = 0; i < 8; ++i) s[i] = 0.f;
     if (col < N) {
-#pragma unroll 4
-        for (int r = r0 + rl; r < r1; r += kRbRowLanes) {
-            const size_t off = (size_t)r * N + col;
-            Bf16x8 g = *reinterpret_cast<const Bf16x8*>(dy + off);
-            if (relu) {
-                const Bf16x8 a = *reinterpret_cast<const Bf16x8*>(y + off);
+        constexpr int U = 4;                        // rows in flight per thread: 2*U 16-B loads before the first use
+        for (int rb = r0 + rl; rb < r1; rb += kRbRowLanes * U) {
+            Bf16x8 g[U], a[U];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float2 av = __bfloat1622float2(a.v[i]);
-                    float2 gv = __bfloat1622float2(g.v[i]);
-                    gv.x = av.x > 0.f ? gv.x : 0.f;
-                    gv.y = av.y > 0.f ? gv.y : 0.f;
-                    g.v[i] = __float22bfloat162_rn(gv);
+            for (int u = 0; u < U; ++u) {
+                const int r = rb + u * kRbRowLanes;
+                if (r < r1) {
+                    const size_t off = (size_t)r * N + col;
+                    g[u] = ld_stream16(dy + off);
+                    if (relu) a[u] = ld_stream16(y + off);
                 }
-                *reinterpret_cast<Bf16x8*>(dz + off) = g;
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float2 gv = __bfloat1622float2(g.v[i]);
-                s[2 * i] += gv.x;
-                s[2 * i + 1] += gv.y;
+            for (int u = 0; u < U; ++u) {
+                const int r = rb + u * kRbRowLanes;
+                if (r < r1) {
+                    if (relu) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float2 av = __bfloat1622float2(a[u].v[i]);
+                            float2 gv = __bfloat1622float2(g[u].v[i]);
+                            gv.x = av.x > 0.f ? gv.x : 0.f;
+                            gv.y = av.y > 0.f ? gv.y : 0.f;
+                            g[u].v[i] = __float22bfloat162_rn(gv);
+                        }
+                        *reinterpret_cast<Bf16x8*>(dz + (size_t)r * N + col) = g[u];
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float2 gv = __bfloat1622float2(g[u].v[i]);
+                        s[2 * i] += gv.x;
+                        s[2 * i + 1] += gv.y;
+                    }
+                }
             }
         }
     }

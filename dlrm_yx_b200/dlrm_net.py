@@ -49,6 +49,53 @@ class _SparseArchLocal(torch.autograd.Function):
         return dfeat[:, 0, :], None, None, None, None, None
 
 
+class _SparseArchLocalMixed(torch.autograd.Function):
+    """_SparseArchLocal between bf16 towers: x arrives as bf16, R leaves as bf16 padded to `out_cols` (the top MLP's
+    K rounded up to 8); pooled embeddings, their gradients and the sparse update stay fp32."""
+
+    @staticmethod
+    def forward(ctx, x, weights, emb, indices, offsets, itself, out_cols):
+        B, D = x.shape
+        T = emb.T
+        feat = torch.empty((B, 1 + T, D), dtype=torch.float32, device=x.device)   # slot 0 stays unused
+        ops.embbag_forward(emb.table_set(), indices, offsets, B, out=feat[:, 1:, :],
+                           stride_b=(1 + T) * D, stride_t=D)
+        x = x.contiguous()
+        ctx.emb, ctx.itself = emb, bool(itself)
+        ctx.save_for_backward(feat, x, indices, offsets)
+        return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
+
+    @staticmethod
+    def backward(ctx, dR):
+        feat, x, indices, offsets = ctx.saved_tensors
+        B, F, D = feat.shape
+        dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
+        ctx.emb.fused_backward(dfeat[:, 1:, :], indices, offsets, B, stride_b=F * D, stride_t=D)
+        return dx, None, None, None, None, None, None
+
+
+class _ExchangeInteractMixed(torch.autograd.Function):
+    """_ExchangeInteract between bf16 towers."""
+
+    @staticmethod
+    def forward(ctx, x, recv, itself, out_cols):
+        lb, D = x.shape
+        T = ext_dist.myreq.a2a_info.global_table_num
+        feat = torch.empty((lb, 1 + T, D), dtype=torch.float32, device=x.device)
+        ctx.info = ext_dist.complete_into(recv, feat, 1)
+        x = x.contiguous()
+        ctx.itself = bool(itself)
+        ctx.save_for_backward(feat, x)
+        return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
+
+    @staticmethod
+    def backward(ctx, dR):
+        feat, x = ctx.saved_tensors
+        dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
+        send = ext_dist.start_backward_from(ctx.info, dfeat, 1)
+        return dx, send, None, None
+
+
 class _ExchangeInteract(torch.autograd.Function):
     """Multi-process: completes the all-to-all into the feature block, then dot interaction.
     backward packs the block gradient and starts the transposed exchange (completed by the request's
@@ -184,6 +231,14 @@ class DLRM_Net(nn.Module):
         from . import mlp
         self.bot_l = mlp.FusedMLP(self.bot_l, lr, optimizer, eps)
         self.top_l = mlp.FusedMLP(self.top_l, lr, optimizer, eps)
+        # bf16 hand-over around the interaction (no cast / pad / slice passes): the bottom tower ends in a fused bf16
+        # layer, the top tower starts with one, and the tensor-core interaction kernels take the shape
+        F, D = 1 + int(self.ln_emb.size), int(self.ln_bot[-1])
+        first, last = self.top_l.layers[0], self.bot_l.layers[-1]
+        nz = ops.tri_count(F, self.arch_interaction_itself)
+        self._mixed = bool(self.fuse_sparse_arch and self.arch_interaction_op == "dot" and first.fused and last.fused
+                           and first.K == D + nz and ops.interact_mixed_supported(F, D))
+        self.bot_l.out_bf16 = self._mixed
         return self
 
     def step_mlps(self):
@@ -243,7 +298,12 @@ class DLRM_Net(nn.Module):
         if self.fuse_sparse_arch:
             with record_function("module::forward_pass::embedding_lookup"):
                 emb = self._batched_module()
-                z = _SparseArchLocal.apply(x, emb.embedding_weights, emb, lS_i, lS_o, self.arch_interaction_itself)
+                if getattr(self, "_mixed", False):
+                    z = _SparseArchLocalMixed.apply(x, emb.embedding_weights, emb, lS_i, lS_o,
+                                                    self.arch_interaction_itself, self.top_l.layers[0].K_pad)
+                else:
+                    z = _SparseArchLocal.apply(x, emb.embedding_weights, emb, lS_i, lS_o,
+                                               self.arch_interaction_itself)
         else:
             with record_function("module::forward_pass::embedding_lookup"):
                 if self.batched_emb:
@@ -277,7 +337,10 @@ class DLRM_Net(nn.Module):
                 ly = list(a2a_req.wait())
         with record_function("module::forward_pass::interaction"):
             if self.fuse_sparse_arch:
-                z = _ExchangeInteract.apply(x, recv, self.arch_interaction_itself)
+                if getattr(self, "_mixed", False):
+                    z = _ExchangeInteractMixed.apply(x, recv, self.arch_interaction_itself, self.top_l.layers[0].K_pad)
+                else:
+                    z = _ExchangeInteract.apply(x, recv, self.arch_interaction_itself)
             else:
                 z = self.interact_features(x, ly)
         with record_function("module::forward_pass::top_mlp"):

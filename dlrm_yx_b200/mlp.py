@@ -47,7 +47,7 @@ class _LinearAct(torch.autograd.Function):
             y = torch._addmm_activation(L.b_shadow, hb, L.w_shadow.t())
         else:
             y = torch.addmm(L.b_shadow, hb, L.w_shadow.t())
-        ctx.mlp, ctx.li = mlp, li
+        ctx.mlp, ctx.li, ctx.in_cols = mlp, li, h.shape[1]
         ctx.save_for_backward(hb, y)
         return y
 
@@ -63,7 +63,7 @@ class _LinearAct(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.mm(dz, L.w_shadow)
-            if L.K_pad != L.K:
+            if ctx.in_cols != L.K_pad:       # the caller's input was unpadded
                 dx = dx[:, :L.K]
         return dx, None, None, None
 
@@ -101,6 +101,7 @@ class FusedMLP(nn.Module):
         self.register_buffer("grad", torch.zeros_like(master), persistent=False)
         self.register_buffer("shadow", master.to(torch.bfloat16), persistent=False)
         self._anchor = torch.zeros(1, device=dev, requires_grad=True)  # makes every layer's backward run
+        self.out_bf16 = False       # True: hand the last fused layer's bf16 output on as it is (no fp32 copy)
         self._bind()
 
     def _bind(self):
@@ -138,7 +139,7 @@ class FusedMLP(nn.Module):
             else:
                 z = F.linear(h.float(), L.w_leaf, L.b_leaf)
                 h = torch.sigmoid(z) if L.act == "sigmoid" else torch.relu(z)
-        return h if h.dtype == torch.float32 else h.float()
+        return h if (h.dtype == torch.float32 or self.out_bf16) else h.float()
 
     @torch.no_grad()
     def step(self, world_size=1):

@@ -228,6 +228,40 @@ def interact_dot_bwd(feat, dout, itself=False, dfeat=None):
     return dfeat
 
 
+def interact_mixed_supported(F, D):
+    return 2 <= F <= 32 and D % 8 == 0 and D <= 512
+
+
+def interact_dot_fwd_mixed(feat, x_bf16, out_cols, itself=False):
+    """feat [B, F, D] fp32 (features 1.. valid), x_bf16 [B, D] (feature 0) -> bf16 [B, out_cols] = [x | tril | 0...]."""
+    _need_cuda(feat, x_bf16)
+    B, F, D = feat.shape
+    if feat.stride(2) != 1 or feat.stride(1) != D or not x_bf16.is_contiguous() or x_bf16.dtype != torch.bfloat16:
+        raise _lib.DlrmxError("interact_dot_fwd_mixed: feat [B, F, D] fp32 with contiguous blocks, x contiguous bf16")
+    out = torch.empty((B, out_cols), dtype=torch.bfloat16, device=feat.device)
+    with _timed("interact_fwd"):
+        rc = _lib.load().dlrmx_interact_dot_fwd_mixed(feat.data_ptr(), feat.stride(0), x_bf16.data_ptr(), B, F, D,
+                                                      int(itself), out.data_ptr(), out.stride(0), _stream())
+        _lib.check(rc, "dlrmx_interact_dot_fwd_mixed")
+    return out
+
+
+def interact_dot_bwd_mixed(feat, x_bf16, dout, itself=False):
+    """-> (dfeat fp32 [B, F, D] with features 1.. written, dx bf16 [B, D])."""
+    _need_cuda(feat, x_bf16, dout)
+    B, F, D = feat.shape
+    if dout.dtype != torch.bfloat16 or dout.stride(1) != 1:
+        raise _lib.DlrmxError("interact_dot_bwd_mixed: dout must be bf16 with unit column stride")
+    dfeat = torch.empty((B, F, D), dtype=torch.float32, device=feat.device)
+    dx = torch.empty((B, D), dtype=torch.bfloat16, device=feat.device)
+    with _timed("interact_bwd"):
+        rc = _lib.load().dlrmx_interact_dot_bwd_mixed(feat.data_ptr(), feat.stride(0), x_bf16.data_ptr(), B, F, D,
+                                                      int(itself), dout.data_ptr(), dout.stride(0), dfeat.data_ptr(),
+                                                      dfeat.stride(0), dx.data_ptr(), _stream())
+        _lib.check(rc, "dlrmx_interact_dot_bwd_mixed")
+    return dfeat, dx
+
+
 def _int_array(values):
     return (ctypes.c_int * len(values))(*[int(v) for v in values])
 
@@ -265,10 +299,14 @@ def rows_update(optimizer, weight, mom, rows, gsum, lr, eps=0.0):
     _lib.check(rc, "dlrmx_rows_update")
 
 
-def relu_bwd_bias_grad(dy, y, relu=True, chunks=64):
-    """(dz bf16 [B,N], db_partial fp32 [chunks,N]): dz = dy * (y > 0) and per-chunk column sums of dz, one pass."""
+def relu_bwd_bias_grad(dy, y, relu=True, chunks=None):
+    """(dz bf16 [B,N], db_partial fp32 [chunks,N]): dz = dy * (y > 0) and per-chunk column sums of dz, one pass.
+    chunks=None sizes the grid for >= 6 CTAs of 256 threads per SM (148 SMs) with at least 32 rows per chunk."""
     _need_cuda(dy, y)
     B, N = dy.shape
+    if chunks is None:
+        col_blocks = (N + 255) // 256
+        chunks = max(1, min((B + 31) // 32, (148 * 6 + col_blocks - 1) // col_blocks))
     dz = torch.empty_like(dy) if relu else dy
     part = torch.empty((chunks, N), dtype=torch.float32, device=dy.device)
     with _timed("relu_bwd_bias_grad"):

@@ -160,6 +160,21 @@ int dlrmx_interact_dot_bwd(const float* feat, int64_t feat_stride_b, int B, int 
                            const float* dout, int64_t dout_stride,
                            float* dfeat, int64_t dfeat_stride_b, dlrmx_stream_t stream);
 
+/* bf16-facing variants for towers that run in bf16 (the same interact_features call, dlrm_s_pytorch.py:627-673, between
+ * a bf16 bottom MLP and a bf16 top MLP):
+ *   feature 0 is NOT read from feat but from x_bf16 [B, D] (the bottom-MLP output as the GEMM epilogue wrote it);
+ *   out_bf16 [B, out_stride] bf16 = [x | tril], columns D+nz .. out_stride-1 are written as zeros (out_stride = the top
+ *   MLP's K rounded up to 8, so the GEMM reads it without a pad/cast pass);
+ *   backward reads dout_bf16 [B, dout_stride] bf16 (dout_stride % 8 == 0), writes the pooled-embedding gradients
+ *   dfeat[:, 1:, :] in fp32 (feature 0 of dfeat is left untouched) and the gradient of x as dx_bf16 [B, D].
+ * Products are single-pass TF32 (operands rounded to nearest) with fp32 accumulation.  Needs 2 <= F <= 32, D % 8 == 0,
+ * D <= 512; other shapes: use the fp32 entry points and cast. */
+int dlrmx_interact_dot_fwd_mixed(const float* feat, int64_t feat_stride_b, const void* x_bf16, int B, int F, int D,
+                                 int itself, void* out_bf16, int64_t out_stride, dlrmx_stream_t stream);
+int dlrmx_interact_dot_bwd_mixed(const float* feat, int64_t feat_stride_b, const void* x_bf16, int B, int F, int D,
+                                 int itself, const void* dout_bf16, int64_t dout_stride, float* dfeat,
+                                 int64_t dfeat_stride_b, void* dx_bf16, dlrmx_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * MLP towers (create_mlp / apply_mlp, dlrm_s_pytorch.py:227-265, 518-524): fused passes around the
  * tensor-core GEMMs, and the dense half of the optimizers.

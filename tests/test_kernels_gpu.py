@@ -230,6 +230,49 @@ def test_interaction_fwd_bwd(F, D, itself):
                                rtol=1e-5, atol=2e-5)
 
 
+@pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (2, 8), (32, 32)])
+@pytest.mark.parametrize("itself", [False, True])
+def test_interaction_mixed_bf16_facing(F, D, itself):
+    """bf16-facing interaction (feature 0 in / result out / dR in / dx out as bf16, single-pass TF32 products, fp32
+    accumulate) against the fp32 oracle on the SAME bf16-rounded inputs.  Bars: bf16 outputs 2^-8 relative (one bf16
+    rounding, half an ulp = 2^-9, with margin) plus the TF32 operand rounding 2^-10 * sum|a||b|; fp32 outputs the
+    TF32 term only.  Padding columns must be exactly zero."""
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    rng = np.random.default_rng(F * 100 + D + 7)
+    B = 21
+    bf = torch.bfloat16
+    feat = rng.normal(size=(B, F, D)).astype(np.float32)
+    x_b = torch.from_numpy(feat[:, 0, :]).to(dev).to(bf)
+    feat[:, 0, :] = x_b.float().cpu().numpy()                     # the oracle sees what the kernel sees
+    df = torch.from_numpy(feat).to(dev).clone()
+    df[:, 0, :] = float("nan")                                    # slot 0 of feat must never be read
+    nz = F * (F + 1) // 2 if itself else F * (F - 1) // 2
+    cols = (D + nz + 7) // 8 * 8 + 8
+    out = ops.interact_dot_fwd_mixed(df, x_b, cols, itself)
+    assert out.dtype == bf and tuple(out.shape) == (B, cols)
+    got = out.float().cpu().numpy()
+    ref = O.interact_dot(feat[:, 0, :], feat[:, 1:, :], itself)
+    mag = O.interact_dot(np.abs(feat[:, 0, :]), np.abs(feat[:, 1:, :]), itself)
+    assert np.array_equal(got[:, :D], feat[:, 0, :])
+    assert np.all(got[:, D + nz:] == 0.0)
+    err = np.abs(got[:, :D + nz] - ref)
+    assert np.all(err <= 2.0 ** -8 * np.abs(ref) + 2.0 ** -10 * mag + 1e-6), err.max()
+
+    dR_b = torch.from_numpy(rng.normal(size=(B, cols)).astype(np.float32)).to(dev).to(bf)
+    dR = dR_b.float().cpu().numpy()[:, :D + nz]
+    dfeat, dx = ops.interact_dot_bwd_mixed(df, x_b, dR_b, itself)
+    rdx, rdemb = O.interact_dot_bwd(feat[:, 0, :], feat[:, 1:, :], dR, itself)
+    # magnitude of the contraction: sum_j |S_ij| |T_j|
+    mdx, mdemb = O.interact_dot_bwd(np.abs(feat[:, 0, :]), np.abs(feat[:, 1:, :]),
+                                    np.concatenate([np.zeros((B, D), np.float32), np.abs(dR[:, D:])], axis=1), itself)
+    e_emb = np.abs(dfeat[:, 1:, :].cpu().numpy() - rdemb)
+    assert np.all(e_emb <= 2.0 ** -10 * mdemb + 1e-6), e_emb.max()
+    assert dx.dtype == bf
+    e_dx = np.abs(dx.float().cpu().numpy() - rdx)
+    assert np.all(e_dx <= 2.0 ** -8 * np.abs(rdx) + 2.0 ** -10 * mdx + 1e-6), e_dx.max()
+
+
 @pytest.mark.parametrize("D", [128, 6])
 def test_a2a_layout_roundtrip(D):
     from dlrm_yx_b200 import ops

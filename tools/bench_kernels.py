@@ -36,12 +36,17 @@ def peak_gbs():
     return 6650.0, "fallback"
 
 
+PRE = [None]
+
+
 def timed(fn, iters, warmup=3):
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
     for s, e in evs:
+        if PRE[0] is not None:
+            PRE[0]()
         s.record()
         fn()
         e.record()
@@ -56,6 +61,10 @@ def main():
     ap.add_argument("--rows-cap", type=int, default=0)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--idx64", action="store_true")
+    ap.add_argument("--flush", action="store_true", help="evict L2 (512 MB memset) before every timed call")
+    ap.add_argument("--gstride", type=int, default=0, help="gradient laid out [B, gstride, D] (features 1..T used)")
+    ap.add_argument("--only", default="")
+    ap.add_argument("--gscale", type=float, default=1.0)
     args = ap.parse_args()
     cfg = SHAPES[args.shape]
     rows = [min(r, args.rows_cap) if args.rows_cap else r for r in cfg["rows"]]
@@ -82,7 +91,12 @@ def main():
     ib = 8 if args.idx64 else 4
     fwd_bytes = N * D * 4 + N * ib + T * B * ib + T * B * D * 4
     out = torch.empty((B, T, D), device=dev)
-    grad = torch.randn((B, T, D), device=dev)
+    GS = args.gstride or T
+    grad_full = torch.randn((B, GS, D), device=dev) * args.gscale
+    grad = grad_full[:, GS - T:, :]
+    if args.flush:
+        junk = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+        PRE[0] = lambda: junk.zero_()
     it = [0]
 
     def report(name, ms, mn, nbytes, extra=None):
@@ -114,16 +128,17 @@ def main():
     uniq = [int(ops.bwd_segments(sk)[2].item()) for sk, _ in sorted_batches]
     U = sum(uniq) / len(uniq)
     for opt, name in ((_lib.OPT_SGD, "sgd"), (_lib.OPT_RWSADAGRAD, "rwsadagrad")):
-        for k in (4,):
+        for k in (32, 64, 128, 256):
+            _lib.set_tunable(3, k)
 
             def u():
                 sk, sb = sorted_batches[it[0] % nbatch]
                 it[0] += 1
-                ops.bwd_update(ts, opt, grad, T * D, D, B, sk, sb, 0.01, 1e-10)
+                ops.bwd_update(ts, opt, grad, GS * D, D, B, sk, sb, 0.01, 1e-10)
             ms, mn = timed(u, args.iters)
             nbytes = T * B * D * 4 + N * 8 + 2 * U * D * 4 + (2 * U * 4 if opt else 0)
             report("bwd_update_" + name, ms, mn, nbytes, dict(K=k, U=int(U)))
-    _lib.set_tunable(_lib.TUNE_BWD_K, 0)
+    _lib.set_tunable(3, 0)
 
     F = T + 1
     feat = torch.randn((B, F, D), device=dev)
