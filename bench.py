@@ -40,7 +40,9 @@ def parse():
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (debug only; marks the run)")
     ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
                     help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
-    ap.add_argument("--sharder", default="greedy")
+    ap.add_argument("--sharder", default="traffic")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: 'peer' = exchange fused into the kernels over NVLink peer memory; 'nccl' = all_to_all_single")
     ap.add_argument("--optimizer", default="rwsadagrad", choices=["rwsadagrad", "sgd"])
     ap.add_argument("--nbatches", type=int, default=8, help="distinct synthetic batches cycled through")
     ap.add_argument("--cpu-batch", type=int, default=4096)
@@ -163,6 +165,8 @@ def build_model(args, cfg, W):
     m = dlrm_net.DLRM_Net(D, np.array(cfg["rows"]), ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
                           sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True, sharder=args.sharder,
                           emb_optimizer=kind, emb_learning_rate=lr, emb_init="device").cuda()
+    if W > 1 and args.exchange == "peer":
+        m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W)
     if args.mlp == "fused-bf16":
         m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd")
         return m, None
@@ -348,7 +352,7 @@ def main():
             calls, ms = r["prof"][name]
             kern[name] = {"ms": round(ms, 4), "calls_per_step": calls / K, "algorithmic_MB": round(nbytes / 1e6, 1),
                           "GBps": round(nbytes / ms / 1e6, 1), "frac": round(nbytes / ms / 1e6 / peak, 4)}
-    for name in ("bwd_sort", "interact_fwd", "interact_bwd", "a2a_unpack", "a2a_pack_grad", "relu_bwd_bias_grad",
+    for name in ("bwd_sort", "interact_fwd", "interact_bwd", "a2a_unpack", "a2a_pack_grad", "a2a_push_grad", "relu_bwd_bias_grad",
                  "dense_opt"):
         if name in r["prof"]:
             kern[name] = {"ms": round(r["prof"][name][1], 4), "calls_per_step": r["prof"][name][0] / K}
@@ -361,7 +365,9 @@ def main():
                  % {"fused-bf16": "bf16 in / fp32 accumulate"}.get(args.mlp, args.mlp), "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, W, Bg), "global_batch": Bg, "per_gpu_batch": lb,
                    "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder), "
-                   "data-parallel MLPs (DDP), NCCL all-to-all" % (W, args.sharder),
+                   "data-parallel MLPs (flat-gradient all-reduce), %s" % (
+                       W, args.sharder, "exchange fused into the lookup / gradient kernels over NVLink peer memory"
+                       if args.exchange == "peer" else "NCCL all-to-all"),
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"
                          % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * 4 / 1e9, args.nbatches),
                    "rows_cap": args.rows_cap or None},

@@ -43,6 +43,36 @@ a2a_layout_kernel(float* __restrict__ chunks, float* __restrict__ block, int64_t
     }
 }
 
+// Gradient half of the exchange WITHOUT a send buffer or a collective: each rank's slice of the feature-block
+// gradient is stored straight into the owning rank's (peer-mapped) gradient buffer over NVLink, one 16-byte
+// lane-store per thread, whole D-float rows contiguous -> full-line NVLink writes.
+struct PeerBases {
+    float* base[kMaxRanks];      // where this rank's [lb, T_p, D] chunk starts inside rank p's buffer
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+a2a_push_kernel(const float* __restrict__ block, int64_t bsb, int feat_off, RankSplit rs, PeerBases pb, int lb, int D) {
+    const int T = rs.first_table[rs.W];
+    const int dv = D / VEC;
+    const int64_t total = (int64_t)lb * T * dv;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        const int d = (int)(e % dv);
+        const int64_t r = e / dv;
+        const int t = (int)(r % T);
+        const int b = (int)(r / T);
+        int p = 0;
+        while (t >= rs.first_table[p + 1]) ++p;
+        const int tp = rs.first_table[p + 1] - rs.first_table[p];
+        float* c = pb.base[p] + ((int64_t)b * tp + (t - rs.first_table[p])) * D + d * VEC;
+        const float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * D + d * VEC;
+        RowVec<VEC> v;
+        v.load_stream(f);
+        v.store(c);
+    }
+}
+
 static int a2a_layout(float* chunks, float* block, int64_t bsb, int feat_off, int W, const int* tpr, int lb,
                       int D, int dir, dlrmx_stream_t stream) {
     DLRMX_REQUIRE(W >= 1 && W <= kMaxRanks, "a2a layout: W=%d out of range", W);
@@ -70,6 +100,35 @@ static int a2a_layout(float* chunks, float* block, int64_t bsb, int feat_off, in
 }  // namespace dlrmx
 
 extern "C" {
+int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+                        const int* host_tables_per_rank, int lb, int D, float* const* host_peer_chunk_bases,
+                        dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(W >= 1 && W <= kMaxRanks, "a2a_push_grad: W=%d out of range", W);
+    DLRMX_REQUIRE(lb >= 0 && D >= 1 && host_peer_chunk_bases != nullptr, "a2a_push_grad: bad arguments");
+    RankSplit rs;
+    PeerBases pb;
+    rs.W = W;
+    rs.first_table[0] = 0;
+    bool vec = (D % 4 == 0) && (dfeat_stride_b % 4 == 0) && ((uintptr_t)dfeat & 15) == 0;
+    for (int p = 0; p < W; ++p) {
+        DLRMX_REQUIRE(host_tables_per_rank[p] >= 0, "a2a_push_grad: negative table count");
+        rs.first_table[p + 1] = rs.first_table[p] + host_tables_per_rank[p];
+        pb.base[p] = host_peer_chunk_bases[p];
+        DLRMX_REQUIRE(host_tables_per_rank[p] == 0 || pb.base[p] != nullptr, "a2a_push_grad: null peer base");
+        vec = vec && ((uintptr_t)pb.base[p] & 15) == 0;
+    }
+    const int T = rs.first_table[W];
+    if (lb == 0 || T == 0) return DLRMX_OK;
+    const int64_t total = (int64_t)lb * T * (vec ? D / 4 : D);
+    int64_t nblk = ceil_div(total, 256);
+    if (nblk > (int64_t)kSMs * 16) nblk = (int64_t)kSMs * 16;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (vec) a2a_push_kernel<4><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, feat_off, rs, pb, lb, D);
+    else     a2a_push_kernel<1><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, feat_off, rs, pb, lb, D);
+    return check_launch("a2a_push_grad");
+}
+
 int dlrmx_a2a_unpack(const float* recv, int W, const int* host_tables_per_rank, int lb, int D, float* dst,
                      int64_t dst_stride_b, int feat_off, dlrmx_stream_t stream) {
     return dlrmx::a2a_layout(const_cast<float*>(recv), dst, dst_stride_b, feat_off, W, host_tables_per_rank, lb, D, 0,

@@ -53,7 +53,8 @@ __global__ void __launch_bounds__(256, (K * U * CH <= 4) ? 4 : ((K * U * CH <= 8
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t total_bags, const float* __restrict__ psw,
-                  float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag) {
+                  float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
+                  float* const* __restrict__ out_peers, int lb) {
     constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
     constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
@@ -164,7 +165,11 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
             if (bag < total_bags) {
                 const int64_t t = bag / B;
                 const int64_t b = bag - t * B;
-                float* o = out + b * stride_b + t * stride_t + col0;
+                // model-parallel exchange fused into the lookup: sample b belongs to rank b / lb, whose (peer-mapped)
+                // interaction input receives the pooled row directly over NVLink -- 512-byte row stores
+                float* o = (out_peers == nullptr)
+                               ? out + b * stride_b + t * stride_t + col0
+                               : out_peers[b / lb] + (b % lb) * stride_b + t * stride_t + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
                     if (col0 + c * G * VEC < D) acc[k][c].store(o + c * G * VEC);
@@ -176,7 +181,8 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
 template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
-                      int64_t stride_b, int64_t stride_t, int* err_flag, cudaStream_t st) {
+                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
+                      cudaStream_t st) {
     const int64_t total_bags = (int64_t)T * B;
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
     const int64_t groups = ceil_div(total_bags, TILE);   // one group of G lanes per tile of TILE bags
@@ -184,15 +190,18 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
     embbag_fwd_kernel<VEC, G, CH, K, U, FULL, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
-        tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag);
+        tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers,
+        lb);
     return check_launch("embbag_fwd");
 }
 
 template <typename IdxT>
 static int embbag_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
-                      int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
+                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
+                      dlrmx_stream_t stream) {
     DLRMX_REQUIRE(T >= 0 && B >= 0 && N >= 0, "embbag_fwd: negative size");
+    DLRMX_REQUIRE(out_peers == nullptr || (lb > 0 && B % lb == 0), "embbag_fwd_scatter: B must be a multiple of lb > 0");
     DLRMX_REQUIRE((int64_t)T * B < (1ll << 31), "embbag_fwd: T*B must be < 2^31");
     RowGeom g;
     DLRMX_REQUIRE(row_geometry(D, &g), "embbag_fwd: unsupported D=%d (need D<=512 if D%%4==0, else D<=128)", D);
@@ -205,7 +214,8 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     // Long bags: K bags per group, U rows of each in flight.  FWD_K tunable: 8 -> K=8 (short) / U=8 (long).
     const bool short_bags = N <= 2 * (int64_t)T * B;
     const int tune = get_tunable(DLRMX_TUNE_FWD_K);
-#define DLRMX_FWD_ARGS tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b, stride_t, err_flag, st
+#define DLRMX_FWD_ARGS \
+    tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b, stride_t, err_flag, out_peers, lb, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                  \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                   \
         if (short_bags) {                                                                              \
@@ -232,13 +242,31 @@ int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows, 
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
     return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b,
-                                      stride_t, err_flag, stream);
+                                      stride_t, err_flag, nullptr, 0, stream);
 }
 int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
                          const int64_t* offsets, int64_t N, int T, int B, int D, const float* psw,
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
     return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b,
-                                      stride_t, err_flag, stream);
+                                      stride_t, err_flag, nullptr, 0, stream);
+}
+int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
+                                 const int32_t* offsets, int64_t N, int T, int B, int D, const float* psw,
+                                 float* const* out_peers, int lb, int64_t stride_b, int64_t stride_t, int* err_flag,
+                                 dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
+    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
+                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, stream);
+}
+int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
+                                 const int64_t* offsets, int64_t N, int T, int B, int D, const float* psw,
+                                 float* const* out_peers, int lb, int64_t stride_b, int64_t stride_t, int* err_flag,
+                                 dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
+    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
+                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, stream);
 }
 }

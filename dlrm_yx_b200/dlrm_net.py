@@ -96,6 +96,41 @@ class _ExchangeInteractMixed(torch.autograd.Function):
         return dx, send, None, None
 
 
+class _PeerInteract(torch.autograd.Function):
+    """Multi-process, exchange fused into the kernels over NVLink peer memory (ext_dist.PeerExchange): the pooled rows
+    were stored into this rank's interaction input by the peers' lookup kernels; backward pushes the gradient slices
+    into the table owners' buffers and runs the fused sort + update of the local tables.  out_cols > 0 selects the
+    bf16-facing interaction kernels (x, R, dR, dx in bf16)."""
+
+    @staticmethod
+    def forward(ctx, x, emb, indices, offsets, peer, itself, out_cols):
+        feat = peer.feat_ready()
+        ctx.emb, ctx.peer, ctx.itself, ctx.mixed = emb, peer, bool(itself), out_cols > 0
+        if ctx.mixed:
+            x = x.contiguous()
+            ctx.save_for_backward(feat, x, indices, offsets)
+            return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
+        feat[:, 0, :].copy_(x)
+        ctx.save_for_backward(feat, x, indices, offsets)
+        return ops.interact_dot_fwd(feat, ctx.itself)
+
+    @staticmethod
+    def backward(ctx, dR):
+        feat, x, indices, offsets = ctx.saved_tensors
+        peer = ctx.peer
+        if ctx.mixed:
+            dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
+        else:
+            dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
+            dx = dfeat[:, 0, :]
+        peer.push_grad(dfeat)
+        grad = peer.grad_ready()
+        T_r = grad.shape[1]
+        if T_r > 0:
+            ctx.emb.fused_backward(grad, indices, offsets, peer.W * peer.lb, stride_b=T_r * peer.D, stride_t=peer.D)
+        return dx, None, None, None, None, None, None
+
+
 class _ExchangeInteract(torch.autograd.Function):
     """Multi-process: completes the all-to-all into the feature block, then dot interaction.
     backward packs the block gradient and starts the transposed exchange (completed by the request's
@@ -316,11 +351,36 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
+    def enable_peer_exchange(self, local_batch):
+        """Replaces the NCCL all-to-all of distributed_forward by kernels that store straight into the peers'
+        memory over NVLink (ext_dist.PeerExchange).  Needs fuse_sparse_arch + batched_emb and a fixed local batch."""
+        if not (self.fuse_sparse_arch and self.batched_emb):
+            raise _lib.DlrmxError("enable_peer_exchange needs batched_emb=True and fuse_sparse_arch=True")
+        dev = next(self.parameters()).device
+        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, int(self.ln_bot[-1]), dev)
+        return self
+
+    def _peer_forward(self, dense_x, lS_o, lS_i):
+        peer = self._peer
+        emb = self._batched_module()
+        with record_function("module::forward_pass::embedding_lookup"):
+            peer.lookup_and_scatter(emb.table_set(), lS_i, lS_o)
+        with record_function("module::forward_pass::bottom_mlp"):
+            x = self.apply_mlp(dense_x, self.bot_l)
+        with record_function("module::forward_pass::interaction"):
+            cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
+            z = _PeerInteract.apply(x, emb, lS_i, lS_o, peer, self.arch_interaction_itself, cols)
+        with record_function("module::forward_pass::top_mlp"):
+            p = self.apply_mlp(z, self.top_l)
+        return self._clamp(p)
+
     def distributed_forward(self, dense_x, lS_o, lS_i):
         """Local tables x full global batch -> all-to-all (overlapped with the bottom MLP) -> local batch x
         all tables -> interaction -> top MLP (dlrm_s_pytorch.py:686-730)."""
         if not isinstance(self.emb_l, nn.ModuleList):
             self.emb_l = nn.ModuleList([self.emb_l])
+        if getattr(self, "_peer", None) is not None:
+            return self._peer_forward(dense_x, lS_o, lS_i)
         with record_function("module::forward_pass::embedding_lookup"):
             if self.batched_emb:
                 ly = self.apply_emb_batched([lS_o], [lS_i])

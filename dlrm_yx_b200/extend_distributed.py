@@ -220,6 +220,65 @@ def alltoall(inputs, per_rank_table_splits, batched_emb=False):
     return myreq
 
 
+class PeerExchange(object):
+    """The alltoall of pooled embeddings / gradients (extend_distributed.py:601-639) WITHOUT a collective: every
+    rank's interaction input [lb, 1+T, D] and pooled-row gradient buffer [W*lb, T_r, D] live in peer-mapped
+    (symmetric) memory, the lookup kernel stores each pooled row straight into the owner rank's interaction input
+    (dlrmx_embbag_fwd_scatter) and the gradient slices are stored straight into the table owners' buffers
+    (dlrmx_a2a_push_grad), all over NVLink.  Ranks meet at a device barrier before the first and after the last remote
+    store of each direction.  One instance per model; buffers are allocated once.
+
+    tables_per_rank[p] = tables held by rank p (rank-major global table order, as the reference's cat produces)."""
+
+    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = dist.group.WORLD if group is None else group
+        self.W, self.rank = my_size, my_rank
+        self.tpr = [int(t) for t in tables_per_rank]
+        self.T = sum(self.tpr)
+        self.lb, self.D = int(local_batch), int(emb_dim)
+        self.first = [sum(self.tpr[:p]) for p in range(self.W)]
+        T_r = self.tpr[self.rank]
+        F = 1 + self.T
+        n_feat = self.lb * F * self.D
+        n_grad = self.W * self.lb * max(T_r, 1) * self.D
+        self._feat_flat = symm_mem.empty(n_feat, dtype=torch.float32, device=device)
+        self._grad_flat = symm_mem.empty(n_grad, dtype=torch.float32, device=device)
+        self.h_feat = symm_mem.rendezvous(self._feat_flat, self.group)
+        self.h_grad = symm_mem.rendezvous(self._grad_flat, self.group)
+        self.feat = self._feat_flat.view(self.lb, F, self.D)                         # my interaction input
+        self.grad = self._grad_flat[:self.W * self.lb * T_r * self.D].view(self.W * self.lb, T_r, self.D)
+        # forward: where MY tables' rows go inside peer p's interaction input (feature slot 1 + first[rank])
+        fptr = [int(q) + (1 + self.first[self.rank]) * self.D * 4 for q in self.h_feat.buffer_ptrs]
+        self.out_peers = torch.tensor(fptr, dtype=torch.int64, device=device)
+        # backward: where MY local batch's chunk starts inside owner p's gradient buffer [W*lb, T_p, D]
+        self.push_bases = [int(q) + self.rank * self.lb * self.tpr[p] * self.D * 4
+                           for p, q in enumerate(self.h_grad.buffer_ptrs)]
+        self.stride_b, self.stride_t = F * self.D, self.D
+
+    def barrier(self, which):
+        (self.h_feat if which == 0 else self.h_grad).barrier()
+
+    def lookup_and_scatter(self, table_set, indices, offsets):
+        """All local tables x the global batch; every pooled row lands in its sample owner's `feat`."""
+        self.h_feat.barrier()                  # peers are done reading the previous contents of their feat
+        ops.embbag_forward_scatter(table_set, indices, offsets, self.W * self.lb, self.out_peers, self.lb,
+                                   self.stride_b, self.stride_t)
+
+    def feat_ready(self):
+        self.h_feat.barrier()                  # every peer's rows have landed in my feat
+        return self.feat
+
+    def push_grad(self, dfeat):
+        """dfeat [lb, 1+T, D]: features 1.. go to the table owners' `grad` buffers."""
+        self.h_grad.barrier()                  # owners are done with the previous step's gradients
+        ops.a2a_push_grad(dfeat, 1, self.tpr, self.lb, self.D, self.push_bases)
+
+    def grad_ready(self):
+        self.h_grad.barrier()
+        return self.grad
+
+
 def all_gather(input, lengths=None, dim=0):
     """Concatenation of every rank's tensor along `dim` (extend_distributed.py:642-645); `lengths[p]` gives
     rank p's extent when they differ."""

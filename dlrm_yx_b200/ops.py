@@ -125,6 +125,26 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
     return out
 
 
+def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b, stride_t, validate=False):
+    """embbag_forward with the exchange fused in: bag (t, b) of the global batch is stored at
+    out_peers[b // lb] + (b % lb)*stride_b + t*stride_t (out_peers: device int64 tensor of peer-mapped pointers)."""
+    tables.refresh()
+    _need_cuda(indices, offsets, out_peers)
+    indices = indices.contiguous()
+    offsets = offsets.contiguous()
+    T, D = tables.T, tables.D
+    if offsets.numel() < T * B:
+        raise _lib.DlrmxError("offsets has %d entries, need at least T*B = %d" % (offsets.numel(), T * B))
+    if out_peers.dtype != torch.int64 or out_peers.numel() * lb != B:
+        raise _lib.DlrmxError("out_peers must hold B / lb int64 pointers")
+    fn = getattr(_lib.load(), "dlrmx_embbag_fwd_scatter_" + _idx_suffix(indices, offsets))
+    with _timed("embbag_fwd"):
+        rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0, indices.data_ptr(),
+                offsets.data_ptr(), indices.numel(), T, B, D, 0, out_peers.data_ptr(), lb, stride_b, stride_t, 0,
+                _stream())
+        _lib.check(rc, "dlrmx_embbag_fwd_scatter")
+
+
 def bwd_sort(tables, indices, offsets, B):
     """(sorted_key uint32-as-int32 tensor [N], sorted_bag int32 [N]): global row ids of all looked-up
     indices, stably sorted, with the bag each one came from."""
@@ -264,6 +284,16 @@ def interact_dot_bwd_mixed(feat, x_bf16, dout, itself=False):
 
 def _int_array(values):
     return (ctypes.c_int * len(values))(*[int(v) for v in values])
+
+
+def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases):
+    """dfeat[:, feat_off + t, :] -> rank p's chunk [lb, T_p, D] at peer_chunk_bases[p] (peer-mapped addresses)."""
+    _need_cuda(dfeat)
+    bases = (ctypes.c_void_p * len(peer_chunk_bases))(*[int(b) for b in peer_chunk_bases])
+    with _timed("a2a_push_grad"):
+        rc = _lib.load().dlrmx_a2a_push_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
+                                             _int_array(tables_per_rank), lb, D, bases, _stream())
+        _lib.check(rc, "dlrmx_a2a_push_grad")
 
 
 def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):

@@ -204,6 +204,33 @@ int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
                         const int* host_tables_per_rank, int lb, int D,
                         float* send, dlrmx_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Exchange fused into the producing kernels over NVLink peer memory (no NCCL call, no send / receive
+ * staging, no unpack pass).  Replaces the same reference code as the block above (ext_dist.alltoall,
+ * extend_distributed.py:405-508, 601-639) when every rank's interaction input and pooled-row gradient
+ * buffer are peer-mapped (CUDA VMM / torch symmetric memory); ranks synchronise with a device barrier
+ * before the first and after the last remote store (host layer: dlrm_yx_b200/extend_distributed.py).
+ *
+ * embbag_fwd_scatter: dlrmx_embbag_fwd, but the pooled row of bag (t, b) of the GLOBAL batch is stored
+ *   at  out_peers[b / lb] + (b % lb)*stride_b + t*stride_t : out_peers is a DEVICE array [B / lb] of
+ *   peer-mapped pointers, each already offset to this rank's first feature slot in that peer's
+ *   [lb, 1+T, D] interaction input.
+ * a2a_push_grad: dfeat [lb, F, D] (this rank's local batch, all tables) -> for every owner rank p the
+ *   chunk [lb, T_p, D] stored at host_peer_chunk_bases[p] (HOST array [W] of peer-mapped device
+ *   pointers = rank p's gradient buffer [W*lb, T_p, D] + my_rank*lb*T_p*D).
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows,
+                                 const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
+                                 int D, const float* per_sample_weights, float* const* out_peers, int lb,
+                                 int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
+int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows,
+                                 const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
+                                 int D, const float* per_sample_weights, float* const* out_peers, int lb,
+                                 int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
+int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+                        const int* host_tables_per_rank, int lb, int D,
+                        float* const* host_peer_chunk_bases, dlrmx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
