@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
                     help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
     ap.add_argument("--sharder", default="traffic")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="launch the step kernel by kernel instead of replaying the captured CUDA graph")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = exchange fused into the kernels over NVLink peer memory; 'nccl' = all_to_all_single")
     ap.add_argument("--optimizer", default="rwsadagrad", choices=["rwsadagrad", "sgd"])
@@ -244,29 +246,47 @@ def run_ours(args):
     for i in range(max(args.warmup, 3)):
         step(*devb[i % nb])
     sync()
+    use_graph = not args.no_graph and opt is None
+    run = step
+    if use_graph:
+        # the whole step (forward, backward, sparse update, tower optimizer) as ONE CUDA graph; a batch is copied
+        # into the graph's input buffers (device-to-device in region 1, pinned host-to-device in region 2)
+        from dlrm_yx_b200.graph import GraphedTrainStep
+        l0 = _lib.launch_count()
+        run = GraphedTrainStep(step, devb[0], warmup=2)
+        launches_per_step = (_lib.launch_count() - l0) // 3          # 2 warm-up steps + the captured one
+        for i in range(3):
+            run(*devb[i % nb])
+        sync()
 
     # ---- timed region 1: inputs resident in HBM --------------------------------------------------
     sampler = ClockSampler(torch.cuda.current_device())
     sampler.start()
-    ops.PROFILE = {}
     l0 = _lib.launch_count()
-    ms_dev, _ = timed(lambda i: step(*devb[i % nb]), args.steps)
-    launches = _lib.launch_count() - l0
-    prof = ops.profile_summary()
-    ops.PROFILE = None
+    ms_dev, _ = timed(lambda i: run(*devb[i % nb]), args.steps)
+    launches = launches_per_step * args.steps if use_graph else _lib.launch_count() - l0
 
     # ---- timed region 2: end to end, host buffers in, loss out, every step --------------------------
     def e2e_step(i):
         hb = host[i % nb]
+        if use_graph:
+            return float(run(*hb).item())                     # pinned H2D into the graph inputs, replay, D2H loss
         X, idx, off, tgt = [t.to(dev, non_blocking=True) for t in hb]
         return float(step(X, idx, off, tgt).item())          # D2H read of the step's result
     for i in range(2):
         e2e_step(i)
     _, wall_e2e = timed(e2e_step, args.steps)
+
+    # ---- per-kernel durations: CUDA events around every launch of libdlrmx, same K steps launched eagerly (a graph
+    #      replay cannot carry per-kernel events) ----------------------------------------------------------
+    ops.PROFILE = {}
+    ms_eager, _ = timed(lambda i: step(*devb[i % nb]), args.steps)
+    prof = ops.profile_summary()
+    ops.PROFILE = None
     clocks = sampler.stop()
     h2d = sum(t.numel() * t.element_size() for t in host[0])
     return dict(W=W, rank=rank, cfg=cfg, lb=lb, B_global=B_global, local_tables=local_tables, ms_dev=ms_dev,
-                wall_e2e=wall_e2e, launches=launches, prof=prof, clocks=clocks, h2d=h2d, devb=devb, model=m)
+                wall_e2e=wall_e2e, launches=launches, prof=prof, ms_eager=ms_eager, use_graph=use_graph, clocks=clocks, h2d=h2d, devb=devb, model=m)
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -378,7 +398,12 @@ def main():
         "roofline": {"kernel": "embbag_fwd_kernel (table-batched embedding-bag forward)", "bound": "hbm",
                      "achieved": f["GBps"], "peak": peak, "unit": "GB/s", "frac": f["frac"], "traffic": None,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": fwd_b,
-                     "ms_per_launch": f["ms"]},
+                     "ms_per_launch": f["ms"],
+                     "timing": "CUDA events around each launch, %d eager steps of the same workload right after the "
+                               "timed regions (%.3f ms/step eager; the headline regions %s)"
+                               % (K, r["ms_eager"] / K, "replay one CUDA graph per step, which cannot carry per-kernel "
+                                  "events" if r["use_graph"] else "are eager too")},
+        "launch_mode": "cuda-graph (whole step)" if r["use_graph"] else "eager",
         "kernels": kern,
     }
     if W == 1 and not args.no_cpu_baseline:

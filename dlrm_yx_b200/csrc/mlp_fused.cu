@@ -35,9 +35,10 @@ __device__ __forceinline__ Bf16x8 ld_stream16(const __nv_bfloat16* p) {   // rea
 
 __global__ void __launch_bounds__(kRbThreads)
 relu_bwd_bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
-                          __nv_bfloat16* __restrict__ dz, float* __restrict__ db_partial, int B, int N,
-                          int rows_per_chunk, int relu) {
+                          __nv_bfloat16* __restrict__ dz, float* __restrict__ db_partial, float* __restrict__ db,
+                          unsigned int* __restrict__ counters, int B, int N, int rows_per_chunk, int relu) {
     __shared__ float red[kRbRowLanes][kRbColVecs * 8 + 8];
+    __shared__ bool is_last;
     const int cv = threadIdx.x % kRbColVecs, rl = threadIdx.x / kRbColVecs;
     const int col = (blockIdx.x * kRbColVecs + cv) * 8;
     const int r0 = blockIdx.y * rows_per_chunk, r1 = min(B, r0 + rows_per_chunk);
@@ -94,6 +95,42 @@ relu_bwd_bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
             db_partial[(size_t)blockIdx.y * N + gc] = t;
         }
     }
+    if (db == nullptr) return;
+    // Second stage without a second launch: the CTA that finishes LAST for this column block adds the per-chunk
+    // partials in a fixed order (row lane q takes chunks q, q+8, ...; the 8 lane sums are then added in lane
+    // order), so the result does not depend on which CTA that is.  The counter is left at zero for the next call.
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int done = atomicAdd(&counters[blockIdx.x], 1u);
+        is_last = (done == gridDim.y - 1);
+        if (is_last) counters[blockIdx.x] = 0u;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = 0.f;
+    if (col < N) {
+        for (int k = rl; k < (int)gridDim.y; k += kRbRowLanes) {
+            const float4* pp = reinterpret_cast<const float4*>(db_partial + (size_t)k * N + col);
+            const float4 a = __ldcg(pp), b4 = __ldcg(pp + 1);
+            s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
+            s[4] += b4.x; s[5] += b4.y; s[6] += b4.z; s[7] += b4.w;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[rl][cv * 8 + i] = s[i];
+    __syncthreads();
+    for (int c = threadIdx.x; c < kRbColVecs * 8; c += kRbThreads) {
+        const int gc = blockIdx.x * kRbColVecs * 8 + c;
+        if (gc < N) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < kRbRowLanes; ++q) t += red[q][c];
+            db[gc] = t;
+        }
+    }
 }
 
 // mode 0: SGD  p -= lr * g ;  mode 1: Adagrad  acc += g*g ; p -= lr * g / (sqrt(acc) + eps)
@@ -143,15 +180,18 @@ dense_opt_kernel(int mode, float* __restrict__ p, float* __restrict__ acc, float
 }  // namespace dlrmx
 
 extern "C" {
-int dlrmx_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db_partial, int B, int N, int chunks,
-                             int relu, dlrmx_stream_t stream) {
+int dlrmx_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db_partial, float* db,
+                             unsigned int* counters, int B, int N, int chunks, int relu, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(B >= 0 && N > 0 && N % 8 == 0 && chunks >= 1, "relu_bwd_bias_grad: need N %% 8 == 0, chunks >= 1");
-    DLRMX_REQUIRE((((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dz) & 15) == 0, "relu_bwd_bias_grad: 16-B alignment");
+    DLRMX_REQUIRE((((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dz | (uintptr_t)db_partial) & 15) == 0,
+                  "relu_bwd_bias_grad: 16-B alignment");
+    DLRMX_REQUIRE(db == nullptr || counters != nullptr, "relu_bwd_bias_grad: db needs the counters workspace");
     const int rows_per_chunk = (int)ceil_div(B > 0 ? B : 1, chunks);
     dim3 grid((unsigned)ceil_div(N, kRbColVecs * 8), (unsigned)chunks);
     relu_bwd_bias_grad_kernel<<<grid, kRbThreads, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dz, db_partial, B, N, rows_per_chunk, relu);
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dz, db_partial, db, counters, B, N,
+        rows_per_chunk, relu);
     return check_launch("relu_bwd_bias_grad");
 }
 

@@ -241,7 +241,7 @@ class PeerExchange(object):
         T_r = self.tpr[self.rank]
         F = 1 + self.T
         n_feat = self.lb * F * self.D
-        n_grad = self.W * self.lb * max(T_r, 1) * self.D
+        n_grad = self.W * self.lb * max(max(self.tpr), 1) * self.D     # symmetric: same size on every rank
         self._feat_flat = symm_mem.empty(n_feat, dtype=torch.float32, device=device)
         self._grad_flat = symm_mem.empty(n_grad, dtype=torch.float32, device=device)
         self.h_feat = symm_mem.rendezvous(self._feat_flat, self.group)

@@ -1,0 +1,43 @@
+"""Whole-step CUDA graph: forward + backward + sparse update + tower optimizer captured once, replayed per batch.
+
+The training step of this path is ~80 short kernels (lookup, interaction, a dozen GEMMs, fused element-wise passes,
+sort, update) of 10-200 us each; launched one by one from Python the GPU idles between them.  Capturing the step
+removes the launch gaps and fixes the cross-stream overlap (sort / sparse update beside the towers) once and for all.
+
+Requirements (checked or documented): static shapes -- the packed index count N must not change between batches
+(fixed bag lengths, e.g. the one-index-per-lookup Criteo layout); constant learning rates (they are baked into the
+kernel arguments at capture); no host synchronisation inside the step.  The warm-up runs before capture ARE real
+training steps on the example batch.
+"""
+import torch
+
+
+class GraphedTrainStep(object):
+    def __init__(self, step_fn, example_inputs, warmup=3, pool=None):
+        """step_fn(*tensors) -> loss tensor, a full training step using only the tensors it is given (plus module
+        state).  example_inputs: device tensors of the shapes / dtypes every later batch will have."""
+        self.static = [t.clone() for t in example_inputs]
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(max(int(warmup), 1)):
+                step_fn(*self.static)
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, pool=pool):
+            self.loss = step_fn(*self.static)
+
+    def load(self, *inputs):
+        """Stream-ordered copies of a batch (device tensors, or pinned host tensors) into the graph's inputs."""
+        for dst, src in zip(self.static, inputs):
+            if dst.shape != src.shape or dst.dtype != src.dtype:
+                raise ValueError("graphed step needs static shapes: got %s %s, captured %s %s"
+                                 % (tuple(src.shape), src.dtype, tuple(dst.shape), dst.dtype))
+            dst.copy_(src, non_blocking=True)
+
+    def __call__(self, *inputs):
+        self.load(*inputs)
+        self.graph.replay()
+        return self.loss

@@ -57,8 +57,7 @@ class _LinearAct(torch.autograd.Function):
         L = ctx.mlp.layers[ctx.li]
         dyb = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         dyb = dyb.contiguous()
-        dz, part = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"))
-        torch.sum(part, dim=0, out=L.gb)
+        dz, _ = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"), db=L.gb)
         L.gW.copy_(torch.mm(dz.t(), hb, out_dtype=torch.float32))
         dx = None
         if ctx.needs_input_grad[0]:

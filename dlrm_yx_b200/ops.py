@@ -329,19 +329,29 @@ def rows_update(optimizer, weight, mom, rows, gsum, lr, eps=0.0):
     _lib.check(rc, "dlrmx_rows_update")
 
 
-def relu_bwd_bias_grad(dy, y, relu=True, chunks=None):
+_RB_COUNTERS = {}
+
+
+def relu_bwd_bias_grad(dy, y, relu=True, chunks=None, db=None):
     """(dz bf16 [B,N], db_partial fp32 [chunks,N]): dz = dy * (y > 0) and per-chunk column sums of dz, one pass.
-    chunks=None sizes the grid for >= 6 CTAs of 256 threads per SM (148 SMs) with at least 32 rows per chunk."""
-    _need_cuda(dy, y)
+    With `db` (fp32 [N]) the kernel also finishes the column sums into it (deterministic last-CTA reduce).
+    chunks=None sizes the grid for >= 4 CTAs of 256 threads per SM (148 SMs) with at least 32 rows per chunk."""
+    _need_cuda(dy, y, db)
     B, N = dy.shape
+    col_blocks = (N + 255) // 256
     if chunks is None:
-        col_blocks = (N + 255) // 256
-        chunks = max(1, min((B + 31) // 32, (148 * 6 + col_blocks - 1) // col_blocks))
+        chunks = max(1, min((B + 31) // 32, (148 * 4 + col_blocks - 1) // col_blocks))
     dz = torch.empty_like(dy) if relu else dy
     part = torch.empty((chunks, N), dtype=torch.float32, device=dy.device)
+    counters = None
+    if db is not None:
+        key = (dy.device, torch.cuda.current_stream().cuda_stream)
+        counters = _RB_COUNTERS.get(key)
+        if counters is None or counters.numel() < col_blocks:
+            counters = _RB_COUNTERS[key] = torch.zeros(max(col_blocks, 64), dtype=torch.int32, device=dy.device)
     with _timed("relu_bwd_bias_grad"):
-        rc = _lib.load().dlrmx_relu_bwd_bias_grad(dy.data_ptr(), y.data_ptr(), dz.data_ptr(), part.data_ptr(), B, N,
-                                                  chunks, int(relu), _stream())
+        rc = _lib.load().dlrmx_relu_bwd_bias_grad(dy.data_ptr(), y.data_ptr(), dz.data_ptr(), part.data_ptr(), _ptr(db),
+                                                  _ptr(counters), B, N, chunks, int(relu), _stream())
         _lib.check(rc, "dlrmx_relu_bwd_bias_grad")
     return dz, part
 

@@ -182,11 +182,14 @@ int dlrmx_interact_dot_bwd_mixed(const float* feat, int64_t feat_stride_b, const
  *   sums of dz into db_partial [chunks, N] fp32 (the bias gradient is their sum over chunks).
  * dense_opt: ONE launch over a flat parameter buffer: mode 0 = torch.optim.SGD (dlrm_s_pytorch.py:1640)
  *   p -= lr*g ; mode 1 = Adagrad, the dense branch of RWSAdagrad.step (optim/rwsadagrad.py:115-118)
+ *   db (optional) [N] receives the column sums themselves: the CTA finishing last per 256-column block adds the
+ *   chunk partials in a fixed order (deterministic); counters = ceil(N/256) uint32, zero before the first call, left
+ *   zero by every call.
  *   acc += g*g ; p -= lr * g / (sqrt(acc) + eps).  g is scaled by grad_scale first and cleared afterwards;
  *   shadow_bf16 (optional) receives the bf16 copy of p that the GEMMs read.
  * ------------------------------------------------------------------------------------------- */
-int dlrmx_relu_bwd_bias_grad(const void* dy_bf16, const void* y_bf16, void* dz_bf16, float* db_partial, int B,
-                             int N, int chunks, int relu, dlrmx_stream_t stream);
+int dlrmx_relu_bwd_bias_grad(const void* dy_bf16, const void* y_bf16, void* dz_bf16, float* db_partial, float* db,
+                             unsigned int* counters, int B, int N, int chunks, int relu, dlrmx_stream_t stream);
 int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
                     float eps, float grad_scale, dlrmx_stream_t stream);
 

@@ -136,6 +136,15 @@ def test_relu_bwd_bias_grad_kernel():
     dz2, part2 = ops.relu_bwd_bias_grad(dy, y, relu=False, chunks=3)
     assert dz2 is dy
     torch.testing.assert_close(part2.sum(0), dy.float().sum(0), rtol=1e-5, atol=1e-4)
+    # in-kernel second stage: deterministic, equal to the sum of the partials, counters self-reset (call it twice)
+    for _ in range(2):
+        db = torch.full((N,), float("nan"), device="cuda")
+        dz3, part3 = ops.relu_bwd_bias_grad(dy, y, relu=True, db=db)
+        assert torch.equal(dz3, dz)
+        torch.testing.assert_close(db, want.sum(0), rtol=1e-5, atol=1e-4)
+    db2 = torch.empty((N,), device="cuda")
+    ops.relu_bwd_bias_grad(dy, y, relu=True, db=db2)
+    assert torch.equal(db, db2)
 
 
 @pytest.mark.parametrize("name", ["c4_terabyte_small_rws", "c2_kaggle_small_rws", "c3_multihot_sgd"])
@@ -177,3 +186,55 @@ def test_bf16_tower_model_tracks_the_reference_step(golden_dir, name):
             assert num ** 0.5 <= 0.2 * den ** 0.5, (num ** 0.5, den ** 0.5)
     np.testing.assert_allclose(losses[0], float(g["loss"]), rtol=1e-2)
     np.testing.assert_allclose(losses[1], float(g["loss2"]), rtol=2e-2)
+
+
+def test_graphed_train_step_equals_eager_steps(golden_dir):
+    """GraphedTrainStep (whole step captured as one CUDA graph) against the same steps launched eagerly: same seeded
+    model, same batch sequence (the graph's 2 warm-up runs are real steps on the example batch).  Tables and
+    accumulators within rtol 1e-4 / atol 1e-6 and losses within 1e-3 (the library GEMMs may pick a different algorithm
+    under capture, which moves bf16 roundings; everything in libdlrmx is launch-mode independent)."""
+    import os
+    from dlrm_yx_b200 import data, dlrm_net, embedding
+    from dlrm_yx_b200.graph import GraphedTrainStep
+    g = np.load(os.path.join(golden_dir, "c4_terabyte_small_rws.npz"))
+    T, D = len(g["meta_ln_emb"]), int(g["meta_misc"][0])
+    lr = float(g["meta_lr"])
+
+    def build():
+        np.random.seed(int(g["meta_misc"][4]))
+        m = dlrm_net.DLRM_Net(D, g["meta_ln_emb"], g["meta_ln_bot"], g["meta_ln_top"], arch_interaction_op="dot",
+                              sigmoid_bot=-1, sigmoid_top=len(g["meta_ln_top"]) - 2, batched_emb=True,
+                              emb_optimizer=embedding.Optimizer.EXACT_ROWWISE_ADAGRAD, emb_learning_rate=lr,
+                              fuse_sparse_arch=True).cuda()
+        return m.fuse_mlps(lr, "adagrad")
+
+    idx, off = data.pack([torch.from_numpy(g["off_%d" % k]) for k in range(T)],
+                         [torch.from_numpy(g["idx_%d" % k]) for k in range(T)])
+    X, tgt = torch.from_numpy(g["X"]).cuda(), torch.from_numpy(g["target"]).cuda()
+    b0 = (X, idx.cuda(), off.cuda(), tgt)
+    gen = torch.Generator().manual_seed(5)
+    rows = torch.from_numpy(np.repeat(g["meta_ln_emb"].astype(np.int64), X.shape[0]))
+    b1 = (torch.rand(X.shape, generator=gen).cuda(),
+          (torch.rand(idx.shape, generator=gen) * (rows - 1)).round().to(idx.dtype).cuda() if idx.numel() == rows.numel()
+          else idx.cuda(), off.cuda(), (torch.rand(tgt.shape, generator=gen) > 0.5).float().cuda())
+
+    def make_step(m):
+        def step(X, idx, off, tgt):
+            loss = m.loss_fn(m(X, off, idx), tgt)
+            loss.backward()
+            m.step_mlps()
+            return loss
+        return step
+
+    me, mg = build(), build()
+    se = make_step(me)
+    eager_losses = [se(*b0).item(), se(*b0).item()]                 # == the graph's two warm-up steps
+    gs = GraphedTrainStep(make_step(mg), b0, warmup=2)
+    for b in (b1, b0, b1):
+        le = se(*b).item()
+        lg = gs(*b).item()
+        np.testing.assert_allclose(lg, le, rtol=1e-3)
+    for we, wg in zip(me._batched_module().split_weights(), mg._batched_module().split_weights()):
+        np.testing.assert_allclose(wg.cpu().numpy(), we.cpu().numpy(), rtol=1e-4, atol=1e-6)
+    with pytest.raises(ValueError):
+        gs(X[:-1], b0[1], b0[2], tgt)                               # static shapes are enforced
