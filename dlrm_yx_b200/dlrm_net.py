@@ -25,6 +25,57 @@ from . import _lib, embedding, interaction, ops, sharders
 from . import extend_distributed as ext_dist
 
 
+# ---- second stream for the gradient-independent / tower-independent halves of the sparse path -----------------
+# forward : the radix sort of the looked-up rows (needed only by the backward) runs beside lookup, interaction and
+#           top MLP;
+# backward: the fused reduce + sparse-optimizer update runs beside the bottom-MLP backward and the tower optimizer.
+# The main stream re-joins when autograd's backward pass ends (engine callback), so anything the caller does after
+# loss.backward() is ordered after the update.  Works eagerly and under CUDA-graph capture (fork / join pattern).
+_SIDE = {}
+OVERLAP_STREAMS = True        # False: everything on the caller's stream (per-kernel timing wants kernels alone)
+
+
+def _side_stream(device):
+    if not OVERLAP_STREAMS:
+        return torch.cuda.current_stream()
+    s = _SIDE.get(device)
+    if s is None:
+        s = _SIDE[device] = torch.cuda.Stream(device=device)
+    return s
+
+
+def _sort_on_side(emb, indices, offsets, B):
+    main = torch.cuda.current_stream()
+    side = _side_stream(indices.device)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        presorted = emb.sort_lookups(indices, offsets, B)
+    return presorted
+
+
+def _update_on_side(emb, grad, indices, offsets, B, stride_b, stride_t, presorted, before=None, keep=()):
+    """Runs `before()` (optional, e.g. the gradient exchange) and the fused update on the side stream, after
+    everything enqueued so far on the main stream; the main stream joins at the end of the backward pass.  `keep`:
+    tensors the side-stream work reads -- held until the join so their memory cannot be handed out earlier."""
+    main = torch.cuda.current_stream()
+    side = _side_stream(grad.device)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        if before is not None:
+            grad = before()
+        if grad is not None:
+            emb.fused_backward(grad, indices, offsets, B, stride_b=stride_b, stride_t=stride_t, presorted=presorted)
+    held = [grad, presorted, keep]
+
+    if side is main or side == main:
+        return
+
+    def join():
+        torch.cuda.current_stream().wait_stream(side)
+        held.clear()
+    torch.autograd.Variable._execution_engine.queue_callback(join)
+
+
 class _SparseArchLocal(torch.autograd.Function):
     """Single-GPU fused lookup + dot interaction.  forward(x [B,D]) -> R [B, D + F(F-1)/2]."""
 
@@ -37,6 +88,7 @@ class _SparseArchLocal(torch.autograd.Function):
                            stride_b=(1 + T) * D, stride_t=D)
         feat[:, 0, :].copy_(x)
         ctx.emb, ctx.itself = emb, bool(itself)
+        ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None
         ctx.save_for_backward(feat, indices, offsets)
         return ops.interact_dot_fwd(feat, ctx.itself)
 
@@ -45,7 +97,8 @@ class _SparseArchLocal(torch.autograd.Function):
         feat, indices, offsets = ctx.saved_tensors
         B, F, D = feat.shape
         dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
-        ctx.emb.fused_backward(dfeat[:, 1:, :], indices, offsets, B, stride_b=F * D, stride_t=D)
+        _update_on_side(ctx.emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, ctx.presorted, keep=(dfeat,))
+        ctx.presorted = None
         return dfeat[:, 0, :], None, None, None, None, None
 
 
@@ -62,6 +115,7 @@ class _SparseArchLocalMixed(torch.autograd.Function):
                            stride_b=(1 + T) * D, stride_t=D)
         x = x.contiguous()
         ctx.emb, ctx.itself = emb, bool(itself)
+        ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None
         ctx.save_for_backward(feat, x, indices, offsets)
         return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
 
@@ -70,7 +124,8 @@ class _SparseArchLocalMixed(torch.autograd.Function):
         feat, x, indices, offsets = ctx.saved_tensors
         B, F, D = feat.shape
         dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
-        ctx.emb.fused_backward(dfeat[:, 1:, :], indices, offsets, B, stride_b=F * D, stride_t=D)
+        _update_on_side(ctx.emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, ctx.presorted, keep=(dfeat,))
+        ctx.presorted = None
         return dx, None, None, None, None, None, None
 
 
@@ -103,9 +158,10 @@ class _PeerInteract(torch.autograd.Function):
     bf16-facing interaction kernels (x, R, dR, dx in bf16)."""
 
     @staticmethod
-    def forward(ctx, x, emb, indices, offsets, peer, itself, out_cols):
-        feat = peer.feat_ready()
+    def forward(ctx, x, emb, indices, offsets, peer, itself, out_cols, presorted):
+        feat = peer.feat
         ctx.emb, ctx.peer, ctx.itself, ctx.mixed = emb, peer, bool(itself), out_cols > 0
+        ctx.presorted = presorted
         if ctx.mixed:
             x = x.contiguous()
             ctx.save_for_backward(feat, x, indices, offsets)
@@ -123,12 +179,16 @@ class _PeerInteract(torch.autograd.Function):
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
-        peer.push_grad(dfeat)
-        grad = peer.grad_ready()
-        T_r = grad.shape[1]
-        if T_r > 0:
-            ctx.emb.fused_backward(grad, indices, offsets, peer.W * peer.lb, stride_b=T_r * peer.D, stride_t=peer.D)
-        return dx, None, None, None, None, None, None
+        T_r = peer.grad.shape[1]
+
+        def exchange():                       # on the side stream: barrier, push over NVLink, barrier
+            peer.push_grad(dfeat)
+            grad = peer.grad_ready()
+            return grad if T_r > 0 else None
+        _update_on_side(ctx.emb, dfeat, indices, offsets, peer.W * peer.lb, T_r * peer.D, peer.D, ctx.presorted,
+                        before=exchange, keep=(dfeat,))
+        ctx.presorted = None
+        return dx, None, None, None, None, None, None, None
 
 
 class _ExchangeInteract(torch.autograd.Function):
@@ -363,13 +423,21 @@ class DLRM_Net(nn.Module):
     def _peer_forward(self, dense_x, lS_o, lS_i):
         peer = self._peer
         emb = self._batched_module()
+        main = torch.cuda.current_stream()
+        side = _side_stream(dense_x.device)
+        side.wait_stream(main)
         with record_function("module::forward_pass::embedding_lookup"):
-            peer.lookup_and_scatter(emb.table_set(), lS_i, lS_o)
+            with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sort) beside the bottom MLP
+                peer.lookup_and_scatter(emb.table_set(), lS_i, lS_o)
+                arrived = side.record_event()
+                presorted = (emb.sort_lookups(lS_i, lS_o, peer.W * peer.lb)
+                             if torch.is_grad_enabled() and emb.T > 0 else None)
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
         with record_function("module::forward_pass::interaction"):
+            main.wait_event(arrived)
             cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
-            z = _PeerInteract.apply(x, emb, lS_i, lS_o, peer, self.arch_interaction_itself, cols)
+            z = _PeerInteract.apply(x, emb, lS_i, lS_o, peer, self.arch_interaction_itself, cols, presorted)
         with record_function("module::forward_pass::top_mlp"):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)

@@ -146,14 +146,19 @@ class TableBatchedEmbeddingBags(nn.Module):
     def current_lr(self):
         return self.learning_rate / (1.0 + self.step_count * self.lr_decay)
 
-    def fused_backward(self, grad_out, indices, offsets, B, stride_b=None, stride_t=None):
+    def sort_lookups(self, indices, offsets, B):
+        """(sorted global row ids, bag of each) -- the gradient-independent half of the backward; callers may run it
+        early (e.g. on a side stream during the forward pass) and hand the result to `fused_backward`."""
+        return ops.bwd_sort(self.table_set(), indices, offsets, B)
+
+    def fused_backward(self, grad_out, indices, offsets, B, stride_b=None, stride_t=None, presorted=None):
         """grad_out: gradient of the pooled rows, [B, T, D] (or any layout given by the strides)."""
         ts = self.table_set()
         if stride_b is None:
             if grad_out.stride(2) != 1 or grad_out.stride(1) % 4 or grad_out.stride(0) % 4:
                 grad_out = grad_out.contiguous()
             stride_b, stride_t = grad_out.stride(0), grad_out.stride(1)
-        skey, sbag = ops.bwd_sort(ts, indices, offsets, B)
+        skey, sbag = presorted if presorted is not None else ops.bwd_sort(ts, indices, offsets, B)
         kind = _lib.OPT_RWSADAGRAD if self.optimizer in _ROWWISE else _lib.OPT_SGD
         ops.bwd_update(ts, kind, grad_out, stride_b, stride_t, B, skey, sbag, self.current_lr(), self.eps)
         self.step_count += 1

@@ -260,14 +260,13 @@ class PeerExchange(object):
         (self.h_feat if which == 0 else self.h_grad).barrier()
 
     def lookup_and_scatter(self, table_set, indices, offsets):
-        """All local tables x the global batch; every pooled row lands in its sample owner's `feat`."""
+        """All local tables x the global batch; every pooled row lands in its sample owner's `feat`.  On return
+        (stream-ordered) every peer's rows have landed in MY `feat` as well."""
         self.h_feat.barrier()                  # peers are done reading the previous contents of their feat
-        ops.embbag_forward_scatter(table_set, indices, offsets, self.W * self.lb, self.out_peers, self.lb,
-                                   self.stride_b, self.stride_t)
-
-    def feat_ready(self):
+        if self.tpr[self.rank] > 0:
+            ops.embbag_forward_scatter(table_set, indices, offsets, self.W * self.lb, self.out_peers, self.lb,
+                                       self.stride_b, self.stride_t)
         self.h_feat.barrier()                  # every peer's rows have landed in my feat
-        return self.feat
 
     def push_grad(self, dfeat):
         """dfeat [lb, 1+T, D]: features 1.. go to the table owners' `grad` buffers."""

@@ -17,6 +17,10 @@ class GraphedTrainStep(object):
         """step_fn(*tensors) -> loss tensor, a full training step using only the tensors it is given (plus module
         state).  example_inputs: device tensors of the shapes / dtypes every later batch will have."""
         self.static = [t.clone() for t in example_inputs]
+        # parameters created on the default stream accumulate their gradients on the capture stream here: intended
+        quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+        if quiet is not None:
+            quiet(False)
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
         side.wait_stream(cur)

@@ -24,8 +24,11 @@ class _timed:
 
     def __enter__(self):
         if PROFILE is not None:
-            self.s = torch.cuda.Event(enable_timing=True)
-            self.e = torch.cuda.Event(enable_timing=True)
+            # under CUDA-graph capture: external events become event-record NODES of the graph, so every replay
+            # re-records them and elapsed_time() gives the kernel's duration inside the replayed step
+            ext = torch.cuda.is_current_stream_capturing()
+            self.s = torch.cuda.Event(enable_timing=True, external=True) if ext else torch.cuda.Event(enable_timing=True)
+            self.e = torch.cuda.Event(enable_timing=True, external=True) if ext else torch.cuda.Event(enable_timing=True)
             self.s.record()
 
     def __exit__(self, *a):
