@@ -33,6 +33,31 @@ class GraphedTrainStep(object):
         with torch.cuda.graph(self.graph, pool=pool):
             self.loss = step_fn(*self.static)
 
+    def prefetch(self, *host_inputs):
+        """Starts the host-to-device copies of the NEXT batch on a copy stream (pinned host tensors), into a staging
+        set, so they run beside the step that is executing; `run_prefetched()` then moves them into the graph inputs
+        with device-to-device copies (a few microseconds) and replays."""
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream()
+            self._staging = [torch.empty_like(t) for t in self.static]
+            self._staged = torch.cuda.Event()
+            self._consumed = torch.cuda.Event()
+            self._consumed.record()
+        self._copy_stream.wait_event(self._consumed)          # the previous staging contents have been consumed
+        with torch.cuda.stream(self._copy_stream):
+            for dst, src in zip(self._staging, host_inputs):
+                dst.copy_(src, non_blocking=True)
+            self._staged.record()
+
+    def run_prefetched(self):
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._staged)
+        for dst, src in zip(self.static, self._staging):
+            dst.copy_(src, non_blocking=True)
+        self._consumed.record()
+        self.graph.replay()
+        return self.loss
+
     def load(self, *inputs):
         """Stream-ordered copies of a batch (device tensors, or pinned host tensors) into the graph's inputs."""
         for dst, src in zip(self.static, inputs):
