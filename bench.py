@@ -421,6 +421,11 @@ def main():
         if name in r["prof"]:
             kern[name] = {"ms": round(r["prof"][name][1], 4), "calls_per_step": r["prof"][name][0] / K}
     f = kern["embbag_fwd"]
+    traffic = None                       # DRAM bytes per launch of that kernel from the committed ncu --set full capture
+    tp = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")
+    if os.path.exists(tp) and W == 1 and args.config == "terabyte" and not args.rows_cap:
+        tj = json.load(open(tp))
+        traffic = tj["embbag_fwd_kernel"]["dram_read_bytes"] + tj["embbag_fwd_kernel"]["dram_write_bytes"]
     line = {
         "metric": "DLRM train samples/sec", "value": Bg * K / (r["ms_dev"] / 1e3), "unit": "samples/s",
         "n_gpus": W, "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / K,
@@ -440,7 +445,7 @@ def main():
         "gpu_launches": r["launches"],
         "clocks": r["clocks"],
         "roofline": {"kernel": "embbag_fwd_kernel (table-batched embedding-bag forward)", "bound": "hbm",
-                     "achieved": f["GBps"], "peak": peak, "unit": "GB/s", "frac": f["frac"], "traffic": None,
+                     "achieved": f["GBps"], "peak": peak, "unit": "GB/s", "frac": f["frac"], "traffic": traffic,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": fwd_b,
                      "ms_per_launch": f["ms"],
                      "timing": ("CUDA events (external event-record nodes) around each launch inside a single-stream CUDA "
