@@ -441,6 +441,14 @@ int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
     return 1;
 }
 
+// one-warp-per-sample kernels of interact_warp.cu; return 1 when they took the shape
+int interact_fwd_warp(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
+                      void* out_bf16, int64_t ostride, cudaStream_t st, int* rc);
+int interact_bwd_warp(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
+                      const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16,
+                      cudaStream_t st, int* rc);
+enum { DLRMX_TUNE_IX_WARP = 4 };     // tunable 4 = 1: one-warp-per-sample kernels (measured slower, see interact_warp.cu)
+
 // bf16-facing variants.  Return 0 on success, a negative code (message set) when the shape is not supported.
 int interact_fwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
                        void* out_bf16, int64_t ostride, cudaStream_t st) {
@@ -450,6 +458,10 @@ int interact_fwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B
         set_error("interact_dot_fwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, even "
                   "out_stride >= D + nz (F=%d D=%d out_stride=%lld)", F, D, (long long)ostride);
         return DLRMX_E_ARG;
+    }
+    if (get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
+        int rc = 0;
+        if (interact_fwd_warp(feat, fsb, x_bf16, B, F, D, itself, out_bf16, ostride, st, &rc)) return rc;
     }
     const size_t smem = (2 * (size_t)F * (D + 4) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4 + 2 * (size_t)D * 2;
     if (smem > 200 * 1024) { set_error("interact_dot_fwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
@@ -474,6 +486,11 @@ int interact_bwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B
                   "dout_stride %% 8 == 0 and >= D + nz rounded up to 8 (F=%d D=%d dout_stride=%lld)", F, D,
                   (long long)dstride);
         return DLRMX_E_ARG;
+    }
+    if (get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
+        int rc = 0;
+        if (interact_bwd_warp(feat, fsb, x_bf16, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, dx_bf16, st, &rc))
+            return rc;
     }
     const int nchunk = (D + nz + 7) >> 3;
     const size_t smem = (2 * ((size_t)F * (D + 8) + 4 * nchunk + 4 + (D >> 1)) + 32 * 36) * 4;

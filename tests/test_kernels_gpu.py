@@ -232,13 +232,16 @@ def test_interaction_fwd_bwd(F, D, itself):
 
 @pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (2, 8), (32, 32)])
 @pytest.mark.parametrize("itself", [False, True])
-def test_interaction_mixed_bf16_facing(F, D, itself):
+@pytest.mark.parametrize("warp_kernel", [0, 1])
+def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, request):
     """bf16-facing interaction (feature 0 in / result out / dR in / dx out as bf16, single-pass TF32 products, fp32
     accumulate) against the fp32 oracle on the SAME bf16-rounded inputs.  Bars: bf16 outputs 2^-8 relative (one bf16
     rounding, half an ulp = 2^-9, with margin) plus the TF32 operand rounding 2^-10 * sum|a||b|; fp32 outputs the
     TF32 term only.  Padding columns must be exactly zero."""
-    from dlrm_yx_b200 import ops
+    from dlrm_yx_b200 import _lib, ops
     dev = cuda()
+    _lib.set_tunable(4, warp_kernel)          # 1: the one-warp-per-sample experiment (interact_warp.cu)
+    request.addfinalizer(lambda: _lib.set_tunable(4, 0))
     rng = np.random.default_rng(F * 100 + D + 7)
     B = 21
     bf = torch.bfloat16

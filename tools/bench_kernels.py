@@ -145,6 +145,17 @@ def main():
     ms, mn = timed(lambda: ops.interact_dot_fwd(feat), args.iters)
     nz = F * (F - 1) // 2
     report("interact_fwd", ms, mn, B * F * D * 4 + B * (D + nz) * 4)
+    if ops.interact_mixed_supported(F, D):
+        cols = (D + nz + 7) // 8 * 8
+        xb = torch.randn((B, D), device=dev).to(torch.bfloat16)
+        doutb = torch.randn((B, cols), device=dev).to(torch.bfloat16)
+        for cta in (0, 1):
+            _lib.set_tunable(4, cta)
+            ms, mn = timed(lambda: ops.interact_dot_fwd_mixed(feat, xb, cols), args.iters)
+            report("interact_mixed_fwd", ms, mn, B * ((F - 1) * D * 4 + D * 2) + B * cols * 2, dict(warp_kernel=cta))
+            ms, mn = timed(lambda: ops.interact_dot_bwd_mixed(feat, xb, doutb), args.iters)
+            report("interact_mixed_bwd", ms, mn, B * (2 * (F - 1) * D * 4 + 2 * D * 2 + cols * 2), dict(warp_kernel=cta))
+        _lib.set_tunable(4, 0)
     dout = torch.randn((B, D + nz), device=dev)
     ms, mn = timed(lambda: ops.interact_dot_bwd(feat, dout), args.iters)
     report("interact_bwd", ms, mn, 2 * B * F * D * 4 + B * (D + nz) * 4)
