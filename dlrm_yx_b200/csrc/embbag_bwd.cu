@@ -16,20 +16,36 @@ __device__ __forceinline__ T bshfl64(unsigned mask, T v, int src) {
 // for run ends, the table-row / accumulator pointers), so the key -> bag -> pointer chain costs one round of
 // memory latency per G positions; positions are then consumed K at a time with K gradient rows (and the table
 // rows of the runs ending there) in flight per lane.
+//
+// Runs that cross a segment boundary INSIDE the CTA (its 256/G groups own consecutive segments) are finished by the CTA
+// itself: every group parks its head / tail partial in shared memory, and after one barrier the group where such a run
+// starts adds the following groups' head partials in ascending order and applies the update.  Only runs that cross a
+// CTA boundary leave partials in global memory (one head / one tail row per CTA) for `bwd_fixup_kernel`, whose chains
+// are 256/G times shorter than with per-segment partials.
+enum { kHasHead = 1, kHeadClosed = 2, kHasTail = 4, kActive = 8 };
+
 template <int VEC, int G, int CH, int K>
 __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(const BwdParams P) {
+    constexpr int GPC = 256 / G;             // groups (= segments) per CTA
+    extern __shared__ __align__(16) float sh_part[];     // [2][GPC][D]: head partials, tail partials
+    __shared__ unsigned char sh_flag[GPC];
     const int gl = threadIdx.x & (G - 1);
+    const int gi = threadIdx.x / G;
     const unsigned gmask = group_mask<G>();
     const int gshift = (threadIdx.x & 31) & ~(G - 1);
-    const int64_t seg = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
-    if (seg >= P.nseg) return;
-    const int64_t p0 = seg * P.seg_len, p1 = min(P.N, p0 + P.seg_len);
+    const int64_t seg = (int64_t)blockIdx.x * GPC + gi;
+    const bool active = seg < P.nseg;
+    const int64_t p0 = seg * P.seg_len, p1 = active ? min(P.N, p0 + P.seg_len) : p0;
     const int col0 = gl * VEC;
     const uint32_t* __restrict__ skey = P.skey;
     const int32_t* __restrict__ sbag = P.sbag;
+    float* sh_head = sh_part + (size_t)gi * P.D;
+    float* sh_tail = sh_part + (size_t)(GPC + gi) * P.D;
+    unsigned flags = active ? kActive : 0;
 
     bool owned = true;                       // does the first run START in this segment?
-    if (p0 > 0) owned = skey[p0 - 1] != skey[p0];
+    if (active && p0 > 0) owned = skey[p0 - 1] != skey[p0];
+    if (!owned) flags |= kHasHead;
     RowVec<VEC> acc[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c) acc[c].zero();
@@ -131,7 +147,7 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
                 for (int j = 0; j < K; ++j)
                     if (l[j]) {
                         mnew[j] = __fadd_rn(mo[j], row_mean(P, ss[j]));
-                        a[j] = __fdiv_rn(-P.lr, __fadd_rn(__fsqrt_rn(mnew[j]), P.eps));
+                        a[j] = adagrad_step(P.lr, mnew[j], P.eps);
                     }
             }
             // ---- stage 4: apply / park the finished runs -----------------------------------------------------
@@ -148,7 +164,8 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
                             }
                         if (P.optimizer == DLRMX_OPT_RWSADAGRAD && gl == 0) *mp[j] = mnew[j];
                     } else {
-                        store_partial<VEC, G, CH>(P.head_partial, seg, P.D, col0, g[j]);
+                        store_partial<VEC, G, CH>(sh_head, 0, P.D, col0, g[j]);
+                        flags |= kHeadClosed;
                     }
                     owned = true;
                 }
@@ -167,8 +184,72 @@ __global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(cons
             }
         }
     }
-    if (open)   // the segment ends inside a run
-        store_partial<VEC, G, CH>(owned ? P.tail_partial : P.head_partial, seg, P.D, col0, acc);
+    if (open) {   // the segment ends inside a run
+        store_partial<VEC, G, CH>(owned ? sh_tail : sh_head, 0, P.D, col0, acc);
+        if (owned) flags |= kHasTail;
+    }
+    if (gl == 0) sh_flag[gi] = (unsigned char)flags;
+    __syncthreads();
+
+    // ---- runs crossing segment boundaries inside this CTA ------------------------------------------------------
+    if ((flags & kHasTail) != 0) {
+        // acc still holds my tail partial; add the head partials of the groups after me, in order
+        int v = gi + 1;
+        bool closed = false;
+        for (; v < GPC && (sh_flag[v] & kActive); ++v) {
+            const float* hp = sh_part + (size_t)v * P.D + col0;
+#pragma unroll
+            for (int c = 0; c < CH; ++c)
+                if (CH == 1 || col0 + c * G * VEC < P.D) {
+                    RowVec<VEC> h;
+                    h.load(hp + c * G * VEC);
+                    acc[c].add(h);
+                }
+            if (sh_flag[v] & kHeadClosed) { closed = true; break; }
+        }
+        if (closed) {
+            const uint32_t key = skey[p1 - 1];
+            const int bag = sbag[p1 - 1];
+            const int t = bag / P.B;
+            const int64_t row = (int64_t)key - P.row_base[t];
+            float* wp = P.tables[t] + row * P.D + col0;
+            RowVec<VEC> w[CH];
+#pragma unroll
+            for (int c = 0; c < CH; ++c)
+                if (CH == 1 || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
+            float* mp = nullptr;
+            float mo = 0.f;
+            if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
+                mp = P.moms[t] + row;
+                mo = *mp;
+            }
+            apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
+        } else {                                   // the run leaves the CTA: one tail partial per CTA
+            store_partial<VEC, G, CH>(P.tail_partial, blockIdx.x, P.D, col0, acc);
+        }
+    }
+    if (gi == 0 && (flags & kHasHead) != 0) {      // the run that entered the CTA from the left: one head partial per CTA
+        RowVec<VEC> hacc[CH];
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            hacc[c].zero();
+            if (CH == 1 || col0 + c * G * VEC < P.D) hacc[c].load(sh_part + col0 + c * G * VEC);
+        }
+        if ((flags & kHeadClosed) == 0) {
+            for (int v = 1; v < GPC && (sh_flag[v] & kActive); ++v) {
+                const float* hp = sh_part + (size_t)v * P.D + col0;
+#pragma unroll
+                for (int c = 0; c < CH; ++c)
+                    if (CH == 1 || col0 + c * G * VEC < P.D) {
+                        RowVec<VEC> h;
+                        h.load(hp + c * G * VEC);
+                        hacc[c].add(h);
+                    }
+                if (sh_flag[v] & kHeadClosed) break;
+            }
+        }
+        store_partial<VEC, G, CH>(P.head_partial, blockIdx.x, P.D, col0, hacc);
+    }
 }
 
 // Finishes runs that cross segment boundaries.  One group per segment; only the segment where a crossing run
@@ -342,11 +423,17 @@ static int launch_rows_update(int optimizer, float* W, float* mom, const int64_t
 template <int VEC, int G, int CH>
 static int launch_update(const BwdParams& P, cudaStream_t st) {
     const int threads = 256;
-    const unsigned blocks = (unsigned)ceil_div(P.nseg * G, threads);
-    bwd_update_kernel<VEC, G, CH, (CH == 1 ? 4 : 2)><<<blocks, threads, 0, st>>>(P);
+    constexpr int GPC = 256 / G;
+    const unsigned blocks = (unsigned)ceil_div(P.nseg, (int64_t)GPC);
+    const size_t smem = (size_t)2 * GPC * P.D * sizeof(float);
+    bwd_update_kernel<VEC, G, CH, (CH == 1 ? 4 : 2)><<<blocks, threads, smem, st>>>(P);
     int rc = check_launch("bwd_update");
     if (rc) return rc;
-    bwd_fixup_kernel<VEC, G, CH><<<blocks, threads, 0, st>>>(P);
+    // the fix-up works on CTA tiles: GPC segments each, one head / tail partial per tile
+    BwdParams Q = P;
+    Q.seg_len = P.seg_len * GPC;
+    Q.nseg = blocks;
+    bwd_fixup_kernel<VEC, G, CH><<<(unsigned)ceil_div((int64_t)blocks * G, threads), threads, 0, st>>>(Q);
     return check_launch("bwd_fixup");
 }
 

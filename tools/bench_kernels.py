@@ -26,6 +26,9 @@ SHAPES = {
     "c2": dict(rows=KAGGLE, D=16, B=128, L=1),
     "c3": dict(rows=[1000000] * 8, D=64, B=2048, L=100),
     "c4": dict(rows=TERABYTE, D=128, B=32768, L=1),
+    "c4d64": dict(rows=TERABYTE, D=64, B=65536, L=1),          # probe: random 256-byte rows, one per bag
+    "c3big": dict(rows=[1000000] * 8, D=64, B=16384, L=100),   # probe: C3 with 8x the bags (no wave-quantisation tail)
+    "c3d128": dict(rows=[1000000] * 8, D=128, B=2048, L=100),  # probe: C3 with 512-byte rows
 }
 
 
