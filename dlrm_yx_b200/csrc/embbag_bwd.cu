@@ -25,7 +25,7 @@ __device__ __forceinline__ T bshfl64(unsigned mask, T v, int src) {
 enum { kHasHead = 1, kHeadClosed = 2, kHasTail = 4, kActive = 8 };
 
 template <int VEC, int G, int CH, int K>
-__global__ void __launch_bounds__(256, (CH == 1) ? 3 : 2) bwd_update_kernel(const BwdParams P) {
+__global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(const BwdParams P) {
     constexpr int GPC = 256 / G;             // groups (= segments) per CTA
     extern __shared__ __align__(16) float sh_part[];     // [2][GPC][D]: head partials, tail partials
     __shared__ unsigned char sh_flag[GPC];
@@ -420,13 +420,13 @@ static int launch_rows_update(int optimizer, float* W, float* mom, const int64_t
     return check_launch("rows_update");
 }
 
-template <int VEC, int G, int CH>
+template <int VEC, int G, int CH, int K = (CH == 1 ? 4 : 2)>
 static int launch_update(const BwdParams& P, cudaStream_t st) {
     const int threads = 256;
     constexpr int GPC = 256 / G;
     const unsigned blocks = (unsigned)ceil_div(P.nseg, (int64_t)GPC);
     const size_t smem = (size_t)2 * GPC * P.D * sizeof(float);
-    bwd_update_kernel<VEC, G, CH, (CH == 1 ? 4 : 2)><<<blocks, threads, smem, st>>>(P);
+    bwd_update_kernel<VEC, G, CH, K><<<blocks, threads, smem, st>>>(P);
     int rc = check_launch("bwd_update");
     if (rc) return rc;
     // the fix-up works on CTA tiles: GPC segments each, one head / tail partial per tile
@@ -518,17 +518,8 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     P.tail_partial = (float*)((char*)workspace + align_up((size_t)P.nseg * D * 4, 256));
     cudaStream_t st = (cudaStream_t)stream;
 #define DLRMX_CALL_UPDATE(V, G_, C) launch_update<V, G_, C>(P, st)
-    // Wide rows (D = 128..512 with 16-B lanes): narrower groups with several column chunks per lane, so one warp
-    // walks 2 or 4 segments at once and the per-position scalar work (shuffles, pointers, sqrt, division) is shared.
-    if (g.vec == 4 && g.g == 32 && D % 128 == 0) {
-        const int tune = get_tunable(DLRMX_TUNE_BWD_K);
-        const int nv = D / 4;
-        if (tune == 8 && nv / 8 <= 4) return launch_update<4, 8, 4>(P, st);
-        if (tune == 16 && nv / 16 <= 4) {
-            if (nv / 16 == 2) return launch_update<4, 16, 2>(P, st);
-            if (nv / 16 == 4) return launch_update<4, 16, 4>(P, st);
-        }
-    }
+    // experiment knob (tunable 1 = 8): 8 positions in flight per lane for one-warp-per-row geometries
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 8) return launch_update<4, 32, 1, 8>(P, st);
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;

@@ -112,11 +112,25 @@ relu_bwd_bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
 #pragma unroll
     for (int i = 0; i < 8; ++i) s[i] = 0.f;
     if (col < N) {
-        for (int k = rl; k < (int)gridDim.y; k += kRbRowLanes) {
-            const float4* pp = reinterpret_cast<const float4*>(db_partial + (size_t)k * N + col);
-            const float4 a = __ldcg(pp), b4 = __ldcg(pp + 1);
-            s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
-            s[4] += b4.x; s[5] += b4.y; s[6] += b4.z; s[7] += b4.w;
+        constexpr int UP = 8;                 // partial rows in flight per thread: this tail is pure L2 latency
+        for (int kb = rl; kb < (int)gridDim.y; kb += kRbRowLanes * UP) {
+            float4 a[UP], b4[UP];
+#pragma unroll
+            for (int u = 0; u < UP; ++u) {
+                const int k = kb + u * kRbRowLanes;
+                if (k < (int)gridDim.y) {
+                    const float4* pp = reinterpret_cast<const float4*>(db_partial + (size_t)k * N + col);
+                    a[u] = __ldcg(pp);
+                    b4[u] = __ldcg(pp + 1);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UP; ++u) {
+                if (kb + u * kRbRowLanes < (int)gridDim.y) {
+                    s[0] += a[u].x; s[1] += a[u].y; s[2] += a[u].z; s[3] += a[u].w;
+                    s[4] += b4[u].x; s[5] += b4[u].y; s[6] += b4[u].z; s[7] += b4[u].w;
+                }
+            }
         }
     }
 #pragma unroll
@@ -177,6 +191,135 @@ dense_opt_kernel(int mode, float* __restrict__ p, float* __restrict__ acc, float
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Head of the top tower: Linear(K -> 1) + Sigmoid (the last create_mlp layer, dlrm_s_pytorch.py:227-265 with
+// sigmoid_layer = last) on a bf16 activation, fp32 master weights.  A 1-column GEMM is a row-wise dot product: HBM-bound
+// on reading h once (forward) and reading h + writing dh once (backward); torch runs it as ~10 kernels (fp32 copy of h,
+// gemv, sigmoid, their backward, casts).
+//   forward : p[b] = sigmoid(sum_k h[b,k] w[k] + bias), one warp per row, 16-byte loads.
+//   backward: dz = dp * p * (1 - p);  dh[b,:] = bf16(dz * w);  gw[k] = sum_b dz[b] h[b,k];  gb = sum_b dz[b]
+//             -- per-chunk partials, finished in a fixed order by the CTA that ends last (deterministic).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
+                float* __restrict__ p, int B, int K, int sigmoid) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= B) return;
+    float acc = 0.f;
+    for (int k8 = lane; k8 < (K >> 3); k8 += 32) {
+        const Bf16x8 hv = ld_stream16(h + row * K + 8 * k8);
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + 8 * k8));
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + 8 * k8) + 1);
+        const float2 a = __bfloat1622float2(hv.v[0]), b2 = __bfloat1622float2(hv.v[1]);
+        const float2 c = __bfloat1622float2(hv.v[2]), d = __bfloat1622float2(hv.v[3]);
+        acc = fmaf(a.x, w0.x, acc); acc = fmaf(a.y, w0.y, acc); acc = fmaf(b2.x, w0.z, acc); acc = fmaf(b2.y, w0.w, acc);
+        acc = fmaf(c.x, w1.x, acc); acc = fmaf(c.y, w1.y, acc); acc = fmaf(d.x, w1.z, acc); acc = fmaf(d.y, w1.w, acc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+        const float z = acc + bias[0];
+        p[row] = sigmoid ? 1.f / (1.f + expf(-z)) : z;
+    }
+}
+
+__global__ void __launch_bounds__(kRbThreads)
+head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const __nv_bfloat16* __restrict__ h,
+                const float* __restrict__ w, __nv_bfloat16* __restrict__ dh, float* __restrict__ gw_partial,
+                float* __restrict__ gw, float* __restrict__ gb, unsigned int* __restrict__ counters, int B, int K,
+                int rows_per_chunk, int sigmoid) {
+    // partial layout: [chunks, K + 8]; column K holds the chunk's sum of dz
+    __shared__ float red[kRbRowLanes][kRbColVecs * 8 + 8];
+    __shared__ float redz[kRbRowLanes];
+    __shared__ bool is_last;
+    const int cv = threadIdx.x % kRbColVecs, rl = threadIdx.x / kRbColVecs;
+    const int col = (blockIdx.x * kRbColVecs + cv) * 8;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(B, r0 + rows_per_chunk);
+    const int KP = K + 8;
+    float s[8], sz = 0.f, wv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { s[i] = 0.f; wv[i] = (col < K) ? w[col + i] : 0.f; }
+    if (col < K) {
+        constexpr int U = 4;
+        for (int rb = r0 + rl; rb < r1; rb += kRbRowLanes * U) {
+            Bf16x8 hv[U];
+            float dz[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int r = rb + u * kRbRowLanes;
+                dz[u] = 0.f;
+                if (r < r1) {
+                    hv[u] = ld_stream16(h + (size_t)r * K + col);
+                    const float pr = __ldg(p + r);
+                    dz[u] = sigmoid ? __ldg(dp + r) * pr * (1.f - pr) : __ldg(dp + r);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int r = rb + u * kRbRowLanes;
+                if (r < r1) {
+                    Bf16x8 o;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float2 hf = __bfloat1622float2(hv[u].v[i]);
+                        s[2 * i] = fmaf(dz[u], hf.x, s[2 * i]);
+                        s[2 * i + 1] = fmaf(dz[u], hf.y, s[2 * i + 1]);
+                        o.v[i] = __floats2bfloat162_rn(dz[u] * wv[2 * i], dz[u] * wv[2 * i + 1]);
+                    }
+                    *reinterpret_cast<Bf16x8*>(dh + (size_t)r * K + col) = o;
+                    sz += dz[u];
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) red[rl][cv * 8 + i] = s[i];
+    if (cv == 0) redz[rl] = sz;
+    __syncthreads();
+    for (int c = threadIdx.x; c < kRbColVecs * 8; c += kRbThreads) {
+        const int gc = blockIdx.x * kRbColVecs * 8 + c;
+        if (gc < K) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < kRbRowLanes; ++q) t += red[q][c];
+            gw_partial[(size_t)blockIdx.y * KP + gc] = t;
+        }
+    }
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int q = 0; q < kRbRowLanes; ++q) t += redz[q];
+        gw_partial[(size_t)blockIdx.y * KP + K] = t;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int done = atomicAdd(&counters[blockIdx.x], 1u);
+        is_last = (done == gridDim.y - 1);
+        if (is_last) counters[blockIdx.x] = 0u;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // fixed-order final sums: thread c owns column c of this column block (and one thread the dz column)
+    for (int c = threadIdx.x; c < kRbColVecs * 8 + 1; c += kRbThreads) {
+        const bool zc = (c == kRbColVecs * 8);
+        const int gc = zc ? K : blockIdx.x * kRbColVecs * 8 + c;
+        if ((zc && blockIdx.x != 0) || (!zc && gc >= K)) continue;
+        float t[4] = {0.f, 0.f, 0.f, 0.f};
+        int k = 0;
+        for (; k + 4 <= (int)gridDim.y; k += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) t[u] += __ldcg(gw_partial + (size_t)(k + u) * KP + gc);
+        }
+        for (; k < (int)gridDim.y; ++k) t[0] += __ldcg(gw_partial + (size_t)k * KP + gc);
+        const float tot = (t[0] + t[1]) + (t[2] + t[3]);
+        if (zc) gb[0] = tot; else gw[gc] = tot;
+    }
+}
+
 }  // namespace dlrmx
 
 extern "C" {
@@ -206,5 +349,33 @@ int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* sha
     dense_opt_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(mode, params, acc, grads, (__nv_bfloat16*)shadow_bf16, n,
                                                              lr, eps, grad_scale);
     return check_launch("dense_opt");
+}
+
+int dlrmx_head_fwd(const void* h_bf16, const float* w, const float* bias, float* p, int B, int K, int sigmoid,
+                   dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(B >= 0 && K > 0 && K % 8 == 0, "head_fwd: need K %% 8 == 0");
+    DLRMX_REQUIRE((((uintptr_t)h_bf16 | (uintptr_t)w) & 15) == 0, "head_fwd: 16-B alignment");
+    if (B == 0) return DLRMX_OK;
+    head_fwd_kernel<<<(unsigned)ceil_div((int64_t)B * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)h_bf16, w, bias, p, B, K, sigmoid);
+    return check_launch("head_fwd");
+}
+
+size_t dlrmx_head_bwd_workspace_bytes(int K, int chunks) { return (size_t)chunks * (K + 8) * sizeof(float); }
+
+int dlrmx_head_bwd(const float* dp, const float* p, const void* h_bf16, const float* w, void* dh_bf16, float* gw,
+                   float* gb, float* workspace, unsigned int* counters, int B, int K, int chunks, int sigmoid,
+                   dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(B >= 0 && K > 0 && K % 8 == 0 && chunks >= 1, "head_bwd: need K %% 8 == 0, chunks >= 1");
+    DLRMX_REQUIRE((((uintptr_t)h_bf16 | (uintptr_t)dh_bf16) & 15) == 0, "head_bwd: 16-B alignment");
+    DLRMX_REQUIRE(workspace != nullptr && counters != nullptr && gw != nullptr && gb != nullptr, "head_bwd: null buffer");
+    const int rows_per_chunk = (int)ceil_div(B > 0 ? B : 1, chunks);
+    dim3 grid((unsigned)ceil_div(K, kRbColVecs * 8), (unsigned)chunks);
+    head_bwd_kernel<<<grid, kRbThreads, 0, (cudaStream_t)stream>>>(dp, p, (const __nv_bfloat16*)h_bf16, w,
+                                                                   (__nv_bfloat16*)dh_bf16, workspace, gw, gb, counters,
+                                                                   B, K, rows_per_chunk, sigmoid);
+    return check_launch("head_bwd");
 }
 }

@@ -67,6 +67,26 @@ class _LinearAct(torch.autograd.Function):
         return dx, None, None, None
 
 
+class _Head(torch.autograd.Function):
+    """Linear(K -> 1) + Sigmoid on a bf16 activation: one row-wise dot-product kernel each way (fp32 master weights)."""
+
+    @staticmethod
+    def forward(ctx, h, anchor, mlp, li):
+        L = mlp.layers[li]
+        h = h.contiguous()
+        p = ops.head_fwd(h, L.w_master.view(-1), L.b_master, sigmoid=(L.act == "sigmoid"))
+        ctx.mlp, ctx.li = mlp, li
+        ctx.save_for_backward(h, p)
+        return p
+
+    @staticmethod
+    def backward(ctx, dp):
+        h, p = ctx.saved_tensors
+        L = ctx.mlp.layers[ctx.li]
+        dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), L.gW.view(-1), L.gb, sigmoid=(L.act == "sigmoid"))
+        return dh, None, None, None
+
+
 class FusedMLP(nn.Module):
     def __init__(self, sequential, lr, optimizer="adagrad", eps=1e-10, initial_accumulator_value=0.0):
         super().__init__()
@@ -86,6 +106,8 @@ class FusedMLP(nn.Module):
             if L.act is None:
                 raise ValueError("unsupported activation %r" % act)
             L.fused = (L.N % 8 == 0) and L.act == "relu"
+            # single-output head (the tower's last layer): row-wise dot-product kernels instead of a 1-column GEMM
+            L.head = (not L.fused) and L.N == 1 and L.K % 8 == 0 and L.act == "sigmoid"
             L.K_pad = _ceil(L.K, 8) if L.fused else L.K
             L.w_off, off = off, _ceil(off + L.N * L.K_pad, 8)
             L.b_off, off = off, _ceil(off + L.N, 8)
@@ -110,6 +132,8 @@ class FusedMLP(nn.Module):
             L.b_shadow = self.shadow[L.b_off:L.b_off + L.N]
             L.gW = self.grad[L.w_off:L.w_off + nW].view(L.N, L.K_pad)
             L.gb = self.grad[L.b_off:L.b_off + L.N]
+            L.w_master = self.master.data[L.w_off:L.w_off + nW].view(L.N, L.K_pad)
+            L.b_master = self.master.data[L.b_off:L.b_off + L.N]
             if not L.fused:     # plain fp32 torch layer on views of the flat buffers
                 L.w_leaf = self.master.data[L.w_off:L.w_off + nW].view(L.N, L.K_pad).requires_grad_()
                 L.b_leaf = self.master.data[L.b_off:L.b_off + L.N].requires_grad_()
@@ -135,6 +159,8 @@ class FusedMLP(nn.Module):
         for i, L in enumerate(self.layers):
             if L.fused:
                 h = _LinearAct.apply(h, self._anchor, self, i)
+            elif L.head and h.dtype == torch.bfloat16:
+                h = _Head.apply(h, self._anchor, self, i)
             else:
                 z = F.linear(h.float(), L.w_leaf, L.b_leaf)
                 h = torch.sigmoid(z) if L.act == "sigmoid" else torch.relu(z)

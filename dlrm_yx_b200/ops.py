@@ -359,6 +359,39 @@ def relu_bwd_bias_grad(dy, y, relu=True, chunks=None, db=None):
     return dz, part
 
 
+def head_fwd(h, w, bias, sigmoid=True):
+    """p [B, 1] fp32 = sigmoid(h @ w + bias) for a bf16 activation h [B, K] and fp32 w [K], bias [1]."""
+    _need_cuda(h, w, bias)
+    B, K = h.shape
+    p = torch.empty((B, 1), dtype=torch.float32, device=h.device)
+    with _timed("head_fwd"):
+        rc = _lib.load().dlrmx_head_fwd(h.data_ptr(), w.data_ptr(), bias.data_ptr(), p.data_ptr(), B, K, int(sigmoid),
+                                        _stream())
+        _lib.check(rc, "dlrmx_head_fwd")
+    return p
+
+
+def head_bwd(dp, p, h, w, gw, gb, sigmoid=True):
+    """dh bf16 [B, K]; writes gw [K] and gb [1] (fp32) -- backward of head_fwd."""
+    _need_cuda(dp, p, h, w, gw, gb)
+    B, K = h.shape
+    lib = _lib.load()
+    col_blocks = (K + 255) // 256
+    chunks = max(1, min((B + 31) // 32, (148 * 4 + col_blocks - 1) // col_blocks))
+    ws = torch.empty(lib.dlrmx_head_bwd_workspace_bytes(K, chunks) // 4, dtype=torch.float32, device=h.device)
+    key = (h.device, torch.cuda.current_stream().cuda_stream, "head")
+    counters = _RB_COUNTERS.get(key)
+    if counters is None or counters.numel() < col_blocks:
+        counters = _RB_COUNTERS[key] = torch.zeros(max(col_blocks, 64), dtype=torch.int32, device=h.device)
+    dh = torch.empty_like(h)
+    dp = dp.contiguous()
+    with _timed("head_bwd"):
+        rc = lib.dlrmx_head_bwd(dp.data_ptr(), p.data_ptr(), h.data_ptr(), w.data_ptr(), dh.data_ptr(), gw.data_ptr(),
+                                gb.data_ptr(), ws.data_ptr(), counters.data_ptr(), B, K, chunks, int(sigmoid), _stream())
+        _lib.check(rc, "dlrmx_head_bwd")
+    return dh
+
+
 def dense_opt(mode, params, acc, grads, shadow, lr, eps=0.0, grad_scale=1.0):
     """One launch over a flat fp32 parameter buffer: SGD (mode 0) or Adagrad (mode 1); refreshes the bf16 shadow and
     clears the gradients."""

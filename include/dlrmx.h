@@ -193,6 +193,19 @@ int dlrmx_relu_bwd_bias_grad(const void* dy_bf16, const void* y_bf16, void* dz_b
 int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
                     float eps, float grad_scale, dlrmx_stream_t stream);
 
+/* Head of the top tower: Linear(K -> 1) + Sigmoid (last layer of create_mlp with sigmoid_layer = last,
+ * dlrm_s_pytorch.py:227-265) on a bf16 activation h [B, K] with fp32 master weights w [K], bias [1].
+ *   head_fwd: p[b] = sigmoid(<h[b,:], w> + bias)            (sigmoid = 0: no activation)
+ *   head_bwd: dz = dp * p * (1 - p);  dh_bf16[b,:] = dz * w;  gw[k] = sum_b dz h[b,k];  gb[0] = sum_b dz.
+ *             workspace: dlrmx_head_bwd_workspace_bytes(K, chunks); counters: ceil(K/256) uint32, zero before the
+ *             first call, left zero.  Sums are finished in a fixed order (deterministic). */
+int dlrmx_head_fwd(const void* h_bf16, const float* w, const float* bias, float* p, int B, int K, int sigmoid,
+                   dlrmx_stream_t stream);
+size_t dlrmx_head_bwd_workspace_bytes(int K, int chunks);
+int dlrmx_head_bwd(const float* dp, const float* p, const void* h_bf16, const float* w, void* dh_bf16, float* gw,
+                   float* gb, float* workspace, unsigned int* counters, int B, int K, int chunks, int sigmoid,
+                   dlrmx_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Model-parallel exchange helpers.  Replaces the cat / split / contiguous copies around
  * dist.all_to_all_single in extend_distributed.py:405-508 (All2All_Req / All2All_Wait).

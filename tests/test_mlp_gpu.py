@@ -103,6 +103,30 @@ def test_fused_mlp_matches_fp32_tower(ln, sig):
     torch.testing.assert_close(fused.shadow.float(), fused.master.data.to(torch.bfloat16).float())
 
 
+def test_head_linear_sigmoid_kernels():
+    """Linear(K -> 1) + Sigmoid head against torch on the same bf16 activation (fp32 weights): forward 1e-5 relative,
+    backward (dh bf16: 2^-8; gw, gb: 1e-4 of their scale -- different summation order over 4099 rows)."""
+    from dlrm_yx_b200 import ops
+    torch.manual_seed(4)
+    B, K = 4099, 256
+    h = torch.randn(B, K, device="cuda").to(torch.bfloat16)
+    w = (torch.randn(K, device="cuda") * 0.1).requires_grad_()
+    b = torch.randn(1, device="cuda").requires_grad_()
+    p = ops.head_fwd(h, w.detach(), b.detach())
+    hf = h.float().requires_grad_()
+    ref = torch.sigmoid(hf @ w[:, None] + b)
+    torch.testing.assert_close(p, ref, rtol=1e-5, atol=1e-6)
+    dp = torch.randn(B, 1, device="cuda")
+    ref.backward(dp)
+    gw, gb = torch.empty(K, device="cuda"), torch.empty(1, device="cuda")
+    for _ in range(2):                                   # counters self-reset
+        dh = ops.head_bwd(dp, p, h, w.detach(), gw, gb)
+        assert dh.dtype == torch.bfloat16
+        assert torch.all((dh.float() - hf.grad).abs() <= 2.0 ** -8 * hf.grad.abs() + 1e-7)
+        torch.testing.assert_close(gw, w.grad, rtol=1e-4, atol=1e-4 * float(w.grad.abs().max()))
+        torch.testing.assert_close(gb, b.grad, rtol=1e-4, atol=1e-4 * float(b.grad.abs().max()))
+
+
 def test_dense_adagrad_kernel_matches_reference_formula():
     """optim/rwsadagrad.py:115-118: sum += g*g ; p -= clr * g / (sqrt(sum) + eps)."""
     from dlrm_yx_b200 import ops

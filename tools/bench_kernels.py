@@ -131,8 +131,9 @@ def main():
     uniq = [int(ops.bwd_segments(sk)[2].item()) for sk, _ in sorted_batches]
     U = sum(uniq) / len(uniq)
     for opt, name in ((_lib.OPT_SGD, "sgd"), (_lib.OPT_RWSADAGRAD, "rwsadagrad")):
-        for k in (32, 64, 128, 256):
-            _lib.set_tunable(3, k)
+        for k in (64, 1064):
+            _lib.set_tunable(3, k % 1000)
+            _lib.set_tunable(_lib.TUNE_BWD_K, 8 if k > 1000 else 0)
 
             def u():
                 sk, sb = sorted_batches[it[0] % nbatch]
@@ -142,6 +143,7 @@ def main():
             nbytes = T * B * D * 4 + N * 8 + 2 * U * D * 4 + (2 * U * 4 if opt else 0)
             report("bwd_update_" + name, ms, mn, nbytes, dict(K=k, U=int(U)))
     _lib.set_tunable(3, 0)
+    _lib.set_tunable(_lib.TUNE_BWD_K, 0)
 
     F = T + 1
     feat = torch.randn((B, F, D), device=dev)
