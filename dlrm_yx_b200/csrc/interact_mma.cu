@@ -89,6 +89,7 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     // MIXED: the bf16 x row of each stage is parked behind the partials and converted at fragment-load time
     __nv_bfloat16* xs_base = reinterpret_cast<__nv_bfloat16*>(smem + 2 * F * DS + kMmaWarps * nzp);
     const int dv = D >> 2;
+    const int dv_shift = (dv & (dv - 1)) == 0 ? 31 - __clz(dv) : -1;
     const bool two_m = F > 16;
     int rowoff[4];                                        // rows >= F only feed discarded outputs: alias row F-1
 #pragma unroll
@@ -111,9 +112,14 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         if (bb < B) {
             const float* src = feat + bb * fsb;
             float* dstt = smem + which * F * DS;
-            for (int f = warp + (MIXED ? 1 : 0); f < F; f += kMmaWarps)
-                for (int k4 = lane; k4 < dv; k4 += 32)
-                    cp_async16(dstt + f * DS + 4 * k4, src + (int64_t)f * D + 4 * k4);
+            // the F x D block is contiguous in global memory: 16-byte chunk e lands at 4e + (row pad) * (e / dv);
+            // a flat loop with a shift instead of nested row / column loops (the staging loop was ~30 % of the
+            // kernel's issued instructions, ncu r01 v4 source view)
+#pragma unroll 4
+            for (int e = (MIXED ? dv : 0) + threadIdx.x; e < F * dv; e += kMmaWarps * 32) {
+                const int f = dv_shift >= 0 ? (e >> dv_shift) : (e / dv);
+                cp_async16(dstt + 4 * e + 4 * f, src + 4 * e);
+            }
             if (MIXED) {
                 for (int k8 = threadIdx.x; k8 < (D >> 3); k8 += kMmaWarps * 32)
                     cp_async16_raw(xs_base + which * D + 8 * k8, xb + bb * D + 8 * k8);
@@ -156,7 +162,8 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
                 for (int h = 0; h < 2; ++h) {
                     float x = tile[rowoff[r] + k0 + t + 4 * h];
                     if (MIXED) {
-                        if (r == 0 && g == 0) x = __bfloat162float(xs[k0 + t + 4 * h]);     // feature 0 arrives as bf16
+                        // feature 0 arrives as bf16 (a warp-local pre-conversion into row 0 was measured slower)
+                        if (r == 0 && g == 0) x = __bfloat162float(xs[k0 + t + 4 * h]);
                         hi[r][h] = round_tf32(x);
                     } else {
                         split_tf32(x, hi[r][h], lo[r][h]);
@@ -239,6 +246,7 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     const int zbase = MIXED ? D : 0;             // index of dZ[0] inside the staged row
     float* S = smem + 2 * stage_floats;
     const int dv = D >> 2;
+    const int dv_shift = (dv & (dv - 1)) == 0 ? 31 - __clz(dv) : -1;
     const bool two_m = F > 16;
     const int ksteps = (F + 7) >> 3;
 
@@ -269,9 +277,11 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         if (bb < B) {
             const float* src = feat + bb * fsb;
             float* dstt = smem + which * stage_floats;
-            for (int f = warp + (MIXED ? 1 : 0); f < F; f += kMmaWarps)
-                for (int k4 = lane; k4 < dv; k4 += 32)
-                    cp_async16(dstt + f * DS + 4 * k4, src + (int64_t)f * D + 4 * k4);
+#pragma unroll 4
+            for (int e = (MIXED ? dv : 0) + threadIdx.x; e < F * dv; e += kMmaWarps * 32) {
+                const int f = dv_shift >= 0 ? (e >> dv_shift) : (e / dv);
+                cp_async16(dstt + 4 * e + 8 * f, src + 4 * e);         // row stride D + 8
+            }
             if (MIXED) {
                 __nv_bfloat16* zr = reinterpret_cast<__nv_bfloat16*>(dstt + F * DS);
                 for (int q = threadIdx.x; q < nchunk; q += kMmaWarps * 32)
@@ -307,6 +317,11 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         float* dst = dfeat + b * dfsb;
         const float* dx = dout + b * dstride;
         for (int nb = 8 * NT * warp; nb < D; nb += 8 * NT * kMmaWarps) {      // NT column tiles per pass
+            if (MIXED) {     // feature 0 arrives as bf16: this warp's 32 columns of it -> fp32 row 0 of the tile
+                float* row0 = smem + buf * stage_floats;
+                if (nb + lane < D) row0[nb + lane] = __bfloat162float(xs[nb + lane]);
+                __syncwarp();
+            }
             float c[NT][2][4];
 #pragma unroll
             for (int n = 0; n < NT; ++n)
@@ -341,10 +356,9 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
                     if (n0 >= D) break;
                     uint32_t bh0, bl0 = 0, bh1, bl1 = 0;
                     if (MIXED) {
-                        float t0 = ok0 ? tile[j0 * DS + n0 + g] : 0.f;
-                        if (j0 == 0) t0 = __bfloat162float(xs[n0 + g]);          // feature 0 arrives as bf16
-                        bh0 = round_tf32(t0);
-                        bh1 = round_tf32(ok1 ? tile[j1 * DS + n0 + g] : 0.f);
+                        // rows >= F meet zero coefficients of S: alias the last real row (finite) instead of a select
+                        bh0 = round_tf32(tile[min(j0, F - 1) * DS + n0 + g]);
+                        bh1 = round_tf32(tile[min(j1, F - 1) * DS + n0 + g]);
                     } else {
                         split_tf32(ok0 ? tile[j0 * DS + n0 + g] : 0.f, bh0, bl0);
                         split_tf32(ok1 ? tile[j1 * DS + n0 + g] : 0.f, bh1, bl1);
@@ -379,7 +393,7 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
                                     v.y = __fadd_rn(v.y, __bfloat162float(zraw[col + 1]));
                                     *reinterpret_cast<__nv_bfloat162*>(dxb + b * D + col) = __floats2bfloat162_rn(v.x, v.y);
                                 } else {
-                                    *reinterpret_cast<float2*>(dst + (int64_t)i * D + col) = v;
+                                    *reinterpret_cast<float2*>(dst + (i * D + col)) = v;     // 32-bit offset: F*D < 2^15
                                 }
                                 continue;
                             }

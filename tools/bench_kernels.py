@@ -145,6 +145,15 @@ def main():
     _lib.set_tunable(3, 0)
     _lib.set_tunable(_lib.TUNE_BWD_K, 0)
 
+    if args.shape == "c4":
+        for N_ in (128, 256, 512, 1024):
+            y = torch.relu(torch.randn(B, N_, device=dev)).to(torch.bfloat16)
+            dy = torch.randn(B, N_, device=dev).to(torch.bfloat16)
+            db = torch.empty(N_, device=dev)
+            ms, mn = timed(lambda: ops.relu_bwd_bias_grad(dy, y, relu=True, db=db), args.iters)
+            report("relu_bwd_bias_grad", ms, mn, 3 * B * N_ * 2, dict(N=N_))
+            ms, mn = timed(lambda: ops.relu_bwd_bias_grad(dy, y, relu=True), args.iters)
+            report("relu_bwd_bias_grad_nodb", ms, mn, 3 * B * N_ * 2, dict(N=N_))
     F = T + 1
     feat = torch.randn((B, F, D), device=dev)
     ms, mn = timed(lambda: ops.interact_dot_fwd(feat), args.iters)
