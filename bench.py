@@ -43,7 +43,11 @@ def parse():
     ap.add_argument("--sharder", default="traffic")
     ap.add_argument("--no-graph", action="store_true",
                     help="launch the step kernel by kernel instead of replaying the captured CUDA graph")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--microbatches", type=int, default=1,
+                    help="N>1, peer exchange: windows of the local batch whose NVLink transfer overlaps the towers")
+    ap.add_argument("--scatter-ctas", type=int, default=0,
+                    help="N>1, peer exchange: cap on the CTAs of the NVLink scatter / push kernels (0 = full width)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "peer-copy", "nccl"],
                     help="N>1: 'peer' = exchange fused into the kernels over NVLink peer memory; 'nccl' = all_to_all_single")
     ap.add_argument("--optimizer", default="rwsadagrad", choices=["rwsadagrad", "sgd"])
     ap.add_argument("--nbatches", type=int, default=8, help="distinct synthetic batches cycled through")
@@ -167,10 +171,13 @@ def build_model(args, cfg, W):
     m = dlrm_net.DLRM_Net(D, np.array(cfg["rows"]), ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
                           sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True, sharder=args.sharder,
                           emb_optimizer=kind, emb_learning_rate=lr, emb_init="device").cuda()
-    if W > 1 and args.exchange == "peer":
-        m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W)
+    if W > 1 and args.exchange.startswith("peer"):
+        m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W,
+                               engine="copy" if args.exchange == "peer-copy" else "sm")
     if args.mlp == "fused-bf16":
         m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd")
+        if W > 1 and args.exchange.startswith("peer"):
+            m.set_microbatches(args.microbatches)
         return m, None
     dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
     if W > 1:
@@ -188,6 +195,8 @@ def run_ours(args):
     if W != args.gpus:
         raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N>1 with torch.distributed.run" % (args.gpus, W))
     ext.init_distributed(use_gpu=True, backend="nccl")
+    if args.scatter_ctas:
+        _lib.set_tunable(5, args.scatter_ctas)
     rank = max(ext.my_rank, 0)
     dev = torch.device("cuda", torch.cuda.current_device())
     if args.mlp == "tf32":
@@ -436,7 +445,9 @@ def main():
                    "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder), "
                    "data-parallel MLPs (flat-gradient all-reduce), %s" % (
                        W, args.sharder, "exchange fused into the lookup / gradient kernels over NVLink peer memory"
-                       if args.exchange == "peer" else "NCCL all-to-all"),
+                       if args.exchange == "peer" else ("pitched copy-engine copies into NVLink peer memory, %d micro-batches"
+                                                       % args.microbatches if args.exchange == "peer-copy"
+                                                       else "NCCL all-to-all")),
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"
                          % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * 4 / 1e9, args.nbatches),
                    "rows_cap": args.rows_cap or None},

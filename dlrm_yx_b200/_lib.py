@@ -24,9 +24,11 @@ SIGNATURES = {
     "dlrmx_embbag_fwd_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                      c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "dlrmx_embbag_fwd_scatter_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
-                                             c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p]),
+                                             c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_void_p,
+                                             c_void_p]),
     "dlrmx_embbag_fwd_scatter_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
-                                             c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p]),
+                                             c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_void_p,
+                                             c_void_p]),
     "dlrmx_bwd_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "dlrmx_bwd_sort_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p,
                                    c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -63,6 +65,7 @@ SIGNATURES = {
                                  c_int, c_void_p]),
     "dlrmx_a2a_pack_grad": (c_int, [c_void_p, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     c_void_p, c_void_p]),
+    "dlrmx_copy2d_async": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
     "dlrmx_a2a_push_grad": (c_int, [c_void_p, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     ctypes.POINTER(c_void_p), c_void_p]),
 }

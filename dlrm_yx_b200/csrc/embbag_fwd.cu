@@ -54,15 +54,30 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
-                  float* const* __restrict__ out_peers, int lb) {
+                  float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len) {
     constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
     constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
     const unsigned gmask = fwd_group_mask<G>();
-    const int64_t tile = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
-    const int64_t tile_bag0 = tile * TILE;
-    if (tile_bag0 >= total_bags) return;      // whole group leaves together
     const int col0 = gl * VEC;
+    // grid-stride over tiles: ordinary launches have one tile per group; the NVLink-bound scatter mode may be launched
+    // NARROW (a few CTAs per SM on a subset of the SMs) so that tower kernels on the other stream get the rest
+    const int64_t tile_stride = (int64_t)gridDim.x * blockDim.x / G;
+    for (int64_t tile = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; tile * TILE < total_bags;
+         tile += tile_stride) {      // whole groups enter / leave together
+    const int64_t tile_bag0 = tile * TILE;
+    // Micro-batched exchange (scatter mode, mb_len < lb): only samples [mb_off, mb_off + mb_len) of every rank's local
+    // batch are looked up by this launch; the launch walks a DENSE index q over (table, rank, sample-in-window) and maps
+    // it to the real bag id t*B + p*lb + b'.  Otherwise the dense index IS the bag id.
+    const bool windowed = out_peers != nullptr && mb_len < lb;
+    const int64_t per_table = windowed ? (int64_t)(B / lb) * mb_len : (int64_t)B;
+    auto real_bag = [&](int64_t q) -> int64_t {
+        if (!windowed) return q;
+        const int64_t t = q / per_table, rem = q - t * per_table;
+        const int64_t p = rem / mb_len;
+        return t * B + p * lb + mb_off + (rem - p * mb_len);
+    };
+    const int64_t all_bags = windowed ? (total_bags / per_table) * B : total_bags;   // T*B: end of the offsets array
 
     // ---- lane-parallel metadata of the tile: lane i (< TILE) describes bag tile_bag0 + i ---------------
     IdxT my_s = 0, my_ix = -1;
@@ -70,10 +85,11 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     const float* my_base = nullptr;
     int64_t my_rows = 0;
     {
-        const int64_t bag = tile_bag0 + gl;
-        if (gl < TILE && bag < total_bags) {
+        const int64_t q = tile_bag0 + gl;
+        if (gl < TILE && q < total_bags) {
+            const int64_t bag = real_bag(q);
             const IdxT s = offsets[bag];
-            const IdxT e = (bag + 1 < total_bags) ? offsets[bag + 1] : (IdxT)N;
+            const IdxT e = (bag + 1 < all_bags) ? offsets[bag + 1] : (IdxT)N;
             const int t = (int)(bag / B);
             my_base = tables[t];
             my_rows = (table_rows != nullptr) ? table_rows[t] : (int64_t)0x7fffffffffffffffll;
@@ -161,8 +177,9 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
 
 #pragma unroll
         for (int k = 0; k < KB; ++k) {
-            const int64_t bag = tile_bag0 + b0 + k;
-            if (bag < total_bags) {
+            const int64_t q = tile_bag0 + b0 + k;
+            if (q < total_bags) {
+                const int64_t bag = real_bag(q);
                 const int64_t t = bag / B;
                 const int64_t b = bag - t * B;
                 // model-parallel exchange fused into the lookup: sample b belongs to rank b / lb, whose (peer-mapped)
@@ -176,31 +193,37 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
             }
         }
     }
+    }   // tile loop
 }
 
 template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
-                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
-                      cudaStream_t st) {
-    const int64_t total_bags = (int64_t)T * B;
+                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
+                      int mb_len, cudaStream_t st) {
+    const bool windowed = out_peers != nullptr && mb_len < lb;
+    const int64_t total_bags = windowed ? (int64_t)T * (B / lb) * mb_len : (int64_t)T * B;
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
     const int64_t groups = ceil_div(total_bags, TILE);   // one group of G lanes per tile of TILE bags
     const int threads = 256;
-    const int64_t blocks = ceil_div(groups * G, threads);
+    int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
+    const int cap = get_tunable(DLRMX_TUNE_SCATTER_CTAS);       // scatter mode only: narrow launch (0 = full width)
+    if (out_peers != nullptr && cap > 0 && blocks > cap) blocks = cap;
     embbag_fwd_kernel<VEC, G, CH, K, U, FULL, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
         tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers,
-        lb);
+        lb, mb_off, mb_len);
     return check_launch("embbag_fwd");
 }
 
 template <typename IdxT>
 static int embbag_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
-                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
-                      dlrmx_stream_t stream) {
+                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
+                      int mb_len, dlrmx_stream_t stream) {
     DLRMX_REQUIRE(T >= 0 && B >= 0 && N >= 0, "embbag_fwd: negative size");
+    DLRMX_REQUIRE(out_peers == nullptr || (mb_off >= 0 && mb_len > 0 && mb_off + mb_len <= lb),
+                  "embbag_fwd_scatter: window [mb_off, mb_off + mb_len) must lie inside the local batch");
     DLRMX_REQUIRE(out_peers == nullptr || (lb > 0 && B % lb == 0), "embbag_fwd_scatter: B must be a multiple of lb > 0");
     DLRMX_REQUIRE((int64_t)T * B < (1ll << 31), "embbag_fwd: T*B must be < 2^31");
     RowGeom g;
@@ -215,7 +238,8 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     const bool short_bags = N <= 2 * (int64_t)T * B;
     const int tune = get_tunable(DLRMX_TUNE_FWD_K);
 #define DLRMX_FWD_ARGS \
-    tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b, stride_t, err_flag, out_peers, lb, st
+    tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, \
+        mb_len, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                  \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                   \
         if (short_bags) {                                                                              \
@@ -242,31 +266,33 @@ int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows, 
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
     return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b,
-                                      stride_t, err_flag, nullptr, 0, stream);
+                                      stride_t, err_flag, nullptr, 0, 0, 0, stream);
 }
 int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
                          const int64_t* offsets, int64_t N, int T, int B, int D, const float* psw,
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
     return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b,
-                                      stride_t, err_flag, nullptr, 0, stream);
+                                      stride_t, err_flag, nullptr, 0, 0, 0, stream);
 }
 int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
                                  const int32_t* offsets, int64_t N, int T, int B, int D, const float* psw,
-                                 float* const* out_peers, int lb, int64_t stride_b, int64_t stride_t, int* err_flag,
-                                 dlrmx_stream_t stream) {
+                                 float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
+                                 int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
     return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
-                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, stream);
+                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, mb_off,
+                                      mb_len, stream);
 }
 int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
                                  const int64_t* offsets, int64_t N, int T, int B, int D, const float* psw,
-                                 float* const* out_peers, int lb, int64_t stride_b, int64_t stride_t, int* err_flag,
-                                 dlrmx_stream_t stream) {
+                                 float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
+                                 int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
     return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
-                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, stream);
+                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, mb_off,
+                                      mb_len, stream);
 }
 }

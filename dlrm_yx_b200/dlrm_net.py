@@ -151,44 +151,60 @@ class _ExchangeInteractMixed(torch.autograd.Function):
         return dx, send, None, None
 
 
+class _PeerStep(object):
+    """Per-step state shared by the micro-batch branches of the peer-memory exchange."""
+
+    def __init__(self, peer, emb, indices, offsets, presorted, nwin):
+        self.peer, self.emb, self.indices, self.offsets = peer, emb, indices, offsets
+        self.presorted, self.pending, self.first_push = presorted, nwin, True
+
+
 class _PeerInteract(torch.autograd.Function):
     """Multi-process, exchange fused into the kernels over NVLink peer memory (ext_dist.PeerExchange): the pooled rows
-    were stored into this rank's interaction input by the peers' lookup kernels; backward pushes the gradient slices
-    into the table owners' buffers and runs the fused sort + update of the local tables.  out_cols > 0 selects the
-    bf16-facing interaction kernels (x, R, dR, dx in bf16)."""
+    of window [off, off+ln) of the local batch were stored into this rank's interaction input by the peers' lookup
+    kernels; backward pushes the window's gradient slices into the table owners' buffers and, once every window has
+    been pushed, runs the fused update of the local tables.  out_cols > 0 selects the bf16-facing interaction kernels
+    (x, R, dR, dx in bf16)."""
 
     @staticmethod
-    def forward(ctx, x, emb, indices, offsets, peer, itself, out_cols, presorted):
-        feat = peer.feat
-        ctx.emb, ctx.peer, ctx.itself, ctx.mixed = emb, peer, bool(itself), out_cols > 0
-        ctx.presorted = presorted
+    def forward(ctx, x, step, off, ln, itself, out_cols):
+        feat = step.peer.feat[off:off + ln]
+        ctx.step, ctx.off, ctx.itself, ctx.mixed = step, off, bool(itself), out_cols > 0
         if ctx.mixed:
             x = x.contiguous()
-            ctx.save_for_backward(feat, x, indices, offsets)
+            ctx.save_for_backward(feat, x)
             return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
         feat[:, 0, :].copy_(x)
-        ctx.save_for_backward(feat, x, indices, offsets)
+        ctx.save_for_backward(feat, x)
         return ops.interact_dot_fwd(feat, ctx.itself)
 
     @staticmethod
     def backward(ctx, dR):
-        feat, x, indices, offsets = ctx.saved_tensors
-        peer = ctx.peer
+        feat, x = ctx.saved_tensors
+        step = ctx.step
+        peer = step.peer
         if ctx.mixed:
             dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
         T_r = peer.grad.shape[1]
+        first, off = step.first_push, ctx.off
+        step.first_push = False
+        step.pending -= 1
+        last = step.pending == 0
 
-        def exchange():                       # on the side stream: barrier, push over NVLink, barrier
-            peer.push_grad(dfeat)
+        def exchange():                       # on the side stream: (barrier,) push over NVLink (, barrier)
+            peer.push_grad(dfeat, mb_off=off, first=first)
+            if not last:
+                return None
             grad = peer.grad_ready()
             return grad if T_r > 0 else None
-        _update_on_side(ctx.emb, dfeat, indices, offsets, peer.W * peer.lb, T_r * peer.D, peer.D, ctx.presorted,
-                        before=exchange, keep=(dfeat,))
-        ctx.presorted = None
-        return dx, None, None, None, None, None, None, None
+        _update_on_side(step.emb, dfeat, step.indices, step.offsets, peer.W * peer.lb, T_r * peer.D, peer.D,
+                        step.presorted if last else None, before=exchange, keep=(dfeat,))
+        if last:
+            step.presorted = None
+        return dx, None, None, None, None, None
 
 
 class _ExchangeInteract(torch.autograd.Function):
@@ -411,35 +427,56 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
-    def enable_peer_exchange(self, local_batch):
+    def enable_peer_exchange(self, local_batch, microbatches=1, engine="sm"):
         """Replaces the NCCL all-to-all of distributed_forward by kernels that store straight into the peers'
         memory over NVLink (ext_dist.PeerExchange).  Needs fuse_sparse_arch + batched_emb and a fixed local batch."""
         if not (self.fuse_sparse_arch and self.batched_emb):
             raise _lib.DlrmxError("enable_peer_exchange needs batched_emb=True and fuse_sparse_arch=True")
         dev = next(self.parameters()).device
-        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, int(self.ln_bot[-1]), dev)
+        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, int(self.ln_bot[-1]), dev, engine=engine)
+        self.set_microbatches(microbatches)
+        return self
+
+    def set_microbatches(self, m):
+        """Micro-batched exchange (peer exchange + FusedMLP towers only): the local batch is cut into m windows; the
+        NVLink transfer of window k+1 (forward) / k-1 (backward) runs beside interaction + top tower of window k."""
+        m = max(1, int(m))
+        if m > 1 and not hasattr(self.top_l, "accumulate"):
+            raise _lib.DlrmxError("micro-batched exchange needs the fused towers (call fuse_mlps first)")
+        self._microbatches = m
+        if hasattr(self.top_l, "accumulate"):
+            self.top_l.accumulate = m > 1
         return self
 
     def _peer_forward(self, dense_x, lS_o, lS_i):
         peer = self._peer
         emb = self._batched_module()
+        M = max(1, int(getattr(self, "_microbatches", 1)))
+        lb = peer.lb
+        cuts = [lb * m // M for m in range(M + 1)]
+        windows = [(cuts[m], cuts[m + 1] - cuts[m]) for m in range(M)]
         main = torch.cuda.current_stream()
         side = _side_stream(dense_x.device)
         side.wait_stream(main)
         with record_function("module::forward_pass::embedding_lookup"):
-            with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sort) beside the bottom MLP
-                peer.lookup_and_scatter(emb.table_set(), lS_i, lS_o)
-                arrived = side.record_event()
-                presorted = (emb.sort_lookups(lS_i, lS_o, peer.W * peer.lb)
+            with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sort) beside the towers
+                arrived = peer.lookup_and_scatter(emb.table_set(), lS_i, lS_o, windows if M > 1 else None)
+                presorted = (emb.sort_lookups(lS_i, lS_o, peer.W * lb)
                              if torch.is_grad_enabled() and emb.T > 0 else None)
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
-        with record_function("module::forward_pass::interaction"):
-            main.wait_event(arrived)
-            cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
-            z = _PeerInteract.apply(x, emb, lS_i, lS_o, peer, self.arch_interaction_itself, cols, presorted)
-        with record_function("module::forward_pass::top_mlp"):
-            p = self.apply_mlp(z, self.top_l)
+        step = _PeerStep(peer, emb, lS_i, lS_o, presorted, M)
+        cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
+        outs = []
+        for m, (off, ln) in enumerate(windows):
+            # window m of the interaction input is complete; window m+1 is still on the wire while m is contracted
+            with record_function("module::forward_pass::interaction"):
+                main.wait_event(arrived[m])
+                z = _PeerInteract.apply(x if M == 1 else x[off:off + ln], step, off, ln, self.arch_interaction_itself,
+                                        cols)
+            with record_function("module::forward_pass::top_mlp"):
+                outs.append(self.apply_mlp(z, self.top_l))
+        p = outs[0] if M == 1 else torch.cat(outs, dim=0)
         return self._clamp(p)
 
     def distributed_forward(self, dense_x, lS_o, lS_i):

@@ -230,8 +230,11 @@ class PeerExchange(object):
 
     tables_per_rank[p] = tables held by rank p (rank-major global table order, as the reference's cat produces)."""
 
-    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None):
+    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, engine="sm"):
+        """engine: "sm" = remote stores issued by the lookup / push kernels; "copy" = pitched copies on the copy engines
+        (the lookup writes a local block first; the SMs stay free, so micro-batched transfers overlap the towers)."""
         import torch.distributed._symmetric_memory as symm_mem
+        self.engine = engine
         self.group = dist.group.WORLD if group is None else group
         self.W, self.rank = my_size, my_rank
         self.tpr = [int(t) for t in tables_per_rank]
@@ -251,6 +254,7 @@ class PeerExchange(object):
         # forward: where MY tables' rows go inside peer p's interaction input (feature slot 1 + first[rank])
         fptr = [int(q) + (1 + self.first[self.rank]) * self.D * 4 for q in self.h_feat.buffer_ptrs]
         self.out_peers = torch.tensor(fptr, dtype=torch.int64, device=device)
+        self.out_peers_host = fptr
         # backward: where MY local batch's chunk starts inside owner p's gradient buffer [W*lb, T_p, D]
         self.push_bases = [int(q) + self.rank * self.lb * self.tpr[p] * self.D * 4
                            for p, q in enumerate(self.h_grad.buffer_ptrs)]
@@ -259,19 +263,55 @@ class PeerExchange(object):
     def barrier(self, which):
         (self.h_feat if which == 0 else self.h_grad).barrier()
 
-    def lookup_and_scatter(self, table_set, indices, offsets):
+    def lookup_and_scatter(self, table_set, indices, offsets, windows=None):
         """All local tables x the global batch; every pooled row lands in its sample owner's `feat`.  On return
-        (stream-ordered) every peer's rows have landed in MY `feat` as well."""
+        (stream-ordered) every peer's rows have landed in MY `feat` as well.
+        windows: list of (mb_off, mb_len) micro-batch windows of the local batch -- one launch + one barrier each, and
+        the list of events after which window m of `feat` is complete is returned (micro-batched exchange: consumers of
+        window m start while window m+1 is still on the wire)."""
+        T_r, D, F, lb = self.tpr[self.rank], self.D, 1 + self.T, self.lb
+        pooled = None
+        if self.engine == "copy" and T_r > 0:   # local lookup of everything first (HBM-bound, ~0.1 ms)
+            pooled = ops.embbag_forward(table_set, indices, offsets, self.W * lb, validate=False)
+            self._pooled = pooled               # stays alive until the next step's lookup
         self.h_feat.barrier()                  # peers are done reading the previous contents of their feat
-        if self.tpr[self.rank] > 0:
-            ops.embbag_forward_scatter(table_set, indices, offsets, self.W * self.lb, self.out_peers, self.lb,
-                                       self.stride_b, self.stride_t)
-        self.h_feat.barrier()                  # every peer's rows have landed in my feat
+        events = []
+        for off, ln in (windows or [(0, lb)]):
+            if T_r > 0 and self.engine == "copy":
+                f0 = 1 + self.first[self.rank]
+                for p in range(self.W):        # pooled[p*lb + off : +ln] ([ln, T_r*D] contiguous) -> peer p's feat
+                    if p == self.rank:         # own share: an SM copy at HBM speed (pitched local CE copies are slow)
+                        self.feat[off:off + ln, f0:f0 + T_r, :].copy_(pooled[p * lb + off:p * lb + off + ln])
+                    else:
+                        ops.copy2d_async(self.out_peers_host[p] + off * F * D * 4, F * D * 4,
+                                         pooled[p * lb + off].data_ptr(), T_r * D * 4, T_r * D * 4, ln)
+            elif T_r > 0:
+                ops.embbag_forward_scatter(table_set, indices, offsets, self.W * lb, self.out_peers, lb,
+                                           self.stride_b, self.stride_t, mb_off=off, mb_len=ln)
+            self.h_feat.barrier()              # every peer's rows of this window have landed in my feat
+            events.append(torch.cuda.current_stream().record_event())
+        return events
 
-    def push_grad(self, dfeat):
-        """dfeat [lb, 1+T, D]: features 1.. go to the table owners' `grad` buffers."""
-        self.h_grad.barrier()                  # owners are done with the previous step's gradients
-        ops.a2a_push_grad(dfeat, 1, self.tpr, self.lb, self.D, self.push_bases)
+    def push_grad(self, dfeat, mb_off=0, first=True):
+        """dfeat [mb_len, 1+T, D] (window starting at local sample mb_off): features 1.. go to the table owners'
+        `grad` buffers."""
+        if first:
+            self.h_grad.barrier()              # owners are done with the previous step's gradients
+        bases = [b + mb_off * self.tpr[p] * self.D * 4 for p, b in enumerate(self.push_bases)]
+        if self.engine == "copy":
+            ln, F, D = dfeat.shape
+            for p in range(self.W):            # dfeat[:, 1+first_p : +T_p, :] (row pitch F*D) -> owner p's buffer
+                if self.tpr[p] == 0:
+                    continue
+                f0 = 1 + self.first[p]
+                if p == self.rank:
+                    r0 = self.rank * self.lb + mb_off
+                    self.grad[r0:r0 + ln].copy_(dfeat[:, f0:f0 + self.tpr[p], :])
+                else:
+                    ops.copy2d_async(bases[p], self.tpr[p] * D * 4, dfeat[0, f0].data_ptr(), F * D * 4,
+                                     self.tpr[p] * D * 4, ln)
+            return
+        ops.a2a_push_grad(dfeat, 1, self.tpr, dfeat.shape[0], self.D, bases)
 
     def grad_ready(self):
         self.h_grad.barrier()

@@ -57,8 +57,16 @@ class _LinearAct(torch.autograd.Function):
         L = ctx.mlp.layers[ctx.li]
         dyb = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         dyb = dyb.contiguous()
-        dz, _ = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"), db=L.gb)
-        L.gW.copy_(torch.mm(dz.t(), hb, out_dtype=torch.float32))
+        acc = ctx.mlp.accumulate       # several forward/backward passes per step (micro-batches): add, don't overwrite
+        gb = torch.empty_like(L.gb) if acc else L.gb
+        dz, _ = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"), db=gb)
+        if acc:
+            L.gb.add_(gb)
+        gW = torch.mm(dz.t(), hb, out_dtype=torch.float32)
+        if acc:
+            L.gW.add_(gW)
+        else:
+            L.gW.copy_(gW)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.mm(dz, L.w_shadow)
@@ -83,7 +91,13 @@ class _Head(torch.autograd.Function):
     def backward(ctx, dp):
         h, p = ctx.saved_tensors
         L = ctx.mlp.layers[ctx.li]
-        dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), L.gW.view(-1), L.gb, sigmoid=(L.act == "sigmoid"))
+        if ctx.mlp.accumulate:
+            gW, gb = torch.empty_like(L.gW), torch.empty_like(L.gb)
+            dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), gW.view(-1), gb, sigmoid=(L.act == "sigmoid"))
+            L.gW.add_(gW)
+            L.gb.add_(gb)
+        else:
+            dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), L.gW.view(-1), L.gb, sigmoid=(L.act == "sigmoid"))
         return dh, None, None, None
 
 
@@ -123,6 +137,7 @@ class FusedMLP(nn.Module):
         self.register_buffer("shadow", master.to(torch.bfloat16), persistent=False)
         self._anchor = torch.zeros(1, device=dev, requires_grad=True)  # makes every layer's backward run
         self.out_bf16 = False       # True: hand the last fused layer's bf16 output on as it is (no fp32 copy)
+        self.accumulate = False     # True: the tower runs several times per step; gradients add up until step()
         self._bind()
 
     def _bind(self):

@@ -128,9 +128,12 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
     return out
 
 
-def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b, stride_t, validate=False):
+def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b, stride_t, validate=False,
+                           mb_off=0, mb_len=None):
     """embbag_forward with the exchange fused in: bag (t, b) of the global batch is stored at
-    out_peers[b // lb] + (b % lb)*stride_b + t*stride_t (out_peers: device int64 tensor of peer-mapped pointers)."""
+    out_peers[b // lb] + (b % lb)*stride_b + t*stride_t (out_peers: device int64 tensor of peer-mapped pointers).
+    mb_off / mb_len: only samples [mb_off, mb_off + mb_len) of every rank's local batch (micro-batched exchange)."""
+    mb_len = lb if mb_len is None else mb_len
     tables.refresh()
     _need_cuda(indices, offsets, out_peers)
     indices = indices.contiguous()
@@ -143,8 +146,8 @@ def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b,
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_scatter_" + _idx_suffix(indices, offsets))
     with _timed("embbag_fwd"):
         rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0, indices.data_ptr(),
-                offsets.data_ptr(), indices.numel(), T, B, D, 0, out_peers.data_ptr(), lb, stride_b, stride_t, 0,
-                _stream())
+                offsets.data_ptr(), indices.numel(), T, B, D, 0, out_peers.data_ptr(), lb, mb_off, mb_len, stride_b,
+                stride_t, 0, _stream())
         _lib.check(rc, "dlrmx_embbag_fwd_scatter")
 
 
@@ -297,6 +300,13 @@ def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases):
         rc = _lib.load().dlrmx_a2a_push_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
                                              _int_array(tables_per_rank), lb, D, bases, _stream())
         _lib.check(rc, "dlrmx_a2a_push_grad")
+
+
+def copy2d_async(dst_ptr, dst_pitch, src_ptr, src_pitch, width, height):
+    """Pitched copy on the copy engines (byte units), stream-ordered on the current stream; pointers may be peer-mapped."""
+    rc = _lib.load().dlrmx_copy2d_async(int(dst_ptr), int(dst_pitch), int(src_ptr), int(src_pitch), int(width),
+                                        int(height), _stream())
+    _lib.check(rc, "dlrmx_copy2d_async")
 
 
 def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):

@@ -230,7 +230,8 @@ int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
  * embbag_fwd_scatter: dlrmx_embbag_fwd, but the pooled row of bag (t, b) of the GLOBAL batch is stored
  *   at  out_peers[b / lb] + (b % lb)*stride_b + t*stride_t : out_peers is a DEVICE array [B / lb] of
  *   peer-mapped pointers, each already offset to this rank's first feature slot in that peer's
- *   [lb, 1+T, D] interaction input.
+ *   [lb, 1+T, D] interaction input.  [mb_off, mb_off + mb_len) selects a window of every rank's local batch
+ *   (micro-batched exchange: the launch covers only those samples; mb_off = 0, mb_len = lb: everything).
  * a2a_push_grad: dfeat [lb, F, D] (this rank's local batch, all tables) -> for every owner rank p the
  *   chunk [lb, T_p, D] stored at host_peer_chunk_bases[p] (HOST array [W] of peer-mapped device
  *   pointers = rank p's gradient buffer [W*lb, T_p, D] + my_rank*lb*T_p*D).
@@ -238,14 +239,22 @@ int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
 int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows,
                                  const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
                                  int D, const float* per_sample_weights, float* const* out_peers, int lb,
-                                 int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
+                                 int mb_off, int mb_len, int64_t stride_b, int64_t stride_t, int* err_flag,
+                                 dlrmx_stream_t stream);
 int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows,
                                  const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
                                  int D, const float* per_sample_weights, float* const* out_peers, int lb,
-                                 int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
+                                 int mb_off, int mb_len, int64_t stride_b, int64_t stride_t, int* err_flag,
+                                 dlrmx_stream_t stream);
 int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D,
                         float* const* host_peer_chunk_bases, dlrmx_stream_t stream);
+/* The same exchange on the COPY ENGINES (no SM is occupied, so the transfer truly overlaps tower kernels on another
+ * stream): one pitched device-to-peer copy per (window, peer) -- forward: rank r's pooled block [ln, T_r*D] -> peer's
+ * interaction input (row pitch F*D); backward: the gradient slice [ln, T_p*D] (row pitch F*D) -> owner's buffer.
+ * Thin stream-ordered wrapper over cudaMemcpy2DAsync(cudaMemcpyDefault); pointers may be peer-mapped. */
+int dlrmx_copy2d_async(void* dst, size_t dst_pitch_bytes, const void* src, size_t src_pitch_bytes,
+                       size_t width_bytes, size_t height, dlrmx_stream_t stream);
 
 #ifdef __cplusplus
 }

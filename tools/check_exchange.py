@@ -9,7 +9,7 @@ towers), peer-memory exchange with the bf16 towers -- trains two steps on its sl
     rank-averaged loss and the first update of the local tables against the golden vectors of the unmodified
     single-process reference on the same global batch (first loss rtol 1e-5; with row-wise Adagrad also the
     first table update, 1e-4 -- see the comment at the check);
-  * the bf16-tower variant tracks it (loss 1e-2).
+  * the bf16-tower variant tracks it (loss 1e-2), and its micro-batched form (2 windows) tracks the one-shot form.
 Prints 'rank r: exchange parity OK' and exits 0, or raises."""
 import os
 import sys
@@ -38,7 +38,7 @@ def main():
     sgd = str(g["meta_opt"]) == "sgd"
     kind = embedding.Optimizer.SGD if sgd else embedding.Optimizer.EXACT_ROWWISE_ADAGRAD
 
-    def build(exchange, bf16):
+    def build(exchange, bf16, micro=1):
         np.random.seed(int(g["meta_misc"][4]))
         m = dlrm_net.DLRM_Net(D, g["meta_ln_emb"], g["meta_ln_bot"], g["meta_ln_top"], arch_interaction_op="dot",
                               sigmoid_bot=-1, sigmoid_top=len(g["meta_ln_top"]) - 2, batched_emb=True,
@@ -53,11 +53,13 @@ def main():
                 for j, l in enumerate(lins):
                     l.weight.copy_(torch.from_numpy(g["%s_W_%d" % (pre, j)]))
                     l.bias.copy_(torch.from_numpy(g["%s_b_%d" % (pre, j)]))
-        if exchange == "peer":
-            m.enable_peer_exchange(lb)
+        if exchange.startswith("peer"):
+            m.enable_peer_exchange(lb, engine="copy" if exchange == "peer-copy" else "sm")
         opt = None
         if bf16:
             m.fuse_mlps(lr, "sgd" if sgd else "adagrad")
+            if micro > 1:
+                m.set_microbatches(micro)
         else:
             dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
             m.bot_l = ext.DDP(m.bot_l, device_ids=[dev.index])
@@ -90,10 +92,12 @@ def main():
 
     ln, tn, local = run(*build("nccl", False))
     lp, tp, _ = run(*build("peer", False))
-    assert ln == lp, (ln, lp)
+    lc, tc, _ = run(*build("peer-copy", False))
+    assert ln == lp == lc, (ln, lp, lc)
     for step in range(2):
-        for a, b in zip(tn[step], tp[step]):
+        for a, b, c in zip(tn[step], tp[step], tc[step]):
             assert torch.equal(a, b), "peer exchange differs from NCCL exchange"
+            assert torch.equal(a, c), "copy-engine exchange differs from NCCL exchange"
     np.testing.assert_allclose(ln[0], float(g["loss"]), rtol=1e-5)
     if not sgd:
         # Row-wise Adagrad normalises the step by the gradient's own scale, so the W-times larger embedding gradients of
@@ -106,6 +110,11 @@ def main():
     lb16, _, _ = run(*build("peer", True))
     np.testing.assert_allclose(lb16[0], float(g["loss"]), rtol=1e-2)
     np.testing.assert_allclose(lb16[1], ln[1], rtol=2e-2)
+    # micro-batched exchange (2 windows of the local batch, transfers overlapping the towers) against the one-shot one:
+    # same arithmetic per sample, only the GEMM batch split and the gradient accumulation order differ
+    lm2, tm2, _ = run(*build("peer-copy", True, micro=2))
+    np.testing.assert_allclose(lm2[0], lb16[0], rtol=2e-3)
+    np.testing.assert_allclose(lm2[1], lb16[1], rtol=5e-3)
     dist.barrier()
     print("rank %d: exchange parity OK (%s, %d ranks, local tables %s)" % (rank, name, W, local), flush=True)
     dist.destroy_process_group()
