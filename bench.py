@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--microbatches", type=int, default=1,
                     help="N>1, peer exchange: windows of the local batch whose NVLink transfer overlaps the towers")
     ap.add_argument("--scatter-ctas", type=int, default=0,
-                    help="N>1, peer exchange: cap on the CTAs of the NVLink scatter / push kernels (0 = full width)")
+                    help="N>1, peer exchange: cap on the CTAs of the NVLink push kernel (0 = full width)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "peer-copy", "nccl"],
                     help="N>1: 'peer' = exchange fused into the kernels over NVLink peer memory; 'nccl' = all_to_all_single")
     ap.add_argument("--optimizer", default="rwsadagrad", choices=["rwsadagrad", "sgd"])

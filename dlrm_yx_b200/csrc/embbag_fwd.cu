@@ -48,7 +48,7 @@ __device__ __forceinline__ int32_t shfl_idx(unsigned mask, int32_t v, int src, i
 // one-index-per-bag Criteo layout), otherwise a tile is one batch of K bags (long bags: more groups, and the
 // memory-level parallelism comes from unrolling ALONG the bag -- loads are issued U at a time, the adds still
 // happen one by one in index order).
-template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
+template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT>
 __global__ void __launch_bounds__(256, (K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2))
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
@@ -59,20 +59,18 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
     const unsigned gmask = fwd_group_mask<G>();
-    const int col0 = gl * VEC;
-    // grid-stride over tiles: ordinary launches have one tile per group; the NVLink-bound scatter mode may be launched
-    // NARROW (a few CTAs per SM on a subset of the SMs) so that tower kernels on the other stream get the rest
-    const int64_t tile_stride = (int64_t)gridDim.x * blockDim.x / G;
-    for (int64_t tile = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; tile * TILE < total_bags;
-         tile += tile_stride) {      // whole groups enter / leave together
+    const int64_t tile = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
     const int64_t tile_bag0 = tile * TILE;
+    if (tile_bag0 >= total_bags) return;      // whole group leaves together
+    const int col0 = gl * VEC;
     // Micro-batched exchange (scatter mode, mb_len < lb): only samples [mb_off, mb_off + mb_len) of every rank's local
     // batch are looked up by this launch; the launch walks a DENSE index q over (table, rank, sample-in-window) and maps
     // it to the real bag id t*B + p*lb + b'.  Otherwise the dense index IS the bag id.
-    const bool windowed = out_peers != nullptr && mb_len < lb;
+    // SCATTER is a template flag so that the ordinary lookup carries none of this (it runs at 64 registers).
+    const bool windowed = SCATTER && mb_len < lb;
     const int64_t per_table = windowed ? (int64_t)(B / lb) * mb_len : (int64_t)B;
     auto real_bag = [&](int64_t q) -> int64_t {
-        if (!windowed) return q;
+        if (!SCATTER || !windowed) return q;
         const int64_t t = q / per_table, rem = q - t * per_table;
         const int64_t p = rem / mb_len;
         return t * B + p * lb + mb_off + (rem - p * mb_len);
@@ -184,16 +182,14 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                 const int64_t b = bag - t * B;
                 // model-parallel exchange fused into the lookup: sample b belongs to rank b / lb, whose (peer-mapped)
                 // interaction input receives the pooled row directly over NVLink -- 512-byte row stores
-                float* o = (out_peers == nullptr)
-                               ? out + b * stride_b + t * stride_t + col0
-                               : out_peers[b / lb] + (b % lb) * stride_b + t * stride_t + col0;
+                float* o = SCATTER ? out_peers[b / lb] + (b % lb) * stride_b + t * stride_t + col0
+                                   : out + b * stride_b + t * stride_t + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
                     if (col0 + c * G * VEC < D) acc[k][c].store(o + c * G * VEC);
             }
         }
     }
-    }   // tile loop
 }
 
 template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
@@ -206,13 +202,16 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
     const int64_t groups = ceil_div(total_bags, TILE);   // one group of G lanes per tile of TILE bags
     const int threads = 256;
-    int64_t blocks = ceil_div(groups * G, threads);
+    const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
-    const int cap = get_tunable(DLRMX_TUNE_SCATTER_CTAS);       // scatter mode only: narrow launch (0 = full width)
-    if (out_peers != nullptr && cap > 0 && blocks > cap) blocks = cap;
-    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
-        tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers,
-        lb, mb_off, mb_len);
+    if (out_peers != nullptr)
+        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, true, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
+            tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
+            out_peers, lb, mb_off, mb_len);
+    else
+        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, false, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
+            tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
+            nullptr, 1, 0, 1);
     return check_launch("embbag_fwd");
 }
 
@@ -246,7 +245,11 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
             if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 8, 1, true, IdxT>(DLRMX_FWD_ARGS); \
             return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);       \
         }                                                                                              \
-        if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS); \
+        /* long bags, measured on B200 at 100 rows per bag: rows <= 256 B (G <= 16) want 8 rows of each bag in flight */ \
+        /* (0.60 of peak at the C3 shape, 0.72 with 8x the bags; 4 rows: 0.40), 512-B rows want 4 (0.70; 8 rows: 0.42). */ \
+        /* A two-round register double buffer was tried and was slower than either (spills at 2 CTAs per SM).          */ \
+        if (CH_ == 1 && (tune == 8 || (tune == 0 && G_ <= 16)))                                        \
+            return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS);                       \
         return launch_fwd<VEC_, G_, CH_, 2, (CH_ == 1 ? 4 : 2), false, IdxT>(DLRMX_FWD_ARGS);          \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)

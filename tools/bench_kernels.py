@@ -109,7 +109,7 @@ def main():
             d.update(extra)
         print(json.dumps(d), flush=True)
 
-    for k in (8, 4):
+    for k in (8, 4, 0):
         _lib.set_tunable(_lib.TUNE_FWD_K, k)
 
         def f():
