@@ -172,8 +172,21 @@ def build_model(args, cfg, W):
                           sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True, sharder=args.sharder,
                           emb_optimizer=kind, emb_learning_rate=lr, emb_init="device").cuda()
     if W > 1 and args.exchange.startswith("peer"):
-        m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W,
-                               engine="copy" if args.exchange == "peer-copy" else "sm")
+        # symmetric (peer-mapped) memory needs CUDA VMM + P2P on the box; every rank must take the same branch, so the
+        # outcome is agreed on with an all-reduce and the NCCL exchange is the common fallback (same results, slower)
+        ok = 1
+        try:
+            m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W,
+                                   engine="copy" if args.exchange == "peer-copy" else "sm")
+        except Exception as ex:                                  # noqa: BLE001
+            sys.stderr.write("bench: peer exchange unavailable on this rank (%r)\n" % (ex,))
+            ok = 0
+        flag = torch.tensor([ok], device="cuda")
+        torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            m._peer = None
+            args.exchange = "nccl"
+            sys.stderr.write("bench: falling back to the NCCL all-to-all exchange\n")
     if args.mlp == "fused-bf16":
         m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd")
         if W > 1 and args.exchange.startswith("peer"):

@@ -75,6 +75,9 @@ OPT_RWSADAGRAD = 1
 TUNE_FWD_K = 0
 TUNE_BWD_K = 1
 TUNE_IX_CUDACORE = 2   # 1: force the CUDA-core interaction kernels (default: 3xTF32 tensor-core kernels)
+TUNE_BWD_SEG = 3       # sorted positions per group of the fused update (32/64/128/256; 0: chosen per optimizer)
+TUNE_IX_WARP = 4       # 1: one-warp-per-sample bf16-facing interaction kernels (experiment, measured slower)
+TUNE_PUSH_CTAS = 5     # cap on the CTAs of the NVLink gradient-push kernel (0: full width)
 
 _lib = None
 

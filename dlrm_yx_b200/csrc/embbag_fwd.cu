@@ -228,7 +228,7 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     RowGeom g;
     DLRMX_REQUIRE(row_geometry(D, &g), "embbag_fwd: unsupported D=%d (need D<=512 if D%%4==0, else D<=128)", D);
     if (g.vec == 4)
-        DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && ((uintptr_t)out & 15) == 0,
+        DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && (out_peers != nullptr || ((uintptr_t)out & 15) == 0),
                       "embbag_fwd: out must be 16-B aligned with strides multiple of 4 when D%%4==0");
     if ((int64_t)T * B == 0) return DLRMX_OK;
     cudaStream_t st = (cudaStream_t)stream;
@@ -285,7 +285,7 @@ int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* tabl
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
     return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
-                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, mb_off,
+                                      nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
                                       mb_len, stream);
 }
 int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
@@ -295,7 +295,7 @@ int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* tabl
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
     return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
-                                      reinterpret_cast<float*>(16), stride_b, stride_t, err_flag, out_peers, lb, mb_off,
+                                      nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
                                       mb_len, stream);
 }
 }
