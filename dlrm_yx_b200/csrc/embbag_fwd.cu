@@ -54,7 +54,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
-                  float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len) {
+                  float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len, int pf_dist) {
     constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
     constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
@@ -125,7 +125,36 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
 #pragma unroll
             for (int c = 0; c < CH; ++c) acc[k][c].zero();
 
+        // Long bags: rows are pulled toward L2 `pf_dist` positions ahead of the walk, LANE-PARALLEL -- the G/KB lanes that
+        // serve bag k each read one index of the window and issue one bulk prefetch (cp.async.bulk.prefetch.L2, a whole
+        // row per instruction, no registers held), so the walk's own loads (U per bag in flight, consumed in index order)
+        // find their rows in L2 instead of paying DRAM latency once per round.
+        constexpr int LPB = G / KB;                   // lanes per bag
+        const int pk = gl / LPB, pj = gl - pk * LPB;  // my bag of the batch, my slot in its window
+        IdxT pstart = 0;
+        int plen = 0;
+        const float* pbase = nullptr;
+        int64_t prows = 0;
+        const bool do_pf = !FULL && VEC == 4 && LPB >= 1 && pf_dist > 0;
+        if (do_pf) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k)
+                if (k == pk) { pstart = start[k]; plen = len[k]; pbase = base[k]; prows = nrows[k]; }
+            for (int pos = U + pj; pos < min(plen, pf_dist); pos += LPB) {
+                const int64_t ixp = (int64_t)indices[pstart + pos];
+                if (ixp >= 0 && ixp < prows)
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pbase + ixp * D), "r"(D * 4) : "memory");
+            }
+        }
+
         for (int r = 0; r < maxlen; r += U) {
+            if (do_pf) {
+                for (int pos = r + pf_dist + pj; pos < min(plen, r + pf_dist + U); pos += LPB) {
+                    const int64_t ixp = (int64_t)indices[pstart + pos];
+                    if (ixp >= 0 && ixp < prows)
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pbase + ixp * D), "r"(D * 4) : "memory");
+                }
+            }
             RowVec<VEC> row[KB][U][CH];
             bool live[KB][U];
 #pragma unroll
@@ -192,11 +221,16 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     }
 }
 
+constexpr int kDefaultFwdPrefetch = 2;   // rounds of U rows the L2 prefetch runs ahead of the long-bag walk
+
 template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
                       int mb_len, cudaStream_t st) {
+    // tunable 8: prefetch distance of the long-bag walk in units of U rows (0: default, -1: off)
+    const int pft = get_tunable(DLRMX_TUNE_FWD_PREFETCH);
+    const int pf_dist = FULL ? 0 : (pft < 0 ? 0 : (pft == 0 ? kDefaultFwdPrefetch : pft) * U);
     const bool windowed = out_peers != nullptr && mb_len < lb;
     const int64_t total_bags = windowed ? (int64_t)T * (B / lb) * mb_len : (int64_t)T * B;
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
@@ -207,11 +241,11 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     if (out_peers != nullptr)
         embbag_fwd_kernel<VEC, G, CH, K, U, FULL, true, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
             tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
-            out_peers, lb, mb_off, mb_len);
+            out_peers, lb, mb_off, mb_len, pf_dist);
     else
         embbag_fwd_kernel<VEC, G, CH, K, U, FULL, false, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
             tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
-            nullptr, 1, 0, 1);
+            nullptr, 1, 0, 1, pf_dist);
     return check_launch("embbag_fwd");
 }
 
@@ -248,6 +282,7 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
         /* long bags, measured on B200 at 100 rows per bag: rows <= 256 B (G <= 16) want 8 rows of each bag in flight */ \
         /* (0.60 of peak at the C3 shape, 0.72 with 8x the bags; 4 rows: 0.40), 512-B rows want 4 (0.70; 8 rows: 0.42). */ \
         /* A two-round register double buffer was tried and was slower than either (spills at 2 CTAs per SM).          */ \
+        if (CH_ == 1 && tune == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT>(DLRMX_FWD_ARGS);  \
         if (CH_ == 1 && (tune == 8 || (tune == 0 && G_ <= 16)))                                        \
             return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS);                       \
         return launch_fwd<VEC_, G_, CH_, 2, (CH_ == 1 ? 4 : 2), false, IdxT>(DLRMX_FWD_ARGS);          \

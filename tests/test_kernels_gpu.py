@@ -104,6 +104,24 @@ def test_forward_long_bags_and_weights():
     assert np.array_equal(outw.cpu().numpy(), np.stack(refw, axis=1))
 
 
+@pytest.mark.parametrize("D", [128, 64, 32, 16])
+@pytest.mark.parametrize("K,pf", [(0, -1), (0, 0), (0, 4), (1, 2), (8, 1), (4, 3)])
+def test_forward_long_bag_variants_bit_exact(D, K, pf, request):
+    """Long-bag walk: every (bags in lockstep, rows in flight, L2 prefetch distance) variant is bit-exact with the
+    sequential oracle -- the prefetch is a hint, the adds stay in index order.  Ragged lengths 0..120."""
+    from dlrm_yx_b200 import ops, _lib
+    dev = cuda()
+    rng = np.random.default_rng(17 + D)
+    rows, B = [3000, 70000, 5], 67
+    Ws, idx, off = make_case(rng, rows, D, B, max_len=120, empty_frac=0.05)
+    ts, di, do = to_dev(Ws, idx, off, dev, torch.int32)
+    _lib.set_tunable(_lib.TUNE_FWD_K, K)
+    _lib.set_tunable(8, pf)
+    request.addfinalizer(lambda: (_lib.set_tunable(_lib.TUNE_FWD_K, 0), _lib.set_tunable(8, 0)))
+    out = ops.embbag_forward(ts, di, do, B)
+    assert np.array_equal(out.cpu().numpy(), O.embbag_fwd_batched(Ws, idx, off, B))
+
+
 def test_forward_flags_out_of_range_index():
     from dlrm_yx_b200 import ops
     dev = cuda()
@@ -204,6 +222,65 @@ def test_fused_backward_update(D, opt):
     gs = ops.bwd_coalesce(dg, T * D, D, B, D, sbag, run_off, nu)
     U = int(nu.item())
     np.testing.assert_allclose(gs.cpu().numpy()[:U], g, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("D", [128, 64, 8])
+@pytest.mark.parametrize("opt", ["sgd", "rwsadagrad"])
+def test_fused_backward_variants_bit_identical(D, opt, request):
+    """The look-back fix-up fused into bwd_update_kernel (default), the L2 prefetch modes and the pipelined metadata
+    must not change a single bit against the plain kernel + separate bwd_fixup_kernel launch: same additions in the
+    same order.  One-row and 7-row tables give runs that span dozens of CTAs (long look-back chains)."""
+    from dlrm_yx_b200 import ops, _lib
+    dev = cuda()
+    rng = np.random.default_rng(5 + D)
+    rows, B = [1, 7, 300, 100000, 50], 12000
+    T = len(rows)
+    idx = np.concatenate([rng.integers(0, r, size=B) for r in rows]).astype(np.int64)
+    off = np.arange(T * B + 1, dtype=np.int64)
+    Ws = [rng.uniform(-1, 1, size=(r, D)).astype(np.float32) for r in rows]
+    moms_np = [rng.uniform(0, 0.5, size=r).astype(np.float32) for r in rows]
+    di, do = torch.from_numpy(idx).to(dev).to(torch.int32), torch.from_numpy(off).to(dev).to(torch.int32)
+    dg = torch.from_numpy(rng.normal(size=(B, T, D)).astype(np.float32)).to(dev)
+    code = _lib.OPT_SGD if opt == "sgd" else _lib.OPT_RWSADAGRAD
+
+    def reset():
+        for k in (1, 3, 6, 7, 9):
+            _lib.set_tunable(k, 0)
+    request.addfinalizer(reset)
+
+    def run(fixup, prefetch, pipe, seg):
+        tw = [torch.from_numpy(w.copy()).to(dev) for w in Ws]
+        tm = [torch.from_numpy(m.copy()).to(dev) for m in moms_np]
+        ts = ops.TableSet(tw, moms=tm)
+        skey, sbag = ops.bwd_sort(ts, di, do, B)
+        _lib.set_tunable(9, fixup)
+        _lib.set_tunable(6, prefetch)
+        _lib.set_tunable(7, pipe)
+        _lib.set_tunable(3, seg)
+        ops.bwd_update(ts, code, dg, T * D, D, B, skey, sbag, 0.05, 1e-10)
+        torch.cuda.synchronize()
+        return torch.cat(tw).cpu().numpy(), torch.cat(tm).cpu().numpy()
+
+    for seg in (32, 64):
+        w0, m0 = run(1, 1, 1, seg)                       # separate fix-up launch, no prefetch, no pipeline
+        for fixup, prefetch, pipe in ((0, 1, 1), (0, 2, 0), (0, 3, 0), (1, 2, 0), (0, 0, 0)):
+            w, m = run(fixup, prefetch, pipe, seg)
+            assert np.array_equal(w, w0), (seg, fixup, prefetch, pipe)
+            assert np.array_equal(m, m0), (seg, fixup, prefetch, pipe)
+    # and the result itself against the oracle (1e-5 / 1e-6 + the fp32 reassociation term of the hot rows)
+    base = np.concatenate([[0], np.cumsum(rows)])
+    art = O.sort_artifacts(idx, off, T, B, base[:-1])
+    grad = dg.cpu().numpy()
+    g = O.embbag_bwd_coalesced(O.go_rows(grad), art, D)
+    Wcat, mom = np.concatenate(Ws, axis=0), np.concatenate(moms_np)
+    if opt == "sgd":
+        O.sgd_update(Wcat, art["unique"], g, 0.05)
+    else:
+        O.rwsadagrad_update(Wcat, mom, art["unique"], g, 0.05, 1e-10)
+    gabs = O.embbag_bwd_coalesced(np.abs(O.go_rows(grad)), art, D)
+    slack = np.zeros_like(Wcat)
+    slack[art["unique"]] = 2 * 1.2e-7 * 0.05 * gabs
+    assert np.all(np.abs(w0 - Wcat) <= 1e-6 + 1e-5 * np.abs(Wcat) + slack), np.abs(w0 - Wcat).max()
 
 
 @pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (4, 2), (2, 8), (33, 32)])
