@@ -33,8 +33,7 @@ inline int check_launch(const char* what) {
 constexpr int kSMs = 148;  // B200
 
 // Experiment knobs (dlrmx_set_tunable); 0 = default.
-enum { DLRMX_TUNE_FWD_K = 0, DLRMX_TUNE_BWD_K = 1, DLRMX_TUNE_BWD_SEG = 3, DLRMX_TUNE_SCATTER_CTAS = 5, DLRMX_TUNE_BWD_PREFETCH = 6,
-       DLRMX_TUNE_BWD_PIPE = 7, DLRMX_TUNE_FWD_PREFETCH = 8, DLRMX_TUNE_BWD_FIXUP = 9, DLRMX_TUNE_COUNT = 16 };
+enum { DLRMX_TUNE_FWD_K = 0, DLRMX_TUNE_BWD_K = 1, DLRMX_TUNE_BWD_SEG = 3, DLRMX_TUNE_SCATTER_CTAS = 5, DLRMX_TUNE_COUNT = 8 };
 int get_tunable(int which);
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
@@ -57,7 +56,6 @@ struct RowVec<4> {
     }
     __device__ __forceinline__ void load(const float* p) { v = *reinterpret_cast<const float4*>(p); }
     __device__ __forceinline__ void load_ro(const float* p) { v = __ldg(reinterpret_cast<const float4*>(p)); }
-    __device__ __forceinline__ void load_cg(const float* p) { v = __ldcg(reinterpret_cast<const float4*>(p)); }
     __device__ __forceinline__ void load_unaligned(const float* p) { v = make_float4(p[0], p[1], p[2], p[3]); }
     __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = v; }
     __device__ __forceinline__ void add(const RowVec& o) {
@@ -85,7 +83,6 @@ struct RowVec<1> {
     __device__ __forceinline__ void load_stream(const float* p) { v = __ldg(p); }
     __device__ __forceinline__ void load(const float* p) { v = *p; }
     __device__ __forceinline__ void load_ro(const float* p) { v = __ldg(p); }
-    __device__ __forceinline__ void load_cg(const float* p) { v = __ldcg(p); }
     __device__ __forceinline__ void load_unaligned(const float* p) { v = *p; }
     __device__ __forceinline__ void store(float* p) const { *p = v; }
     __device__ __forceinline__ void add(const RowVec& o) { v = __fadd_rn(v, o.v); }

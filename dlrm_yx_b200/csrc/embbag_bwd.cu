@@ -24,21 +24,7 @@ __device__ __forceinline__ T bshfl64(unsigned mask, T v, int src) {
 // are 256/G times shorter than with per-segment partials.
 enum { kHasHead = 1, kHeadClosed = 2, kHasTail = 4, kActive = 8 };
 
-// L2 prefetch of the rows a sub-tile is about to touch, issued LANE-PARALLEL right after the metadata (lane i knows the
-// gradient row of position i and, where a run ends there, its table row and accumulator): one bulk-prefetch instruction
-// per lane puts G whole rows in flight toward L2 at no register cost, so only the first batch of a sub-tile pays DRAM
-// latency and the later batches find their rows in L2.  mode 1: cp.async.bulk.prefetch.L2 (one TMA request per row),
-// mode 2: prefetch.global.L2 per 128-byte line.
-__device__ __forceinline__ void l2_prefetch_row(const float* p, int row_bytes, int mode) {
-    if (mode == 1) {
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(row_bytes) : "memory");
-    } else {
-        for (int o = 0; o < row_bytes; o += 128)
-            asm volatile("prefetch.global.L2 [%0];" ::"l"((const char*)p + o) : "memory");
-    }
-}
-
-template <int VEC, int G, int CH, int K, bool PIPE>
+template <int VEC, int G, int CH, int K>
 __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(const BwdParams P) {
     constexpr int GPC = 256 / G;             // groups (= segments) per CTA
     extern __shared__ __align__(16) float sh_part[];     // [2][GPC][D]: head partials, tail partials
@@ -65,14 +51,16 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
     for (int c = 0; c < CH; ++c) acc[c].zero();
     bool open = false;                       // does the position walked last belong to a run that is not finished?
 
-    // lane-parallel metadata of the sub-tile starting at sorted position pt (+ its L2 prefetches)
-    auto fetch_meta = [&](int64_t pt, bool& last, const float*& gptr, float*& wptr, float*& mptr) {
-        last = false;
-        gptr = nullptr;
-        wptr = nullptr;
-        mptr = nullptr;
+#pragma unroll 1
+    for (int64_t pt = p0; pt < p1; pt += G) {
+        const int nvalid = (int)min((int64_t)G, p1 - pt);
+        // ---- lane-parallel metadata ---------------------------------------------------------------------
         const int64_t p = pt + gl;
-        if (p < p1) {
+        bool last = false;
+        const float* gptr = nullptr;
+        float* wptr = nullptr;
+        float* mptr = nullptr;
+        if (gl < nvalid) {
             const uint32_t key = skey[p];
             const uint32_t knext = (p + 1 < P.N) ? skey[p + 1] : ~key;
             const int bag = sbag[p];
@@ -80,37 +68,11 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             const int t = bag / P.B;
             const int b = bag - t * P.B;
             gptr = P.grad + (int64_t)b * P.stride_b + (int64_t)t * P.stride_t;    // row start; col0 added after broadcast
-            if (VEC == 4 && P.prefetch != 0) l2_prefetch_row(gptr, P.D * 4, P.prefetch);
             if (last) {
                 const int64_t row = (int64_t)key - P.row_base[t];
                 wptr = P.tables[t] + row * P.D;
-                if (VEC == 4 && P.prefetch != 0) l2_prefetch_row(wptr, P.D * 4, P.prefetch);
-                if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-                    mptr = P.moms[t] + row;
-                    if (P.prefetch != 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(mptr) : "memory");
-                }
+                if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mptr = P.moms[t] + row;
             }
-        }
-    };
-    bool n_last = false;
-    const float* n_gptr = nullptr;
-    float* n_wptr = nullptr;
-    float* n_mptr = nullptr;
-    if (PIPE && p0 < p1) fetch_meta(p0, n_last, n_gptr, n_wptr, n_mptr);
-
-#pragma unroll 1
-    for (int64_t pt = p0; pt < p1; pt += G) {
-        const int nvalid = (int)min((int64_t)G, p1 - pt);
-        bool last;
-        const float* gptr;
-        float* wptr;
-        float* mptr;
-        if (PIPE) {
-            // software pipeline: the next sub-tile's metadata (and prefetches) are requested before this one is walked
-            last = n_last; gptr = n_gptr; wptr = n_wptr; mptr = n_mptr;
-            if (pt + G < p1) fetch_meta(pt + G, n_last, n_gptr, n_wptr, n_mptr);
-        } else {
-            fetch_meta(pt, last, gptr, wptr, mptr);
         }
         const unsigned lastmask = (__ballot_sync(gmask, last) >> gshift);
 
@@ -266,18 +228,14 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             store_partial<VEC, G, CH>(P.tail_partial, blockIdx.x, P.D, col0, acc);
         }
     }
-    // the run that entered the CTA from the left: group 0 sums the in-CTA pieces of it (ascending)
-    const bool head_group = gi == 0 && (flags & kHasHead) != 0;
-    bool hclosed = false;                          // does that run END inside this CTA?
-    RowVec<VEC> hacc[CH];
-    if (head_group) {
+    if (gi == 0 && (flags & kHasHead) != 0) {      // the run that entered the CTA from the left: one head partial per CTA
+        RowVec<VEC> hacc[CH];
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
             hacc[c].zero();
             if (CH == 1 || col0 + c * G * VEC < P.D) hacc[c].load(sh_part + col0 + c * G * VEC);
         }
-        hclosed = (flags & kHeadClosed) != 0;
-        if (!hclosed) {
+        if ((flags & kHeadClosed) == 0) {
             for (int v = 1; v < GPC && (sh_flag[v] & kActive); ++v) {
                 const float* hp = sh_part + (size_t)v * P.D + col0;
 #pragma unroll
@@ -287,100 +245,10 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                         h.load(hp + c * G * VEC);
                         hacc[c].add(h);
                     }
-                if (sh_flag[v] & kHeadClosed) { hclosed = true; break; }
+                if (sh_flag[v] & kHeadClosed) break;
             }
         }
-        // separate fix-up kernel: every head partial is published; fused look-back: only those of runs that go on
-        if (!P.fused_fixup || !hclosed) store_partial<VEC, G, CH>(P.head_partial, blockIdx.x, P.D, col0, hacc);
-    }
-    if (!P.fused_fixup) return;
-
-    // ---- runs crossing CTA boundaries, finished in this launch (decoupled look-back) -------------------------------
-    // Every CTA publishes "my partials are in global memory" (ready[cta] = 1); the CTA in which a crossing run ENDS finds
-    // the CTA where it started from the sorted keys alone, waits for the flags of the CTAs in between (all of lower
-    // index: CTAs are dispatched in index order, and every CTA publishes before it waits, so the wait cannot deadlock)
-    // and adds  tail[start] + head[start+1] + ... + head[me-1] + (my head, still in registers)  in that fixed order --
-    // the same order of additions as bwd_fixup_kernel, hence bit-identical results, without a second launch.
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(P.ready + blockIdx.x), "r"(1) : "memory");
-    if (!(head_group && hclosed)) return;
-    {
-        constexpr int KF = (CH == 1) ? 8 : 2;
-        constexpr unsigned gbits = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
-        const int64_t tile_len = (int64_t)GPC * P.seg_len;
-        const int64_t cta_p0 = (int64_t)blockIdx.x * tile_len;
-        const uint32_t key = skey[cta_p0];
-        int64_t b = (int64_t)blockIdx.x - 1, start = -1;
-        while (start < 0) {                        // lane i: does the run start in tile b - i?
-            const int64_t bb = b - gl;
-            bool isstart = false;
-            if (bb >= 0) {
-                const int64_t pb = bb * tile_len;
-                isstart = (pb == 0) || (skey[pb - 1] != key);
-            }
-            const unsigned m = (__ballot_sync(gmask, isstart) >> gshift) & gbits;
-            if (m != 0u) start = b - (__ffs(m) - 1);
-            else b -= G;
-        }
-        RowVec<VEC> racc[CH];
-#pragma unroll
-        for (int c = 0; c < CH; ++c) racc[c].zero();
-        for (int64_t s0 = start; s0 < (int64_t)blockIdx.x; s0 += G) {
-            const int cnt = (int)min((int64_t)G, (int64_t)blockIdx.x - s0);
-            if (gl < cnt) {                        // lane-parallel wait on the producers' flags
-                const int* f = P.ready + s0 + gl;
-                int v = 0, tries = 0;
-                for (;;) {
-                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-                    if (v != 0) break;
-                    if (++tries > (1 << 22)) __trap();      // a lost producer must not hang the GPU
-                    __nanosleep(64);
-                }
-            }
-            __syncwarp(gmask);
-            __threadfence();
-            for (int q0 = 0; q0 < cnt; q0 += KF) {
-                RowVec<VEC> h[KF][CH];
-#pragma unroll
-                for (int j = 0; j < KF; ++j)
-                    if (q0 + j < cnt) {
-                        const int64_t s = s0 + q0 + j;
-                        const float* hp = ((s == start) ? P.tail_partial : P.head_partial) + s * P.D + col0;
-#pragma unroll
-                        for (int c = 0; c < CH; ++c)
-                            if (CH == 1 || col0 + c * G * VEC < P.D) h[j][c].load_cg(hp + c * G * VEC);
-                    }
-#pragma unroll
-                for (int j = 0; j < KF; ++j)
-                    if (q0 + j < cnt) {
-#pragma unroll
-                        for (int c = 0; c < CH; ++c)
-                            if (CH == 1 || col0 + c * G * VEC < P.D) {
-                                if (s0 + q0 + j == start) racc[c] = h[j][c];
-                                else racc[c].add(h[j][c]);
-                            }
-                    }
-            }
-        }
-#pragma unroll
-        for (int c = 0; c < CH; ++c)
-            if (CH == 1 || col0 + c * G * VEC < P.D) racc[c].add(hacc[c]);
-        const int bag = sbag[cta_p0];
-        const int t = bag / P.B;
-        const int64_t row = (int64_t)key - P.row_base[t];
-        float* wp = P.tables[t] + row * P.D + col0;
-        RowVec<VEC> w[CH];
-#pragma unroll
-        for (int c = 0; c < CH; ++c)
-            if (CH == 1 || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
-        float* mp = nullptr;
-        float mo = 0.f;
-        if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-            mp = P.moms[t] + row;
-            mo = *mp;
-        }
-        apply_row<VEC, G, CH>(P, wp, mp, mo, w, racc, col0);
+        store_partial<VEC, G, CH>(P.head_partial, blockIdx.x, P.D, col0, hacc);
     }
 }
 
@@ -524,7 +392,6 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
     const int64_t row = rows[u];
     BwdParams P;
     P.optimizer = optimizer; P.D = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
-    P.prefetch = 0; P.fused_fixup = 0; P.ready = nullptr;
     RowVec<VEC> g[CH], w[CH];
     float* wp = W + row * D + col0;
     const float* gp = gsum + u * D + col0;
@@ -553,22 +420,15 @@ static int launch_rows_update(int optimizer, float* W, float* mom, const int64_t
     return check_launch("rows_update");
 }
 
-template <int VEC, int G, int CH, int K = (CH == 1 ? 4 : 2), bool PIPE = false>
+template <int VEC, int G, int CH, int K = (CH == 1 ? 4 : 2)>
 static int launch_update(const BwdParams& P, cudaStream_t st) {
     const int threads = 256;
     constexpr int GPC = 256 / G;
     const unsigned blocks = (unsigned)ceil_div(P.nseg, (int64_t)GPC);
     const size_t smem = (size_t)2 * GPC * P.D * sizeof(float);
-    if (P.fused_fixup) {
-        cudaError_t e = cudaMemsetAsync(P.ready, 0, (size_t)blocks * sizeof(int), st);
-        if (e != cudaSuccess) {
-            set_error("bwd_update: memset of the look-back flags: %s", cudaGetErrorString(e));
-            return DLRMX_E_CUDA;
-        }
-    }
-    bwd_update_kernel<VEC, G, CH, K, PIPE><<<blocks, threads, smem, st>>>(P);
+    bwd_update_kernel<VEC, G, CH, K><<<blocks, threads, smem, st>>>(P);
     int rc = check_launch("bwd_update");
-    if (rc || P.fused_fixup) return rc;
+    if (rc) return rc;
     // the fix-up works on CTA tiles: GPC segments each, one head / tail partial per tile
     BwdParams Q = P;
     Q.seg_len = P.seg_len * GPC;
@@ -621,11 +481,9 @@ static int seg_len_for(int64_t N, int optimizer) {
     return optimizer == DLRMX_OPT_SGD ? 128 : 64;
 }
 
-constexpr int kDefaultPrefetch = 1;   // bulk L2 prefetch (measured on B200)
-
 static size_t update_workspace_bytes(int64_t N, int D) {
     const int64_t nseg = ceil_div(N > 0 ? N : 1, kSeg);       // sized for the smallest segment length
-    return align_up((size_t)nseg * D * 4, 256) * 2 + align_up((size_t)nseg * sizeof(int), 256);   // partials + look-back flags
+    return align_up((size_t)nseg * D * 4, 256) * 2;
 }
 
 }  // namespace dlrmx
@@ -658,22 +516,10 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
     P.head_partial = (float*)workspace;
     P.tail_partial = (float*)((char*)workspace + align_up((size_t)P.nseg * D * 4, 256));
-    P.ready = (int*)((char*)workspace + 2 * align_up((size_t)P.nseg * D * 4, 256));
-    P.fused_fixup = get_tunable(DLRMX_TUNE_BWD_FIXUP) != 1;      // tunable 9 = 1: separate bwd_fixup_kernel launch
     cudaStream_t st = (cudaStream_t)stream;
 #define DLRMX_CALL_UPDATE(V, G_, C) launch_update<V, G_, C>(P, st)
     // experiment knob (tunable 1 = 8): 8 positions in flight per lane for one-warp-per-row geometries
     if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 8) return launch_update<4, 32, 1, 8>(P, st);
-    // tunable 6: L2 prefetch mode of the sub-tile rows (0 default, 1 off, 2 bulk, 3 per line); tunable 7 = 1: metadata pipeline off
-    {
-        const int pf = get_tunable(DLRMX_TUNE_BWD_PREFETCH);
-        P.prefetch = (pf == 0) ? kDefaultPrefetch : pf - 1;
-        const bool pipe = get_tunable(DLRMX_TUNE_BWD_PIPE) != 1;
-        if (pipe && g.vec == 4 && g.ch == 1) {
-            if (g.g == 32) return launch_update<4, 32, 1, 4, true>(P, st);
-            if (g.g == 16) return launch_update<4, 16, 1, 4, true>(P, st);
-        }
-    }
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;

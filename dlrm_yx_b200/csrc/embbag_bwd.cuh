@@ -37,13 +37,10 @@ struct BwdParams {
     const int32_t* sbag;
     int64_t N, nseg;
     int seg_len;          // sorted positions per group (multiple of 32)
-    int prefetch;         // L2 prefetch of the rows of a sub-tile: 0 none, 1 bulk (TMA) prefetch per row, 2 per 128-B line
     float lr, eps;
     float inv_D;          // 1/D when D is a power of two, else 0 (row_mean)
     float* head_partial;  // [nseg, D]
     float* tail_partial;  // [nseg, D]
-    int* ready;           // [CTAs] look-back flags (fused fix-up), zeroed before every launch
-    int fused_fixup;      // 1: crossing runs are finished inside bwd_update_kernel (look-back), 0: by bwd_fixup_kernel
 };
 
 template <int G>

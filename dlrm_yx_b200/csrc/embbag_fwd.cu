@@ -48,13 +48,14 @@ __device__ __forceinline__ int32_t shfl_idx(unsigned mask, int32_t v, int src, i
 // one-index-per-bag Criteo layout), otherwise a tile is one batch of K bags (long bags: more groups, and the
 // memory-level parallelism comes from unrolling ALONG the bag -- loads are issued U at a time, the adds still
 // happen one by one in index order).
-template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT>
-__global__ void __launch_bounds__(256, (K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2))
+// OCC > 0 overrides the CTAs-per-SM target of the register allocation.
+template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT, int OCC = 0>
+__global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2)))
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
-                  float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len, int pf_dist) {
+                  float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len) {
     constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
     constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
@@ -125,36 +126,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
 #pragma unroll
             for (int c = 0; c < CH; ++c) acc[k][c].zero();
 
-        // Long bags: rows are pulled toward L2 `pf_dist` positions ahead of the walk, LANE-PARALLEL -- the G/KB lanes that
-        // serve bag k each read one index of the window and issue one bulk prefetch (cp.async.bulk.prefetch.L2, a whole
-        // row per instruction, no registers held), so the walk's own loads (U per bag in flight, consumed in index order)
-        // find their rows in L2 instead of paying DRAM latency once per round.
-        constexpr int LPB = G / KB;                   // lanes per bag
-        const int pk = gl / LPB, pj = gl - pk * LPB;  // my bag of the batch, my slot in its window
-        IdxT pstart = 0;
-        int plen = 0;
-        const float* pbase = nullptr;
-        int64_t prows = 0;
-        const bool do_pf = !FULL && VEC == 4 && LPB >= 1 && pf_dist > 0;
-        if (do_pf) {
-#pragma unroll
-            for (int k = 0; k < KB; ++k)
-                if (k == pk) { pstart = start[k]; plen = len[k]; pbase = base[k]; prows = nrows[k]; }
-            for (int pos = U + pj; pos < min(plen, pf_dist); pos += LPB) {
-                const int64_t ixp = (int64_t)indices[pstart + pos];
-                if (ixp >= 0 && ixp < prows)
-                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pbase + ixp * D), "r"(D * 4) : "memory");
-            }
-        }
-
         for (int r = 0; r < maxlen; r += U) {
-            if (do_pf) {
-                for (int pos = r + pf_dist + pj; pos < min(plen, r + pf_dist + U); pos += LPB) {
-                    const int64_t ixp = (int64_t)indices[pstart + pos];
-                    if (ixp >= 0 && ixp < prows)
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pbase + ixp * D), "r"(D * 4) : "memory");
-                }
-            }
             RowVec<VEC> row[KB][U][CH];
             bool live[KB][U];
 #pragma unroll
@@ -221,16 +193,11 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     }
 }
 
-constexpr int kDefaultFwdPrefetch = 2;   // rounds of U rows the L2 prefetch runs ahead of the long-bag walk
-
-template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT>
+template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
                       int mb_len, cudaStream_t st) {
-    // tunable 8: prefetch distance of the long-bag walk in units of U rows (0: default, -1: off)
-    const int pft = get_tunable(DLRMX_TUNE_FWD_PREFETCH);
-    const int pf_dist = FULL ? 0 : (pft < 0 ? 0 : (pft == 0 ? kDefaultFwdPrefetch : pft) * U);
     const bool windowed = out_peers != nullptr && mb_len < lb;
     const int64_t total_bags = windowed ? (int64_t)T * (B / lb) * mb_len : (int64_t)T * B;
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
@@ -239,13 +206,13 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
     if (out_peers != nullptr)
-        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, true, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
+        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, true, IdxT, OCC><<<(unsigned)blocks, threads, 0, st>>>(
             tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
-            out_peers, lb, mb_off, mb_len, pf_dist);
+            out_peers, lb, mb_off, mb_len);
     else
-        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, false, IdxT><<<(unsigned)blocks, threads, 0, st>>>(
+        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, false, IdxT, OCC><<<(unsigned)blocks, threads, 0, st>>>(
             tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
-            nullptr, 1, 0, 1, pf_dist);
+            nullptr, 1, 0, 1);
     return check_launch("embbag_fwd");
 }
 
@@ -279,13 +246,18 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
             if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 8, 1, true, IdxT>(DLRMX_FWD_ARGS); \
             return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);       \
         }                                                                                              \
-        /* long bags, measured on B200 at 100 rows per bag: rows <= 256 B (G <= 16) want 8 rows of each bag in flight */ \
-        /* (0.60 of peak at the C3 shape, 0.72 with 8x the bags; 4 rows: 0.40), 512-B rows want 4 (0.70; 8 rows: 0.42). */ \
-        /* A two-round register double buffer was tried and was slower than either (spills at 2 CTAs per SM).          */ \
-        if (CH_ == 1 && tune == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT>(DLRMX_FWD_ARGS);  \
-        if (CH_ == 1 && (tune == 8 || (tune == 0 && G_ <= 16)))                                        \
-            return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS);                       \
-        return launch_fwd<VEC_, G_, CH_, 2, (CH_ == 1 ? 4 : 2), false, IdxT>(DLRMX_FWD_ARGS);          \
+        /* long bags, measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the bags /  */ \
+        /* 512-byte rows): ONE bag per group with 8 of its rows in flight wins everywhere -- 0.61 / 0.76 / 0.98 against   */ \
+        /* 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128 registers, 2 CTAs per SM, half as many work units  */ \
+        /* for the launch's tail).  An L2 bulk prefetch ahead of the walk (cp.async.bulk.prefetch.L2, lane-parallel)     */ \
+        /* and a two-round register double buffer were tried and were slower.  FWD_K tunable: 1/2/3 one bag per group at */ \
+        /* 4 / 3 CTAs per SM / 16 rows in flight, 8 and 4: the older two-bag variants.                                    */ \
+        if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS);  \
+        if (CH_ == 1 && tune == 4) return launch_fwd<VEC_, G_, CH_, 2, 4, false, IdxT>(DLRMX_FWD_ARGS);  \
+        if (CH_ == 1 && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 3>(DLRMX_FWD_ARGS); \
+        if (CH_ == 1 && tune == 3) return launch_fwd<VEC_, G_, CH_, 1, 16, false, IdxT, 2>(DLRMX_FWD_ARGS); \
+        if (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS);            \
+        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3>(DLRMX_FWD_ARGS);          \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
     DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)

@@ -85,3 +85,59 @@ def local_packed(lS_o, lS_i, local_tables, dtype=torch.int32):
     """Packed batch restricted to this rank's tables (what dlrm_wrap + distribute_batched_emb_data hand to a
     rank, dlrm_s_pytorch.py:147-148, 772-802)."""
     return pack([lS_o[k] for k in local_tables], [lS_i[k] for k in local_tables], dtype)
+
+
+class CriteoBinDataset:
+    """Device-side twin of the reference's CriteoBinDataset (data_loader_terabyte.py:205-252; same constructor
+    arguments and item layout): item `idx` is batch `idx` of the binary file (records of 40 int32: label, 13 dense,
+    26 categorical).  The raw bytes of the batch are read into a pinned staging buffer, copied to the device as they
+    are (160 B per sample) and split / log-transformed / taken modulo max_ind_range / transposed by ONE kernel
+    (csrc/criteo_bin.cu), so the tensors the model consumes are born on the GPU:
+        (X [B,13] fp32, lS_o, lS_i, T [B,1] fp32)   with lS_o / lS_i int64 [26, B], or, with
+        batched_or_fbgemm_emb, offsets int32 [26*B+1] / indices int32 [26*B].
+    counts_file is optional here (the reference loads it and never uses it on this path)."""
+
+    tar_fea, den_fea, spa_fea = 1, 13, 26
+
+    def __init__(self, data_file, counts_file=None, batch_size=1, max_ind_range=-1, bytes_per_feature=4,
+                 batched_or_fbgemm_emb=False, device="cuda"):
+        import math
+        import os
+        if bytes_per_feature != 4:
+            raise ValueError("CriteoBinDataset: the binary format has 4 bytes per feature")
+        self.tad_fea = self.tar_fea + self.den_fea
+        self.tot_fea = self.tad_fea + self.spa_fea
+        self.batch_size = batch_size
+        self.max_ind_range = max_ind_range
+        self.bytes_per_entry = bytes_per_feature * self.tot_fea * batch_size
+        self.num_entries = math.ceil(os.path.getsize(data_file) / self.bytes_per_entry)
+        self.file = open(data_file, "rb")
+        self.counts = None
+        if counts_file is not None:
+            with np.load(counts_file) as data:
+                self.counts = data["counts"]
+        self.m_den = 13
+        self.batched_or_fbgemm_emb = batched_or_fbgemm_emb
+        self.device = torch.device(device)
+        self._stage = torch.empty((batch_size, self.tot_fea), dtype=torch.int32).pin_memory()
+
+    def __len__(self):
+        return self.num_entries
+
+    def __getitem__(self, idx):
+        from . import ops
+        if idx < 0 or idx >= self.num_entries:
+            raise IndexError(idx)
+        self.file.seek(idx * self.bytes_per_entry, 0)
+        buf = self._stage.numpy().reshape(-1).view(np.uint8)
+        n = self.file.readinto(memoryview(buf))
+        nrec = n // (4 * self.tot_fea)                       # the last batch of a file may be short
+        rec = self._stage[:nrec].to(self.device, non_blocking=True)
+        out = ops.criteo_bin_batch(rec, self.max_ind_range, batched=self.batched_or_fbgemm_emb)
+        torch.cuda.current_stream().synchronize()            # the staging buffer is reused by the next item
+        return out
+
+    def __del__(self):
+        f = getattr(self, "file", None)
+        if f is not None:
+            f.close()

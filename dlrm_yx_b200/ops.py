@@ -410,3 +410,28 @@ def dense_opt(mode, params, acc, grads, shadow, lr, eps=0.0, grad_scale=1.0):
         rc = _lib.load().dlrmx_dense_opt(mode, params.data_ptr(), _ptr(acc), grads.data_ptr(), _ptr(shadow),
                                          params.numel(), float(lr), float(eps), float(grad_scale), _stream())
         _lib.check(rc, "dlrmx_dense_opt")
+
+
+def criteo_bin_batch(records, max_ind_range=-1, batched=True, index_dtype=None):
+    """records: int32 [B, 40] CUDA tensor of raw Criteo-Terabyte binary records -> (X [B,13] fp32, offsets, indices,
+    target [B,1] fp32) exactly as CriteoBinDataset.__getitem__ / _transform_features return them
+    (data_loader_terabyte.py:68-95, 236-249): batched -> indices int32 [26*B], offsets int32 [26*B+1];
+    otherwise lS_o / lS_i int64 [26, B]."""
+    _need_cuda(records)
+    if records.dtype != torch.int32 or records.dim() != 2 or records.shape[1] != 40 or not records.is_contiguous():
+        raise _lib.DlrmxError("criteo_bin_batch: records must be a contiguous int32 [B, 40] tensor")
+    B = int(records.shape[0])
+    dt = index_dtype or (torch.int32 if batched else torch.int64)
+    dev = records.device
+    X = torch.empty((B, 13), dtype=torch.float32, device=dev)
+    tgt = torch.empty((B, 1), dtype=torch.float32, device=dev)
+    indices = torch.empty(26 * B, dtype=dt, device=dev)
+    offsets = torch.empty(26 * B + (1 if batched else 0), dtype=dt, device=dev)
+    fn = _lib.load().dlrmx_criteo_bin_batch_i32 if dt == torch.int32 else _lib.load().dlrmx_criteo_bin_batch_i64
+    with _timed("criteo_bin_batch"):
+        rc = fn(records.data_ptr(), B, int(max_ind_range), 1 if batched else 0, X.data_ptr(), indices.data_ptr(),
+                offsets.data_ptr(), tgt.data_ptr(), _stream())
+    _lib.check(rc, "dlrmx_criteo_bin_batch")
+    if batched:
+        return X, offsets, indices, tgt
+    return X, offsets.view(26, B), indices.view(26, B), tgt

@@ -256,6 +256,25 @@ int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
 int dlrmx_copy2d_async(void* dst, size_t dst_pitch_bytes, const void* src, size_t src_pitch_bytes,
                        size_t width_bytes, size_t height, dlrmx_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Criteo Terabyte binary records -> one batch in the hot path's input layout.
+ * Replaces CriteoBinDataset.__getitem__ + _transform_features (data_loader_terabyte.py:205-252, 68-95),
+ * which the reference runs on the host with torch CPU ops.
+ *   records  [B, 40] int32 as they lie in the file: label, 13 dense counts, 26 categorical ids
+ *            (device copy of the raw bytes, 16-byte aligned)
+ *   dense    [B, 13] fp32 = log(float(count) + 1)
+ *   indices  [26*B]  categorical ids, table-major (the reference's x_cat.t()), taken modulo
+ *            max_ind_range when max_ind_range > 0 (floor modulo, like torch's % on int32)
+ *   offsets  batched != 0: [26*B + 1] = arange (packed layout of the batched op, data_loader_terabyte.py:88-93);
+ *            batched == 0: [26, B], every row arange(B) (lS_o of the per-table API)
+ *   target   [B] fp32 = float(label)   (the reference views it as [B, 1])
+ * Integer outputs are bit-exact with the reference; dense differs by the device logf (<= 2 ulp).
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_criteo_bin_batch_i32(const int32_t* records, int B, int max_ind_range, int batched, float* dense,
+                               int32_t* indices, int32_t* offsets, float* target, dlrmx_stream_t stream);
+int dlrmx_criteo_bin_batch_i64(const int32_t* records, int B, int max_ind_range, int batched, float* dense,
+                               int64_t* indices, int64_t* offsets, float* target, dlrmx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

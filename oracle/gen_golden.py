@@ -132,11 +132,53 @@ def sharder_golden(ns):
     return out
 
 
+def criteo_bin_golden(ns):
+    """The reference's CriteoBinDataset (data_loader_terabyte.py:205-252) run on a small synthetic binary file:
+    150 records in batches of 64 (the last batch is short), categorical ids up to 2^31-1 plus a few negative ones
+    (floor-modulo semantics of `%`), dense counts 0..10^6; per-table and batched layouts, with and without
+    max_ind_range."""
+    import importlib
+    import tempfile
+    dlt = importlib.import_module("data_loader_terabyte")
+    rng = np.random.default_rng(2024)
+    n, bs = 150, 64
+    rec = np.zeros((n, 40), dtype=np.int32)
+    rec[:, 0] = rng.integers(0, 2, size=n)
+    rec[:, 1:14] = (10 ** rng.uniform(0, 6, size=(n, 13))).astype(np.int32) - 1
+    rec[:, 14:] = rng.integers(0, 2 ** 31 - 1, size=(n, 26), dtype=np.int64).astype(np.int32)
+    rec[::17, 20] = -rec[::17, 20] - 1
+    rec[5, 14:] = 0
+    out = {"records": rec, "batch_size": np.array(bs)}
+    with tempfile.TemporaryDirectory() as d:
+        f = os.path.join(d, "day.bin")
+        rec.tofile(f)
+        cf = os.path.join(d, "counts.npz")
+        np.savez(cf, counts=np.arange(26))
+        for batched in (False, True):
+            for mir in (-1, 1000, 40000000):
+                ds = dlt.CriteoBinDataset(f, cf, batch_size=bs, max_ind_range=mir, batched_or_fbgemm_emb=batched)
+                out["len"] = np.array(len(ds))
+                for i in range(len(ds)):
+                    X, lS_o, lS_i, T = ds[i]
+                    tag = "%s_%d_%d" % ("batched" if batched else "tables", mir, i)
+                    out["X_" + tag] = X.numpy()
+                    out["off_" + tag] = lS_o.numpy()
+                    out["idx_" + tag] = lS_i.numpy()
+                    out["T_" + tag] = T.numpy()
+                del ds
+    return out
+
+
 def main():
     sys.path.insert(0, ROOT)
     from oracle.ref_shim import load_reference
     ns = load_reference()
     os.makedirs(GOLDEN, exist_ok=True)
+    cb = criteo_bin_golden(ns)
+    np.savez_compressed(os.path.join(GOLDEN, "criteo_bin.npz"), **cb)
+    print("wrote criteo_bin.npz")
+    if "--only-criteo" in sys.argv:
+        return
     for case in CASES:
         out = run_case(ns, *case)
         path = os.path.join(GOLDEN, case[0] + ".npz")

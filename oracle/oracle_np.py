@@ -310,3 +310,25 @@ def bce_loss(p, t):
     loss = -np.mean(t64 * np.maximum(np.log(p64), -100) + (1 - t64) * np.maximum(np.log(1 - p64), -100))
     dp = (p64 - t64) / np.maximum(p64 * (1 - p64), 1e-12) / n
     return f32(loss), dp.astype(f32)
+
+
+def criteo_bin_transform(records, max_ind_range=-1, batched=False):
+    """CriteoBinDataset.__getitem__ + _transform_features (data_loader_terabyte.py:236-249, 68-95) on one batch of
+    raw records [B, 40] int32 = [label | 13 dense | 26 categorical]:
+      x_cat % max_ind_range when max_ind_range > 0 (torch int32 `%`: floor modulo), X = log(float32(dense) + 1),
+      lS_i = x_cat.t() as int64 [26, B], lS_o = arange(B) per table, T = float32(label) [B, 1];
+      batched: indices = lS_i flattened table-major as int32, offsets = arange(26*B + 1) int32 (88-93)."""
+    rec = np.asarray(records, dtype=np.int32).reshape(-1, 40)
+    B = rec.shape[0]
+    y = rec[:, 0].astype(np.float32).reshape(-1, 1)
+    x_int = np.log(rec[:, 1:14].astype(np.float32) + np.float32(1.0)).astype(np.float32)
+    x_cat = rec[:, 14:]
+    if max_ind_range > 0:
+        x_cat = np.mod(x_cat, np.int32(max_ind_range))          # floor modulo, sign of the divisor
+    lS_i = np.ascontiguousarray(x_cat.T).astype(np.int64)
+    lS_o = np.tile(np.arange(B, dtype=np.int64), (26, 1))
+    if batched:
+        indices = lS_i.reshape(-1).astype(np.int32)
+        offsets = np.arange(26 * B + 1, dtype=np.int32)
+        return x_int, offsets, indices, y
+    return x_int, lS_o, lS_i, y

@@ -201,3 +201,28 @@ def test_rwsadagrad_steps_torch_embeddingbag_grads_too():
     O.rwsadagrad_update(W0, mom, art["unique"], gs, 0.05)
     np.testing.assert_allclose(E.weight.detach().cpu().numpy(), W0, rtol=RT, atol=AT)
     np.testing.assert_allclose(opt.state[E.weight]["momentum"].cpu().numpy(), mom, rtol=RT, atol=1e-9)
+
+
+@pytest.mark.parametrize("batched", [False, True])
+@pytest.mark.parametrize("mir", [-1, 1000, 40000000])
+def test_criteo_bin_dataset_on_device(golden_dir, tmp_path, batched, mir):
+    """data.CriteoBinDataset (raw records -> device, one kernel) against the reference's CriteoBinDataset outputs
+    (tests/golden/criteo_bin.npz): indices, offsets and targets bit-exact (dtype and shape included), dense features
+    within 2 ulp (device logf vs torch CPU log), short last batch included."""
+    from dlrm_yx_b200 import data
+    g = np.load(os.path.join(golden_dir, "criteo_bin.npz"))
+    f = tmp_path / "day.bin"
+    g["records"].tofile(str(f))
+    ds = data.CriteoBinDataset(str(f), None, batch_size=int(g["batch_size"]), max_ind_range=mir,
+                               batched_or_fbgemm_emb=batched)
+    assert len(ds) == int(g["len"])
+    for i in range(len(ds)):
+        X, off, idx, T = ds[i]
+        tag = "%s_%d_%d" % ("batched" if batched else "tables", mir, i)
+        for got, name in ((off, "off_"), (idx, "idx_"), (T, "T_")):
+            ref = g[name + tag]
+            assert got.is_cuda and tuple(got.shape) == ref.shape and str(got.dtype).endswith(str(ref.dtype)), name
+            assert np.array_equal(got.cpu().numpy(), ref), name
+        np.testing.assert_allclose(X.cpu().numpy(), g["X_" + tag], rtol=2.4e-7, atol=0)
+    with pytest.raises(IndexError):
+        ds[len(ds)]

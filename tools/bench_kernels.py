@@ -111,23 +111,19 @@ def main():
 
     only = set(args.only.split(",")) if args.only else None
     long_bags = L > 2
-    fwd_variants = [(k, 0) for k in (8, 4, 0)]
-    if long_bags:     # (K tunable, prefetch distance in rounds of U rows; -1 = off)
-        fwd_variants = [(0, -1), (0, 1), (0, 2), (0, 4), (1, -1), (1, 2), (1, 4), (8, 2), (4, 2)]
-    for k, pf in fwd_variants:
+    fwd_variants = (0, 2, 3, 8, 4) if long_bags else (8, 4, 0)   # see the FWD_K tunable in csrc/embbag_fwd.cu
+    for k in fwd_variants:
         if only and "fwd" not in only:
             break
         _lib.set_tunable(_lib.TUNE_FWD_K, k)
-        _lib.set_tunable(8, pf)
 
         def f():
             idx, off = batches[it[0] % nbatch]
             it[0] += 1
             ops.embbag_forward(ts, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=False)
         ms, mn = timed(f, args.iters)
-        report("embbag_fwd", ms, mn, fwd_bytes, dict(K=k, prefetch=pf))
+        report("embbag_fwd", ms, mn, fwd_bytes, dict(K=k))
     _lib.set_tunable(_lib.TUNE_FWD_K, 0)
-    _lib.set_tunable(8, 0)
 
     def s():
         idx, off = batches[it[0] % nbatch]
@@ -140,19 +136,12 @@ def main():
     sorted_batches = [ops.bwd_sort(ts, idx, off, B) for idx, off in batches]
     uniq = [int(ops.bwd_segments(sk)[2].item()) for sk, _ in sorted_batches]
     U = sum(uniq) / len(uniq)
-    # (segment length, K tunable, fix-up: 0 fused look-back / 1 separate launch, prefetch: 1 off / 2 bulk / 3 per line,
-    #  metadata pipeline: 0 on / 1 off)
-    variants = [(0, 0, 1, 1, 1), (0, 0, 0, 1, 1), (0, 0, 0, 2, 1), (0, 0, 0, 3, 1), (0, 0, 0, 1, 0), (0, 0, 0, 2, 0),
-                (0, 0, 0, 3, 0), (128, 0, 0, 3, 0), (128, 0, 0, 2, 0), (32, 0, 0, 3, 0), (0, 8, 0, 3, 1), (0, 0, 0, 0, 0)]
     for opt, name in ((_lib.OPT_SGD, "sgd"), (_lib.OPT_RWSADAGRAD, "rwsadagrad")):
         if only and "bwd" not in only:
             break
-        for seg, k8, fix, pf, pipe in variants:
+        for seg, k8 in ((0, 0), (64, 0), (128, 0), (0, 8)):
             _lib.set_tunable(3, seg)
             _lib.set_tunable(_lib.TUNE_BWD_K, k8)
-            _lib.set_tunable(9, fix)
-            _lib.set_tunable(6, pf)
-            _lib.set_tunable(7, pipe)
 
             def u():
                 sk, sb = sorted_batches[it[0] % nbatch]
@@ -160,8 +149,8 @@ def main():
                 ops.bwd_update(ts, opt, grad, GS * D, D, B, sk, sb, 0.01, 1e-10)
             ms, mn = timed(u, args.iters)
             nbytes = T * B * D * 4 + N * 8 + 2 * U * D * 4 + (2 * U * 4 if opt else 0)
-            report("bwd_update_" + name, ms, mn, nbytes, dict(seg=seg, K=k8, separate_fixup=fix, prefetch=pf, pipe_off=pipe, U=int(U)))
-    for k in (3, 1, 9, 6, 7):
+            report("bwd_update_" + name, ms, mn, nbytes, dict(seg=seg, K=k8, U=int(U)))
+    for k in (3, 1):
         _lib.set_tunable(k, 0)
     if only and "dense" not in only:
         return
