@@ -19,16 +19,16 @@ SIGNATURES = {
     "dlrmx_last_error": (ctypes.c_char_p, []),
     "dlrmx_launch_count": (c_int64, []),
     "dlrmx_set_tunable": (c_int, [c_int, c_int]),
-    "dlrmx_embbag_fwd_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+    "dlrmx_embbag_fwd_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,
                                      c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
-    "dlrmx_embbag_fwd_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+    "dlrmx_embbag_fwd_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,
                                      c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "dlrmx_embbag_fwd_scatter_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
-                                             c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_void_p,
-                                             c_void_p]),
+                                             c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64,
+                                             c_void_p, c_void_p]),
     "dlrmx_embbag_fwd_scatter_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
-                                             c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_void_p,
-                                             c_void_p]),
+                                             c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64,
+                                             c_void_p, c_void_p]),
     "dlrmx_bwd_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "dlrmx_bwd_sort_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p,
                                    c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -38,7 +38,7 @@ SIGNATURES = {
     "dlrmx_bwd_segments": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                    c_void_p]),
     "dlrmx_bwd_update_workspace_bytes": (c_size_t, [c_int64, c_int]),
-    "dlrmx_bwd_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int64,
+    "dlrmx_bwd_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_int64,
                                  c_int64, c_void_p, c_void_p, c_int64, c_float, c_float, c_void_p, c_size_t,
                                  c_void_p]),
     "dlrmx_bwd_coalesce": (c_int, [c_int, c_int, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,

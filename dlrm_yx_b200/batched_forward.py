@@ -71,7 +71,7 @@ def _forward_cuda(weights, table_offsets, offsets, indices, L_max, BT_block_size
             ptrs = _table_ptrs(w, toff)
             slot = out[:, d * T:(d + 1) * T, :]                        # peer stores when d is not dev0
             rc = lib.dlrmx_embbag_fwd_i32(ptrs.data_ptr(), 0, idx.contiguous().data_ptr(),
-                                          off.contiguous().data_ptr(), idx.numel(), T, B, D, 0,
+                                          off.contiguous().data_ptr(), idx.numel(), T, B, D, 0, 0,
                                           slot.data_ptr(), n * T * D, D, 0, st.cuda_stream)
             _lib.check(rc, "dlrmx_embbag_fwd_i32")
             ev = torch.cuda.Event()

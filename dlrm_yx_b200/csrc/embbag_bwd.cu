@@ -70,8 +70,8 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             gptr = P.grad + (int64_t)b * P.stride_b + (int64_t)t * P.stride_t;    // row start; col0 added after broadcast
             if (last) {
                 const int64_t row = (int64_t)key - P.row_base[t];
-                wptr = P.tables[t] + row * P.D;
-                if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mptr = P.moms[t] + row;
+                wptr = P.tables[t] + row * P.ld;
+                if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mptr = P.moms != nullptr ? P.moms[t] + row : wptr + P.D;
             }
         }
         const unsigned lastmask = (__ballot_sync(gmask, last) >> gshift);
@@ -95,13 +95,13 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                 if (v[j]) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
+                        if (col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
                 }
                 if (l[j]) {
                     wp[j] = bshfl64<float*, G>(gmask, wptr, jj & (G - 1)) + col0;
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < P.D) w[j][c].load(wp[j] + c * G * VEC);
+                        if (col0 + c * G * VEC < P.D) w[j][c].load(wp[j] + c * G * VEC);
                     if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
                         mp[j] = bshfl64<float*, G>(gmask, mptr, jj & (G - 1));
                         mo[j] = *mp[j];
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                 if (v[j]) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < P.D) {
+                        if (col0 + c * G * VEC < P.D) {
                             if (j == 0) g[0][c].add(acc[c]);
                             else if (!l[j > 0 ? j - 1 : 0]) g[j][c].add(g[j > 0 ? j - 1 : 0][c]);
                         }
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                         const float aj = a[j];
 #pragma unroll
                         for (int c = 0; c < CH; ++c)
-                            if (CH == 1 || col0 + c * G * VEC < P.D) {
+                            if (col0 + c * G * VEC < P.D) {
                                 w[j][c].map(g[j][c], [aj](float wv, float gv) { return __fmaf_rn(aj, gv, wv); });
                                 w[j][c].store(wp[j] + c * G * VEC);
                             }
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             const float* hp = sh_part + (size_t)v * P.D + col0;
 #pragma unroll
             for (int c = 0; c < CH; ++c)
-                if (CH == 1 || col0 + c * G * VEC < P.D) {
+                if (col0 + c * G * VEC < P.D) {
                     RowVec<VEC> h;
                     h.load(hp + c * G * VEC);
                     acc[c].add(h);
@@ -212,15 +212,15 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             const int bag = sbag[p1 - 1];
             const int t = bag / P.B;
             const int64_t row = (int64_t)key - P.row_base[t];
-            float* wp = P.tables[t] + row * P.D + col0;
+            float* wp = P.tables[t] + row * P.ld + col0;
             RowVec<VEC> w[CH];
 #pragma unroll
             for (int c = 0; c < CH; ++c)
-                if (CH == 1 || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
+                if (col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
             float* mp = nullptr;
             float mo = 0.f;
             if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-                mp = P.moms[t] + row;
+                mp = P.moms != nullptr ? P.moms[t] + row : P.tables[t] + row * P.ld + P.D;
                 mo = *mp;
             }
             apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
@@ -233,14 +233,14 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
             hacc[c].zero();
-            if (CH == 1 || col0 + c * G * VEC < P.D) hacc[c].load(sh_part + col0 + c * G * VEC);
+            if (col0 + c * G * VEC < P.D) hacc[c].load(sh_part + col0 + c * G * VEC);
         }
         if ((flags & kHeadClosed) == 0) {
             for (int v = 1; v < GPC && (sh_flag[v] & kActive); ++v) {
                 const float* hp = sh_part + (size_t)v * P.D + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < P.D) {
+                    if (col0 + c * G * VEC < P.D) {
                         RowVec<VEC> h;
                         h.load(hp + c * G * VEC);
                         hacc[c].add(h);
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
         const float* tp = P.tail_partial + seg * P.D + col0;
 #pragma unroll
         for (int c = 0; c < CH; ++c)
-            if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].load(tp + c * G * VEC);
+            if (col0 + c * G * VEC < P.D) acc[c].load(tp + c * G * VEC);
     }
     bool done = false;
     int64_t s = seg + 1;
@@ -306,14 +306,14 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
                     const float* hp = P.head_partial + (s + q0 + j) * P.D + col0;
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < P.D) h[j][c].load(hp + c * G * VEC);
+                        if (col0 + c * G * VEC < P.D) h[j][c].load(hp + c * G * VEC);
                 }
 #pragma unroll
             for (int j = 0; j < KF; ++j)
                 if (q0 + j < cnt) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (CH == 1 || col0 + c * G * VEC < P.D) acc[c].add(h[j][c]);
+                        if (col0 + c * G * VEC < P.D) acc[c].add(h[j][c]);
                 }
         }
         s += cnt;
@@ -321,15 +321,15 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
     const int bag = P.sbag[p1 - 1];
     const int t = bag / P.B;
     const int64_t row = (int64_t)key - P.row_base[t];
-    float* wp = P.tables[t] + row * P.D + col0;
+    float* wp = P.tables[t] + row * P.ld + col0;
     RowVec<VEC> w[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c)
-        if (CH == 1 || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
+        if (col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
     float* mp = nullptr;
     float mo = 0.f;
     if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-        mp = P.moms[t] + row;
+        mp = P.moms != nullptr ? P.moms[t] + row : P.tables[t] + row * P.ld + P.D;
         mo = *mp;
     }
     apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
@@ -360,20 +360,20 @@ bwd_coalesce_kernel(int B, int D, const float* __restrict__ grad, int64_t stride
                 const float* gp = grad + (int64_t)b * stride_b + (int64_t)t * stride_t + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < D) g[j][c].load_ro(gp + c * G * VEC);
+                    if (col0 + c * G * VEC < D) g[j][c].load_ro(gp + c * G * VEC);
             }
 #pragma unroll
         for (int j = 0; j < K; ++j)
             if (pb + j < p1) {
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
-                    if (CH == 1 || col0 + c * G * VEC < D) acc[c].add(g[j][c]);
+                    if (col0 + c * G * VEC < D) acc[c].add(g[j][c]);
             }
     }
     float* o = gsum + u * D + col0;
 #pragma unroll
     for (int c = 0; c < CH; ++c)
-        if (CH == 1 || col0 + c * G * VEC < D) acc[c].store(o + c * G * VEC);
+        if (col0 + c * G * VEC < D) acc[c].store(o + c * G * VEC);
 }
 
 
@@ -391,13 +391,13 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
     const int col0 = gl * VEC;
     const int64_t row = rows[u];
     BwdParams P;
-    P.optimizer = optimizer; P.D = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
+    P.optimizer = optimizer; P.D = D; P.ld = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
     RowVec<VEC> g[CH], w[CH];
     float* wp = W + row * D + col0;
     const float* gp = gsum + u * D + col0;
 #pragma unroll
     for (int c = 0; c < CH; ++c)
-        if (CH == 1 || col0 + c * G * VEC < D) {
+        if (col0 + c * G * VEC < D) {
             g[c].load_ro(gp + c * G * VEC);
             w[c].load(wp + c * G * VEC);
         } else {
@@ -492,18 +492,21 @@ extern "C" {
 size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D) { return dlrmx::update_workspace_bytes(N, D); }
 
 int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, const int64_t* table_row_base,
-                     int T, int B, int D, const float* grad, int64_t stride_b, int64_t stride_t,
+                     int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
                      const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, float lr, float eps,
                      void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || optimizer == DLRMX_OPT_RWSADAGRAD, "bwd_update: bad optimizer %d", optimizer);
-    DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || moms != nullptr, "bwd_update: rwsadagrad needs accumulators");
+    const int64_t ld = table_ld > 0 ? table_ld : D;
+    DLRMX_REQUIRE(ld >= D, "bwd_update: table_ld must be >= D");
+    DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || moms != nullptr || ld > D,
+                  "bwd_update: rwsadagrad needs accumulators (moms, or a padded row with table_ld > D)");
     DLRMX_REQUIRE(N >= 0 && N < (1ll << 31) && T >= 0 && B > 0, "bwd_update: bad sizes");
     RowGeom g;
     DLRMX_REQUIRE(row_geometry(D, &g), "bwd_update: unsupported D=%d", D);
     if (g.vec == 4)
-        DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && ((uintptr_t)grad & 15) == 0,
-                      "bwd_update: grad must be 16-B aligned with strides multiple of 4 when D%%4==0");
+        DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && ((uintptr_t)grad & 15) == 0 && ld % 4 == 0,
+                      "bwd_update: grad must be 16-B aligned with strides (and table_ld) multiple of 4 when D%%4==0");
     if (N == 0) return DLRMX_OK;
     if (workspace_bytes < update_workspace_bytes(N, D)) {
         set_error("bwd_update: workspace %zu < %zu", workspace_bytes, update_workspace_bytes(N, D));
@@ -511,7 +514,7 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     }
     BwdParams P;
     P.optimizer = optimizer; P.tables = tables; P.moms = moms; P.row_base = table_row_base;
-    P.B = B; P.D = D; P.grad = grad; P.stride_b = stride_b; P.stride_t = stride_t;
+    P.B = B; P.D = D; P.ld = ld; P.grad = grad; P.stride_b = stride_b; P.stride_t = stride_t;
     P.skey = sorted_key; P.sbag = sorted_bag; P.N = N; P.seg_len = seg_len_for(N, optimizer); P.nseg = ceil_div(N, (int64_t)P.seg_len);
     P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
     P.head_partial = (float*)workspace;

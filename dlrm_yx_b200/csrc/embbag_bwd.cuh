@@ -31,6 +31,8 @@ struct BwdParams {
     float* const* moms;
     const int64_t* row_base;
     int B, D;
+    int64_t ld;           // row pitch of the tables in floats (>= D); the row-wise accumulator of a row may live in its
+                          // padding (moms == nullptr: column D of the row), i.e. in the DRAM page the update opens anyway
     const float* grad;
     int64_t stride_b, stride_t;
     const uint32_t* skey;
@@ -72,7 +74,7 @@ __device__ __forceinline__ void apply_row(const BwdParams& P, float* wp, float* 
         const float a = -P.lr;
 #pragma unroll
         for (int c = 0; c < CH; ++c)
-            if (CH == 1 || col0 + c * G * VEC < P.D) {
+            if (col0 + c * G * VEC < P.D) {
                 w[c].map(acc[c], [a](float wv, float gv) { return __fmaf_rn(a, gv, wv); });
                 w[c].store(wp + c * G * VEC);
             }
@@ -91,7 +93,7 @@ __device__ __forceinline__ void apply_row(const BwdParams& P, float* wp, float* 
         const float a = adagrad_step(P.lr, mom, P.eps);
 #pragma unroll
         for (int c = 0; c < CH; ++c)
-            if (CH == 1 || col0 + c * G * VEC < P.D) {
+            if (col0 + c * G * VEC < P.D) {
                 w[c].map(acc[c], [a](float wv, float gv) { return __fmaf_rn(a, gv, wv); });
                 w[c].store(wp + c * G * VEC);
             }
@@ -105,6 +107,6 @@ __device__ __forceinline__ void store_partial(float* base, int64_t seg, int D, i
     float* p = base + seg * D + col0;
 #pragma unroll
     for (int c = 0; c < CH; ++c)
-        if (CH == 1 || col0 + c * G * VEC < D) acc[c].store(p + c * G * VEC);
+        if (col0 + c * G * VEC < D) acc[c].store(p + c * G * VEC);
 }
 }  // namespace dlrmx

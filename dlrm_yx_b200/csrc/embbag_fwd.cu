@@ -53,7 +53,7 @@ template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typenam
 __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2)))
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
-                  int B, int D, int64_t total_bags, const float* __restrict__ psw,
+                  int B, int D, int64_t ld, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
                   float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len) {
     constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
@@ -139,10 +139,10 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                         live[k][u] = false;
                     }
                     if (live[k][u]) {
-                        const float* p = base[k] + (int64_t)ix[k][u] * D + col0;
+                        const float* p = base[k] + (int64_t)ix[k][u] * ld + col0;
 #pragma unroll
                         for (int c = 0; c < CH; ++c)
-                            if (CH == 1 || col0 + c * G * VEC < D) row[k][u][c].load_stream(p + c * G * VEC);
+                            if (col0 + c * G * VEC < D) row[k][u][c].load_stream(p + c * G * VEC);
                     }
                 }
             // request the next rounds' indices before this round's rows are consumed
@@ -160,12 +160,12 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                         if (psw == nullptr) {
 #pragma unroll
                             for (int c = 0; c < CH; ++c)
-                                if (CH == 1 || col0 + c * G * VEC < D) acc[k][c].add(row[k][u][c]);
+                                if (col0 + c * G * VEC < D) acc[k][c].add(row[k][u][c]);
                         } else {
                             const float w = __ldg(psw + start[k] + r + u);
 #pragma unroll
                             for (int c = 0; c < CH; ++c)
-                                if (CH == 1 || col0 + c * G * VEC < D) acc[k][c].add_scaled(row[k][u][c], w);
+                                if (col0 + c * G * VEC < D) acc[k][c].add_scaled(row[k][u][c], w);
                         }
                     }
 #pragma unroll
@@ -195,7 +195,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
 
 template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
-                      const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
+                      const IdxT* offsets, int64_t N, int T, int B, int D, int64_t ld, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
                       int mb_len, cudaStream_t st) {
     const bool windowed = out_peers != nullptr && mb_len < lb;
@@ -207,18 +207,18 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     if (blocks == 0) return DLRMX_OK;
     if (out_peers != nullptr)
         embbag_fwd_kernel<VEC, G, CH, K, U, FULL, true, IdxT, OCC><<<(unsigned)blocks, threads, 0, st>>>(
-            tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
+            tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag,
             out_peers, lb, mb_off, mb_len);
     else
         embbag_fwd_kernel<VEC, G, CH, K, U, FULL, false, IdxT, OCC><<<(unsigned)blocks, threads, 0, st>>>(
-            tables, table_rows, indices, offsets, N, B, D, total_bags, psw, out, stride_b, stride_t, err_flag,
+            tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag,
             nullptr, 1, 0, 1);
     return check_launch("embbag_fwd");
 }
 
 template <typename IdxT>
 static int embbag_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
-                      const IdxT* offsets, int64_t N, int T, int B, int D, const float* psw, float* out,
+                      const IdxT* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
                       int mb_len, dlrmx_stream_t stream) {
     DLRMX_REQUIRE(T >= 0 && B >= 0 && N >= 0, "embbag_fwd: negative size");
@@ -228,6 +228,8 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     DLRMX_REQUIRE((int64_t)T * B < (1ll << 31), "embbag_fwd: T*B must be < 2^31");
     RowGeom g;
     DLRMX_REQUIRE(row_geometry(D, &g), "embbag_fwd: unsupported D=%d (need D<=512 if D%%4==0, else D<=128)", D);
+    const int64_t ld = table_ld > 0 ? table_ld : D;      // row pitch of the tables in floats
+    DLRMX_REQUIRE(ld >= D && (g.vec != 4 || ld % 4 == 0), "embbag_fwd: table_ld must be >= D (and a multiple of 4 when D%%4==0)");
     if (g.vec == 4)
         DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && (out_peers != nullptr || ((uintptr_t)out & 15) == 0),
                       "embbag_fwd: out must be 16-B aligned with strides multiple of 4 when D%%4==0");
@@ -238,7 +240,7 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     const bool short_bags = N <= 2 * (int64_t)T * B;
     const int tune = get_tunable(DLRMX_TUNE_FWD_K);
 #define DLRMX_FWD_ARGS \
-    tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, \
+    tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, \
         mb_len, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                  \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                   \
@@ -247,16 +249,18 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
             return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);       \
         }                                                                                              \
         /* long bags, measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the bags /  */ \
-        /* 512-byte rows): ONE bag per group with 8 of its rows in flight wins everywhere -- 0.61 / 0.76 / 0.98 against   */ \
-        /* 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128 registers, 2 CTAs per SM, half as many work units  */ \
-        /* for the launch's tail).  An L2 bulk prefetch ahead of the walk (cp.async.bulk.prefetch.L2, lane-parallel)     */ \
-        /* and a two-round register double buffer were tried and were slower.  FWD_K tunable: 1/2/3 one bag per group at */ \
-        /* 4 / 3 CTAs per SM / 16 rows in flight, 8 and 4: the older two-bag variants.                                    */ \
+        /* 512-byte rows): ONE bag per group with 8 of its rows in flight at 3 CTAs per SM (72-74 registers, no spills)   */ \
+        /* wins everywhere -- 0.60 / 0.76 / 0.99 against 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128      */ \
+        /* registers, 2 CTAs per SM, half as many work units for the launch's tail), 0.57 / 0.67 / 0.56 when squeezed to  */ \
+        /* 64 registers for 4 CTAs per SM (spills) and 0.56 / 0.67 / 0.84 with 16 rows in flight.  An L2 bulk prefetch    */ \
+        /* ahead of the walk (cp.async.bulk.prefetch.L2, lane-parallel) and a two-round register double buffer were tried */ \
+        /* and were slower.  FWD_K tunable: 2 / 3: one bag per group at 4 CTAs per SM / 16 rows in flight; 8 / 4: the     */ \
+        /* older two-bag variants.                                                                                        */ \
         if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS);  \
         if (CH_ == 1 && tune == 4) return launch_fwd<VEC_, G_, CH_, 2, 4, false, IdxT>(DLRMX_FWD_ARGS);  \
-        if (CH_ == 1 && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 3>(DLRMX_FWD_ARGS); \
+        if (CH_ == 1 && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS); \
         if (CH_ == 1 && tune == 3) return launch_fwd<VEC_, G_, CH_, 1, 16, false, IdxT, 2>(DLRMX_FWD_ARGS); \
-        if (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS);            \
+        if (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 3>(DLRMX_FWD_ARGS);            \
         return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3>(DLRMX_FWD_ARGS);          \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
@@ -272,36 +276,36 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
 
 extern "C" {
 int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
-                         const int32_t* offsets, int64_t N, int T, int B, int D, const float* psw,
+                         const int32_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
-    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b,
+    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw, out, stride_b,
                                       stride_t, err_flag, nullptr, 0, 0, 0, stream);
 }
 int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
-                         const int64_t* offsets, int64_t N, int T, int B, int D, const float* psw,
+                         const int64_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
-    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw, out, stride_b,
+    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw, out, stride_b,
                                       stride_t, err_flag, nullptr, 0, 0, 0, stream);
 }
 int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
-                                 const int32_t* offsets, int64_t N, int T, int B, int D, const float* psw,
+                                 const int32_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
                                  float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
                                  int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
-    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
+    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw,
                                       nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
                                       mb_len, stream);
 }
 int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
-                                 const int64_t* offsets, int64_t N, int T, int B, int D, const float* psw,
+                                 const int64_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
                                  float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
                                  int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
-    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, psw,
+    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw,
                                       nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
                                       mb_len, stream);
 }

@@ -64,9 +64,12 @@ class TableSet:
     SURVEY.md section 5) -- the arrays are rebuilt whenever a tensor's storage moves.
     """
 
-    def __init__(self, weights, moms=None):
+    def __init__(self, weights, moms=None, acc_in_row=False):
         self.weights = list(weights)
         self.moms = None if moms is None else list(moms)
+        # padded rows (row pitch ld > D, e.g. views [:, :D] of a [rows, D+4] allocation): the row-wise Adagrad
+        # accumulator of a row may live in the float right after it (acc_in_row) instead of in a separate array
+        self.acc_in_row = bool(acc_in_row)
         self._key = None
         self.refresh()
 
@@ -77,9 +80,14 @@ class TableSet:
             return
         _need_cuda(*ws)
         D = ws[0].shape[1]
+        ld = ws[0].stride(0) if ws[0].shape[0] > 1 else D
         for w in ws:
-            if w.dtype != torch.float32 or w.dim() != 2 or w.shape[1] != D or not w.is_contiguous():
-                raise _lib.DlrmxError("tables must be contiguous fp32 [rows, D] with a common D")
+            if w.dtype != torch.float32 or w.dim() != 2 or w.shape[1] != D or w.stride(1) != 1 or \
+                    (w.shape[0] > 1 and w.stride(0) != ld):
+                raise _lib.DlrmxError("tables must be row-major fp32 [rows, D] with a common D and a common row pitch")
+        if ld < D or (self.acc_in_row and ld <= D):
+            raise _lib.DlrmxError("bad table row pitch %d for D=%d (acc_in_row needs padded rows)" % (ld, D))
+        self.ld = int(ld)
         dev = ws[0].device
         self.device, self.D, self.T = dev, D, len(ws)
         rows = [int(w.shape[0]) for w in ws]
@@ -122,7 +130,7 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_" + _idx_suffix(indices, offsets))
     with _timed("embbag_fwd"):
         rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0,
-                indices.data_ptr(), offsets.data_ptr(), indices.numel(), T, B, D, _ptr(per_sample_weights),
+                indices.data_ptr(), offsets.data_ptr(), indices.numel(), T, B, D, tables.ld, _ptr(per_sample_weights),
                 out.data_ptr(), stride_b, stride_t, _ptr(err_flag), _stream())
         _lib.check(rc, "dlrmx_embbag_fwd")
     return out
@@ -146,8 +154,8 @@ def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b,
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_scatter_" + _idx_suffix(indices, offsets))
     with _timed("embbag_fwd"):
         rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0, indices.data_ptr(),
-                offsets.data_ptr(), indices.numel(), T, B, D, 0, out_peers.data_ptr(), lb, mb_off, mb_len, stride_b,
-                stride_t, 0, _stream())
+                offsets.data_ptr(), indices.numel(), T, B, D, tables.ld, 0, out_peers.data_ptr(), lb, mb_off, mb_len,
+                stride_b, stride_t, 0, _stream())
         _lib.check(rc, "dlrmx_embbag_fwd_scatter")
 
 
@@ -197,13 +205,14 @@ def bwd_update(tables, optimizer, grad, stride_b, stride_t, B, skey, sbag, lr, e
     _need_cuda(grad, skey, sbag)
     N = skey.numel()
     lib = _lib.load()
-    if optimizer == _lib.OPT_RWSADAGRAD and tables.mom_ptrs is None:
-        raise _lib.DlrmxError("RWSAdagrad update needs row-wise accumulators (TableSet(moms=...))")
+    if optimizer == _lib.OPT_RWSADAGRAD and tables.mom_ptrs is None and not tables.acc_in_row:
+        raise _lib.DlrmxError("RWSAdagrad update needs row-wise accumulators (TableSet(moms=...) or acc_in_row)")
     wsb = lib.dlrmx_bwd_update_workspace_bytes(N, tables.D)
     ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=tables.device)
     with _timed("bwd_update"):
-        rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(), _ptr(tables.mom_ptrs),
-                                  tables.row_base.data_ptr(), tables.T, B, tables.D, grad.data_ptr(), stride_b,
+        rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(),
+                                  0 if tables.acc_in_row else _ptr(tables.mom_ptrs),
+                                  tables.row_base.data_ptr(), tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b,
                                   stride_t, skey.data_ptr(), sbag.data_ptr(), N, float(lr), float(eps),
                                   ws.data_ptr(), wsb, _stream())
         _lib.check(rc, "dlrmx_bwd_update")

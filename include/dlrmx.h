@@ -62,6 +62,8 @@ int dlrmx_set_tunable(int which, int value);
  *   tables      [T] device array of row-major fp32 table base pointers ([rows_t, D] each, 16-B aligned
  *               when D % 4 == 0)
  *   table_rows  [T] device int64 row counts, or NULL to skip index validation
+ *   table_ld    row pitch of the tables in floats (0 = D).  A pitch > D leaves padding after every row; the
+ *               fused update can keep the row-wise Adagrad accumulator there (see dlrmx_bwd_update)
  *   indices     [N] row ids local to their table; offsets [>= T*B] bag starts (see conventions)
  *   psw         [N] per-sample weights (dlrm_s_pytorch.py:544-547) or NULL
  *   out         pooled rows, fp32, written for every bag (empty bag -> zeros)
@@ -70,12 +72,12 @@ int dlrmx_set_tunable(int which, int value);
  * ------------------------------------------------------------------------------------------- */
 int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows,
                          const int32_t* indices, const int32_t* offsets, int64_t N,
-                         int T, int B, int D, const float* psw,
+                         int T, int B, int D, int64_t table_ld, const float* psw,
                          float* out, int64_t stride_b, int64_t stride_t,
                          int* err_flag, dlrmx_stream_t stream);
 int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows,
                          const int64_t* indices, const int64_t* offsets, int64_t N,
-                         int T, int B, int D, const float* psw,
+                         int T, int B, int D, int64_t table_ld, const float* psw,
                          float* out, int64_t stride_b, int64_t stride_t,
                          int* err_flag, dlrmx_stream_t stream);
 
@@ -119,14 +121,18 @@ int dlrmx_bwd_segments(const uint32_t* sorted_key, int64_t N,
  * RWSAdagrad.step's sparse branch (optim/rwsadagrad.py:97-113).
  *   grad        gradient of the pooled rows, addressed like `out` of the forward
  *   psw         per-sample weights [N] indexed by ORIGINAL position -- not supported when fused: NULL
- *   moms        [T] device array of row-wise accumulator pointers ([rows_t] fp32), RWSADAGRAD only
+ *   moms        [T] device array of row-wise accumulator pointers ([rows_t] fp32), RWSADAGRAD only; NULL with
+ *               table_ld > D: the accumulator of a row is the float right after it (column D of the padded
+ *               row), i.e. in the DRAM page the row update opens anyway -- the separate 4-byte accumulator
+ *               arrays of optim/rwsadagrad.py:72-78 cost a DRAM access per row as expensive as the row itself
+ *   table_ld    row pitch of the tables in floats (0 = D)
  *   lr          SGD: lr.  RWSADAGRAD: clr = lr / (1 + (step-1)*lr_decay), computed by the caller
  * Deterministic: each run is summed in sorted (stable) order; runs longer than one 32-position
  * segment are reduced per segment and the segment partials added in ascending order.
  * ------------------------------------------------------------------------------------------- */
 size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D);
 int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms,
-                     const int64_t* table_row_base, int T, int B, int D,
+                     const int64_t* table_row_base, int T, int B, int D, int64_t table_ld,
                      const float* grad, int64_t stride_b, int64_t stride_t,
                      const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N,
                      float lr, float eps,
@@ -238,12 +244,12 @@ int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
  * ------------------------------------------------------------------------------------------- */
 int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows,
                                  const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
-                                 int D, const float* per_sample_weights, float* const* out_peers, int lb,
+                                 int D, int64_t table_ld, const float* per_sample_weights, float* const* out_peers, int lb,
                                  int mb_off, int mb_len, int64_t stride_b, int64_t stride_t, int* err_flag,
                                  dlrmx_stream_t stream);
 int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows,
                                  const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
-                                 int D, const float* per_sample_weights, float* const* out_peers, int lb,
+                                 int D, int64_t table_ld, const float* per_sample_weights, float* const* out_peers, int lb,
                                  int mb_off, int mb_len, int64_t stride_b, int64_t stride_t, int* err_flag,
                                  dlrmx_stream_t stream);
 int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,

@@ -39,13 +39,13 @@ def test_every_declared_symbol_is_exported_and_bound():
 def test_argument_errors_are_reported_not_crashed():
     lib = _lib.load()
     # unsupported D is rejected before any launch, with a message
-    rc = lib.dlrmx_embbag_fwd_i32(0, 0, 0, 0, 0, 1, 1, 5000, 0, 0, 0, 0, 0, 0)
+    rc = lib.dlrmx_embbag_fwd_i32(0, 0, 0, 0, 0, 1, 1, 5000, 0, 0, 0, 0, 0, 0, 0)
     assert rc == -1
     assert b"unsupported D" in lib.dlrmx_last_error()
     assert lib.dlrmx_set_tunable(99, 1) == -1
     assert lib.dlrmx_bwd_sort_workspace_bytes(1 << 20, 1 << 10) > (1 << 23)
     # empty problems succeed without touching the device
-    assert lib.dlrmx_embbag_fwd_i64(0, 0, 0, 0, 0, 0, 0, 128, 0, 0, 0, 0, 0, 0) == 0
+    assert lib.dlrmx_embbag_fwd_i64(0, 0, 0, 0, 0, 0, 0, 128, 0, 0, 0, 0, 0, 0, 0) == 0
 
 
 def test_no_cpu_fallback():

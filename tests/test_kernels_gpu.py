@@ -172,7 +172,7 @@ def test_sort_and_segments_bit_exact(rows, B, max_len, hot, dtype):
     assert np.array_equal(run_off.cpu().numpy()[:U + 1].astype(np.int64), art["run_off"])
 
 
-@pytest.mark.parametrize("D", [128, 64, 16, 2])
+@pytest.mark.parametrize("D", [128, 64, 16, 2, 96, 6, 3, 200])     # 96 / 6 / 3 / 200: lanes beyond the row must stay idle
 @pytest.mark.parametrize("opt", ["sgd", "rwsadagrad"])
 def test_fused_backward_update(D, opt):
     from dlrm_yx_b200 import ops, _lib
@@ -221,6 +221,51 @@ def test_fused_backward_update(D, opt):
     gs = ops.bwd_coalesce(dg, T * D, D, B, D, sbag, run_off, nu)
     U = int(nu.item())
     np.testing.assert_allclose(gs.cpu().numpy()[:U], g, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("D,pad", [(128, 4), (64, 4), (16, 8), (6, 1)])
+@pytest.mark.parametrize("opt", ["sgd", "rwsadagrad"])
+def test_padded_rows_accumulator_in_row_bit_identical(D, pad, opt):
+    """Tables with a row pitch of D + pad floats and the row-wise Adagrad accumulator stored in the first padding
+    float of its row (TableSet(acc_in_row=True)): lookup, update and accumulators are bit-identical to the contiguous
+    layout with separate accumulator arrays -- only the addresses differ."""
+    from dlrm_yx_b200 import ops, _lib
+    dev = cuda()
+    rng = np.random.default_rng(D + pad)
+    rows, B = [400, 3, 1, 90, 2000], 300
+    T = len(rows)
+    Ws, idx, off = make_case(rng, rows, D, B, max_len=4, empty_frac=0.1)
+    moms_np = [rng.uniform(0, 0.5, size=r).astype(np.float32) for r in rows]
+    di, do = torch.from_numpy(idx).to(dev).to(torch.int32), torch.from_numpy(off).to(dev).to(torch.int32)
+    dg = torch.from_numpy(rng.normal(size=(B, T, D)).astype(np.float32)).to(dev)
+    code = _lib.OPT_SGD if opt == "sgd" else _lib.OPT_RWSADAGRAD
+    # contiguous layout
+    tw = [torch.from_numpy(w.copy()).to(dev) for w in Ws]
+    tm = [torch.from_numpy(m.copy()).to(dev) for m in moms_np]
+    ts = ops.TableSet(tw, moms=tm)
+    out0 = ops.embbag_forward(ts, di, do, B)
+    skey, sbag = ops.bwd_sort(ts, di, do, B)
+    ops.bwd_update(ts, code, dg, T * D, D, B, skey, sbag, 0.1, 1e-10)
+    # padded layout
+    full = [torch.full((r, D + pad), 7.0, device=dev) for r in rows]
+    for f, w, m in zip(full, Ws, moms_np):
+        f[:, :D] = torch.from_numpy(w).to(dev)
+        f[:, D] = torch.from_numpy(m).to(dev)
+    tp = ops.TableSet([f[:, :D] for f in full], acc_in_row=True)
+    assert tp.ld == D + pad
+    out1 = ops.embbag_forward(tp, di, do, B)
+    assert torch.equal(out0, out1)
+    sk1, sb1 = ops.bwd_sort(tp, di, do, B)
+    assert torch.equal(skey, sk1) and torch.equal(sbag, sb1)
+    ops.bwd_update(tp, code, dg, T * D, D, B, sk1, sb1, 0.1, 1e-10)
+    for f, w, m, m0 in zip(full, tw, tm, moms_np):
+        assert torch.equal(f[:, :D], w)
+        if opt == "rwsadagrad":
+            assert torch.equal(f[:, D], m)
+        else:
+            assert np.array_equal(f[:, D].cpu().numpy(), m0)
+        if pad > 1:
+            assert bool((f[:, D + 1:] == 7.0).all())          # the rest of the padding is never touched
 
 
 @pytest.mark.parametrize("D", [128, 64, 8])

@@ -68,6 +68,7 @@ def main():
     ap.add_argument("--gstride", type=int, default=0, help="gradient laid out [B, gstride, D] (features 1..T used)")
     ap.add_argument("--only", default="")
     ap.add_argument("--gscale", type=float, default=1.0)
+    ap.add_argument("--pad", type=int, default=0, help="floats of padding after every table row (accumulator in the row)")
     args = ap.parse_args()
     cfg = SHAPES[args.shape]
     rows = [min(r, args.rows_cap) if args.rows_cap else r for r in cfg["rows"]]
@@ -76,9 +77,16 @@ def main():
     dev = torch.device("cuda:0")
     torch.manual_seed(1)
     t0 = time.time()
-    tw = [torch.empty((r, D), device=dev).uniform_(-(1.0 / r) ** 0.5, (1.0 / r) ** 0.5) for r in rows]
-    tm = [torch.zeros(r, device=dev) for r in rows]
-    ts = ops.TableSet(tw, moms=tm)
+    if args.pad:
+        full = [torch.zeros((r, D + args.pad), device=dev) for r in rows]
+        tw = [f[:, :D] for f in full]
+        for w, r in zip(tw, rows):
+            w.uniform_(-(1.0 / r) ** 0.5, (1.0 / r) ** 0.5)
+        ts = ops.TableSet(tw, acc_in_row=True)
+    else:
+        tw = [torch.empty((r, D), device=dev).uniform_(-(1.0 / r) ** 0.5, (1.0 / r) ** 0.5) for r in rows]
+        tm = [torch.zeros(r, device=dev) for r in rows]
+        ts = ops.TableSet(tw, moms=tm)
     idt = torch.int64 if args.idx64 else torch.int32
     # several distinct batches so consecutive iterations touch different rows (inputs exceed L2 anyway)
     nbatch = 4
@@ -103,7 +111,7 @@ def main():
     it = [0]
 
     def report(name, ms, mn, nbytes, extra=None):
-        d = dict(kernel=name, shape=args.shape, ms=round(ms, 4), ms_min=round(mn, 4),
+        d = dict(kernel=name, shape=args.shape, pad=args.pad, ms=round(ms, 4), ms_min=round(mn, 4),
                  gbs=round(nbytes / ms / 1e6, 1), frac=round(nbytes / ms / 1e6 / peak, 3), peak=src)
         if extra:
             d.update(extra)
