@@ -396,6 +396,73 @@ def workload_name(args, cfg, W, B_global):
     return "%s, global batch %d, %s" % (base, B_global, args.optimizer)
 
 
+def embbag_c3_probe(peak, iters=20):
+    """BASELINE.json configs[2] (bench/dlrm_s_benchmark.sh:36-42: 8 tables x 1M rows, D=64, 100 indices per lookup,
+    batch 2048, SGD) as a kernel-level line: the bandwidth-bound embedding-bag of metric (ii), timed with CUDA events,
+    4 rotating batches, 2 GB of tables (>> L2).  Algorithmic bytes as in DESIGN.md section 4."""
+    from dlrm_yx_b200 import _lib, ops
+    dev = torch.device("cuda", torch.cuda.current_device())
+    T, R, D, B, L = 8, 1000000, 64, 2048, 100
+    sampler = ClockSampler(torch.cuda.current_device())
+    sampler.start()
+    g = torch.Generator(device=dev)
+    g.manual_seed(727)
+    tw = [torch.empty((R, D), device=dev).uniform_(-(1.0 / R) ** 0.5, (1.0 / R) ** 0.5, generator=g) for _ in range(T)]
+    ts = ops.TableSet(tw)
+    N = T * B * L
+    batches = []
+    for _ in range(4):     # the reference draws L distinct sorted ids per bag (dlrm_data_pytorch.py:1195-1208)
+        idx = torch.sort(torch.randint(0, R, (T * B, L), device=dev, generator=g), dim=1)[0].reshape(-1).to(torch.int32)
+        batches.append((idx, (torch.arange(T * B + 1, device=dev) * L).to(torch.int32)))
+    out = torch.empty((B, T, D), device=dev)
+    grad = torch.randn((B, T, D), device=dev, generator=g)
+    it = [0]
+
+    def timed(fn):
+        for _ in range(10):
+            fn()
+        torch.cuda.synchronize()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+        for s_, e_ in evs:
+            s_.record()
+            fn()
+            e_.record()
+        torch.cuda.synchronize()
+        ms = sorted(a.elapsed_time(b) for a, b in evs)
+        return ms[len(ms) // 2]
+
+    def fwd():
+        idx, off = batches[it[0] % 4]
+        it[0] += 1
+        ops.embbag_forward(ts, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=False)
+    ms_f = timed(fwd)
+    srt = [ops.bwd_sort(ts, idx, off, B) for idx, off in batches]
+    U = sum(int(ops.bwd_segments(sk)[2].item()) for sk, _ in srt) / 4.0
+
+    def sort():
+        idx, off = batches[it[0] % 4]
+        it[0] += 1
+        ops.bwd_sort(ts, idx, off, B)
+    ms_s = timed(sort)
+
+    def upd():
+        sk, sb = srt[it[0] % 4]
+        it[0] += 1
+        ops.bwd_update(ts, _lib.OPT_SGD, grad, T * D, D, B, sk, sb, 0.01, 0.0)
+    ms_u = timed(upd)
+    fb = N * D * 4 + N * 4 + T * B * 4 + T * B * D * 4
+    ub = T * B * D * 4 + N * 8 + 2 * U * D * 4
+    res = {"workload": "dlrm_s_benchmark.sh shape: 8 tables x 1M rows, dim 64, 100 indices/lookup, batch 2048, SGD",
+           "embbag_fwd": {"ms": round(ms_f, 4), "algorithmic_MB": round(fb / 1e6, 1), "GBps": round(fb / ms_f / 1e6, 1),
+                          "frac": round(fb / ms_f / 1e6 / peak, 4)},
+           "bwd_sort": {"ms": round(ms_s, 4)},
+           "bwd_update": {"ms": round(ms_u, 4), "algorithmic_MB": round(ub / 1e6, 1), "GBps": round(ub / ms_u / 1e6, 1),
+                          "frac": round(ub / ms_u / 1e6 / peak, 4), "unique_rows": int(U)}}
+    res["clocks"] = sampler.stop()
+    del tw, ts, batches, srt, out, grad
+    return res
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -480,6 +547,11 @@ def main():
         "launch_mode": "cuda-graph (whole step)" if r["use_graph"] else "eager",
         "kernels": kern,
     }
+    if W == 1 and args.config == "terabyte":
+        try:
+            line["embedding_bag_c3"] = embbag_c3_probe(peak)
+        except Exception as ex:                       # the probe must never cost the headline line
+            line["embedding_bag_c3"] = {"error": repr(ex)}
     if W == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_reference(args, args.cpu_steps)[0]
     print(json.dumps(line), flush=True)

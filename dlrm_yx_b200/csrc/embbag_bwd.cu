@@ -24,8 +24,9 @@ __device__ __forceinline__ T bshfl64(unsigned mask, T v, int src) {
 // are 256/G times shorter than with per-segment partials.
 enum { kHasHead = 1, kHeadClosed = 2, kHasTail = 4, kActive = 8 };
 
-template <int VEC, int G, int CH, int K>
-__global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(const BwdParams P) {
+// EXACT: D == VEC*G*CH, every lane owns columns of the row (no per-lane guard in the loop).
+template <int VEC, int G, int CH, int K, int OCC = 0, bool EXACT = false>
+__global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) bwd_update_kernel(const BwdParams P) {
     constexpr int GPC = 256 / G;             // groups (= segments) per CTA
     extern __shared__ __align__(16) float sh_part[];     // [2][GPC][D]: head partials, tail partials
     __shared__ unsigned char sh_flag[GPC];
@@ -95,13 +96,13 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                 if (v[j]) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
+                        if (EXACT || col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
                 }
                 if (l[j]) {
                     wp[j] = bshfl64<float*, G>(gmask, wptr, jj & (G - 1)) + col0;
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (col0 + c * G * VEC < P.D) w[j][c].load(wp[j] + c * G * VEC);
+                        if (EXACT || col0 + c * G * VEC < P.D) w[j][c].load(wp[j] + c * G * VEC);
                     if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
                         mp[j] = bshfl64<float*, G>(gmask, mptr, jj & (G - 1));
                         mo[j] = *mp[j];
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                 if (v[j]) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (col0 + c * G * VEC < P.D) {
+                        if (EXACT || col0 + c * G * VEC < P.D) {
                             if (j == 0) g[0][c].add(acc[c]);
                             else if (!l[j > 0 ? j - 1 : 0]) g[j][c].add(g[j > 0 ? j - 1 : 0][c]);
                         }
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                     if (l[j]) {
 #pragma unroll
                         for (int c = 0; c < CH; ++c)
-                            if (col0 + c * G * VEC < P.D) ss[j] = __fadd_rn(ss[j], g[j][c].sumsq());
+                            if (EXACT || col0 + c * G * VEC < P.D) ss[j] = __fadd_rn(ss[j], g[j][c].sumsq());
                     }
                 }
 #pragma unroll
@@ -158,7 +159,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
                         const float aj = a[j];
 #pragma unroll
                         for (int c = 0; c < CH; ++c)
-                            if (col0 + c * G * VEC < P.D) {
+                            if (EXACT || col0 + c * G * VEC < P.D) {
                                 w[j][c].map(g[j][c], [aj](float wv, float gv) { return __fmaf_rn(aj, gv, wv); });
                                 w[j][c].store(wp[j] + c * G * VEC);
                             }
@@ -200,7 +201,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             const float* hp = sh_part + (size_t)v * P.D + col0;
 #pragma unroll
             for (int c = 0; c < CH; ++c)
-                if (col0 + c * G * VEC < P.D) {
+                if (EXACT || col0 + c * G * VEC < P.D) {
                     RowVec<VEC> h;
                     h.load(hp + c * G * VEC);
                     acc[c].add(h);
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
             RowVec<VEC> w[CH];
 #pragma unroll
             for (int c = 0; c < CH; ++c)
-                if (col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
+                if (EXACT || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
             float* mp = nullptr;
             float mo = 0.f;
             if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
@@ -233,14 +234,14 @@ __global__ void __launch_bounds__(256, (K * CH <= 4) ? 3 : 2) bwd_update_kernel(
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
             hacc[c].zero();
-            if (col0 + c * G * VEC < P.D) hacc[c].load(sh_part + col0 + c * G * VEC);
+            if (EXACT || col0 + c * G * VEC < P.D) hacc[c].load(sh_part + col0 + c * G * VEC);
         }
         if ((flags & kHeadClosed) == 0) {
             for (int v = 1; v < GPC && (sh_flag[v] & kActive); ++v) {
                 const float* hp = sh_part + (size_t)v * P.D + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
-                    if (col0 + c * G * VEC < P.D) {
+                    if (EXACT || col0 + c * G * VEC < P.D) {
                         RowVec<VEC> h;
                         h.load(hp + c * G * VEC);
                         hacc[c].add(h);
@@ -420,13 +421,14 @@ static int launch_rows_update(int optimizer, float* W, float* mom, const int64_t
     return check_launch("rows_update");
 }
 
-template <int VEC, int G, int CH, int K = (CH == 1 ? 4 : 2)>
+template <int VEC, int G, int CH, int K = (CH == 1 ? 4 : 2), int OCC = 0>
 static int launch_update(const BwdParams& P, cudaStream_t st) {
     const int threads = 256;
     constexpr int GPC = 256 / G;
     const unsigned blocks = (unsigned)ceil_div(P.nseg, (int64_t)GPC);
     const size_t smem = (size_t)2 * GPC * P.D * sizeof(float);
-    bwd_update_kernel<VEC, G, CH, K><<<blocks, threads, smem, st>>>(P);
+    if (P.D == VEC * G * CH) bwd_update_kernel<VEC, G, CH, K, OCC, true><<<blocks, threads, smem, st>>>(P);
+    else bwd_update_kernel<VEC, G, CH, K, OCC, false><<<blocks, threads, smem, st>>>(P);
     int rc = check_launch("bwd_update");
     if (rc) return rc;
     // the fix-up works on CTA tiles: GPC segments each, one head / tail partial per tile
@@ -523,6 +525,19 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
 #define DLRMX_CALL_UPDATE(V, G_, C) launch_update<V, G_, C>(P, st)
     // experiment knob (tunable 1 = 8): 8 positions in flight per lane for one-warp-per-row geometries
     if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 8) return launch_update<4, 32, 1, 8>(P, st);
+    // experiments: 4 positions in flight squeezed into 64 registers (4 CTAs per SM), 2 and 3 positions at 4 CTAs per SM
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 64) return launch_update<4, 32, 1, 4, 4>(P, st);
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 2) return launch_update<4, 32, 1, 2, 4>(P, st);
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 3) return launch_update<4, 32, 1, 3, 4>(P, st);
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 6) return launch_update<4, 32, 1, 6, 2>(P, st);
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 25) return launch_update<4, 32, 1, 2, 5>(P, st);
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 16) return launch_update<4, 32, 1, 1, 6>(P, st);
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 4) return launch_update<4, 32, 1, 4, 3>(P, st);
+    // Row-wise Adagrad on 512-byte rows: 2 positions in flight per warp at 4 CTAs per SM (64 registers, no spills) beat 4
+    // positions at 3 CTAs per SM (0.175 vs 0.183 ms on the Terabyte shape: the sum-of-squares butterfly, square root and
+    // division lengthen every batch, and more resident warps hide that better than deeper batches); plain SGD prefers 4.
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD && get_tunable(DLRMX_TUNE_BWD_K) == 0)
+        return launch_update<4, 32, 1, 2, 4>(P, st);
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;

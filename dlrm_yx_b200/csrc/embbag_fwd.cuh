@@ -16,6 +16,7 @@
 //   * 64-bit row addressing, per-table base pointers, strided output so pooled rows land directly in the
 //     [B, 1+T, D] interaction input (no torch.cat afterwards).
 // HBM-bound: algorithmic bytes = N*D*4 (rows) + N*ib + T*B*ob + T*B*D*4 (pooled rows).
+#pragma once
 #include "common.cuh"
 
 namespace dlrmx {
@@ -49,7 +50,8 @@ __device__ __forceinline__ int32_t shfl_idx(unsigned mask, int32_t v, int src, i
 // memory-level parallelism comes from unrolling ALONG the bag -- loads are issued U at a time, the adds still
 // happen one by one in index order).
 // OCC > 0 overrides the CTAs-per-SM target of the register allocation.
-template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT, int OCC = 0>
+// EXACT: D == VEC*G*CH, every lane owns columns of the row (no per-lane guard).
+template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT, int OCC = 0, bool EXACT = false>
 __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2)))
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
@@ -142,7 +144,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                         const float* p = base[k] + (int64_t)ix[k][u] * ld + col0;
 #pragma unroll
                         for (int c = 0; c < CH; ++c)
-                            if (col0 + c * G * VEC < D) row[k][u][c].load_stream(p + c * G * VEC);
+                            if (EXACT || col0 + c * G * VEC < D) row[k][u][c].load_stream(p + c * G * VEC);
                     }
                 }
             // request the next rounds' indices before this round's rows are consumed
@@ -160,12 +162,12 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                         if (psw == nullptr) {
 #pragma unroll
                             for (int c = 0; c < CH; ++c)
-                                if (col0 + c * G * VEC < D) acc[k][c].add(row[k][u][c]);
+                                if (EXACT || col0 + c * G * VEC < D) acc[k][c].add(row[k][u][c]);
                         } else {
                             const float w = __ldg(psw + start[k] + r + u);
 #pragma unroll
                             for (int c = 0; c < CH; ++c)
-                                if (col0 + c * G * VEC < D) acc[k][c].add_scaled(row[k][u][c], w);
+                                if (EXACT || col0 + c * G * VEC < D) acc[k][c].add_scaled(row[k][u][c], w);
                         }
                     }
 #pragma unroll
@@ -187,7 +189,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                                    : out + b * stride_b + t * stride_t + col0;
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
-                    if (col0 + c * G * VEC < D) acc[k][c].store(o + c * G * VEC);
+                    if (EXACT || col0 + c * G * VEC < D) acc[k][c].store(o + c * G * VEC);
             }
         }
     }
@@ -205,14 +207,17 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     const int threads = 256;
     const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
-    if (out_peers != nullptr)
-        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, true, IdxT, OCC><<<(unsigned)blocks, threads, 0, st>>>(
-            tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag,
-            out_peers, lb, mb_off, mb_len);
-    else
-        embbag_fwd_kernel<VEC, G, CH, K, U, FULL, false, IdxT, OCC><<<(unsigned)blocks, threads, 0, st>>>(
-            tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag,
-            nullptr, 1, 0, 1);
+#define DLRMX_FWD_LAUNCH(SC, EX, ...) \
+    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, SC, IdxT, OCC, EX><<<(unsigned)blocks, threads, 0, st>>>(__VA_ARGS__)
+    const bool exact = D == VEC * G * CH;
+    if (out_peers != nullptr) {
+        if (exact) DLRMX_FWD_LAUNCH(true, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, mb_len);
+        else DLRMX_FWD_LAUNCH(true, false, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, mb_len);
+    } else {
+        if (exact) DLRMX_FWD_LAUNCH(false, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, nullptr, 1, 0, 1);
+        else DLRMX_FWD_LAUNCH(false, false, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, nullptr, 1, 0, 1);
+    }
+#undef DLRMX_FWD_LAUNCH
     return check_launch("embbag_fwd");
 }
 
@@ -242,26 +247,25 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
 #define DLRMX_FWD_ARGS \
     tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, \
         mb_len, st
-#define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                  \
-    if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                   \
-        if (short_bags) {                                                                              \
-            if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 8, 1, true, IdxT>(DLRMX_FWD_ARGS); \
-            return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);       \
-        }                                                                                              \
-        /* long bags, measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the bags /  */ \
-        /* 512-byte rows): ONE bag per group with 8 of its rows in flight at 3 CTAs per SM (72-74 registers, no spills)   */ \
-        /* wins everywhere -- 0.60 / 0.76 / 0.99 against 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128      */ \
-        /* registers, 2 CTAs per SM, half as many work units for the launch's tail), 0.57 / 0.67 / 0.56 when squeezed to  */ \
-        /* 64 registers for 4 CTAs per SM (spills) and 0.56 / 0.67 / 0.84 with 16 rows in flight.  An L2 bulk prefetch    */ \
-        /* ahead of the walk (cp.async.bulk.prefetch.L2, lane-parallel) and a two-round register double buffer were tried */ \
-        /* and were slower.  FWD_K tunable: 2 / 3: one bag per group at 4 CTAs per SM / 16 rows in flight; 8 / 4: the     */ \
-        /* older two-bag variants.                                                                                        */ \
-        if (CH_ == 1 && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS);  \
-        if (CH_ == 1 && tune == 4) return launch_fwd<VEC_, G_, CH_, 2, 4, false, IdxT>(DLRMX_FWD_ARGS);  \
-        if (CH_ == 1 && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS); \
-        if (CH_ == 1 && tune == 3) return launch_fwd<VEC_, G_, CH_, 1, 16, false, IdxT, 2>(DLRMX_FWD_ARGS); \
-        if (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 3>(DLRMX_FWD_ARGS);            \
-        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3>(DLRMX_FWD_ARGS);          \
+    // Long bags, measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the bags /
+    // 512-byte rows): ONE bag per group with 8 of its rows in flight at 3 CTAs per SM (72-74 registers, no spills) wins
+    // everywhere -- 0.60 / 0.76 / 0.99 against 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128 registers,
+    // 2 CTAs per SM, half as many work units for the launch's tail), 0.57 / 0.67 / 0.56 when squeezed to 64 registers for
+    // 4 CTAs per SM (spills) and 0.56 / 0.67 / 0.84 with 16 rows in flight.  An L2 bulk prefetch ahead of the walk
+    // (cp.async.bulk.prefetch.L2, lane-parallel) and a two-round register double buffer were tried and were slower.
+    // FWD_K tunable (experiment variants, built for the 256- and 512-byte row geometries only): short bags 8: K=8;
+    // long bags 2 / 3: one bag per group at 4 CTAs per SM / 16 rows in flight; 8 / 4: the older two-bag variants.
+#define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                       \
+    if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                        \
+        if constexpr (VEC_ == 4 && CH_ == 1 && G_ >= 16) {                                                  \
+            if (short_bags && tune == 8) return launch_fwd<VEC_, G_, CH_, 8, 1, true, IdxT>(DLRMX_FWD_ARGS);  \
+            if (!short_bags && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS); \
+            if (!short_bags && tune == 4) return launch_fwd<VEC_, G_, CH_, 2, 4, false, IdxT>(DLRMX_FWD_ARGS); \
+            if (!short_bags && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS); \
+            if (!short_bags && tune == 3) return launch_fwd<VEC_, G_, CH_, 1, 16, false, IdxT, 2>(DLRMX_FWD_ARGS); \
+        }                                                                                                   \
+        if (short_bags) return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);  \
+        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 1 ? 8 : (CH_ == 2 ? 4 : 2)), false, IdxT, 3>(DLRMX_FWD_ARGS); \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
     DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)
@@ -274,39 +278,3 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
 
 }  // namespace dlrmx
 
-extern "C" {
-int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
-                         const int32_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
-                         float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
-                         dlrmx_stream_t stream) {
-    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw, out, stride_b,
-                                      stride_t, err_flag, nullptr, 0, 0, 0, stream);
-}
-int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
-                         const int64_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
-                         float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
-                         dlrmx_stream_t stream) {
-    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw, out, stride_b,
-                                      stride_t, err_flag, nullptr, 0, 0, 0, stream);
-}
-int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
-                                 const int32_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
-                                 float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
-                                 int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
-    using namespace dlrmx;
-    DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
-    return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw,
-                                      nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
-                                      mb_len, stream);
-}
-int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows, const int64_t* indices,
-                                 const int64_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
-                                 float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
-                                 int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
-    using namespace dlrmx;
-    DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
-    return dlrmx::embbag_fwd<int64_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw,
-                                      nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
-                                      mb_len, stream);
-}
-}

@@ -68,6 +68,7 @@ def main():
     ap.add_argument("--gstride", type=int, default=0, help="gradient laid out [B, gstride, D] (features 1..T used)")
     ap.add_argument("--only", default="")
     ap.add_argument("--gscale", type=float, default=1.0)
+    ap.add_argument("--sorted", action="store_true", help="ids sorted within each bag (the reference's generator)")
     ap.add_argument("--pad", type=int, default=0, help="floats of padding after every table row (accumulator in the row)")
     args = ap.parse_args()
     cfg = SHAPES[args.shape]
@@ -93,6 +94,8 @@ def main():
     batches = []
     for i in range(nbatch):
         idx = torch.cat([torch.randint(0, r, (B * L,), device=dev) for r in rows]).to(idt)
+        if args.sorted:
+            idx = torch.sort(idx.view(T * B, L), dim=1)[0].reshape(-1).contiguous()
         off = (torch.arange(T * B + 1, device=dev) * L).to(idt)
         batches.append((idx, off))
     N = T * B * L
@@ -119,7 +122,7 @@ def main():
 
     only = set(args.only.split(",")) if args.only else None
     long_bags = L > 2
-    fwd_variants = (0, 2, 3, 8, 4) if long_bags else (8, 4, 0)   # see the FWD_K tunable in csrc/embbag_fwd.cu
+    fwd_variants = (0, 2, 3, 8, 4) if long_bags else (8, 4, 0)   # see the FWD_K tunable in csrc/embbag_fwd.cuh
     for k in fwd_variants:
         if only and "fwd" not in only:
             break
@@ -147,7 +150,7 @@ def main():
     for opt, name in ((_lib.OPT_SGD, "sgd"), (_lib.OPT_RWSADAGRAD, "rwsadagrad")):
         if only and "bwd" not in only:
             break
-        for seg, k8 in ((0, 0), (64, 0), (128, 0), (0, 8)):
+        for seg, k8 in ((0, 0), (0, 4), (0, 2), (32, 2), (128, 2), (0, 25), (0, 16), (32, 16)):
             _lib.set_tunable(3, seg)
             _lib.set_tunable(_lib.TUNE_BWD_K, k8)
 
