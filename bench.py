@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--cpu-rows-cap", type=int, default=1000000)
     ap.add_argument("--cpu-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-c3-probe", action="store_true", help="skip the C3-shape embedding-bag kernel lines")
     return ap.parse_args()
 
 
@@ -547,7 +548,7 @@ def main():
         "launch_mode": "cuda-graph (whole step)" if r["use_graph"] else "eager",
         "kernels": kern,
     }
-    if W == 1 and args.config == "terabyte":
+    if W == 1 and args.config == "terabyte" and not args.no_c3_probe:
         try:
             line["embedding_bag_c3"] = embbag_c3_probe(peak)
         except Exception as ex:                       # the probe must never cost the headline line
