@@ -49,9 +49,9 @@ SIGNATURES = {
                                        c_void_p]),
     "dlrmx_interact_dot_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64,
                                        c_void_p, c_int64, c_void_p]),
-    "dlrmx_interact_dot_fwd_mixed": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+    "dlrmx_interact_dot_fwd_mixed": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                              c_int64, c_void_p]),
-    "dlrmx_interact_dot_bwd_mixed": (c_int, [c_void_p, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+    "dlrmx_interact_dot_bwd_mixed": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                              c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "dlrmx_relu_bwd_bias_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                          c_int, c_int, c_void_p]),
@@ -118,5 +118,14 @@ def launch_count():
     return int(load().dlrmx_launch_count())
 
 
+_TUNABLES = {}
+
+
 def set_tunable(which, value):
     check(load().dlrmx_set_tunable(which, value), "dlrmx_set_tunable")
+    _TUNABLES[which] = value
+
+
+def get_tunable_py(which):
+    """Value last set through set_tunable (0 = default)."""
+    return _TUNABLES.get(which, 0)

@@ -33,7 +33,7 @@ inline int check_launch(const char* what) {
 constexpr int kSMs = 148;  // B200
 
 // Experiment knobs (dlrmx_set_tunable); 0 = default.
-enum { DLRMX_TUNE_FWD_K = 0, DLRMX_TUNE_BWD_K = 1, DLRMX_TUNE_BWD_SEG = 3, DLRMX_TUNE_SCATTER_CTAS = 5, DLRMX_TUNE_COUNT = 8 };
+enum { DLRMX_TUNE_FWD_K = 0, DLRMX_TUNE_BWD_K = 1, DLRMX_TUNE_BWD_SEG = 3, DLRMX_TUNE_SCATTER_CTAS = 5, DLRMX_TUNE_COUNT = 16 };
 int get_tunable(int which);
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -64,6 +64,39 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 // all but the most recent group have landed
 __device__ __forceinline__ void cp_async_wait_prev() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
+// ---- TMA bulk-copy staging (cp.async.bulk global -> shared, completion counted in bytes on an mbarrier) ----------
+// The staging loop of per-thread 16-byte cp.async copies is a third of the forward kernel's issued instructions (ncu r01
+// v6 source view) in a kernel that is instruction-bound.  When the interaction input is laid out in HBM with the SAME row
+// pitch as the shared-memory tile (D + 8 floats: the lookup kernel writes pooled rows with that
+// stride), a sample's F-1 embedding rows are ONE contiguous block and ONE bulk copy issued by one thread stages them,
+// padding included; the bf16 x row (and the dR row in the backward) are one more bulk copy each.  (One bulk copy per
+// 512-byte row into padded rows from an unpadded input was tried first and was slower than cp.async: the copy
+// instruction is issued from the uniform datapath, lane-parallel issue becomes a 27-iteration loop in one warp.)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_init_fence() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    uint32_t ok, tries = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+        if (!ok && ++tries > (1u << 24)) __trap();       // a copy that never lands must not hang the GPU
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 __host__ __device__ inline int tri_count_mma(int F, int itself) { return itself ? F * (F + 1) / 2 : F * (F - 1) / 2; }
 
 constexpr int kMmaWarps = 4;
@@ -74,14 +107,19 @@ constexpr int kMmaWarps = 4;
 // writes its partial triangle to shared memory, and the four partials are added in a fixed order with
 // round-to-nearest adds (short accumulation chains inside the tensor core, deterministic result).
 // ---------------------------------------------------------------------------------------------------------
-template <bool MIXED>
-__global__ void __launch_bounds__(kMmaWarps * 32)
-interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
+template <bool MIXED, bool BULK>
+__global__ void __launch_bounds__(kMmaWarps * 32, MIXED ? 6 : 4)
+interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int64_t fst, int B, int F, int D, int itself,
                         void* __restrict__ out_, int64_t ostride, const __nv_bfloat16* __restrict__ xb) {
+    static_assert(!BULK || MIXED, "bulk staging serves the bf16-facing kernels");
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
-    const int DS = D + 4;          // fragment loads T[g + 8r][k0 + t + 4h]: banks 4g + t, all distinct
+    // fragment loads T[g + 8r][k0 + t + 4h]: with a row pitch of D + 4 the banks are 4g + t, all distinct.  BULK: the tile
+    // has the input's own pitch D + 8 (one bulk copy per sample; rows of the input must start on 32-byte sectors or the
+    // lookup's row stores become partial-sector writes: a pitch of D + 4 cost the lookup kernel 25 %), where rows g and
+    // g + 4 share a bank -- 2-way conflicts on 8 loads per k-step, far cheaper than the staging loop they replace.
+    const int DS = BULK ? D + 8 : D + 4;
     const int nz = tri_count_mma(F, itself);
     const int nzp = (nz + 3) & ~3;
     // two tile buffers [F][DS]: the next sample is copied in (cp.async) while this one is being contracted
@@ -108,7 +146,26 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
                 zdst[m][n][q] = keep ? (itself ? i * (i + 1) / 2 + j : i * (i - 1) / 2 + j) : -1;
             }
 
+    __shared__ uint64_t mbar[2];            // BULK: one per stage, a phase completes when the stage's bytes have landed
+    if (BULK) {
+        if (threadIdx.x == 0) {
+            mbar_init(&mbar[0], 1);
+            mbar_init(&mbar[1], 1);
+            mbar_init_fence();
+        }
+        __syncthreads();
+    }
     auto stage = [&](int64_t bb, int which) {
+        if (BULK) {
+            // fst == DS: rows 1..F-1 of the sample are one contiguous block with the tile's own row pitch
+            if (threadIdx.x == 0 && bb < B) {
+                const uint32_t nb_rows = (uint32_t)((F - 1) * DS * 4);
+                mbar_expect_tx(&mbar[which], nb_rows + (uint32_t)(D * 2));
+                bulk_g2s(smem + which * F * DS + DS, feat + bb * fsb + fst, nb_rows, &mbar[which]);
+                bulk_g2s(xs_base + which * D, xb + bb * D, (uint32_t)(D * 2), &mbar[which]);
+            }
+            return;
+        }
         if (bb < B) {
             const float* src = feat + bb * fsb;
             float* dstt = smem + which * F * DS;
@@ -128,10 +185,12 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         cp_async_commit();
     };
     int buf = 0;
+    uint32_t it = 0;
     stage(blockIdx.x, 0);
-    for (int64_t b = blockIdx.x; b < B; b += gridDim.x, buf ^= 1) {
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x, buf ^= 1, ++it) {
         stage(b + gridDim.x, buf ^ 1);       // that buffer's last readers finished before the previous barrier
-        cp_async_wait_prev();
+        if (BULK) mbar_wait(&mbar[buf], (it >> 1) & 1u);
+        else cp_async_wait_prev();
         __syncthreads();
         const float* tile = smem + buf * F * DS;
         const __nv_bfloat16* xs = xs_base + buf * D;
@@ -224,15 +283,16 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
 // backward:  dfeat[b, i, :] = sum_j S[i][j] * feat[b, j, :]  (+ dR[b, :D] on i = 0),  S = dZ + dZ^t
 // One CTA per sample; the D output columns are split across the 4 warps in 8-column tiles.
 // ---------------------------------------------------------------------------------------------------------
-template <bool MIXED>
+template <bool MIXED, bool BULK>
 __global__ void __launch_bounds__(kMmaWarps * 32, 4)
-interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
+interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int64_t fst, int B, int F, int D, int itself,
                         const void* __restrict__ dout_, int64_t dstride, float* __restrict__ dfeat, int64_t dfsb,
                         const __nv_bfloat16* __restrict__ xb, __nv_bfloat16* __restrict__ dxb) {
+    static_assert(!BULK || MIXED, "bulk staging serves the bf16-facing kernels");
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
-    const int DS = D + 8;          // B fragments T[k0 + t (+4)][n0 + g]: banks 8t + g, all distinct
+    const int DS = D + 8;          // B fragments T[k0 + t (+4)][n0 + g]: banks 8t + g, all distinct (BULK: the input's own pitch)
     constexpr int SS = 36;         // A fragments S[g (+8)][k0 + t (+4)]: banks 4g + t, all distinct
     constexpr int NT = 4;          // 8-column output tiles per warp and pass
     const int nz = tri_count_mma(F, itself);
@@ -273,7 +333,28 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     const float* dout = reinterpret_cast<const float*>(dout_);
     const __nv_bfloat16* doutb = reinterpret_cast<const __nv_bfloat16*>(dout_);
 
+    __shared__ uint64_t mbar[2];
+    if (BULK) {
+        if (threadIdx.x == 0) {
+            mbar_init(&mbar[0], 1);
+            mbar_init(&mbar[1], 1);
+            mbar_init_fence();
+        }
+        __syncthreads();
+    }
     auto stage = [&](int64_t bb, int which) {
+        if (BULK) {
+            if (threadIdx.x == 0 && bb < B) {
+                float* dstt = smem + which * stage_floats;
+                __nv_bfloat16* zr = reinterpret_cast<__nv_bfloat16*>(dstt + F * DS);
+                const uint32_t nb_rows = (uint32_t)((F - 1) * DS * 4);
+                mbar_expect_tx(&mbar[which], nb_rows + (uint32_t)(nchunk * 16 + D * 2));
+                bulk_g2s(dstt + DS, feat + bb * fsb + fst, nb_rows, &mbar[which]);
+                bulk_g2s(zr, doutb + bb * dstride, (uint32_t)(nchunk * 16), &mbar[which]);
+                bulk_g2s(zr + 8 * nchunk + 8, xb + bb * D, (uint32_t)(D * 2), &mbar[which]);
+            }
+            return;
+        }
         if (bb < B) {
             const float* src = feat + bb * fsb;
             float* dstt = smem + which * stage_floats;
@@ -297,9 +378,11 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
         cp_async_commit();
     };
     int buf = 0;
+    uint32_t it = 0;
     stage(blockIdx.x, 0);
-    for (int64_t b = blockIdx.x; b < B; b += gridDim.x, buf ^= 1) {
-        cp_async_wait_all();                 // this sample's stage has landed (the only group in flight)
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x, buf ^= 1, ++it) {
+        if (BULK) mbar_wait(&mbar[buf], (it >> 1) & 1u);
+        if (!BULK) cp_async_wait_all();      // this sample's stage has landed (the only group in flight)
         __syncthreads();                     // ... and every warp is done contracting the previous sample,
         stage(b + gridDim.x, buf ^ 1);       // so its stage can be refilled while this one is worked on
         const float* tile = smem + buf * stage_floats;
@@ -411,8 +494,13 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int B, int 
     }
 }
 
+// tunable 10 = 1: per-thread cp.async staging instead of TMA bulk copies; tunable 11: CTAs per SM of the persistent grid
+enum { DLRMX_TUNE_IX_STAGE = 10, DLRMX_TUNE_IX_GRID = 11 };
+static bool use_bulk() { return get_tunable(DLRMX_TUNE_IX_STAGE) != 1; }
+
 static int mma_grid(int B) {
-    const int64_t cap = (int64_t)kSMs * 12;      // persistent: a few CTAs per SM, each loops over samples
+    const int per_sm = get_tunable(DLRMX_TUNE_IX_GRID) > 0 ? get_tunable(DLRMX_TUNE_IX_GRID) : 12;
+    const int64_t cap = (int64_t)kSMs * per_sm;  // persistent: a few CTAs per SM, each loops over samples
     return (int)(B < cap ? B : cap);
 }
 
@@ -427,11 +515,11 @@ int interact_fwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
     if (smem > 200 * 1024) return 0;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(interact_fwd_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_fwd_mma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
-    interact_fwd_mma_kernel<false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, out, ostride,
-                                                                              nullptr);
+    interact_fwd_mma_kernel<false, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, D, B, F, D, itself, out,
+                                                                                     ostride, nullptr);
     *rc = check_launch("interact_dot_fwd(mma)");
     return 1;
 }
@@ -446,11 +534,11 @@ int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
     if (smem > 200 * 1024) return 0;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(interact_bwd_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_bwd_mma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
-    interact_bwd_mma_kernel<false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, B, F, D, itself, dout, dstride,
-                                                                              dfeat, dfsb, nullptr, nullptr);
+    interact_bwd_mma_kernel<false, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+        feat, fsb, D, B, F, D, itself, dout, dstride, dfeat, dfsb, nullptr, nullptr);
     *rc = check_launch("interact_dot_bwd(mma)");
     return 1;
 }
@@ -464,44 +552,62 @@ int interact_bwd_warp(const float* feat, int64_t fsb, const void* x_bf16, int B,
 enum { DLRMX_TUNE_IX_WARP = 4 };     // tunable 4 = 1: one-warp-per-sample kernels (measured slower, see interact_warp.cu)
 
 // bf16-facing variants.  Return 0 on success, a negative code (message set) when the shape is not supported.
-int interact_fwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
+int interact_fwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* x_bf16, int B, int F, int D, int itself,
                        void* out_bf16, int64_t ostride, cudaStream_t st) {
     const int nz = tri_count_mma(F, itself);
+    if (fst <= 0) fst = D;
     if (!mma_shape_ok(F, D) || fsb % 4 != 0 || ((uintptr_t)feat & 15) != 0 || ((uintptr_t)x_bf16 & 15) != 0 ||
-        ((uintptr_t)out_bf16 & 3) != 0 || ostride % 2 != 0 || ostride < D + nz) {
-        set_error("interact_dot_fwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, even "
-                  "out_stride >= D + nz (F=%d D=%d out_stride=%lld)", F, D, (long long)ostride);
+        ((uintptr_t)out_bf16 & 3) != 0 || ostride % 2 != 0 || ostride < D + nz || (fst != D && fst != D + 8)) {
+        set_error("interact_dot_fwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, feature pitch D "
+                  "or D + 8, even out_stride >= D + nz (F=%d D=%d pitch=%lld out_stride=%lld)", F, D, (long long)fst,
+                  (long long)ostride);
         return DLRMX_E_ARG;
     }
-    if (get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
+    const bool padded = fst == D + 8;          // the input has the shared-memory tile's row pitch: bulk-copy staging
+    if (padded && !(use_bulk() && D % 32 == 0)) {
+        set_error("interact_dot_fwd_mixed: a feature pitch of D + 8 needs D %% 32 == 0 (bulk-copy staging)");
+        return DLRMX_E_ARG;
+    }
+    if (!padded && get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
         int rc = 0;
         if (interact_fwd_warp(feat, fsb, x_bf16, B, F, D, itself, out_bf16, ostride, st, &rc)) return rc;
     }
-    const size_t smem = (2 * (size_t)F * (D + 4) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4 + 2 * (size_t)D * 2;
+    const size_t smem = (2 * (size_t)F * (D + (padded ? 8 : 4)) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4 + 2 * (size_t)D * 2;
     if (smem > 200 * 1024) { set_error("interact_dot_fwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(interact_fwd_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_fwd_mma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_fwd_mma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
-    interact_fwd_mma_kernel<true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
-        feat, fsb, B, F, D, itself, out_bf16, ostride, (const __nv_bfloat16*)x_bf16);
+    if (padded)
+        interact_fwd_mma_kernel<true, true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+            feat, fsb, fst, B, F, D, itself, out_bf16, ostride, (const __nv_bfloat16*)x_bf16);
+    else
+        interact_fwd_mma_kernel<true, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+            feat, fsb, fst, B, F, D, itself, out_bf16, ostride, (const __nv_bfloat16*)x_bf16);
     return check_launch("interact_dot_fwd_mixed");
 }
 
-int interact_bwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
+int interact_bwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* x_bf16, int B, int F, int D, int itself,
                        const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16,
                        cudaStream_t st) {
     const int nz = tri_count_mma(F, itself);
+    if (fst <= 0) fst = D;
     if (!mma_shape_ok(F, D) || fsb % 4 != 0 || dfsb % 2 != 0 || ((uintptr_t)feat & 15) != 0 ||
         ((uintptr_t)dfeat & 7) != 0 || ((uintptr_t)x_bf16 & 15) != 0 || ((uintptr_t)dout_bf16 & 15) != 0 ||
-        ((uintptr_t)dx_bf16 & 3) != 0 || dstride % 8 != 0 || dstride < ((D + nz + 7) & ~7)) {
-        set_error("interact_dot_bwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, "
-                  "dout_stride %% 8 == 0 and >= D + nz rounded up to 8 (F=%d D=%d dout_stride=%lld)", F, D,
-                  (long long)dstride);
+        ((uintptr_t)dx_bf16 & 3) != 0 || dstride % 8 != 0 || dstride < ((D + nz + 7) & ~7) || (fst != D && fst != D + 8)) {
+        set_error("interact_dot_bwd_mixed: needs 2 <= F <= 32, D %% 8 == 0, D <= 512, 16-B aligned inputs, feature pitch D "
+                  "or D + 8, dout_stride %% 8 == 0 and >= D + nz rounded up to 8 (F=%d D=%d pitch=%lld dout_stride=%lld)",
+                  F, D, (long long)fst, (long long)dstride);
         return DLRMX_E_ARG;
     }
-    if (get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
+    const bool padded = fst == D + 8;
+    if (padded && !(use_bulk() && D % 32 == 0)) {
+        set_error("interact_dot_bwd_mixed: a feature pitch of D + 8 needs D %% 32 == 0 (bulk-copy staging)");
+        return DLRMX_E_ARG;
+    }
+    if (!padded && get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
         int rc = 0;
         if (interact_bwd_warp(feat, fsb, x_bf16, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, dx_bf16, st, &rc))
             return rc;
@@ -511,12 +617,18 @@ int interact_bwd_mixed(const float* feat, int64_t fsb, const void* x_bf16, int B
     if (smem > 200 * 1024) { set_error("interact_dot_bwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(interact_bwd_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_bwd_mma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(interact_bwd_mma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_done = true;
     }
-    interact_bwd_mma_kernel<true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
-        feat, fsb, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, (const __nv_bfloat16*)x_bf16,
-        (__nv_bfloat16*)dx_bf16);
+    if (padded)
+        interact_bwd_mma_kernel<true, true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+            feat, fsb, fst, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, (const __nv_bfloat16*)x_bf16,
+            (__nv_bfloat16*)dx_bf16);
+    else
+        interact_bwd_mma_kernel<true, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
+            feat, fsb, fst, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, (const __nv_bfloat16*)x_bf16,
+            (__nv_bfloat16*)dx_bf16);
     return check_launch("interact_dot_bwd_mixed");
 }
 

@@ -110,9 +110,10 @@ class _SparseArchLocalMixed(torch.autograd.Function):
     def forward(ctx, x, weights, emb, indices, offsets, itself, out_cols):
         B, D = x.shape
         T = emb.T
-        feat = torch.empty((B, 1 + T, D), dtype=torch.float32, device=x.device)   # slot 0 stays unused
+        # slot 0 stays unused; rows are pitched for the interaction kernels' one-bulk-copy staging (D + 8 when D % 32 == 0)
+        feat = ops.alloc_features(B, 1 + T, D, x.device)
         ops.embbag_forward(emb.table_set(), indices, offsets, B, out=feat[:, 1:, :],
-                           stride_b=(1 + T) * D, stride_t=D)
+                           stride_b=feat.stride(0), stride_t=feat.stride(1))
         x = x.contiguous()
         ctx.emb, ctx.itself = emb, bool(itself)
         ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None

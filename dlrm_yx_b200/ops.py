@@ -267,15 +267,28 @@ def interact_mixed_supported(F, D):
     return 2 <= F <= 32 and D % 8 == 0 and D <= 512
 
 
+def interact_feature_pitch(F, D):
+    """Row pitch (floats) the bf16-facing interaction kernels like best for their [B, F, D] input: D + 8 (the pitch of
+    their shared-memory tile, so that ONE TMA bulk copy stages a sample) when D % 32 == 0, else D."""
+    return D + 8 if (interact_mixed_supported(F, D) and D % 32 == 0 and _lib.get_tunable_py(10) != 1) else D
+
+
+def alloc_features(B, F, D, device, pitch=None):
+    """[B, F, D] fp32 view with row pitch `pitch` (default interact_feature_pitch) of a fresh allocation."""
+    pitch = interact_feature_pitch(F, D) if pitch is None else pitch
+    return torch.empty((B, F, pitch), dtype=torch.float32, device=device)[:, :, :D]
+
+
 def interact_dot_fwd_mixed(feat, x_bf16, out_cols, itself=False):
     """feat [B, F, D] fp32 (features 1.. valid), x_bf16 [B, D] (feature 0) -> bf16 [B, out_cols] = [x | tril | 0...]."""
     _need_cuda(feat, x_bf16)
     B, F, D = feat.shape
-    if feat.stride(2) != 1 or feat.stride(1) != D or not x_bf16.is_contiguous() or x_bf16.dtype != torch.bfloat16:
-        raise _lib.DlrmxError("interact_dot_fwd_mixed: feat [B, F, D] fp32 with contiguous blocks, x contiguous bf16")
+    if feat.stride(2) != 1 or feat.stride(1) not in (D, D + 8) or not x_bf16.is_contiguous() or \
+            x_bf16.dtype != torch.bfloat16:
+        raise _lib.DlrmxError("interact_dot_fwd_mixed: feat [B, F, D] fp32 with feature pitch D or D + 8, x contiguous bf16")
     out = torch.empty((B, out_cols), dtype=torch.bfloat16, device=feat.device)
     with _timed("interact_fwd"):
-        rc = _lib.load().dlrmx_interact_dot_fwd_mixed(feat.data_ptr(), feat.stride(0), x_bf16.data_ptr(), B, F, D,
+        rc = _lib.load().dlrmx_interact_dot_fwd_mixed(feat.data_ptr(), feat.stride(0), feat.stride(1), x_bf16.data_ptr(), B, F, D,
                                                       int(itself), out.data_ptr(), out.stride(0), _stream())
         _lib.check(rc, "dlrmx_interact_dot_fwd_mixed")
     return out
@@ -290,7 +303,7 @@ def interact_dot_bwd_mixed(feat, x_bf16, dout, itself=False):
     dfeat = torch.empty((B, F, D), dtype=torch.float32, device=feat.device)
     dx = torch.empty((B, D), dtype=torch.bfloat16, device=feat.device)
     with _timed("interact_bwd"):
-        rc = _lib.load().dlrmx_interact_dot_bwd_mixed(feat.data_ptr(), feat.stride(0), x_bf16.data_ptr(), B, F, D,
+        rc = _lib.load().dlrmx_interact_dot_bwd_mixed(feat.data_ptr(), feat.stride(0), feat.stride(1), x_bf16.data_ptr(), B, F, D,
                                                       int(itself), dout.data_ptr(), dout.stride(0), dfeat.data_ptr(),
                                                       dfeat.stride(0), dx.data_ptr(), _stream())
         _lib.check(rc, "dlrmx_interact_dot_bwd_mixed")

@@ -173,11 +173,15 @@ int dlrmx_interact_dot_bwd(const float* feat, int64_t feat_stride_b, int B, int 
  *   MLP's K rounded up to 8, so the GEMM reads it without a pad/cast pass);
  *   backward reads dout_bf16 [B, dout_stride] bf16 (dout_stride % 8 == 0), writes the pooled-embedding gradients
  *   dfeat[:, 1:, :] in fp32 (feature 0 of dfeat is left untouched) and the gradient of x as dx_bf16 [B, D].
+ *   feat_stride_f = row pitch of the features inside a sample, in floats: D (contiguous [F, D] blocks; 0 means D), or
+ *   D + 8 when D % 32 == 0 -- the interaction input then has the row pitch of the kernels' shared-memory tile (the
+ *   lookup writes pooled rows with stride_t = D + 8: rows stay 32-byte aligned, so its stores stay full sectors), and a
+ *   sample is staged by ONE TMA bulk copy (cp.async.bulk + mbarrier) instead of F*D/4 per-thread 16-byte cp.async copies.
  * Products are single-pass TF32 (operands rounded to nearest) with fp32 accumulation.  Needs 2 <= F <= 32, D % 8 == 0,
  * D <= 512; other shapes: use the fp32 entry points and cast. */
-int dlrmx_interact_dot_fwd_mixed(const float* feat, int64_t feat_stride_b, const void* x_bf16, int B, int F, int D,
+int dlrmx_interact_dot_fwd_mixed(const float* feat, int64_t feat_stride_b, int64_t feat_stride_f, const void* x_bf16, int B, int F, int D,
                                  int itself, void* out_bf16, int64_t out_stride, dlrmx_stream_t stream);
-int dlrmx_interact_dot_bwd_mixed(const float* feat, int64_t feat_stride_b, const void* x_bf16, int B, int F, int D,
+int dlrmx_interact_dot_bwd_mixed(const float* feat, int64_t feat_stride_b, int64_t feat_stride_f, const void* x_bf16, int B, int F, int D,
                                  int itself, const void* dout_bf16, int64_t dout_stride, float* dfeat,
                                  int64_t dfeat_stride_b, void* dx_bf16, dlrmx_stream_t stream);
 

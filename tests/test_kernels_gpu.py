@@ -314,11 +314,15 @@ def test_fused_backward_long_chains(D, opt, seg, request):
 
 @pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (4, 2), (2, 8), (33, 32)])
 @pytest.mark.parametrize("itself", [False, True])
-def test_interaction_fwd_bwd(F, D, itself):
-    from dlrm_yx_b200 import ops
+@pytest.mark.parametrize("B", [19, 333])
+def test_interaction_fwd_bwd(F, D, itself, B, request):
+    """B = 333 with the persistent grid capped at one CTA per SM (tunable 11) makes every CTA loop over several samples
+    (both shared-memory stages)."""
+    from dlrm_yx_b200 import ops, _lib
     dev = cuda()
+    _lib.set_tunable(11, 1 if B > 100 else 0)
+    request.addfinalizer(lambda: _lib.set_tunable(11, 0))
     rng = np.random.default_rng(F * 100 + D)
-    B = 19
     feat = rng.normal(size=(B, F, D)).astype(np.float32)
     df = torch.from_numpy(feat).to(dev)
     out = ops.interact_dot_fwd(df, itself)
@@ -336,10 +340,10 @@ def test_interaction_fwd_bwd(F, D, itself):
                                rtol=1e-5, atol=2e-5)
 
 
-@pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (2, 8), (32, 32)])
+@pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (2, 8), (32, 32), (5, 256)])
 @pytest.mark.parametrize("itself", [False, True])
-@pytest.mark.parametrize("warp_kernel", [0, 1])
-def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, request):
+@pytest.mark.parametrize("warp_kernel,staging,B", [(0, 0, 21), (1, 0, 21), (0, 1, 21), (0, 0, 500), (0, 1, 500)])
+def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, staging, B, request):
     """bf16-facing interaction (feature 0 in / result out / dR in / dx out as bf16, single-pass TF32 products, fp32
     accumulate) against the fp32 oracle on the SAME bf16-rounded inputs.  Bars: bf16 outputs 2^-8 relative (one bf16
     rounding, half an ulp = 2^-9, with margin) plus the TF32 operand rounding 2^-10 * sum|a||b|; fp32 outputs the
@@ -347,9 +351,11 @@ def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, request):
     from dlrm_yx_b200 import _lib, ops
     dev = cuda()
     _lib.set_tunable(4, warp_kernel)          # 1: the one-warp-per-sample experiment (interact_warp.cu)
-    request.addfinalizer(lambda: _lib.set_tunable(4, 0))
+    # staging 1: the input has a feature pitch of D + 8 (where the kernels take it: D % 32 == 0) -> one TMA bulk copy +
+    # mbarrier per sample instead of per-thread cp.async; the results must not change by a single bit
+    _lib.set_tunable(11, 1 if B > 100 else 0) # one CTA per SM: every CTA loops over several samples (both stages / phases)
+    request.addfinalizer(lambda: (_lib.set_tunable(4, 0), _lib.set_tunable(11, 0)))
     rng = np.random.default_rng(F * 100 + D + 7)
-    B = 21
     bf = torch.bfloat16
     feat = rng.normal(size=(B, F, D)).astype(np.float32)
     x_b = torch.from_numpy(feat[:, 0, :]).to(dev).to(bf)
@@ -380,6 +386,17 @@ def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, request):
     assert dx.dtype == bf
     e_dx = np.abs(dx.float().cpu().numpy() - rdx)
     assert np.all(e_dx <= 2.0 ** -8 * np.abs(rdx) + 2.0 ** -10 * mdx + 1e-6), e_dx.max()
+
+    if staging == 1 and D % 32 == 0 and warp_kernel == 0:
+        # pitched input (feature pitch D + 8, padding poisoned): TMA bulk-copy staging, same bits as above
+        dfp = torch.full((B, F, D + 8), float("nan"), device=dev)[:, :, :D]
+        dfp[:, 1:, :] = df[:, 1:, :]
+        assert dfp.stride(1) == D + 8
+        out_p = ops.interact_dot_fwd_mixed(dfp, x_b, cols, itself)
+        assert torch.equal(out_p.view(torch.int16), out.view(torch.int16))
+        dfeat_p, dx_p = ops.interact_dot_bwd_mixed(dfp, x_b, dR_b, itself)
+        assert torch.equal(dfeat_p[:, 1:, :], dfeat[:, 1:, :])
+        assert torch.equal(dx_p.view(torch.int16), dx.view(torch.int16))
 
 
 @pytest.mark.parametrize("D", [128, 6])

@@ -163,10 +163,10 @@ def main():
             report("bwd_update_" + name, ms, mn, nbytes, dict(seg=seg, K=k8, U=int(U)))
     for k in (3, 1):
         _lib.set_tunable(k, 0)
-    if only and "dense" not in only:
+    if only and "dense" not in only and "ix" not in only:
         return
 
-    if args.shape == "c4":
+    if args.shape == "c4" and (not only or "dense" in only):
         for N_ in (128, 256, 512, 1024):
             y = torch.relu(torch.randn(B, N_, device=dev)).to(torch.bfloat16)
             dy = torch.randn(B, N_, device=dev).to(torch.bfloat16)
@@ -184,13 +184,17 @@ def main():
         cols = (D + nz + 7) // 8 * 8
         xb = torch.randn((B, D), device=dev).to(torch.bfloat16)
         doutb = torch.randn((B, cols), device=dev).to(torch.bfloat16)
-        for cta in (0, 1):
-            _lib.set_tunable(4, cta)
-            ms, mn = timed(lambda: ops.interact_dot_fwd_mixed(feat, xb, cols), args.iters)
-            report("interact_mixed_fwd", ms, mn, B * ((F - 1) * D * 4 + D * 2) + B * cols * 2, dict(warp_kernel=cta))
-            ms, mn = timed(lambda: ops.interact_dot_bwd_mixed(feat, xb, doutb), args.iters)
-            report("interact_mixed_bwd", ms, mn, B * (2 * (F - 1) * D * 4 + 2 * D * 2 + cols * 2), dict(warp_kernel=cta))
-        _lib.set_tunable(4, 0)
+        featp = torch.empty((B, F, D + 8), device=dev)[:, :, :D]        # pitched input: one TMA bulk copy per sample
+        featp.copy_(feat)
+        for padded, grid in ((0, 0), (1, 0), (1, 6), (1, 8), (1, 18), (1, 24)):   # CTAs per SM of the persistent grid
+            _lib.set_tunable(11, grid)
+            fin = featp if padded else feat
+            ms, mn = timed(lambda: ops.interact_dot_fwd_mixed(fin, xb, cols), args.iters)
+            report("interact_mixed_fwd", ms, mn, B * ((F - 1) * D * 4 + D * 2) + B * cols * 2, dict(bulk_padded=padded, ctas_per_sm=grid))
+            ms, mn = timed(lambda: ops.interact_dot_bwd_mixed(fin, xb, doutb), args.iters)
+            report("interact_mixed_bwd", ms, mn, B * (2 * (F - 1) * D * 4 + 2 * D * 2 + cols * 2), dict(bulk_padded=padded, ctas_per_sm=grid))
+        _lib.set_tunable(10, 0)
+        _lib.set_tunable(11, 0)
     dout = torch.randn((B, D + nz), device=dev)
     ms, mn = timed(lambda: ops.interact_dot_bwd(feat, dout), args.iters)
     report("interact_bwd", ms, mn, 2 * B * F * D * 4 + B * (D + nz) * 4)
