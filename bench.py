@@ -178,7 +178,8 @@ def build_model(args, cfg, W):
         ok = 1
         try:
             m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W,
-                                   engine="copy" if args.exchange == "peer-copy" else "sm")
+                                   engine="copy" if args.exchange == "peer-copy" else "sm",
+                                   mixed=(args.mlp == "fused-bf16" and args.microbatches == 1))
         except Exception as ex:                                  # noqa: BLE001
             sys.stderr.write("bench: peer exchange unavailable on this rank (%r)\n" % (ex,))
             ok = 0

@@ -428,13 +428,18 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
-    def enable_peer_exchange(self, local_batch, microbatches=1, engine="sm"):
+    def enable_peer_exchange(self, local_batch, microbatches=1, engine="sm", mixed=None):
         """Replaces the NCCL all-to-all of distributed_forward by kernels that store straight into the peers'
-        memory over NVLink (ext_dist.PeerExchange).  Needs fuse_sparse_arch + batched_emb and a fixed local batch."""
+        memory over NVLink (ext_dist.PeerExchange).  Needs fuse_sparse_arch + batched_emb and a fixed local batch.
+        mixed=True (bf16 towers will be fused in: fuse_mlps) lays the interaction input out with the row pitch the
+        bf16-facing interaction kernels stage with one bulk copy per sample."""
         if not (self.fuse_sparse_arch and self.batched_emb):
             raise _lib.DlrmxError("enable_peer_exchange needs batched_emb=True and fuse_sparse_arch=True")
         dev = next(self.parameters()).device
-        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, int(self.ln_bot[-1]), dev, engine=engine)
+        D = int(self.ln_bot[-1])
+        pitch = ops.interact_feature_pitch(1 + int(sum(self.n_emb_per_rank)), D) \
+            if ((getattr(self, "_mixed", False) if mixed is None else mixed) and engine == "sm") else D
+        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, D, dev, engine=engine, feature_pitch=pitch)
         self.set_microbatches(microbatches)
         return self
 

@@ -230,7 +230,7 @@ class PeerExchange(object):
 
     tables_per_rank[p] = tables held by rank p (rank-major global table order, as the reference's cat produces)."""
 
-    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, engine="sm"):
+    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, engine="sm", feature_pitch=None):
         """engine: "sm" = remote stores issued by the lookup / push kernels; "copy" = pitched copies on the copy engines
         (the lookup writes a local block first; the SMs stay free, so micro-batched transfers overlap the towers)."""
         import torch.distributed._symmetric_memory as symm_mem
@@ -243,22 +243,27 @@ class PeerExchange(object):
         self.first = [sum(self.tpr[:p]) for p in range(self.W)]
         T_r = self.tpr[self.rank]
         F = 1 + self.T
-        n_feat = self.lb * F * self.D
+        # row pitch of the features inside a sample (floats): D, or the interaction kernels' bulk-copy pitch
+        # (ops.interact_feature_pitch) -- the remote row stores are addressed with strides, so any pitch works
+        P = self.pitch = int(feature_pitch or self.D)
+        n_feat = self.lb * F * P
         n_grad = self.W * self.lb * max(max(self.tpr), 1) * self.D     # symmetric: same size on every rank
         self._feat_flat = symm_mem.empty(n_feat, dtype=torch.float32, device=device)
         self._grad_flat = symm_mem.empty(n_grad, dtype=torch.float32, device=device)
         self.h_feat = symm_mem.rendezvous(self._feat_flat, self.group)
         self.h_grad = symm_mem.rendezvous(self._grad_flat, self.group)
-        self.feat = self._feat_flat.view(self.lb, F, self.D)                         # my interaction input
+        self.feat = self._feat_flat.view(self.lb, F, P)[:, :, :self.D]               # my interaction input
         self.grad = self._grad_flat[:self.W * self.lb * T_r * self.D].view(self.W * self.lb, T_r, self.D)
         # forward: where MY tables' rows go inside peer p's interaction input (feature slot 1 + first[rank])
-        fptr = [int(q) + (1 + self.first[self.rank]) * self.D * 4 for q in self.h_feat.buffer_ptrs]
+        fptr = [int(q) + (1 + self.first[self.rank]) * P * 4 for q in self.h_feat.buffer_ptrs]
         self.out_peers = torch.tensor(fptr, dtype=torch.int64, device=device)
         self.out_peers_host = fptr
         # backward: where MY local batch's chunk starts inside owner p's gradient buffer [W*lb, T_p, D]
         self.push_bases = [int(q) + self.rank * self.lb * self.tpr[p] * self.D * 4
                            for p, q in enumerate(self.h_grad.buffer_ptrs)]
-        self.stride_b, self.stride_t = F * self.D, self.D
+        self.stride_b, self.stride_t = F * P, P
+        if engine == "copy" and P != self.D:
+            raise ValueError("the copy-engine exchange needs an unpitched interaction input")
 
     def barrier(self, which):
         (self.h_feat if which == 0 else self.h_grad).barrier()

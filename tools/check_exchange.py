@@ -54,7 +54,7 @@ def main():
                     l.weight.copy_(torch.from_numpy(g["%s_W_%d" % (pre, j)]))
                     l.bias.copy_(torch.from_numpy(g["%s_b_%d" % (pre, j)]))
         if exchange.startswith("peer"):
-            m.enable_peer_exchange(lb, engine="copy" if exchange == "peer-copy" else "sm")
+            m.enable_peer_exchange(lb, engine="copy" if exchange == "peer-copy" else "sm", mixed=bool(bf16 and micro == 1))
         opt = None
         if bf16:
             m.fuse_mlps(lr, "sgd" if sgd else "adagrad")
