@@ -508,7 +508,7 @@ def main():
             kern[name] = {"ms": round(ms, 4), "calls_per_step": calls / K, "algorithmic_MB": round(nbytes / 1e6, 1),
                           "GBps": round(nbytes / ms / 1e6, 1), "frac": round(nbytes / ms / 1e6 / peak, 4)}
     for name in ("bwd_sort", "interact_fwd", "interact_bwd", "a2a_unpack", "a2a_pack_grad", "a2a_push_grad", "relu_bwd_bias_grad",
-                 "dense_opt"):
+                 "head_fwd", "head_bwd", "dense_opt"):
         if name in r["prof"]:
             kern[name] = {"ms": round(r["prof"][name][1], 4), "calls_per_step": r["prof"][name][0] / K}
     f = kern["embbag_fwd"]
