@@ -465,9 +465,28 @@ def embbag_c3_probe(peak, iters=20):
     return res
 
 
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """stdout carries exactly ONE JSON line: everything else that libraries write to file descriptor 1 (NCCL prints its
+    version banner there) is sent to stderr; the line itself goes to a duplicate of the original descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
+    _guard_stdout()
     if args.impl == "reference":
         if rank != 0:
             return
@@ -483,7 +502,7 @@ def main():
                 "e2e": {"value": base["value"], "unit": "samples/s", "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        _emit(line)
         return
 
     r = run_ours(args)
@@ -556,7 +575,7 @@ def main():
             line["embedding_bag_c3"] = {"error": repr(ex)}
     if W == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_reference(args, args.cpu_steps)[0]
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 if __name__ == "__main__":

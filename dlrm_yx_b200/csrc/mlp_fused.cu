@@ -231,7 +231,7 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
                 float* __restrict__ gw, float* __restrict__ gb, unsigned int* __restrict__ counters, int B, int K,
                 int rows_per_chunk, int sigmoid) {
     // partial layout: [chunks, K + 8]; column K holds the chunk's sum of dz
-    __shared__ float red[kRbRowLanes][kRbColVecs * 8 + 8];
+    __shared__ __align__(16) float red[kRbRowLanes][kRbColVecs * 8 + 8];
     __shared__ float redz[kRbRowLanes];
     __shared__ bool is_last;
     const int cv = threadIdx.x % kRbColVecs, rl = threadIdx.x / kRbColVecs;
@@ -303,20 +303,44 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    // fixed-order final sums: thread c owns column c of this column block (and one thread the dz column)
-    for (int c = threadIdx.x; c < kRbColVecs * 8 + 1; c += kRbThreads) {
-        const bool zc = (c == kRbColVecs * 8);
-        const int gc = zc ? K : blockIdx.x * kRbColVecs * 8 + c;
-        if ((zc && blockIdx.x != 0) || (!zc && gc >= K)) continue;
-        float t[4] = {0.f, 0.f, 0.f, 0.f};
-        int k = 0;
-        for (; k + 4 <= (int)gridDim.y; k += 4) {
+    // fixed-order final sums.  The tail is pure L2 latency (one CTA, chunks x (K+8) floats), so it is spread over the
+    // whole CTA: thread (cg, sl) sums float4 column group cg (the last group holds the dz column) over chunks
+    // sl, sl + S, ... with 16 independent loads in flight, and slice 0 then adds the S slice sums in slice order.
+    // (One thread per column walking all chunks 4 at a time took 45 us of this kernel's 53 at 592 chunks.)
+    {
+        constexpr int S = 3, UNR = 16;
+        const int ngroups = (kRbColVecs * 8 + 8) / 4;                 // 66 float4 groups per column block incl. the dz group
+        float4* red4 = reinterpret_cast<float4*>(&red[0][0]);         // [S][ngroups] float4 fits in the staging array
+        const int cg = threadIdx.x % ngroups, sl = threadIdx.x / ngroups;
+        const int gc0 = (cg == ngroups - 2) ? K : blockIdx.x * kRbColVecs * 8 + 4 * cg;   // group 64 = columns K..K+3
+        const bool live = sl < S && cg < ngroups - 1 && (cg == ngroups - 2 ? blockIdx.x == 0 : gc0 < K);
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (live) {
+            for (int k0 = sl; k0 < (int)gridDim.y; k0 += S * UNR) {
+                float4 v[UNR];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) t[u] += __ldcg(gw_partial + (size_t)(k + u) * KP + gc);
+                for (int u = 0; u < UNR; ++u) {
+                    const int k = k0 + u * S;
+                    v[u] = (k < (int)gridDim.y) ? __ldcg(reinterpret_cast<const float4*>(gw_partial + (size_t)k * KP + gc0))
+                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < UNR; ++u) { t.x += v[u].x; t.y += v[u].y; t.z += v[u].z; t.w += v[u].w; }
+            }
         }
-        for (; k < (int)gridDim.y; ++k) t[0] += __ldcg(gw_partial + (size_t)k * KP + gc);
-        const float tot = (t[0] + t[1]) + (t[2] + t[3]);
-        if (zc) gb[0] = tot; else gw[gc] = tot;
+        __syncthreads();                                              // everyone is done with `red` from the first stage
+        if (sl < S) red4[sl * ngroups + cg] = t;
+        __syncthreads();
+        if (live && sl == 0) {
+            float4 a = red4[cg];
+#pragma unroll
+            for (int q = 1; q < S; ++q) {
+                const float4 o = red4[q * ngroups + cg];
+                a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
+            }
+            if (cg == ngroups - 2) gb[0] = a.x;
+            else { gw[gc0] = a.x; gw[gc0 + 1] = a.y; gw[gc0 + 2] = a.z; gw[gc0 + 3] = a.w; }
+        }
     }
 }
 

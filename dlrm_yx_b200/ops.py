@@ -409,7 +409,8 @@ def head_bwd(dp, p, h, w, gw, gb, sigmoid=True):
     B, K = h.shape
     lib = _lib.load()
     col_blocks = (K + 255) // 256
-    chunks = max(1, min((B + 31) // 32, (148 * 4 + col_blocks - 1) // col_blocks))
+    # 2 CTAs per SM: the main pass is a few microseconds either way, the last CTA's reduction over the chunks is not
+    chunks = max(1, min((B + 31) // 32, (148 * 2 + col_blocks - 1) // col_blocks))
     ws = torch.empty(lib.dlrmx_head_bwd_workspace_bytes(K, chunks) // 4, dtype=torch.float32, device=h.device)
     key = (h.device, torch.cuda.current_stream().cuda_stream, "head")
     counters = _RB_COUNTERS.get(key)
