@@ -370,12 +370,12 @@ _RB_COUNTERS = {}
 def relu_bwd_bias_grad(dy, y, relu=True, chunks=None, db=None):
     """(dz bf16 [B,N], db_partial fp32 [chunks,N]): dz = dy * (y > 0) and per-chunk column sums of dz, one pass.
     With `db` (fp32 [N]) the kernel also finishes the column sums into it (deterministic last-CTA reduce).
-    chunks=None sizes the grid for >= 4 CTAs of 256 threads per SM (148 SMs) with at least 32 rows per chunk."""
+    chunks=None sizes the grid for ~2 CTAs of 256 threads per SM (148 SMs; more chunks only lengthen the last CTA's reduction) with at least 32 rows per chunk."""
     _need_cuda(dy, y, db)
     B, N = dy.shape
     col_blocks = (N + 255) // 256
     if chunks is None:
-        chunks = max(1, min((B + 31) // 32, (148 * 4 + col_blocks - 1) // col_blocks))
+        chunks = max(1, min((B + 31) // 32, (148 * 2 + col_blocks - 1) // col_blocks))
     dz = torch.empty_like(dy) if relu else dy
     part = torch.empty((chunks, N), dtype=torch.float32, device=dy.device)
     counters = None
