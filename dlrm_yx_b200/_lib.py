@@ -68,6 +68,12 @@ SIGNATURES = {
     "dlrmx_copy2d_async": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
     "dlrmx_a2a_push_grad": (c_int, [c_void_p, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     ctypes.POINTER(c_void_p), c_void_p]),
+    "dlrmx_embbag_psw_grad_i32": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p,
+                                          c_int64, c_void_p, c_void_p]),
+    "dlrmx_embbag_psw_grad_i64": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p,
+                                          c_int64, c_void_p, c_void_p]),
+    "dlrmx_bwd_coalesce_weighted": (c_int, [c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                            c_int64, c_void_p, c_void_p]),
     "dlrmx_criteo_bin_batch_i32": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                            c_void_p]),
     "dlrmx_criteo_bin_batch_i64": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,

@@ -181,13 +181,47 @@ class _BagLookup(torch.autograd.Function):
         out = ops.embbag_forward(ts, indices, offsets, B, per_sample_weights=psw)
         ctx.module = module
         ctx.has_psw = psw is not None
-        ctx.save_for_backward(indices, offsets)
+        if psw is None:
+            ctx.save_for_backward(indices, offsets)
+        else:
+            ctx.save_for_backward(indices, offsets, psw)
         return out.view(B, ts.D)
+
+    @staticmethod
+    def _backward_weighted(ctx, grad_out):
+        """Weighted pooling (dlrm_s_pytorch.py:544-547): gradient of the per-sample weights, and the table rows'
+        gradient with each lookup's weight applied -- lookups sorted by row with their original position as payload
+        (every lookup its own bag), runs reduced by dlrmx_bwd_coalesce_weighted; no [N, D] expansion."""
+        indices, offsets, psw = ctx.saved_tensors
+        m = ctx.module
+        B, N = offsets.numel(), indices.numel()
+        dev = indices.device
+        grad_out = grad_out.contiguous()
+        ts = m.table_set()
+        # before any row is updated: dpsw[l] = <grad_out[bag(l)], W[idx[l]]>
+        dpsw = ops.embbag_psw_grad(m.weight.data, indices, offsets, grad_out) if ctx.needs_input_grad[4] else None
+        if N == 0:
+            return None, None, None, None, dpsw
+        one_each = torch.arange(N + 1, dtype=indices.dtype, device=dev)
+        skey, spos = ops.bwd_sort(ts, indices, one_each, N)
+        uniq, run_off, nu = ops.bwd_segments(skey)
+        ends = torch.cat([offsets[1:].to(torch.int64), torch.tensor([N], dtype=torch.int64, device=dev)])
+        pos2bag = torch.repeat_interleave(torch.arange(B, dtype=torch.int32, device=dev), ends - offsets.to(torch.int64),
+                                          output_size=N)
+        gsum = ops.bwd_coalesce_weighted(grad_out, spos, pos2bag, psw.to(torch.float32), run_off, nu)
+        U = int(nu.item())
+        rows = (uniq[:U].to(torch.int64) & 0xFFFFFFFF)
+        if m._fused is not None:
+            kind, lr, eps = m._fused.hyper(m.weight)
+            ops.rows_update(kind, m.weight.data, m._fused.momentum(m.weight), rows.contiguous(), gsum[:U], lr, eps)
+            return None, None, None, None, dpsw
+        g = torch.sparse_coo_tensor(rows.view(1, U), gsum[:U], size=tuple(m.weight.shape), is_coalesced=True)
+        return g, None, None, None, dpsw
 
     @staticmethod
     def backward(ctx, grad_out):
         if ctx.has_psw:
-            raise _lib.DlrmxError("backward through per_sample_weights is not implemented (SURVEY.md 8.f rank 4)")
+            return _BagLookup._backward_weighted(ctx, grad_out)
         indices, offsets = ctx.saved_tensors
         m = ctx.module
         B = offsets.numel()

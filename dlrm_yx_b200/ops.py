@@ -458,3 +458,33 @@ def criteo_bin_batch(records, max_ind_range=-1, batched=True, index_dtype=None):
     if batched:
         return X, offsets, indices, tgt
     return X, offsets.view(26, B), indices.view(26, B), tgt
+
+
+def embbag_psw_grad(weight, indices, offsets, grad_out):
+    """dpsw [N] fp32: gradient of EmbeddingBag(mode="sum")'s per_sample_weights for ONE table --
+    dpsw[l] = <grad_out[bag(l)], weight[indices[l]]>."""
+    _need_cuda(weight, indices, offsets, grad_out)
+    indices, offsets, grad_out = indices.contiguous(), offsets.contiguous(), grad_out.contiguous()
+    N, B, D = indices.numel(), offsets.numel(), weight.shape[1]
+    dpsw = torch.empty(N, dtype=torch.float32, device=weight.device)
+    fn = getattr(_lib.load(), "dlrmx_embbag_psw_grad_" + _idx_suffix(indices, offsets))
+    with _timed("embbag_psw_grad"):
+        rc = fn(weight.data_ptr(), weight.stride(0), weight.shape[0], indices.data_ptr(), offsets.data_ptr(), N, B, D,
+                grad_out.data_ptr(), grad_out.stride(0), dpsw.data_ptr(), _stream())
+        _lib.check(rc, "dlrmx_embbag_psw_grad")
+    return dpsw
+
+
+def bwd_coalesce_weighted(grad_out, sorted_pos, pos2bag, psw, run_off, nuniq):
+    """Weighted coalesced gradient rows [N, D] (first num_unique valid) of ONE table: sorted_pos from bwd_sort run with
+    every lookup as its own bag, pos2bag int32 [N], psw fp32 [N] (original order)."""
+    _need_cuda(grad_out, sorted_pos, pos2bag, psw, run_off, nuniq)
+    grad_out = grad_out.contiguous()
+    N, D = sorted_pos.numel(), grad_out.shape[1]
+    gsum = torch.empty((N, D), dtype=torch.float32, device=grad_out.device)
+    with _timed("bwd_coalesce_weighted"):
+        rc = _lib.load().dlrmx_bwd_coalesce_weighted(D, grad_out.data_ptr(), grad_out.stride(0), sorted_pos.data_ptr(),
+                                                     pos2bag.contiguous().data_ptr(), psw.contiguous().data_ptr(),
+                                                     run_off.data_ptr(), nuniq.data_ptr(), N, gsum.data_ptr(), _stream())
+        _lib.check(rc, "dlrmx_bwd_coalesce_weighted")
+    return gsum

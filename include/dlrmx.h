@@ -267,6 +267,26 @@ int dlrmx_copy2d_async(void* dst, size_t dst_pitch_bytes, const void* src, size_
                        size_t width_bytes, size_t height, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Weighted pooling, backward (per-table path).  The reference gathers one weight per looked-up index from a per-row
+ * vector, `per_sample_weights = v_W_l[k].gather(0, indices)` (dlrm_s_pytorch.py:544-547); with
+ * weighted_pooling="learned" that vector is a Parameter (475-478), so EmbeddingBag's backward must deliver
+ *   dpsw[l] = < grad_out[bag(l), :], W[indices[l], :] >                                   (embbag_psw_grad)
+ *   gsum[u] = sum over the lookups l of unique row u of  psw[l] * grad_out[bag(l), :]     (bwd_coalesce_weighted)
+ * bwd_coalesce_weighted is dlrmx_bwd_coalesce with weights: the sort is run with every lookup as its own bag, so its
+ * payload sorted_pos[p] is the ORIGINAL position of sorted element p; pos2bag [N] maps a position to its bag.
+ * grad is [B, D] with row stride stride_b (one table).  No [N, D] gradient expansion is written.
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_embbag_psw_grad_i32(const float* table, int64_t table_ld, int64_t rows, const int32_t* indices,
+                              const int32_t* offsets, int64_t N, int B, int D, const float* grad, int64_t stride_b,
+                              float* dpsw, dlrmx_stream_t stream);
+int dlrmx_embbag_psw_grad_i64(const float* table, int64_t table_ld, int64_t rows, const int64_t* indices,
+                              const int64_t* offsets, int64_t N, int B, int D, const float* grad, int64_t stride_b,
+                              float* dpsw, dlrmx_stream_t stream);
+int dlrmx_bwd_coalesce_weighted(int D, const float* grad, int64_t stride_b, const int32_t* sorted_pos,
+                                const int32_t* pos2bag, const float* psw, const int32_t* run_off,
+                                const int32_t* num_unique, int64_t N, float* gsum, dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Criteo Terabyte binary records -> one batch in the hot path's input layout.
  * Replaces CriteoBinDataset.__getitem__ + _transform_features (data_loader_terabyte.py:205-252, 68-95),
  * which the reference runs on the host with torch CPU ops.

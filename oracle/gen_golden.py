@@ -169,6 +169,43 @@ def criteo_bin_golden(ns):
     return out
 
 
+def weighted_pooling_golden(ns):
+    """The reference's weighted pooling (weighted_pooling="learned": one learnable weight per table ROW, gathered per
+    looked-up index, dlrm_s_pytorch.py:475-478, 544-547) on a small model: pooled rows, their gradients, the gradient
+    of the per-row weights and the coalesced sparse table gradients, all from the unmodified DLRM_Net on CPU."""
+    np.random.seed(321)
+    torch.manual_seed(321)
+    ln_emb, D, B = np.array([50, 7, 300]), 16, 32
+    ln_bot, ln_top = np.array([5, 8, D]), np.array([D + 6, 8, 1])
+    m = ns.dlrm.DLRM_Net(D, ln_emb, ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
+                         sigmoid_top=ln_top.size - 2, weighted_pooling="learned")
+    with torch.no_grad():
+        for v in m.v_W_l:
+            v.uniform_(0.5, 1.5)
+    X, lS_o, lS_i = ns.dp.generate_dist_input_batch(int(ln_bot[0]), ln_emb, B, 6, False, "uniform", 0, 1, -1, 1)
+    Tgt = ns.dp.generate_random_output_batch(B, 1, True)
+    out = {"X": X.numpy(), "target": Tgt.numpy(), "D": np.array(D), "B": np.array(B), "ln_emb": ln_emb}
+    x = m.apply_mlp(X, m.bot_l)
+    ly = m.apply_emb(lS_o, lS_i)
+    for t in ly:
+        t.retain_grad()
+    p = m.apply_mlp(m.interact_features(x, ly), m.top_l)
+    loss = m.loss_fn(p, Tgt)
+    loss.backward()
+    for k in range(len(ln_emb)):
+        out["W_%d" % k] = m.emb_l[k].weight.detach().numpy().copy()
+        out["vW_%d" % k] = m.v_W_l[k].detach().numpy().copy()
+        out["idx_%d" % k] = lS_i[k].numpy().astype(np.int64)
+        out["off_%d" % k] = lS_o[k].numpy().astype(np.int64)
+        out["pooled_%d" % k] = ly[k].detach().numpy().copy()
+        out["d_pooled_%d" % k] = ly[k].grad.numpy().copy()
+        out["vW_grad_%d" % k] = m.v_W_l[k].grad.numpy().copy()
+        gc = m.emb_l[k].weight.grad.coalesce()
+        out["gco_idx_%d" % k] = gc._indices().numpy().copy()[0]
+        out["gco_val_%d" % k] = gc._values().numpy().copy()
+    return out
+
+
 def main():
     sys.path.insert(0, ROOT)
     from oracle.ref_shim import load_reference
@@ -177,7 +214,10 @@ def main():
     cb = criteo_bin_golden(ns)
     np.savez_compressed(os.path.join(GOLDEN, "criteo_bin.npz"), **cb)
     print("wrote criteo_bin.npz")
-    if "--only-criteo" in sys.argv:
+    wp = weighted_pooling_golden(ns)
+    np.savez_compressed(os.path.join(GOLDEN, "weighted_pooling.npz"), **wp)
+    print("wrote weighted_pooling.npz")
+    if "--only-criteo" in sys.argv or "--only-small" in sys.argv:
         return
     for case in CASES:
         out = run_case(ns, *case)

@@ -332,3 +332,26 @@ def criteo_bin_transform(records, max_ind_range=-1, batched=False):
         offsets = np.arange(26 * B + 1, dtype=np.int32)
         return x_int, offsets, indices, y
     return x_int, lS_o, lS_i, y
+
+
+def embbag_bwd_weighted(W, indices, offsets, psw, grad_out):
+    """Backward of EmbeddingBag(mode="sum") with per_sample_weights for one table, as autograd delivers it to the
+    reference (dlrm_s_pytorch.py:544-547, 571-577):
+      dpsw[l]  = <grad_out[bag(l)], W[indices[l]]>
+      sparse table gradient, coalesced: unique rows (ascending) and, per row, the sum over its lookups in original
+      order of  psw[l] * grad_out[bag(l)]  (product rounded to fp32, then added)."""
+    indices = np.asarray(indices, dtype=np.int64)
+    offsets = np.asarray(offsets, dtype=np.int64)
+    N, B = indices.size, offsets.size
+    ends = np.concatenate([offsets[1:], [N]])
+    bag = np.repeat(np.arange(B), ends - offsets)
+    dpsw = np.zeros(N, dtype=f32)
+    for l in range(N):
+        dpsw[l] = np.dot(grad_out[bag[l]].astype(np.float64), W[indices[l]].astype(np.float64))
+    uniq = np.unique(indices)
+    pos_of = {int(r): u for u, r in enumerate(uniq)}
+    g = np.zeros((uniq.size, W.shape[1]), dtype=f32)
+    for l in range(N):
+        u = pos_of[int(indices[l])]
+        g[u] = (g[u] + (f32(psw[l]) * grad_out[bag[l]]).astype(f32)).astype(f32)
+    return dpsw, uniq, g
