@@ -364,6 +364,8 @@ class DLRM_Net(nn.Module):
         for k, sparse_index_group_batch in enumerate(lS_i):
             sparse_offset_group_batch = lS_o[k]
             if self.v_W_l[k] is not None:
+                if self.v_W_l[k].device != sparse_index_group_batch.device:     # "fixed" weights are plain tensors
+                    self.v_W_l[k] = self.v_W_l[k].to(sparse_index_group_batch.device)
                 per_sample_weights = self.v_W_l[k].gather(0, sparse_index_group_batch)
             else:
                 per_sample_weights = None

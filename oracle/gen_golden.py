@@ -192,6 +192,13 @@ def weighted_pooling_golden(ns):
     p = m.apply_mlp(m.interact_features(x, ly), m.top_l)
     loss = m.loss_fn(p, Tgt)
     loss.backward()
+    out["loss"] = np.array(loss.item(), dtype=np.float32)
+    out["ln_bot"], out["ln_top"] = ln_bot, ln_top
+    for pre, mlp in (("bot", m.bot_l), ("top", m.top_l)):
+        lins = [l for l in mlp if isinstance(l, torch.nn.Linear)]
+        for j, l in enumerate(lins):
+            out["%s_W_%d" % (pre, j)] = l.weight.detach().numpy().copy()
+            out["%s_b_%d" % (pre, j)] = l.bias.detach().numpy().copy()
     for k in range(len(ln_emb)):
         out["W_%d" % k] = m.emb_l[k].weight.detach().numpy().copy()
         out["vW_%d" % k] = m.v_W_l[k].detach().numpy().copy()

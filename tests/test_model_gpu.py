@@ -263,3 +263,29 @@ def test_weighted_pooling_backward_matches_reference(golden_dir, fused):
             assert gr._nnz() == E.weight.grad._nnz()
             assert np.array_equal(gr._indices().cpu().numpy()[0], rows)
             np.testing.assert_allclose(gr._values().cpu().numpy(), vals, rtol=1e-6, atol=1e-8)
+
+
+def test_weighted_pooling_model_matches_reference(golden_dir):
+    """DLRM_Net(weighted_pooling="learned") end to end (apply_emb gathers per-row weights, dlrm_s_pytorch.py:544-547):
+    loss and the gradients of the learnable per-row weights against the reference's run on the same weights."""
+    from dlrm_yx_b200 import dlrm_net
+    g = np.load(os.path.join(golden_dir, "weighted_pooling.npz"))
+    T, D = len(g["ln_emb"]), int(g["D"])
+    np.random.seed(1)
+    m = dlrm_net.DLRM_Net(D, g["ln_emb"], g["ln_bot"], g["ln_top"], arch_interaction_op="dot", sigmoid_bot=-1,
+                          sigmoid_top=len(g["ln_top"]) - 2, weighted_pooling="learned").cuda()
+    load_mlps(m, g)
+    with torch.no_grad():
+        for k in range(T):
+            m.emb_l[k].weight.copy_(cu(g["W_%d" % k]))
+            m.v_W_l[k].copy_(cu(g["vW_%d" % k]))
+    lS_o = [cu(g["off_%d" % k]) for k in range(T)]
+    lS_i = [cu(g["idx_%d" % k]) for k in range(T)]
+    loss = m.loss_fn(m(cu(g["X"]), lS_o, lS_i), cu(g["target"]))
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), float(g["loss"]), rtol=RT)
+    for k in range(T):
+        np.testing.assert_allclose(m.v_W_l[k].grad.cpu().numpy(), g["vW_grad_%d" % k], rtol=1e-4, atol=1e-6)
+        gr = m.emb_l[k].weight.grad.coalesce()
+        assert np.array_equal(gr._indices().cpu().numpy()[0], g["gco_idx_%d" % k])
+        np.testing.assert_allclose(gr._values().cpu().numpy(), g["gco_val_%d" % k], rtol=1e-4, atol=1e-7)
