@@ -134,6 +134,13 @@ def main():
             ops.embbag_forward(ts, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=False)
         ms, mn = timed(f, args.iters)
         report("embbag_fwd", ms, mn, fwd_bytes, dict(K=k))
+
+        def fv():
+            idx, off = batches[it[0] % nbatch]
+            it[0] += 1
+            ops.embbag_forward(ts, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=True)
+        ms, mn = timed(fv, args.iters)
+        report("embbag_fwd", ms, mn, fwd_bytes, dict(K=k, validate=1))
     _lib.set_tunable(_lib.TUNE_FWD_K, 0)
 
     def s():
