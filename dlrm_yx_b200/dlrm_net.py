@@ -258,8 +258,21 @@ class DLRM_Net(nn.Module):
                 continue
             n = int(ln[i])
             a = np.sqrt(1 / n)
-            W = np.random.uniform(low=-a, high=a, size=(n, m)).astype(np.float32)
-            emb_l.append(embedding.EmbeddingBagSum(n, m, _weight=torch.tensor(W)))
+            if self.qr_flag and n > self.qr_threshold:        # dlrm_s_pytorch.py:281-289
+                from .tricks import QREmbeddingBag
+                emb_l.append(QREmbeddingBag(n, m, self.qr_collisions, operation=self.qr_operation, mode="sum", sparse=True))
+            elif self.md_flag and n > self.md_threshold:      # 290-299: narrow table + projection to the base dimension
+                from .tricks import PrEmbeddingBag
+                base = max(m)
+                _m = int(m[i])
+                EE = PrEmbeddingBag(n, _m, int(base))
+                W = np.random.uniform(low=-a, high=a, size=(n, _m)).astype(np.float32)
+                EE.embs.weight.data = torch.tensor(W)
+                emb_l.append(EE)
+            else:
+                _m = int(max(m)) if self.md_flag else m
+                W = np.random.uniform(low=-a, high=a, size=(n, _m)).astype(np.float32)
+                emb_l.append(embedding.EmbeddingBagSum(n, _m, _weight=torch.tensor(W)))
             v_W_l.append(None if weighted_pooling is None else torch.ones(n, dtype=torch.float32))
         return emb_l, v_W_l
 
@@ -276,6 +289,7 @@ class DLRM_Net(nn.Module):
                  arch_interaction_itself=False, sigmoid_bot=-1, sigmoid_top=-1, sync_dense_params=True,
                  loss_threshold=0.0, ndevices=-1, weighted_pooling=None, loss_function="bce",
                  batched_emb=False, sharder="naive", allocation=None,
+                 qr_flag=False, qr_operation="mult", qr_collisions=0, qr_threshold=200, md_flag=False, md_threshold=200,
                  # additions (keyword-only in spirit): the fused optimizer of the batched module
                  emb_optimizer=embedding.Optimizer.SGD, emb_learning_rate=0.1, emb_eps=None, emb_init="auto",
                  fuse_sparse_arch=False):
@@ -294,6 +308,11 @@ class DLRM_Net(nn.Module):
         self.weighted_pooling = ("learned" if weighted_pooling not in (None, "fixed") else weighted_pooling)
         self.batched_emb = batched_emb
         self.fbgemm_emb = False
+        # QR / mixed-dimension embedding tricks (dlrm_s_pytorch.py:425-433), per-table path only
+        self.qr_flag, self.qr_collisions, self.qr_operation, self.qr_threshold = qr_flag, qr_collisions, qr_operation, qr_threshold
+        self.md_flag, self.md_threshold = md_flag, md_threshold
+        if (qr_flag or md_flag) and batched_emb:
+            raise _lib.DlrmxError("QR / mixed-dimension embeddings use the per-table path (batched_emb=False), as in the reference")
         self.sharder = sharder
         self.emb_optimizer, self.emb_eps, self.emb_init = emb_optimizer, emb_eps, emb_init
         self.fuse_sparse_arch = bool(fuse_sparse_arch)

@@ -213,6 +213,45 @@ def weighted_pooling_golden(ns):
     return out
 
 
+def tricks_golden(ns):
+    """The reference's QREmbeddingBag (tricks/qr_embedding_bag.py, all three operations) and PrEmbeddingBag
+    (tricks/md_embedding_bag.py) on CPU: outputs, coalesced sparse gradients of the tables, projection gradient."""
+    import importlib
+    qr = importlib.import_module("tricks.qr_embedding_bag")
+    md = importlib.import_module("tricks.md_embedding_bag")
+    torch.manual_seed(99)
+    rng = np.random.default_rng(99)
+    n, D, c, B = 1000, 16, 37, 24
+    lens = rng.integers(0, 6, size=B)
+    idx = torch.from_numpy(rng.integers(0, n, size=int(lens.sum())).astype(np.int64))
+    off = torch.from_numpy(np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64))
+    out = {"idx": idx.numpy(), "off": off.numpy(), "meta": np.array([n, D, c, B])}
+    nq = int(np.ceil(n / c))
+    Wq = torch.randn(nq, D) * 0.5
+    Wr = torch.randn(c, D) * 0.5
+    out["Wq"], out["Wr"] = Wq.numpy().copy(), Wr.numpy().copy()
+    for op in ("mult", "add", "concat"):
+        E = qr.QREmbeddingBag(n, D, c, operation=op, mode="sum", sparse=True, _weight=[Wq.clone(), Wr.clone()])
+        y = E(idx, off)
+        gy = torch.randn(y.shape)
+        y.backward(gy)
+        out["qr_%s_out" % op], out["qr_%s_gy" % op] = y.detach().numpy().copy(), gy.numpy().copy()
+        for nm, w in (("q", E.weight_q), ("r", E.weight_r)):
+            gco = w.grad.coalesce()
+            out["qr_%s_g%s_idx" % (op, nm)] = gco._indices().numpy().copy()[0]
+            out["qr_%s_g%s_val" % (op, nm)] = gco._values().numpy().copy()
+    P = md.PrEmbeddingBag(n, 8, D)
+    out["md_W"], out["md_proj"] = P.embs.weight.detach().numpy().copy(), P.proj.weight.detach().numpy().copy()
+    y = P(idx, off)
+    gy = torch.randn(y.shape)
+    y.backward(gy)
+    gco = P.embs.weight.grad.coalesce()
+    out["md_out"], out["md_gy"] = y.detach().numpy().copy(), gy.numpy().copy()
+    out["md_g_idx"], out["md_g_val"] = gco._indices().numpy().copy()[0], gco._values().numpy().copy()
+    out["md_gproj"] = P.proj.weight.grad.numpy().copy()
+    return out
+
+
 def main():
     sys.path.insert(0, ROOT)
     from oracle.ref_shim import load_reference
@@ -221,6 +260,9 @@ def main():
     cb = criteo_bin_golden(ns)
     np.savez_compressed(os.path.join(GOLDEN, "criteo_bin.npz"), **cb)
     print("wrote criteo_bin.npz")
+    tg = tricks_golden(ns)
+    np.savez_compressed(os.path.join(GOLDEN, "tricks.npz"), **tg)
+    print("wrote tricks.npz")
     wp = weighted_pooling_golden(ns)
     np.savez_compressed(os.path.join(GOLDEN, "weighted_pooling.npz"), **wp)
     print("wrote weighted_pooling.npz")

@@ -289,3 +289,66 @@ def test_weighted_pooling_model_matches_reference(golden_dir):
         gr = m.emb_l[k].weight.grad.coalesce()
         assert np.array_equal(gr._indices().cpu().numpy()[0], g["gco_idx_%d" % k])
         np.testing.assert_allclose(gr._values().cpu().numpy(), g["gco_val_%d" % k], rtol=1e-4, atol=1e-7)
+
+
+def _coo(grad):
+    g = grad.coalesce()
+    return g._indices().cpu().numpy()[0], g._values().cpu().numpy()
+
+
+@pytest.mark.parametrize("op", ["mult", "add", "concat"])
+def test_qr_embedding_bag_matches_reference(golden_dir, op):
+    """tricks.QREmbeddingBag (two libdlrmx lookups + combine) against the reference's QREmbeddingBag on the same weights:
+    output and the coalesced sparse gradients of both tables (tests/golden/tricks.npz)."""
+    from dlrm_yx_b200 import tricks
+    g = np.load(os.path.join(golden_dir, "tricks.npz"))
+    n, D, c, B = [int(v) for v in g["meta"]]
+    E = tricks.QREmbeddingBag(n, D, c, operation=op, mode="sum", sparse=True, _weight=[cu(g["Wq"]), cu(g["Wr"])]).cuda()
+    y = E(cu(g["idx"]), cu(g["off"]))
+    np.testing.assert_allclose(y.detach().cpu().numpy(), g["qr_%s_out" % op], rtol=1e-6, atol=1e-7)
+    y.backward(cu(g["qr_%s_gy" % op]))
+    for nm, w in (("q", E.weight_q), ("r", E.weight_r)):
+        rows, vals = _coo(w.grad)
+        assert np.array_equal(rows, g["qr_%s_g%s_idx" % (op, nm)])
+        np.testing.assert_allclose(vals, g["qr_%s_g%s_val" % (op, nm)], rtol=1e-5, atol=1e-6)
+
+
+def test_md_embedding_bag_matches_reference(golden_dir):
+    """tricks.PrEmbeddingBag (narrow table + bias-free projection) against the reference's on the same weights."""
+    from dlrm_yx_b200 import tricks
+    g = np.load(os.path.join(golden_dir, "tricks.npz"))
+    n, D, c, B = [int(v) for v in g["meta"]]
+    P = tricks.PrEmbeddingBag(n, 8, D).cuda()
+    with torch.no_grad():
+        P.embs.weight.copy_(cu(g["md_W"]))
+        P.proj.weight.copy_(cu(g["md_proj"]))
+    y = P(cu(g["idx"]), cu(g["off"]))
+    np.testing.assert_allclose(y.detach().cpu().numpy(), g["md_out"], rtol=1e-5, atol=1e-6)
+    y.backward(cu(g["md_gy"]))
+    rows, vals = _coo(P.embs.weight.grad)
+    assert np.array_equal(rows, g["md_g_idx"])
+    np.testing.assert_allclose(vals, g["md_g_val"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(P.proj.weight.grad.cpu().numpy(), g["md_gproj"], rtol=1e-4, atol=1e-5)
+
+
+def test_model_with_qr_and_md_tables_trains():
+    """DLRM_Net(qr_flag / md_flag) builds the trick modules for tables above the threshold (dlrm_s_pytorch.py:281-299) and
+    a training step runs through them (finite loss, gradients on every table)."""
+    from dlrm_yx_b200 import dlrm_net, tricks
+    from dlrm_yx_b200 import data as D_
+    rows = np.array([500, 40, 900])
+    np.random.seed(3)
+    m = dlrm_net.DLRM_Net(16, rows, np.array([5, 8, 16]), np.array([16 + 6, 8, 1]), arch_interaction_op="dot",
+                          sigmoid_bot=-1, sigmoid_top=1, qr_flag=True, qr_collisions=7, qr_threshold=200).cuda()
+    assert isinstance(m.emb_l[0], tricks.QREmbeddingBag) and not isinstance(m.emb_l[1], tricks.QREmbeddingBag)
+    np.random.seed(3)
+    m2 = dlrm_net.DLRM_Net([4, 16, 8], rows, np.array([5, 8, 16]), np.array([16 + 6, 8, 1]), arch_interaction_op="dot",
+                           sigmoid_bot=-1, sigmoid_top=1, md_flag=True, md_threshold=200).cuda()
+    assert isinstance(m2.emb_l[0], tricks.PrEmbeddingBag) and isinstance(m2.emb_l[2], tricks.PrEmbeddingBag)
+    rng = np.random.default_rng(0)
+    X, lS_o, lS_i, tgt = D_.random_batch(list(rows), 32, 3, 5, fixed=False, rng=rng)
+    for net in (m, m2):
+        loss = net.loss_fn(net(X.cuda(), [o.cuda() for o in lS_o], [i.cuda() for i in lS_i]), tgt.cuda())
+        loss.backward()
+        assert np.isfinite(loss.item())
+        assert all(p.grad is not None for p in net.emb_l.parameters())
