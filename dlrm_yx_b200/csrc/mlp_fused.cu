@@ -201,27 +201,46 @@ dense_opt_kernel(int mode, float* __restrict__ p, float* __restrict__ acc, float
 //   backward: dz = dp * p * (1 - p);  dh[b,:] = bf16(dz * w);  gw[k] = sum_b dz[b] h[b,k];  gb = sum_b dz[b]
 //             -- per-chunk partials, finished in a fixed order by the CTA that ends last (deterministic).
 // ---------------------------------------------------------------------------------------------------------
+constexpr int kHeadRows = 4;     // rows per warp: their loads are all issued before the first is consumed
+
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
                 float* __restrict__ p, int B, int K, int sigmoid) {
     const int lane = threadIdx.x & 31;
-    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row >= B) return;
-    float acc = 0.f;
+    const int64_t row0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kHeadRows;
+    if (row0 >= B) return;
+    float acc[kHeadRows];
+#pragma unroll
+    for (int r = 0; r < kHeadRows; ++r) acc[r] = 0.f;
     for (int k8 = lane; k8 < (K >> 3); k8 += 32) {
-        const Bf16x8 hv = ld_stream16(h + row * K + 8 * k8);
+        Bf16x8 hv[kHeadRows];
+#pragma unroll
+        for (int r = 0; r < kHeadRows; ++r)
+            if (row0 + r < B) hv[r] = ld_stream16(h + (row0 + r) * K + 8 * k8);
         const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + 8 * k8));
         const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + 8 * k8) + 1);
-        const float2 a = __bfloat1622float2(hv.v[0]), b2 = __bfloat1622float2(hv.v[1]);
-        const float2 c = __bfloat1622float2(hv.v[2]), d = __bfloat1622float2(hv.v[3]);
-        acc = fmaf(a.x, w0.x, acc); acc = fmaf(a.y, w0.y, acc); acc = fmaf(b2.x, w0.z, acc); acc = fmaf(b2.y, w0.w, acc);
-        acc = fmaf(c.x, w1.x, acc); acc = fmaf(c.y, w1.y, acc); acc = fmaf(d.x, w1.z, acc); acc = fmaf(d.y, w1.w, acc);
+#pragma unroll
+        for (int r = 0; r < kHeadRows; ++r) {
+            if (row0 + r >= B) break;
+            const float2 a = __bfloat1622float2(hv[r].v[0]), b2 = __bfloat1622float2(hv[r].v[1]);
+            const float2 c = __bfloat1622float2(hv[r].v[2]), d = __bfloat1622float2(hv[r].v[3]);
+            float t = acc[r];
+            t = fmaf(a.x, w0.x, t); t = fmaf(a.y, w0.y, t); t = fmaf(b2.x, w0.z, t); t = fmaf(b2.y, w0.w, t);
+            t = fmaf(c.x, w1.x, t); t = fmaf(c.y, w1.y, t); t = fmaf(d.x, w1.z, t); t = fmaf(d.y, w1.w, t);
+            acc[r] = t;
+        }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) {
-        const float z = acc + bias[0];
-        p[row] = sigmoid ? 1.f / (1.f + expf(-z)) : z;
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < kHeadRows; ++r) acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], o);
+    }
+    if (lane < kHeadRows && row0 + lane < B) {
+        float z = acc[0];
+#pragma unroll
+        for (int r = 1; r < kHeadRows; ++r) z = (lane == r) ? acc[r] : z;
+        z += bias[0];
+        p[row0 + lane] = sigmoid ? 1.f / (1.f + expf(-z)) : z;
     }
 }
 
@@ -381,7 +400,7 @@ int dlrmx_head_fwd(const void* h_bf16, const float* w, const float* bias, float*
     DLRMX_REQUIRE(B >= 0 && K > 0 && K % 8 == 0, "head_fwd: need K %% 8 == 0");
     DLRMX_REQUIRE((((uintptr_t)h_bf16 | (uintptr_t)w) & 15) == 0, "head_fwd: 16-B alignment");
     if (B == 0) return DLRMX_OK;
-    head_fwd_kernel<<<(unsigned)ceil_div((int64_t)B * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+    head_fwd_kernel<<<(unsigned)ceil_div(ceil_div((int64_t)B, kHeadRows) * 32, 256), 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)h_bf16, w, bias, p, B, K, sigmoid);
     return check_launch("head_fwd");
 }
