@@ -76,6 +76,21 @@ def _update_on_side(emb, grad, indices, offsets, B, stride_b, stride_t, presorte
     torch.autograd.Variable._execution_engine.queue_callback(join)
 
 
+class _BCELoss(torch.nn.BCELoss):
+    """dlrm.loss_fn for --loss-function=bce (dlrm_s_pytorch.py:505-507): torch.nn.BCELoss(reduction="mean"), computed
+    by one libdlrmx kernel each way when predictions and targets are fp32 CUDA tensors (ops.bce_mean); anything else
+    (CPU tensors in host-side checks, other dtypes) takes torch's implementation."""
+
+    def __init__(self):
+        super().__init__(reduction="mean")
+
+    def forward(self, input, target):
+        if input.is_cuda and target.is_cuda and input.dtype == torch.float32 and target.dtype == torch.float32 \
+                and input.shape == target.shape and input.numel() > 0:
+            return ops.bce_mean(input, target)
+        return super().forward(input, target)
+
+
 class _SparseArchLocal(torch.autograd.Function):
     """Single-GPU fused lookup + dot interaction.  forward(x [B,D]) -> R [B, D + F(F-1)/2]."""
 
@@ -348,7 +363,7 @@ class DLRM_Net(nn.Module):
         if loss_function == "mse":
             self.loss_fn = torch.nn.MSELoss(reduction="mean")
         elif loss_function == "bce":
-            self.loss_fn = torch.nn.BCELoss(reduction="mean")
+            self.loss_fn = _BCELoss()
         else:
             sys.exit("ERROR: --loss-function=" + loss_function + " is not supported")
 

@@ -488,3 +488,44 @@ def bwd_coalesce_weighted(grad_out, sorted_pos, pos2bag, psw, run_off, nuniq):
                                                      run_off.data_ptr(), nuniq.data_ptr(), N, gsum.data_ptr(), _stream())
         _lib.check(rc, "dlrmx_bwd_coalesce_weighted")
     return gsum
+
+
+class _BCEMean(torch.autograd.Function):
+    """torch.nn.BCELoss(reduction="mean") as one kernel each way (csrc/loss.cu)."""
+
+    @staticmethod
+    def forward(ctx, p, target):
+        p, target = p.contiguous(), target.contiguous()
+        n = p.numel()
+        lib = _lib.load()
+        ws = torch.empty(max(lib.dlrmx_bce_mean_workspace_bytes(n) // 4, 1), dtype=torch.float32, device=p.device)
+        key = (p.device, torch.cuda.current_stream().cuda_stream, "bce")
+        counter = _RB_COUNTERS.get(key)
+        if counter is None:
+            counter = _RB_COUNTERS[key] = torch.zeros(1, dtype=torch.int32, device=p.device)
+        loss = torch.empty((), dtype=torch.float32, device=p.device)
+        with _timed("bce_mean"):
+            rc = lib.dlrmx_bce_mean_fwd(p.data_ptr(), target.data_ptr(), n, ws.data_ptr(), counter.data_ptr(),
+                                        loss.data_ptr(), _stream())
+            _lib.check(rc, "dlrmx_bce_mean_fwd")
+        ctx.save_for_backward(p, target)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        p, target = ctx.saved_tensors
+        dp = torch.empty_like(p)
+        dloss = dloss.contiguous().to(torch.float32)
+        with _timed("bce_mean"):
+            rc = _lib.load().dlrmx_bce_mean_bwd(p.data_ptr(), target.data_ptr(), dloss.data_ptr(), p.numel(), dp.data_ptr(),
+                                                _stream())
+            _lib.check(rc, "dlrmx_bce_mean_bwd")
+        return dp, None
+
+
+def bce_mean(p, target):
+    """Mean binary cross-entropy of predictions p against targets (both fp32 CUDA, same shape)."""
+    _need_cuda(p, target)
+    if p.dtype != torch.float32 or target.dtype != torch.float32 or p.shape != target.shape:
+        raise _lib.DlrmxError("bce_mean: p and target must be fp32 tensors of the same shape")
+    return _BCEMean.apply(p, target)

@@ -267,6 +267,20 @@ int dlrmx_copy2d_async(void* dst, size_t dst_pitch_bytes, const void* src, size_
                        size_t width_bytes, size_t height, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Loss: binary cross-entropy, mean reduction.  Replaces dlrm.loss_fn = torch.nn.BCELoss(reduction="mean")
+ * (dlrm_s_pytorch.py:505-507, called through loss_fn_wrap 170-173) and its backward: one kernel each way instead of
+ * five element-wise / reduce launches, same arithmetic as ATen (log clamped at -100, gradient denominator at 1e-12).
+ *   p, target [n] fp32;  loss [1] fp32 (device);  dloss [1] fp32 (device: the incoming gradient of the loss);
+ *   workspace: dlrmx_bce_mean_workspace_bytes(n); counter: device uint32, zero before the first call (self-resetting).
+ * The sum is deterministic (fixed tree per CTA, partials added in index order).
+ * ------------------------------------------------------------------------------------------- */
+size_t dlrmx_bce_mean_workspace_bytes(int64_t n);
+int dlrmx_bce_mean_fwd(const float* p, const float* target, int64_t n, float* workspace, unsigned int* counter,
+                       float* loss, dlrmx_stream_t stream);
+int dlrmx_bce_mean_bwd(const float* p, const float* target, const float* dloss, int64_t n, float* dp,
+                       dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Weighted pooling, backward (per-table path).  The reference gathers one weight per looked-up index from a per-row
  * vector, `per_sample_weights = v_W_l[k].gather(0, indices)` (dlrm_s_pytorch.py:544-547); with
  * weighted_pooling="learned" that vector is a Parameter (475-478), so EmbeddingBag's backward must deliver

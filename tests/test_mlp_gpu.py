@@ -262,3 +262,24 @@ def test_graphed_train_step_equals_eager_steps(golden_dir):
         np.testing.assert_allclose(wg.cpu().numpy(), we.cpu().numpy(), rtol=1e-4, atol=1e-6)
     with pytest.raises(ValueError):
         gs(X[:-1], b0[1], b0[2], tgt)                               # static shapes are enforced
+
+
+@pytest.mark.parametrize("n", [1, 37, 4096, 32768, 100003])
+def test_bce_mean_kernels_match_torch(n):
+    """ops.bce_mean against torch.nn.BCELoss(reduction="mean") on the same fp32 inputs (saturated predictions included:
+    the -100 clamp of the logs and the 1e-12 clamp of the gradient's denominator): loss 1e-5 relative (summation order), gradient 1e-6."""
+    from dlrm_yx_b200 import ops
+    torch.manual_seed(n)
+    p = torch.rand(n, 1, device="cuda")
+    p[::7] = 0.0
+    p[3::11] = 1.0
+    y = torch.round(torch.rand(n, 1, device="cuda"))
+    p1 = p.clone().requires_grad_()
+    p2 = p.clone().requires_grad_()
+    for _ in range(2):                                   # the counter resets itself
+        l1 = ops.bce_mean(p1, y)
+    l2 = torch.nn.BCELoss(reduction="mean")(p2, y)
+    torch.testing.assert_close(l1, l2, rtol=1e-5, atol=1e-6)
+    (l1 * 3.0).backward()
+    (l2 * 3.0).backward()
+    torch.testing.assert_close(p1.grad, p2.grad, rtol=1e-6, atol=1e-12)
