@@ -58,7 +58,7 @@ SIGNATURES = {
     "dlrmx_head_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "dlrmx_head_bwd_workspace_bytes": (c_size_t, [c_int, c_int]),
     "dlrmx_head_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                               c_int, c_int, c_int, c_int, c_void_p]),
+                               c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "dlrmx_dense_opt": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                                 c_void_p]),
     "dlrmx_a2a_unpack": (c_int, [c_void_p, c_int, ctypes.POINTER(c_int), c_int, c_int, c_void_p, c_int64,

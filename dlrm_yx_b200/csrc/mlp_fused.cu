@@ -248,7 +248,12 @@ __global__ void __launch_bounds__(kRbThreads)
 head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const __nv_bfloat16* __restrict__ h,
                 const float* __restrict__ w, __nv_bfloat16* __restrict__ dh, float* __restrict__ gw_partial,
                 float* __restrict__ gw, float* __restrict__ gb, unsigned int* __restrict__ counters, int B, int K,
-                int rows_per_chunk, int sigmoid) {
+                int rows_per_chunk, int sigmoid, float* __restrict__ gbp_partial, float* __restrict__ gbp) {
+    // gbp != nullptr: h is the output of a Linear + ReLU layer whose backward is fused in here -- dh leaves as that layer's
+    // dz = dh * (h > 0) and gbp [K] receives its bias gradient (column sums of the bf16-rounded dz), so the layer needs no
+    // dlrmx_relu_bwd_bias_grad pass.  gbp_partial: [chunks, K] floats.
+    const bool fuse_relu = gbp != nullptr;
+    float sb[8];
     // partial layout: [chunks, K + 8]; column K holds the chunk's sum of dz
     __shared__ __align__(16) float red[kRbRowLanes][kRbColVecs * 8 + 8];
     __shared__ float redz[kRbRowLanes];
@@ -259,7 +264,7 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
     const int KP = K + 8;
     float s[8], sz = 0.f, wv[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { s[i] = 0.f; wv[i] = (col < K) ? w[col + i] : 0.f; }
+    for (int i = 0; i < 8; ++i) { s[i] = 0.f; sb[i] = 0.f; wv[i] = (col < K) ? w[col + i] : 0.f; }
     if (col < K) {
         constexpr int U = 4;
         for (int rb = r0 + rl; rb < r1; rb += kRbRowLanes * U) {
@@ -285,7 +290,17 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
                         const float2 hf = __bfloat1622float2(hv[u].v[i]);
                         s[2 * i] = fmaf(dz[u], hf.x, s[2 * i]);
                         s[2 * i + 1] = fmaf(dz[u], hf.y, s[2 * i + 1]);
-                        o.v[i] = __floats2bfloat162_rn(dz[u] * wv[2 * i], dz[u] * wv[2 * i + 1]);
+                        float ox = dz[u] * wv[2 * i], oy = dz[u] * wv[2 * i + 1];
+                        if (fuse_relu) {
+                            ox = hf.x > 0.f ? ox : 0.f;
+                            oy = hf.y > 0.f ? oy : 0.f;
+                        }
+                        o.v[i] = __floats2bfloat162_rn(ox, oy);
+                        if (fuse_relu) {
+                            const float2 of = __bfloat1622float2(o.v[i]);
+                            sb[2 * i] += of.x;
+                            sb[2 * i + 1] += of.y;
+                        }
                     }
                     *reinterpret_cast<Bf16x8*>(dh + (size_t)r * K + col) = o;
                     sz += dz[u];
@@ -312,6 +327,21 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
         for (int q = 0; q < kRbRowLanes; ++q) t += redz[q];
         gw_partial[(size_t)blockIdx.y * KP + K] = t;
     }
+    if (fuse_relu) {          // same fixed-order column sums for the fused layer's bias gradient
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) red[rl][cv * 8 + i] = sb[i];
+        __syncthreads();
+        for (int c = threadIdx.x; c < kRbColVecs * 8; c += kRbThreads) {
+            const int gc = blockIdx.x * kRbColVecs * 8 + c;
+            if (gc < K) {
+                float t = 0.f;
+#pragma unroll
+                for (int q = 0; q < kRbRowLanes; ++q) t += red[q][c];
+                gbp_partial[(size_t)blockIdx.y * K + gc] = t;
+            }
+        }
+    }
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -333,7 +363,21 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
         const int cg = threadIdx.x % ngroups, sl = threadIdx.x / ngroups;
         const int gc0 = (cg == ngroups - 2) ? K : blockIdx.x * kRbColVecs * 8 + 4 * cg;   // group 64 = columns K..K+3
         const bool live = sl < S && cg < ngroups - 1 && (cg == ngroups - 2 ? blockIdx.x == 0 : gc0 < K);
-        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f), t2 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool live2 = fuse_relu && live && cg < ngroups - 2;
+        if (live2) {
+            for (int k0 = sl; k0 < (int)gridDim.y; k0 += S * UNR) {
+                float4 v[UNR];
+#pragma unroll
+                for (int u = 0; u < UNR; ++u) {
+                    const int k = k0 + u * S;
+                    v[u] = (k < (int)gridDim.y) ? __ldcg(reinterpret_cast<const float4*>(gbp_partial + (size_t)k * K + gc0))
+                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < UNR; ++u) { t2.x += v[u].x; t2.y += v[u].y; t2.z += v[u].z; t2.w += v[u].w; }
+            }
+        }
         if (live) {
             for (int k0 = sl; k0 < (int)gridDim.y; k0 += S * UNR) {
                 float4 v[UNR];
@@ -359,6 +403,20 @@ head_bwd_kernel(const float* __restrict__ dp, const float* __restrict__ p, const
             }
             if (cg == ngroups - 2) gb[0] = a.x;
             else { gw[gc0] = a.x; gw[gc0 + 1] = a.y; gw[gc0 + 2] = a.z; gw[gc0 + 3] = a.w; }
+        }
+        if (fuse_relu) {
+            __syncthreads();
+            if (sl < S) red4[sl * ngroups + cg] = t2;
+            __syncthreads();
+            if (live2 && sl == 0) {
+                float4 a = red4[cg];
+#pragma unroll
+                for (int q = 1; q < S; ++q) {
+                    const float4 o = red4[q * ngroups + cg];
+                    a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
+                }
+                gbp[gc0] = a.x; gbp[gc0 + 1] = a.y; gbp[gc0 + 2] = a.z; gbp[gc0 + 3] = a.w;
+            }
         }
     }
 }
@@ -405,11 +463,11 @@ int dlrmx_head_fwd(const void* h_bf16, const float* w, const float* bias, float*
     return check_launch("head_fwd");
 }
 
-size_t dlrmx_head_bwd_workspace_bytes(int K, int chunks) { return (size_t)chunks * (K + 8) * sizeof(float); }
+size_t dlrmx_head_bwd_workspace_bytes(int K, int chunks) { return (size_t)chunks * (2 * K + 8) * sizeof(float); }
 
 int dlrmx_head_bwd(const float* dp, const float* p, const void* h_bf16, const float* w, void* dh_bf16, float* gw,
                    float* gb, float* workspace, unsigned int* counters, int B, int K, int chunks, int sigmoid,
-                   dlrmx_stream_t stream) {
+                   float* gb_prev_relu, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(B >= 0 && K > 0 && K % 8 == 0 && chunks >= 1, "head_bwd: need K %% 8 == 0, chunks >= 1");
     DLRMX_REQUIRE((((uintptr_t)h_bf16 | (uintptr_t)dh_bf16) & 15) == 0, "head_bwd: 16-B alignment");
@@ -418,7 +476,8 @@ int dlrmx_head_bwd(const float* dp, const float* p, const void* h_bf16, const fl
     dim3 grid((unsigned)ceil_div(K, kRbColVecs * 8), (unsigned)chunks);
     head_bwd_kernel<<<grid, kRbThreads, 0, (cudaStream_t)stream>>>(dp, p, (const __nv_bfloat16*)h_bf16, w,
                                                                    (__nv_bfloat16*)dh_bf16, workspace, gw, gb, counters,
-                                                                   B, K, rows_per_chunk, sigmoid);
+                                                                   B, K, rows_per_chunk, sigmoid,
+                                                                   workspace + (size_t)chunks * (K + 8), gb_prev_relu);
     return check_launch("head_bwd");
 }
 }

@@ -48,6 +48,9 @@ class _LinearAct(torch.autograd.Function):
         else:
             y = torch.addmm(L.b_shadow, hb, L.w_shadow.t())
         ctx.mlp, ctx.li, ctx.in_cols = mlp, li, h.shape[1]
+        # a consumer that fuses this layer's ReLU backward + bias gradient into its own backward (the head) sets the flag
+        ctx.flag = {"pre_masked": False}
+        mlp._last_relu = (li, ctx.flag) if L.act == "relu" else None
         ctx.save_for_backward(hb, y)
         return y
 
@@ -58,10 +61,13 @@ class _LinearAct(torch.autograd.Function):
         dyb = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         dyb = dyb.contiguous()
         acc = ctx.mlp.accumulate       # several forward/backward passes per step (micro-batches): add, don't overwrite
-        gb = torch.empty_like(L.gb) if acc else L.gb
-        dz, _ = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"), db=gb)
-        if acc:
-            L.gb.add_(gb)
+        if ctx.flag["pre_masked"]:
+            dz = dyb                   # the head's backward applied this layer's ReLU mask and wrote its bias gradient
+        else:
+            gb = torch.empty_like(L.gb) if acc else L.gb
+            dz, _ = ops.relu_bwd_bias_grad(dyb, y, relu=(L.act == "relu"), db=gb)
+            if acc:
+                L.gb.add_(gb)
         gW = torch.mm(dz.t(), hb, out_dtype=torch.float32)
         if acc:
             L.gW.add_(gW)
@@ -84,6 +90,11 @@ class _Head(torch.autograd.Function):
         h = h.contiguous()
         p = ops.head_fwd(h, L.w_master.view(-1), L.b_master, sigmoid=(L.act == "sigmoid"))
         ctx.mlp, ctx.li = mlp, li
+        # the producer of h is the previous layer's Linear + ReLU: take over its ReLU backward and bias gradient
+        last = getattr(mlp, "_last_relu", None)
+        ctx.fuse_prev = bool(last is not None and last[0] == li - 1 and mlp.layers[li - 1].fused)
+        if ctx.fuse_prev:
+            last[1]["pre_masked"] = True
         ctx.save_for_backward(h, p)
         return p
 
@@ -91,13 +102,18 @@ class _Head(torch.autograd.Function):
     def backward(ctx, dp):
         h, p = ctx.saved_tensors
         L = ctx.mlp.layers[ctx.li]
+        P = ctx.mlp.layers[ctx.li - 1] if ctx.fuse_prev else None
         if ctx.mlp.accumulate:
             gW, gb = torch.empty_like(L.gW), torch.empty_like(L.gb)
-            dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), gW.view(-1), gb, sigmoid=(L.act == "sigmoid"))
+            gbp = torch.empty_like(P.gb) if P is not None else None
+            dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), gW.view(-1), gb, sigmoid=(L.act == "sigmoid"), gb_prev_relu=gbp)
             L.gW.add_(gW)
             L.gb.add_(gb)
+            if P is not None:
+                P.gb.add_(gbp)
         else:
-            dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), L.gW.view(-1), L.gb, sigmoid=(L.act == "sigmoid"))
+            dh = ops.head_bwd(dp, p, h, L.w_master.view(-1), L.gW.view(-1), L.gb, sigmoid=(L.act == "sigmoid"),
+                              gb_prev_relu=(P.gb if P is not None else None))
         return dh, None, None, None
 
 

@@ -403,8 +403,9 @@ def head_fwd(h, w, bias, sigmoid=True):
     return p
 
 
-def head_bwd(dp, p, h, w, gw, gb, sigmoid=True):
-    """dh bf16 [B, K]; writes gw [K] and gb [1] (fp32) -- backward of head_fwd."""
+def head_bwd(dp, p, h, w, gw, gb, sigmoid=True, gb_prev_relu=None):
+    """dh bf16 [B, K]; writes gw [K] and gb [1] (fp32) -- backward of head_fwd.  gb_prev_relu [K] fp32: h is the output of
+    a Linear + ReLU layer; its ReLU backward and bias gradient are fused in (the result is that layer's dz)."""
     _need_cuda(dp, p, h, w, gw, gb)
     B, K = h.shape
     lib = _lib.load()
@@ -420,7 +421,8 @@ def head_bwd(dp, p, h, w, gw, gb, sigmoid=True):
     dp = dp.contiguous()
     with _timed("head_bwd"):
         rc = lib.dlrmx_head_bwd(dp.data_ptr(), p.data_ptr(), h.data_ptr(), w.data_ptr(), dh.data_ptr(), gw.data_ptr(),
-                                gb.data_ptr(), ws.data_ptr(), counters.data_ptr(), B, K, chunks, int(sigmoid), _stream())
+                                gb.data_ptr(), ws.data_ptr(), counters.data_ptr(), B, K, chunks, int(sigmoid),
+                                _ptr(gb_prev_relu), _stream())
         _lib.check(rc, "dlrmx_head_bwd")
     return dh
 

@@ -207,6 +207,8 @@ int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* sha
  * dlrm_s_pytorch.py:227-265) on a bf16 activation h [B, K] with fp32 master weights w [K], bias [1].
  *   head_fwd: p[b] = sigmoid(<h[b,:], w> + bias)            (sigmoid = 0: no activation)
  *   head_bwd: dz = dp * p * (1 - p);  dh_bf16[b,:] = dz * w;  gw[k] = sum_b dz h[b,k];  gb[0] = sum_b dz.
+ *             gb_prev_relu != NULL: h is the output of a Linear + ReLU layer whose backward is fused in -- dh leaves as
+ *             that layer's dz = dh * (h > 0) and gb_prev_relu [K] receives its bias gradient (no relu_bwd_bias_grad pass).
  *             workspace: dlrmx_head_bwd_workspace_bytes(K, chunks); counters: ceil(K/256) uint32, zero before the
  *             first call, left zero.  Sums are finished in a fixed order (deterministic). */
 int dlrmx_head_fwd(const void* h_bf16, const float* w, const float* bias, float* p, int B, int K, int sigmoid,
@@ -214,7 +216,7 @@ int dlrmx_head_fwd(const void* h_bf16, const float* w, const float* bias, float*
 size_t dlrmx_head_bwd_workspace_bytes(int K, int chunks);
 int dlrmx_head_bwd(const float* dp, const float* p, const void* h_bf16, const float* w, void* dh_bf16, float* gw,
                    float* gb, float* workspace, unsigned int* counters, int B, int K, int chunks, int sigmoid,
-                   dlrmx_stream_t stream);
+                   float* gb_prev_relu, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Model-parallel exchange helpers.  Replaces the cat / split / contiguous copies around

@@ -125,6 +125,17 @@ def test_head_linear_sigmoid_kernels(B, K):
         assert torch.all((dh.float() - hf.grad).abs() <= 2.0 ** -8 * hf.grad.abs() + 1e-7)
         torch.testing.assert_close(gw, w.grad, rtol=1e-4, atol=1e-4 * float(w.grad.abs().max()))
         torch.testing.assert_close(gb, b.grad, rtol=1e-4, atol=1e-4 * float(b.grad.abs().max()))
+    # with the producing Linear + ReLU layer's backward fused in: dh leaves masked by (h > 0), gbp = its column sums
+    hr = torch.relu(h.float()).to(torch.bfloat16)
+    p2 = ops.head_fwd(hr, w.detach(), b.detach())
+    gbp = torch.empty(K + 1, device="cuda")[1:]
+    for _ in range(2):
+        dz = ops.head_bwd(dp, p2, hr, w.detach(), gw, gb, gb_prev_relu=gbp)
+        dzl = (dp * p2 * (1 - p2)) * w.detach()[None, :]
+        ref_dz = torch.where(hr.float() > 0, dzl, torch.zeros_like(dzl))
+        assert torch.all((dz.float() - ref_dz).abs() <= 2.0 ** -8 * ref_dz.abs() + 1e-7)
+        assert bool(((dz.float() == 0) | (hr.float() > 0)).all())
+        torch.testing.assert_close(gbp, dz.float().sum(0), rtol=1e-4, atol=1e-4 * float(dz.float().abs().sum(0).max()))
 
 
 def test_dense_adagrad_kernel_matches_reference_formula():
