@@ -51,8 +51,11 @@ __device__ __forceinline__ int32_t shfl_idx(unsigned mask, int32_t v, int src, i
 // happen one by one in index order).
 // OCC > 0 overrides the CTAs-per-SM target of the register allocation.
 // EXACT: D == VEC*G*CH, every lane owns columns of the row (no per-lane guard).
-template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT, int OCC = 0, bool EXACT = false>
-__global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2)))
+// THREADS: CTA size (224 x 4 CTAs per SM = 28 warps at up to 72 registers: between the 24 warps of 256 x 3 and the 64-register
+// budget of 256 x 4).
+template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT, int OCC = 0, bool EXACT = false,
+          int THREADS = 256>
+__global__ void __launch_bounds__(THREADS, OCC > 0 ? OCC : ((K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2)))
 embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t ld, int64_t total_bags, const float* __restrict__ psw,
@@ -195,7 +198,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     }
 }
 
-template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0>
+template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0, int THREADS = 256>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, int64_t ld, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
@@ -204,11 +207,11 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     const int64_t total_bags = windowed ? (int64_t)T * (B / lb) * mb_len : (int64_t)T * B;
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
     const int64_t groups = ceil_div(total_bags, TILE);   // one group of G lanes per tile of TILE bags
-    const int threads = 256;
+    const int threads = THREADS;
     const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
 #define DLRMX_FWD_LAUNCH(SC, EX, ...) \
-    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, SC, IdxT, OCC, EX><<<(unsigned)blocks, threads, 0, st>>>(__VA_ARGS__)
+    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, SC, IdxT, OCC, EX, THREADS><<<(unsigned)blocks, threads, 0, st>>>(__VA_ARGS__)
     const bool exact = D == VEC * G * CH;
     if (out_peers != nullptr) {
         if (exact) DLRMX_FWD_LAUNCH(true, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, mb_len);
@@ -248,13 +251,15 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, \
         mb_len, st
     // Long bags, measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the bags /
-    // 512-byte rows): ONE bag per group with 8 of its rows in flight at 3 CTAs per SM (72-74 registers, no spills) wins
-    // everywhere -- 0.60 / 0.76 / 0.99 against 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128 registers,
+    // 512-byte rows): ONE bag per group with 8 of its rows in flight, in CTAs of 224 threads at 4 CTAs per SM (28 warps,
+    // 69-72 registers, no spills): 0.80 / 0.87 / 1.06.  The same kernel in CTAs of 256 threads at 3 per SM (24 warps)
+    // reaches 0.61 / 0.78 / 0.99 -- at the C3 shape an SM owns 110.7 bags, which is three rounds of 48 resident groups
+    // but two rounds of 56 -- against 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128 registers,
     // 2 CTAs per SM, half as many work units for the launch's tail), 0.57 / 0.67 / 0.56 when squeezed to 64 registers for
     // 4 CTAs per SM (spills) and 0.56 / 0.67 / 0.84 with 16 rows in flight.  An L2 bulk prefetch ahead of the walk
     // (cp.async.bulk.prefetch.L2, lane-parallel) and a two-round register double buffer were tried and were slower.
     // FWD_K tunable (experiment variants, built for the 256- and 512-byte row geometries only): short bags 8: K=8;
-    // long bags 2 / 3: one bag per group at 4 CTAs per SM / 16 rows in flight; 8 / 4: the older two-bag variants.
+    // long bags 7: 256 x 3; 2 / 3: 256 x 4 (64 registers) / 16 rows in flight; 6: 160 x 5; 8 / 4: the older two-bag variants.
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                       \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                        \
         if constexpr (VEC_ == 4 && CH_ == 1 && G_ >= 16) {                                                  \
@@ -263,9 +268,15 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
             if (!short_bags && tune == 4) return launch_fwd<VEC_, G_, CH_, 2, 4, false, IdxT>(DLRMX_FWD_ARGS); \
             if (!short_bags && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS); \
             if (!short_bags && tune == 3) return launch_fwd<VEC_, G_, CH_, 1, 16, false, IdxT, 2>(DLRMX_FWD_ARGS); \
+            if (!short_bags && tune == 5) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224>(DLRMX_FWD_ARGS); \
+            if (!short_bags && tune == 6) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 5, 160>(DLRMX_FWD_ARGS); \
         }                                                                                                   \
         if (short_bags) return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);  \
-        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 1 ? 8 : (CH_ == 2 ? 4 : 2)), false, IdxT, 3>(DLRMX_FWD_ARGS); \
+        if constexpr (CH_ == 1) {                                                                           \
+            if (tune == 7) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 3>(DLRMX_FWD_ARGS);          \
+            return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224>(DLRMX_FWD_ARGS);                    \
+        }                                                                                                   \
+        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3>(DLRMX_FWD_ARGS);           \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
     DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)

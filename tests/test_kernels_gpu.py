@@ -105,7 +105,7 @@ def test_forward_long_bags_and_weights():
 
 
 @pytest.mark.parametrize("D", [128, 64, 32, 16, 256])
-@pytest.mark.parametrize("K", [0, 2, 3, 8, 4])
+@pytest.mark.parametrize("K", [0, 2, 3, 8, 4, 5, 6, 7])
 def test_forward_long_bag_variants_bit_exact(D, K, request):
     """Long-bag walk: every (bags in lockstep, rows in flight, CTAs per SM) variant is bit-exact with the sequential
     oracle -- loads are issued U at a time, the adds stay in index order.  Ragged lengths 0..120."""

@@ -122,7 +122,7 @@ def main():
 
     only = set(args.only.split(",")) if args.only else None
     long_bags = L > 2
-    fwd_variants = (0, 2, 3, 8, 4) if long_bags else (8, 4, 0)   # see the FWD_K tunable in csrc/embbag_fwd.cuh
+    fwd_variants = (0, 7, 6, 2, 8) if long_bags else (8, 4, 0)   # see the FWD_K tunable in csrc/embbag_fwd.cuh
     for k in fwd_variants:
         if only and "fwd" not in only:
             break
