@@ -533,11 +533,16 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 25) return launch_update<4, 32, 1, 2, 5>(P, st);
     if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 16) return launch_update<4, 32, 1, 1, 6>(P, st);
     if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 4) return launch_update<4, 32, 1, 4, 3>(P, st);
+    // 256-byte rows (D = 64, two segments per warp): experiment variants
+    if (g.vec == 4 && g.g == 16 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 2) return launch_update<4, 16, 1, 2, 4>(P, st);
     // Row-wise Adagrad on 512-byte rows: 2 positions in flight per warp at 4 CTAs per SM (64 registers, no spills) beat 4
     // positions at 3 CTAs per SM (0.175 vs 0.183 ms on the Terabyte shape: the sum-of-squares butterfly, square root and
     // division lengthen every batch, and more resident warps hide that better than deeper batches); plain SGD prefers 4.
     if (g.vec == 4 && g.g == 32 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD && get_tunable(DLRMX_TUNE_BWD_K) == 0)
         return launch_update<4, 32, 1, 2, 4>(P, st);
+    // the same holds for 256-byte rows (C3 shape, 1.48 M distinct rows: 0.261 -> 0.224 ms)
+    if (g.vec == 4 && g.g == 16 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD && get_tunable(DLRMX_TUNE_BWD_K) == 0)
+        return launch_update<4, 16, 1, 2, 4>(P, st);
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;
