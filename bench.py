@@ -203,7 +203,25 @@ def build_model(args, cfg, W):
     return m, opt
 
 
+def _ensure_built():
+    """The harness (not the product code) compiles libdlrmx.so in-tree when it is missing or stale; with several ranks
+    only local rank 0 builds, the others wait for the stamp."""
+    import time
+    sys.path.insert(0, ROOT)
+    from dlrm_yx_b200 import build
+    if not build.needs_build():
+        return
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        build.build()
+    else:
+        for _ in range(600):
+            if not build.needs_build():
+                return
+            time.sleep(1.0)
+
+
 def run_ours(args):
+    _ensure_built()
     from dlrm_yx_b200 import _lib, ops
     from dlrm_yx_b200 import extend_distributed as ext
     W = int(os.environ.get("WORLD_SIZE", "1"))
