@@ -43,17 +43,24 @@ def parse():
     ap.add_argument("--sharder", default="traffic")
     ap.add_argument("--no-graph", action="store_true",
                     help="launch the step kernel by kernel instead of replaying the captured CUDA graph")
-    ap.add_argument("--microbatches", type=int, default=1,
-                    help="N>1, peer exchange: windows of the local batch whose NVLink transfer overlaps the towers")
-    ap.add_argument("--scatter-ctas", type=int, default=0,
-                    help="N>1, peer exchange: cap on the CTAs of the NVLink push kernel (0 = full width)")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "peer-copy", "nccl"],
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = exchange fused into the kernels over NVLink peer memory; 'nccl' = all_to_all_single")
+    ap.add_argument("--replicate-below", type=int, default=100000,
+                    help="N>1: tables with fewer rows are kept on every rank (looked up for the local batch, dense gradient "
+                         "all-reduce) instead of being sharded and exchanged; 0 = shard everything as the reference does")
+    ap.add_argument("--index-dist", default="uniform", choices=["uniform", "zipf"],
+                    help="uniform: the reference's generator (dlrm_data_pytorch.py:1195-1208); zipf: P(row k) ~ k^-1.05")
+    ap.add_argument("--no-parity-check", action="store_true",
+                    help="N>1: skip the pre-timing correctness checks (peer vs NCCL step, received rows vs direct gather)")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip the ATen-on-the-same-GPU reference leg (N=1)")
     ap.add_argument("--optimizer", default="rwsadagrad", choices=["rwsadagrad", "sgd"])
     ap.add_argument("--nbatches", type=int, default=8, help="distinct synthetic batches cycled through")
-    ap.add_argument("--cpu-batch", type=int, default=4096)
-    ap.add_argument("--cpu-rows-cap", type=int, default=1000000)
-    ap.add_argument("--cpu-steps", type=int, default=4)
+    ap.add_argument("--cpu-batch", type=int, default=0, help="CPU arm batch (default: the config's own batch)")
+    ap.add_argument("--cpu-rows-cap", type=int, default=-1,
+                    help="CPU arm: cap on rows per table; -1 = none when the host has >= 160 GB available, else 10 M "
+                         "(BASELINE.md section 3), else 1 M below 48 GB")
+    ap.add_argument("--cpu-steps", type=int, default=20)
+    ap.add_argument("--cpu-warmup", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c3-probe", action="store_true", help="skip the C3-shape embedding-bag kernel lines")
     return ap.parse_args()
@@ -124,27 +131,44 @@ def config_of(args):
     return cfg
 
 
-def make_batches(cfg, B_global, local_tables, lb_slice, n, seed):
-    """n pinned host batches for one rank: dense X / targets for the LOCAL batch slice, packed int32 lookups of
-    the LOCAL tables for the FULL global batch (dlrm_wrap's split, dlrm_s_pytorch.py:145-148)."""
+def draw_ids(rng, B, L, E, dist):
+    """Row ids [B, L] of one table: the reference's uniform generator round(U * (E - 1)) (dlrm_data_pytorch.py:1195-1208),
+    or a bounded Zipf(1.05) over the rows (inverse CDF of the continuous power law; row 0 is the hottest)."""
+    u = rng.random((B, L))
+    if dist == "uniform" or E < 2:
+        return np.round(u * (E - 1)).astype(np.int32)
+    a = 1.0 - 1.05
+    k = np.floor(((float(E) ** a - 1.0) * u + 1.0) ** (1.0 / a))
+    return (np.clip(k, 1, E) - 1).astype(np.int32)
+
+
+def make_batches(cfg, B_global, local_tables, rep_tables, lb_slice, n, seed, dist="uniform"):
+    """n pinned host batches for one rank: dense X / targets for the LOCAL batch slice, packed int32 lookups of the LOCAL
+    sharded tables for the FULL global batch (dlrm_wrap's split, dlrm_s_pytorch.py:145-148) and -- with replicated
+    tables -- packed lookups of those tables for the local slice: [X, idx, off, tgt(, idx_rep, off_rep)]."""
     rng = np.random.default_rng(seed)          # same seed on every rank -> every rank draws the same global batch
     T_all, L = len(cfg["rows"]), cfg["L"]
+    lb = lb_slice.stop - lb_slice.start
     out = []
     for _ in range(n):
         X = rng.random((B_global, cfg["bot"][0]), dtype=np.float32)
         tgt = np.round(rng.random((B_global, 1))).astype(np.float32)
-        idx_parts = []
+        parts = {}
         for t in range(T_all):
-            E = cfg["rows"][t]
-            ids = np.round(rng.random((B_global, L)) * (E - 1)).astype(np.int32)
+            ids = draw_ids(rng, B_global, L, cfg["rows"][t], dist)
             if L > 1:
                 ids.sort(axis=1)
             if t in local_tables:
-                idx_parts.append(ids.reshape(-1))
-        idx = np.concatenate(idx_parts)
+                parts[t] = ids.reshape(-1)
+            elif t in rep_tables:
+                parts[t] = np.ascontiguousarray(ids[lb_slice]).reshape(-1)
+        idx = np.concatenate([parts[t] for t in local_tables]) if local_tables else np.zeros(0, np.int32)
         off = (np.arange(len(local_tables) * B_global + 1, dtype=np.int64) * L).astype(np.int32)
         host = [torch.from_numpy(np.ascontiguousarray(X[lb_slice])), torch.from_numpy(idx), torch.from_numpy(off),
                 torch.from_numpy(np.ascontiguousarray(tgt[lb_slice]))]
+        if rep_tables:
+            host.append(torch.from_numpy(np.concatenate([parts[t] for t in rep_tables])))
+            host.append(torch.from_numpy((np.arange(len(rep_tables) * lb + 1, dtype=np.int64) * L).astype(np.int32)))
         out.append([t.pin_memory() for t in host])
     return out
 
@@ -160,8 +184,9 @@ def algorithmic_bytes(N, TB, D, U, ib=4):
 # ------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------
-def build_model(args, cfg, W):
+def build_model(args, cfg, W, exchange=None):
     from dlrm_yx_b200 import data, dlrm_net, embedding, rwsadagrad
+    exchange = args.exchange if exchange is None else exchange
     D, T = cfg["D"], len(cfg["rows"])
     ln_bot = np.array(cfg["bot"])
     ln_top = np.array([data.num_interactions(T, D)] + list(cfg["top"][1:]))
@@ -171,28 +196,14 @@ def build_model(args, cfg, W):
     torch.manual_seed(123)
     m = dlrm_net.DLRM_Net(D, np.array(cfg["rows"]), ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
                           sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True, sharder=args.sharder,
-                          emb_optimizer=kind, emb_learning_rate=lr, emb_init="device").cuda()
-    if W > 1 and args.exchange.startswith("peer"):
-        # symmetric (peer-mapped) memory needs CUDA VMM + P2P on the box; every rank must take the same branch, so the
-        # outcome is agreed on with an all-reduce and the NCCL exchange is the common fallback (same results, slower)
-        ok = 1
-        try:
-            m.enable_peer_exchange(cfg["B"] if not args.global_batch else args.global_batch // W,
-                                   engine="copy" if args.exchange == "peer-copy" else "sm",
-                                   mixed=(args.mlp == "fused-bf16" and args.microbatches == 1))
-        except Exception as ex:                                  # noqa: BLE001
-            sys.stderr.write("bench: peer exchange unavailable on this rank (%r)\n" % (ex,))
-            ok = 0
-        flag = torch.tensor([ok], device="cuda")
-        torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN)
-        if int(flag.item()) == 0:
-            m._peer = None
-            args.exchange = "nccl"
-            sys.stderr.write("bench: falling back to the NCCL all-to-all exchange\n")
+                          emb_optimizer=kind, emb_learning_rate=lr, emb_init="device",
+                          replicate_rows_below=(args.replicate_below if W > 1 else 0)).cuda()
+    m.sync_replicas()
+    if W > 1 and exchange == "peer":
+        lb = cfg["B"] if not args.global_batch else args.global_batch // W
+        m.enable_peer_exchange(lb, mixed=(args.mlp == "fused-bf16"))
     if args.mlp == "fused-bf16":
         m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd")
-        if W > 1 and args.exchange.startswith("peer"):
-            m.set_microbatches(args.microbatches)
         return m, None
     dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
     if W > 1:
@@ -201,6 +212,102 @@ def build_model(args, cfg, W):
         m.top_l = ext.DDP(m.top_l, device_ids=[torch.cuda.current_device()])
     opt = (rwsadagrad.RWSAdagrad(dense, lr=lr) if args.optimizer == "rwsadagrad" else torch.optim.SGD(dense, lr=lr))
     return m, opt
+
+
+def make_step(args, m, opt):
+    autocast = torch.autocast("cuda", dtype=torch.bfloat16, enabled=(args.mlp == "bf16"))
+
+    def step(X, idx, off, tgt, idx_rep=None, off_rep=None):
+        o, i = ((off, off_rep), (idx, idx_rep)) if idx_rep is not None else (off, idx)
+        with autocast:
+            p = m(X, o, i)
+        loss = m.loss_fn(p.float(), tgt)
+        if opt is None:
+            loss.backward()
+            m.step_mlps()
+        else:
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+        return loss
+    return step
+
+
+def _sparse_state(m):
+    ts = [("tables", m._batched_module().embedding_weights.data), ("accumulators", m._batched_module().row_momentum)]
+    if m.emb_rep is not None:
+        ts += [("replicated tables", m.emb_rep.embedding_weights.data), ("replicated accumulators", m.emb_rep.row_momentum)]
+    return [(n, t) for n, t in ts if t is not None]
+
+
+def parity_step_vs_nccl(args, cfg, W, m, step, batch):
+    """N > 1, before any timing: ONE training step of the benchmark model (peer-memory exchange) and ONE of a second model
+    built from the same seeds with the NCCL all-to-all, on the same batch; loss, every local table row, every
+    accumulator and the towers must agree bit for bit (only the transport differs).  Raises on mismatch."""
+    m2, opt2 = build_model(args, cfg, W, exchange="nccl")
+    step2 = make_step(args, m2, opt2)
+    for (n, a), (_, b) in zip(_sparse_state(m), _sparse_state(m2)):
+        if not torch.equal(a, b):
+            raise SystemExit("bench parity: the two seeded builds differ before the first step (%s)" % n)
+    l1 = step(*batch)
+    l2 = step2(*batch)
+    torch.cuda.synchronize()
+    if l1.item() != l2.item():
+        raise SystemExit("bench parity: peer exchange loss %r != NCCL exchange loss %r" % (l1.item(), l2.item()))
+    checked = 0
+    for (n, a), (_, b) in zip(_sparse_state(m), _sparse_state(m2)):
+        if not torch.equal(a, b):
+            raise SystemExit("bench parity: %s differ between the peer and the NCCL exchange after one step" % n)
+        checked += a.numel()
+    for ta, tb in ((m.bot_l, m2.bot_l), (m.top_l, m2.top_l)):
+        if hasattr(ta, "master") and not torch.equal(ta.master.data, tb.master.data):
+            raise SystemExit("bench parity: tower parameters differ between the peer and the NCCL exchange")
+    del m2, opt2, step2
+    torch.cuda.empty_cache()
+    return {"peer_vs_nccl": "bit-exact", "values_compared": int(checked)}
+
+
+def parity_rows_vs_gather(cfg, W, rank, m, run, batch, nrows=1024):
+    """N > 1 with one index per lookup (pooled row == table row): the interaction input that rank 0 receives through the
+    benchmarked launch (`run`: the captured graph when there is one) against rows gathered directly from the owning
+    ranks' tables BEFORE the step touches them.  Bit-exact or raises.  Returns the number of rows compared."""
+    import torch.distributed as dist
+    if cfg["L"] != 1 or getattr(m, "_peer", None) is None:
+        return 0
+    peer = m._peer
+    lb, D = peer.lb, peer.D
+    n = min(nrows, lb)
+    Bg = lb * W
+    emb = m._batched_module()
+    idx = batch[1]
+    expect = {}                                # feature slot -> [n, D] rows of rank 0's first n samples
+    slot = 1
+    for r in range(W):
+        for j in range(peer.tpr[r]):
+            rows = torch.empty((n, D), device=idx.device)
+            if r == rank:
+                w = emb.split_weights()[j]
+                rows.copy_(w[idx[j * Bg:j * Bg + n].long()])       # rank 0 owns global samples [0, lb)
+            dist.broadcast(rows, r)
+            expect[slot] = rows
+            slot += 1
+    if m.emb_rep is not None and rank == 0:
+        ridx = batch[4]
+        for j, w in enumerate(m.emb_rep.split_weights()):
+            expect[slot + j] = w[ridx[j * lb:j * lb + n].long()].clone()
+    run(*batch)
+    torch.cuda.synchronize()
+    bad = 0
+    if rank == 0:
+        for sl, rows in expect.items():
+            if not torch.equal(peer.feat[:n, sl, :], rows):
+                bad += 1
+    flag = torch.tensor([bad], device=idx.device)
+    dist.all_reduce(flag)
+    if int(flag.item()) != 0:
+        raise SystemExit("bench parity: %d feature slots of rank 0's interaction input differ from a direct gather"
+                         % int(flag.item()))
+    return n * len(expect) if rank == 0 else 0
 
 
 def _ensure_built():
@@ -228,8 +335,6 @@ def run_ours(args):
     if W != args.gpus:
         raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N>1 with torch.distributed.run" % (args.gpus, W))
     ext.init_distributed(use_gpu=True, backend="nccl")
-    if args.scatter_ctas:
-        _lib.set_tunable(5, args.scatter_ctas)
     rank = max(ext.my_rank, 0)
     dev = torch.device("cuda", torch.cuda.current_device())
     if args.mlp == "tf32":
@@ -241,26 +346,41 @@ def run_ours(args):
     lb = cfg["B"] if not args.global_batch else args.global_batch // W
     B_global = lb * W
     T = len(cfg["rows"])
-    m, opt = build_model(args, cfg, W)
+    gpu_ref = None
+    if W == 1 and not args.no_gpu_reference:
+        try:
+            gpu_ref = gpu_reference(args, cfg)      # before our model exists: both hold the full tables in HBM
+        except Exception as ex:                     # noqa: BLE001  (the comparator must never cost the headline line)
+            gpu_ref = {"error": repr(ex)}
+        torch.cuda.empty_cache()
+    if W > 1 and args.exchange == "peer":
+        # symmetric (peer-mapped) memory needs CUDA VMM + P2P on the box; every rank must take the same branch, so the
+        # outcome is agreed on with an all-reduce and the NCCL exchange is the common fallback (same results, slower)
+        ok = 1
+        try:
+            m, opt = build_model(args, cfg, W)
+        except Exception as ex:                                  # noqa: BLE001
+            sys.stderr.write("bench: peer exchange unavailable on this rank (%r)\n" % (ex,))
+            ok, m = 0, None
+        flag = torch.tensor([ok], device="cuda")
+        torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            del m
+            torch.cuda.empty_cache()
+            args.exchange = "nccl"
+            sys.stderr.write("bench: falling back to the NCCL all-to-all exchange\n")
+            m, opt = build_model(args, cfg, W)
+    else:
+        m, opt = build_model(args, cfg, W)
     local_tables = list(range(T)) if W == 1 else list(m.local_emb_indices)
+    rep_tables = [] if W == 1 else list(m.replicated_emb_indices)
     lb_slice = slice(rank * lb, (rank + 1) * lb)
-    host = make_batches(cfg, B_global, set(local_tables), lb_slice, args.nbatches, seed=727)
+    host = make_batches(cfg, B_global, local_tables, rep_tables, lb_slice, args.nbatches, seed=727, dist=args.index_dist)
     devb = [[t.to(dev) for t in b] for b in host]
-    autocast = torch.autocast("cuda", dtype=torch.bfloat16, enabled=(args.mlp == "bf16"))
-    loss_buf = torch.zeros(1, device=dev)
-
-    def step(X, idx, off, tgt):
-        with autocast:
-            p = m(X, off, idx)
-        loss = m.loss_fn(p.float(), tgt)
-        if opt is None:
-            loss.backward()
-            m.step_mlps()
-        else:
-            opt.zero_grad(set_to_none=True)
-            loss.backward()
-            opt.step()
-        return loss
+    step = make_step(args, m, opt)
+    parity = None
+    if W > 1 and args.exchange == "peer" and not args.no_parity_check:
+        parity = parity_step_vs_nccl(args, cfg, W, m, step, devb[0])
 
     def sync():
         if W > 1:
@@ -300,6 +420,12 @@ def run_ours(args):
         for i in range(3):
             run(*devb[i % nb])
         sync()
+    if parity is not None:
+        parity["rows_checked"] = parity_rows_vs_gather(cfg, W, rank, m, run, devb[1 % nb])
+        parity["rows_check"] = ("rank 0's interaction input after the benchmarked launch (%s) == rows gathered directly from "
+                                "the owners' tables, bit for bit" % ("CUDA-graph replay" if use_graph else "eager step"))
+        ops.check_index_errors()
+        sync()
 
     # ---- timed region 1: inputs resident in HBM --------------------------------------------------
     sampler = ClockSampler(torch.cuda.current_device())
@@ -320,8 +446,7 @@ def run_ours(args):
             loss = run.run_prefetched()
             run.prefetch(*host[(i + 1) % nb])
             return float(loss.item())
-        X, idx, off, tgt = [t.to(dev, non_blocking=True) for t in hb]
-        return float(step(X, idx, off, tgt).item())          # D2H read of the step's result
+        return float(step(*[t.to(dev, non_blocking=True) for t in hb]).item())      # D2H read of the step's result
     for i in range(2):
         e2e_step(i)
     _, wall_e2e = timed(e2e_step, args.steps)
@@ -371,41 +496,152 @@ def run_ours(args):
     ms_eager = ms_prof
     clocks = sampler.stop()
     h2d = sum(t.numel() * t.element_size() for t in host[0])
-    return dict(W=W, rank=rank, cfg=cfg, lb=lb, B_global=B_global, local_tables=local_tables, ms_dev=ms_dev,
+    ops.check_index_errors()
+    return dict(W=W, rank=rank, cfg=cfg, lb=lb, B_global=B_global, local_tables=local_tables, rep_tables=rep_tables,
+                parity=parity, gpu_ref=gpu_ref, ms_dev=ms_dev,
                 wall_e2e=wall_e2e, launches=launches, prof=prof, ms_eager=ms_eager, use_graph=use_graph, prof_mode=prof_mode, clocks=clocks, h2d=h2d, devb=devb, model=m)
 
 
 # ------------------------------------------------------------------------------------------------------
 # CPU baseline / reference arm: the reference's CPU path (oracle port over the same ATen CPU operators)
 # ------------------------------------------------------------------------------------------------------
-def cpu_reference(args, steps, warmup=1):
-    """Times oracle/oracle_torch.py (nn.EmbeddingBag sparse + bmm/tril interaction + RWSAdagrad, all host threads)
-    on a bounded sample of the workload: per-step batch `--cpu-batch`, rows per table capped at `--cpu-rows-cap`
-    (the full 96 GB of tables would take minutes just to initialise on the host)."""
+def host_info():
+    model, avail = "unknown", None
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable"):
+                avail = int(line.split()[1]) / 1048576.0
+    except OSError:
+        pass
+    return model, avail
+
+
+def cpu_reference(args, steps, warmup):
+    """Times oracle/oracle_torch.py (nn.EmbeddingBag sparse + bmm/tril interaction + RWSAdagrad / SGD, all host threads) on
+    the benchmark's OWN configuration -- same tables, same batch (32768 at the Terabyte shape), same optimizer -- with the
+    protocol of BASELINE.md section 3: 5 warm-up steps, median of >= 20, per-phase wall times.  Only when the host
+    cannot hold the 96 GB of tables are rows capped (10 M per table below 160 GB available, 1 M below 48 GB); the cap is
+    written into the line's config."""
     from dlrm_yx_b200 import data
     from oracle import oracle_torch as OT
     cfg = config_of(args)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    rows = [min(r, args.cpu_rows_cap) for r in cfg["rows"]]
-    D, T, B = cfg["D"], len(rows), min(args.cpu_batch, cfg["B"])
+    cpu_model, avail = host_info()
+    need = sum(cfg["rows"]) * cfg["D"] * 4 / 2 ** 30
+    cap = args.cpu_rows_cap
+    if cap < 0:
+        cap = 0 if (avail is None or avail >= max(160.0, 1.6 * need) or need < 8) else (10000000 if avail >= 48 else 1000000)
+        if avail is None and need >= 8:
+            cap = 10000000
+    rows = [min(r, cap) if cap else r for r in cfg["rows"]]
+    D, T, B = cfg["D"], len(rows), (args.cpu_batch or cfg["B"])
     ln_top = [data.num_interactions(T, D)] + list(cfg["top"][1:])
     np.random.seed(123)
     torch.manual_seed(123)
     model = OT.Model(rows, D, cfg["bot"], ln_top, init="torch")
     rng = np.random.default_rng(727)
     batches = [data.random_batch(rows, B, cfg["L"], cfg["bot"][0], fixed=True, rng=rng) for _ in range(2)]
+    phases = {"bottom_mlp": [], "embedding_fwd": [], "interaction": [], "top_mlp_loss": [], "backward": [], "optimizer": []}
+    times = []
+
+    def one(i, record):
+        X, lS_o, lS_i, tgt = batches[i % 2]
+        t = [time.perf_counter()]
+        for p in model.params():
+            p.grad = None
+        x = model.bot(X); t.append(time.perf_counter())                               # noqa: E702
+        ly = OT.lookup(model.tables, lS_o, lS_i); t.append(time.perf_counter())      # noqa: E702
+        z = OT.interact(x, ly, model.op, model.itself); t.append(time.perf_counter())  # noqa: E702
+        loss = model.loss_fn(model.top(z), tgt); t.append(time.perf_counter())       # noqa: E702
+        loss.backward(); t.append(time.perf_counter())                                # noqa: E702
+        model.steps += 1
+        model.apply_optimizer(0.01, args.optimizer)
+        t.append(time.perf_counter())
+        if record:
+            for k, a, b in zip(phases, t[:-1], t[1:]):
+                phases[k].append((b - a) * 1e3)
+            times.append((t[-1] - t[0]) * 1e3)
     for i in range(warmup):
-        X, lS_o, lS_i, tgt = batches[i % 2]
-        model.train_step(X, lS_o, lS_i, tgt, 0.01, args.optimizer)
-    t0 = time.perf_counter()
+        one(i, False)
     for i in range(steps):
-        X, lS_o, lS_i, tgt = batches[i % 2]
-        model.train_step(X, lS_o, lS_i, tgt, 0.01, args.optimizer)
-    dt = time.perf_counter() - t0
-    sample = ("%d steps of batch %d, %s tables capped at %d rows (sum %.1f M rows), torch %s CPU ops, %d threads"
-              % (steps, B, args.config, args.cpu_rows_cap, sum(rows) / 1e6, torch.__version__, cores))
-    return dict(value=steps * B / dt, unit="samples/s", cores=cores, kind="port", sample=sample), dt / steps * 1e3, B
+        one(i, True)
+    med = float(np.median(times))
+    sample = ("median of %d steps after %d warm-ups; batch %d; %s tables%s (sum %.1f M rows, %.1f GB); torch %s CPU ops, "
+              "%d threads on %s; host RAM available %s GB"
+              % (steps, warmup, B, args.config, (" capped at %d rows" % cap) if cap else " at full size", sum(rows) / 1e6,
+                 sum(rows) * D * 4 / 1e9, torch.__version__, cores, cpu_model, "?" if avail is None else "%.0f" % avail))
+    base = dict(value=B / (med / 1e3), unit="samples/s", cores=cores, kind="port", sample=sample, cpu_model=cpu_model,
+                ms_per_step_median=med, rows_cap=cap or None, batch=B,
+                phases_ms_median={k: round(float(np.median(v)), 3) for k, v in phases.items()})
+    return base, med, B, rows
+
+
+def gpu_reference(args, cfg, steps=20, warmup=5):
+    """The reference's GPU path on THIS GPU (N = 1): the same ATen CUDA operators the unmodified reference runs with
+    --use-gpu -- nn.EmbeddingBag(sparse=True) per table, bmm + tril gather, torch's sparse SGD update (the reference
+    refuses rwsadagrad on GPU, dlrm_s_pytorch.py:1636-1637), fp32 cuBLAS towers -- strung together by
+    oracle/oracle_torch.py, CUDA-event timed as the reference times itself (dlrm_s_pytorch.py:1844-1846, 1936-1939).
+    A reported comparator, never on the product path."""
+    from dlrm_yx_b200 import data
+    from oracle import oracle_torch as OT
+    dev = torch.device("cuda", torch.cuda.current_device())
+    D, T, B = cfg["D"], len(cfg["rows"]), cfg["B"]
+    ln_top = [data.num_interactions(T, D)] + list(cfg["top"][1:])
+    np.random.seed(123)
+    torch.manual_seed(123)
+    model = OT.Model(cfg["rows"], D, cfg["bot"], ln_top, init="torch", device=dev)
+    rng = np.random.default_rng(727)
+    batches = []
+    for _ in range(4):
+        X, lS_o, lS_i, tgt = data.random_batch(cfg["rows"], B, cfg["L"], cfg["bot"][0], fixed=True, rng=rng)
+        batches.append((X.to(dev), [o.to(dev) for o in lS_o], [i.to(dev) for i in lS_i], tgt.to(dev)))
+    ev = {k: [] for k in ("step", "embedding_fwd", "interaction", "backward", "optimizer")}
+
+    def one(i, record):
+        X, lS_o, lS_i, tgt = batches[i % 4]
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(7)]
+        for p in model.params():
+            p.grad = None
+        marks[0].record()
+        x = model.bot(X)
+        marks[1].record()
+        ly = OT.lookup(model.tables, lS_o, lS_i)
+        marks[2].record()
+        z = OT.interact(x, ly, model.op, model.itself)
+        marks[3].record()
+        loss = model.loss_fn(model.top(z), tgt)
+        marks[4].record()
+        loss.backward()
+        marks[5].record()
+        model.steps += 1
+        model.apply_optimizer(0.01, "sgd")
+        marks[6].record()
+        if record:
+            ev["step"].append((marks[0], marks[6]))
+            ev["embedding_fwd"].append((marks[1], marks[2]))
+            ev["interaction"].append((marks[2], marks[3]))
+            ev["backward"].append((marks[4], marks[5]))
+            ev["optimizer"].append((marks[5], marks[6]))
+    for i in range(warmup):
+        one(i, False)
+    torch.cuda.synchronize()
+    for i in range(steps):
+        one(i, True)
+    torch.cuda.synchronize()
+    med = {k: float(np.median([a.elapsed_time(b) for a, b in v])) for k, v in ev.items()}
+    out = {"what": "ATen CUDA nn.EmbeddingBag(sparse) + bmm/tril interaction + sparse SGD + fp32 cuBLAS towers (the "
+                   "reference's --use-gpu operators via oracle/oracle_torch.py), same GPU, same shape, batch %d; CUDA events, "
+                   "median of %d steps after %d warm-ups" % (B, steps, warmup),
+           "optimizer": "sgd (the reference refuses rwsadagrad on GPU)", "ms_per_step": round(med["step"], 4),
+           "samples_per_s": B / (med["step"] / 1e3),
+           "phases_ms_median": {k: round(v, 4) for k, v in med.items() if k != "step"}}
+    del model, batches
+    return out
 
 
 def workload_name(args, cfg, W, B_global):
@@ -509,13 +745,18 @@ def main():
         if rank != 0:
             return
         cfg = config_of(args)
-        base, ms, B = cpu_reference(args, max(args.steps, 1), max(args.warmup, 1))
+        base, ms, B, rows = cpu_reference(args, max(args.steps, 1), max(args.warmup, 1))
+        capped = base["rows_cap"] is not None
         line = {"impl": "reference", "metric": "DLRM train samples/sec", "value": base["value"], "unit": "samples/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32",
                 "data": "synthetic",
-                "config": {"workload": workload_name(args, cfg, 1, cfg["B"] * args.gpus), "global_batch": cfg["B"] * args.gpus,
-                           "device": "host CPU cores (bounded sample, see cpu_baseline.sample)"},
+                "config": {"workload": workload_name(args, cfg, 1, B) + (
+                               " -- CPU arm: rows capped at %d per table (host RAM), %.1f M rows in all" % (
+                                   base["rows_cap"], sum(rows) / 1e6) if capped else ""),
+                           "global_batch": B, "per_gpu_batch": B,
+                           "device": "host CPU cores, one process (%d threads, %s)" % (base["cores"], base["cpu_model"]),
+                           "rows_cap": base["rows_cap"]},
                 "cpu_baseline": base,
                 "e2e": {"value": base["value"], "unit": "samples/s", "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": 0},
@@ -535,38 +776,45 @@ def main():
     # distinct rows touched per step on rank 0 (measured on the first resident batch)
     from dlrm_yx_b200 import ops
     emb = r["model"]._batched_module()
-    skey, _ = ops.bwd_sort(emb.table_set(), r["devb"][0][1], r["devb"][0][2], Bg)
-    U = int(ops.bwd_segments(skey)[2].item())
+    U = 0
+    if Tl > 0:
+        skey, _ = ops.bwd_sort(emb.table_set(), r["devb"][0][1], r["devb"][0][2], Bg)
+        U = int(ops.bwd_segments(skey)[2].item())
     fwd_b, bwd_b = algorithmic_bytes(Nl, Tl * Bg, D, U)
     kern = {}
     for name, nbytes in (("embbag_fwd", fwd_b), ("bwd_update", bwd_b)):
         if name in r["prof"]:
             calls, ms = r["prof"][name]
-            kern[name] = {"ms": round(ms, 4), "calls_per_step": calls / K, "algorithmic_MB": round(nbytes / 1e6, 1),
-                          "GBps": round(nbytes / ms / 1e6, 1), "frac": round(nbytes / ms / 1e6 / peak, 4)}
-    for name in ("bwd_sort", "interact_fwd", "interact_bwd", "a2a_unpack", "a2a_pack_grad", "a2a_push_grad", "relu_bwd_bias_grad",
-                 "head_fwd", "head_bwd", "dense_opt"):
-        if name in r["prof"]:
+            kern[name] = {"ms": round(ms, 4), "calls_per_step": calls / K}
+            if W == 1:      # one launch per step at N = 1: the algorithmic bytes of that launch
+                kern[name].update({"algorithmic_MB": round(nbytes / 1e6, 1), "GBps": round(nbytes / ms / 1e6, 1),
+                                   "frac": round(nbytes / ms / 1e6 / peak, 4)})
+    for name in r["prof"]:
+        if name not in kern:
             kern[name] = {"ms": round(r["prof"][name][1], 4), "calls_per_step": r["prof"][name][0] / K}
-    f = kern["embbag_fwd"]
+    f = kern.get("embbag_fwd", {"ms": None})
     traffic = None                       # DRAM bytes per launch of that kernel from the committed ncu --set full capture
-    tp = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")
+    tp = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")
     if os.path.exists(tp) and W == 1 and args.config == "terabyte" and not args.rows_cap:
         tj = json.load(open(tp))
         traffic = tj["embbag_fwd_kernel"]["dram_read_bytes"] + tj["embbag_fwd_kernel"]["dram_write_bytes"]
+    mlp_txt = {"fused-bf16": "bf16 in / fp32 accumulate (tcgen05 GEMMs), bf16 activations"}.get(args.mlp, args.mlp)
+    ix_txt = ("single-pass TF32 products, fp32 accumulate, bf16 x / R / dR / dx" if args.mlp == "fused-bf16"
+              else "3xTF32 (fp32-accurate), fp32 I/O")
     line = {
         "metric": "DLRM train samples/sec", "value": Bg * K / (r["ms_dev"] / 1e3), "unit": "samples/s",
         "n_gpus": W, "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / K,
         "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
-        "dtype": "fp32 (embedding/interaction/sparse optimizer fp32; MLP GEMMs %s)"
-                 % {"fused-bf16": "bf16 in / fp32 accumulate"}.get(args.mlp, args.mlp), "data": "synthetic",
+        "dtype": "fp32 embedding tables, pooled rows, gradients and sparse optimizer; interaction: %s; MLP GEMMs: %s"
+                 % (ix_txt, mlp_txt), "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, W, Bg), "global_batch": Bg, "per_gpu_batch": lb,
-                   "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder), "
-                   "data-parallel MLPs (flat-gradient all-reduce), %s" % (
-                       W, args.sharder, "exchange fused into the lookup / gradient kernels over NVLink peer memory"
-                       if args.exchange == "peer" else ("pitched copy-engine copies into NVLink peer memory, %d micro-batches"
-                                                       % args.microbatches if args.exchange == "peer-copy"
-                                                       else "NCCL all-to-all")),
+                   "index_distribution": args.index_dist,
+                   "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder) for the %d tables "
+                   "with >= %d rows, the other %d replicated on every rank (local lookups, dense-gradient all-reduce); "
+                   "data-parallel MLPs (flat-gradient all-reduce); %s" % (
+                       W, args.sharder, len(cfg["rows"]) - len(r["rep_tables"]), args.replicate_below, len(r["rep_tables"]),
+                       "exchange fused into the lookup / gradient kernels over NVLink peer memory"
+                       if args.exchange == "peer" else "NCCL all-to-all"),
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"
                          % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * 4 / 1e9, args.nbatches),
                    "rows_cap": args.rows_cap or None},
@@ -574,25 +822,43 @@ def main():
                 "d2h_bytes_per_step": 4, "ms_per_step": r["wall_e2e"] / K},
         "gpu_launches": r["launches"],
         "clocks": r["clocks"],
-        "roofline": {"kernel": "embbag_fwd_kernel (table-batched embedding-bag forward)", "bound": "hbm",
-                     "achieved": f["GBps"], "peak": peak, "unit": "GB/s", "frac": f["frac"], "traffic": traffic,
-                     "peak_source": peak_src, "algorithmic_bytes_per_launch": fwd_b,
-                     "ms_per_launch": f["ms"],
-                     "timing": ("CUDA events (external event-record nodes) around each launch inside a single-stream CUDA "
-                                "graph of the same step, replayed %d times right after the timed regions (%.3f ms/step)"
-                                if r["prof_mode"] == "graph" else
-                                "CUDA events around each launch, %d eager single-stream steps right after the timed "
-                                "regions (%.3f ms/step)") % (K, r["ms_eager"] / K)},
         "launch_mode": "cuda-graph (whole step)" if r["use_graph"] else "eager",
         "kernels": kern,
     }
+    timing = (("CUDA events (external event-record nodes) around each launch inside a single-stream CUDA "
+               "graph of the same step, replayed %d times right after the timed regions (%.3f ms/step)"
+               if r["prof_mode"] == "graph" else
+               "CUDA events around each launch, %d eager single-stream steps right after the timed "
+               "regions (%.3f ms/step)") % (K, r["ms_eager"] / K))
+    if W == 1 and "GBps" in f:
+        line["roofline"] = {"kernel": "embbag_fwd_kernel (table-batched embedding-bag forward)", "bound": "hbm",
+                            "achieved": f["GBps"], "peak": peak, "unit": "GB/s", "frac": f["frac"], "traffic": traffic,
+                            "peak_source": peak_src, "algorithmic_bytes_per_launch": fwd_b, "ms_per_launch": f["ms"],
+                            "timing": timing}
+    else:
+        # N > 1: the lookup of the sharded tables is NVLink-bound (remote row stores): bytes that leave this rank / time
+        remote = (W - 1) / W * Tl * Bg * D * 4
+        ms = f["ms"]
+        line["roofline"] = {"kernel": "embbag_fwd_kernel<SCATTER> (lookup storing pooled rows into the peers' memory)",
+                            "bound": "nvlink", "achieved": round(remote / ms / 1e6, 1) if ms else None, "peak": 770.0,
+                            "unit": "GB/s", "frac": round(remote / ms / 1e6 / 770.0, 4) if ms else None, "traffic": None,
+                            "peak_source": "B200_PROFILING.md: measured peer copy 770 GB/s per direction (900 nominal)",
+                            "algorithmic_bytes_per_launch": remote, "ms_per_launch": ms, "timing": timing}
+    if r["parity"] is not None:
+        line["parity"] = r["parity"]
+    if r["gpu_ref"] is not None:
+        line["gpu_reference"] = r["gpu_ref"]
+        if "samples_per_s" in r["gpu_ref"]:
+            line["gpu_reference"]["ours_over_it"] = round(line["value"] / r["gpu_ref"]["samples_per_s"], 2)
     if W == 1 and args.config == "terabyte" and not args.no_c3_probe:
         try:
             line["embedding_bag_c3"] = embbag_c3_probe(peak)
         except Exception as ex:                       # the probe must never cost the headline line
             line["embedding_bag_c3"] = {"error": repr(ex)}
     if W == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_reference(args, args.cpu_steps)[0]
+        del r["model"], r["devb"]
+        torch.cuda.empty_cache()
+        line["cpu_baseline"] = cpu_reference(args, args.cpu_steps, args.cpu_warmup)[0]
     _emit(line)
 
 

@@ -24,27 +24,29 @@ SIGNATURES = {
     "dlrmx_embbag_fwd_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,
                                      c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "dlrmx_embbag_fwd_scatter_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
-                                             c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64,
+                                             c_int64, c_void_p, c_void_p, c_int, c_int64, c_int64,
                                              c_void_p, c_void_p]),
     "dlrmx_embbag_fwd_scatter_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
-                                             c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64,
+                                             c_int64, c_void_p, c_void_p, c_int, c_int64, c_int64,
                                              c_void_p, c_void_p]),
     "dlrmx_bwd_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "dlrmx_bwd_sort_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p,
-                                   c_void_p, c_void_p, c_size_t, c_void_p]),
+                                   c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "dlrmx_bwd_sort_i64": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p,
-                                   c_void_p, c_void_p, c_size_t, c_void_p]),
+                                   c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "dlrmx_bwd_segments_workspace_bytes": (c_size_t, [c_int64]),
     "dlrmx_bwd_segments": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                    c_void_p]),
     "dlrmx_bwd_update_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "dlrmx_bwd_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_int64,
-                                 c_int64, c_void_p, c_void_p, c_int64, c_float, c_float, c_void_p, c_size_t,
+                                 c_int64, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_size_t,
                                  c_void_p]),
     "dlrmx_bwd_coalesce": (c_int, [c_int, c_int, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_void_p, c_void_p]),
     "dlrmx_rows_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float,
                                   c_float, c_void_p]),
+    "dlrmx_dense_rows_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_float, c_float,
+                                        c_void_p]),
     "dlrmx_interact_dot_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64,
                                        c_void_p]),
     "dlrmx_interact_dot_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64,
@@ -65,7 +67,6 @@ SIGNATURES = {
                                  c_int, c_void_p]),
     "dlrmx_a2a_pack_grad": (c_int, [c_void_p, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     c_void_p, c_void_p]),
-    "dlrmx_copy2d_async": (c_int, [c_void_p, c_size_t, c_void_p, c_size_t, c_size_t, c_size_t, c_void_p]),
     "dlrmx_a2a_push_grad": (c_int, [c_void_p, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     ctypes.POINTER(c_void_p), c_void_p]),
     "dlrmx_bce_mean_workspace_bytes": (c_size_t, [c_int64]),
@@ -85,12 +86,11 @@ SIGNATURES = {
 
 OPT_SGD = 0
 OPT_RWSADAGRAD = 1
-TUNE_FWD_K = 0
-TUNE_BWD_K = 1
+# test hooks (include/dlrmx.h: dlrmx_set_tunable)
 TUNE_IX_CUDACORE = 2   # 1: force the CUDA-core interaction kernels (default: 3xTF32 tensor-core kernels)
 TUNE_BWD_SEG = 3       # sorted positions per group of the fused update (32/64/128/256; 0: chosen per optimizer)
-TUNE_IX_WARP = 4       # 1: one-warp-per-sample bf16-facing interaction kernels (experiment, measured slower)
-TUNE_PUSH_CTAS = 5     # cap on the CTAs of the NVLink gradient-push kernel (0: full width)
+TUNE_IX_STAGE = 10     # 1: per-thread cp.async staging instead of TMA bulk copies (interaction kernels)
+TUNE_IX_GRID = 11      # CTAs per SM of the interaction kernels' persistent grid
 
 _lib = None
 

@@ -29,7 +29,8 @@ _ptr_cache = {}
 
 def _table_ptrs(w, toff):
     """Device array of per-table base pointers for a concatenated weight matrix (cached per storage)."""
-    key = (w.data_ptr(), toff.data_ptr(), toff.numel(), w.device.index)
+    # _version: table_offsets rewritten in place under the same pointer must not hit a stale entry
+    key = (w.data_ptr(), toff.data_ptr(), toff.numel(), w.device.index, toff._version)
     hit = _ptr_cache.get(key)
     if hit is None:
         rows = toff.to(torch.int64)

@@ -100,21 +100,6 @@ static int a2a_layout(float* chunks, float* block, int64_t bsb, int feat_off, in
 }  // namespace dlrmx
 
 extern "C" {
-int dlrmx_copy2d_async(void* dst, size_t dst_pitch_bytes, const void* src, size_t src_pitch_bytes, size_t width_bytes,
-                       size_t height, dlrmx_stream_t stream) {
-    using namespace dlrmx;
-    DLRMX_REQUIRE(dst != nullptr && src != nullptr && width_bytes <= dst_pitch_bytes && width_bytes <= src_pitch_bytes,
-                  "copy2d_async: bad arguments");
-    if (width_bytes == 0 || height == 0) return DLRMX_OK;
-    const cudaError_t e = cudaMemcpy2DAsync(dst, dst_pitch_bytes, src, src_pitch_bytes, width_bytes, height,
-                                            cudaMemcpyDefault, (cudaStream_t)stream);
-    if (e != cudaSuccess) {
-        set_error("copy2d_async: %s", cudaGetErrorString(e));
-        return DLRMX_E_CUDA;
-    }
-    return DLRMX_OK;
-}
-
 int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D, float* const* host_peer_chunk_bases,
                         dlrmx_stream_t stream) {
@@ -138,8 +123,6 @@ int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
     const int64_t total = (int64_t)lb * T * (vec ? D / 4 : D);
     int64_t nblk = ceil_div(total, 256);
     if (nblk > (int64_t)kSMs * 16) nblk = (int64_t)kSMs * 16;
-    const int cap = get_tunable(DLRMX_TUNE_SCATTER_CTAS);       // narrow launch: NVLink-bound, leaves SMs to the towers
-    if (cap > 0 && nblk > cap) nblk = cap;
     cudaStream_t st = (cudaStream_t)stream;
     if (vec) a2a_push_kernel<4><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, feat_off, rs, pb, lb, D);
     else     a2a_push_kernel<1><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, feat_off, rs, pb, lb, D);

@@ -32,8 +32,22 @@ inline int check_launch(const char* what) {
 
 constexpr int kSMs = 148;  // B200
 
-// Experiment knobs (dlrmx_set_tunable); 0 = default.
-enum { DLRMX_TUNE_FWD_K = 0, DLRMX_TUNE_BWD_K = 1, DLRMX_TUNE_BWD_SEG = 3, DLRMX_TUNE_SCATTER_CTAS = 5, DLRMX_TUNE_COUNT = 16 };
+// Per-device one-time setup (cudaFuncSetAttribute opt-ins are per device): first() is true once per CUDA device.
+struct DeviceOnce {
+    std::atomic<bool> done[64];
+    DeviceOnce() { for (auto& d : done) d.store(false); }
+    bool first() {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+        return !done[dev].exchange(true);
+    }
+};
+
+// Test hooks (dlrmx_set_tunable); 0 = default.  2: force the CUDA-core interaction kernels; 3: sorted positions per
+// group of the fused update (32/64/128/256); 10: cp.async staging instead of TMA bulk copies in the interaction kernels;
+// 11: CTAs per SM of the interaction kernels' persistent grid.  They select between code paths that ship anyway (tests
+// compare them bit for bit); the kernel-variant sweeps of round 1 are gone (numbers in DESIGN.md).
+enum { DLRMX_TUNE_BWD_SEG = 3, DLRMX_TUNE_COUNT = 16 };
 int get_tunable(int which);
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

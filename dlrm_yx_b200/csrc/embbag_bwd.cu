@@ -69,11 +69,7 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
             const int t = bag / P.B;
             const int b = bag - t * P.B;
             gptr = P.grad + (int64_t)b * P.stride_b + (int64_t)t * P.stride_t;    // row start; col0 added after broadcast
-            if (last) {
-                const int64_t row = (int64_t)key - P.row_base[t];
-                wptr = P.tables[t] + row * P.ld;
-                if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mptr = P.moms != nullptr ? P.moms[t] + row : wptr + P.D;
-            }
+            if (last) run_target(P, key, bag, wptr, mptr);
         }
         const unsigned lastmask = (__ballot_sync(gmask, last) >> gshift);
 
@@ -209,21 +205,15 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
             if (sh_flag[v] & kHeadClosed) { closed = true; break; }
         }
         if (closed) {
-            const uint32_t key = skey[p1 - 1];
-            const int bag = sbag[p1 - 1];
-            const int t = bag / P.B;
-            const int64_t row = (int64_t)key - P.row_base[t];
-            float* wp = P.tables[t] + row * P.ld + col0;
+            float* wp;
+            float* mp;
+            run_target(P, skey[p1 - 1], sbag[p1 - 1], wp, mp);
+            wp += col0;
             RowVec<VEC> w[CH];
 #pragma unroll
             for (int c = 0; c < CH; ++c)
                 if (EXACT || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
-            float* mp = nullptr;
-            float mo = 0.f;
-            if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-                mp = P.moms != nullptr ? P.moms[t] + row : P.tables[t] + row * P.ld + P.D;
-                mo = *mp;
-            }
+            const float mo = (P.optimizer == DLRMX_OPT_RWSADAGRAD) ? *mp : 0.f;
             apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
         } else {                                   // the run leaves the CTA: one tail partial per CTA
             store_partial<VEC, G, CH>(P.tail_partial, blockIdx.x, P.D, col0, acc);
@@ -319,20 +309,15 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
         }
         s += cnt;
     }
-    const int bag = P.sbag[p1 - 1];
-    const int t = bag / P.B;
-    const int64_t row = (int64_t)key - P.row_base[t];
-    float* wp = P.tables[t] + row * P.ld + col0;
+    float* wp;
+    float* mp;
+    run_target(P, key, P.sbag[p1 - 1], wp, mp);
+    wp += col0;
     RowVec<VEC> w[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c)
         if (col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
-    float* mp = nullptr;
-    float mo = 0.f;
-    if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
-        mp = P.moms != nullptr ? P.moms[t] + row : P.tables[t] + row * P.ld + P.D;
-        mo = *mp;
-    }
+    const float mo = (P.optimizer == DLRMX_OPT_RWSADAGRAD) ? *mp : 0.f;
     apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
 }
 
@@ -393,6 +378,7 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
     const int64_t row = rows[u];
     BwdParams P;
     P.optimizer = optimizer; P.D = D; P.ld = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
+    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr;
     RowVec<VEC> g[CH], w[CH];
     float* wp = W + row * D + col0;
     const float* gp = gsum + u * D + col0;
@@ -411,6 +397,63 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
         mo = *mp;
     }
     apply_row<VEC, G, CH>(P, wp, mp, mo, w, g, col0);
+}
+
+// Replicated (data-parallel) tables: gsum [rows, D] holds the pooled-row gradients of the whole global batch summed per
+// row (every rank accumulated its local batch into a zeroed buffer, the buffers were all-reduced).  Each group of G lanes
+// takes rows r, r + stride, ...: a row whose summed gradient is all zero was not looked up (or cancels exactly) and keeps
+// its bits -- as in the reference's sparse step, where only coalesced rows are touched (optim/rwsadagrad.py:97-113) --
+// every other row gets the optimizer step, and its gradient row is cleared for the next step.
+template <int VEC, int G, int CH>
+__global__ void __launch_bounds__(256)
+dense_rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom, float* __restrict__ gsum,
+                         int64_t rows, int D, int64_t ld, float lr, float eps) {
+    const int gl = threadIdx.x & (G - 1);
+    const unsigned gmask = group_mask<G>();
+    const int col0 = gl * VEC;
+    BwdParams P;
+    P.optimizer = optimizer; P.D = D; P.ld = ld; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
+    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr;
+    const int64_t ngroups = ((int64_t)gridDim.x * blockDim.x) / G;
+    for (int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; r < rows; r += ngroups) {
+        RowVec<VEC> g[CH], w[CH];
+        float* gp = gsum + r * D + col0;
+        bool nz = false;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            g[c].zero();
+            if (col0 + c * G * VEC < D) {
+                g[c].load(gp + c * G * VEC);
+                nz = nz || g[c].sumsq() != 0.f;
+            }
+        }
+        if (__ballot_sync(gmask, nz) == 0u) continue;           // group-uniform: the whole row is zero
+        float* wp = W + r * ld + col0;
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+            if (col0 + c * G * VEC < D) w[c].load(wp + c * G * VEC);
+        float* mp = nullptr;
+        float mo = 0.f;
+        if (optimizer == DLRMX_OPT_RWSADAGRAD) {
+            mp = mom + r;
+            mo = *mp;
+        }
+        apply_row<VEC, G, CH>(P, wp, mp, mo, w, g, col0);
+        RowVec<VEC> z;
+        z.zero();
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+            if (col0 + c * G * VEC < D) z.store(gp + c * G * VEC);
+    }
+}
+
+template <int VEC, int G, int CH>
+static int launch_dense_rows_update(int optimizer, float* W, float* mom, float* gsum, int64_t rows, int D, int64_t ld,
+                                    float lr, float eps, cudaStream_t st) {
+    int64_t blocks = ceil_div(rows * G, 256);
+    if (blocks > (int64_t)kSMs * 8) blocks = (int64_t)kSMs * 8;
+    dense_rows_update_kernel<VEC, G, CH><<<(unsigned)blocks, 256, 0, st>>>(optimizer, W, mom, gsum, rows, D, ld, lr, eps);
+    return check_launch("dense_rows_update");
 }
 
 template <int VEC, int G, int CH>
@@ -485,7 +528,7 @@ static int seg_len_for(int64_t N, int optimizer) {
 
 static size_t update_workspace_bytes(int64_t N, int D) {
     const int64_t nseg = ceil_div(N > 0 ? N : 1, kSeg);       // sized for the smallest segment length
-    return align_up((size_t)nseg * D * 4, 256) * 2;
+    return align_up((size_t)nseg * D * 4, 256) * 2 + align_up((size_t)(D + 4) * 4, 256);   // + the scratch row
 }
 
 }  // namespace dlrmx
@@ -495,8 +538,8 @@ size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D) { return dlrmx::update
 
 int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, const int64_t* table_row_base,
                      int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
-                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, float lr, float eps,
-                     void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
+                     float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || optimizer == DLRMX_OPT_RWSADAGRAD, "bwd_update: bad optimizer %d", optimizer);
     const int64_t ld = table_ld > 0 ? table_ld : D;
@@ -521,27 +564,17 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
     P.head_partial = (float*)workspace;
     P.tail_partial = (float*)((char*)workspace + align_up((size_t)P.nseg * D * 4, 256));
+    P.scratch_row = (float*)((char*)workspace + update_workspace_bytes(N, D) - align_up((size_t)(D + 4) * 4, 256));
+    P.invalid_key = (uint32_t)total_rows;
     cudaStream_t st = (cudaStream_t)stream;
 #define DLRMX_CALL_UPDATE(V, G_, C) launch_update<V, G_, C>(P, st)
-    // experiment knob (tunable 1 = 8): 8 positions in flight per lane for one-warp-per-row geometries
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 8) return launch_update<4, 32, 1, 8>(P, st);
-    // experiments: 4 positions in flight squeezed into 64 registers (4 CTAs per SM), 2 and 3 positions at 4 CTAs per SM
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 64) return launch_update<4, 32, 1, 4, 4>(P, st);
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 2) return launch_update<4, 32, 1, 2, 4>(P, st);
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 3) return launch_update<4, 32, 1, 3, 4>(P, st);
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 6) return launch_update<4, 32, 1, 6, 2>(P, st);
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 25) return launch_update<4, 32, 1, 2, 5>(P, st);
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 16) return launch_update<4, 32, 1, 1, 6>(P, st);
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 4) return launch_update<4, 32, 1, 4, 3>(P, st);
-    // 256-byte rows (D = 64, two segments per warp): experiment variants
-    if (g.vec == 4 && g.g == 16 && g.ch == 1 && get_tunable(DLRMX_TUNE_BWD_K) == 2) return launch_update<4, 16, 1, 2, 4>(P, st);
     // Row-wise Adagrad on 512-byte rows: 2 positions in flight per warp at 4 CTAs per SM (64 registers, no spills) beat 4
     // positions at 3 CTAs per SM (0.175 vs 0.183 ms on the Terabyte shape: the sum-of-squares butterfly, square root and
     // division lengthen every batch, and more resident warps hide that better than deeper batches); plain SGD prefers 4.
-    if (g.vec == 4 && g.g == 32 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD && get_tunable(DLRMX_TUNE_BWD_K) == 0)
+    if (g.vec == 4 && g.g == 32 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD)
         return launch_update<4, 32, 1, 2, 4>(P, st);
     // the same holds for 256-byte rows (C3 shape, 1.48 M distinct rows: 0.261 -> 0.224 ms)
-    if (g.vec == 4 && g.g == 16 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD && get_tunable(DLRMX_TUNE_BWD_K) == 0)
+    if (g.vec == 4 && g.g == 16 && g.ch == 1 && optimizer == DLRMX_OPT_RWSADAGRAD)
         return launch_update<4, 16, 1, 2, 4>(P, st);
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
@@ -582,6 +615,26 @@ int dlrmx_rows_update(int optimizer, float* table, float* mom, const int64_t* ro
 #define DLRMX_CALL_ROWS(V, G_, C) launch_rows_update<V, G_, C>(optimizer, table, mom, rows, gsum, U, D, lr, eps, st)
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_ROWS);
     set_error("rows_update: no kernel for D=%d", D);
+    return DLRMX_E_ARG;
+}
+
+int dlrmx_dense_rows_update(int optimizer, float* table, float* mom, float* gsum, int64_t rows, int D, int64_t table_ld,
+                            float lr, float eps, dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || optimizer == DLRMX_OPT_RWSADAGRAD, "dense_rows_update: bad optimizer %d", optimizer);
+    DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || mom != nullptr, "dense_rows_update: rwsadagrad needs the accumulator");
+    RowGeom g;
+    DLRMX_REQUIRE(row_geometry(D, &g), "dense_rows_update: unsupported D=%d", D);
+    const int64_t ld = table_ld > 0 ? table_ld : D;
+    DLRMX_REQUIRE(rows >= 0 && ld >= D, "dense_rows_update: bad sizes");
+    if (g.vec == 4)
+        DLRMX_REQUIRE((((uintptr_t)table | (uintptr_t)gsum) & 15) == 0 && ld % 4 == 0,
+                      "dense_rows_update: table/gsum must be 16-B aligned, table_ld a multiple of 4");
+    if (rows == 0) return DLRMX_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+#define DLRMX_CALL_DENSE(V, G_, C) launch_dense_rows_update<V, G_, C>(optimizer, table, mom, gsum, rows, D, ld, lr, eps, st)
+    DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_DENSE);
+    set_error("dense_rows_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;
 }
 }

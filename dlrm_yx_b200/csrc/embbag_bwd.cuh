@@ -43,7 +43,23 @@ struct BwdParams {
     float inv_D;          // 1/D when D is a power of two, else 0 (row_mean)
     float* head_partial;  // [nseg, D]
     float* tail_partial;  // [nseg, D]
+    uint32_t invalid_key; // key of lookups whose index was out of range (dlrmx_bwd_sort): their run, sorted to the very end,
+    float* scratch_row;   // is "applied" to this scratch row [D + 1] instead of a table row -- no branch in the hot loop
 };
+
+// Where the run of `key` (looked up through bag `bag`) lives: table row and, for row-wise Adagrad, its accumulator.
+__device__ __forceinline__ void run_target(const BwdParams& P, uint32_t key, int bag, float*& wp, float*& mp) {
+    if (key == P.invalid_key) {
+        wp = P.scratch_row;
+        mp = P.scratch_row + P.D;
+        return;
+    }
+    const int t = bag / P.B;
+    const int64_t row = (int64_t)key - P.row_base[t];
+    wp = P.tables[t] + row * P.ld;
+    mp = nullptr;
+    if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mp = P.moms != nullptr ? P.moms[t] + row : wp + P.D;
+}
 
 template <int G>
 __device__ __forceinline__ unsigned group_mask() {

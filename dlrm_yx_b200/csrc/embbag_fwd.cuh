@@ -60,7 +60,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t ld, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
-                  float* const* __restrict__ out_peers, int lb, int mb_off, int mb_len) {
+                  float* const* __restrict__ out_peers, int lb) {
     constexpr int KB = (K < G) ? K : G;       // bags walked in lockstep
     constexpr int TILE = FULL ? G : KB;       // bags per group
     const int gl = threadIdx.x & (G - 1);
@@ -69,20 +69,6 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     const int64_t tile_bag0 = tile * TILE;
     if (tile_bag0 >= total_bags) return;      // whole group leaves together
     const int col0 = gl * VEC;
-    // Micro-batched exchange (scatter mode, mb_len < lb): only samples [mb_off, mb_off + mb_len) of every rank's local
-    // batch are looked up by this launch; the launch walks a DENSE index q over (table, rank, sample-in-window) and maps
-    // it to the real bag id t*B + p*lb + b'.  Otherwise the dense index IS the bag id.
-    // SCATTER is a template flag so that the ordinary lookup carries none of this (it runs at 64 registers).
-    const bool windowed = SCATTER && mb_len < lb;
-    const int64_t per_table = windowed ? (int64_t)(B / lb) * mb_len : (int64_t)B;
-    auto real_bag = [&](int64_t q) -> int64_t {
-        if (!SCATTER || !windowed) return q;
-        const int64_t t = q / per_table, rem = q - t * per_table;
-        const int64_t p = rem / mb_len;
-        return t * B + p * lb + mb_off + (rem - p * mb_len);
-    };
-    const int64_t all_bags = windowed ? (total_bags / per_table) * B : total_bags;   // T*B: end of the offsets array
-
     // ---- lane-parallel metadata of the tile: lane i (< TILE) describes bag tile_bag0 + i ---------------
     IdxT my_s = 0, my_ix = -1;
     int my_len = 0;
@@ -91,9 +77,9 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     {
         const int64_t q = tile_bag0 + gl;
         if (gl < TILE && q < total_bags) {
-            const int64_t bag = real_bag(q);
+            const int64_t bag = q;
             const IdxT s = offsets[bag];
-            const IdxT e = (bag + 1 < all_bags) ? offsets[bag + 1] : (IdxT)N;
+            const IdxT e = (bag + 1 < total_bags) ? offsets[bag + 1] : (IdxT)N;
             const int t = (int)(bag / B);
             my_base = tables[t];
             my_rows = (table_rows != nullptr) ? table_rows[t] : (int64_t)0x7fffffffffffffffll;
@@ -183,7 +169,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
         for (int k = 0; k < KB; ++k) {
             const int64_t q = tile_bag0 + b0 + k;
             if (q < total_bags) {
-                const int64_t bag = real_bag(q);
+                const int64_t bag = q;
                 const int64_t t = bag / B;
                 const int64_t b = bag - t * B;
                 // model-parallel exchange fused into the lookup: sample b belongs to rank b / lb, whose (peer-mapped)
@@ -201,10 +187,9 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
 template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0, int THREADS = 256>
 static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, int64_t ld, const float* psw, float* out,
-                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
-                      int mb_len, cudaStream_t st) {
-    const bool windowed = out_peers != nullptr && mb_len < lb;
-    const int64_t total_bags = windowed ? (int64_t)T * (B / lb) * mb_len : (int64_t)T * B;
+                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
+                      cudaStream_t st) {
+    const int64_t total_bags = (int64_t)T * B;
     constexpr int TILE = FULL ? G : ((K < G) ? K : G);
     const int64_t groups = ceil_div(total_bags, TILE);   // one group of G lanes per tile of TILE bags
     const int threads = THREADS;
@@ -214,11 +199,11 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     embbag_fwd_kernel<VEC, G, CH, K, U, FULL, SC, IdxT, OCC, EX, THREADS><<<(unsigned)blocks, threads, 0, st>>>(__VA_ARGS__)
     const bool exact = D == VEC * G * CH;
     if (out_peers != nullptr) {
-        if (exact) DLRMX_FWD_LAUNCH(true, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, mb_len);
-        else DLRMX_FWD_LAUNCH(true, false, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, mb_len);
+        if (exact) DLRMX_FWD_LAUNCH(true, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb);
+        else DLRMX_FWD_LAUNCH(true, false, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb);
     } else {
-        if (exact) DLRMX_FWD_LAUNCH(false, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, nullptr, 1, 0, 1);
-        else DLRMX_FWD_LAUNCH(false, false, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, nullptr, 1, 0, 1);
+        if (exact) DLRMX_FWD_LAUNCH(false, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, nullptr, 1);
+        else DLRMX_FWD_LAUNCH(false, false, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, nullptr, 1);
     }
 #undef DLRMX_FWD_LAUNCH
     return check_launch("embbag_fwd");
@@ -227,11 +212,9 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
 template <typename IdxT>
 static int embbag_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw, float* out,
-                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb, int mb_off,
-                      int mb_len, dlrmx_stream_t stream) {
+                      int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
+                      dlrmx_stream_t stream) {
     DLRMX_REQUIRE(T >= 0 && B >= 0 && N >= 0, "embbag_fwd: negative size");
-    DLRMX_REQUIRE(out_peers == nullptr || (mb_off >= 0 && mb_len > 0 && mb_off + mb_len <= lb),
-                  "embbag_fwd_scatter: window [mb_off, mb_off + mb_len) must lie inside the local batch");
     DLRMX_REQUIRE(out_peers == nullptr || (lb > 0 && B % lb == 0), "embbag_fwd_scatter: B must be a multiple of lb > 0");
     DLRMX_REQUIRE((int64_t)T * B < (1ll << 31), "embbag_fwd: T*B must be < 2^31");
     RowGeom g;
@@ -244,38 +227,18 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     if ((int64_t)T * B == 0) return DLRMX_OK;
     cudaStream_t st = (cudaStream_t)stream;
     // Short bags (<= 2 indices on average, e.g. Criteo's one per bag): tiles of G bags, K in lockstep.
-    // Long bags: K bags per group, U rows of each in flight.  FWD_K tunable: 8 -> K=8 (short) / U=8 (long).
+    // Long bags: ONE bag per group with 8 of its rows in flight, in CTAs of 224 threads at 4 CTAs per SM (28 warps, 69-72
+    // registers, no spills) -- measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the
+    // bags / 512-byte rows): 0.80 / 0.87 / 1.06.  The variants that lost (256 x 3 CTAs: 0.61 / 0.78 / 0.99; two bags in
+    // lockstep: 0.52 / 0.62 / 0.50; 16 rows in flight: 0.56 / 0.67 / 0.84; L2 bulk prefetch; register double buffer) are
+    // recorded in DESIGN.md section 4 and no longer built.
     const bool short_bags = N <= 2 * (int64_t)T * B;
-    const int tune = get_tunable(DLRMX_TUNE_FWD_K);
 #define DLRMX_FWD_ARGS \
-    tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, mb_off, \
-        mb_len, st
-    // Long bags, measured on B200 at 100 rows per bag (fraction of the measured copy peak; C3 shape / 8x the bags /
-    // 512-byte rows): ONE bag per group with 8 of its rows in flight, in CTAs of 224 threads at 4 CTAs per SM (28 warps,
-    // 69-72 registers, no spills): 0.80 / 0.87 / 1.06.  The same kernel in CTAs of 256 threads at 3 per SM (24 warps)
-    // reaches 0.61 / 0.78 / 0.99 -- at the C3 shape an SM owns 110.7 bags, which is three rounds of 48 resident groups
-    // but two rounds of 56 -- against 0.52 / 0.62 / 0.50 for two bags in lockstep (K=2, U=8: 128 registers,
-    // 2 CTAs per SM, half as many work units for the launch's tail), 0.57 / 0.67 / 0.56 when squeezed to 64 registers for
-    // 4 CTAs per SM (spills) and 0.56 / 0.67 / 0.84 with 16 rows in flight.  An L2 bulk prefetch ahead of the walk
-    // (cp.async.bulk.prefetch.L2, lane-parallel) and a two-round register double buffer were tried and were slower.
-    // FWD_K tunable (experiment variants, built for the 256- and 512-byte row geometries only): short bags 8: K=8;
-    // long bags 7: 256 x 3; 2 / 3: 256 x 4 (64 registers) / 16 rows in flight; 6: 160 x 5; 8 / 4: the older two-bag variants.
+    tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                       \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                        \
-        if constexpr (VEC_ == 4 && CH_ == 1 && G_ >= 16) {                                                  \
-            if (short_bags && tune == 8) return launch_fwd<VEC_, G_, CH_, 8, 1, true, IdxT>(DLRMX_FWD_ARGS);  \
-            if (!short_bags && tune == 8) return launch_fwd<VEC_, G_, CH_, 2, 8, false, IdxT>(DLRMX_FWD_ARGS); \
-            if (!short_bags && tune == 4) return launch_fwd<VEC_, G_, CH_, 2, 4, false, IdxT>(DLRMX_FWD_ARGS); \
-            if (!short_bags && tune == 2) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4>(DLRMX_FWD_ARGS); \
-            if (!short_bags && tune == 3) return launch_fwd<VEC_, G_, CH_, 1, 16, false, IdxT, 2>(DLRMX_FWD_ARGS); \
-            if (!short_bags && tune == 5) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224>(DLRMX_FWD_ARGS); \
-            if (!short_bags && tune == 6) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 5, 160>(DLRMX_FWD_ARGS); \
-        }                                                                                                   \
         if (short_bags) return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);  \
-        if constexpr (CH_ == 1) {                                                                           \
-            if (tune == 7) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 3>(DLRMX_FWD_ARGS);          \
-            return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224>(DLRMX_FWD_ARGS);                    \
-        }                                                                                                   \
+        if constexpr (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224>(DLRMX_FWD_ARGS); \
         return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3>(DLRMX_FWD_ARGS);           \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)

@@ -8,16 +8,15 @@ int dlrmx_embbag_fwd_i32(const float* const* tables, const int64_t* table_rows, 
                          float* out, int64_t stride_b, int64_t stride_t, int* err_flag,
                          dlrmx_stream_t stream) {
     return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw, out, stride_b,
-                                      stride_t, err_flag, nullptr, 0, 0, 0, stream);
+                                      stride_t, err_flag, nullptr, 0, stream);
 }
 int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows, const int32_t* indices,
                                  const int32_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
-                                 float* const* out_peers, int lb, int mb_off, int mb_len, int64_t stride_b,
+                                 float* const* out_peers, int lb, int64_t stride_b,
                                  int64_t stride_t, int* err_flag, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(out_peers != nullptr, "embbag_fwd_scatter: out_peers is null");
     return dlrmx::embbag_fwd<int32_t>(tables, table_rows, indices, offsets, N, T, B, D, table_ld, psw,
-                                      nullptr, stride_b, stride_t, err_flag, out_peers, lb, mb_off,
-                                      mb_len, stream);
+                                      nullptr, stride_b, stride_t, err_flag, out_peers, lb, stream);
 }
 }

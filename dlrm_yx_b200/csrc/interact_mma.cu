@@ -513,10 +513,9 @@ int interact_fwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
     const int nz = tri_count_mma(F, itself);
     const size_t smem = (2 * (size_t)F * (D + 4) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4;
     if (smem > 200 * 1024) return 0;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce once;         // the opt-in is per device, not per process
+    if (once.first()) {
         cudaFuncSetAttribute(interact_fwd_mma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_done = true;
     }
     interact_fwd_mma_kernel<false, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(feat, fsb, D, B, F, D, itself, out,
                                                                                      ostride, nullptr);
@@ -532,24 +531,15 @@ int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
     const int nz = tri_count_mma(F, itself);
     const size_t smem = (2 * ((size_t)F * (D + 8) + ((nz + 3) & ~3) + 4) + 32 * 36) * 4;
     if (smem > 200 * 1024) return 0;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce once;         // the opt-in is per device, not per process
+    if (once.first()) {
         cudaFuncSetAttribute(interact_bwd_mma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_done = true;
     }
     interact_bwd_mma_kernel<false, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
         feat, fsb, D, B, F, D, itself, dout, dstride, dfeat, dfsb, nullptr, nullptr);
     *rc = check_launch("interact_dot_bwd(mma)");
     return 1;
 }
-
-// one-warp-per-sample kernels of interact_warp.cu; return 1 when they took the shape
-int interact_fwd_warp(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
-                      void* out_bf16, int64_t ostride, cudaStream_t st, int* rc);
-int interact_bwd_warp(const float* feat, int64_t fsb, const void* x_bf16, int B, int F, int D, int itself,
-                      const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16,
-                      cudaStream_t st, int* rc);
-enum { DLRMX_TUNE_IX_WARP = 4 };     // tunable 4 = 1: one-warp-per-sample kernels (measured slower, see interact_warp.cu)
 
 // bf16-facing variants.  Return 0 on success, a negative code (message set) when the shape is not supported.
 int interact_fwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* x_bf16, int B, int F, int D, int itself,
@@ -568,17 +558,12 @@ int interact_fwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* 
         set_error("interact_dot_fwd_mixed: a feature pitch of D + 8 needs D %% 32 == 0 (bulk-copy staging)");
         return DLRMX_E_ARG;
     }
-    if (!padded && get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
-        int rc = 0;
-        if (interact_fwd_warp(feat, fsb, x_bf16, B, F, D, itself, out_bf16, ostride, st, &rc)) return rc;
-    }
     const size_t smem = (2 * (size_t)F * (D + (padded ? 8 : 4)) + (size_t)kMmaWarps * ((nz + 3) & ~3)) * 4 + 2 * (size_t)D * 2;
     if (smem > 200 * 1024) { set_error("interact_dot_fwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce once;         // the opt-in is per device, not per process
+    if (once.first()) {
         cudaFuncSetAttribute(interact_fwd_mma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         cudaFuncSetAttribute(interact_fwd_mma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_done = true;
     }
     if (padded)
         interact_fwd_mma_kernel<true, true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
@@ -607,19 +592,13 @@ int interact_bwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* 
         set_error("interact_dot_bwd_mixed: a feature pitch of D + 8 needs D %% 32 == 0 (bulk-copy staging)");
         return DLRMX_E_ARG;
     }
-    if (!padded && get_tunable(DLRMX_TUNE_IX_WARP) == 1) {
-        int rc = 0;
-        if (interact_bwd_warp(feat, fsb, x_bf16, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, dx_bf16, st, &rc))
-            return rc;
-    }
     const int nchunk = (D + nz + 7) >> 3;
     const size_t smem = (2 * ((size_t)F * (D + 8) + 4 * nchunk + 4 + (D >> 1)) + 32 * 36) * 4;
     if (smem > 200 * 1024) { set_error("interact_dot_bwd_mixed: F*D too large for shared memory"); return DLRMX_E_ARG; }
-    static bool attr_done = false;
-    if (!attr_done) {
+    static DeviceOnce once;         // the opt-in is per device, not per process
+    if (once.first()) {
         cudaFuncSetAttribute(interact_bwd_mma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         cudaFuncSetAttribute(interact_bwd_mma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_done = true;
     }
     if (padded)
         interact_bwd_mma_kernel<true, true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(

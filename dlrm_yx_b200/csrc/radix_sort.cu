@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(kSortThreads)
 build_keys_kernel(const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int64_t total_bags, int B, const int64_t* __restrict__ table_row_base, int passes,
                   int n_tiles, uint32_t* __restrict__ keys, int32_t* __restrict__ bags,
-                  int* __restrict__ tile_counts0, int* __restrict__ hist) {
+                  int* __restrict__ tile_counts0, int* __restrict__ hist, uint32_t invalid_key,
+                  int* __restrict__ err_flag) {
     __shared__ int s_hist[kMaxPasses][256];
     __shared__ int64_t s_range[2];
     const int tile = blockIdx.x;
@@ -63,7 +64,15 @@ build_keys_kernel(const IdxT* __restrict__ indices, const IdxT* __restrict__ off
             }
             const int64_t bag = lo - 1;
             const int t = (int)(bag / B);
-            const uint32_t key = (uint32_t)(table_row_base[t] + (int64_t)indices[p]);
+            // an index outside [0, rows_t) would alias a row of another table (or run past the last one): it gets the
+            // key one past the last valid row -- sorted to the very end, skipped by the update -- and raises the flag
+            // (nn.EmbeddingBag raises / device-asserts on the same input)
+            const int64_t base_t = table_row_base[t], ix = (int64_t)indices[p];
+            uint32_t key = (uint32_t)(base_t + ix);
+            if (ix < 0 || ix >= table_row_base[t + 1] - base_t) {
+                key = invalid_key;
+                if (err_flag != nullptr) atomicOr(err_flag, 2);
+            }
             keys[p] = key;
             bags[p] = (int32_t)bag;
             for (int q = 0; q < passes; ++q) atomicAdd(&s_hist[q][digit_of(key, q)], 1);
@@ -195,9 +204,9 @@ size_t sort_workspace_bytes(int64_t N) {
 template <typename IdxT>
 static int bwd_sort(const IdxT* indices, const IdxT* offsets, int64_t N, int T, int B,
                     const int64_t* table_row_base, int64_t total_rows, uint32_t* sorted_key,
-                    int32_t* sorted_bag, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+                    int32_t* sorted_bag, int* err_flag, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
     DLRMX_REQUIRE(N >= 0 && N < (1ll << 31), "bwd_sort: N must be < 2^31");
-    DLRMX_REQUIRE(total_rows >= 0 && total_rows <= (1ll << 32), "bwd_sort: total rows must be <= 2^32");
+    DLRMX_REQUIRE(total_rows >= 0 && total_rows < (1ll << 32) - 1, "bwd_sort: total rows must be < 2^32 - 1");
     DLRMX_REQUIRE((int64_t)T * B < (1ll << 31), "bwd_sort: T*B must be < 2^31");
     if (N == 0) return DLRMX_OK;
     if (workspace_bytes < sort_workspace_bytes(N)) {
@@ -206,7 +215,7 @@ static int bwd_sort(const IdxT* indices, const IdxT* offsets, int64_t N, int T, 
     }
     cudaStream_t st = (cudaStream_t)stream;
     int bits = 1;
-    while (bits < 32 && ((int64_t)1 << bits) < total_rows) ++bits;
+    while (bits < 32 && ((int64_t)1 << bits) < total_rows + 1) ++bits;   // keys 0 .. total_rows (= the invalid key)
     const int passes = (bits + 7) / 8;
     const int n_tiles = (int)ceil_div(N, kSortTile);
 
@@ -230,7 +239,8 @@ static int bwd_sort(const IdxT* indices, const IdxT* offsets, int64_t N, int T, 
 
     build_keys_kernel<IdxT><<<n_tiles, kSortThreads, 0, st>>>(indices, offsets, N, (int64_t)T * B, B,
                                                              table_row_base, passes, n_tiles, kbuf[0],
-                                                             vbuf[0], counts, hist);
+                                                             vbuf[0], counts, hist, (uint32_t)total_rows,
+                                                             err_flag);
     int rc = check_launch("build_keys");
     if (rc) return rc;
     for (int p = 0; p < passes; ++p) {
@@ -254,14 +264,16 @@ size_t dlrmx_bwd_sort_workspace_bytes(int64_t N, int64_t total_bags) {
 }
 int dlrmx_bwd_sort_i32(const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
                        const int64_t* table_row_base, int64_t total_rows, uint32_t* sorted_key,
-                       int32_t* sorted_bag, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+                       int32_t* sorted_bag, int* err_flag, void* workspace, size_t workspace_bytes,
+                       dlrmx_stream_t stream) {
     return dlrmx::bwd_sort<int32_t>(indices, offsets, N, T, B, table_row_base, total_rows, sorted_key,
-                                    sorted_bag, workspace, workspace_bytes, stream);
+                                    sorted_bag, err_flag, workspace, workspace_bytes, stream);
 }
 int dlrmx_bwd_sort_i64(const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
                        const int64_t* table_row_base, int64_t total_rows, uint32_t* sorted_key,
-                       int32_t* sorted_bag, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+                       int32_t* sorted_bag, int* err_flag, void* workspace, size_t workspace_bytes,
+                       dlrmx_stream_t stream) {
     return dlrmx::bwd_sort<int64_t>(indices, offsets, N, T, B, table_row_base, total_rows, sorted_key,
-                                    sorted_bag, workspace, workspace_bytes, stream);
+                                    sorted_bag, err_flag, workspace, workspace_bytes, stream);
 }
 }

@@ -145,47 +145,32 @@ class _SparseArchLocalMixed(torch.autograd.Function):
         return dx, None, None, None, None, None, None
 
 
-class _ExchangeInteractMixed(torch.autograd.Function):
-    """_ExchangeInteract between bf16 towers."""
+class _DistStep(object):
+    """What one multi-process training step shares between the forward halves and the autograd nodes."""
+
+    def __init__(self, model, lb):
+        self.model, self.lb = model, lb
+        self.peer = None            # ext_dist.PeerExchange, or None: NCCL all-to-all
+        self.feat = None            # [lb, F, D] interaction input (feature pitch may exceed D)
+        self.emb = self.indices = self.offsets = self.presorted = None      # sharded tables (local), global batch
+        self.rep = self.rep_indices = self.rep_offsets = self.rep_sorted = None   # replicated tables, local batch
+        self.info = None            # NCCL: the exchange descriptor
+
+
+class _DistInteract(torch.autograd.Function):
+    """Multi-process sparse arch behind the exchange: the interaction input [lb, 1 + T_s + T_rep, D] holds the pooled rows
+    of the sharded tables (rank-major order, delivered by the peers' lookup kernels over NVLink or unpacked from the NCCL
+    all-to-all) followed by those of the replicated tables (looked up locally).  backward: interaction gradient, then --
+    on the side stream, beside the bottom-MLP backward -- the transposed exchange + fused update of the local sharded
+    tables, and the accumulate / all-reduce / update of the replicated ones.  out_cols > 0 selects the bf16-facing
+    interaction kernels (x, R, dR, dx in bf16)."""
 
     @staticmethod
-    def forward(ctx, x, recv, itself, out_cols):
-        lb, D = x.shape
-        T = ext_dist.myreq.a2a_info.global_table_num
-        feat = torch.empty((lb, 1 + T, D), dtype=torch.float32, device=x.device)
-        ctx.info = ext_dist.complete_into(recv, feat, 1)
-        x = x.contiguous()
-        ctx.itself = bool(itself)
-        ctx.save_for_backward(feat, x)
-        return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
-
-    @staticmethod
-    def backward(ctx, dR):
-        feat, x = ctx.saved_tensors
-        dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
-        send = ext_dist.start_backward_from(ctx.info, dfeat, 1)
-        return dx, send, None, None
-
-
-class _PeerStep(object):
-    """Per-step state shared by the micro-batch branches of the peer-memory exchange."""
-
-    def __init__(self, peer, emb, indices, offsets, presorted, nwin):
-        self.peer, self.emb, self.indices, self.offsets = peer, emb, indices, offsets
-        self.presorted, self.pending, self.first_push = presorted, nwin, True
-
-
-class _PeerInteract(torch.autograd.Function):
-    """Multi-process, exchange fused into the kernels over NVLink peer memory (ext_dist.PeerExchange): the pooled rows
-    of window [off, off+ln) of the local batch were stored into this rank's interaction input by the peers' lookup
-    kernels; backward pushes the window's gradient slices into the table owners' buffers and, once every window has
-    been pushed, runs the fused update of the local tables.  out_cols > 0 selects the bf16-facing interaction kernels
-    (x, R, dR, dx in bf16)."""
-
-    @staticmethod
-    def forward(ctx, x, step, off, ln, itself, out_cols):
-        feat = step.peer.feat[off:off + ln]
-        ctx.step, ctx.off, ctx.itself, ctx.mixed = step, off, bool(itself), out_cols > 0
+    def forward(ctx, x, recv, step, itself, out_cols):
+        feat = step.feat
+        if step.peer is None:
+            step.info = ext_dist.complete_into(recv, feat, 1)
+        ctx.step, ctx.itself, ctx.mixed = step, bool(itself), out_cols > 0
         if ctx.mixed:
             x = x.contiguous()
             ctx.save_for_backward(feat, x)
@@ -198,53 +183,32 @@ class _PeerInteract(torch.autograd.Function):
     def backward(ctx, dR):
         feat, x = ctx.saved_tensors
         step = ctx.step
-        peer = step.peer
         if ctx.mixed:
             dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
-        T_r = peer.grad.shape[1]
-        first, off = step.first_push, ctx.off
-        step.first_push = False
-        step.pending -= 1
-        last = step.pending == 0
+        peer, lb = step.peer, step.lb
+        F, D = dfeat.shape[1], dfeat.shape[2]
+        T_s = F - 1 - (step.rep.T if step.rep is not None else 0)
+        send = None
+        if peer is None:      # NCCL: pack + start the transposed all-to-all; _A2AReq.backward completes it and the batched
+            send = ext_dist.start_backward_from(step.info, dfeat, 1)      # lookup's own backward runs the fused update
 
-        def exchange():                       # on the side stream: (barrier,) push over NVLink (, barrier)
-            peer.push_grad(dfeat, mb_off=off, first=first)
-            if not last:
-                return None
-            grad = peer.grad_ready()
-            return grad if T_r > 0 else None
-        _update_on_side(step.emb, dfeat, step.indices, step.offsets, peer.W * peer.lb, T_r * peer.D, peer.D,
-                        step.presorted if last else None, before=exchange, keep=(dfeat,))
-        if last:
-            step.presorted = None
-        return dx, None, None, None, None, None
-
-
-class _ExchangeInteract(torch.autograd.Function):
-    """Multi-process: completes the all-to-all into the feature block, then dot interaction.
-    backward packs the block gradient and starts the transposed exchange (completed by the request's
-    own backward, so it overlaps with the bottom-MLP backward exactly as in the reference)."""
-
-    @staticmethod
-    def forward(ctx, x, recv, itself):
-        lb, D = x.shape
-        T = ext_dist.myreq.a2a_info.global_table_num
-        feat = torch.empty((lb, 1 + T, D), dtype=torch.float32, device=x.device)
-        ctx.info = ext_dist.complete_into(recv, feat, 1)
-        feat[:, 0, :].copy_(x)
-        ctx.itself = bool(itself)
-        ctx.save_for_backward(feat)
-        return ops.interact_dot_fwd(feat, ctx.itself)
-
-    @staticmethod
-    def backward(ctx, dR):
-        (feat,) = ctx.saved_tensors
-        dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
-        send = ext_dist.start_backward_from(ctx.info, dfeat, 1)
-        return dfeat[:, 0, :], send, None
+        def sparse_updates():                 # on the side stream
+            if peer is not None:
+                grad = peer.push_grad(dfeat)
+                if step.emb.T > 0:
+                    step.emb.fused_backward(grad, step.indices, step.offsets, peer.W * lb, stride_b=grad.stride(0),
+                                            stride_t=grad.stride(1), presorted=step.presorted)
+            if step.rep is not None:
+                step.rep.fused_backward(dfeat[:, 1 + T_s:, :], step.rep_indices, step.rep_offsets, lb,
+                                        stride_b=dfeat.stride(0), stride_t=dfeat.stride(1), presorted=step.rep_sorted)
+            return None
+        if peer is not None or step.rep is not None:
+            _update_on_side(None, dfeat, None, None, 0, 0, 0, None, before=sparse_updates, keep=(dfeat, step))
+        step.presorted = step.rep_sorted = None
+        return dx, send, None, None, None
 
 
 class DLRM_Net(nn.Module):
@@ -292,13 +256,19 @@ class DLRM_Net(nn.Module):
         return emb_l, v_W_l
 
     def create_emb_batched(self, D, Es, weighted_pooling=None, learning_rate=0.1):
-        """dlrm_s_pytorch.py:321-334: one table-batched module over the local tables, optimizer fused."""
+        """dlrm_s_pytorch.py:321-334: one table-batched module over the local tables, optimizer fused.  With
+        `replicate_rows_below` (multi-process only) the tables below that row count get a second, data-parallel module
+        (`self.emb_rep`, embedding.ReplicatedTableBatchedEmbeddingBags) that every rank holds in full."""
         assert weighted_pooling is None, "Weighted pooling not supported yet!"
         self.Es = Es[self.local_emb_indices] if ext_dist.my_size > 1 else Es
         T = len(self.Es)
-        return embedding.TableBatchedEmbeddingBags(
-            T, self.Es, D, optimizer=self.emb_optimizer, learning_rate=learning_rate,
-            eps=self.emb_eps, stochastic_rounding=False, init=self.emb_init), [None] * T
+        kw = dict(optimizer=self.emb_optimizer, learning_rate=learning_rate, eps=self.emb_eps, stochastic_rounding=False,
+                  init=self.emb_init)
+        self.emb_rep = None
+        if ext_dist.my_size > 1 and len(self.replicated_emb_indices) > 0:
+            rows = Es[self.replicated_emb_indices]
+            self.emb_rep = embedding.ReplicatedTableBatchedEmbeddingBags(len(rows), rows, D, **kw)
+        return embedding.TableBatchedEmbeddingBags(T, self.Es, D, **kw), [None] * T
 
     def __init__(self, m_spa=None, ln_emb=None, ln_bot=None, ln_top=None, arch_interaction_op=None,
                  arch_interaction_itself=False, sigmoid_bot=-1, sigmoid_top=-1, sync_dense_params=True,
@@ -307,7 +277,7 @@ class DLRM_Net(nn.Module):
                  qr_flag=False, qr_operation="mult", qr_collisions=0, qr_threshold=200, md_flag=False, md_threshold=200,
                  # additions (keyword-only in spirit): the fused optimizer of the batched module
                  emb_optimizer=embedding.Optimizer.SGD, emb_learning_rate=0.1, emb_eps=None, emb_init="auto",
-                 fuse_sparse_arch=False):
+                 fuse_sparse_arch=False, replicate_rows_below=0):
         super().__init__()
         if any(a is None for a in (m_spa, ln_emb, ln_bot, ln_top, arch_interaction_op)):
             return
@@ -335,20 +305,40 @@ class DLRM_Net(nn.Module):
             raise ValueError("fuse_sparse_arch needs batched_emb=True and arch_interaction_op='dot'")
         self.device_indices = [0]
 
+        self.replicated_emb_indices, self.emb_rep = [], None
         if ext_dist.my_size > 1:       # table-wise model parallel (dlrm_s_pytorch.py:444-468)
             n_emb = len(self.ln_emb)
-            if n_emb < ext_dist.my_size:
+            # tables kept on every rank instead of being sharded (fused batched path only): ascending table order
+            if replicate_rows_below > 0:
+                if not (batched_emb and self.fuse_sparse_arch):
+                    raise _lib.DlrmxError("replicate_rows_below needs batched_emb=True and fuse_sparse_arch=True")
+                self.replicated_emb_indices = [i for i in range(n_emb) if int(self.ln_emb[i]) < replicate_rows_below]
+            self.sharded_emb_indices = [i for i in range(n_emb) if i not in set(self.replicated_emb_indices)]
+            n_sh = len(self.sharded_emb_indices)
+            if n_sh < ext_dist.my_size and not self.replicated_emb_indices:
                 sys.exit("only (%d) sparse features for (%d) devices, table partitions will fail"
                          % (n_emb, ext_dist.my_size))
             self.n_global_emb = n_emb
             if sharder == "input":
-                self.device_indices = list(map(int, allocation.split(",")))
-            else:
-                self.device_indices = sharders.shard(self.ln_emb, ext_dist.my_size, sharder)
+                owners = list(map(int, allocation.split(",")))
+                if len(owners) != n_sh:
+                    sys.exit("ERROR: --allocation lists %d devices for %d sharded tables" % (len(owners), n_sh))
+            elif n_sh >= ext_dist.my_size:
+                owners = sharders.shard(self.ln_emb[self.sharded_emb_indices], ext_dist.my_size, sharder)
+            else:                       # fewer sharded tables than ranks (the rest is replicated): one each, some ranks none
+                owners = list(range(n_sh))
+            # device_indices[i] = owner rank of table i, -1 for a replicated table
+            self.device_indices = [-1] * n_emb
+            for i, r in zip(self.sharded_emb_indices, owners):
+                self.device_indices[i] = int(r)
             self.n_emb_per_rank = [0] * ext_dist.my_size
-            for i in range(n_emb):
+            for i in self.sharded_emb_indices:
                 self.n_emb_per_rank[self.device_indices[i]] += m_spa // int(self.ln_bot[-1])
             self.local_emb_indices = [i for i, j in enumerate(self.device_indices) if j == ext_dist.my_local_rank]
+            # feature order of the interaction input: sharded tables in rank-major order (what the reference's cat of the
+            # all-to-all outputs produces), then the replicated tables in table order
+            self.feature_tables = [i for r in range(ext_dist.my_size) for i in self.sharded_emb_indices
+                                   if self.device_indices[i] == r] + list(self.replicated_emb_indices)
         if batched_emb:
             self.emb_l, w_list = self.create_emb_batched(m_spa, self.ln_emb, weighted_pooling=weighted_pooling,
                                                          learning_rate=emb_learning_rate)
@@ -388,6 +378,7 @@ class DLRM_Net(nn.Module):
         return self
 
     def step_mlps(self):
+        """Optimizer step of the fused towers (gradient all-reduce across the data-parallel replicas included)."""
         w = max(ext_dist.my_size, 1)
         self.bot_l.step(w)
         self.top_l.step(w)
@@ -464,7 +455,7 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
-    def enable_peer_exchange(self, local_batch, microbatches=1, engine="sm", mixed=None):
+    def enable_peer_exchange(self, local_batch, mixed=None):
         """Replaces the NCCL all-to-all of distributed_forward by kernels that store straight into the peers'
         memory over NVLink (ext_dist.PeerExchange).  Needs fuse_sparse_arch + batched_emb and a fixed local batch.
         mixed=True (bf16 towers will be fused in: fuse_mlps) lays the interaction input out with the row pitch the
@@ -473,52 +464,66 @@ class DLRM_Net(nn.Module):
             raise _lib.DlrmxError("enable_peer_exchange needs batched_emb=True and fuse_sparse_arch=True")
         dev = next(self.parameters()).device
         D = int(self.ln_bot[-1])
-        pitch = ops.interact_feature_pitch(1 + int(sum(self.n_emb_per_rank)), D) \
-            if ((getattr(self, "_mixed", False) if mixed is None else mixed) and engine == "sm") else D
-        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, D, dev, engine=engine, feature_pitch=pitch)
-        self.set_microbatches(microbatches)
+        n_rep = len(self.replicated_emb_indices)
+        F = 1 + int(sum(self.n_emb_per_rank)) + n_rep
+        pitch = ops.interact_feature_pitch(F, D) if (getattr(self, "_mixed", False) if mixed is None else mixed) else D
+        self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, D, dev, feature_pitch=pitch,
+                                           extra_features=n_rep)
         return self
 
-    def set_microbatches(self, m):
-        """Micro-batched exchange (peer exchange + FusedMLP towers only): the local batch is cut into m windows; the
-        NVLink transfer of window k+1 (forward) / k-1 (backward) runs beside interaction + top tower of window k."""
-        m = max(1, int(m))
-        if m > 1 and not hasattr(self.top_l, "accumulate"):
-            raise _lib.DlrmxError("micro-batched exchange needs the fused towers (call fuse_mlps first)")
-        self._microbatches = m
-        if hasattr(self.top_l, "accumulate"):
-            self.top_l.accumulate = m > 1
+    def sync_replicas(self):
+        """Replicated tables start (or restart, after loading a checkpoint) from rank 0's rows on every rank."""
+        if self.emb_rep is not None:
+            self.emb_rep.sync_replicas(0)
         return self
+
+    def _split_inputs(self, lS_o, lS_i):
+        """(sharded offsets, indices), (replicated offsets, indices or None): with replicated tables the caller hands
+        pairs -- lS_o = (offsets of the local sharded tables x GLOBAL batch, offsets of the replicated tables x LOCAL
+        batch), lS_i likewise (what distribute_batched_emb_data returns)."""
+        if self.emb_rep is None:
+            return (lS_o, lS_i), (None, None)
+        if not (isinstance(lS_o, (tuple, list)) and len(lS_o) == 2 and isinstance(lS_i, (tuple, list)) and len(lS_i) == 2):
+            raise _lib.DlrmxError("replicated tables: pass lS_o = (sharded_offsets, replicated_offsets) and lS_i likewise")
+        return (lS_o[0], lS_i[0]), (lS_o[1], lS_i[1])
+
+    def _replicated_lookup(self, step, feat, T_s, off, idx):
+        """Pooled rows of the replicated tables for the LOCAL batch, straight into their feature slots; the sort for
+        their backward is issued right behind (side stream)."""
+        rep = self.emb_rep
+        step.rep, step.rep_indices, step.rep_offsets = rep, idx, off
+        ops.embbag_forward(rep.table_set(), idx, off, step.lb, out=feat[:, 1 + T_s:, :], stride_b=feat.stride(0),
+                           stride_t=feat.stride(1))
+        if torch.is_grad_enabled():
+            step.rep_sorted = rep.sort_lookups(idx, off, step.lb)
 
     def _peer_forward(self, dense_x, lS_o, lS_i):
         peer = self._peer
         emb = self._batched_module()
-        M = max(1, int(getattr(self, "_microbatches", 1)))
-        lb = peer.lb
-        cuts = [lb * m // M for m in range(M + 1)]
-        windows = [(cuts[m], cuts[m + 1] - cuts[m]) for m in range(M)]
+        (off, idx), (roff, ridx) = self._split_inputs(lS_o, lS_i)
+        lb, T_s = peer.lb, peer.T
+        step = _DistStep(self, lb)
+        step.peer, step.feat, step.emb, step.indices, step.offsets = peer, peer.feat, emb, idx, off
         main = torch.cuda.current_stream()
         side = _side_stream(dense_x.device)
         side.wait_stream(main)
         with record_function("module::forward_pass::embedding_lookup"):
-            with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sort) beside the towers
-                arrived = peer.lookup_and_scatter(emb.table_set(), lS_i, lS_o, windows if M > 1 else None)
-                presorted = (emb.sort_lookups(lS_i, lS_o, peer.W * lb)
-                             if torch.is_grad_enabled() and emb.T > 0 else None)
+            with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sorts) beside the bottom tower
+                peer.lookup_and_scatter(emb.table_set(), idx, off)
+                if self.emb_rep is not None:
+                    self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
+                peer.wait_rows()
+                arrived = side.record_event()
+                if torch.is_grad_enabled() and emb.T > 0:
+                    step.presorted = emb.sort_lookups(idx, off, peer.W * lb)
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
-        step = _PeerStep(peer, emb, lS_i, lS_o, presorted, M)
         cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
-        outs = []
-        for m, (off, ln) in enumerate(windows):
-            # window m of the interaction input is complete; window m+1 is still on the wire while m is contracted
-            with record_function("module::forward_pass::interaction"):
-                main.wait_event(arrived[m])
-                z = _PeerInteract.apply(x if M == 1 else x[off:off + ln], step, off, ln, self.arch_interaction_itself,
-                                        cols)
-            with record_function("module::forward_pass::top_mlp"):
-                outs.append(self.apply_mlp(z, self.top_l))
-        p = outs[0] if M == 1 else torch.cat(outs, dim=0)
+        with record_function("module::forward_pass::interaction"):
+            main.wait_event(arrived)
+            z = _DistInteract.apply(x, None, step, self.arch_interaction_itself, cols)
+        with record_function("module::forward_pass::top_mlp"):
+            p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
     def distributed_forward(self, dense_x, lS_o, lS_i):
@@ -528,11 +533,12 @@ class DLRM_Net(nn.Module):
             self.emb_l = nn.ModuleList([self.emb_l])
         if getattr(self, "_peer", None) is not None:
             return self._peer_forward(dense_x, lS_o, lS_i)
+        (off, idx), (roff, ridx) = self._split_inputs(lS_o, lS_i)
         with record_function("module::forward_pass::embedding_lookup"):
             if self.batched_emb:
-                ly = self.apply_emb_batched([lS_o], [lS_i])
+                ly = self.apply_emb_batched([off], [idx])
             else:
-                ly = self.apply_emb(lS_o, lS_i)
+                ly = self.apply_emb(off, idx)
             if len(self.emb_l) != len(ly):
                 sys.exit("ERROR: corrupted intermediate result in distributed_forward call")
             a2a_req = ext_dist.alltoall(ly, self.n_emb_per_rank, self.batched_emb)
@@ -544,10 +550,16 @@ class DLRM_Net(nn.Module):
                 ly = list(a2a_req.wait())
         with record_function("module::forward_pass::interaction"):
             if self.fuse_sparse_arch:
-                if getattr(self, "_mixed", False):
-                    z = _ExchangeInteractMixed.apply(x, recv, self.arch_interaction_itself, self.top_l.layers[0].K_pad)
-                else:
-                    z = _ExchangeInteract.apply(x, recv, self.arch_interaction_itself)
+                mixed = getattr(self, "_mixed", False)
+                lb, D = x.shape
+                T_s = int(sum(self.n_emb_per_rank))
+                F = 1 + T_s + len(self.replicated_emb_indices)
+                step = _DistStep(self, lb)
+                step.feat = ops.alloc_features(lb, F, D, x.device, pitch=None if mixed else D)
+                if self.emb_rep is not None:
+                    self._replicated_lookup(step, step.feat, T_s, roff, ridx)
+                z = _DistInteract.apply(x, recv, step, self.arch_interaction_itself,
+                                        self.top_l.layers[0].K_pad if mixed else 0)
             else:
                 z = self.interact_features(x, ly)
         with record_function("module::forward_pass::top_mlp"):
@@ -557,17 +569,35 @@ class DLRM_Net(nn.Module):
     def distribute_batched_emb_data(self, batch_size, lS_o, lS_i):
         """Packed global batch (all T tables) -> this rank's packed batch (local tables, offsets re-based),
         dlrm_s_pytorch.py:772-802 (distributed branch).  Unlike the reference it does not assume a fixed
-        number of indices per lookup: each table's index range comes from its own offsets."""
+        number of indices per lookup: each table's index range comes from its own offsets.  With replicated tables
+        the result is ([offsets], [indices]) of PAIRS: (local sharded tables x global batch, replicated tables x this
+        rank's slice of the batch)."""
         B = batch_size
         if ext_dist.my_size <= 1:
             return [lS_o], [lS_i]
-        o_parts, i_parts, run = [], [], 0
         bounds = lS_o[::B].tolist() if lS_o.numel() % B == 1 else None
-        for k in self.local_emb_indices:
-            o = lS_o[k * B:(k + 1) * B + 1]
-            lo, hi = (bounds[k], bounds[k + 1]) if bounds else (int(o[0]), int(o[-1]))
-            i_parts.append(lS_i[lo:hi])
-            rel = o - lo + run
-            o_parts.append(rel if not o_parts else rel[1:])
-            run += hi - lo
-        return [torch.cat(o_parts, dim=0)], [torch.cat(i_parts, dim=0)]
+
+        def gather(tables, b0, b1):
+            o_parts, i_parts, run = [], [], 0
+            for k in tables:
+                o = lS_o[k * B + b0:k * B + b1 + 1]
+                if o.numel() == b1 - b0:           # last table without the trailing total: close it with N
+                    o = torch.cat([o, o.new_tensor([lS_i.numel()])])
+                if b0 == 0 and b1 == B and bounds:
+                    lo, hi = bounds[k], bounds[k + 1]
+                else:
+                    lo, hi = int(o[0]), int(o[-1])
+                i_parts.append(lS_i[lo:hi])
+                rel = o - lo + run
+                o_parts.append(rel if not o_parts else rel[1:])
+                run += hi - lo
+            if not o_parts:
+                return lS_o.new_zeros(1), lS_i[:0]
+            return torch.cat(o_parts, dim=0), torch.cat(i_parts, dim=0)
+
+        off, idx = gather(self.local_emb_indices, 0, B)
+        if self.emb_rep is None:
+            return [off], [idx]
+        lb = B // ext_dist.my_size
+        roff, ridx = gather(self.replicated_emb_indices, ext_dist.my_rank * lb, (ext_dist.my_rank + 1) * lb)
+        return [(off, roff)], [(idx, ridx)]

@@ -164,6 +164,56 @@ class TableBatchedEmbeddingBags(nn.Module):
         self.step_count += 1
 
 
+class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
+    """Data-parallel twin of the batched module for tables that are cheaper to keep on EVERY rank than to exchange (a
+    sharding policy beside the reference's table-wise one, dlrm_s_pytorch.py:444-468: the Terabyte set has 18 tables
+    with fewer rows than one mini-batch -- 62 MB in all -- whose pooled rows and gradients would otherwise cross NVLink
+    for every sample).  Each rank looks the tables up for its LOCAL batch only; in backward the local pooled-row gradients
+    are summed per row into a dense [rows, D] buffer (sorted segmented reduce, deterministic), the buffers are all-reduced,
+    and one kernel applies the optimizer to every row with a non-zero summed gradient.  The result equals the sharded
+    owner's update up to the order of the floating-point sum over ranks; replicas stay bit-identical to one another."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.register_buffer("grad_sum", torch.zeros_like(self.embedding_weights.data), persistent=False)
+        self._gts = None
+
+    def _grad_table_set(self):
+        if self._gts is None or self._gts_key != self.grad_sum.data_ptr():
+            views, base = [], 0
+            for r in self.rows:
+                views.append(self.grad_sum[base * self.D:(base + r) * self.D].view(r, self.D))
+                base += r
+            self._gts, self._gts_key = ops.TableSet(views), self.grad_sum.data_ptr()
+        return self._gts
+
+    def sync_replicas(self, src=0):
+        """Every rank adopts rank `src`'s rows and accumulators (after construction / after loading a checkpoint)."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.broadcast(self.embedding_weights.data, src)
+            if self.row_momentum is not None:
+                dist.broadcast(self.row_momentum, src)
+
+    def fused_backward(self, grad_out, indices, offsets, B, stride_b=None, stride_t=None, presorted=None):
+        import torch.distributed as dist
+        if stride_b is None:
+            if grad_out.stride(2) != 1 or grad_out.stride(1) % 4 or grad_out.stride(0) % 4:
+                grad_out = grad_out.contiguous()
+            stride_b, stride_t = grad_out.stride(0), grad_out.stride(1)
+        gts = self._grad_table_set()
+        skey, sbag = presorted if presorted is not None else ops.bwd_sort(self.table_set(), indices, offsets, B)
+        # SGD with lr = -1 on the zeroed buffer: grad_sum[row] = sum of the local gradient rows, in sorted (stable) order
+        ops.bwd_update(gts, _lib.OPT_SGD, grad_out, stride_b, stride_t, B, skey, sbag, -1.0, 0.0)
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.grad_sum)
+        kind = _lib.OPT_RWSADAGRAD if self.optimizer in _ROWWISE else _lib.OPT_SGD
+        total = sum(self.rows)
+        ops.dense_rows_update(kind, self.embedding_weights.data.view(total, self.D), self.row_momentum,
+                              self.grad_sum.view(total, self.D), self.current_lr(), self.eps)
+        self.step_count += 1
+
+
 def install_table_batched_embeddings_ops():
     """Publishes this module as `table_batched_embeddings_ops` so that the reference's
     `create_emb_batched` (dlrm_s_pytorch.py:323) imports it unmodified."""
@@ -210,6 +260,7 @@ class _BagLookup(torch.autograd.Function):
                                           output_size=N)
         gsum = ops.bwd_coalesce_weighted(grad_out, spos, pos2bag, psw.to(torch.float32), run_off, nu)
         U = int(nu.item())
+        ops.check_index_errors(dev)         # the host is synchronised here anyway: a bad index raises like nn.EmbeddingBag
         rows = (uniq[:U].to(torch.int64) & 0xFFFFFFFF)
         if m._fused is not None:
             kind, lr, eps = m._fused.hyper(m.weight)
@@ -237,6 +288,7 @@ class _BagLookup(torch.autograd.Function):
         uniq, run_off, nu = ops.bwd_segments(skey)
         gsum = ops.bwd_coalesce(grad_out, D, D, B, D, sbag, run_off, nu)
         U = int(nu.item())
+        ops.check_index_errors(indices.device)   # the host is synchronised here anyway: a bad index raises like nn.EmbeddingBag
         rows = (uniq[:U].to(torch.int64) & 0xFFFFFFFF).view(1, U)
         g = torch.sparse_coo_tensor(rows, gsum[:U], size=tuple(m.weight.shape), is_coalesced=True)
         return g, None, None, None, None

@@ -20,6 +20,7 @@ import os
 import torch
 import torch.distributed as dist
 from torch.autograd import Function
+from torch.autograd.profiler import record_function
 from torch.nn.parallel import DistributedDataParallel as DDP  # noqa: F401  (re-export, as the reference does)
 
 from . import ops
@@ -123,13 +124,14 @@ class _A2AReq(Function):
     def forward(ctx, info, *inputs):
         global myreq
         send_split, recv_split = _split_sizes(info)
-        if info.batched_emb:
-            send = inputs[0].contiguous().view(-1)                  # [B, T_r, D] already is the send layout
-        else:
-            send = torch.cat(inputs, dim=1).view(-1)                # T_r x [B, D] -> [B, T_r*D]
-        recv = send.new_empty([info.global_table_num * info.local_batch_num * info.emb_dim])
-        myreq.req = dist.all_to_all_single(recv, send, recv_split, send_split, async_op=True)
-        myreq.tensor = (recv,)
+        with record_function("DLRM alltoall_req_fwd_single"):
+            if info.batched_emb:
+                send = inputs[0].contiguous().view(-1)              # [B, T_r, D] already is the send layout
+            else:
+                send = torch.cat(inputs, dim=1).view(-1)            # T_r x [B, D] -> [B, T_r*D]
+            recv = send.new_empty([info.global_table_num * info.local_batch_num * info.emb_dim])
+            myreq.req = dist.all_to_all_single(recv, send, recv_split, send_split, async_op=True)
+            myreq.tensor = (recv,)
         info.send_split, info.recv_split = send_split, recv_split
         myreq.a2a_info = info
         ctx.info = info
@@ -139,10 +141,11 @@ class _A2AReq(Function):
     def backward(ctx, *unused):
         global myreq
         info = ctx.info
-        myreq.req.wait()
-        myreq.req = None
-        g = myreq.tensor
-        myreq.tensor = None
+        with record_function("DLRM alltoall_req_bwd_single"):
+            myreq.req.wait()
+            myreq.req = None
+            g = myreq.tensor
+            myreq.tensor = None
         if info.batched_emb:
             grads = [g.view(info.batch_size, -1, info.emb_dim)]
         else:
@@ -152,9 +155,10 @@ class _A2AReq(Function):
 
 def _issue_backward(info, send):
     global myreq
-    recv = send.new_empty([info.batch_size * info.local_table_num * info.emb_dim])
-    myreq.req = dist.all_to_all_single(recv, send, info.send_split, info.recv_split, async_op=True)
-    myreq.tensor = recv
+    with record_function("DLRM alltoall_wait_bwd_single"):
+        recv = send.new_empty([info.batch_size * info.local_table_num * info.emb_dim])
+        myreq.req = dist.all_to_all_single(recv, send, info.send_split, info.recv_split, async_op=True)
+        myreq.tensor = recv
 
 
 class _A2AWait(Function):
@@ -163,9 +167,10 @@ class _A2AWait(Function):
         global myreq
         info = myreq.a2a_info
         ctx.info = info
-        myreq.req.wait()
-        myreq.req = None
-        myreq.tensor = None
+        with record_function("DLRM alltoall_wait_fwd_single"):
+            myreq.req.wait()
+            myreq.req = None
+            myreq.tensor = None
         chunks = recv.split(info.recv_split)
         if info.batched_emb:
             return tuple(c.view(info.local_batch_num, -1, info.emb_dim) for c in chunks)
@@ -184,9 +189,10 @@ def complete_into(recv, feat, feat_off=1):
     kernel.  Returns the exchange descriptor needed by `start_backward_from`."""
     global myreq
     info = myreq.a2a_info
-    myreq.req.wait()
-    myreq.req = None
-    myreq.tensor = None
+    with record_function("DLRM alltoall_wait_fwd_single"):
+        myreq.req.wait()
+        myreq.req = None
+        myreq.tensor = None
     ops.a2a_unpack(recv, info.tables_per_rank, info.local_batch_num, info.emb_dim, feat, feat_off)
     return info
 
@@ -228,13 +234,11 @@ class PeerExchange(object):
     (dlrmx_a2a_push_grad), all over NVLink.  Ranks meet at a device barrier before the first and after the last remote
     store of each direction.  One instance per model; buffers are allocated once.
 
-    tables_per_rank[p] = tables held by rank p (rank-major global table order, as the reference's cat produces)."""
+    tables_per_rank[p] = SHARDED tables held by rank p (rank-major order, as the reference's cat produces);
+    extra_features = feature slots behind them that every rank fills locally (replicated tables)."""
 
-    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, engine="sm", feature_pitch=None):
-        """engine: "sm" = remote stores issued by the lookup / push kernels; "copy" = pitched copies on the copy engines
-        (the lookup writes a local block first; the SMs stay free, so micro-batched transfers overlap the towers)."""
+    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, feature_pitch=None, extra_features=0):
         import torch.distributed._symmetric_memory as symm_mem
-        self.engine = engine
         self.group = dist.group.WORLD if group is None else group
         self.W, self.rank = my_size, my_rank
         self.tpr = [int(t) for t in tables_per_rank]
@@ -242,7 +246,7 @@ class PeerExchange(object):
         self.lb, self.D = int(local_batch), int(emb_dim)
         self.first = [sum(self.tpr[:p]) for p in range(self.W)]
         T_r = self.tpr[self.rank]
-        F = 1 + self.T
+        F = self.F = 1 + self.T + int(extra_features)
         # row pitch of the features inside a sample (floats): D, or the interaction kernels' bulk-copy pitch
         # (ops.interact_feature_pitch) -- the remote row stores are addressed with strides, so any pitch works
         P = self.pitch = int(feature_pitch or self.D)
@@ -257,69 +261,32 @@ class PeerExchange(object):
         # forward: where MY tables' rows go inside peer p's interaction input (feature slot 1 + first[rank])
         fptr = [int(q) + (1 + self.first[self.rank]) * P * 4 for q in self.h_feat.buffer_ptrs]
         self.out_peers = torch.tensor(fptr, dtype=torch.int64, device=device)
-        self.out_peers_host = fptr
         # backward: where MY local batch's chunk starts inside owner p's gradient buffer [W*lb, T_p, D]
         self.push_bases = [int(q) + self.rank * self.lb * self.tpr[p] * self.D * 4
                            for p, q in enumerate(self.h_grad.buffer_ptrs)]
         self.stride_b, self.stride_t = F * P, P
-        if engine == "copy" and P != self.D:
-            raise ValueError("the copy-engine exchange needs an unpitched interaction input")
 
-    def barrier(self, which):
-        (self.h_feat if which == 0 else self.h_grad).barrier()
+    def lookup_and_scatter(self, table_set, indices, offsets):
+        """All local sharded tables x the global batch; every pooled row lands in its sample owner's `feat`.  On return
+        (stream-ordered) every peer's rows have landed in MY `feat` as well."""
+        with record_function("DLRM alltoall_req_fwd_single"):
+            self.h_feat.barrier()                  # peers are done reading the previous contents of their feat
+            if self.tpr[self.rank] > 0:
+                ops.embbag_forward_scatter(table_set, indices, offsets, self.W * self.lb, self.out_peers, self.lb,
+                                           self.stride_b, self.stride_t)
 
-    def lookup_and_scatter(self, table_set, indices, offsets, windows=None):
-        """All local tables x the global batch; every pooled row lands in its sample owner's `feat`.  On return
-        (stream-ordered) every peer's rows have landed in MY `feat` as well.
-        windows: list of (mb_off, mb_len) micro-batch windows of the local batch -- one launch + one barrier each, and
-        the list of events after which window m of `feat` is complete is returned (micro-batched exchange: consumers of
-        window m start while window m+1 is still on the wire)."""
-        T_r, D, F, lb = self.tpr[self.rank], self.D, 1 + self.T, self.lb
-        pooled = None
-        if self.engine == "copy" and T_r > 0:   # local lookup of everything first (HBM-bound, ~0.1 ms)
-            pooled = ops.embbag_forward(table_set, indices, offsets, self.W * lb, validate=False)
-            self._pooled = pooled               # stays alive until the next step's lookup
-        self.h_feat.barrier()                  # peers are done reading the previous contents of their feat
-        events = []
-        for off, ln in (windows or [(0, lb)]):
-            if T_r > 0 and self.engine == "copy":
-                f0 = 1 + self.first[self.rank]
-                for p in range(self.W):        # pooled[p*lb + off : +ln] ([ln, T_r*D] contiguous) -> peer p's feat
-                    if p == self.rank:         # own share: an SM copy at HBM speed (pitched local CE copies are slow)
-                        self.feat[off:off + ln, f0:f0 + T_r, :].copy_(pooled[p * lb + off:p * lb + off + ln])
-                    else:
-                        ops.copy2d_async(self.out_peers_host[p] + off * F * D * 4, F * D * 4,
-                                         pooled[p * lb + off].data_ptr(), T_r * D * 4, T_r * D * 4, ln)
-            elif T_r > 0:
-                ops.embbag_forward_scatter(table_set, indices, offsets, self.W * lb, self.out_peers, lb,
-                                           self.stride_b, self.stride_t, mb_off=off, mb_len=ln)
-            self.h_feat.barrier()              # every peer's rows of this window have landed in my feat
-            events.append(torch.cuda.current_stream().record_event())
-        return events
+    def wait_rows(self):
+        with record_function("DLRM alltoall_wait_fwd_single"):
+            self.h_feat.barrier()                  # every peer's rows have landed in my feat
 
-    def push_grad(self, dfeat, mb_off=0, first=True):
-        """dfeat [mb_len, 1+T, D] (window starting at local sample mb_off): features 1.. go to the table owners'
-        `grad` buffers."""
-        if first:
-            self.h_grad.barrier()              # owners are done with the previous step's gradients
-        bases = [b + mb_off * self.tpr[p] * self.D * 4 for p, b in enumerate(self.push_bases)]
-        if self.engine == "copy":
-            ln, F, D = dfeat.shape
-            for p in range(self.W):            # dfeat[:, 1+first_p : +T_p, :] (row pitch F*D) -> owner p's buffer
-                if self.tpr[p] == 0:
-                    continue
-                f0 = 1 + self.first[p]
-                if p == self.rank:
-                    r0 = self.rank * self.lb + mb_off
-                    self.grad[r0:r0 + ln].copy_(dfeat[:, f0:f0 + self.tpr[p], :])
-                else:
-                    ops.copy2d_async(bases[p], self.tpr[p] * D * 4, dfeat[0, f0].data_ptr(), F * D * 4,
-                                     self.tpr[p] * D * 4, ln)
-            return
-        ops.a2a_push_grad(dfeat, 1, self.tpr, dfeat.shape[0], self.D, bases)
-
-    def grad_ready(self):
-        self.h_grad.barrier()
+    def push_grad(self, dfeat):
+        """dfeat [lb, F, D]: the sharded features 1 .. T go to the table owners' `grad` buffers; returns my buffer
+        [W*lb, T_r, D] once every peer's slices have landed (stream-ordered)."""
+        with record_function("DLRM alltoall_wait_bwd_single"):       # the reference's names: issue = wait_bwd ...
+            self.h_grad.barrier()                  # owners are done with the previous step's gradients
+            ops.a2a_push_grad(dfeat, 1, self.tpr, dfeat.shape[0], self.D, self.push_bases)
+        with record_function("DLRM alltoall_req_bwd_single"):        # ... completion = req_bwd (extend_distributed.py:449, 492)
+            self.h_grad.barrier()
         return self.grad
 
 

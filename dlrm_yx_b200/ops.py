@@ -75,7 +75,9 @@ class TableSet:
 
     def refresh(self):
         ws = self.weights
-        key = tuple(w.data_ptr() for w in ws) + tuple(() if self.moms is None else (m.data_ptr() for m in self.moms))
+        # only addresses, shapes and pitches are cached (never contents), so in-place updates need no refresh
+        key = tuple((w.data_ptr(), tuple(w.shape), w.stride(0)) for w in ws) + \
+            tuple(() if self.moms is None else (m.data_ptr() for m in self.moms))
         if key == self._key:
             return
         _need_cuda(*ws)
@@ -106,6 +108,36 @@ class TableSet:
         self._key = key
 
 
+# ---- index validation ------------------------------------------------------------------------------------------
+# One device-side error word per device: the lookup sets bit 0, the backward's key builder bit 1, when an index lies
+# outside [0, rows_t) (the row is then skipped / the update dropped -- nothing is corrupted).  nn.EmbeddingBag raises
+# on such input; reading the word costs a device synchronisation, so it is read where the host synchronises anyway
+# (`check_index_errors()`: end of a step that reads its loss, the parity seam, tests, bench.py, smoke()).
+_ERR_FLAGS = {}
+
+
+def err_flag(device):
+    f = _ERR_FLAGS.get(device)
+    if f is None:
+        f = _ERR_FLAGS[device] = torch.zeros(1, dtype=torch.int32, device=device)
+    return f
+
+
+def check_index_errors(device=None):
+    """Raises DlrmxError if any lookup since the last check carried an index outside its table (synchronises)."""
+    devs = list(_ERR_FLAGS) if device is None else [torch.device(device)]
+    for d in devs:
+        f = _ERR_FLAGS.get(d)
+        if f is None:
+            continue
+        v = int(f.item())
+        if v:
+            f.zero_()
+            raise _lib.DlrmxError("embedding index out of range (%s): an index was negative or >= the row count of its "
+                                  "table; the offending lookups were skipped" %
+                                  " and ".join(n for b, n in ((1, "forward lookup"), (2, "backward sort")) if v & b))
+
+
 def _idx_suffix(indices, offsets):
     if indices.dtype != offsets.dtype or indices.dtype not in (torch.int32, torch.int64):
         raise _lib.DlrmxError("indices and offsets must both be int32 or both int64")
@@ -128,6 +160,8 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
         out = torch.empty((B, T, D), dtype=torch.float32, device=tables.device)
         stride_b, stride_t = T * D, D
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_" + _idx_suffix(indices, offsets))
+    if err_flag is None and validate:
+        err_flag = globals()["err_flag"](tables.device)
     with _timed("embbag_fwd"):
         rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0,
                 indices.data_ptr(), offsets.data_ptr(), indices.numel(), T, B, D, tables.ld, _ptr(per_sample_weights),
@@ -136,12 +170,9 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
     return out
 
 
-def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b, stride_t, validate=False,
-                           mb_off=0, mb_len=None):
+def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b, stride_t, validate=False):
     """embbag_forward with the exchange fused in: bag (t, b) of the global batch is stored at
-    out_peers[b // lb] + (b % lb)*stride_b + t*stride_t (out_peers: device int64 tensor of peer-mapped pointers).
-    mb_off / mb_len: only samples [mb_off, mb_off + mb_len) of every rank's local batch (micro-batched exchange)."""
-    mb_len = lb if mb_len is None else mb_len
+    out_peers[b // lb] + (b % lb)*stride_b + t*stride_t (out_peers: device int64 tensor of peer-mapped pointers)."""
     tables.refresh()
     _need_cuda(indices, offsets, out_peers)
     indices = indices.contiguous()
@@ -154,7 +185,7 @@ def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b,
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_scatter_" + _idx_suffix(indices, offsets))
     with _timed("embbag_fwd"):
         rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0, indices.data_ptr(),
-                offsets.data_ptr(), indices.numel(), T, B, D, tables.ld, 0, out_peers.data_ptr(), lb, mb_off, mb_len,
+                offsets.data_ptr(), indices.numel(), T, B, D, tables.ld, 0, out_peers.data_ptr(), lb,
                 stride_b, stride_t, 0, _stream())
         _lib.check(rc, "dlrmx_embbag_fwd_scatter")
 
@@ -176,7 +207,8 @@ def bwd_sort(tables, indices, offsets, B):
     fn = getattr(lib, "dlrmx_bwd_sort_" + _idx_suffix(indices, offsets))
     with _timed("bwd_sort"):
         rc = fn(indices.data_ptr(), offsets.data_ptr(), N, tables.T, B, tables.row_base.data_ptr(),
-                tables.total_rows, skey.data_ptr(), sbag.data_ptr(), ws.data_ptr(), wsb, _stream())
+                tables.total_rows, skey.data_ptr(), sbag.data_ptr(), err_flag(dev).data_ptr(), ws.data_ptr(), wsb,
+                _stream())
         _lib.check(rc, "dlrmx_bwd_sort")
     return skey, sbag
 
@@ -213,7 +245,7 @@ def bwd_update(tables, optimizer, grad, stride_b, stride_t, B, skey, sbag, lr, e
         rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(),
                                   0 if tables.acc_in_row else _ptr(tables.mom_ptrs),
                                   tables.row_base.data_ptr(), tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b,
-                                  stride_t, skey.data_ptr(), sbag.data_ptr(), N, float(lr), float(eps),
+                                  stride_t, skey.data_ptr(), sbag.data_ptr(), N, tables.total_rows, float(lr), float(eps),
                                   ws.data_ptr(), wsb, _stream())
         _lib.check(rc, "dlrmx_bwd_update")
 
@@ -324,13 +356,6 @@ def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases):
         _lib.check(rc, "dlrmx_a2a_push_grad")
 
 
-def copy2d_async(dst_ptr, dst_pitch, src_ptr, src_pitch, width, height):
-    """Pitched copy on the copy engines (byte units), stream-ordered on the current stream; pointers may be peer-mapped."""
-    rc = _lib.load().dlrmx_copy2d_async(int(dst_ptr), int(dst_pitch), int(src_ptr), int(src_pitch), int(width),
-                                        int(height), _stream())
-    _lib.check(rc, "dlrmx_copy2d_async")
-
-
 def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):
     """recv = concat_p [lb, T_p, D]  ->  dst[:, feat_off + t, :] (rank-major table order)."""
     _need_cuda(recv, dst)
@@ -362,6 +387,19 @@ def rows_update(optimizer, weight, mom, rows, gsum, lr, eps=0.0):
     rc = _lib.load().dlrmx_rows_update(optimizer, weight.data_ptr(), _ptr(mom), rows.data_ptr(), gsum.data_ptr(),
                                        U, D, float(lr), float(eps), _stream())
     _lib.check(rc, "dlrmx_rows_update")
+
+
+def dense_rows_update(optimizer, weight, mom, gsum, lr, eps=0.0):
+    """Replicated tables: optimizer step of every row of weight [rows, D] whose all-reduced gradient row gsum [rows, D]
+    is non-zero; clears those rows of gsum."""
+    _need_cuda(weight, mom, gsum)
+    rows, D = weight.shape
+    if gsum.shape != weight.shape or not gsum.is_contiguous() or weight.stride(1) != 1:
+        raise _lib.DlrmxError("dense_rows_update: gsum must be contiguous [rows, D] like the table")
+    with _timed("dense_rows_update"):
+        rc = _lib.load().dlrmx_dense_rows_update(optimizer, weight.data_ptr(), _ptr(mom), gsum.data_ptr(), rows, D,
+                                                 weight.stride(0) if rows > 1 else D, float(lr), float(eps), _stream())
+        _lib.check(rc, "dlrmx_dense_rows_update")
 
 
 _RB_COUNTERS = {}

@@ -66,9 +66,13 @@ class RWSAdagrad(Optimizer):
 
     def _momentum(self, p):
         st = self.state[p]
-        if "momentum" not in st or st["momentum"].device != p.device:
+        if "momentum" not in st:
             init = self._group_of(p)["initial_accumulator_value"]
             st["momentum"] = torch.full([p.shape[0]], init, dtype=torch.float32, device=p.device)
+        elif st["momentum"].device != p.device:
+            # the model moved after the optimizer gathered state (or state was restored onto another device): the
+            # accumulated history follows the parameter, it is never re-initialised
+            st["momentum"] = st["momentum"].to(p.device)
         return st["momentum"]
 
     def _fused_hyper(self, p):

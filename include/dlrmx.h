@@ -50,8 +50,10 @@ int dlrmx_version(void);
 const char* dlrmx_last_error(void);
 /* Number of kernels launched by this library since load (bench.py's gpu_launches claim). */
 int64_t dlrmx_launch_count(void);
-/* Experiment knobs for kernel-variant sweeps (0 = default): which 0 = forward bags-in-lockstep K
- * (4 or 8), 1 = backward positions-in-flight.  Not part of the reference-facing surface. */
+/* Test hooks (0 = default) that select between code paths the library ships anyway, so the tests can compare them bit
+ * for bit: 2 = force the CUDA-core interaction kernels, 3 = sorted positions per group of the fused update
+ * (32/64/128/256), 10 = per-thread cp.async staging instead of TMA bulk copies in the interaction kernels, 11 = CTAs per
+ * SM of their persistent grid.  Not part of the reference-facing surface. */
 int dlrmx_set_tunable(int which, int value);
 
 /* ---------------------------------------------------------------------------------------------
@@ -91,17 +93,21 @@ int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows,
  * sorted by key with an LSD radix sort (8-bit digits, only ceil(log2(total_rows)/8) passes), STABLE
  * in p -- identical to torch.sort(stable=True) on the keys.
  *   table_row_base  [T+1] device int64 exclusive prefix of the table row counts
- *   total_rows      host copy of table_row_base[T]
+ *   total_rows      host copy of table_row_base[T] (< 2^32 - 1)
  *   sorted_key [N] uint32, sorted_bag [N] int32: outputs
+ *   err_flag        device int, or NULL; bit 1 is set if an index is outside [0, rows_t).  Such a lookup gets the key
+ *                   `total_rows` (one past the last valid row): it sorts to the very end and dlrmx_bwd_update skips it, so a
+ *                   bad index can neither alias another table's row nor write out of bounds (nn.EmbeddingBag raises /
+ *                   device-asserts on the same input; the host layer raises when it reads the flag)
  * ------------------------------------------------------------------------------------------- */
 size_t dlrmx_bwd_sort_workspace_bytes(int64_t N, int64_t total_bags);
 int dlrmx_bwd_sort_i32(const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
                        const int64_t* table_row_base, int64_t total_rows,
-                       uint32_t* sorted_key, int32_t* sorted_bag,
+                       uint32_t* sorted_key, int32_t* sorted_bag, int* err_flag,
                        void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
 int dlrmx_bwd_sort_i64(const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
                        const int64_t* table_row_base, int64_t total_rows,
-                       uint32_t* sorted_key, int32_t* sorted_bag,
+                       uint32_t* sorted_key, int32_t* sorted_bag, int* err_flag,
                        void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
 
 /* Backward, step 2 (only needed by the non-fused "parity seam" and the tests): run-length
@@ -126,6 +132,7 @@ int dlrmx_bwd_segments(const uint32_t* sorted_key, int64_t N,
  *               row), i.e. in the DRAM page the row update opens anyway -- the separate 4-byte accumulator
  *               arrays of optim/rwsadagrad.py:72-78 cost a DRAM access per row as expensive as the row itself
  *   table_ld    row pitch of the tables in floats (0 = D)
+ *   total_rows  as given to dlrmx_bwd_sort: runs with that key (out-of-range lookups) update nothing
  *   lr          SGD: lr.  RWSADAGRAD: clr = lr / (1 + (step-1)*lr_decay), computed by the caller
  * Deterministic: each run is summed in sorted (stable) order; runs longer than one 32-position
  * segment are reduced per segment and the segment partials added in ascending order.
@@ -134,7 +141,7 @@ size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D);
 int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms,
                      const int64_t* table_row_base, int T, int B, int D, int64_t table_ld,
                      const float* grad, int64_t stride_b, int64_t stride_t,
-                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N,
+                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows,
                      float lr, float eps,
                      void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
 
@@ -151,6 +158,16 @@ int dlrmx_bwd_coalesce(int B, int D, const float* grad, int64_t stride_b, int64_
  * dlrm_s_pytorch.py:1636-1637).  rows [U] int64 unique row ids, gsum [U, D] summed gradient rows. */
 int dlrmx_rows_update(int optimizer, float* table, float* mom, const int64_t* rows, const float* gsum,
                       int64_t U, int D, float lr, float eps, dlrmx_stream_t stream);
+
+/* Replicated (data-parallel) tables -- a sharding policy next to the reference's table-wise one (sharders.py:23-60,
+ * dlrm_s_pytorch.py:444-468): tables with fewer rows than the batch are cheaper to keep on every rank than to exchange.
+ * Each rank accumulates its LOCAL batch's pooled-row gradients per row into a zeroed dense buffer gsum [rows, D]
+ * (dlrmx_bwd_update with DLRMX_OPT_SGD, lr = -1 and gsum as the "table": w + 1*g on w = 0 is exact), the buffers are
+ * summed across ranks (all-reduce), and this call applies the sparse optimizer step of optim/rwsadagrad.py:97-113 /
+ * torch.optim.SGD to every row whose summed gradient is non-zero -- untouched rows keep their bits, as in the reference --
+ * and clears those rows of gsum for the next step.  table [rows, D] with row pitch table_ld (0 = D), mom [rows]. */
+int dlrmx_dense_rows_update(int optimizer, float* table, float* mom, float* gsum, int64_t rows, int D,
+                            int64_t table_ld, float lr, float eps, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Dot / cat feature interaction.  Replaces DLRM_Net.interact_features (dlrm_s_pytorch.py:627-673):
@@ -242,8 +259,7 @@ int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
  * embbag_fwd_scatter: dlrmx_embbag_fwd, but the pooled row of bag (t, b) of the GLOBAL batch is stored
  *   at  out_peers[b / lb] + (b % lb)*stride_b + t*stride_t : out_peers is a DEVICE array [B / lb] of
  *   peer-mapped pointers, each already offset to this rank's first feature slot in that peer's
- *   [lb, 1+T, D] interaction input.  [mb_off, mb_off + mb_len) selects a window of every rank's local batch
- *   (micro-batched exchange: the launch covers only those samples; mb_off = 0, mb_len = lb: everything).
+ *   [lb, 1+T, D] interaction input.
  * a2a_push_grad: dfeat [lb, F, D] (this rank's local batch, all tables) -> for every owner rank p the
  *   chunk [lb, T_p, D] stored at host_peer_chunk_bases[p] (HOST array [W] of peer-mapped device
  *   pointers = rank p's gradient buffer [W*lb, T_p, D] + my_rank*lb*T_p*D).
@@ -251,22 +267,14 @@ int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
 int dlrmx_embbag_fwd_scatter_i32(const float* const* tables, const int64_t* table_rows,
                                  const int32_t* indices, const int32_t* offsets, int64_t N, int T, int B,
                                  int D, int64_t table_ld, const float* per_sample_weights, float* const* out_peers, int lb,
-                                 int mb_off, int mb_len, int64_t stride_b, int64_t stride_t, int* err_flag,
-                                 dlrmx_stream_t stream);
+                                 int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
 int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* table_rows,
                                  const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
                                  int D, int64_t table_ld, const float* per_sample_weights, float* const* out_peers, int lb,
-                                 int mb_off, int mb_len, int64_t stride_b, int64_t stride_t, int* err_flag,
-                                 dlrmx_stream_t stream);
+                                 int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
 int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D,
                         float* const* host_peer_chunk_bases, dlrmx_stream_t stream);
-/* The same exchange on the COPY ENGINES (no SM is occupied, so the transfer truly overlaps tower kernels on another
- * stream): one pitched device-to-peer copy per (window, peer) -- forward: rank r's pooled block [ln, T_r*D] -> peer's
- * interaction input (row pitch F*D); backward: the gradient slice [ln, T_p*D] (row pitch F*D) -> owner's buffer.
- * Thin stream-ordered wrapper over cudaMemcpy2DAsync(cudaMemcpyDefault); pointers may be peer-mapped. */
-int dlrmx_copy2d_async(void* dst, size_t dst_pitch_bytes, const void* src, size_t src_pitch_bytes,
-                       size_t width_bytes, size_t height, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Loss: binary cross-entropy, mean reduction.  Replaces dlrm.loss_fn = torch.nn.BCELoss(reduction="mean")

@@ -18,20 +18,23 @@ import torch
 from torch import nn
 
 
-def build_tables(rows, D, init="numpy"):
+def build_tables(rows, D, init="numpy", device=None):
     """create_emb (dlrm_s_pytorch.py:267-318): one nn.EmbeddingBag(n, D, mode='sum', sparse=True) per table,
-    U(+-sqrt(1/n)) weights; numpy RNG in table order (parity) or torch RNG (large timing runs)."""
+    U(+-sqrt(1/n)) weights; numpy RNG in table order (parity) or torch RNG (large timing runs: the weight is drawn
+    once, directly on `device`, instead of nn.EmbeddingBag's own normal_ fill followed by the overwrite)."""
     tables = nn.ModuleList()
     for n in rows:
         n = int(n)
-        E = nn.EmbeddingBag(n, D, mode="sum", sparse=True)
         a = float(np.sqrt(1 / n))
         if init == "numpy":
+            E = nn.EmbeddingBag(n, D, mode="sum", sparse=True)
             E.weight.data = torch.tensor(np.random.uniform(low=-a, high=a, size=(n, D)).astype(np.float32),
                                          requires_grad=True)
+            if device is not None:
+                E = E.to(device)
         else:
-            with torch.no_grad():
-                E.weight.uniform_(-a, a)
+            w = torch.empty((n, D), dtype=torch.float32, device=device).uniform_(-a, a)
+            E = nn.EmbeddingBag(n, D, mode="sum", sparse=True, _weight=w)
         tables.append(E)
     return tables
 
@@ -89,10 +92,12 @@ class Model:
     """The pieces of DLRM_Net that lie on the hot path, in the reference's construction order (tables, then
     bottom MLP, then top MLP -- dlrm_s_pytorch.py:469-496) so that numpy-seeded weights match."""
 
-    def __init__(self, rows, D, ln_bot, ln_top, init="numpy", interaction_op="dot", itself=False):
-        self.tables = build_tables(rows, D, init)
+    def __init__(self, rows, D, ln_bot, ln_top, init="numpy", interaction_op="dot", itself=False, device=None):
+        self.tables = build_tables(rows, D, init, device)
         self.bot = build_mlp(ln_bot, -1)
         self.top = build_mlp(ln_top, len(ln_top) - 2)
+        if device is not None:
+            self.bot, self.top = self.bot.to(device), self.top.to(device)
         self.op, self.itself = interaction_op, itself
         self.loss_fn = nn.BCELoss(reduction="mean")
         self.state = {}
@@ -115,6 +120,12 @@ class Model:
         loss = self.loss_fn(self.forward(X, lS_o, lS_i), target)
         loss.backward()
         self.steps += 1
+        self.apply_optimizer(lr, optimizer, eps)
+        return float(loss.item())
+
+    def apply_optimizer(self, lr, optimizer="rwsadagrad", eps=1e-10):
+        """The optimizer half of the iteration: torch.optim.SGD (dlrm_s_pytorch.py:1640) or RWSAdagrad.step
+        (optim/rwsadagrad.py:56-122) on the gradients the backward pass left."""
         with torch.no_grad():
             for p in self.params():
                 if p.grad is None:
@@ -122,9 +133,10 @@ class Model:
                 if optimizer == "sgd":                      # torch.optim.SGD: p += -lr * grad (sparse or dense)
                     p.data.add_(p.grad, alpha=-lr)
                 elif p.grad.is_sparse:
-                    mom = self.state.setdefault(p, torch.zeros(p.shape[0]))
-                    rwsadagrad_sparse_step(p, p.grad, mom, lr, eps, self.steps)
+                    if p not in self.state:
+                        self.state[p] = torch.zeros(p.shape[0], device=p.device)
+                    rwsadagrad_sparse_step(p, p.grad, self.state[p], lr, eps, self.steps)
                 else:
-                    acc = self.state.setdefault(p, torch.zeros_like(p))
-                    adagrad_dense_step(p, p.grad, acc, lr, eps)
-        return float(loss.item())
+                    if p not in self.state:
+                        self.state[p] = torch.zeros_like(p)
+                    adagrad_dense_step(p, p.grad, self.state[p], lr, eps)

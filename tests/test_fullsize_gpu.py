@@ -3,6 +3,8 @@
 
 The numpy oracle cannot walk these sizes in seconds, so the kernels are held to properties that do not depend on size:
   * the sort is checked EXACTLY against torch.sort(stable=True) on the same keys (integer work: bit-exact);
+  * the lookup is checked EXACTLY where that is cheap: with one id per bag (Terabyte) the pooled row is the table row, so all
+    852 K bags are compared bit for bit; with 100 ids per bag a 1 % sample of the bags against the sequential numpy oracle;
   * lookup linearity: scaling every table by 2 (exact in fp32) must scale every pooled row by exactly 2;
   * lookup checksum: sum of all pooled rows == sum over all looked-up rows, accumulated in fp64;
   * fused SGD update: sum(W') - sum(W) == -lr * sum over lookups of the gradient row (fp64 checksum), rows that were
@@ -69,6 +71,18 @@ def _properties(rows, D, B, L, dev, lr=0.05):
     got_sum = float(out.sum(dtype=torch.float64))
     scale = float(out.abs().sum(dtype=torch.float64))
     assert abs(got_sum - ref_sum) <= 1e-8 * scale + 1e-2, (got_sum, ref_sum)     # one dropped row would move it by ~5
+    # ---- lookup: EXACT checks at full size ------------------------------------------------------------------------------
+    if L == 1:      # one id per bag: the pooled row IS the table row -- every one of the T*B bags, bit for bit
+        for t in range(T):
+            assert torch.equal(out[:, t, :], tw[t][idx[t * B:(t + 1) * B].long()]), t
+    else:           # a 1 % sample of the bags against the sequential numpy oracle (index order, plain fp32 adds)
+        from oracle import oracle_np as O
+        rs = np.random.default_rng(5)
+        for t in rs.choice(T, size=min(T, 4), replace=False):
+            for b in rs.choice(B, size=max(1, (B * T // 100) // 4), replace=False):
+                ids = idx[(t * B + b) * L:(t * B + b + 1) * L].long()
+                ref = O.embbag_fwd_table(tw[t][ids].cpu().numpy(), np.arange(L), np.array([0]))
+                assert np.array_equal(out[b, t, :].cpu().numpy(), ref[0]), (t, b)
     for w in tw:
         w.mul_(2.0)
     out2 = ops.embbag_forward(ts, idx, off, B)

@@ -123,3 +123,89 @@ def test_alltoall_two_ranks_gloo(tmp_path, batched):
         assert np.array_equal(got["out"], want[r])
         assert np.array_equal(got["grad"], want_grad[r])
         assert got["slice"].tolist() == [r * 3, r * 3 + 3]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# multi-process path: fixtures of the reference's own 2-process run (oracle/gen_golden_dist.py) against the single-process
+# fixtures, and the host-side input split with replicated tables
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case,sharder", [("c4_terabyte_small_rws", "naive_chunk"), ("c4_terabyte_small_rws", "greedy"),
+                                           ("c3_multihot_sgd", "naive")])
+def test_distributed_reference_fixture_is_rank_major_slices_of_the_single_process_one(golden_dir, case, sharder):
+    """What the reference's all-to-all delivers to rank r (extend_distributed.py:405-508): its batch slice of every table's
+    pooled rows, tables in RANK-MAJOR order -- bit-identical to slices of the single-process run; the
+    oracle's permutation (oracle_np.alltoall_fwd) restates exactly that."""
+    g = np.load(os.path.join(golden_dir, case + ".npz"))
+    d = np.load(os.path.join(golden_dir, "dist_w2_%s_%s.npz" % (case, sharder)))
+    W, T = int(d["meta_W"]), len(g["meta_ln_emb"])
+    B = int(g["meta_misc"][1])
+    lb = B // W
+    dev = d["device_indices"].tolist()
+    assert dev == sharders.shard(g["meta_ln_emb"], W, sharder)
+    order = [i for r in range(W) for i in range(T) if dev[i] == r]
+    pooled = g["pooled"]                                     # [B, T, D] single process
+    per_rank = [pooled[:, [i for i in range(T) if dev[i] == r], :] for r in range(W)]
+    for r in range(W):
+        got = d["r%d_feat_ly" % r]
+        assert np.array_equal(got, pooled[r * lb:(r + 1) * lb][:, order, :])
+        assert np.array_equal(O.alltoall_fwd(per_rank, W)[r], got)
+        assert np.array_equal(d["r%d_feat_x" % r], g["x_bot"][r * lb:(r + 1) * lb])
+    # each rank's loss is the mean over ITS slice; with equal slices their mean is the single-process loss -- when the
+    # rank-major feature order is the table order (otherwise the top tower's columns meet other features: the reference's
+    # multi-process model is a different function of the same weights)
+    if order == list(range(T)):
+        np.testing.assert_allclose(    np.mean([float(d["r%d_loss1" % r]) for r in range(W)]), float(g["loss"]), rtol=1e-6)
+
+
+def test_distribute_batched_emb_data_with_replicated_tables():
+    """DLRM_Net.distribute_batched_emb_data (dlrm_s_pytorch.py:772-802): local sharded tables x GLOBAL batch, and -- with
+    replicated tables -- those tables x this rank's slice, offsets re-based; ragged bags."""
+    from dlrm_yx_b200 import dlrm_net
+    from dlrm_yx_b200 import extend_distributed as ext
+    rng = np.random.default_rng(11)
+    rows, B, W = [50, 7, 3, 1000, 9], 8, 2
+    X, lS_o, lS_i, tgt = data.random_batch(rows, B, 4, 3, fixed=False, rng=rng)
+    idx, off = data.pack(lS_o, lS_i)
+    saved = (ext.my_size, ext.my_rank, ext.my_local_rank)
+    try:
+        for rank in range(W):
+            ext.my_size, ext.my_rank, ext.my_local_rank = W, rank, rank
+            m = dlrm_net.DLRM_Net()
+            m.local_emb_indices = [0, 3] if rank == 0 else [4]
+            m.replicated_emb_indices = [1, 2]
+            m.emb_rep = object()
+            o, i = m.distribute_batched_emb_data(B, off, idx)
+            (so, ro), (si, ri) = o[0], i[0]
+            ei, eo = data.local_packed(lS_o, lS_i, m.local_emb_indices)
+            assert torch.equal(so, eo) and torch.equal(si, ei)
+            lb = B // W
+            ends = [torch.cat([lS_o[k], torch.tensor([lS_i[k].numel()])]) for k in range(len(rows))]
+            exp_o, exp_i = [], []
+            for k in m.replicated_emb_indices:
+                lo, hi = int(ends[k][rank * lb]), int(ends[k][(rank + 1) * lb])
+                exp_o.append(lS_o[k][rank * lb:(rank + 1) * lb] - lo)
+                exp_i.append(lS_i[k][lo:hi])
+            xi, xo = data.pack(exp_o, exp_i)
+            assert torch.equal(ro, xo) and torch.equal(ri, xi)
+            m.emb_rep = None
+            o, i = m.distribute_batched_emb_data(B, off, idx)
+            assert torch.equal(o[0], eo) and torch.equal(i[0], ei)
+    finally:
+        ext.my_size, ext.my_rank, ext.my_local_rank = saved
+
+
+def test_installed_module_has_the_surface_the_reference_imports():
+    """dlrm_s_pytorch.py:321-334 does `import table_batched_embeddings_ops` and calls
+    TableBatchedEmbeddingBags(T, Es, D, optimizer=Optimizer.SGD, learning_rate=..., eps=0.1, stochastic_rounding=False)."""
+    import importlib
+    import inspect
+    from dlrm_yx_b200 import embedding
+    embedding.install_table_batched_embeddings_ops()
+    mod = importlib.import_module("table_batched_embeddings_ops")
+    assert mod.Optimizer.SGD is embedding.Optimizer.SGD
+    sig = inspect.signature(mod.TableBatchedEmbeddingBags.__init__)
+    names = list(sig.parameters)
+    assert names[1:4] == ["num_tables", "num_embeddings", "embedding_dim"]
+    for kw in ("optimizer", "learning_rate", "eps", "stochastic_rounding"):
+        assert kw in sig.parameters
+    assert list(inspect.signature(mod.TableBatchedEmbeddingBags.forward).parameters)[1:] == ["indices", "offsets"]

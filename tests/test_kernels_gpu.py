@@ -104,21 +104,48 @@ def test_forward_long_bags_and_weights():
     assert np.array_equal(outw.cpu().numpy(), np.stack(refw, axis=1))
 
 
-@pytest.mark.parametrize("D", [128, 64, 32, 16, 256])
-@pytest.mark.parametrize("K", [0, 2, 3, 8, 4, 5, 6, 7])
-def test_forward_long_bag_variants_bit_exact(D, K, request):
-    """Long-bag walk: every (bags in lockstep, rows in flight, CTAs per SM) variant is bit-exact with the sequential
-    oracle -- loads are issued U at a time, the adds stay in index order.  Ragged lengths 0..120."""
-    from dlrm_yx_b200 import ops, _lib
+@pytest.mark.parametrize("D", [128, 64, 32, 16, 256, 96])
+def test_forward_long_bags_bit_exact(D):
+    """Long-bag walk (one bag per group, 8 rows in flight): bit-exact with the sequential oracle -- loads are issued U at
+    a time, the adds stay in index order.  Ragged lengths 0..120."""
+    from dlrm_yx_b200 import ops
     dev = cuda()
     rng = np.random.default_rng(17 + D)
     rows, B = [3000, 70000, 5], 67
     Ws, idx, off = make_case(rng, rows, D, B, max_len=120, empty_frac=0.05)
     ts, di, do = to_dev(Ws, idx, off, dev, torch.int32)
-    _lib.set_tunable(_lib.TUNE_FWD_K, K)
-    request.addfinalizer(lambda: _lib.set_tunable(_lib.TUNE_FWD_K, 0))
     out = ops.embbag_forward(ts, di, do, B)
     assert np.array_equal(out.cpu().numpy(), O.embbag_fwd_batched(Ws, idx, off, B))
+
+
+def test_backward_flags_and_skips_out_of_range_index():
+    """An index >= rows_t (or negative) must neither alias a row of the next table nor write out of bounds: the sort gives
+    it the key one past the last valid row, the fused update drops that run, the error word is set and the host layer
+    raises -- nn.EmbeddingBag raises on the same input."""
+    from dlrm_yx_b200 import _lib, ops
+    dev = cuda()
+    rows, D, B = [4, 6], 8, 5
+    tw = [torch.ones((r, D), device=dev) for r in rows]
+    ts = ops.TableSet(tw, moms=[torch.zeros(r, device=dev) for r in rows])
+    # table 0: one index == rows (would alias row 0 of table 1), one negative; table 1: one far out of range
+    idx = torch.tensor([1, 4, 2, -1, 3, 0, 5, 99, 1, 2], dtype=torch.int32, device=dev)
+    off = torch.arange(2 * B + 1, dtype=torch.int32, device=dev)
+    ops.check_index_errors()
+    skey, sbag = ops.bwd_sort(ts, idx, off, B)
+    assert skey.cpu().numpy().view(np.uint32).max() == sum(rows)           # the invalid key, sorted last
+    assert int((skey.cpu().numpy().view(np.uint32) == sum(rows)).sum()) == 3
+    grad = torch.ones((B, 2, D), device=dev)
+    for opt in (_lib.OPT_SGD, _lib.OPT_RWSADAGRAD):
+        before = [w.clone() for w in tw]
+        ops.bwd_update(ts, opt, grad, 2 * D, D, B, skey, sbag, 0.5, 1e-10)
+        touched0, touched1 = {1, 2, 3}, {0, 5, 1, 2}
+        for r in range(rows[0]):
+            assert (not torch.equal(tw[0][r], before[0][r])) == (r in touched0)
+        for r in range(rows[1]):
+            assert (not torch.equal(tw[1][r], before[1][r])) == (r in touched1)
+    with pytest.raises(_lib.DlrmxError, match="out of range"):
+        ops.check_index_errors()
+    ops.check_index_errors()          # the word is cleared by the raise
 
 
 def test_forward_flags_out_of_range_index():
@@ -342,19 +369,18 @@ def test_interaction_fwd_bwd(F, D, itself, B, request):
 
 @pytest.mark.parametrize("F,D", [(27, 128), (27, 16), (9, 64), (2, 8), (32, 32), (5, 256)])
 @pytest.mark.parametrize("itself", [False, True])
-@pytest.mark.parametrize("warp_kernel,staging,B", [(0, 0, 21), (1, 0, 21), (0, 1, 21), (0, 0, 500), (0, 1, 500)])
-def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, staging, B, request):
+@pytest.mark.parametrize("staging,B", [(0, 21), (1, 21), (0, 500), (1, 500)])
+def test_interaction_mixed_bf16_facing(F, D, itself, staging, B, request):
     """bf16-facing interaction (feature 0 in / result out / dR in / dx out as bf16, single-pass TF32 products, fp32
     accumulate) against the fp32 oracle on the SAME bf16-rounded inputs.  Bars: bf16 outputs 2^-8 relative (one bf16
     rounding, half an ulp = 2^-9, with margin) plus the TF32 operand rounding 2^-10 * sum|a||b|; fp32 outputs the
     TF32 term only.  Padding columns must be exactly zero."""
     from dlrm_yx_b200 import _lib, ops
     dev = cuda()
-    _lib.set_tunable(4, warp_kernel)          # 1: the one-warp-per-sample experiment (interact_warp.cu)
     # staging 1: the input has a feature pitch of D + 8 (where the kernels take it: D % 32 == 0) -> one TMA bulk copy +
     # mbarrier per sample instead of per-thread cp.async; the results must not change by a single bit
     _lib.set_tunable(11, 1 if B > 100 else 0) # one CTA per SM: every CTA loops over several samples (both stages / phases)
-    request.addfinalizer(lambda: (_lib.set_tunable(4, 0), _lib.set_tunable(11, 0)))
+    request.addfinalizer(lambda: _lib.set_tunable(11, 0))
     rng = np.random.default_rng(F * 100 + D + 7)
     bf = torch.bfloat16
     feat = rng.normal(size=(B, F, D)).astype(np.float32)
@@ -387,7 +413,7 @@ def test_interaction_mixed_bf16_facing(F, D, itself, warp_kernel, staging, B, re
     e_dx = np.abs(dx.float().cpu().numpy() - rdx)
     assert np.all(e_dx <= 2.0 ** -8 * np.abs(rdx) + 2.0 ** -10 * mdx + 1e-6), e_dx.max()
 
-    if staging == 1 and D % 32 == 0 and warp_kernel == 0:
+    if staging == 1 and D % 32 == 0:
         # pitched input (feature pitch D + 8, padding poisoned): TMA bulk-copy staging, same bits as above
         dfp = torch.full((B, F, D + 8), float("nan"), device=dev)[:, :, :D]
         dfp[:, 1:, :] = df[:, 1:, :]

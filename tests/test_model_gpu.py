@@ -10,6 +10,7 @@ import numpy as np
 import pytest
 import torch
 
+from dlrm_yx_b200 import data
 from oracle import oracle_np as O
 
 pytestmark = pytest.mark.gpu
@@ -180,6 +181,65 @@ def test_torch_op_batched_forward_single_device():
     out = torch.ops.batched_forward.forward([cu(np.concatenate(Ws))], [cu(toff)], [cu(off)], [cu(idx)], L, 8, False)
     assert tuple(out.shape) == (B, len(rows), D)
     assert np.array_equal(out.cpu().numpy(), O.embbag_fwd_batched(Ws, idx, off, B))
+
+
+def test_torch_op_batched_forward_two_devices():
+    """The multi-device branch of the yx op (yx_modfs/dlrm.py:94-119: one weights / table_offsets / offsets / indices tensor
+    per GPU, output [B, nGPU*T, D] on the device of weights[0]): device 1's lookup kernel stores its pooled rows straight
+    into device 0's output over NVLink (P2P stores).  Needs 2 GPUs."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import dlrm_yx_b200.batched_forward  # noqa: F401
+    rng = np.random.default_rng(4)
+    rows, D, B, L = [40, 7, 300], 64, 33, 5
+    devs = [torch.device("cuda", 0), torch.device("cuda", 1)]
+    Ws, idxs, args = [], [], ([], [], [], [])
+    off = (np.arange(len(rows) * B + 1) * L).astype(np.int32)
+    toff = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int32)
+    for d in devs:
+        W = [rng.uniform(-1, 1, size=(r, D)).astype(np.float32) for r in rows]
+        idx = np.concatenate([rng.integers(0, r, size=B * L) for r in rows]).astype(np.int32)
+        Ws.append(W)
+        idxs.append(idx)
+        for lst, a in zip(args, (np.concatenate(W), toff, off, idx)):
+            lst.append(torch.from_numpy(a).to(d))
+    out = torch.ops.batched_forward.forward(args[0], args[1], args[2], args[3], L, 8, False)
+    torch.cuda.synchronize(0)
+    torch.cuda.synchronize(1)
+    assert out.device == devs[0] and tuple(out.shape) == (B, 2 * len(rows), D)
+    ref = np.concatenate([O.embbag_fwd_batched(Ws[k], idxs[k], off, B) for k in range(2)], axis=1)
+    assert np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_installed_module_runs_as_the_reference_calls_it():
+    """dlrm_s_pytorch.py:321-334, 589-591: `import table_batched_embeddings_ops`, construct with the reference's keyword
+    arguments, call `emb(indices, offsets)`; the optimizer is fused into backward and the parameters are ALSO handed to an
+    outer optimizer (1650), whose step must then be a no-op for them (grad stays None)."""
+    import importlib
+    from dlrm_yx_b200 import embedding
+    embedding.install_table_batched_embeddings_ops()
+    tbe = importlib.import_module("table_batched_embeddings_ops")
+    rng = np.random.default_rng(9)
+    rows, D, B = [30, 5, 100], 16, 12
+    np.random.seed(3)
+    emb = tbe.TableBatchedEmbeddingBags(len(rows), np.array(rows), D, optimizer=tbe.Optimizer.SGD, learning_rate=0.1,
+                                        eps=0.1, stochastic_rounding=False).to("cuda")
+    Ws = [w.cpu().numpy().copy() for w in emb.split_weights()]
+    X, lS_o, lS_i, tgt = data.random_batch(rows, B, 3, 4, fixed=False, rng=rng)
+    idx, off = data.pack(lS_o, lS_i)
+    outer = torch.optim.SGD(emb.parameters(), lr=0.1)
+    out = emb(idx.cuda(), off.cuda())
+    assert np.array_equal(out.detach().cpu().numpy(), O.embbag_fwd_batched(Ws, idx.numpy(), off.numpy(), B))
+    go = torch.randn_like(out)
+    out.backward(go)
+    assert emb.embedding_weights.grad is None
+    outer.step()
+    base = np.concatenate([[0], np.cumsum(rows)])
+    art = O.sort_artifacts(idx.numpy(), off.numpy(), len(rows), B, base[:-1])
+    g = O.embbag_bwd_coalesced(O.go_rows(go.cpu().numpy()), art, D)
+    Wcat = np.concatenate(Ws)
+    O.sgd_update(Wcat, art["unique"], g, 0.1)
+    np.testing.assert_allclose(torch.cat(emb.split_weights()).cpu().numpy(), Wcat, rtol=RT, atol=AT)
 
 
 def test_rwsadagrad_steps_torch_embeddingbag_grads_too():

@@ -1,7 +1,11 @@
-"""Needs >= 2 GPUs on the box (skipped otherwise): the peer-memory exchange (embbag_fwd_scatter / a2a_push_grad over
-NVLink) against the NCCL all-to-all path, bit for bit, and against the reference's golden vectors.  The checker is
-tools/check_exchange.py, launched with torch.distributed.run as the driver launches bench.py."""
+"""Needs >= 2 GPUs on the box (skipped otherwise): the model-parallel path -- NCCL all-to-all, peer-memory exchange
+(embbag_fwd_scatter / a2a_push_grad over NVLink), replicated small tables, CUDA-graph replay -- against each other bit
+for bit and against the fixtures the unmodified reference produced as a 2-process gloo run (tests/golden/dist_w2_*.npz).
+The checker is tools/check_exchange.py, launched with torch.distributed.run as the driver launches bench.py.  On a
+1-GPU box the same properties are checked by bench.py itself before its timed region whenever it runs with N > 1
+(the "parity" key of its JSON line)."""
 import os
+import socket
 import subprocess
 import sys
 
@@ -12,12 +16,22 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("name", ["c4_terabyte_small_rws", "c3_multihot_sgd"])
-def test_peer_exchange_matches_nccl_and_reference(name):
-    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("name,sharders", [("c4_terabyte_small_rws", "naive_chunk,greedy,traffic"),
+                                           ("c3_multihot_sgd", "naive")])
+def test_exchange_paths_match_each_other_and_the_reference(name, sharders):
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n < 2:
         pytest.skip("needs 2 GPUs")
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tools", "check_exchange.py"), name]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    W = 4 if (n >= 4 and name.startswith("c4")) else 2
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(W), "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tools", "check_exchange.py"),
+           "--case", name, "--sharders", sharders]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count("exchange parity OK") == 2
+    assert r.stdout.count("exchange parity OK") == W

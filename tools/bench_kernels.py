@@ -121,27 +121,20 @@ def main():
         print(json.dumps(d), flush=True)
 
     only = set(args.only.split(",")) if args.only else None
-    long_bags = L > 2
-    fwd_variants = (0, 7, 6, 2, 8) if long_bags else (8, 4, 0)   # see the FWD_K tunable in csrc/embbag_fwd.cuh
-    for k in fwd_variants:
-        if only and "fwd" not in only:
-            break
-        _lib.set_tunable(_lib.TUNE_FWD_K, k)
-
+    if not only or "fwd" in only:
         def f():
             idx, off = batches[it[0] % nbatch]
             it[0] += 1
             ops.embbag_forward(ts, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=False)
         ms, mn = timed(f, args.iters)
-        report("embbag_fwd", ms, mn, fwd_bytes, dict(K=k))
+        report("embbag_fwd", ms, mn, fwd_bytes)
 
         def fv():
             idx, off = batches[it[0] % nbatch]
             it[0] += 1
             ops.embbag_forward(ts, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=True)
         ms, mn = timed(fv, args.iters)
-        report("embbag_fwd", ms, mn, fwd_bytes, dict(K=k, validate=1))
-    _lib.set_tunable(_lib.TUNE_FWD_K, 0)
+        report("embbag_fwd", ms, mn, fwd_bytes, dict(validate=1))
 
     def s():
         idx, off = batches[it[0] % nbatch]
@@ -157,9 +150,8 @@ def main():
     for opt, name in ((_lib.OPT_SGD, "sgd"), (_lib.OPT_RWSADAGRAD, "rwsadagrad")):
         if only and "bwd" not in only:
             break
-        for seg, k8 in ((0, 0), (0, 4), (0, 2), (32, 2), (128, 2), (0, 25), (0, 16), (32, 16)):
+        for seg in (0, 32, 64, 128, 256):        # sorted positions per group (test hook 3; 0 = the default choice)
             _lib.set_tunable(3, seg)
-            _lib.set_tunable(_lib.TUNE_BWD_K, k8)
 
             def u():
                 sk, sb = sorted_batches[it[0] % nbatch]
@@ -167,9 +159,8 @@ def main():
                 ops.bwd_update(ts, opt, grad, GS * D, D, B, sk, sb, 0.01, 1e-10)
             ms, mn = timed(u, args.iters)
             nbytes = T * B * D * 4 + N * 8 + 2 * U * D * 4 + (2 * U * 4 if opt else 0)
-            report("bwd_update_" + name, ms, mn, nbytes, dict(seg=seg, K=k8, U=int(U)))
-    for k in (3, 1):
-        _lib.set_tunable(k, 0)
+            report("bwd_update_" + name, ms, mn, nbytes, dict(seg=seg, U=int(U)))
+    _lib.set_tunable(3, 0)
     if only and "dense" not in only and "ix" not in only:
         return
 
