@@ -57,6 +57,13 @@ SIGNATURES = {
                                              c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
     "dlrmx_relu_bwd_bias_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                          c_int, c_int, c_void_p]),
+    "dlrmx_gemm_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_int, c_int, c_int,
+                                c_void_p, c_void_p, c_int64, c_void_p]),
+    "dlrmx_gemm_wgrad_workspace_bytes": (c_size_t, [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_int]),
+    "dlrmx_gemm_wgrad_bf16": (c_int, [c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), ctypes.POINTER(c_void_p),
+                                      ctypes.POINTER(c_int64), ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64),
+                                      ctypes.POINTER(c_void_p), ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_int,
+                                      c_void_p, c_size_t, c_void_p]),
     "dlrmx_head_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "dlrmx_head_bwd_workspace_bytes": (c_size_t, [c_int, c_int]),
     "dlrmx_head_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

@@ -429,6 +429,57 @@ def relu_bwd_bias_grad(dy, y, relu=True, chunks=None, db=None):
     return dz, part
 
 
+EPI_NONE, EPI_BIAS_RELU, EPI_RELU_MASK, EPI_BIAS = 0, 1, 2, 3
+
+
+def gemm_bf16(a, b, b_is_kn=False, epilogue=EPI_NONE, bias=None, relu_mask=None, out=None):
+    """Tensor-core GEMM (tcgen05 / TMEM / TMA): out [M, N] bf16 = epilogue(a [M, K] . op(b)); b is [N, K] (y = x W^t) or,
+    with b_is_kn, [K, N] (dx = dz W).  Row-major bf16 operands with unit column stride."""
+    _need_cuda(a, b, bias, relu_mask, out)
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.stride(1) != 1 or b.stride(1) != 1:
+        raise _lib.DlrmxError("gemm_bf16: bf16 row-major operands with unit column stride")
+    M, K = a.shape
+    N = b.shape[1] if b_is_kn else b.shape[0]
+    if (b.shape[0] if b_is_kn else b.shape[1]) != K:
+        raise _lib.DlrmxError("gemm_bf16: contraction sizes differ (%s x %s)" % (tuple(a.shape), tuple(b.shape)))
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    with _timed("gemm_bf16"):
+        rc = _lib.load().dlrmx_gemm_bf16(a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), int(b_is_kn), out.data_ptr(),
+                                         out.stride(0), M, N, K, int(epilogue), _ptr(bias), _ptr(relu_mask),
+                                         0 if relu_mask is None else relu_mask.stride(0), _stream())
+        _lib.check(rc, "dlrmx_gemm_bf16")
+    return out
+
+
+def gemm_wgrad_workspace(Ns, Ks, M, device):
+    """Zeroed workspace for gemm_wgrad_bf16 on layers of these shapes (keep it: the kernel leaves its counters zero)."""
+    n = len(Ns)
+    nbytes = _lib.load().dlrmx_gemm_wgrad_workspace_bytes(n, _int_array(Ns), _int_array(Ks), int(M))
+    return torch.zeros(nbytes, dtype=torch.uint8, device=device)
+
+
+def gemm_wgrad_bf16(dzs, xs, dws, dbs, workspace):
+    """For every layer l: dws[l] [N_l, K_l] fp32 = dzs[l]^t xs[l], dbs[l] [N_l] = column sums of dzs[l] (None: skip) -- all
+    layers in ONE stream-K tensor-core launch; dzs[l] [M, N_l], xs[l] [M, K_l] bf16 row-major."""
+    n = len(dzs)
+    _need_cuda(*dzs, *xs, *dws, workspace)
+    M = dzs[0].shape[0]
+    vp = lambda ts: (ctypes.c_void_p * n)(*[0 if t is None else t.data_ptr() for t in ts])      # noqa: E731
+    i64 = lambda vs: (ctypes.c_int64 * n)(*[int(v) for v in vs])                               # noqa: E731
+    for dz, x, dw in zip(dzs, xs, dws):
+        if dz.dtype != torch.bfloat16 or x.dtype != torch.bfloat16 or dw.dtype != torch.float32 or dz.shape[0] != M or \
+                x.shape[0] != M or dz.stride(1) != 1 or x.stride(1) != 1 or dw.stride(1) != 1 or \
+                tuple(dw.shape) != (dz.shape[1], x.shape[1]):
+            raise _lib.DlrmxError("gemm_wgrad_bf16: dz [M, N] / x [M, K] bf16 row-major, dw [N, K] fp32")
+    with _timed("gemm_wgrad"):
+        rc = _lib.load().dlrmx_gemm_wgrad_bf16(
+            n, vp(dzs), i64([t.stride(0) for t in dzs]), vp(xs), i64([t.stride(0) for t in xs]), vp(dws),
+            i64([t.stride(0) for t in dws]), vp(dbs) if dbs is not None else None, _int_array([t.shape[1] for t in dzs]),
+            _int_array([t.shape[1] for t in xs]), M, workspace.data_ptr(), workspace.numel(), _stream())
+        _lib.check(rc, "dlrmx_gemm_wgrad_bf16")
+
+
 def head_fwd(h, w, bias, sigmoid=True):
     """p [B, 1] fp32 = sigmoid(h @ w + bias) for a bf16 activation h [B, K] and fp32 w [K], bias [1]."""
     _need_cuda(h, w, bias)

@@ -220,6 +220,30 @@ int dlrmx_relu_bwd_bias_grad(const void* dy_bf16, const void* y_bf16, void* dz_b
 int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
                     float eps, float grad_scale, dlrmx_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Tower GEMMs on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands staged by TMA), bf16 in /
+ * fp32 accumulate.  Replaces the cuBLAS GEMMs of nn.Linear in create_mlp / apply_mlp (dlrm_s_pytorch.py:227-265, 518-524)
+ * and of their autograd backward.
+ *
+ * gemm_bf16:  C[M, N] (bf16, row pitch ldc) = epilogue( A[M, K] . op(B) ), A bf16 row-major (pitch lda)
+ *   b_is_kn = 0: B is [N, K] row-major  (forward:  y = x W^t with W [N, K] as nn.Linear stores it)
+ *   b_is_kn = 1: B is [K, N] row-major  (dgrad:    dx = dz W with the same W, no transposed copy)
+ *   epilogue 0: none;  1: + bias[N] (fp32), ReLU;  2: C = acc where relu_mask[M, N] (bf16, pitch ld_mask) > 0 else 0 -- the
+ *   ReLU backward of the layer that produced this GEMM's output gradient, so the result is that layer's dz;  3: + bias.
+ *   N % 8 == 0, K % 8 == 0, all pointers 16-byte aligned, pitches multiples of 8 elements.
+ * gemm_wgrad_bf16: for every layer l of a tower, in ONE launch:  dW[l] [N_l, K_l] (fp32, pitch ld_dw) = dZ[l]^t X[l]  and
+ *   db[l] [N_l] = column sums of dZ[l]  (dZ[l] [M, N_l], X[l] [M, K_l] bf16 row-major).  The (tile, k-step) space of all
+ *   layers is split evenly over the SMs (stream-K); partial tiles are combined in a fixed order by the CTA that finishes a
+ *   tile last, so the result is deterministic and there is no split-K reduction launch.  workspace: the size the query
+ *   returns, ZEROED before the first call (the call leaves its counters zero).  Host arrays of device pointers / sizes.
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_is_kn, void* C, int64_t ldc, int M, int N,
+                    int K, int epilogue, const float* bias, const void* relu_mask, int64_t ld_mask, dlrmx_stream_t stream);
+size_t dlrmx_gemm_wgrad_workspace_bytes(int n_layers, const int* N, const int* K, int M);
+int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld_dz, const void* const* X,
+                          const int64_t* ld_x, float* const* dW, const int64_t* ld_dw, float* const* db, const int* N,
+                          const int* K, int M, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+
 /* Head of the top tower: Linear(K -> 1) + Sigmoid (last layer of create_mlp with sigmoid_layer = last,
  * dlrm_s_pytorch.py:227-265) on a bf16 activation h [B, K] with fp32 master weights w [K], bias [1].
  *   head_fwd: p[b] = sigmoid(<h[b,:], w> + bias)            (sigmoid = 0: no activation)
