@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU mini-batch (default: the config's)")
     ap.add_argument("--global-batch", type=int, default=0, help="fix the GLOBAL batch (strong scaling)")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (debug only; marks the run)")
+    ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"],
+                    help="fused-bf16 towers: tc = the repo's tcgen05/TMEM/TMA GEMM kernels; cublas = cuBLASLt through torch, "
+                         "the measured comparator (never a fallback)")
     ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
                     help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
     ap.add_argument("--sharder", default="traffic")
@@ -203,7 +206,7 @@ def build_model(args, cfg, W, exchange=None):
         lb = cfg["B"] if not args.global_batch else args.global_batch // W
         m.enable_peer_exchange(lb, mixed=(args.mlp == "fused-bf16"))
     if args.mlp == "fused-bf16":
-        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd")
+        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm)
         return m, None
     dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
     if W > 1:
@@ -798,7 +801,8 @@ def main():
     if os.path.exists(tp) and W == 1 and args.config == "terabyte" and not args.rows_cap:
         tj = json.load(open(tp))
         traffic = tj["embbag_fwd_kernel"]["dram_read_bytes"] + tj["embbag_fwd_kernel"]["dram_write_bytes"]
-    mlp_txt = {"fused-bf16": "bf16 in / fp32 accumulate (tcgen05 GEMMs), bf16 activations"}.get(args.mlp, args.mlp)
+    gemm_txt = "the repo's tcgen05 GEMM kernels" if args.tower_gemm == "tc" else "cuBLASLt GEMMs (comparator run)"
+    mlp_txt = {"fused-bf16": "bf16 in / fp32 accumulate (%s), bf16 activations" % gemm_txt}.get(args.mlp, args.mlp)
     ix_txt = ("single-pass TF32 products, fp32 accumulate, bf16 x / R / dR / dx" if args.mlp == "fused-bf16"
               else "3xTF32 (fp32-accurate), fp32 I/O")
     line = {

@@ -9,9 +9,10 @@
 //   wgrad     dW = dZ^t X,  db = dZ^t 1     wgrad_streamk_kernel: ALL layers of a tower in ONE launch.  Both operands are
 //                                           MN-major (the contraction runs over the batch), tiles [128 n] x [<=256 k]; the
 //                                           (tile, k-step) space of all layers is cut into equal contiguous ranges, one per
-//                                           SM (stream-K), partial tiles are combined in a fixed order by the CTA that
-//                                           finishes a tile last (deterministic, no split-K reduce launches); the bias
-//                                           gradient rides along as one extra N = 16 MMA against a tile of ones.
+//                                           SM (stream-K); tiles cut into several segments leave fp32 partials that
+//                                           wgrad_reduce_kernel sums in segment order (deterministic, ONE reduce launch
+//                                           for the whole tower, element-parallel over all SMs); the bias gradient
+//                                           rides along as one extra N = 16 MMA against a tile of ones.
 // Kernel shape (both): one CTA per SM, persistent; warp 0 = TMA producer (cp.async.bulk.tensor into 128-byte-swizzled
 // stages, mbarrier expect_tx), warp 1 = MMA issuer (one elected lane issues tcgen05.mma, tcgen05.commit releases stages),
 // warps 2-5 = epilogue (tcgen05.ld 32x32b from the warp's TMEM lane quarter -> registers -> global).  The forward / dgrad
@@ -246,23 +247,32 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
             const int as = it & 1;
             const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
-            mbar_wait(&acc_full[as], aphase);
-            tc_fence_after();
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < P.M;
             __nv_bfloat16* crow = P.C + (int64_t)row * P.ldc;
             const __nv_bfloat16* mrow = P.mask + (int64_t)row * P.ld_mask;
+            const bool masked = P.epilogue == EPI_RELU_MASK && row_ok;
+            // the ReLU mask is read one 32-column chunk ahead (the first chunk before the accumulator is even complete):
+            // its global-load latency overlaps the MMAs / the previous chunk instead of stalling every chunk
+            uint4 mk[4], mk_next[4];
+            auto load_mask = [&](uint4 (&dst)[4], int col0) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (col0 + 8 * j < P.N) dst[j] = __ldg(reinterpret_cast<const uint4*>(mrow + col0 + 8 * j));
+            };
+            if (masked) load_mask(mk_next, n0);
+            mbar_wait(&acc_full[as], aphase);
+            tc_fence_after();
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 const int col0 = n0 + c * 32;
                 if (col0 >= P.N) break;                      // warp-uniform
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
-                uint4 mk[4];
-                if (P.epilogue == EPI_RELU_MASK && row_ok) {
+                if (masked) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (col0 + 8 * j < P.N) mk[j] = __ldg(reinterpret_cast<const uint4*>(mrow + col0 + 8 * j));
+                    for (int j = 0; j < 4; ++j) mk[j] = mk_next[j];
+                    if (c + 1 < BN / 32 && col0 + 32 < P.N) load_mask(mk_next, col0 + 32);
                 }
                 tmem_ld_wait();
                 float f[32];
@@ -339,7 +349,6 @@ struct WgradParams {
     int n_layers, M, ksteps, total_tiles, max_segs;
     WgradLayer L[kMaxLayers];
     float* partials;          // [total_tiles][max_segs][128][WN + 32] fp32
-    unsigned int* counters;   // [total_tiles], zero before the first launch, left zero
 };
 struct WgradMaps {
     CUtensorMap dz[kMaxLayers];   // [M, N] bf16, box {64 n, 64 m}
@@ -395,7 +404,6 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
     uint64_t* acc_full = empty + kWStages;
     uint64_t* acc_empty = acc_full + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
-    int* last_flag = reinterpret_cast<int*>(tmem_slot + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x, cta = blockIdx.x;
@@ -478,7 +486,6 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
     } else {
         // ===== epilogue =====
         const int q = warp & 3;
-        const int et = threadIdx.x - 64;                  // 0..127 within the epilogue group
         int it = 0;
         for (int64_t g = g_begin; g < g_end; ++it) {
             const Segment s = segment_at(P, g, g_end, total, G, cta);
@@ -517,37 +524,6 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty);        // the next segment's MMAs may overwrite the accumulator
-            if (single) continue;
-            // ---- combine: the CTA whose partial arrives last adds all partials of the tile in segment order ----------
-            __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (et == 0) {
-                const unsigned int done = atomicAdd(&P.counters[s.tile], 1u);
-                *last_flag = (done == (unsigned)(s.nsegs - 1));
-                if (*last_flag) P.counters[s.tile] = 0u;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            const bool last = *last_flag != 0;
-            asm volatile("bar.sync 1, 128;" ::: "memory");   // everyone has read the flag before it can be rewritten
-            if (!last) continue;
-            __threadfence();
-            const float* p0 = P.partials + (((int64_t)s.tile * P.max_segs) * BM + r) * kPartialPitch;
-            const int64_t seg_stride = (int64_t)BM * kPartialPitch;
-            if (n < L.N) {
-                for (int c4 = 0; c4 < kw; c4 += 4) {
-                    float4 a = __ldcg(reinterpret_cast<const float4*>(p0 + c4));
-                    for (int sgi = 1; sgi < s.nsegs; ++sgi) {
-                        const float4 b = __ldcg(reinterpret_cast<const float4*>(p0 + sgi * seg_stride + c4));
-                        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-                    }
-                    *reinterpret_cast<float4*>(wrow + c4) = a;
-                }
-                if (with_bias) {
-                    float a = __ldcg(p0 + WN);
-                    for (int sgi = 1; sgi < s.nsegs; ++sgi) a += __ldcg(p0 + sgi * seg_stride + WN);
-                    L.db[n] = a;
-                }
-            }
         }
     }
     tc_fence_before();
@@ -555,6 +531,49 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// Second pass of the stream-K wgrad: every tile that was cut into several segments is summed in segment order (a fixed
+// order: deterministic) into dW / db.  Element-parallel over all SMs: CTA (tile, slice of 16 rows), 256 threads, float4
+// columns, coalesced.  Tiles computed by one CTA were written by wgrad_streamk_kernel itself.
+constexpr int kReduceRows = 16;
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const WgradParams P, const int G) {
+    const int tile = blockIdx.x / (BM / kReduceRows);
+    const int r0 = (blockIdx.x % (BM / kReduceRows)) * kReduceRows;
+    const int64_t total = (int64_t)P.total_tiles * P.ksteps;
+    const int c_first = owner_of((int64_t)tile * P.ksteps, total, G);
+    const int c_last = owner_of((int64_t)(tile + 1) * P.ksteps - 1, total, G);
+    const int nsegs = c_last - c_first + 1;
+    if (nsegs == 1) return;
+    int l = 0;
+    while (l + 1 < P.n_layers && P.L[l + 1].tile_base <= tile) ++l;
+    const WgradLayer& L = P.L[l];
+    const int local = tile - L.tile_base;
+    const int n0 = (local / L.k_tiles) * BM, k0 = (local % L.k_tiles) * WN;
+    const int kw = min(WN, L.K - k0);
+    const int q4 = kw >> 2;                                   // float4 columns of the tile (K % 8 == 0)
+    const float* p0 = P.partials + (int64_t)tile * P.max_segs * BM * kPartialPitch;
+    const int64_t seg_stride = (int64_t)BM * kPartialPitch;
+    const int rows = min(kReduceRows, L.N - n0 - r0);
+    for (int idx = threadIdx.x; idx < rows * q4; idx += 256) {
+        const int r = r0 + idx / q4, c = (idx % q4) << 2;
+        const float* src = p0 + (int64_t)r * kPartialPitch + c;
+        float4 a = __ldcg(reinterpret_cast<const float4*>(src));
+#pragma unroll 4
+        for (int sgi = 1; sgi < nsegs; ++sgi) {
+            const float4 b = __ldcg(reinterpret_cast<const float4*>(src + sgi * seg_stride));
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        *reinterpret_cast<float4*>(L.dW + (int64_t)(n0 + r) * L.ld_dw + k0 + c) = a;
+    }
+    if (k0 == 0 && L.db != nullptr && (int)threadIdx.x < rows) {
+        const int r = r0 + threadIdx.x;
+        const float* src = p0 + (int64_t)r * kPartialPitch + WN;
+        float a = __ldcg(src);
+        for (int sgi = 1; sgi < nsegs; ++sgi) a += __ldcg(src + sgi * seg_stride);
+        L.db[n0 + r] = a;
     }
 }
 
@@ -703,11 +722,16 @@ int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld
     P.total_tiles = tiles;
     P.max_segs = wgrad_max_segs(tiles, M);
     P.partials = (float*)workspace;
-    P.counters = (unsigned int*)((char*)workspace + (size_t)tiles * P.max_segs * BM * kPartialPitch * 4);
     static DeviceOnce once;
     if (once.first())
         cudaFuncSetAttribute(wgrad_streamk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgradSmem::kBytes);
-    wgrad_streamk_kernel<<<wgrad_grid(tiles, M), kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
-    return check_launch("gemm_wgrad");
+    const int G = wgrad_grid(tiles, M);
+    wgrad_streamk_kernel<<<G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
+    if (int rc = check_launch("gemm_wgrad")) return rc;
+    if (G > tiles || (int64_t)tiles * P.ksteps % G != 0 || ((int64_t)tiles * P.ksteps / G) % P.ksteps != 0) {   // some tile is split
+        wgrad_reduce_kernel<<<tiles * (BM / kReduceRows), 256, 0, (cudaStream_t)stream>>>(P, G);
+        return check_launch("gemm_wgrad_reduce");
+    }
+    return DLRMX_OK;
 }
 }

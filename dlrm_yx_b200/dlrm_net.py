@@ -360,13 +360,13 @@ class DLRM_Net(nn.Module):
     def apply_mlp(self, x, layers):
         return layers(x)
 
-    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10):
+    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10, gemm="tc"):
         """Replaces the two nn.Sequential towers by FusedMLP (bf16 tensor-core GEMMs with fused epilogues, flat
         parameter buffers, one-kernel optimizer step).  After this, call `step_mlps()` instead of putting the tower
         parameters into an outer optimizer."""
         from . import mlp
-        self.bot_l = mlp.FusedMLP(self.bot_l, lr, optimizer, eps)
-        self.top_l = mlp.FusedMLP(self.top_l, lr, optimizer, eps)
+        self.bot_l = mlp.FusedMLP(self.bot_l, lr, optimizer, eps, gemm=gemm)
+        self.top_l = mlp.FusedMLP(self.top_l, lr, optimizer, eps, gemm=gemm)
         # bf16 hand-over around the interaction (no cast / pad / slice passes): the bottom tower ends in a fused bf16
         # layer, the top tower starts with one, and the tensor-core interaction kernels take the shape
         F, D = 1 + int(self.ln_emb.size), int(self.ln_bot[-1])

@@ -4,10 +4,13 @@ call shape (apply_mlp: `layers(x)`, 518-524).
 `FusedMLP(sequential, ...)` takes over the Linear layers that create_mlp built (same numpy-initialised weights):
   * all weights and biases of the tower live in ONE flat fp32 master buffer (+ one flat gradient buffer, one flat
     Adagrad accumulator, one flat bf16 shadow that the GEMMs read);
-  * forward per layer = one tensor-core GEMM, bf16 operands, fp32 accumulate, bias + ReLU in the GEMM epilogue
-    (a plain library GEMM: cuBLASLt through torch);
-  * backward per layer = one fused pass dz = dy*(y>0) + bias-gradient partial sums (dlrmx_relu_bwd_bias_grad), then
-    the two GEMMs dW = dz^t x (fp32 out, written straight into the flat gradient buffer) and dx = dz W;
+  * forward per layer = one tcgen05 GEMM (csrc/gemm_tc.cu: TMA-staged bf16 operands, fp32 accumulators in TMEM),
+    fp32 bias + ReLU in the epilogue;
+  * backward of a run of layers (`_Tower`) = per layer one tcgen05 dgrad GEMM dz_prev = (dz W) * (y_prev > 0) whose
+    epilogue applies the PREVIOUS layer's ReLU mask (no separate ReLU-backward pass), then ONE stream-K tcgen05 launch
+    for the weight AND bias gradients of every layer of the run (fp32, written straight into the flat gradient buffer);
+  * `gemm="cublas"` keeps the round-1 path (cuBLASLt GEMMs through torch + dlrmx_relu_bwd_bias_grad) as the measured
+    comparator of tools/gemm_check.py and bench.py --mlp fused-bf16-cublas; it is never a fallback;
   * `step()` = (all-reduce of the flat gradient buffer when data-parallel, the reference wraps the towers in DDP,
     dlrm_s_pytorch.py:1626-1633) + ONE kernel for the whole tower (dlrmx_dense_opt): SGD, or the dense Adagrad branch
     of RWSAdagrad (optim/rwsadagrad.py:115-118), which also refreshes the bf16 shadow and clears the gradients.
@@ -81,6 +84,53 @@ class _LinearAct(torch.autograd.Function):
         return dx, None, None, None
 
 
+class _Tower(torch.autograd.Function):
+    """Layers [i0, i1) of a FusedMLP (all Linear + ReLU, widths multiples of 8) as ONE autograd node on the tcgen05 GEMMs."""
+
+    @staticmethod
+    def forward(ctx, h, anchor, mlp, i0, i1):
+        first = mlp.layers[i0]
+        hb = h if h.dtype == torch.bfloat16 else h.to(torch.bfloat16)
+        if hb.shape[1] != first.K_pad:
+            padded = hb.new_zeros((hb.shape[0], first.K_pad))
+            padded[:, :first.K].copy_(hb)
+            hb = padded
+        acts = [hb.contiguous()]
+        for li in range(i0, i1):
+            L = mlp.layers[li]
+            acts.append(ops.gemm_bf16(acts[-1], L.w_shadow, epilogue=ops.EPI_BIAS_RELU, bias=L.b_master))
+        ctx.mlp, ctx.i0, ctx.i1, ctx.in_cols = mlp, i0, i1, h.shape[1]
+        # a consumer that fuses the last layer's ReLU backward + bias gradient into its own backward (the head) sets the flag
+        ctx.flag = {"pre_masked": False}
+        mlp._last_relu = (i1 - 1, ctx.flag)
+        ctx.save_for_backward(*acts)
+        return acts[-1]
+
+    @staticmethod
+    def backward(ctx, dy):
+        acts = ctx.saved_tensors
+        mlp, i0, i1 = ctx.mlp, ctx.i0, ctx.i1
+        layers = mlp.layers[i0:i1]
+        n = len(layers)
+        dyb = (dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)).contiguous()
+        dzs, dbs = [None] * n, [L.gb for L in layers]
+        if ctx.flag["pre_masked"]:
+            dzs[-1] = dyb              # the head's backward applied the last ReLU mask and wrote that bias gradient
+            dbs[-1] = None
+        else:
+            dzs[-1], _ = ops.relu_bwd_bias_grad(dyb, acts[-1], relu=True, db=layers[-1].gb)
+            dbs[-1] = None
+        for j in range(n - 1, 0, -1):  # dz of layer j-1 = (dz_j W_j) masked by layer j-1's output
+            dzs[j - 1] = ops.gemm_bf16(dzs[j], layers[j].w_shadow, b_is_kn=True, epilogue=ops.EPI_RELU_MASK, relu_mask=acts[j])
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.gemm_bf16(dzs[0], layers[0].w_shadow, b_is_kn=True)
+            if ctx.in_cols != layers[0].K_pad:       # the caller's input was unpadded
+                dx = dx[:, :layers[0].K]
+        ops.gemm_wgrad_bf16(dzs, list(acts[:-1]), [L.gW for L in layers], dbs, mlp._wgrad_workspace(i0, i1, dyb.shape[0]))
+        return dx, None, None, None, None
+
+
 class _Head(torch.autograd.Function):
     """Linear(K -> 1) + Sigmoid on a bf16 activation: one row-wise dot-product kernel each way (fp32 master weights)."""
 
@@ -118,8 +168,12 @@ class _Head(torch.autograd.Function):
 
 
 class FusedMLP(nn.Module):
-    def __init__(self, sequential, lr, optimizer="adagrad", eps=1e-10, initial_accumulator_value=0.0):
+    def __init__(self, sequential, lr, optimizer="adagrad", eps=1e-10, initial_accumulator_value=0.0, gemm="tc"):
         super().__init__()
+        if gemm not in ("tc", "cublas"):
+            raise ValueError("gemm must be 'tc' (tcgen05 kernels) or 'cublas' (the library comparator)")
+        self.gemm = gemm
+        self._ws = {}
         mods = list(sequential)
         if len(mods) % 2 or not all(isinstance(m, nn.Linear) for m in mods[0::2]):
             raise ValueError("FusedMLP expects the Linear/activation pairs that create_mlp builds")
@@ -173,6 +227,7 @@ class FusedMLP(nn.Module):
     def _apply(self, fn, *args, **kwargs):       # .to()/.cuda() re-allocate the flat buffers: re-create the views
         out = super()._apply(fn, *args, **kwargs)
         self._anchor = torch.zeros(1, device=self.master.device, requires_grad=True)
+        self._ws = {}
         self._bind()
         return out
 
@@ -185,9 +240,25 @@ class FusedMLP(nn.Module):
         L = self.layers[i]
         return self.master.data[L.b_off:L.b_off + L.N]
 
+    def _wgrad_workspace(self, i0, i1, M):
+        key = (i0, i1, M, torch.cuda.current_stream().cuda_stream)
+        ws = self._ws.get(key)
+        if ws is None:
+            ls = self.layers[i0:i1]
+            ws = self._ws[key] = ops.gemm_wgrad_workspace([L.N for L in ls], [L.K_pad for L in ls], M, self.master.device)
+        return ws
+
     def forward(self, x):
-        h = x
-        for i, L in enumerate(self.layers):
+        h, i, n = x, 0, len(self.layers)
+        while i < n:
+            L = self.layers[i]
+            if L.fused and self.gemm == "tc":
+                j = i
+                while j < n and self.layers[j].fused:
+                    j += 1
+                h = _Tower.apply(h, self._anchor, self, i, j)
+                i = j
+                continue
             if L.fused:
                 h = _LinearAct.apply(h, self._anchor, self, i)
             elif L.head and h.dtype == torch.bfloat16:
@@ -195,6 +266,7 @@ class FusedMLP(nn.Module):
             else:
                 z = F.linear(h.float(), L.w_leaf, L.b_leaf)
                 h = torch.sigmoid(z) if L.act == "sigmoid" else torch.relu(z)
+            i += 1
         return h if (h.dtype == torch.float32 or self.out_bf16) else h.float()
 
     @torch.no_grad()

@@ -38,7 +38,8 @@ def emulate(fused, x, go):
     for i, L in enumerate(fused.layers):
         if L.fused:
             hb = h.to(bf).float()
-            y = torch.relu(hb @ fused.weight(i).to(bf).float().t() + fused.bias(i).to(bf).float()).to(bf).float()
+            bias = fused.bias(i) if fused.gemm == "tc" else fused.bias(i).to(bf).float()     # tcgen05 epilogue: fp32 bias
+            y = torch.relu(hb @ fused.weight(i).to(bf).float().t() + bias).to(bf).float()
             saved.append((hb, y))
             h = y
         else:
@@ -61,16 +62,19 @@ def emulate(fused, x, go):
     return out.detach(), dy, grads
 
 
+@pytest.mark.parametrize("gemm", ["tc", "cublas"])
 @pytest.mark.parametrize("ln,sig", [([13, 64, 32, 16], -1), ([479, 128, 64, 1], 2), ([16, 8], -1),
-                                    ([13, 512, 256, 128], -1)])
-def test_fused_mlp_matches_fp32_tower(ln, sig):
+                                    ([13, 512, 256, 128], -1), ([479, 1024, 1024, 512, 256, 1], 4)])
+def test_fused_mlp_matches_fp32_tower(ln, sig, gemm):
     """Two bars: (1) against the same-rounding fp32 emulation: 5e-3 relative Frobenius error everywhere (what is left
     is accumulation order and 1-ulp bf16 ties); (2) against the true fp32 tower create_mlp builds: forward 1e-2; the
     gradients 0.15 -- a pre-activation that bf16 rounding moves across zero flips its ReLU gate and changes single
-    gradient entries by a full |dy*w|, so the fp32 gradient bar is a sanity bound, not a precision claim."""
+    gradient entries by a full |dy*w|, so the fp32 gradient bar is a sanity bound, not a precision claim.  The
+    five-layer 1024-wide Terabyte top tower gets 2e-2 on bar (1) for its gradients: accumulation-order differences
+    flip a few gates per layer there too (every GEMM alone is held to 2e-3 by tools/gemm_check.py)."""
     from dlrm_yx_b200 import mlp
     ref = make_tower(ln, sig)
-    fused = mlp.FusedMLP(make_tower(ln, sig), lr=0.1, optimizer="sgd")
+    fused = mlp.FusedMLP(make_tower(ln, sig), lr=0.1, optimizer="sgd", gemm=gemm)
     B = 257
     torch.manual_seed(0)
     x = torch.rand(B, ln[0], device="cuda")
@@ -81,15 +85,16 @@ def test_fused_mlp_matches_fp32_tower(ln, sig):
     ye, dxe, ge = emulate(fused, x, go)
     yr.backward(go)
     yf.backward(go)
+    gtol = 2e-2 if len(ln) > 4 else 5e-3
     scale_close(yf, ye, 5e-3)
-    scale_close(xf.grad, dxe, 5e-3)
+    scale_close(xf.grad, dxe, gtol)
     scale_close(yf, yr, 1e-2)
     scale_close(xf.grad, xr.grad, 0.15)
     lins = [m for m in ref if isinstance(m, torch.nn.Linear)]
     for i, lin in enumerate(lins):
         L = fused.layers[i]
-        scale_close(L.gW[:, :L.K], ge[i][0], 5e-3)
-        scale_close(L.gb, ge[i][1], 5e-3)
+        scale_close(L.gW[:, :L.K], ge[i][0], gtol)
+        scale_close(L.gb, ge[i][1], gtol)
         scale_close(L.gW[:, :L.K], lin.weight.grad, 0.15)
         scale_close(L.gb, lin.bias.grad, 0.15)
         if L.K_pad != L.K:

@@ -23,18 +23,30 @@ SHAPES = {"terabyte_bot": [(16, 512), (512, 256), (256, 128)],
           "kaggle": [(16, 512), (256, 64), (64, 16), (368, 512)]}
 
 
-def timed(fn, iters):
-    for _ in range(3):
+def timed(fn, iters, reps=10):
+    """Median ms per call: `reps` back-to-back calls captured in one CUDA graph (the whole training step runs as a graph,
+    so host launch cost must not be part of a kernel's time), replayed `iters` times between CUDA events."""
+    for _ in range(2):
         fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            for _ in range(reps):
+                fn()
+    torch.cuda.synchronize()
+    g.replay()
     torch.cuda.synchronize()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
     for s, e in ev:
         s.record()
-        fn()
+        g.replay()
         e.record()
     torch.cuda.synchronize()
     t = sorted(a.elapsed_time(b) for a, b in ev)
-    return t[len(t) // 2]
+    return t[len(t) // 2] / reps
 
 
 def rel_err(got, ref):
@@ -73,8 +85,9 @@ def main():
                 ref = torch.relu(x.float() @ w.float().t() + b)
                 got = ops.gemm_bf16(x, w, epilogue=ops.EPI_BIAS_RELU, bias=b)
                 err = rel_err(got, ref)
-                ms = timed(lambda: ops.gemm_bf16(x, w, epilogue=ops.EPI_BIAS_RELU, bias=b), args.iters)
-                ms_lib = timed(lambda: torch._addmm_activation(b.to(bf), x, w.t()), args.iters)
+                y_out, bb = torch.empty_like(got), b.to(bf)
+                ms = timed(lambda: ops.gemm_bf16(x, w, epilogue=ops.EPI_BIAS_RELU, bias=b, out=y_out), args.iters)
+                ms_lib = timed(lambda: torch._addmm_activation(bb, x, w.t(), out=y_out), args.iters)
                 ok = err < 6e-3
                 bad += not ok
                 print(json.dumps(dict(kind="fwd", group=gname, M=M, K=K, N=N, rel_err=err, ok=ok, ms=round(ms, 4),
@@ -86,13 +99,15 @@ def main():
                 err = rel_err(got, ref)
                 got2 = ops.gemm_bf16(dz, w, b_is_kn=True)
                 err2 = rel_err(got2, dz.float() @ w.float())
-                ms = timed(lambda: ops.gemm_bf16(dz, w, b_is_kn=True, epilogue=ops.EPI_RELU_MASK, relu_mask=yprev), args.iters)
-                ms_lib = timed(lambda: torch.mm(dz, w), args.iters)
+                dx_out = torch.empty_like(got)
+                ms = timed(lambda: ops.gemm_bf16(dz, w, b_is_kn=True, epilogue=ops.EPI_RELU_MASK, relu_mask=yprev, out=dx_out), args.iters)
+                ms_nomask = timed(lambda: ops.gemm_bf16(dz, w, b_is_kn=True, out=dx_out), args.iters)
+                ms_lib = timed(lambda: torch.mm(dz, w, out=dx_out), args.iters)
                 ok = err < 6e-3 and err2 < 6e-3
                 bad += not ok
                 print(json.dumps(dict(kind="dgrad", group=gname, M=M, K=N, N=K, rel_err=err, rel_err_nomask=err2, ok=ok,
-                                      ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1), cublas_ms=round(ms_lib, 4),
-                                      cublas_tflops=round(flops / ms_lib / 1e9, 1))), flush=True)
+                                      ms=round(ms, 4), ms_nomask=round(ms_nomask, 4), tflops=round(flops / ms / 1e9, 1),
+                                      cublas_ms=round(ms_lib, 4), cublas_tflops=round(flops / ms_lib / 1e9, 1))), flush=True)
         if "wgrad" in only:
             dws = [torch.full((w.shape[0], w.shape[1]), float("nan"), device=dev) for w in ws]
             dbs = [torch.full((w.shape[0],), float("nan"), device=dev) for w in ws]
@@ -108,12 +123,20 @@ def main():
             det = all(torch.equal(a, b) for a, b in zip(again, dws))
             ms = timed(lambda: ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, wsb), args.iters)
             ms_lib = timed(lambda: [torch.mm(dz.t(), x, out_dtype=torch.float32) for dz, x in zip(dzs, xs)], args.iters)
+            per_layer = []
+            for dz, x, dw, db in zip(dzs, xs, dws, dbs):
+                ws1 = ops.gemm_wgrad_workspace([dz.shape[1]], [x.shape[1]], M, dev)
+                t1 = timed(lambda: ops.gemm_wgrad_bf16([dz], [x], [dw], [db], ws1), args.iters)
+                t0 = timed(lambda: ops.gemm_wgrad_bf16([dz], [x], [dw], None, ws1), args.iters)
+                tl = timed(lambda: torch.mm(dz.t(), x, out_dtype=torch.float32), args.iters)
+                per_layer.append(dict(N=dz.shape[1], K=x.shape[1], ms=round(t1, 4), ms_nobias=round(t0, 4), cublas_ms=round(tl, 4)))
             flops = sum(2.0 * M * w.shape[0] * w.shape[1] for w in ws)
             ok = max(errs) < 3e-3 and max(errb) < 3e-3 and det
             bad += not ok
             print(json.dumps(dict(kind="wgrad", group=gname, M=M, layers=shapes, rel_err=errs, rel_err_bias=errb,
                                   deterministic=det, ok=ok, ms=round(ms, 4), tflops=round(flops / ms / 1e9, 1),
-                                  cublas_ms=round(ms_lib, 4), cublas_tflops=round(flops / ms_lib / 1e9, 1))), flush=True)
+                                  cublas_ms=round(ms_lib, 4), cublas_tflops=round(flops / ms_lib / 1e9, 1),
+                                  per_layer=per_layer)), flush=True)
     print("gemm_check:", "FAILED (%d)" % bad if bad else "all shapes OK", flush=True)
     sys.exit(1 if bad else 0)
 
