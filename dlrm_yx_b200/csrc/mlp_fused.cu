@@ -439,6 +439,76 @@ int dlrmx_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db_
     return check_launch("relu_bwd_bias_grad");
 }
 
+// ---- relu_bwd_bias_grad without any allocation ---------------------------------------------------------------------
+// Same kernel, same grid as the Python wrapper of dlrmx_relu_bwd_bias_grad picks (so the sums are bit-identical), but its
+// scratch (chunk partials + last-CTA counters) is this file-scope device array: nothing is allocated, by the caller or
+// here.  Every GPU that loads the library holds the array (304 KB) until the process exits; every call on a device shares
+// it, so calls that overlap on one GPU race on it.
+namespace dlrmx {
+constexpr int kNoAllocMaxN = 2048;                                     // widest layer accepted
+constexpr int kNoAllocCtas = 2 * kSMs;                                 // chunks x column blocks ~ 2 CTAs per SM
+constexpr int kNoAllocPartialFloats = kNoAllocCtas * kRbColVecs * 8 + kNoAllocMaxN;   // bound of chunks * N, see below
+constexpr int kNoAllocCounterBytes = 256;
+static __device__ __align__(256) unsigned char g_rb_noalloc_scratch[kNoAllocPartialFloats * 4 + kNoAllocCounterBytes];
+
+// Device address of the scratch array on the CURRENT device (the symbol's name is only a host-side stand-in): looked up
+// once per device with cudaGetSymbolAddress, with that device current.
+static unsigned char* rb_noalloc_scratch() {
+    static std::atomic<unsigned char*> ptrs[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("relu_bwd_bias_grad_noalloc: cudaGetDevice failed or device index >= 64");
+        return nullptr;
+    }
+    unsigned char* p = ptrs[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        void* q = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&q, g_rb_noalloc_scratch);
+        if (e != cudaSuccess || q == nullptr) {
+            set_error("relu_bwd_bias_grad_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return nullptr;
+        }
+        p = static_cast<unsigned char*>(q);
+        ptrs[dev].store(p, std::memory_order_release);
+    }
+    return p;
+}
+}  // namespace dlrmx
+
+int dlrmx_relu_bwd_bias_grad_noalloc(const void* dy, const void* y, void* dz, float* db, int B, int N, int relu,
+                                     dlrmx_stream_t stream) {
+    using namespace dlrmx;
+    DLRMX_REQUIRE(B >= 0 && N > 0 && N % 8 == 0, "relu_bwd_bias_grad_noalloc: need N %% 8 == 0 (B=%d N=%d)", B, N);
+    DLRMX_REQUIRE(N <= kNoAllocMaxN, "relu_bwd_bias_grad_noalloc: N = %d exceeds the static scratch (N <= %d); use "
+                  "dlrmx_relu_bwd_bias_grad with a caller-provided workspace", N, kNoAllocMaxN);
+    DLRMX_REQUIRE(dy != nullptr && db != nullptr && (relu == 0 || (y != nullptr && dz != nullptr)),
+                  "relu_bwd_bias_grad_noalloc: dy, db (and y, dz when relu != 0) must be given");
+    DLRMX_REQUIRE((((uintptr_t)dy | (uintptr_t)y | (uintptr_t)dz) & 15) == 0, "relu_bwd_bias_grad_noalloc: 16-B alignment");
+    const int col_blocks = (int)ceil_div(N, kRbColVecs * 8);
+    // as ops.relu_bwd_bias_grad(chunks=None): ~2 CTAs per SM, at least 32 rows per chunk.
+    // chunks <= kNoAllocCtas / col_blocks + 1 and N <= 256 * col_blocks, so chunks * N <= kNoAllocPartialFloats.
+    int chunks = (int)ceil_div(kNoAllocCtas, col_blocks);
+    const int by_rows = (int)ceil_div(B > 0 ? B : 1, 32);
+    if (chunks > by_rows) chunks = by_rows;
+    if (chunks < 1) chunks = 1;
+    DLRMX_REQUIRE((int64_t)chunks * N <= kNoAllocPartialFloats, "relu_bwd_bias_grad_noalloc: internal scratch bound");
+    unsigned char* scratch = rb_noalloc_scratch();
+    if (scratch == nullptr) return DLRMX_E_CUDA;
+    float* partial = reinterpret_cast<float*>(scratch);
+    unsigned int* counters = reinterpret_cast<unsigned int*>(scratch + (size_t)kNoAllocPartialFloats * 4);
+    // the array keeps the previous call's contents: the counters must start at zero (the partials are fully overwritten)
+    if (cudaMemsetAsync(counters, 0, kNoAllocCounterBytes, (cudaStream_t)stream) != cudaSuccess) {
+        set_error("relu_bwd_bias_grad_noalloc: cudaMemsetAsync: %s", cudaGetErrorString(cudaGetLastError()));
+        return DLRMX_E_CUDA;
+    }
+    const int rows_per_chunk = (int)ceil_div(B > 0 ? B : 1, chunks);
+    dim3 grid((unsigned)col_blocks, (unsigned)chunks);
+    relu_bwd_bias_grad_kernel<<<grid, kRbThreads, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dz, partial, db, counters, B, N, rows_per_chunk,
+        relu);
+    return check_launch("relu_bwd_bias_grad_noalloc");
+}
+
 int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
                     float eps, float grad_scale, dlrmx_stream_t stream) {
     using namespace dlrmx;

@@ -220,6 +220,16 @@ int dlrmx_relu_bwd_bias_grad(const void* dy_bf16, const void* y_bf16, void* dz_b
 int dlrmx_dense_opt(int mode, float* params, float* acc, float* grads, void* shadow_bf16, int64_t n, float lr,
                     float eps, float grad_scale, dlrmx_stream_t stream);
 
+/* relu_bwd_bias_grad_noalloc: NO COUNTERPART IN THE REFERENCE -- added for callers
+ * that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The same
+ * kernel and grid as dlrmx_relu_bwd_bias_grad with the default chunking (results bit-identical), but the scratch (chunk
+ * partials + counters) is a static 304 KB __device__ array inside the library: the call allocates nothing and the caller
+ * passes only inputs and outputs.  dz [B, N] bf16 = dy * (y > 0) (relu != 0; with relu == 0 dz and y are ignored) and
+ * db [N] fp32 = column sums of dz (of dy when relu == 0).  Limit: N <= 2048 (N % 8 == 0); larger N returns DLRMX_E_ARG.
+ * Every call on a device shares the one array: calls that overlap on the same GPU (different streams) race on it. */
+int dlrmx_relu_bwd_bias_grad_noalloc(const void* dy_bf16, const void* y_bf16, void* dz_bf16, float* db, int B, int N,
+                                     int relu, dlrmx_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Tower GEMMs on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands staged by TMA), bf16 in /
  * fp32 accumulate.  Replaces the cuBLAS GEMMs of nn.Linear in create_mlp / apply_mlp (dlrm_s_pytorch.py:227-265, 518-524)
