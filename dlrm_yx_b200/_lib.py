@@ -59,7 +59,7 @@ SIGNATURES = {
                                          c_int, c_int, c_void_p]),
     "dlrmx_relu_bwd_bias_grad_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "dlrmx_gemm_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_int, c_int, c_int,
-                                c_void_p, c_void_p, c_int64, c_void_p]),
+                                c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "dlrmx_gemm_wgrad_workspace_bytes": (c_size_t, [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_int]),
     "dlrmx_gemm_wgrad_bf16": (c_int, [c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), ctypes.POINTER(c_void_p),
                                       ctypes.POINTER(c_int64), ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64),

@@ -7,9 +7,9 @@
 //                                           (no transposed weight copy), epilogue applies the PREVIOUS layer's ReLU mask, so
 //                                           its result is that layer's dZ -- no separate ReLU-backward pass
 //   wgrad     dW = dZ^t X,  db = dZ^t 1     wgrad_streamk_kernel: ALL layers of a tower in ONE launch.  Both operands are
-//                                           MN-major (the contraction runs over the batch), tiles [128 n] x [<=256 k]; the
+//                                           MN-major (the contraction runs over the batch), tiles [256 n] x [<=256 k]; the
 //                                           (tile, k-step) space of all layers is cut into equal contiguous ranges, one per
-//                                           SM (stream-K); tiles cut into several segments leave fp32 partials that
+//                                           CTA pair (stream-K); tiles cut into several segments leave fp32 partials that
 //                                           wgrad_reduce_kernel sums in segment order (deterministic, ONE reduce launch
 //                                           for the whole tower, element-parallel over all SMs); the bias gradient
 //                                           rides along as one extra N = 16 MMA against a tile of ones.
@@ -99,6 +99,60 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- CTA pairs (cta_group::2): two CTAs of one cluster, on the two SMs of a TPC, run ONE MMA of M = 256 -------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory variable in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t cta_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(cta_addr), "r"(rank));
+    return r;
+}
+// (default .release.cta: an explicit .release.cluster costs a MEMBAR.ALL.GPU per arrive -- measured: it paced the whole pipeline)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load issued by either CTA of a pair into its OWN shared memory; the bytes are counted on the barrier at cluster address
+// `bar_cluster` (the leader CTA's)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(saddr(dst)), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(saddr(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// one MMA of M = 256 over the pair: rows 0..127 of D accumulate in the leader's TMEM, rows 128..255 in the peer's; A rows and
+// the two halves of B's N extent are read from the two CTAs' shared memory at the SAME offsets
+__device__ __forceinline__ void umma_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far have completed
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(saddr(bar)), "h"((uint16_t)3) : "memory");
+}
+// TMA store of a shared-memory box (128-byte swizzled) into the tensor; rows / columns beyond the tensor are clipped
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(saddr(src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---- shared-memory matrix descriptors (SWIZZLE_128B, version 1 = Blackwell) -------------------------------------------
 // K-major operand tile [rows][64 bf16]: a row is one 128-byte swizzle line, 8 rows form a 1024-byte atom; SBO = distance
 // between 8-row groups; one MMA (K = 16) reads 32 bytes of every row: the next k-step starts 32 bytes further.
@@ -118,9 +172,9 @@ __device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int k) { ret
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int k) { return make_desc(tile_addr + k * (UK * 128), kAtomBytes, 1024); }
 
 // instruction descriptor: fp32 accumulate, bf16 x bf16, M = 128
-__host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn, bool b_mn) {
+__host__ __device__ constexpr uint32_t make_idesc(int n, bool a_mn, bool b_mn, int m = BM) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) |
-           ((uint32_t)(BM >> 4) << 24);
+           ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -331,15 +385,245 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// wgrad, all layers of a tower in one launch (stream-K)
+// forward / dgrad GEMM on CTA pairs.  The single-CTA kernel above moves 48 KB from L2 per 128 x 256 x 64 block of MMA work
+// and is bound by the L2 -> SM fabric (~12 TB/s over the chip); here the two CTAs of a cluster (the two SMs of a TPC) run
+// ONE tcgen05.mma.cta_group::2 of M = 256: each CTA stages its own 128 rows of A and only HALF of the B tile (32 KB per
+// the same MMA work), the tensor core reads both halves.  The epilogue goes registers -> 128-byte-swizzled shared memory
+// -> TMA store (full-line writes instead of 32 scattered 16-byte stores per instruction), and the ReLU gates travel as one
+// bit per element: the forward writes them next to Y (relu_bits), the dgrad epilogue reads 4 bytes per 32 columns.
+//   pair tile [256 m] x [BN n];  CTA r: A rows m0 + 128 r .. +127, B rows (N) n0 + r BN/2 .. (K-major) or the same columns
+//   of the [K, N] matrix (MN-major, 64-column blocks), D rows 128 r .. in its own TMEM (2 x BN columns, double-buffered).
+//   Barriers: full[s] lives in the leader (its arrive.expect_tx counts both CTAs' bytes; the peer's TMA signals it remotely),
+//   empty[s] / acc_full[a] in both CTAs (multicast tcgen05.commit from the leader), acc_empty[a] in the leader (8 epilogue
+//   warps arrive, the peer's remotely).
+// ------------------------------------------------------------------------------------------------------------------
+enum { EPI_RELU_BITS = 4 };
+
+struct PairParams {
+    int M, N, K;
+    const float* bias;              // [N] fp32 (EPI_BIAS_RELU / EPI_BIAS)
+    uint32_t* bits_out;             // EPI_BIAS_RELU, optional: bit (n & 31) of word [m, n >> 5] = (Y[m, n] > 0)
+    const uint32_t* bits_in;        // EPI_RELU_BITS: C = acc where the bit is set, else 0
+    int64_t ld_bits;                // words per row of either bit matrix
+    int epilogue;
+};
+
+template <int BN>
+struct PairSmem {
+    static constexpr uint32_t kABytes = BM * BK * 2, kBBytes = (BN / 2) * BK * 2;
+    static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+    static constexpr uint32_t kOutBytes = 4 * 2 * 4096;                       // 4 epilogue warps x 2 buffers x [32 rows][128 B]
+    static constexpr int kStages = (227 * 1024 - 2048 - (int)kOutBytes) / (int)kStageBytes > 8
+                                       ? 8 : (227 * 1024 - 2048 - (int)kOutBytes) / (int)kStageBytes;
+    static constexpr uint32_t kOutOff = kStages * kStageBytes;
+    static constexpr uint32_t kBarOff = kOutOff + kOutBytes;
+    static constexpr uint32_t kBytes = kBarOff + 512 + 1024;                  // barriers + the alignment slack
+};
+
+template <int BN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ CUtensorMap map_c, const PairParams P) {
+    using S = PairSmem<BN>;
+    constexpr int STAGES = S::kStages;
+    static_assert(!B_MN || BN >= 128, "an MN-major B half must span whole 64-column swizzle blocks");
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+    uint64_t* empty = full + STAGES;
+    uint64_t* acc_full = empty + STAGES;
+    uint64_t* acc_empty = acc_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int m_tiles = (P.M + 2 * BM - 1) / (2 * BM), n_tiles = (P.N + BN - 1) / BN;
+    const int tiles = m_tiles * n_tiles;
+    const int kblocks = (P.K + BK - 1) / BK;
+    const int pair = blockIdx.x >> 1, pairs = gridDim.x >> 1;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&map_a);
+        prefetch_tmap(&map_b);
+        prefetch_tmap(&map_c);
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 8); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, 2 * BN);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();            // the peer's barriers are initialised before anything arrives on them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs: own A rows, own half of B) =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = pair; tile < tiles; tile += pairs) {
+                const int m0 = (tile / n_tiles) * (2 * BM) + (int)rank * BM;
+                const int n0 = (tile % n_tiles) * BN + (int)rank * (BN / 2);
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1u);
+                    uint8_t* sa = smem + stage * S::kStageBytes;
+                    uint8_t* sb = sa + S::kABytes;
+                    const uint32_t bar = mapa(saddr(&full[stage]), 0);
+                    // the leader alone arrives, expecting both CTAs' bytes: the peer cannot reach this phase of the barrier early,
+                    // its empty[stage] is released by the same commit that follows the leader's wait on the previous phase
+                    if (leader) mbar_arrive_expect_tx(&full[stage], 2 * S::kStageBytes);
+                    tma_load_2d_pair(sa, &map_a, bar, kb * BK, m0);
+                    if (!B_MN) {
+                        tma_load_2d_pair(sb, &map_b, bar, kb * BK, n0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 128; ++j)
+                            tma_load_2d_pair(sb + j * kAtomBytes, &map_b, bar, n0 + 64 * j, kb * BK);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (leader) {
+            constexpr uint32_t idesc = make_idesc(BN, false, B_MN, 2 * BM);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = pair; tile < tiles; tile += pairs, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
+                mbar_wait(&acc_empty[as], aphase ^ 1u);          // both CTAs' epilogues have drained this accumulator
+                tc_fence_after();
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sa = saddr(smem + stage * S::kStageBytes);
+                        const uint32_t sb = sa + S::kABytes;
+#pragma unroll
+                        for (int k = 0; k < BK / UK; ++k) {
+                            const uint64_t ad = desc_kmajor(sa, k);
+                            const uint64_t bd = B_MN ? desc_mnmajor(sb, k) : desc_kmajor(sb, k);
+                            umma_pair(tmem_base + as * BN, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit_pair(&empty[stage]);         // frees the stage in both CTAs
+                        if (kb == kblocks - 1) umma_commit_pair(&acc_full[as]);
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: 4 warps per CTA, warp w reads TMEM lanes 32*(w % 4) .. +31 = rows of this CTA's half of the tile =====
+        const int q = warp & 3;
+        uint8_t* obuf = smem + S::kOutOff + q * 8192;              // two [32 rows][128 B] swizzled boxes
+        const uint32_t acc_empty_leader0 = mapa(saddr(&acc_empty[0]), 0), acc_empty_leader1 = mapa(saddr(&acc_empty[1]), 0);
+        int it = 0;
+        int ob = 0;
+        for (int tile = pair; tile < tiles; tile += pairs, ++it) {
+            const int m0 = (tile / n_tiles) * (2 * BM) + (int)rank * BM, n0 = (tile % n_tiles) * BN;
+            const int as = it & 1;
+            const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
+            const int row = m0 + q * 32 + lane;
+            const bool row_ok = row < P.M;
+            uint32_t gate[BN / 32];
+            if (P.epilogue == EPI_RELU_BITS) {                      // the whole tile row's gates, before the accumulator is ready
+#pragma unroll
+                for (int c = 0; c < BN / 32; ++c)
+                    gate[c] = (row_ok && n0 + c * 32 < P.N) ? __ldg(P.bits_in + (int64_t)row * P.ld_bits + ((n0 >> 5) + c)) : 0u;
+            }
+            mbar_wait(&acc_full[as], aphase);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < BN / 32; ++c) {
+                const int col0 = n0 + c * 32;
+                if (col0 < P.N) {                                   // warp-uniform
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                    if ((c & 1) == 0) {                             // a new 64-column box: its buffer's previous store has been read
+                        if (lane == 0) bulk_wait_read<1>();
+                        __syncwarp();
+                    }
+                    tmem_ld_wait();
+                    float f[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+                    if (P.epilogue == EPI_BIAS_RELU || P.epilogue == EPI_BIAS) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            if (col0 + j < P.N) {
+                                const float4 b = __ldg(reinterpret_cast<const float4*>(P.bias + col0 + j));
+                                f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
+                            }
+                        }
+                        if (P.epilogue == EPI_BIAS_RELU) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                        }
+                    } else if (P.epilogue == EPI_RELU_BITS) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] = ((gate[c] >> j) & 1u) ? f[j] : 0.f;
+                    }
+                    uint32_t pk[16], bits = 0u;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        pk[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+                        bits |= ((pk[j] & 0x7fffu) != 0u ? 1u : 0u) << (2 * j);
+                        bits |= ((pk[j] & 0x7fff0000u) != 0u ? 1u : 0u) << (2 * j + 1);
+                    }
+                    if (P.epilogue == EPI_BIAS_RELU && P.bits_out != nullptr && row_ok)
+                        P.bits_out[(int64_t)row * P.ld_bits + (col0 >> 5)] = bits;      // after ReLU: non-zero == positive
+                    // 16-byte chunk j of this thread's 64-byte half row goes to chunk ((c & 1) * 4 + j) ^ (row & 7) of its line
+                    uint8_t* line = obuf + ob * 4096 + lane * 128;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int ch = (((c & 1) << 2) + j) ^ (lane & 7);
+                        *reinterpret_cast<uint4*>(line + (ch << 4)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                    }
+                    if ((c & 1) == 1 || col0 + 32 >= P.N) {         // the box is complete (or the tensor ends in its first half)
+                        fence_proxy_async();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&map_c, obuf + ob * 4096, n0 + (c >> 1) * 64, m0 + q * 32);
+                            bulk_commit();
+                        }
+                        ob ^= 1;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(as ? acc_empty_leader1 : acc_empty_leader0);
+        }
+        if (lane == 0) bulk_wait_all();
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();            // the leader's MMAs read the peer's shared memory; nobody leaves before everybody is done
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, 2 * BN);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// wgrad, all layers of a tower in one launch (stream-K over CTA pairs)
+//   pair tile [256 n] x [<= 256 k] of dW; one tcgen05.mma.cta_group::2 of M = 256 per 16 batch rows.  CTA r of the pair
+//   stages dZ columns n0 + 128 r .. +127 (A, MN-major) and X columns k0 + r bn/2 .. (B, MN-major), 64 batch rows per stage.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kMaxLayers = 8;
+constexpr int WM = 2 * BM;                 // n-rows of a dW tile (UMMA M of the pair)
 constexpr int WN = 256;                    // k-columns of a dW tile (UMMA N), at most
-constexpr int kWStages = 4;
+constexpr int kWStages = 6;
 
 struct WgradLayer {
     int N, K;                 // dW is [N, K] (row pitch ld_dw floats)
-    int n_tiles, k_tiles;     // tiles of 128 n x up to 256 k
+    int n_tiles, k_tiles;     // tiles of 256 n x up to 256 k
     int tile_base;            // first tile id of this layer
     float* dW;
     int64_t ld_dw;
@@ -348,7 +632,7 @@ struct WgradLayer {
 struct WgradParams {
     int n_layers, M, ksteps, total_tiles, max_segs;
     WgradLayer L[kMaxLayers];
-    float* partials;          // [total_tiles][max_segs][128][WN + 32] fp32
+    float* partials;          // [total_tiles][max_segs][256][WN + 32] fp32
 };
 struct WgradMaps {
     CUtensorMap dz[kMaxLayers];   // [M, N] bf16, box {64 n, 64 m}
@@ -358,7 +642,7 @@ constexpr int kPartialPitch = WN + 32;     // columns 0..255: the dW tile; colum
 
 struct Segment { int layer, n0, k0, bn, tile, ks0, ks1, seg, nsegs; };
 
-// CTA c of G owns the global k-steps [c*total/G, (c+1)*total/G) of the flattened (tile, k-step) space
+// pair c of G owns the global k-steps [c*total/G, (c+1)*total/G) of the flattened (tile, k-step) space
 __device__ __forceinline__ int64_t range_begin(int64_t c, int64_t total, int G) { return c * total / G; }
 __device__ __forceinline__ int owner_of(int64_t g, int64_t total, int G) {
     int c = (int)(g * G / total);
@@ -366,7 +650,7 @@ __device__ __forceinline__ int owner_of(int64_t g, int64_t total, int G) {
     while (c > 0 && range_begin(c, total, G) > g) --c;
     return c;
 }
-__device__ __forceinline__ Segment segment_at(const WgradParams& P, int64_t g, int64_t g_end, int64_t total, int G, int cta) {
+__device__ __forceinline__ Segment segment_at(const WgradParams& P, int64_t g, int64_t g_end, int64_t total, int G, int pair) {
     Segment s;
     s.tile = (int)(g / P.ksteps);
     s.ks0 = (int)(g - (int64_t)s.tile * P.ksteps);
@@ -375,26 +659,25 @@ __device__ __forceinline__ Segment segment_at(const WgradParams& P, int64_t g, i
     while (l + 1 < P.n_layers && P.L[l + 1].tile_base <= s.tile) ++l;
     s.layer = l;
     const int local = s.tile - P.L[l].tile_base;
-    s.n0 = (local / P.L[l].k_tiles) * BM;
+    s.n0 = (local / P.L[l].k_tiles) * WM;
     s.k0 = (local % P.L[l].k_tiles) * WN;
-    const int kw = min(WN, P.L[l].K - s.k0);
-    s.bn = (kw + 63) & ~63;                               // UMMA N / TMA blocks in 64-column units
+    s.bn = (P.L[l].K - s.k0) > 128 ? 256 : 128;           // UMMA N; each CTA stages bn / 2 columns (whole 64-column blocks)
     const int c_first = owner_of((int64_t)s.tile * P.ksteps, total, G);
     const int c_last = owner_of((int64_t)(s.tile + 1) * P.ksteps - 1, total, G);
-    s.seg = cta - c_first;
+    s.seg = pair - c_first;
     s.nsegs = c_last - c_first + 1;
     return s;
 }
 
 struct WgradSmem {
-    static constexpr uint32_t kABytes = BM * BK * 2, kBBytes = WN * BK * 2;
-    static constexpr uint32_t kStageBytes = kABytes + kBBytes;            // 48 KB
+    static constexpr uint32_t kABytes = BM * BK * 2, kBBytes = (WN / 2) * BK * 2;
+    static constexpr uint32_t kStageBytes = kABytes + kBBytes;            // 32 KB
     static constexpr uint32_t kOnesOff = kWStages * kStageBytes;          // 16 rows x 128 B of bf16 ones (K-major B operand)
     static constexpr uint32_t kBarOff = kOnesOff + 2048;
     static constexpr uint32_t kBytes = kBarOff + 256 + 1024;
 };
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P) {
     using S = WgradSmem;
     extern __shared__ uint8_t smem_raw[];
@@ -406,102 +689,111 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int G = gridDim.x, cta = blockIdx.x;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int G = gridDim.x >> 1, pair = blockIdx.x >> 1;
     const int64_t total = (int64_t)P.total_tiles * P.ksteps;
-    const int64_t g_begin = range_begin(cta, total, G), g_end = range_begin(cta + 1, total, G);
+    const int64_t g_begin = range_begin(pair, total, G), g_end = range_begin(pair + 1, total, G);
 
     if (threadIdx.x == 0) {
         for (int l = 0; l < P.n_layers; ++l) { prefetch_tmap(&maps.dz[l]); prefetch_tmap(&maps.x[l]); }
         for (int i = 0; i < kWStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
         mbar_init(acc_full, 1);
-        mbar_init(acc_empty, 4);
+        mbar_init(acc_empty, 8);
         fence_barrier_init();
     }
     // the tile of ones behind the bias gradient: every element 1.0 (bf16 0x3f80), so its layout does not matter
     for (int i = threadIdx.x; i < 2048 / 4; i += kThreads) reinterpret_cast<uint32_t*>(smem + S::kOnesOff)[i] = 0x3f803f80u;
     fence_proxy_async();           // generic-proxy writes -> visible to the tensor core's async proxy
-    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    if (warp == 1) tmem_alloc_pair(tmem_slot, 512);
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (both CTAs) =====
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
             for (int64_t g = g_begin; g < g_end;) {
-                const Segment s = segment_at(P, g, g_end, total, G, cta);
-                const uint32_t bytes = S::kABytes + (uint32_t)s.bn * (BK * 2);
+                const Segment s = segment_at(P, g, g_end, total, G, pair);
+                const uint32_t bytes = S::kABytes + (uint32_t)(s.bn / 2) * (BK * 2);
+                const int na = s.n0 + (int)rank * BM, kb0 = s.k0 + (int)rank * (s.bn / 2);
                 for (int ks = s.ks0; ks < s.ks1; ++ks) {
                     mbar_wait(&empty[stage], phase ^ 1u);
                     uint8_t* sa = smem + stage * S::kStageBytes;
                     uint8_t* sb = sa + S::kABytes;
-                    mbar_arrive_expect_tx(&full[stage], bytes);
-                    // A = dZ^t: [64 batch rows][64 n] blocks, two of them for the tile's 128 n
-                    tma_load_2d(sa, &maps.dz[s.layer], &full[stage], s.n0, ks * BK);
-                    tma_load_2d(sa + kAtomBytes, &maps.dz[s.layer], &full[stage], s.n0 + 64, ks * BK);
-                    // B = X: [64 batch rows][64 k] blocks
-                    for (int j = 0; j < s.bn / 64; ++j)
-                        tma_load_2d(sb + j * kAtomBytes, &maps.x[s.layer], &full[stage], s.k0 + 64 * j, ks * BK);
+                    const uint32_t bar = mapa(saddr(&full[stage]), 0);
+                    if (leader) mbar_arrive_expect_tx(&full[stage], 2 * bytes);
+                    // A = dZ^t: [64 batch rows][64 n] blocks, two of them for this CTA's 128 n
+                    tma_load_2d_pair(sa, &maps.dz[s.layer], bar, na, ks * BK);
+                    tma_load_2d_pair(sa + kAtomBytes, &maps.dz[s.layer], bar, na + 64, ks * BK);
+                    // B = X: [64 batch rows][64 k] blocks, bn / 128 of them for this CTA's half
+                    for (int j = 0; j < s.bn / 128; ++j)
+                        tma_load_2d_pair(sb + j * kAtomBytes, &maps.x[s.layer], bar, kb0 + 64 * j, ks * BK);
                     if (++stage == kWStages) { stage = 0; phase ^= 1u; }
                 }
                 g += s.ks1 - s.ks0;
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        int stage = 0;
-        uint32_t phase = 0;
-        int it = 0;
-        const uint32_t ones = saddr(smem + S::kOnesOff);
-        for (int64_t g = g_begin; g < g_end; ++it) {
-            const Segment s = segment_at(P, g, g_end, total, G, cta);
-            const uint32_t idesc = make_idesc(s.bn, true, true);
-            const uint32_t idesc_b = make_idesc(16, true, false);
-            const bool with_bias = s.k0 == 0 && P.L[s.layer].db != nullptr;
-            mbar_wait(acc_empty, ((uint32_t)it & 1u) ^ 1u);
-            tc_fence_after();
-            for (int ks = s.ks0; ks < s.ks1; ++ks) {
-                mbar_wait(&full[stage], phase);
+        // ===== MMA issuer (leader CTA only) =====
+        if (leader) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            const uint32_t ones = saddr(smem + S::kOnesOff);
+            for (int64_t g = g_begin; g < g_end; ++it) {
+                const Segment s = segment_at(P, g, g_end, total, G, pair);
+                const uint32_t idesc = make_idesc(s.bn, true, true, WM);
+                const uint32_t idesc_b = make_idesc(16, true, false, WM);
+                const bool with_bias = s.k0 == 0 && P.L[s.layer].db != nullptr;
+                mbar_wait(acc_empty, ((uint32_t)it & 1u) ^ 1u);
                 tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t sa = saddr(smem + stage * S::kStageBytes);
-                    const uint32_t sb = sa + S::kABytes;
+                for (int ks = s.ks0; ks < s.ks1; ++ks) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sa = saddr(smem + stage * S::kStageBytes);
+                        const uint32_t sb = sa + S::kABytes;
 #pragma unroll
-                    for (int k = 0; k < BK / UK; ++k) {
-                        const uint32_t acc = (ks > s.ks0 || k > 0) ? 1u : 0u;
-                        umma(tmem_base, desc_mnmajor(sa, k), desc_mnmajor(sb, k), idesc, acc);
-                        if (with_bias) umma(tmem_base + WN, desc_mnmajor(sa, k), make_desc(ones, 16, 1024), idesc_b, acc);
+                        for (int k = 0; k < BK / UK; ++k) {
+                            const uint32_t acc = (ks > s.ks0 || k > 0) ? 1u : 0u;
+                            umma_pair(tmem_base, desc_mnmajor(sa, k), desc_mnmajor(sb, k), idesc, acc);
+                            if (with_bias) umma_pair(tmem_base + WN, desc_mnmajor(sa, k), make_desc(ones, 16, 1024), idesc_b, acc);
+                        }
+                        umma_commit_pair(&empty[stage]);
+                        if (ks == s.ks1 - 1) umma_commit_pair(acc_full);
                     }
-                    umma_commit(&empty[stage]);
-                    if (ks == s.ks1 - 1) umma_commit(acc_full);
+                    __syncwarp();
+                    if (++stage == kWStages) { stage = 0; phase ^= 1u; }
                 }
-                __syncwarp();
-                if (++stage == kWStages) { stage = 0; phase ^= 1u; }
+                g += s.ks1 - s.ks0;
             }
-            g += s.ks1 - s.ks0;
         }
     } else {
-        // ===== epilogue =====
+        // ===== epilogue (both CTAs: their own 128 n-rows of the tile) =====
         const int q = warp & 3;
+        const uint32_t acc_empty_leader = mapa(saddr(acc_empty), 0);
         int it = 0;
         for (int64_t g = g_begin; g < g_end; ++it) {
-            const Segment s = segment_at(P, g, g_end, total, G, cta);
+            const Segment s = segment_at(P, g, g_end, total, G, pair);
             g += s.ks1 - s.ks0;
             const WgradLayer& L = P.L[s.layer];
             const bool with_bias = s.k0 == 0 && L.db != nullptr;
-            const int r = q * 32 + lane;                  // row of the tile = n index
+            const int r = (int)rank * BM + q * 32 + lane;  // row of the tile = n index
             const int n = s.n0 + r;
             const bool single = s.nsegs == 1;
             mbar_wait(acc_full, (uint32_t)it & 1u);
             tc_fence_after();
-            float* prow = P.partials + (((int64_t)s.tile * P.max_segs + s.seg) * BM + r) * kPartialPitch;
+            float* prow = P.partials + (((int64_t)s.tile * P.max_segs + s.seg) * WM + r) * kPartialPitch;
             float* wrow = L.dW + (int64_t)n * L.ld_dw + s.k0;
             const int kw = min(WN, L.K - s.k0);
 #pragma unroll 1
             for (int c = 0; c < s.bn / 32; ++c) {
+                if (c * 32 >= kw) break;                   // columns past K are zero padding of the tile
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
                 tmem_ld_wait();
@@ -523,14 +815,15 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(acc_empty);        // the next segment's MMAs may overwrite the accumulator
+            if (lane == 0) mbar_arrive_cluster(acc_empty_leader);     // the next segment's MMAs may overwrite the accumulator
         }
     }
     tc_fence_before();
     __syncthreads();
+    cluster_sync_all();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        tmem_dealloc_pair(tmem_base, 512);
     }
 }
 
@@ -540,8 +833,8 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
 constexpr int kReduceRows = 16;
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const WgradParams P, const int G) {
-    const int tile = blockIdx.x / (BM / kReduceRows);
-    const int r0 = (blockIdx.x % (BM / kReduceRows)) * kReduceRows;
+    const int tile = blockIdx.x / (WM / kReduceRows);
+    const int r0 = (blockIdx.x % (WM / kReduceRows)) * kReduceRows;
     const int64_t total = (int64_t)P.total_tiles * P.ksteps;
     const int c_first = owner_of((int64_t)tile * P.ksteps, total, G);
     const int c_last = owner_of((int64_t)(tile + 1) * P.ksteps - 1, total, G);
@@ -551,11 +844,11 @@ wgrad_reduce_kernel(const WgradParams P, const int G) {
     while (l + 1 < P.n_layers && P.L[l + 1].tile_base <= tile) ++l;
     const WgradLayer& L = P.L[l];
     const int local = tile - L.tile_base;
-    const int n0 = (local / L.k_tiles) * BM, k0 = (local % L.k_tiles) * WN;
+    const int n0 = (local / L.k_tiles) * WM, k0 = (local % L.k_tiles) * WN;
     const int kw = min(WN, L.K - k0);
     const int q4 = kw >> 2;                                   // float4 columns of the tile (K % 8 == 0)
-    const float* p0 = P.partials + (int64_t)tile * P.max_segs * BM * kPartialPitch;
-    const int64_t seg_stride = (int64_t)BM * kPartialPitch;
+    const float* p0 = P.partials + (int64_t)tile * P.max_segs * WM * kPartialPitch;
+    const int64_t seg_stride = (int64_t)WM * kPartialPitch;
     const int rows = min(kReduceRows, L.N - n0 - r0);
     for (int idx = threadIdx.x; idx < rows * q4; idx += 256) {
         const int r = r0 + idx / q4, c = (idx % q4) << 2;
@@ -627,56 +920,95 @@ static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const GemmP
     return check_launch("gemm_bf16");
 }
 
+template <int BN, bool B_MN>
+static int launch_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const PairParams& P, cudaStream_t st) {
+    using S = PairSmem<BN>;
+    static DeviceOnce once;
+    if (once.first())
+        cudaFuncSetAttribute(gemm_pair_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kBytes);
+    const int tiles = (int)(ceil_div(P.M, 2 * BM) * ceil_div(P.N, BN));
+    const int pairs = tiles < kSMs / 2 ? tiles : kSMs / 2;
+    gemm_pair_kernel<BN, B_MN><<<2 * pairs, kThreads, S::kBytes, st>>>(ma, mb, mc, P);
+    return check_launch("gemm_bf16");
+}
+
 }  // namespace tc
 }  // namespace dlrmx
 
 extern "C" {
 
 int dlrmx_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_is_kn, void* C, int64_t ldc, int M, int N,
-                    int K, int epilogue, const float* bias, const void* relu_mask, int64_t ld_mask, dlrmx_stream_t stream) {
+                    int K, int epilogue, const float* bias, const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out,
+                    dlrmx_stream_t stream) {
     using namespace dlrmx;
     using namespace dlrmx::tc;
     DLRMX_REQUIRE(M >= 0 && N > 0 && K > 0 && N % 8 == 0 && K % 8 == 0, "gemm_bf16: need N %% 8 == 0 and K %% 8 == 0 (M=%d N=%d K=%d)", M, N, K);
     DLRMX_REQUIRE(A != nullptr && B != nullptr && C != nullptr && ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0,
                   "gemm_bf16: C must be 16-byte aligned with ldc %% 8 == 0");
-    DLRMX_REQUIRE(epilogue >= EPI_NONE && epilogue <= EPI_BIAS, "gemm_bf16: bad epilogue %d", epilogue);
+    DLRMX_REQUIRE(epilogue >= EPI_NONE && epilogue <= EPI_RELU_BITS, "gemm_bf16: bad epilogue %d", epilogue);
     DLRMX_REQUIRE((epilogue != EPI_BIAS_RELU && epilogue != EPI_BIAS) || (bias != nullptr && (reinterpret_cast<uintptr_t>(bias) & 15) == 0),
                   "gemm_bf16: the bias epilogues need a 16-byte aligned bias");
     DLRMX_REQUIRE(epilogue != EPI_RELU_MASK || (relu_mask != nullptr && ld_mask % 8 == 0 && (reinterpret_cast<uintptr_t>(relu_mask) & 15) == 0),
                   "gemm_bf16: the ReLU-mask epilogue needs a 16-byte aligned mask with ld_mask %% 8 == 0");
+    DLRMX_REQUIRE(epilogue != EPI_RELU_BITS || (relu_mask != nullptr && ld_mask >= (N + 31) / 32 && (reinterpret_cast<uintptr_t>(relu_mask) & 3) == 0),
+                  "gemm_bf16: the ReLU-bits epilogue needs the gate words with ld_mask >= ceil(N / 32)");
+    DLRMX_REQUIRE(relu_bits_out == nullptr || (epilogue == EPI_BIAS_RELU && ld_mask >= (N + 31) / 32),
+                  "gemm_bf16: relu_bits_out goes with the bias + ReLU epilogue and ld_mask >= ceil(N / 32) words");
     if (M == 0) return DLRMX_OK;
-    const int BN = N > 128 ? 256 : (N > 64 ? 128 : 64);
+    cudaStream_t st = (cudaStream_t)stream;
     CUtensorMap ma, mb;
     if (!make_map(&ma, A, M, K, lda, BK, BM)) return DLRMX_E_ARG;
+    if (epilogue == EPI_RELU_MASK) {
+        // bf16 mask matrix: the single-CTA kernel
+        const int BN = N > 128 ? 256 : (N > 64 ? 128 : 64);
+        if (b_is_kn) {
+            if (!make_map(&mb, B, K, N, ldb, 64, BK)) return DLRMX_E_ARG;          // [K, N]: blocks of 64 k-rows x 64 n
+        } else {
+            if (!make_map(&mb, B, N, K, ldb, BK, BN)) return DLRMX_E_ARG;          // [N, K]: BN rows x 64 k
+        }
+        GemmParams P;
+        P.M = M; P.N = N; P.K = K; P.C = (__nv_bfloat16*)C; P.ldc = ldc; P.bias = bias;
+        P.mask = (const __nv_bfloat16*)relu_mask; P.ld_mask = ld_mask; P.epilogue = epilogue;
+        if (b_is_kn) {
+            if (BN == 256) return launch_gemm<256, true>(ma, mb, P, st);
+            if (BN == 128) return launch_gemm<128, true>(ma, mb, P, st);
+            return launch_gemm<64, true>(ma, mb, P, st);
+        }
+        if (BN == 256) return launch_gemm<256, false>(ma, mb, P, st);
+        if (BN == 128) return launch_gemm<128, false>(ma, mb, P, st);
+        return launch_gemm<64, false>(ma, mb, P, st);
+    }
+    // CTA-pair kernel.  An MN-major B half must cover whole 64-column blocks: BN >= 128 there (columns past N are zero-filled)
+    const int BN = N > 128 ? 256 : ((N > 64 || b_is_kn) ? 128 : 64);
+    CUtensorMap mc;
+    if (!make_map(&mc, C, M, N, ldc, 64, 32)) return DLRMX_E_ARG;                  // store boxes: 32 rows x 64 columns
     if (b_is_kn) {
-        if (!make_map(&mb, B, K, N, ldb, 64, BK)) return DLRMX_E_ARG;          // [K, N]: blocks of 64 k-rows x 64 n
+        if (!make_map(&mb, B, K, N, ldb, 64, BK)) return DLRMX_E_ARG;
     } else {
-        if (!make_map(&mb, B, N, K, ldb, BK, BN)) return DLRMX_E_ARG;          // [N, K]: BN rows x 64 k
+        if (!make_map(&mb, B, N, K, ldb, BK, BN / 2)) return DLRMX_E_ARG;          // each CTA of the pair: BN / 2 rows x 64 k
     }
-    GemmParams P;
-    P.M = M; P.N = N; P.K = K; P.C = (__nv_bfloat16*)C; P.ldc = ldc; P.bias = bias;
-    P.mask = (const __nv_bfloat16*)relu_mask; P.ld_mask = ld_mask; P.epilogue = epilogue;
-    cudaStream_t st = (cudaStream_t)stream;
+    PairParams P;
+    P.M = M; P.N = N; P.K = K; P.bias = bias; P.bits_out = relu_bits_out;
+    P.bits_in = (const uint32_t*)relu_mask; P.ld_bits = ld_mask; P.epilogue = epilogue;
     if (b_is_kn) {
-        if (BN == 256) return launch_gemm<256, true>(ma, mb, P, st);
-        if (BN == 128) return launch_gemm<128, true>(ma, mb, P, st);
-        return launch_gemm<64, true>(ma, mb, P, st);
+        if (BN == 256) return launch_pair<256, true>(ma, mb, mc, P, st);
+        return launch_pair<128, true>(ma, mb, mc, P, st);
     }
-    if (BN == 256) return launch_gemm<256, false>(ma, mb, P, st);
-    if (BN == 128) return launch_gemm<128, false>(ma, mb, P, st);
-    return launch_gemm<64, false>(ma, mb, P, st);
+    if (BN == 256) return launch_pair<256, false>(ma, mb, mc, P, st);
+    if (BN == 128) return launch_pair<128, false>(ma, mb, mc, P, st);
+    return launch_pair<64, false>(ma, mb, mc, P, st);
 }
 
 static int wgrad_tiles(int n_layers, const int* N, const int* K) {
     int t = 0;
-    for (int l = 0; l < n_layers; ++l) t += (int)(dlrmx::ceil_div(N[l], dlrmx::tc::BM) * dlrmx::ceil_div(K[l], dlrmx::tc::WN));
+    for (int l = 0; l < n_layers; ++l) t += (int)(dlrmx::ceil_div(N[l], dlrmx::tc::WM) * dlrmx::ceil_div(K[l], dlrmx::tc::WN));
     return t;
 }
 static int wgrad_grid(int total_tiles, int M) {
     const int64_t total = (int64_t)total_tiles * dlrmx::ceil_div(M, dlrmx::tc::BK);
-    int64_t g = total / 8;                      // at least 8 k-steps per CTA
+    int64_t g = total / 8;                      // at least 8 k-steps per CTA pair
     if (g < 1) g = 1;
-    return (int)(g < dlrmx::kSMs ? g : dlrmx::kSMs);
+    return (int)(g < dlrmx::kSMs / 2 ? g : dlrmx::kSMs / 2);      // pairs
 }
 static int wgrad_max_segs(int total_tiles, int M) {
     const int ksteps = (int)dlrmx::ceil_div(M, dlrmx::tc::BK);
@@ -690,7 +1022,7 @@ static int wgrad_max_segs(int total_tiles, int M) {
 size_t dlrmx_gemm_wgrad_workspace_bytes(int n_layers, const int* N, const int* K, int M) {
     if (n_layers <= 0 || M <= 0) return 256;
     const int tiles = wgrad_tiles(n_layers, N, K);
-    return (size_t)tiles * wgrad_max_segs(tiles, M) * dlrmx::tc::BM * dlrmx::tc::kPartialPitch * 4 + dlrmx::align_up((size_t)tiles * 4, 256);
+    return (size_t)tiles * wgrad_max_segs(tiles, M) * dlrmx::tc::WM * dlrmx::tc::kPartialPitch * 4 + 256;
 }
 
 int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld_dz, const void* const* X, const int64_t* ld_x,
@@ -715,7 +1047,7 @@ int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld
         if (!make_map(&maps.dz[l], dZ[l], M, N[l], ld_dz[l], 64, BK)) return DLRMX_E_ARG;
         if (!make_map(&maps.x[l], X[l], M, K[l], ld_x[l], 64, BK)) return DLRMX_E_ARG;
         WgradLayer& L = P.L[l];
-        L.N = N[l]; L.K = K[l]; L.n_tiles = (int)ceil_div(N[l], BM); L.k_tiles = (int)ceil_div(K[l], WN);
+        L.N = N[l]; L.K = K[l]; L.n_tiles = (int)ceil_div(N[l], WM); L.k_tiles = (int)ceil_div(K[l], WN);
         L.tile_base = tiles; L.dW = dW[l]; L.ld_dw = ld_dw[l]; L.db = db != nullptr ? db[l] : nullptr;
         tiles += L.n_tiles * L.k_tiles;
     }
@@ -726,10 +1058,10 @@ int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld
     if (once.first())
         cudaFuncSetAttribute(wgrad_streamk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgradSmem::kBytes);
     const int G = wgrad_grid(tiles, M);
-    wgrad_streamk_kernel<<<G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
+    wgrad_streamk_kernel<<<2 * G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
     if (int rc = check_launch("gemm_wgrad")) return rc;
     if (G > tiles || (int64_t)tiles * P.ksteps % G != 0 || ((int64_t)tiles * P.ksteps / G) % P.ksteps != 0) {   // some tile is split
-        wgrad_reduce_kernel<<<tiles * (BM / kReduceRows), 256, 0, (cudaStream_t)stream>>>(P, G);
+        wgrad_reduce_kernel<<<tiles * (WM / kReduceRows), 256, 0, (cudaStream_t)stream>>>(P, G);
         return check_launch("gemm_wgrad_reduce");
     }
     return DLRMX_OK;

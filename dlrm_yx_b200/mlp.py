@@ -95,21 +95,24 @@ class _Tower(torch.autograd.Function):
             padded = hb.new_zeros((hb.shape[0], first.K_pad))
             padded[:, :first.K].copy_(hb)
             hb = padded
-        acts = [hb.contiguous()]
+        acts, gates = [hb.contiguous()], []
         for li in range(i0, i1):
             L = mlp.layers[li]
-            acts.append(ops.gemm_bf16(acts[-1], L.w_shadow, epilogue=ops.EPI_BIAS_RELU, bias=L.b_master))
+            # every layer but the run's last also leaves its ReLU gates as one bit per element for the next layer's dgrad
+            bits = ops.relu_bits_empty(hb.shape[0], L.N, hb.device) if li + 1 < i1 else None
+            acts.append(ops.gemm_bf16(acts[-1], L.w_shadow, epilogue=ops.EPI_BIAS_RELU, bias=L.b_master, relu_bits_out=bits))
+            gates.append(bits)
         ctx.mlp, ctx.i0, ctx.i1, ctx.in_cols = mlp, i0, i1, h.shape[1]
         # a consumer that fuses the last layer's ReLU backward + bias gradient into its own backward (the head) sets the flag
         ctx.flag = {"pre_masked": False}
         mlp._last_relu = (i1 - 1, ctx.flag)
-        ctx.save_for_backward(*acts)
+        ctx.save_for_backward(*acts, *gates[:-1])
         return acts[-1]
 
     @staticmethod
     def backward(ctx, dy):
-        acts = ctx.saved_tensors
         mlp, i0, i1 = ctx.mlp, ctx.i0, ctx.i1
+        acts, gates = ctx.saved_tensors[:i1 - i0 + 1], ctx.saved_tensors[i1 - i0 + 1:]
         layers = mlp.layers[i0:i1]
         n = len(layers)
         dyb = (dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)).contiguous()
@@ -121,7 +124,7 @@ class _Tower(torch.autograd.Function):
             dzs[-1], _ = ops.relu_bwd_bias_grad(dyb, acts[-1], relu=True, db=layers[-1].gb)
             dbs[-1] = None
         for j in range(n - 1, 0, -1):  # dz of layer j-1 = (dz_j W_j) masked by layer j-1's output
-            dzs[j - 1] = ops.gemm_bf16(dzs[j], layers[j].w_shadow, b_is_kn=True, epilogue=ops.EPI_RELU_MASK, relu_mask=acts[j])
+            dzs[j - 1] = ops.gemm_bf16(dzs[j], layers[j].w_shadow, b_is_kn=True, epilogue=ops.EPI_RELU_BITS, relu_mask=gates[j - 1])
         dx = None
         if ctx.needs_input_grad[0]:
             dx = ops.gemm_bf16(dzs[0], layers[0].w_shadow, b_is_kn=True)

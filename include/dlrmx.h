@@ -238,17 +238,22 @@ int dlrmx_relu_bwd_bias_grad_noalloc(const void* dy_bf16, const void* y_bf16, vo
  * gemm_bf16:  C[M, N] (bf16, row pitch ldc) = epilogue( A[M, K] . op(B) ), A bf16 row-major (pitch lda)
  *   b_is_kn = 0: B is [N, K] row-major  (forward:  y = x W^t with W [N, K] as nn.Linear stores it)
  *   b_is_kn = 1: B is [K, N] row-major  (dgrad:    dx = dz W with the same W, no transposed copy)
- *   epilogue 0: none;  1: + bias[N] (fp32), ReLU;  2: C = acc where relu_mask[M, N] (bf16, pitch ld_mask) > 0 else 0 -- the
- *   ReLU backward of the layer that produced this GEMM's output gradient, so the result is that layer's dz;  3: + bias.
+ *   epilogue 0: none;  1: + bias[N] (fp32), ReLU -- with relu_bits_out the gates (Y > 0) are also written as one bit per
+ *   element, word [m, n >> 5] bit (n & 31), row pitch ld_mask words;  3: + bias;
+ *   4: C = acc where the gate bit of relu_mask (such a bit matrix, pitch ld_mask words) is set, else 0 -- the ReLU backward
+ *   of the layer that produced this GEMM's output gradient, so the result is that layer's dz;
+ *   2: the same with relu_mask a bf16 matrix [M, N] (pitch ld_mask elements), gate = mask > 0.
+ *   Epilogues 0, 1, 3, 4 run on CTA pairs (tcgen05.mma.cta_group::2, M = 256 per MMA, TMA-store epilogue); 2 on single CTAs.
  *   N % 8 == 0, K % 8 == 0, all pointers 16-byte aligned, pitches multiples of 8 elements.
  * gemm_wgrad_bf16: for every layer l of a tower, in ONE launch:  dW[l] [N_l, K_l] (fp32, pitch ld_dw) = dZ[l]^t X[l]  and
  *   db[l] [N_l] = column sums of dZ[l]  (dZ[l] [M, N_l], X[l] [M, K_l] bf16 row-major).  The (tile, k-step) space of all
- *   layers is split evenly over the SMs (stream-K); partial tiles are combined in a fixed order by the CTA that finishes a
- *   tile last, so the result is deterministic and there is no split-K reduction launch.  workspace: the size the query
- *   returns, ZEROED before the first call (the call leaves its counters zero).  Host arrays of device pointers / sizes.
+ *   layers is split evenly over the CTA pairs (stream-K); tiles cut into several segments leave fp32 partials in the
+ *   workspace that ONE second launch sums in segment order, so the result is deterministic.  workspace: the size the query
+ *   returns (contents need no initialisation).  Host arrays of device pointers / sizes.
  * ------------------------------------------------------------------------------------------- */
 int dlrmx_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_is_kn, void* C, int64_t ldc, int M, int N,
-                    int K, int epilogue, const float* bias, const void* relu_mask, int64_t ld_mask, dlrmx_stream_t stream);
+                    int K, int epilogue, const float* bias, const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out,
+                    dlrmx_stream_t stream);
 size_t dlrmx_gemm_wgrad_workspace_bytes(int n_layers, const int* N, const int* K, int M);
 int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld_dz, const void* const* X,
                           const int64_t* ld_x, float* const* dW, const int64_t* ld_dw, float* const* db, const int* N,

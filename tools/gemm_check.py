@@ -49,6 +49,15 @@ def timed(fn, iters, reps=10):
     return t[len(t) // 2] / reps
 
 
+def pack_bits(gate):
+    """bool [M, N] -> int32 [M, ceil(N / 32)] gate words as the forward epilogue writes them."""
+    M, N = gate.shape
+    padded = torch.zeros(M, (N + 31) // 32 * 32, dtype=torch.int64, device=gate.device)
+    padded[:, :N] = gate
+    words = (padded.view(M, -1, 32) << torch.arange(32, device=gate.device, dtype=torch.int64)).sum(-1)
+    return torch.where(words >= 2 ** 31, words - 2 ** 32, words).to(torch.int32)
+
+
 def rel_err(got, ref):
     return float((got.float() - ref).norm() / ref.norm().clamp_min(1e-30))
 
@@ -86,7 +95,8 @@ def main():
                 got = ops.gemm_bf16(x, w, epilogue=ops.EPI_BIAS_RELU, bias=b)
                 err = rel_err(got, ref)
                 y_out, bb = torch.empty_like(got), b.to(bf)
-                ms = timed(lambda: ops.gemm_bf16(x, w, epilogue=ops.EPI_BIAS_RELU, bias=b, out=y_out), args.iters)
+                gbits = ops.relu_bits_empty(M, N, dev)
+                ms = timed(lambda: ops.gemm_bf16(x, w, epilogue=ops.EPI_BIAS_RELU, bias=b, out=y_out, relu_bits_out=gbits), args.iters)
                 ms_lib = timed(lambda: torch._addmm_activation(bb, x, w.t(), out=y_out), args.iters)
                 ok = err < 6e-3
                 bad += not ok
@@ -95,12 +105,13 @@ def main():
                                       cublas_tflops=round(flops / ms_lib / 1e9, 1))), flush=True)
             if "dgrad" in only:
                 ref = (dz.float() @ w.float()) * (yprev.float() > 0)
-                got = ops.gemm_bf16(dz, w, b_is_kn=True, epilogue=ops.EPI_RELU_MASK, relu_mask=yprev)
+                bits = pack_bits(yprev.float() > 0)
+                got = ops.gemm_bf16(dz, w, b_is_kn=True, epilogue=ops.EPI_RELU_BITS, relu_mask=bits)
                 err = rel_err(got, ref)
                 got2 = ops.gemm_bf16(dz, w, b_is_kn=True)
                 err2 = rel_err(got2, dz.float() @ w.float())
                 dx_out = torch.empty_like(got)
-                ms = timed(lambda: ops.gemm_bf16(dz, w, b_is_kn=True, epilogue=ops.EPI_RELU_MASK, relu_mask=yprev, out=dx_out), args.iters)
+                ms = timed(lambda: ops.gemm_bf16(dz, w, b_is_kn=True, epilogue=ops.EPI_RELU_BITS, relu_mask=bits, out=dx_out), args.iters)
                 ms_nomask = timed(lambda: ops.gemm_bf16(dz, w, b_is_kn=True, out=dx_out), args.iters)
                 ms_lib = timed(lambda: torch.mm(dz, w, out=dx_out), args.iters)
                 ok = err < 6e-3 and err2 < 6e-3
