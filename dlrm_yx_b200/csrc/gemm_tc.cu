@@ -6,11 +6,12 @@
 //   dgrad     dX = (dZ W) * (Y_prev > 0)    gemm_bf16_kernel<BN, /*B_MN=*/true>: W [N, K] row-major is the MN-major B operand
 //                                           (no transposed weight copy), epilogue applies the PREVIOUS layer's ReLU mask, so
 //                                           its result is that layer's dZ -- no separate ReLU-backward pass
-//   wgrad     dW = dZ^t X,  db = dZ^t 1     wgrad_streamk_kernel: ALL layers of a tower in ONE launch.  Both operands are
+//   wgrad     dW = dZ^t X,  db = dZ^t 1     wgrad_splitk_kernel: ALL layers of a tower in ONE launch.  Both operands are
 //                                           MN-major (the contraction runs over the batch), tiles [256 n] x [<=256 k]; the
-//                                           (tile, k-step) space of all layers is cut into equal contiguous ranges, one per
-//                                           CTA pair (stream-K); tiles cut into several segments leave fp32 partials that
-//                                           wgrad_reduce_kernel sums in segment order (deterministic, ONE reduce launch
+//                                           batch range of every tile is cut into `split` chunks, work units (chunk, tile)
+//                                           go to the CTA pairs chunk-major (concurrent pairs walk the same batch rows:
+//                                           operands come from DRAM once); the chunks leave fp32 partials that
+//                                           wgrad_reduce_kernel sums in chunk order (deterministic, ONE reduce launch
 //                                           for the whole tower, element-parallel over all SMs); the bias gradient
 //                                           rides along as one extra N = 16 MMA against a tile of ones.
 // Kernel shape (both): one CTA per SM, persistent; warp 0 = TMA producer (cp.async.bulk.tensor into 128-byte-swizzled
@@ -394,7 +395,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 //   pair tile [256 m] x [BN n];  CTA r: A rows m0 + 128 r .. +127, B rows (N) n0 + r BN/2 .. (K-major) or the same columns
 //   of the [K, N] matrix (MN-major, 64-column blocks), D rows 128 r .. in its own TMEM (2 x BN columns, double-buffered).
 //   Barriers: full[s] lives in the leader (its arrive.expect_tx counts both CTAs' bytes; the peer's TMA signals it remotely),
-//   empty[s] / acc_full[a] in both CTAs (multicast tcgen05.commit from the leader), acc_empty[a] in the leader (8 epilogue
+//   empty[s] / acc_full[a] in both CTAs (multicast tcgen05.commit from the leader), acc_empty[a] in the leader (16 epilogue
 //   warps arrive, the peer's remotely).
 // ------------------------------------------------------------------------------------------------------------------
 enum { EPI_RELU_BITS = 4 };
@@ -412,7 +413,7 @@ template <int BN>
 struct PairSmem {
     static constexpr uint32_t kABytes = BM * BK * 2, kBBytes = (BN / 2) * BK * 2;
     static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-    static constexpr uint32_t kOutBytes = 4 * 2 * 4096;                       // 4 epilogue warps x 2 buffers x [32 rows][128 B]
+    static constexpr uint32_t kOutBytes = 8 * 2 * 4096;                       // 8 epilogue warps x 2 buffers x [32 rows][128 B]
     static constexpr int kStages = (227 * 1024 - 2048 - (int)kOutBytes) / (int)kStageBytes > 8
                                        ? 8 : (227 * 1024 - 2048 - (int)kOutBytes) / (int)kStageBytes;
     static constexpr uint32_t kOutOff = kStages * kStageBytes;
@@ -420,8 +421,10 @@ struct PairSmem {
     static constexpr uint32_t kBytes = kBarOff + 512 + 1024;                  // barriers + the alignment slack
 };
 
+constexpr int kPairThreads = 320;          // warp 0: TMA producer, warp 1: MMA issuer, warps 2-9: epilogue
+
 template <int BN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_c, const PairParams P) {
     using S = PairSmem<BN>;
@@ -448,7 +451,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         prefetch_tmap(&map_b);
         prefetch_tmap(&map_c);
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 8); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 16); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc_pair(tmem_slot, 2 * BN);
@@ -519,10 +522,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
         }
     } else {
-        // ===== epilogue: 4 warps per CTA, warp w reads TMEM lanes 32*(w % 4) .. +31 = rows of this CTA's half of the tile =====
-        const int q = warp & 3;
-        uint8_t* obuf = smem + S::kOutOff + q * 8192;              // two [32 rows][128 B] swizzled boxes
+        // ===== epilogue: 8 warps per CTA.  Warp w reads TMEM lanes 32*(w % 4) .. +31 (rows of this CTA's half of the tile);
+        // the two warps of a lane quarter split the tile's 64-column boxes (even / odd), each with two staging buffers =====
+        const int q = warp & 3, h = (warp - 2) >> 2;
+        constexpr int BOXES = BN / 64, MYB = (BOXES + 1) / 2;      // boxes per tile, and per warp at most
+        uint8_t* obuf = smem + S::kOutOff + (warp - 2) * 8192;     // two [32 rows][128 B] swizzled boxes
         const uint32_t acc_empty_leader0 = mapa(saddr(&acc_empty[0]), 0), acc_empty_leader1 = mapa(saddr(&acc_empty[1]), 0);
+        const bool with_bias = P.epilogue == EPI_BIAS_RELU || P.epilogue == EPI_BIAS;
         int it = 0;
         int ob = 0;
         for (int tile = pair; tile < tiles; tile += pairs, ++it) {
@@ -531,74 +537,89 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < P.M;
-            uint32_t gate[BN / 32];
-            if (P.epilogue == EPI_RELU_BITS) {                      // the whole tile row's gates, before the accumulator is ready
+            uint32_t gate[2 * MYB], outw[2 * MYB];
+            if (P.epilogue == EPI_RELU_BITS) {                      // this warp's gates of the tile row, before the accumulator is ready
 #pragma unroll
-                for (int c = 0; c < BN / 32; ++c)
-                    gate[c] = (row_ok && n0 + c * 32 < P.N) ? __ldg(P.bits_in + (int64_t)row * P.ld_bits + ((n0 >> 5) + c)) : 0u;
+                for (int i = 0; i < 2 * MYB; ++i) {
+                    const int c = 2 * (h + 2 * (i >> 1)) + (i & 1);
+                    gate[i] = (row_ok && c < BN / 32 && n0 + c * 32 < P.N) ? __ldg(P.bits_in + (int64_t)row * P.ld_bits + ((n0 >> 5) + c)) : 0u;
+                }
             }
             mbar_wait(&acc_full[as], aphase);
             tc_fence_after();
 #pragma unroll
-            for (int c = 0; c < BN / 32; ++c) {
-                const int col0 = n0 + c * 32;
-                if (col0 < P.N) {                                   // warp-uniform
-                    uint32_t v[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
-                    if ((c & 1) == 0) {                             // a new 64-column box: its buffer's previous store has been read
-                        if (lane == 0) bulk_wait_read<1>();
-                        __syncwarp();
-                    }
-                    tmem_ld_wait();
-                    float f[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-                    if (P.epilogue == EPI_BIAS_RELU || P.epilogue == EPI_BIAS) {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            if (col0 + j < P.N) {
-                                const float4 b = __ldg(reinterpret_cast<const float4*>(P.bias + col0 + j));
-                                f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
-                            }
-                        }
-                        if (P.epilogue == EPI_BIAS_RELU) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-                        }
-                    } else if (P.epilogue == EPI_RELU_BITS) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] = ((gate[c] >> j) & 1u) ? f[j] : 0.f;
-                    }
-                    uint32_t pk[16], bits = 0u;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        pk[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
-                        bits |= ((pk[j] & 0x7fffu) != 0u ? 1u : 0u) << (2 * j);
-                        bits |= ((pk[j] & 0x7fff0000u) != 0u ? 1u : 0u) << (2 * j + 1);
-                    }
-                    if (P.epilogue == EPI_BIAS_RELU && P.bits_out != nullptr && row_ok)
-                        P.bits_out[(int64_t)row * P.ld_bits + (col0 >> 5)] = bits;      // after ReLU: non-zero == positive
-                    // 16-byte chunk j of this thread's 64-byte half row goes to chunk ((c & 1) * 4 + j) ^ (row & 7) of its line
+            for (int bi = 0; bi < MYB; ++bi) {
+                const int bx = h + 2 * bi;                          // box of 64 columns
+                if (bx < BOXES && n0 + bx * 64 < P.N) {             // warp-uniform
+                    if (lane == 0) bulk_wait_read<1>();             // the store that last used this buffer has read it
+                    __syncwarp();
                     uint8_t* line = obuf + ob * 4096 + lane * 128;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int ch = (((c & 1) << 2) + j) ^ (lane & 7);
-                        *reinterpret_cast<uint4*>(line + (ch << 4)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-                    }
-                    if ((c & 1) == 1 || col0 + 32 >= P.N) {         // the box is complete (or the tensor ends in its first half)
-                        fence_proxy_async();
-                        __syncwarp();
-                        if (lane == 0) {
-                            tma_store_2d(&map_c, obuf + ob * 4096, n0 + (c >> 1) * 64, m0 + q * 32);
-                            bulk_commit();
+                    for (int cc = 0; cc < 2; ++cc) {
+                        const int c = 2 * bx + cc;
+                        const int col0 = n0 + c * 32;
+                        if (col0 < P.N) {
+                            uint32_t v[32];
+                            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                            float4 bv[8];                           // the bias loads fly while the TMEM load does
+                            if (with_bias) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j)
+                                    bv[j] = (col0 + 4 * j < P.N) ? __ldg(reinterpret_cast<const float4*>(P.bias + col0 + 4 * j))
+                                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+                            }
+                            tmem_ld_wait();
+                            float f[32];
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+                            if (with_bias) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) {
+                                    f[4 * j] += bv[j].x; f[4 * j + 1] += bv[j].y; f[4 * j + 2] += bv[j].z; f[4 * j + 3] += bv[j].w;
+                                }
+                                if (P.epilogue == EPI_BIAS_RELU) {
+#pragma unroll
+                                    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                                }
+                            } else if (P.epilogue == EPI_RELU_BITS) {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) f[j] = ((gate[2 * bi + cc] >> j) & 1u) ? f[j] : 0.f;
+                            }
+                            uint32_t pk[16], bits = 0u;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                pk[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+                                bits |= ((pk[j] & 0x7fffu) != 0u ? 1u : 0u) << (2 * j);
+                                bits |= ((pk[j] & 0x7fff0000u) != 0u ? 1u : 0u) << (2 * j + 1);
+                            }
+                            outw[2 * bi + cc] = bits;               // after ReLU: non-zero == positive
+                            // 16-byte chunk j of this thread's 64-byte half row goes to chunk (cc * 4 + j) ^ (row & 7) of its line
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int ch = ((cc << 2) + j) ^ (lane & 7);
+                                *reinterpret_cast<uint4*>(line + (ch << 4)) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                            }
                         }
-                        ob ^= 1;
                     }
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&map_c, obuf + ob * 4096, n0 + bx * 64, m0 + q * 32);      // clipped at M and N
+                        bulk_commit();
+                    }
+                    ob ^= 1;
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(as ? acc_empty_leader1 : acc_empty_leader0);
+            if (lane == 0) mbar_arrive_cluster(as ? acc_empty_leader1 : acc_empty_leader0);   // the accumulator is drained
+            if (P.epilogue == EPI_BIAS_RELU && P.bits_out != nullptr && row_ok) {   // the gate words, off the critical path
+#pragma unroll
+                for (int i = 0; i < 2 * MYB; ++i) {
+                    const int c = 2 * (h + 2 * (i >> 1)) + (i & 1);
+                    if (c < BN / 32 && n0 + c * 32 < P.N) P.bits_out[(int64_t)row * P.ld_bits + ((n0 >> 5) + c)] = outw[i];
+                }
+            }
         }
         if (lane == 0) bulk_wait_all();
     }
@@ -612,7 +633,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// wgrad, all layers of a tower in one launch (stream-K over CTA pairs)
+// wgrad, all layers of a tower in one launch (split-K over CTA pairs)
 //   pair tile [256 n] x [<= 256 k] of dW; one tcgen05.mma.cta_group::2 of M = 256 per 16 batch rows.  CTA r of the pair
 //   stages dZ columns n0 + 128 r .. +127 (A, MN-major) and X columns k0 + r bn/2 .. (B, MN-major), 64 batch rows per stage.
 // ------------------------------------------------------------------------------------------------------------------
@@ -630,9 +651,10 @@ struct WgradLayer {
     float* db;                // [N] or nullptr
 };
 struct WgradParams {
-    int n_layers, M, ksteps, total_tiles, max_segs;
+    int n_layers, M, ksteps, total_tiles;
+    int split, per;           // every tile's batch (k-step) range is cut into `split` chunks of `per` k-steps
     WgradLayer L[kMaxLayers];
-    float* partials;          // [total_tiles][max_segs][256][WN + 32] fp32
+    float* partials;          // [total_tiles][split][256][WN + 32] fp32 (used when split > 1)
 };
 struct WgradMaps {
     CUtensorMap dz[kMaxLayers];   // [M, N] bf16, box {64 n, 64 m}
@@ -640,21 +662,18 @@ struct WgradMaps {
 };
 constexpr int kPartialPitch = WN + 32;     // columns 0..255: the dW tile; column 256: the bias-gradient column
 
-struct Segment { int layer, n0, k0, bn, tile, ks0, ks1, seg, nsegs; };
+struct Segment { int layer, n0, k0, bn, tile, ks0, ks1, seg; };
 
-// pair c of G owns the global k-steps [c*total/G, (c+1)*total/G) of the flattened (tile, k-step) space
-__device__ __forceinline__ int64_t range_begin(int64_t c, int64_t total, int G) { return c * total / G; }
-__device__ __forceinline__ int owner_of(int64_t g, int64_t total, int G) {
-    int c = (int)(g * G / total);
-    while (c + 1 < G && range_begin(c + 1, total, G) <= g) ++c;
-    while (c > 0 && range_begin(c, total, G) > g) --c;
-    return c;
-}
-__device__ __forceinline__ Segment segment_at(const WgradParams& P, int64_t g, int64_t g_end, int64_t total, int G, int pair) {
+// Work unit u of a launch = (batch chunk u / total_tiles, tile u % total_tiles): chunk-major, so the pairs that run at the same
+// time walk the SAME batch rows of dZ and X -- every operand block comes from DRAM once and is shared through L2 by the tiles
+// that need it.  (The first version cut the tile-major (tile, k-step) space into equal ranges, classic stream-K: every pair
+// started somewhere else in the batch and the Terabyte top tower read 1.1 GB from DRAM instead of 0.38 GB -- HBM-bound.)
+__device__ __forceinline__ Segment segment_of(const WgradParams& P, int u) {
     Segment s;
-    s.tile = (int)(g / P.ksteps);
-    s.ks0 = (int)(g - (int64_t)s.tile * P.ksteps);
-    s.ks1 = (int)min((int64_t)P.ksteps, s.ks0 + (g_end - g));
+    s.seg = u / P.total_tiles;
+    s.tile = u - s.seg * P.total_tiles;
+    s.ks0 = s.seg * P.per;
+    s.ks1 = min(P.ksteps, s.ks0 + P.per);
     int l = 0;
     while (l + 1 < P.n_layers && P.L[l + 1].tile_base <= s.tile) ++l;
     s.layer = l;
@@ -662,10 +681,6 @@ __device__ __forceinline__ Segment segment_at(const WgradParams& P, int64_t g, i
     s.n0 = (local / P.L[l].k_tiles) * WM;
     s.k0 = (local % P.L[l].k_tiles) * WN;
     s.bn = (P.L[l].K - s.k0) > 128 ? 256 : 128;           // UMMA N; each CTA stages bn / 2 columns (whole 64-column blocks)
-    const int c_first = owner_of((int64_t)s.tile * P.ksteps, total, G);
-    const int c_last = owner_of((int64_t)(s.tile + 1) * P.ksteps - 1, total, G);
-    s.seg = pair - c_first;
-    s.nsegs = c_last - c_first + 1;
     return s;
 }
 
@@ -678,7 +693,7 @@ struct WgradSmem {
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P) {
+wgrad_splitk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P) {
     using S = WgradSmem;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -692,8 +707,7 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
     const int G = gridDim.x >> 1, pair = blockIdx.x >> 1;
-    const int64_t total = (int64_t)P.total_tiles * P.ksteps;
-    const int64_t g_begin = range_begin(pair, total, G), g_end = range_begin(pair + 1, total, G);
+    const int units = P.total_tiles * P.split;
 
     if (threadIdx.x == 0) {
         for (int l = 0; l < P.n_layers; ++l) { prefetch_tmap(&maps.dz[l]); prefetch_tmap(&maps.x[l]); }
@@ -717,8 +731,8 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int64_t g = g_begin; g < g_end;) {
-                const Segment s = segment_at(P, g, g_end, total, G, pair);
+            for (int u = pair; u < units; u += G) {
+                const Segment s = segment_of(P, u);
                 const uint32_t bytes = S::kABytes + (uint32_t)(s.bn / 2) * (BK * 2);
                 const int na = s.n0 + (int)rank * BM, kb0 = s.k0 + (int)rank * (s.bn / 2);
                 for (int ks = s.ks0; ks < s.ks1; ++ks) {
@@ -735,7 +749,6 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
                         tma_load_2d_pair(sb + j * kAtomBytes, &maps.x[s.layer], bar, kb0 + 64 * j, ks * BK);
                     if (++stage == kWStages) { stage = 0; phase ^= 1u; }
                 }
-                g += s.ks1 - s.ks0;
             }
         }
     } else if (warp == 1) {
@@ -745,8 +758,8 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
             uint32_t phase = 0;
             int it = 0;
             const uint32_t ones = saddr(smem + S::kOnesOff);
-            for (int64_t g = g_begin; g < g_end; ++it) {
-                const Segment s = segment_at(P, g, g_end, total, G, pair);
+            for (int u = pair; u < units; u += G, ++it) {
+                const Segment s = segment_of(P, u);
                 const uint32_t idesc = make_idesc(s.bn, true, true, WM);
                 const uint32_t idesc_b = make_idesc(16, true, false, WM);
                 const bool with_bias = s.k0 == 0 && P.L[s.layer].db != nullptr;
@@ -770,25 +783,23 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
                     __syncwarp();
                     if (++stage == kWStages) { stage = 0; phase ^= 1u; }
                 }
-                g += s.ks1 - s.ks0;
             }
         }
     } else {
         // ===== epilogue (both CTAs: their own 128 n-rows of the tile) =====
         const int q = warp & 3;
         const uint32_t acc_empty_leader = mapa(saddr(acc_empty), 0);
+        const bool single = P.split == 1;
         int it = 0;
-        for (int64_t g = g_begin; g < g_end; ++it) {
-            const Segment s = segment_at(P, g, g_end, total, G, pair);
-            g += s.ks1 - s.ks0;
+        for (int u = pair; u < units; u += G, ++it) {
+            const Segment s = segment_of(P, u);
             const WgradLayer& L = P.L[s.layer];
             const bool with_bias = s.k0 == 0 && L.db != nullptr;
             const int r = (int)rank * BM + q * 32 + lane;  // row of the tile = n index
             const int n = s.n0 + r;
-            const bool single = s.nsegs == 1;
             mbar_wait(acc_full, (uint32_t)it & 1u);
             tc_fence_after();
-            float* prow = P.partials + (((int64_t)s.tile * P.max_segs + s.seg) * WM + r) * kPartialPitch;
+            float* prow = P.partials + (((int64_t)s.tile * P.split + s.seg) * WM + r) * kPartialPitch;
             float* wrow = L.dW + (int64_t)n * L.ld_dw + s.k0;
             const int kw = min(WN, L.K - s.k0);
 #pragma unroll 1
@@ -815,7 +826,7 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(acc_empty_leader);     // the next segment's MMAs may overwrite the accumulator
+            if (lane == 0) mbar_arrive_cluster(acc_empty_leader);     // the next unit's MMAs may overwrite the accumulator
         }
     }
     tc_fence_before();
@@ -827,19 +838,15 @@ wgrad_streamk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P
     }
 }
 
-// Second pass of the stream-K wgrad: every tile that was cut into several segments is summed in segment order (a fixed
-// order: deterministic) into dW / db.  Element-parallel over all SMs: CTA (tile, slice of 16 rows), 256 threads, float4
-// columns, coalesced.  Tiles computed by one CTA were written by wgrad_streamk_kernel itself.
-constexpr int kReduceRows = 16;
+// Second pass of the split-K wgrad: the `split` partials of every tile are summed in chunk order (a fixed order:
+// deterministic) into dW / db.  Element-parallel over all SMs: CTA (tile, slice of 8 rows), 256 threads, float4 columns,
+// coalesced, up to 8 partials in flight per thread.
+constexpr int kReduceRows = 8;
 __global__ void __launch_bounds__(256)
-wgrad_reduce_kernel(const WgradParams P, const int G) {
+wgrad_reduce_kernel(const WgradParams P) {
     const int tile = blockIdx.x / (WM / kReduceRows);
     const int r0 = (blockIdx.x % (WM / kReduceRows)) * kReduceRows;
-    const int64_t total = (int64_t)P.total_tiles * P.ksteps;
-    const int c_first = owner_of((int64_t)tile * P.ksteps, total, G);
-    const int c_last = owner_of((int64_t)(tile + 1) * P.ksteps - 1, total, G);
-    const int nsegs = c_last - c_first + 1;
-    if (nsegs == 1) return;
+    const int nsegs = P.split;
     int l = 0;
     while (l + 1 < P.n_layers && P.L[l + 1].tile_base <= tile) ++l;
     const WgradLayer& L = P.L[l];
@@ -847,25 +854,29 @@ wgrad_reduce_kernel(const WgradParams P, const int G) {
     const int n0 = (local / L.k_tiles) * WM, k0 = (local % L.k_tiles) * WN;
     const int kw = min(WN, L.K - k0);
     const int q4 = kw >> 2;                                   // float4 columns of the tile (K % 8 == 0)
-    const float* p0 = P.partials + (int64_t)tile * P.max_segs * WM * kPartialPitch;
+    const float* p0 = P.partials + (int64_t)tile * P.split * WM * kPartialPitch;
     const int64_t seg_stride = (int64_t)WM * kPartialPitch;
     const int rows = min(kReduceRows, L.N - n0 - r0);
     for (int idx = threadIdx.x; idx < rows * q4; idx += 256) {
         const int r = r0 + idx / q4, c = (idx % q4) << 2;
         const float* src = p0 + (int64_t)r * kPartialPitch + c;
-        float4 a = __ldcg(reinterpret_cast<const float4*>(src));
-#pragma unroll 4
-        for (int sgi = 1; sgi < nsegs; ++sgi) {
-            const float4 b = __ldcg(reinterpret_cast<const float4*>(src + sgi * seg_stride));
-            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s0 = 0; s0 < nsegs; s0 += 8) {
+            float4 b[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (s0 + i < nsegs) b[i] = __ldcg(reinterpret_cast<const float4*>(src + (s0 + i) * seg_stride));
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (s0 + i < nsegs) { a.x += b[i].x; a.y += b[i].y; a.z += b[i].z; a.w += b[i].w; }
         }
         *reinterpret_cast<float4*>(L.dW + (int64_t)(n0 + r) * L.ld_dw + k0 + c) = a;
     }
     if (k0 == 0 && L.db != nullptr && (int)threadIdx.x < rows) {
         const int r = r0 + threadIdx.x;
         const float* src = p0 + (int64_t)r * kPartialPitch + WN;
-        float a = __ldcg(src);
-        for (int sgi = 1; sgi < nsegs; ++sgi) a += __ldcg(src + sgi * seg_stride);
+        float a = 0.f;
+        for (int sgi = 0; sgi < nsegs; ++sgi) a += __ldcg(src + sgi * seg_stride);
         L.db[n0 + r] = a;
     }
 }
@@ -928,7 +939,7 @@ static int launch_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
         cudaFuncSetAttribute(gemm_pair_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kBytes);
     const int tiles = (int)(ceil_div(P.M, 2 * BM) * ceil_div(P.N, BN));
     const int pairs = tiles < kSMs / 2 ? tiles : kSMs / 2;
-    gemm_pair_kernel<BN, B_MN><<<2 * pairs, kThreads, S::kBytes, st>>>(ma, mb, mc, P);
+    gemm_pair_kernel<BN, B_MN><<<2 * pairs, kPairThreads, S::kBytes, st>>>(ma, mb, mc, P);
     return check_launch("gemm_bf16");
 }
 
@@ -1004,25 +1015,27 @@ static int wgrad_tiles(int n_layers, const int* N, const int* K) {
     for (int l = 0; l < n_layers; ++l) t += (int)(dlrmx::ceil_div(N[l], dlrmx::tc::WM) * dlrmx::ceil_div(K[l], dlrmx::tc::WN));
     return t;
 }
-static int wgrad_grid(int total_tiles, int M) {
-    const int64_t total = (int64_t)total_tiles * dlrmx::ceil_div(M, dlrmx::tc::BK);
-    int64_t g = total / 8;                      // at least 8 k-steps per CTA pair
-    if (g < 1) g = 1;
-    return (int)(g < dlrmx::kSMs / 2 ? g : dlrmx::kSMs / 2);      // pairs
-}
-static int wgrad_max_segs(int total_tiles, int M) {
-    const int ksteps = (int)dlrmx::ceil_div(M, dlrmx::tc::BK);
-    const int G = wgrad_grid(total_tiles, M);
-    const int64_t total = (int64_t)total_tiles * ksteps;
-    const int64_t per = total / G > 0 ? total / G : 1;
-    int64_t s = ksteps / per + 2;
-    return (int)(s < G ? s : G);
+// Split factor of the batch (k-step) range: the launch runs ceil(tiles * S / pairs) waves of units of ceil(ksteps / S) k-steps,
+// each followed by an accumulator drain worth ~10 k-steps (single-buffered); the S with the least such time wins.
+static void wgrad_split(int total_tiles, int M, int* split, int* per) {
+    const int ksteps = (int)dlrmx::ceil_div(M, dlrmx::tc::BK), pairs = dlrmx::kSMs / 2;
+    int best_s = 1;
+    int64_t best = -1;
+    for (int s = 1; s <= 32 && s <= ksteps; ++s) {
+        const int64_t waves = dlrmx::ceil_div((int64_t)total_tiles * s, pairs);
+        const int64_t cost = waves * (dlrmx::ceil_div(ksteps, s) + 10);
+        if (best < 0 || cost < best) { best = cost; best_s = s; }
+    }
+    *per = (int)dlrmx::ceil_div(ksteps, best_s);
+    *split = (int)dlrmx::ceil_div(ksteps, *per);          // no empty chunks
 }
 
 size_t dlrmx_gemm_wgrad_workspace_bytes(int n_layers, const int* N, const int* K, int M) {
     if (n_layers <= 0 || M <= 0) return 256;
     const int tiles = wgrad_tiles(n_layers, N, K);
-    return (size_t)tiles * wgrad_max_segs(tiles, M) * dlrmx::tc::WM * dlrmx::tc::kPartialPitch * 4 + 256;
+    int split, per;
+    wgrad_split(tiles, M, &split, &per);
+    return (size_t)tiles * split * dlrmx::tc::WM * dlrmx::tc::kPartialPitch * 4 + 256;
 }
 
 int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld_dz, const void* const* X, const int64_t* ld_x,
@@ -1052,16 +1065,17 @@ int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld
         tiles += L.n_tiles * L.k_tiles;
     }
     P.total_tiles = tiles;
-    P.max_segs = wgrad_max_segs(tiles, M);
+    wgrad_split(tiles, M, &P.split, &P.per);
     P.partials = (float*)workspace;
     static DeviceOnce once;
     if (once.first())
-        cudaFuncSetAttribute(wgrad_streamk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgradSmem::kBytes);
-    const int G = wgrad_grid(tiles, M);
-    wgrad_streamk_kernel<<<2 * G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
+        cudaFuncSetAttribute(wgrad_splitk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgradSmem::kBytes);
+    const int units = tiles * P.split;
+    const int G = units < kSMs / 2 ? units : kSMs / 2;      // CTA pairs
+    wgrad_splitk_kernel<<<2 * G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
     if (int rc = check_launch("gemm_wgrad")) return rc;
-    if (G > tiles || (int64_t)tiles * P.ksteps % G != 0 || ((int64_t)tiles * P.ksteps / G) % P.ksteps != 0) {   // some tile is split
-        wgrad_reduce_kernel<<<tiles * (WM / kReduceRows), 256, 0, (cudaStream_t)stream>>>(P, G);
+    if (P.split > 1) {
+        wgrad_reduce_kernel<<<tiles * (WM / kReduceRows), 256, 0, (cudaStream_t)stream>>>(P);
         return check_launch("gemm_wgrad_reduce");
     }
     return DLRMX_OK;

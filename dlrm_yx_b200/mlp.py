@@ -7,7 +7,7 @@ call shape (apply_mlp: `layers(x)`, 518-524).
   * forward per layer = one tcgen05 GEMM (csrc/gemm_tc.cu: TMA-staged bf16 operands, fp32 accumulators in TMEM),
     fp32 bias + ReLU in the epilogue;
   * backward of a run of layers (`_Tower`) = per layer one tcgen05 dgrad GEMM dz_prev = (dz W) * (y_prev > 0) whose
-    epilogue applies the PREVIOUS layer's ReLU mask (no separate ReLU-backward pass), then ONE stream-K tcgen05 launch
+    epilogue applies the PREVIOUS layer's ReLU mask (no separate ReLU-backward pass), then ONE split-K tcgen05 launch
     for the weight AND bias gradients of every layer of the run (fp32, written straight into the flat gradient buffer);
   * `gemm="cublas"` keeps the round-1 path (cuBLASLt GEMMs through torch + dlrmx_relu_bwd_bias_grad) as the measured
     comparator of tools/gemm_check.py and bench.py --mlp fused-bf16-cublas; it is never a fallback;

@@ -468,7 +468,7 @@ def gemm_bf16(a, b, b_is_kn=False, epilogue=EPI_NONE, bias=None, relu_mask=None,
 
 
 def gemm_wgrad_workspace(Ns, Ks, M, device):
-    """Workspace for gemm_wgrad_bf16 on layers of these shapes (stream-K partial tiles)."""
+    """Workspace for gemm_wgrad_bf16 on layers of these shapes (split-K partial tiles)."""
     n = len(Ns)
     nbytes = _lib.load().dlrmx_gemm_wgrad_workspace_bytes(n, _int_array(Ns), _int_array(Ks), int(M))
     return torch.zeros(nbytes, dtype=torch.uint8, device=device)
@@ -476,7 +476,7 @@ def gemm_wgrad_workspace(Ns, Ks, M, device):
 
 def gemm_wgrad_bf16(dzs, xs, dws, dbs, workspace):
     """For every layer l: dws[l] [N_l, K_l] fp32 = dzs[l]^t xs[l], dbs[l] [N_l] = column sums of dzs[l] (None: skip) -- all
-    layers in ONE stream-K tensor-core launch; dzs[l] [M, N_l], xs[l] [M, K_l] bf16 row-major."""
+    layers in ONE split-K tensor-core launch; dzs[l] [M, N_l], xs[l] [M, K_l] bf16 row-major."""
     n = len(dzs)
     _need_cuda(*dzs, *xs, *dws, workspace)
     M = dzs[0].shape[0]

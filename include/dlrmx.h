@@ -246,9 +246,9 @@ int dlrmx_relu_bwd_bias_grad_noalloc(const void* dy_bf16, const void* y_bf16, vo
  *   Epilogues 0, 1, 3, 4 run on CTA pairs (tcgen05.mma.cta_group::2, M = 256 per MMA, TMA-store epilogue); 2 on single CTAs.
  *   N % 8 == 0, K % 8 == 0, all pointers 16-byte aligned, pitches multiples of 8 elements.
  * gemm_wgrad_bf16: for every layer l of a tower, in ONE launch:  dW[l] [N_l, K_l] (fp32, pitch ld_dw) = dZ[l]^t X[l]  and
- *   db[l] [N_l] = column sums of dZ[l]  (dZ[l] [M, N_l], X[l] [M, K_l] bf16 row-major).  The (tile, k-step) space of all
- *   layers is split evenly over the CTA pairs (stream-K); tiles cut into several segments leave fp32 partials in the
- *   workspace that ONE second launch sums in segment order, so the result is deterministic.  workspace: the size the query
+ *   db[l] [N_l] = column sums of dZ[l]  (dZ[l] [M, N_l], X[l] [M, K_l] bf16 row-major).  The batch range of every
+ *   256 x 256 tile of every layer is cut into chunks that go to the CTA pairs chunk-major (split-K); the chunks leave fp32
+ *   partials in the workspace that ONE second launch sums in chunk order, so the result is deterministic.  workspace: the size the query
  *   returns (contents need no initialisation).  Host arrays of device pointers / sizes.
  * ------------------------------------------------------------------------------------------- */
 int dlrmx_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_is_kn, void* C, int64_t ldc, int M, int N,

@@ -91,7 +91,7 @@ def test_dgrad_with_gate_bits_and_bf16_mask(M, K, N):
                                       (1000, [(16, 512), (256, 64), (64, 16), (368, 512)]),
                                       (64, [(8, 8)]), (70000, [(72, 40), (104, 1024)])])
 def test_wgrad_all_layers_one_launch(M, layers):
-    """dW_l = dZ_l^t X_l and db_l = column sums of dZ_l for every layer in one stream-K launch (+ one reduce launch);
+    """dW_l = dZ_l^t X_l and db_l = column sums of dZ_l for every layer in one split-K launch (+ one reduce launch);
     deterministic (two calls, bit-equal); a layer with db = None gets no bias gradient."""
     from dlrm_yx_b200 import ops
     g = torch.Generator(device="cuda").manual_seed(4)
