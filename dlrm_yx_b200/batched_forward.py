@@ -68,7 +68,9 @@ def _forward_cuda(weights, table_offsets, offsets, indices, L_max, BT_block_size
             if w.device != dev0 and not torch.cuda.can_device_access_peer(w.device.index, dev0.index):
                 raise RuntimeError("batched_forward: device %s cannot store to %s over NVLink/P2P" % (w.device, dev0))
             if w.device != dev0:
-                torch.empty(1, device=w.device).copy_(out.view(-1)[:1])   # makes torch enable peer access
+                # torch enables peer access lazily and per direction: a copy whose SOURCE lives on w.device lets w.device
+                # reach dev0's memory, which is what this device's lookup kernel needs to store into `out`
+                torch.empty(1, device=dev0).copy_(torch.zeros(1, device=w.device))
             ptrs = _table_ptrs(w, toff)
             slot = out[:, d * T:(d + 1) * T, :]                        # peer stores when d is not dev0
             rc = lib.dlrmx_embbag_fwd_i32(ptrs.data_ptr(), 0, idx.contiguous().data_ptr(),

@@ -20,7 +20,7 @@ struct RankSplit {
 // dir 0: recv chunks -> feature block ; dir 1: feature-block gradient -> send chunks
 template <int VEC>
 __global__ void __launch_bounds__(256)
-a2a_layout_kernel(float* __restrict__ chunks, float* __restrict__ block, int64_t bsb, int feat_off,
+a2a_layout_kernel(float* __restrict__ chunks, float* __restrict__ block, int64_t bsb, int64_t bsf, int feat_off,
                   RankSplit rs, int lb, int D, int dir) {
     const int T = rs.first_table[rs.W];
     const int dv = D / VEC;
@@ -36,7 +36,7 @@ a2a_layout_kernel(float* __restrict__ chunks, float* __restrict__ block, int64_t
         const int tp = rs.first_table[p + 1] - rs.first_table[p];
         // chunk p starts at lb*first_table[p]*D and is [lb, tp, D]
         float* c = chunks + ((int64_t)lb * rs.first_table[p] + (int64_t)b * tp + (t - rs.first_table[p])) * D + d * VEC;
-        float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * D + d * VEC;
+        float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * bsf + d * VEC;      // bsf: feature pitch (>= D)
         RowVec<VEC> v;
         if (dir == 0) { v.load(c); v.store(f); }
         else          { v.load(f); v.store(c); }
@@ -52,7 +52,8 @@ struct PeerBases {
 
 template <int VEC>
 __global__ void __launch_bounds__(256)
-a2a_push_kernel(const float* __restrict__ block, int64_t bsb, int feat_off, RankSplit rs, PeerBases pb, int lb, int D) {
+a2a_push_kernel(const float* __restrict__ block, int64_t bsb, int64_t bsf, int feat_off, RankSplit rs, PeerBases pb, int lb,
+                int D) {
     const int T = rs.first_table[rs.W];
     const int dv = D / VEC;
     const int64_t total = (int64_t)lb * T * dv;
@@ -66,17 +67,17 @@ a2a_push_kernel(const float* __restrict__ block, int64_t bsb, int feat_off, Rank
         while (t >= rs.first_table[p + 1]) ++p;
         const int tp = rs.first_table[p + 1] - rs.first_table[p];
         float* c = pb.base[p] + ((int64_t)b * tp + (t - rs.first_table[p])) * D + d * VEC;
-        const float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * D + d * VEC;
+        const float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * bsf + d * VEC;
         RowVec<VEC> v;
         v.load_stream(f);
         v.store(c);
     }
 }
 
-static int a2a_layout(float* chunks, float* block, int64_t bsb, int feat_off, int W, const int* tpr, int lb,
+static int a2a_layout(float* chunks, float* block, int64_t bsb, int64_t bsf, int feat_off, int W, const int* tpr, int lb,
                       int D, int dir, dlrmx_stream_t stream) {
     DLRMX_REQUIRE(W >= 1 && W <= kMaxRanks, "a2a layout: W=%d out of range", W);
-    DLRMX_REQUIRE(lb >= 0 && D >= 1, "a2a layout: bad sizes");
+    DLRMX_REQUIRE(lb >= 0 && D >= 1 && bsf >= D, "a2a layout: bad sizes (feature pitch %lld < D = %d)", (long long)bsf, D);
     RankSplit rs;
     rs.W = W;
     rs.first_table[0] = 0;
@@ -86,31 +87,31 @@ static int a2a_layout(float* chunks, float* block, int64_t bsb, int feat_off, in
     }
     const int T = rs.first_table[W];
     if (lb == 0 || T == 0) return DLRMX_OK;
-    const bool vec = (D % 4 == 0) && (bsb % 4 == 0) && (((uintptr_t)chunks | (uintptr_t)block) & 15) == 0;
+    const bool vec = (D % 4 == 0) && (bsb % 4 == 0) && (bsf % 4 == 0) && (((uintptr_t)chunks | (uintptr_t)block) & 15) == 0;
     const int64_t total = (int64_t)lb * T * (vec ? D / 4 : D);
     int64_t nblk = ceil_div(total, 256);
     if (nblk > (int64_t)kSMs * 16) nblk = (int64_t)kSMs * 16;
     const unsigned blocks = (unsigned)nblk;
     cudaStream_t st = (cudaStream_t)stream;
-    if (vec) a2a_layout_kernel<4><<<blocks, 256, 0, st>>>(chunks, block, bsb, feat_off, rs, lb, D, dir);
-    else     a2a_layout_kernel<1><<<blocks, 256, 0, st>>>(chunks, block, bsb, feat_off, rs, lb, D, dir);
+    if (vec) a2a_layout_kernel<4><<<blocks, 256, 0, st>>>(chunks, block, bsb, bsf, feat_off, rs, lb, D, dir);
+    else     a2a_layout_kernel<1><<<blocks, 256, 0, st>>>(chunks, block, bsb, bsf, feat_off, rs, lb, D, dir);
     return check_launch(dir == 0 ? "a2a_unpack" : "a2a_pack_grad");
 }
 
 }  // namespace dlrmx
 
 extern "C" {
-int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D, float* const* host_peer_chunk_bases,
                         dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(W >= 1 && W <= kMaxRanks, "a2a_push_grad: W=%d out of range", W);
-    DLRMX_REQUIRE(lb >= 0 && D >= 1 && host_peer_chunk_bases != nullptr, "a2a_push_grad: bad arguments");
+    DLRMX_REQUIRE(lb >= 0 && D >= 1 && dfeat_stride_f >= D && host_peer_chunk_bases != nullptr, "a2a_push_grad: bad arguments");
     RankSplit rs;
     PeerBases pb;
     rs.W = W;
     rs.first_table[0] = 0;
-    bool vec = (D % 4 == 0) && (dfeat_stride_b % 4 == 0) && ((uintptr_t)dfeat & 15) == 0;
+    bool vec = (D % 4 == 0) && (dfeat_stride_b % 4 == 0) && (dfeat_stride_f % 4 == 0) && ((uintptr_t)dfeat & 15) == 0;
     for (int p = 0; p < W; ++p) {
         DLRMX_REQUIRE(host_tables_per_rank[p] >= 0, "a2a_push_grad: negative table count");
         rs.first_table[p + 1] = rs.first_table[p] + host_tables_per_rank[p];
@@ -124,19 +125,19 @@ int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off
     int64_t nblk = ceil_div(total, 256);
     if (nblk > (int64_t)kSMs * 16) nblk = (int64_t)kSMs * 16;
     cudaStream_t st = (cudaStream_t)stream;
-    if (vec) a2a_push_kernel<4><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, feat_off, rs, pb, lb, D);
-    else     a2a_push_kernel<1><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, feat_off, rs, pb, lb, D);
+    if (vec) a2a_push_kernel<4><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
+    else     a2a_push_kernel<1><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
     return check_launch("a2a_push_grad");
 }
 
 int dlrmx_a2a_unpack(const float* recv, int W, const int* host_tables_per_rank, int lb, int D, float* dst,
-                     int64_t dst_stride_b, int feat_off, dlrmx_stream_t stream) {
-    return dlrmx::a2a_layout(const_cast<float*>(recv), dst, dst_stride_b, feat_off, W, host_tables_per_rank, lb, D, 0,
-                             stream);
+                     int64_t dst_stride_b, int64_t dst_stride_f, int feat_off, dlrmx_stream_t stream) {
+    return dlrmx::a2a_layout(const_cast<float*>(recv), dst, dst_stride_b, dst_stride_f, feat_off, W, host_tables_per_rank, lb,
+                             D, 0, stream);
 }
-int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D, float* send, dlrmx_stream_t stream) {
-    return dlrmx::a2a_layout(send, const_cast<float*>(dfeat), dfeat_stride_b, feat_off, W, host_tables_per_rank, lb, D,
-                             1, stream);
+    return dlrmx::a2a_layout(send, const_cast<float*>(dfeat), dfeat_stride_b, dfeat_stride_f, feat_off, W,
+                             host_tables_per_rank, lb, D, 1, stream);
 }
 }

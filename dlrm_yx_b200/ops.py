@@ -351,7 +351,7 @@ def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases):
     _need_cuda(dfeat)
     bases = (ctypes.c_void_p * len(peer_chunk_bases))(*[int(b) for b in peer_chunk_bases])
     with _timed("a2a_push_grad"):
-        rc = _lib.load().dlrmx_a2a_push_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
+        rc = _lib.load().dlrmx_a2a_push_grad(dfeat.data_ptr(), dfeat.stride(0), dfeat.stride(1), feat_off, len(tables_per_rank),
                                              _int_array(tables_per_rank), lb, D, bases, _stream())
         _lib.check(rc, "dlrmx_a2a_push_grad")
 
@@ -361,7 +361,7 @@ def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):
     _need_cuda(recv, dst)
     with _timed("a2a_unpack"):
         rc = _lib.load().dlrmx_a2a_unpack(recv.data_ptr(), len(tables_per_rank), _int_array(tables_per_rank), lb, D,
-                                          dst.data_ptr(), dst.stride(0), feat_off, _stream())
+                                          dst.data_ptr(), dst.stride(0), dst.stride(1), feat_off, _stream())
         _lib.check(rc, "dlrmx_a2a_unpack")
     return dst
 
@@ -372,7 +372,7 @@ def a2a_pack_grad(dfeat, feat_off, tables_per_rank, lb, D, send=None):
     if send is None:
         send = torch.empty(lb * T * D, dtype=torch.float32, device=dfeat.device)
     with _timed("a2a_pack_grad"):
-        rc = _lib.load().dlrmx_a2a_pack_grad(dfeat.data_ptr(), dfeat.stride(0), feat_off, len(tables_per_rank),
+        rc = _lib.load().dlrmx_a2a_pack_grad(dfeat.data_ptr(), dfeat.stride(0), dfeat.stride(1), feat_off, len(tables_per_rank),
                                              _int_array(tables_per_rank), lb, D, send.data_ptr(), _stream())
         _lib.check(rc, "dlrmx_a2a_pack_grad")
     return send

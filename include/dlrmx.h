@@ -280,11 +280,12 @@ int dlrmx_head_bwd(const float* dp, const float* p, const void* h_bf16, const fl
  * a2a_unpack: recv buffer = concat over source ranks p of [lb, T_p, D]  ->  dst [lb, F, D] features
  *             feat_off + (rank-major table order), i.e. straight into the interaction input.
  * a2a_pack_grad: the transpose, dfeat [lb, F, D] -> send buffer concat over p of [lb, T_p, D].
- *   tables_per_rank: HOST int array [W].
+ *   tables_per_rank: HOST int array [W].  *_stride_b / *_stride_f: floats between samples / between features of the
+ *   [lb, F, D] block (stride_f >= D: the interaction input may be pitched, e.g. D + 8 for the bulk-copy staging).
  * ------------------------------------------------------------------------------------------- */
 int dlrmx_a2a_unpack(const float* recv, int W, const int* host_tables_per_rank, int lb, int D,
-                     float* dst, int64_t dst_stride_b, int feat_off, dlrmx_stream_t stream);
-int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+                     float* dst, int64_t dst_stride_b, int64_t dst_stride_f, int feat_off, dlrmx_stream_t stream);
+int dlrmx_a2a_pack_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D,
                         float* send, dlrmx_stream_t stream);
 
@@ -311,7 +312,7 @@ int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* tabl
                                  const int64_t* indices, const int64_t* offsets, int64_t N, int T, int B,
                                  int D, int64_t table_ld, const float* per_sample_weights, float* const* out_peers, int lb,
                                  int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
-int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int feat_off, int W,
+int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D,
                         float* const* host_peer_chunk_bases, dlrmx_stream_t stream);
 

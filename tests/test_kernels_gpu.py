@@ -440,3 +440,11 @@ def test_a2a_layout_roundtrip(D):
     assert np.array_equal(feat.cpu().numpy()[:, 1:, :], ref)
     send = ops.a2a_pack_grad(feat, 1, tpr, lb, D)
     assert np.array_equal(send.cpu().numpy(), recv.cpu().numpy())
+    # pitched interaction input (feature pitch D + 8, what the bf16-facing interaction kernels stage with one bulk copy):
+    # the NCCL path of the benchmarked configuration unpacks into / packs from it
+    pitched = ops.alloc_features(lb, 1 + T, D, dev, pitch=D + 8)
+    pitched.zero_()
+    ops.a2a_unpack(recv, tpr, lb, D, pitched, 1)
+    assert np.array_equal(pitched.cpu().numpy()[:, 1:, :], ref)
+    send2 = ops.a2a_pack_grad(pitched, 1, tpr, lb, D)
+    assert np.array_equal(send2.cpu().numpy(), recv.cpu().numpy())

@@ -67,6 +67,7 @@ class Case(object):
         self.W, self.rank = ext.my_size, ext.my_rank
         assert self.B % self.W == 0, "fixture batch %d not divisible by %d ranks" % (self.B, self.W)
         self.lb = self.B // self.W
+        self.tower_gemm = "tc"
 
     def build(self, sharder, exchange, bf16, replicate_below):
         g, dev = self.g, self.dev
@@ -96,7 +97,7 @@ class Case(object):
             m.enable_peer_exchange(self.lb, mixed=bool(bf16))
         opt = None
         if bf16:
-            m.fuse_mlps(self.lr, "sgd" if self.sgd else "adagrad")
+            m.fuse_mlps(self.lr, "sgd" if self.sgd else "adagrad", gemm=self.tower_gemm)
         else:
             dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
             m.bot_l = ext.DDP(m.bot_l, device_ids=[dev.index])
@@ -196,12 +197,15 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--replicate-below", type=int, default=100)
     ap.add_argument("--out", default="")
+    ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"], help="GEMMs of the fused bf16 towers (cublas: comparator)")
+    ap.add_argument("--losses-only", action="store_true", help="debug: print the bf16 variants' losses instead of asserting")
     args = ap.parse_args()
     ext.init_distributed(use_gpu=True, backend="nccl")
     W, rank = ext.my_size, ext.my_rank
     dev = torch.device("cuda", torch.cuda.current_device())
     torch.backends.cuda.matmul.allow_tf32 = False
     c = Case(args.case, dev)
+    c.tower_gemm = args.tower_gemm
     report = {"case": args.case, "world_size": W, "steps": args.steps, "checks": []}
 
     def note(msg):
@@ -229,6 +233,10 @@ def main():
             C = c.run(*c.build(sharder, "nccl", True, rep_below), steps=args.steps)
             Dm = c.build(sharder, "peer", True, rep_below)
             Dr = c.run(*Dm, steps=args.steps)
+            if args.losses_only:
+                print("rank %d %s gemm=%s  fp32 A %s | bf16 nccl C %s | bf16 peer D %s | feat equal %s" % (
+                    rank, tag, args.tower_gemm, A["losses"], C["losses"], Dr["losses"], torch.equal(C["feat"], Dr["feat"])), flush=True)
+                continue
             same(C, Dr, tag + ": peer vs NCCL (bf16 towers)")
             E = c.run(*c.build(sharder, "peer", True, rep_below), steps=args.steps, graph=True)
             same(Dr, E, tag + ": CUDA-graph replay vs eager (peer, bf16 towers)")
