@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"],
                     help="fused-bf16 towers: tc = the repo's tcgen05/TMEM/TMA GEMM kernels; cublas = cuBLASLt through torch, "
                          "the measured comparator (never a fallback)")
+    ap.add_argument("--defer-wgrad", type=int, default=1,
+                    help="1: the top tower's weight-gradient launch moves to the end of the backward pass, beside the sparse update")
     ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
                     help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
     ap.add_argument("--sharder", default="traffic")
@@ -207,6 +209,7 @@ def build_model(args, cfg, W, exchange=None):
         m.enable_peer_exchange(lb, mixed=(args.mlp == "fused-bf16"))
     if args.mlp == "fused-bf16":
         m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm)
+        m.top_l.defer_wgrad = bool(m.top_l.defer_wgrad and args.defer_wgrad)
         return m, None
     dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
     if W > 1:

@@ -76,6 +76,13 @@ def _update_on_side(emb, grad, indices, offsets, B, stride_b, stride_t, presorte
     torch.autograd.Variable._execution_engine.queue_callback(join)
 
 
+def _flush_deferred_wgrads():
+    """The fused top tower's deferred weight-gradient kernel goes out here: behind the interaction backward, ahead of and
+    beside the sparse update (mlp.flush_deferred)."""
+    from . import mlp
+    mlp.flush_deferred()
+
+
 class _BCELoss(torch.nn.BCELoss):
     """dlrm.loss_fn for --loss-function=bce (dlrm_s_pytorch.py:505-507): torch.nn.BCELoss(reduction="mean"), computed
     by one libdlrmx kernel each way when predictions and targets are fp32 CUDA tensors (ops.bce_mean); anything else
@@ -140,6 +147,7 @@ class _SparseArchLocalMixed(torch.autograd.Function):
         feat, x, indices, offsets = ctx.saved_tensors
         B, F, D = feat.shape
         dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
+        _flush_deferred_wgrads()
         _update_on_side(ctx.emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, ctx.presorted, keep=(dfeat,))
         ctx.presorted = None
         return dx, None, None, None, None, None, None
@@ -185,6 +193,7 @@ class _DistInteract(torch.autograd.Function):
         step = ctx.step
         if ctx.mixed:
             dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
+            _flush_deferred_wgrads()
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
@@ -375,6 +384,9 @@ class DLRM_Net(nn.Module):
         self._mixed = bool(self.fuse_sparse_arch and self.arch_interaction_op == "dot" and first.fused and last.fused
                            and first.K == D + nz and ops.interact_mixed_supported(F, D))
         self.bot_l.out_bf16 = self._mixed
+        # the top tower's backward comes first: its weight gradients wait for the end of the pass, where they overlap the
+        # sparse update on the side stream instead of delaying the interaction backward
+        self.top_l.defer_wgrad = bool(self.fuse_sparse_arch and gemm == "tc")
         return self
 
     def step_mlps(self):

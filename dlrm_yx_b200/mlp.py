@@ -84,6 +84,42 @@ class _LinearAct(torch.autograd.Function):
         return dx, None, None, None
 
 
+# ---- deferred weight-gradient launches ------------------------------------------------------------------------------
+# The top tower's backward runs first; launched in place, its wgrad kernel (tensor-bound, ~0.15 ms at the Terabyte shape)
+# sits between the tower's dgrads and the interaction backward with nothing to overlap.  Deferred, it is launched right
+# after the interaction backward on a HIGH-PRIORITY stream: one persistent CTA per SM (200 KB of shared memory, 15 K
+# registers) next to the sparse update of the side stream (HBM-bound, 16 bytes of shared memory per CTA), which keeps
+# two of its CTAs resident beside it.  Priority matters: a CTA of an already running grid is never preempted, so the
+# wgrad CTAs must be placed before the update's grid has filled the register files.
+_DEFERRED = []
+_HP = {}
+
+
+def flush_deferred():
+    if not _DEFERRED:
+        return
+    from . import dlrm_net
+    main = torch.cuda.current_stream()
+    if dlrm_net.OVERLAP_STREAMS:
+        hp = _HP.get(main.device)
+        if hp is None:
+            hp = _HP[main.device] = torch.cuda.Stream(device=main.device, priority=-1)
+        hp.wait_stream(main)
+        with torch.cuda.stream(hp):
+            for launch in _DEFERRED:
+                launch()
+        held = list(_DEFERRED)        # the closures own the operands: alive until the main stream has joined
+
+        def join():
+            torch.cuda.current_stream().wait_stream(hp)
+            held.clear()
+        torch.autograd.Variable._execution_engine.queue_callback(join)
+    else:
+        for launch in _DEFERRED:
+            launch()
+    _DEFERRED.clear()
+
+
 class _Tower(torch.autograd.Function):
     """Layers [i0, i1) of a FusedMLP (all Linear + ReLU, widths multiples of 8) as ONE autograd node on the tcgen05 GEMMs."""
 
@@ -130,7 +166,14 @@ class _Tower(torch.autograd.Function):
             dx = ops.gemm_bf16(dzs[0], layers[0].w_shadow, b_is_kn=True)
             if ctx.in_cols != layers[0].K_pad:       # the caller's input was unpadded
                 dx = dx[:, :layers[0].K]
-        ops.gemm_wgrad_bf16(dzs, list(acts[:-1]), [L.gW for L in layers], dbs, mlp._wgrad_workspace(i0, i1, dyb.shape[0]))
+        xs, dws, ws = list(acts[:-1]), [L.gW for L in layers], mlp._wgrad_workspace(i0, i1, dyb.shape[0])
+        if mlp.defer_wgrad:
+            # the weight gradients are needed only by step(): their launch waits for flush_deferred() -- called by the sparse
+            # arch right after the interaction backward, or at the end of the pass (see there)
+            _DEFERRED.append(lambda: ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws))
+            torch.autograd.Variable._execution_engine.queue_callback(flush_deferred)
+        else:
+            ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws)
         return dx, None, None, None, None
 
 
@@ -176,6 +219,7 @@ class FusedMLP(nn.Module):
         if gemm not in ("tc", "cublas"):
             raise ValueError("gemm must be 'tc' (tcgen05 kernels) or 'cublas' (the library comparator)")
         self.gemm = gemm
+        self.defer_wgrad = False    # True: the wgrad launch waits for flush_deferred() (see there)
         self._ws = {}
         mods = list(sequential)
         if len(mods) % 2 or not all(isinstance(m, nn.Linear) for m in mods[0::2]):
