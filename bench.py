@@ -43,6 +43,8 @@ def parse():
                          "the measured comparator (never a fallback)")
     ap.add_argument("--defer-wgrad", type=int, default=1,
                     help="1: the top tower's weight-gradient launch moves to the end of the backward pass, beside the sparse update")
+    ap.add_argument("--trace", default="", help="after the timed regions: CUPTI kernel timeline (torch.profiler) of 3 more steps, "
+                    "written as text (start / duration / stream / kernel) for the LAST of them; every rank writes <trace>.rank<r>")
     ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
                     help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
     ap.add_argument("--sharder", default="traffic")
@@ -457,6 +459,9 @@ def run_ours(args):
         e2e_step(i)
     _, wall_e2e = timed(e2e_step, args.steps)
 
+    if args.trace:
+        write_trace(args.trace + (".rank%d" % rank if W > 1 else ""), lambda i: run(*devb[i % nb]), sync)
+
     # ---- per-kernel durations: CUDA events around every libdlrmx launch.  Graph mode: a second capture of the same
     #      step on ONE stream with external event-record nodes around each kernel; it is replayed K times and the
     #      events are read after each replay, so the kernels are timed inside a dense replayed step, each alone on
@@ -506,6 +511,36 @@ def run_ours(args):
     return dict(W=W, rank=rank, cfg=cfg, lb=lb, B_global=B_global, local_tables=local_tables, rep_tables=rep_tables,
                 parity=parity, gpu_ref=gpu_ref, ms_dev=ms_dev,
                 wall_e2e=wall_e2e, launches=launches, prof=prof, ms_eager=ms_eager, use_graph=use_graph, prof_mode=prof_mode, clocks=clocks, h2d=h2d, devb=devb, model=m)
+
+
+def write_trace(path, step_fn, sync):
+    """Kernel timeline of one step as CUPTI sees it (never a timed number: the profiler is attached): per kernel the start
+    relative to the step's first kernel, the duration, the stream and the name -- what overlaps what."""
+    import tempfile
+    from torch.profiler import ProfilerActivity, profile
+    sync()
+    marks = []
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        for i in range(3):
+            step_fn(i)
+            torch.cuda.synchronize()
+            marks.append(time.perf_counter())
+    tmp = tempfile.mktemp(suffix=".json")
+    prof.export_chrome_trace(tmp)
+    ev = json.load(open(tmp))["traceEvents"]
+    os.remove(tmp)
+    ks = sorted((e for e in ev if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset") and "ts" in e), key=lambda e: e["ts"])
+    if not ks:
+        return
+    # the last step = the kernels after the largest gap among the final third of the list is fragile; use three equal groups
+    n = len(ks) // 3
+    last = ks[len(ks) - n:]
+    t0 = last[0]["ts"]
+    with open(path, "w") as f:
+        f.write("# one step, %d GPU activities; columns: start_us dur_us stream name\n" % len(last))
+        for e in last:
+            f.write("%9.1f %8.1f %4s %s\n" % (e["ts"] - t0, e.get("dur", 0.0), e.get("args", {}).get("stream", "?"), e["name"][:110]))
+        f.write("# step span %.1f us\n" % (last[-1]["ts"] + last[-1].get("dur", 0.0) - t0))
 
 
 # ------------------------------------------------------------------------------------------------------

@@ -54,7 +54,7 @@ SIGNATURES = {
     "dlrmx_interact_dot_fwd_mixed": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                              c_int64, c_void_p]),
     "dlrmx_interact_dot_bwd_mixed": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
-                                             c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
+                                             c_int64, c_void_p, c_int64, c_void_p, c_int, c_void_p]),
     "dlrmx_relu_bwd_bias_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                          c_int, c_int, c_void_p]),
     "dlrmx_relu_bwd_bias_grad_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),

@@ -206,7 +206,7 @@ int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
 int interact_fwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* x_bf16, int B, int F, int D, int itself,
                        void* out_bf16, int64_t ostride, cudaStream_t st);
 int interact_bwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* x_bf16, int B, int F, int D, int itself,
-                       const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16,
+                       const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16, int relu_x,
                        cudaStream_t st);
 enum { DLRMX_TUNE_IX_CUDACORE = 2 };   // tunable 2 = 1 forces the CUDA-core kernels (tests compare both)
 
@@ -224,13 +224,13 @@ int dlrmx_interact_dot_fwd_mixed(const float* feat, int64_t feat_stride_b, int64
 
 int dlrmx_interact_dot_bwd_mixed(const float* feat, int64_t feat_stride_b, int64_t feat_stride_f, const void* x_bf16, int B, int F, int D,
                                  int itself, const void* dout_bf16, int64_t dout_stride, float* dfeat,
-                                 int64_t dfeat_stride_b, void* dx_bf16, dlrmx_stream_t stream) {
+                                 int64_t dfeat_stride_b, void* dx_bf16, int relu_x, dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(B >= 0 && F >= 2 && D >= 1 && feat != nullptr && x_bf16 != nullptr && dout_bf16 != nullptr &&
                       dfeat != nullptr && dx_bf16 != nullptr, "interact_dot_bwd_mixed: bad arguments");
     if (B == 0) return DLRMX_OK;
     return interact_bwd_mixed(feat, feat_stride_b, feat_stride_f, x_bf16, B, F, D, itself, dout_bf16, dout_stride, dfeat,
-                              dfeat_stride_b, dx_bf16, (cudaStream_t)stream);
+                              dfeat_stride_b, dx_bf16, relu_x, (cudaStream_t)stream);
 }
 
 int dlrmx_interact_dot_fwd(const float* feat, int64_t feat_stride_b, int B, int F, int D, int itself,

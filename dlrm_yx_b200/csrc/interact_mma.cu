@@ -287,7 +287,7 @@ template <bool MIXED, bool BULK>
 __global__ void __launch_bounds__(kMmaWarps * 32, 4)
 interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int64_t fst, int B, int F, int D, int itself,
                         const void* __restrict__ dout_, int64_t dstride, float* __restrict__ dfeat, int64_t dfsb,
-                        const __nv_bfloat16* __restrict__ xb, __nv_bfloat16* __restrict__ dxb) {
+                        const __nv_bfloat16* __restrict__ xb, __nv_bfloat16* __restrict__ dxb, int relu_x) {
     static_assert(!BULK || MIXED, "bulk staging serves the bf16-facing kernels");
     extern __shared__ __align__(16) float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -474,6 +474,10 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int64_t fst
                                 if (i == 0) {      // dense pass-through R[:, 0:D] = x; gradient of x leaves as bf16
                                     v.x = __fadd_rn(v.x, __bfloat162float(zraw[col]));
                                     v.y = __fadd_rn(v.y, __bfloat162float(zraw[col + 1]));
+                                    if (relu_x) {      // x is the output of a Linear + ReLU layer: its ReLU backward rides along
+                                        if (!(__bfloat162float(xs[col]) > 0.f)) v.x = 0.f;
+                                        if (!(__bfloat162float(xs[col + 1]) > 0.f)) v.y = 0.f;
+                                    }
                                     *reinterpret_cast<__nv_bfloat162*>(dxb + b * D + col) = __floats2bfloat162_rn(v.x, v.y);
                                 } else {
                                     *reinterpret_cast<float2*>(dst + (i * D + col)) = v;     // 32-bit offset: F*D < 2^15
@@ -536,7 +540,7 @@ int interact_bwd_mma(const float* feat, int64_t fsb, int B, int F, int D, int it
         cudaFuncSetAttribute(interact_bwd_mma_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     }
     interact_bwd_mma_kernel<false, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
-        feat, fsb, D, B, F, D, itself, dout, dstride, dfeat, dfsb, nullptr, nullptr);
+        feat, fsb, D, B, F, D, itself, dout, dstride, dfeat, dfsb, nullptr, nullptr, 0);
     *rc = check_launch("interact_dot_bwd(mma)");
     return 1;
 }
@@ -575,7 +579,7 @@ int interact_fwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* 
 }
 
 int interact_bwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* x_bf16, int B, int F, int D, int itself,
-                       const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16,
+                       const void* dout_bf16, int64_t dstride, float* dfeat, int64_t dfsb, void* dx_bf16, int relu_x,
                        cudaStream_t st) {
     const int nz = tri_count_mma(F, itself);
     if (fst <= 0) fst = D;
@@ -603,11 +607,11 @@ int interact_bwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* 
     if (padded)
         interact_bwd_mma_kernel<true, true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
             feat, fsb, fst, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, (const __nv_bfloat16*)x_bf16,
-            (__nv_bfloat16*)dx_bf16);
+            (__nv_bfloat16*)dx_bf16, relu_x);
     else
         interact_bwd_mma_kernel<true, false><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
             feat, fsb, fst, B, F, D, itself, dout_bf16, dstride, dfeat, dfsb, (const __nv_bfloat16*)x_bf16,
-            (__nv_bfloat16*)dx_bf16);
+            (__nv_bfloat16*)dx_bf16, relu_x);
     return check_launch("interact_dot_bwd_mixed");
 }
 

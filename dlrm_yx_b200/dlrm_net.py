@@ -53,13 +53,17 @@ def _sort_on_side(emb, indices, offsets, B):
     return presorted
 
 
-def _update_on_side(emb, grad, indices, offsets, B, stride_b, stride_t, presorted, before=None, keep=()):
+def _update_on_side(emb, grad, indices, offsets, B, stride_b, stride_t, presorted, before=None, keep=(), after=None):
     """Runs `before()` (optional, e.g. the gradient exchange) and the fused update on the side stream, after
-    everything enqueued so far on the main stream; the main stream joins at the end of the backward pass.  `keep`:
-    tensors the side-stream work reads -- held until the join so their memory cannot be handed out earlier."""
+    everything enqueued so far on the main stream (or after the event `after`, recorded on it earlier); the main stream
+    joins at the end of the backward pass.  `keep`: tensors the side-stream work reads -- held until the join so their
+    memory cannot be handed out earlier."""
     main = torch.cuda.current_stream()
     side = _side_stream(grad.device)
-    side.wait_stream(main)
+    if after is not None and side != main:
+        side.wait_event(after)
+    else:
+        side.wait_stream(main)
     with torch.cuda.stream(side):
         if before is not None:
             grad = before()
@@ -77,10 +81,13 @@ def _update_on_side(emb, grad, indices, offsets, B, stride_b, stride_t, presorte
 
 
 def _flush_deferred_wgrads():
-    """The fused top tower's deferred weight-gradient kernel goes out here: behind the interaction backward, ahead of and
-    beside the sparse update (mlp.flush_deferred)."""
+    """The fused top tower's deferred weight-gradient kernel goes out here, behind the interaction backward
+    (mlp.flush_deferred).  Returns the event that marks the interaction backward's end on this stream: the sparse update
+    forks from THERE, so it runs beside the weight-gradient kernel, not behind it."""
     from . import mlp
+    done = torch.cuda.current_stream().record_event()
     mlp.flush_deferred()
+    return done
 
 
 class _BCELoss(torch.nn.BCELoss):
@@ -106,11 +113,11 @@ class _SparseArchLocal(torch.autograd.Function):
         B, D = x.shape
         T = emb.T
         feat = torch.empty((B, 1 + T, D), dtype=torch.float32, device=x.device)
+        ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None
         ops.embbag_forward(emb.table_set(), indices, offsets, B, out=feat[:, 1:, :],
                            stride_b=(1 + T) * D, stride_t=D)
         feat[:, 0, :].copy_(x)
         ctx.emb, ctx.itself = emb, bool(itself)
-        ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None
         ctx.save_for_backward(feat, indices, offsets)
         return ops.interact_dot_fwd(feat, ctx.itself)
 
@@ -129,16 +136,18 @@ class _SparseArchLocalMixed(torch.autograd.Function):
     K rounded up to 8); pooled embeddings, their gradients and the sparse update stay fp32."""
 
     @staticmethod
-    def forward(ctx, x, weights, emb, indices, offsets, itself, out_cols):
+    def forward(ctx, x, weights, emb, indices, offsets, itself, out_cols, relu_x):
         B, D = x.shape
         T = emb.T
+        ctx.relu_x = bool(relu_x)
         # slot 0 stays unused; rows are pitched for the interaction kernels' one-bulk-copy staging (D + 8 when D % 32 == 0)
         feat = ops.alloc_features(B, 1 + T, D, x.device)
+        # the sort goes out first: forked here, it runs beside the lookup instead of beside the top tower's GEMMs
+        ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None
         ops.embbag_forward(emb.table_set(), indices, offsets, B, out=feat[:, 1:, :],
                            stride_b=feat.stride(0), stride_t=feat.stride(1))
         x = x.contiguous()
         ctx.emb, ctx.itself = emb, bool(itself)
-        ctx.presorted = _sort_on_side(emb, indices, offsets, B) if ctx.needs_input_grad[0] else None
         ctx.save_for_backward(feat, x, indices, offsets)
         return ops.interact_dot_fwd_mixed(feat, x, out_cols, ctx.itself)
 
@@ -146,11 +155,11 @@ class _SparseArchLocalMixed(torch.autograd.Function):
     def backward(ctx, dR):
         feat, x, indices, offsets = ctx.saved_tensors
         B, F, D = feat.shape
-        dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
-        _flush_deferred_wgrads()
-        _update_on_side(ctx.emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, ctx.presorted, keep=(dfeat,))
+        dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself, relu_x=ctx.relu_x)
+        done = _flush_deferred_wgrads()
+        _update_on_side(ctx.emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, ctx.presorted, keep=(dfeat,), after=done)
         ctx.presorted = None
-        return dx, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None
 
 
 class _DistStep(object):
@@ -174,11 +183,11 @@ class _DistInteract(torch.autograd.Function):
     interaction kernels (x, R, dR, dx in bf16)."""
 
     @staticmethod
-    def forward(ctx, x, recv, step, itself, out_cols):
+    def forward(ctx, x, recv, step, itself, out_cols, relu_x=False):
         feat = step.feat
         if step.peer is None:
             step.info = ext_dist.complete_into(recv, feat, 1)
-        ctx.step, ctx.itself, ctx.mixed = step, bool(itself), out_cols > 0
+        ctx.step, ctx.itself, ctx.mixed, ctx.relu_x = step, bool(itself), out_cols > 0, bool(relu_x)
         if ctx.mixed:
             x = x.contiguous()
             ctx.save_for_backward(feat, x)
@@ -192,11 +201,11 @@ class _DistInteract(torch.autograd.Function):
         feat, x = ctx.saved_tensors
         step = ctx.step
         if ctx.mixed:
-            dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself)
-            _flush_deferred_wgrads()
+            dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself, relu_x=ctx.relu_x)
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
+        done = _flush_deferred_wgrads()
         peer, lb = step.peer, step.lb
         F, D = dfeat.shape[1], dfeat.shape[2]
         T_s = F - 1 - (step.rep.T if step.rep is not None else 0)
@@ -215,9 +224,9 @@ class _DistInteract(torch.autograd.Function):
                                         stride_b=dfeat.stride(0), stride_t=dfeat.stride(1), presorted=step.rep_sorted)
             return None
         if peer is not None or step.rep is not None:
-            _update_on_side(None, dfeat, None, None, 0, 0, 0, None, before=sparse_updates, keep=(dfeat, step))
+            _update_on_side(None, dfeat, None, None, 0, 0, 0, None, before=sparse_updates, keep=(dfeat, step), after=done)
         step.presorted = step.rep_sorted = None
-        return dx, send, None, None, None
+        return dx, send, None, None, None, None
 
 
 class DLRM_Net(nn.Module):
@@ -441,6 +450,17 @@ class DLRM_Net(nn.Module):
     def _batched_module(self):
         return self.emb_l[0] if isinstance(self.emb_l, nn.ModuleList) else self.emb_l
 
+    def _take_over_bottom_relu(self):
+        """Call right after the fused bottom tower's forward: True if the bf16-facing interaction backward may gate dx by
+        (x > 0), i.e. apply the ReLU backward of the tower's last layer (x is that layer's output); the tower's backward
+        then skips its ReLU-backward pass and takes the bias gradient from its weight-gradient kernel."""
+        bot = self.bot_l
+        last = getattr(bot, "_last_relu", None)
+        if getattr(bot, "gemm", None) != "tc" or last is None or last[0] != len(bot.layers) - 1 or not torch.is_grad_enabled():
+            return False
+        last[1]["pre_masked"] = "nobias"
+        return True
+
     def sequential_forward(self, dense_x, lS_o, lS_i):
         if not isinstance(self.emb_l, nn.ModuleList):
             self.emb_l = nn.ModuleList([self.emb_l])
@@ -451,7 +471,8 @@ class DLRM_Net(nn.Module):
                 emb = self._batched_module()
                 if getattr(self, "_mixed", False):
                     z = _SparseArchLocalMixed.apply(x, emb.embedding_weights, emb, lS_i, lS_o,
-                                                    self.arch_interaction_itself, self.top_l.layers[0].K_pad)
+                                                    self.arch_interaction_itself, self.top_l.layers[0].K_pad,
+                                                    self._take_over_bottom_relu())
                 else:
                     z = _SparseArchLocal.apply(x, emb.embedding_weights, emb, lS_i, lS_o,
                                                self.arch_interaction_itself)
@@ -533,7 +554,8 @@ class DLRM_Net(nn.Module):
         cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
         with record_function("module::forward_pass::interaction"):
             main.wait_event(arrived)
-            z = _DistInteract.apply(x, None, step, self.arch_interaction_itself, cols)
+            z = _DistInteract.apply(x, None, step, self.arch_interaction_itself, cols,
+                                    cols > 0 and self._take_over_bottom_relu())
         with record_function("module::forward_pass::top_mlp"):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
@@ -547,7 +569,12 @@ class DLRM_Net(nn.Module):
             return self._peer_forward(dense_x, lS_o, lS_i)
         (off, idx), (roff, ridx) = self._split_inputs(lS_o, lS_i)
         with record_function("module::forward_pass::embedding_lookup"):
-            if self.batched_emb:
+            if self.batched_emb and self._batched_module().T == 0:
+                # a rank without sharded tables (fewer of them than ranks, the rest replicated) still takes part in the
+                # exchange, with an empty [B, 0, D] block that requires grad so that its backward half runs here too
+                ly = [torch.zeros((dense_x.shape[0] * ext_dist.my_size, 0, int(self.m_spa)), device=dense_x.device,
+                                  requires_grad=True)]
+            elif self.batched_emb:
                 ly = self.apply_emb_batched([off], [idx])
             else:
                 ly = self.apply_emb(off, idx)
@@ -571,7 +598,7 @@ class DLRM_Net(nn.Module):
                 if self.emb_rep is not None:
                     self._replicated_lookup(step, step.feat, T_s, roff, ridx)
                 z = _DistInteract.apply(x, recv, step, self.arch_interaction_itself,
-                                        self.top_l.layers[0].K_pad if mixed else 0)
+                                        self.top_l.layers[0].K_pad if mixed else 0, mixed and self._take_over_bottom_relu())
             else:
                 z = self.interact_features(x, ly)
         with record_function("module::forward_pass::top_mlp"):

@@ -30,7 +30,11 @@ class GraphedTrainStep(object):
         cur.wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph, pool=pool):
+        # The step's main chain is captured on a HIGH-priority stream (kernel nodes inherit it); the sparse update forks onto a
+        # default-priority side stream.  A CTA of a running grid is never preempted, but whenever a slot frees up the
+        # scheduler serves the higher priority first: without this the bottom tower's backward GEMMs (one 226 KB CTA per SM)
+        # starved behind the update's large grid of small CTAs until that grid was exhausted.
+        with torch.cuda.graph(self.graph, pool=pool, stream=torch.cuda.Stream(priority=-1)):
             self.loss = step_fn(*self.static)
 
     def prefetch(self, *host_inputs):

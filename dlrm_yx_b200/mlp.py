@@ -87,36 +87,19 @@ class _LinearAct(torch.autograd.Function):
 # ---- deferred weight-gradient launches ------------------------------------------------------------------------------
 # The top tower's backward runs first; launched in place, its wgrad kernel (tensor-bound, ~0.15 ms at the Terabyte shape)
 # sits between the tower's dgrads and the interaction backward with nothing to overlap.  Deferred, it is launched right
-# after the interaction backward on a HIGH-PRIORITY stream: one persistent CTA per SM (200 KB of shared memory, 15 K
-# registers) next to the sparse update of the side stream (HBM-bound, 16 bytes of shared memory per CTA), which keeps
-# two of its CTAs resident beside it.  Priority matters: a CTA of an already running grid is never preempted, so the
-# wgrad CTAs must be placed before the update's grid has filled the register files.
+# after the interaction backward, on the same stream, while the sparse update forks onto the side stream from the point
+# BEFORE it: one persistent wgrad CTA per SM (200 KB of shared memory, 15 K registers) next to two or three CTAs of the
+# update (HBM-bound, 16 bytes of shared memory each).  Under CUDA-graph capture the main chain has the higher stream
+# priority (graph.py), so the GEMMs that follow get SM slots as the update's short-lived CTAs retire instead of waiting
+# for its whole grid to be dispatched.  (Measured alternatives, Terabyte shape: wgrad on a third, high-priority stream
+# with equal-priority main / side streams 1.196 ms -- the bottom tower's GEMMs starve behind the update's grid; the same
+# with a high-priority main stream 1.240 ms -- the update starves while two high-priority grids share the SMs.)
 _DEFERRED = []
-_HP = {}
 
 
 def flush_deferred():
-    if not _DEFERRED:
-        return
-    from . import dlrm_net
-    main = torch.cuda.current_stream()
-    if dlrm_net.OVERLAP_STREAMS:
-        hp = _HP.get(main.device)
-        if hp is None:
-            hp = _HP[main.device] = torch.cuda.Stream(device=main.device, priority=-1)
-        hp.wait_stream(main)
-        with torch.cuda.stream(hp):
-            for launch in _DEFERRED:
-                launch()
-        held = list(_DEFERRED)        # the closures own the operands: alive until the main stream has joined
-
-        def join():
-            torch.cuda.current_stream().wait_stream(hp)
-            held.clear()
-        torch.autograd.Variable._execution_engine.queue_callback(join)
-    else:
-        for launch in _DEFERRED:
-            launch()
+    for launch in _DEFERRED:
+        launch()
     _DEFERRED.clear()
 
 
@@ -153,7 +136,9 @@ class _Tower(torch.autograd.Function):
         n = len(layers)
         dyb = (dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)).contiguous()
         dzs, dbs = [None] * n, [L.gb for L in layers]
-        if ctx.flag["pre_masked"]:
+        if ctx.flag["pre_masked"] == "nobias":
+            dzs[-1] = dyb              # the consumer (interaction backward) applied the last ReLU mask; db comes from the wgrad
+        elif ctx.flag["pre_masked"]:
             dzs[-1] = dyb              # the head's backward applied the last ReLU mask and wrote that bias gradient
             dbs[-1] = None
         else:
@@ -288,7 +273,7 @@ class FusedMLP(nn.Module):
         return self.master.data[L.b_off:L.b_off + L.N]
 
     def _wgrad_workspace(self, i0, i1, M):
-        key = (i0, i1, M, torch.cuda.current_stream().cuda_stream)
+        key = (i0, i1, M)
         ws = self._ws.get(key)
         if ws is None:
             ls = self.layers[i0:i1]

@@ -326,8 +326,8 @@ def interact_dot_fwd_mixed(feat, x_bf16, out_cols, itself=False):
     return out
 
 
-def interact_dot_bwd_mixed(feat, x_bf16, dout, itself=False):
-    """-> (dfeat fp32 [B, F, D] with features 1.. written, dx bf16 [B, D])."""
+def interact_dot_bwd_mixed(feat, x_bf16, dout, itself=False, relu_x=False):
+    """-> (dfeat fp32 [B, F, D] with features 1.. written, dx bf16 [B, D]); relu_x: dx is gated by (x > 0)."""
     _need_cuda(feat, x_bf16, dout)
     B, F, D = feat.shape
     if dout.dtype != torch.bfloat16 or dout.stride(1) != 1:
@@ -337,7 +337,7 @@ def interact_dot_bwd_mixed(feat, x_bf16, dout, itself=False):
     with _timed("interact_bwd"):
         rc = _lib.load().dlrmx_interact_dot_bwd_mixed(feat.data_ptr(), feat.stride(0), feat.stride(1), x_bf16.data_ptr(), B, F, D,
                                                       int(itself), dout.data_ptr(), dout.stride(0), dfeat.data_ptr(),
-                                                      dfeat.stride(0), dx.data_ptr(), _stream())
+                                                      dfeat.stride(0), dx.data_ptr(), int(relu_x), _stream())
         _lib.check(rc, "dlrmx_interact_dot_bwd_mixed")
     return dfeat, dx
 
@@ -471,7 +471,7 @@ def gemm_wgrad_workspace(Ns, Ks, M, device):
     """Workspace for gemm_wgrad_bf16 on layers of these shapes (split-K partial tiles)."""
     n = len(Ns)
     nbytes = _lib.load().dlrmx_gemm_wgrad_workspace_bytes(n, _int_array(Ns), _int_array(Ks), int(M))
-    return torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
 
 def gemm_wgrad_bf16(dzs, xs, dws, dbs, workspace):

@@ -189,7 +189,9 @@ int dlrmx_interact_dot_bwd(const float* feat, int64_t feat_stride_b, int B, int 
  *   out_bf16 [B, out_stride] bf16 = [x | tril], columns D+nz .. out_stride-1 are written as zeros (out_stride = the top
  *   MLP's K rounded up to 8, so the GEMM reads it without a pad/cast pass);
  *   backward reads dout_bf16 [B, dout_stride] bf16 (dout_stride % 8 == 0), writes the pooled-embedding gradients
- *   dfeat[:, 1:, :] in fp32 (feature 0 of dfeat is left untouched) and the gradient of x as dx_bf16 [B, D].
+ *   dfeat[:, 1:, :] in fp32 (feature 0 of dfeat is left untouched) and the gradient of x as dx_bf16 [B, D]; with relu_x != 0
+ *   dx is also gated by (x > 0): x is then the output of a Linear + ReLU layer (the bottom tower's last) and dx leaves as
+ *   that layer's pre-activation gradient, no separate ReLU-backward pass.
  *   feat_stride_f = row pitch of the features inside a sample, in floats: D (contiguous [F, D] blocks; 0 means D), or
  *   D + 8 when D % 32 == 0 -- the interaction input then has the row pitch of the kernels' shared-memory tile (the
  *   lookup writes pooled rows with stride_t = D + 8: rows stay 32-byte aligned, so its stores stay full sectors), and a
@@ -200,7 +202,7 @@ int dlrmx_interact_dot_fwd_mixed(const float* feat, int64_t feat_stride_b, int64
                                  int itself, void* out_bf16, int64_t out_stride, dlrmx_stream_t stream);
 int dlrmx_interact_dot_bwd_mixed(const float* feat, int64_t feat_stride_b, int64_t feat_stride_f, const void* x_bf16, int B, int F, int D,
                                  int itself, const void* dout_bf16, int64_t dout_stride, float* dfeat,
-                                 int64_t dfeat_stride_b, void* dx_bf16, dlrmx_stream_t stream);
+                                 int64_t dfeat_stride_b, void* dx_bf16, int relu_x, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * MLP towers (create_mlp / apply_mlp, dlrm_s_pytorch.py:227-265, 518-524): fused passes around the

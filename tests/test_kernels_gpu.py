@@ -410,6 +410,13 @@ def test_interaction_mixed_bf16_facing(F, D, itself, staging, B, request):
     e_emb = np.abs(dfeat[:, 1:, :].cpu().numpy() - rdemb)
     assert np.all(e_emb <= 2.0 ** -10 * mdemb + 1e-6), e_emb.max()
     assert dx.dtype == bf
+    # relu_x: the same dx gated by (x > 0) -- the ReLU backward of the layer that produced x -- and nothing else changes
+    dfeat_r, dx_r = ops.interact_dot_bwd_mixed(df, x_b, dR_b, itself, relu_x=True)
+    assert torch.equal(dfeat_r[:, 1:, :], dfeat[:, 1:, :])
+    gate = x_b.float() > 0
+    assert bool(gate.any()) and bool((~gate).any())
+    assert torch.equal(dx_r.view(torch.int16)[gate], dx.view(torch.int16)[gate])
+    assert float(dx_r.float()[~gate].abs().max()) == 0.0
     e_dx = np.abs(dx.float().cpu().numpy() - rdx)
     assert np.all(e_dx <= 2.0 ** -8 * np.abs(rdx) + 2.0 ** -10 * mdx + 1e-6), e_dx.max()
 
