@@ -44,6 +44,19 @@ def _side_stream(device):
     return s
 
 
+_COMM = {}
+
+
+def _comm_stream(device):
+    """Stream of the collectives that run beside compute (gradient all-reduces)."""
+    if not OVERLAP_STREAMS:
+        return torch.cuda.current_stream()
+    s = _COMM.get(device)
+    if s is None:
+        s = _COMM[device] = torch.cuda.Stream(device=device)
+    return s
+
+
 def _sort_on_side(emb, indices, offsets, B):
     main = torch.cuda.current_stream()
     side = _side_stream(indices.device)
@@ -205,7 +218,7 @@ class _DistInteract(torch.autograd.Function):
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
-        done = _flush_deferred_wgrads()
+        done = torch.cuda.current_stream().record_event()        # the interaction backward's end: the sparse updates fork here
         peer, lb = step.peer, step.lb
         F, D = dfeat.shape[1], dfeat.shape[2]
         T_s = F - 1 - (step.rep.T if step.rep is not None else 0)
@@ -214,17 +227,28 @@ class _DistInteract(torch.autograd.Function):
             send = ext_dist.start_backward_from(step.info, dfeat, 1)      # lookup's own backward runs the fused update
 
         def sparse_updates():                 # on the side stream
+            cur = torch.cuda.current_stream()
+            comm = _comm_stream(dfeat.device)
+            if step.rep is not None:
+                # replicated tables first: their gradient all-reduce (62 MB at the Terabyte shape, ~0.26 ms on 8 GPUs) and
+                # row update go to the communication stream and run beside the push / update of the sharded tables
+                step.rep.fused_backward(dfeat[:, 1 + T_s:, :], step.rep_indices, step.rep_offsets, lb,
+                                        stride_b=dfeat.stride(0), stride_t=dfeat.stride(1), presorted=step.rep_sorted,
+                                        comm_stream=comm)
             if peer is not None:
                 grad = peer.push_grad(dfeat)
                 if step.emb.T > 0:
                     step.emb.fused_backward(grad, step.indices, step.offsets, peer.W * lb, stride_b=grad.stride(0),
                                             stride_t=grad.stride(1), presorted=step.presorted)
-            if step.rep is not None:
-                step.rep.fused_backward(dfeat[:, 1 + T_s:, :], step.rep_indices, step.rep_offsets, lb,
-                                        stride_b=dfeat.stride(0), stride_t=dfeat.stride(1), presorted=step.rep_sorted)
+            if comm != cur:
+                cur.wait_stream(comm)         # whoever joins the side stream has joined the communication stream too
             return None
         if peer is not None or step.rep is not None:
             _update_on_side(None, dfeat, None, None, 0, 0, 0, None, before=sparse_updates, keep=(dfeat, step), after=done)
+        # the deferred weight-gradient kernel of the top tower (and the all-reduce of its gradients) goes out AFTER the sparse
+        # updates have been issued: collectives of one process group run in issue order, and the all-reduce of the replicated
+        # tables' gradients must not queue behind one that waits for the weight-gradient kernel
+        _flush_deferred_wgrads()
         step.presorted = step.rep_sorted = None
         return dx, send, None, None, None, None
 
@@ -396,6 +420,8 @@ class DLRM_Net(nn.Module):
         # the top tower's backward comes first: its weight gradients wait for the end of the pass, where they overlap the
         # sparse update on the side stream instead of delaying the interaction backward
         self.top_l.defer_wgrad = bool(self.fuse_sparse_arch and gemm == "tc")
+        if gemm == "tc" and ext_dist.my_size > 1:      # step_mlps() averages over the replicas: start that in the backward
+            self.bot_l.dp_world = self.top_l.dp_world = ext_dist.my_size
         return self
 
     def step_mlps(self):
@@ -543,14 +569,15 @@ class DLRM_Net(nn.Module):
         with record_function("module::forward_pass::embedding_lookup"):
             with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sorts) beside the bottom tower
                 peer.lookup_and_scatter(emb.table_set(), idx, off)
-                if self.emb_rep is not None:
-                    self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
                 peer.wait_rows()
                 arrived = side.record_event()
                 if torch.is_grad_enabled() and emb.T > 0:
                     step.presorted = emb.sort_lookups(idx, off, peer.W * lb)
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
+        if self.emb_rep is not None:            # local rows of the replicated tables: HBM work beside the NVLink-bound scatter
+            with record_function("module::forward_pass::embedding_lookup"):
+                self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
         cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
         with record_function("module::forward_pass::interaction"):
             main.wait_event(arrived)

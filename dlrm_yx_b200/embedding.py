@@ -195,7 +195,10 @@ class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
             if self.row_momentum is not None:
                 dist.broadcast(self.row_momentum, src)
 
-    def fused_backward(self, grad_out, indices, offsets, B, stride_b=None, stride_t=None, presorted=None):
+    def fused_backward(self, grad_out, indices, offsets, B, stride_b=None, stride_t=None, presorted=None, comm_stream=None):
+        """comm_stream: the all-reduce of the summed gradients and the row update that follows are enqueued THERE (after
+        the accumulation on the current stream), so that whatever the caller enqueues next on the current stream -- the
+        gradient push and the update of the sharded tables -- runs beside them; the caller joins comm_stream."""
         import torch.distributed as dist
         if stride_b is None:
             if grad_out.stride(2) != 1 or grad_out.stride(1) % 4 or grad_out.stride(0) % 4:
@@ -205,12 +208,18 @@ class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
         skey, sbag = presorted if presorted is not None else ops.bwd_sort(self.table_set(), indices, offsets, B)
         # SGD with lr = -1 on the zeroed buffer: grad_sum[row] = sum of the local gradient rows, in sorted (stable) order
         ops.bwd_update(gts, _lib.OPT_SGD, grad_out, stride_b, stride_t, B, skey, sbag, -1.0, 0.0)
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(self.grad_sum)
-        kind = _lib.OPT_RWSADAGRAD if self.optimizer in _ROWWISE else _lib.OPT_SGD
-        total = sum(self.rows)
-        ops.dense_rows_update(kind, self.embedding_weights.data.view(total, self.D), self.row_momentum,
-                              self.grad_sum.view(total, self.D), self.current_lr(), self.eps)
+        cur = torch.cuda.current_stream()
+        if comm_stream is None or comm_stream == cur:
+            comm_stream = cur
+        else:
+            comm_stream.wait_stream(cur)
+        with torch.cuda.stream(comm_stream):
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                dist.all_reduce(self.grad_sum)
+            kind = _lib.OPT_RWSADAGRAD if self.optimizer in _ROWWISE else _lib.OPT_SGD
+            total = sum(self.rows)
+            ops.dense_rows_update(kind, self.embedding_weights.data.view(total, self.D), self.row_momentum,
+                                  self.grad_sum.view(total, self.D), self.current_lr(), self.eps)
         self.step_count += 1
 
 

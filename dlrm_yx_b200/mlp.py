@@ -152,13 +152,17 @@ class _Tower(torch.autograd.Function):
             if ctx.in_cols != layers[0].K_pad:       # the caller's input was unpadded
                 dx = dx[:, :layers[0].K]
         xs, dws, ws = list(acts[:-1]), [L.gW for L in layers], mlp._wgrad_workspace(i0, i1, dyb.shape[0])
+        def launch():
+            ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws)
+            if i0 == 0:                # the tower's first layers come last in the backward: its gradients are complete
+                mlp._start_allreduce()
         if mlp.defer_wgrad:
             # the weight gradients are needed only by step(): their launch waits for flush_deferred() -- called by the sparse
             # arch right after the interaction backward, or at the end of the pass (see there)
-            _DEFERRED.append(lambda: ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws))
+            _DEFERRED.append(launch)
             torch.autograd.Variable._execution_engine.queue_callback(flush_deferred)
         else:
-            ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws)
+            launch()
         return dx, None, None, None, None
 
 
@@ -205,6 +209,8 @@ class FusedMLP(nn.Module):
             raise ValueError("gemm must be 'tc' (tcgen05 kernels) or 'cublas' (the library comparator)")
         self.gemm = gemm
         self.defer_wgrad = False    # True: the wgrad launch waits for flush_deferred() (see there)
+        self.dp_world = 1           # > 1: data-parallel replicas; the backward pass starts the gradient all-reduce itself
+        self._ar_stream = None
         self._ws = {}
         mods = list(sequential)
         if len(mods) % 2 or not all(isinstance(m, nn.Linear) for m in mods[0::2]):
@@ -301,11 +307,31 @@ class FusedMLP(nn.Module):
             i += 1
         return h if (h.dtype == torch.float32 or self.out_bf16) else h.float()
 
+    def _start_allreduce(self):
+        """Data-parallel replicas (dp_world > 1): the all-reduce of the flat gradient buffer starts as soon as the tower's
+        backward has written it, on a communication stream beside the rest of the backward pass; step() joins it."""
+        if self.dp_world <= 1:
+            return
+        from . import dlrm_net
+        cur = torch.cuda.current_stream()
+        comm = dlrm_net._comm_stream(self.grad.device)
+        if comm != cur:
+            comm.wait_stream(cur)
+        with torch.cuda.stream(comm):
+            dist.all_reduce(self.grad)
+        self._ar_stream = comm
+
     @torch.no_grad()
     def step(self, world_size=1):
         scale = 1.0
         if world_size > 1:
-            dist.all_reduce(self.grad)
+            if self._ar_stream is not None:   # started by the backward pass
+                if self.dp_world != world_size:
+                    raise _lib.DlrmxError("FusedMLP.step: dp_world (%d) != world_size (%d)" % (self.dp_world, world_size))
+                torch.cuda.current_stream().wait_stream(self._ar_stream)
+                self._ar_stream = None
+            else:
+                dist.all_reduce(self.grad)
             scale = 1.0 / world_size          # DDP averages the replicas' gradients
         ops.dense_opt(self.mode, self.master.data, self.acc if self.mode == 1 else None, self.grad, self.shadow,
                       self.lr, self.eps, scale)

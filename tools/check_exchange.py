@@ -215,8 +215,8 @@ def main():
 
     hooked = dlrm_net._DistInteract.forward
 
-    def spy(ctx, x, recv, step, itself, out_cols):          # remember the interaction input of the last forward
-        r = hooked(ctx, x, recv, step, itself, out_cols)
+    def spy(ctx, x, recv, step, itself, out_cols, relu_x=False):     # remember the interaction input of the last forward
+        r = hooked(ctx, x, recv, step, itself, out_cols, relu_x)
         step.model._last_feat = step.feat
         return r
     dlrm_net._DistInteract.forward = staticmethod(spy)
