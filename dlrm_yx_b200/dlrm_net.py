@@ -240,7 +240,7 @@ class _DistInteract(torch.autograd.Function):
                 if step.emb.T > 0:
                     step.emb.fused_backward(grad, step.indices, step.offsets, peer.W * lb, stride_b=grad.stride(0),
                                             stride_t=grad.stride(1), presorted=step.presorted)
-            if comm != cur:
+            if step.rep is not None and comm != cur:
                 cur.wait_stream(comm)         # whoever joins the side stream has joined the communication stream too
             return None
         if peer is not None or step.rep is not None:
