@@ -495,7 +495,8 @@ def run_ours(args):
             ms_prof, prof_mode = t_rep, "graph"
             del gprof
         except Exception as ex:                      # external events unsupported: fall back to the eager pass
-            sys.stderr.write("bench: graph-event profiling failed (%r), using the eager pass\n" % (ex,))
+            import traceback
+            sys.stderr.write("bench: graph-event profiling failed (%r), using the eager pass\n%s\n" % (ex, traceback.format_exc()))
             ops.PROFILE = None
             prof = None
     if prof is None:

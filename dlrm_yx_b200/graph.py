@@ -12,6 +12,17 @@ training steps on the example batch.
 import torch
 
 
+_CAPTURE = {}
+
+
+def _capture_stream():
+    dev = torch.cuda.current_device()
+    s = _CAPTURE.get(dev)
+    if s is None:
+        s = _CAPTURE[dev] = torch.cuda.Stream(priority=-1)
+    return s
+
+
 class GraphedTrainStep(object):
     def __init__(self, step_fn, example_inputs, warmup=3, pool=None):
         """step_fn(*tensors) -> loss tensor, a full training step using only the tensors it is given (plus module
@@ -32,9 +43,11 @@ class GraphedTrainStep(object):
         self.graph = torch.cuda.CUDAGraph()
         # The step's main chain is captured on a HIGH-priority stream (kernel nodes inherit it); the sparse update forks onto a
         # default-priority side stream.  A CTA of a running grid is never preempted, but whenever a slot frees up the
-        # scheduler serves the higher priority first: without this the bottom tower's backward GEMMs (one 226 KB CTA per SM)
-        # starved behind the update's large grid of small CTAs until that grid was exhausted.
-        with torch.cuda.graph(self.graph, pool=pool, stream=torch.cuda.Stream(priority=-1)):
+        # scheduler serves the higher priority first: the tensor-core GEMMs of the main chain (one 226 KB CTA per SM) get SM
+        # slots as the update's short-lived CTAs retire instead of waiting for its whole grid to be dispatched.  One stream
+        # per device for every capture of the process (as torch's own default capture stream): autograd remembers the stream
+        # a leaf first accumulated its gradient on, and a later capture on another stream would depend on that one.
+        with torch.cuda.graph(self.graph, pool=pool, stream=_capture_stream()):
             self.loss = step_fn(*self.static)
 
     def prefetch(self, *host_inputs):

@@ -310,9 +310,9 @@ class FusedMLP(nn.Module):
     def _start_allreduce(self):
         """Data-parallel replicas (dp_world > 1): the all-reduce of the flat gradient buffer starts as soon as the tower's
         backward has written it, on a communication stream beside the rest of the backward pass; step() joins it."""
-        if self.dp_world <= 1:
-            return
         from . import dlrm_net
+        if self.dp_world <= 1 or not dlrm_net.OVERLAP_STREAMS:       # single-stream mode: step() issues it, as before
+            return
         cur = torch.cuda.current_stream()
         comm = dlrm_net._comm_stream(self.grad.device)
         if comm != cur:
