@@ -218,7 +218,10 @@ class _DistInteract(torch.autograd.Function):
         else:
             dfeat = ops.interact_dot_bwd(feat, dR.contiguous(), ctx.itself)
             dx = dfeat[:, 0, :]
-        done = torch.cuda.current_stream().record_event()        # the interaction backward's end: the sparse updates fork here
+        # the interaction backward's end: the sparse updates fork from here; the deferred weight-gradient kernel of the top
+        # tower and the all-reduce of its gradients are issued first -- collectives of one process group run in issue order,
+        # and this one (10 MB, ready when the replicated tables' sums are) must not wait for that one (the largest)
+        done = _flush_deferred_wgrads()
         peer, lb = step.peer, step.lb
         F, D = dfeat.shape[1], dfeat.shape[2]
         T_s = F - 1 - (step.rep.T if step.rep is not None else 0)
@@ -245,10 +248,6 @@ class _DistInteract(torch.autograd.Function):
             return None
         if peer is not None or step.rep is not None:
             _update_on_side(None, dfeat, None, None, 0, 0, 0, None, before=sparse_updates, keep=(dfeat, step), after=done)
-        # the deferred weight-gradient kernel of the top tower (and the all-reduce of its gradients) goes out AFTER the sparse
-        # updates have been issued: collectives of one process group run in issue order, and the all-reduce of the replicated
-        # tables' gradients must not queue behind one that waits for the weight-gradient kernel
-        _flush_deferred_wgrads()
         step.presorted = step.rep_sorted = None
         return dx, send, None, None, None, None
 
@@ -422,6 +421,8 @@ class DLRM_Net(nn.Module):
         self.top_l.defer_wgrad = bool(self.fuse_sparse_arch and gemm == "tc")
         if gemm == "tc" and ext_dist.my_size > 1:      # step_mlps() averages over the replicas: start that in the backward
             self.bot_l.dp_world = self.top_l.dp_world = ext_dist.my_size
+        if self.emb_rep is not None and self._mixed:
+            self.emb_rep.wire_bf16 = True              # mixed-precision mode: the replicated tables' gradients cross NVLink as bf16
         return self
 
     def step_mlps(self):
@@ -568,7 +569,7 @@ class DLRM_Net(nn.Module):
         side.wait_stream(main)
         with record_function("module::forward_pass::embedding_lookup"):
             with torch.cuda.stream(side):       # lookup + NVLink scatter (and the backward's sorts) beside the bottom tower
-                peer.lookup_and_scatter(emb.table_set(), idx, off)
+                peer.lookup_and_scatter(emb.table_set() if emb.T > 0 else None, idx, off)   # a rank may hold no sharded table
                 peer.wait_rows()
                 arrived = side.record_event()
                 if torch.is_grad_enabled() and emb.T > 0:

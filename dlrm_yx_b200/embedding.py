@@ -177,6 +177,7 @@ class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
         super().__init__(*args, **kwargs)
         self.register_buffer("grad_sum", torch.zeros_like(self.embedding_weights.data), persistent=False)
         self._gts = None
+        self.wire_bf16 = False      # True: the gradient all-reduce moves bf16 (set with the bf16 towers, DLRM_Net.fuse_mlps)
 
     def _grad_table_set(self):
         if self._gts is None or self._gts_key != self.grad_sum.data_ptr():
@@ -215,7 +216,15 @@ class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
             comm_stream.wait_stream(cur)
         with torch.cuda.stream(comm_stream):
             if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-                dist.all_reduce(self.grad_sum)
+                if self.wire_bf16:
+                    # bf16 on the wire (the towers' mixed-precision mode only): every rank's partial sums are rounded to
+                    # bf16 before they are added, the sum is widened back -- half the NVLink bytes of the one collective
+                    # that is as large as the tables themselves; replicas stay bit-identical (NCCL's result is)
+                    wire = self.grad_sum.to(torch.bfloat16)
+                    dist.all_reduce(wire)
+                    self.grad_sum.copy_(wire)
+                else:
+                    dist.all_reduce(self.grad_sum)
             kind = _lib.OPT_RWSADAGRAD if self.optimizer in _ROWWISE else _lib.OPT_SGD
             total = sum(self.rows)
             ops.dense_rows_update(kind, self.embedding_weights.data.view(total, self.D), self.row_momentum,
