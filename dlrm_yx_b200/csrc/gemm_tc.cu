@@ -1,10 +1,12 @@
-// MLP-tower GEMMs on the 5th-generation tensor cores: tcgen05.mma with TMEM accumulators, operands staged by TMA.  sm_100a.
+// MLP-tower GEMMs on the 5th-generation tensor cores: tcgen05.mma.cta_group::2 (CTA pairs, M = 256 per MMA) with TMEM
+// accumulators, operands staged by TMA.  sm_100a.
 //
 // Replaces the cuBLAS GEMMs behind create_mlp / apply_mlp (dlrm_s_pytorch.py:227-265, 518-524: nn.Linear + ReLU stacks)
 // and their autograd backward, for bf16 operands with fp32 accumulation:
-//   forward   Y  = relu(X W^t + b)          gemm_bf16_kernel<BN, /*B_MN=*/false>, epilogue BIAS_RELU -> bf16
-//   dgrad     dX = (dZ W) * (Y_prev > 0)    gemm_bf16_kernel<BN, /*B_MN=*/true>: W [N, K] row-major is the MN-major B operand
-//                                           (no transposed weight copy), epilogue applies the PREVIOUS layer's ReLU mask, so
+//   forward   Y  = relu(X W^t + b)          gemm_pair_kernel<BN, /*B_MN=*/false>, epilogue BIAS_RELU -> bf16 (+ 1 gate bit per
+//                                           element for the backward)
+//   dgrad     dX = (dZ W) * (Y_prev > 0)    gemm_pair_kernel<BN, /*B_MN=*/true>: W [N, K] row-major is the MN-major B operand
+//                                           (no transposed weight copy), epilogue applies the PREVIOUS layer's ReLU gates, so
 //                                           its result is that layer's dZ -- no separate ReLU-backward pass
 //   wgrad     dW = dZ^t X,  db = dZ^t 1     wgrad_splitk_kernel: ALL layers of a tower in ONE launch.  Both operands are
 //                                           MN-major (the contraction runs over the batch), tiles [256 n] x [<=256 k]; the
@@ -14,10 +16,12 @@
 //                                           wgrad_reduce_kernel sums in chunk order (deterministic, ONE reduce launch
 //                                           for the whole tower, element-parallel over all SMs); the bias gradient
 //                                           rides along as one extra N = 16 MMA against a tile of ones.
-// Kernel shape (both): one CTA per SM, persistent; warp 0 = TMA producer (cp.async.bulk.tensor into 128-byte-swizzled
-// stages, mbarrier expect_tx), warp 1 = MMA issuer (one elected lane issues tcgen05.mma, tcgen05.commit releases stages),
-// warps 2-5 = epilogue (tcgen05.ld 32x32b from the warp's TMEM lane quarter -> registers -> global).  The forward / dgrad
-// kernel double-buffers the accumulator in TMEM (2 x BN columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+// Kernel shape (both): persistent, one CTA per SM, two CTAs of a cluster (the SMs of a TPC) per tile; warp 0 = TMA producer
+// (cp.async.bulk.tensor.cta_group::2 into 128-byte-swizzled stages, bytes counted on the leader's mbarrier), warp 1 of the
+// leader = MMA issuer (one elected lane issues tcgen05.mma, multicast tcgen05.commit releases the stages of both CTAs), the
+// other warps = epilogue (tcgen05.ld 32x32b from the warp's TMEM lane quarter -> registers -> shared memory -> TMA store, or
+// fp32 rows straight to global in the wgrad).  The forward / dgrad kernel double-buffers the accumulator in TMEM (2 x BN
+// columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -187,203 +191,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // forward / dgrad GEMM:  C[M, N] (bf16) = epilogue( A[M, K] . op(B) )
 //   B_MN = false: B is [N, K] row-major (contraction contiguous)  -> y = x W^t
 //   B_MN = true : B is [K, N] row-major (output dim contiguous)   -> dx = dz W with W [N_layer, K_layer] as stored
+// (Round 2's first version ran one CTA per SM with M = 128 MMAs: 48 KB from L2 per 128 x 256 x 64 block of MMA work put it
+// on the ~12 TB/s L2 -> SM limit, 1.02 PFLOP/s at 1024 x 1024 against cuBLAS' 1.18, and its 16-byte row stores made the
+// epilogue the bottleneck of every layer with K <= 512.  Replaced by the CTA-pair kernel below; numbers in DESIGN.md.)
 // ------------------------------------------------------------------------------------------------------------------
-enum { EPI_NONE = 0, EPI_BIAS_RELU = 1, EPI_RELU_MASK = 2, EPI_BIAS = 3 };
-
-struct GemmParams {
-    int M, N, K;
-    __nv_bfloat16* C;
-    int64_t ldc;
-    const float* bias;              // [N]            (EPI_BIAS_RELU / EPI_BIAS)
-    const __nv_bfloat16* mask;      // [M, N] bf16: C = acc where mask > 0, else 0   (EPI_RELU_MASK)
-    int64_t ld_mask;
-    int epilogue;
-};
-
-template <int BN>
-struct GemmSmem {
-    static constexpr int kStages = (BN == 256) ? 4 : 6;
-    static constexpr uint32_t kABytes = BM * BK * 2, kBBytes = BN * BK * 2;
-    static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-    static constexpr uint32_t kBarOff = kStages * kStageBytes;
-    static constexpr uint32_t kBytes = kBarOff + 256 + 1024;      // barriers + the alignment slack of the dynamic window
-};
-
-template <int BN, bool B_MN>
-__global__ void __launch_bounds__(kThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const GemmParams P) {
-    using S = GemmSmem<BN>;
-    constexpr int STAGES = S::kStages;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
-    uint64_t* empty = full + STAGES;
-    uint64_t* acc_full = empty + STAGES;
-    uint64_t* acc_empty = acc_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m_tiles = (P.M + BM - 1) / BM, n_tiles = (P.N + BN - 1) / BN;
-    const int tiles = m_tiles * n_tiles;
-    const int kblocks = (P.K + BK - 1) / BK;
-
-    if (threadIdx.x == 0) {
-        prefetch_tmap(&map_a);
-        prefetch_tmap(&map_b);
-        for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
-        fence_barrier_init();
-    }
-    if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-
-    if (warp == 0) {
-        // ===== TMA producer =====
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-                const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
-                for (int kb = 0; kb < kblocks; ++kb) {
-                    mbar_wait(&empty[stage], phase ^ 1u);
-                    uint8_t* sa = smem + stage * S::kStageBytes;
-                    uint8_t* sb = sa + S::kABytes;
-                    mbar_arrive_expect_tx(&full[stage], S::kStageBytes);
-                    tma_load_2d(sa, &map_a, &full[stage], kb * BK, m0);
-                    if (!B_MN) {
-                        tma_load_2d(sb, &map_b, &full[stage], kb * BK, n0);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < BN / 64; ++j)
-                            tma_load_2d(sb + j * kAtomBytes, &map_b, &full[stage], n0 + 64 * j, kb * BK);
-                    }
-                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
-        constexpr uint32_t idesc = make_idesc(BN, false, B_MN);
-        int stage = 0;
-        uint32_t phase = 0;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
-            const int as = it & 1;
-            const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
-            mbar_wait(&acc_empty[as], aphase ^ 1u);          // the epilogue has drained this accumulator
-            tc_fence_after();
-            for (int kb = 0; kb < kblocks; ++kb) {
-                mbar_wait(&full[stage], phase);
-                tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t sa = saddr(smem + stage * S::kStageBytes);
-                    const uint32_t sb = sa + S::kABytes;
-#pragma unroll
-                    for (int k = 0; k < BK / UK; ++k) {
-                        const uint64_t ad = desc_kmajor(sa, k);
-                        const uint64_t bd = B_MN ? desc_mnmajor(sb, k) : desc_kmajor(sb, k);
-                        umma(tmem_base + as * BN, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
-                    }
-                    umma_commit(&empty[stage]);              // the stage is free once these MMAs have read it
-                    if (kb == kblocks - 1) umma_commit(&acc_full[as]);
-                }
-                __syncwarp();
-                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-            }
-        }
-    } else {
-        // ===== epilogue: 4 warps, warp w reads TMEM lanes 32*(w % 4) .. +31 =====
-        const int q = warp & 3;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
-            const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
-            const int as = it & 1;
-            const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
-            const int row = m0 + q * 32 + lane;
-            const bool row_ok = row < P.M;
-            __nv_bfloat16* crow = P.C + (int64_t)row * P.ldc;
-            const __nv_bfloat16* mrow = P.mask + (int64_t)row * P.ld_mask;
-            const bool masked = P.epilogue == EPI_RELU_MASK && row_ok;
-            // the ReLU mask is read one 32-column chunk ahead (the first chunk before the accumulator is even complete):
-            // its global-load latency overlaps the MMAs / the previous chunk instead of stalling every chunk
-            uint4 mk[4], mk_next[4];
-            auto load_mask = [&](uint4 (&dst)[4], int col0) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (col0 + 8 * j < P.N) dst[j] = __ldg(reinterpret_cast<const uint4*>(mrow + col0 + 8 * j));
-            };
-            if (masked) load_mask(mk_next, n0);
-            mbar_wait(&acc_full[as], aphase);
-            tc_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                const int col0 = n0 + c * 32;
-                if (col0 >= P.N) break;                      // warp-uniform
-                uint32_t v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
-                if (masked) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) mk[j] = mk_next[j];
-                    if (c + 1 < BN / 32 && col0 + 32 < P.N) load_mask(mk_next, col0 + 32);
-                }
-                tmem_ld_wait();
-                float f[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-                if (P.epilogue == EPI_BIAS_RELU || P.epilogue == EPI_BIAS) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        if (col0 + j < P.N) {
-                            const float4 b = __ldg(reinterpret_cast<const float4*>(P.bias + col0 + j));
-                            f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
-                        }
-                    }
-                    if (P.epilogue == EPI_BIAS_RELU) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-                    }
-                } else if (P.epilogue == EPI_RELU_MASK && row_ok) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint32_t w4[4] = {mk[j].x, mk[j].y, mk[j].z, mk[j].w};
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            // bf16 > 0  <=>  sign bit clear and magnitude non-zero
-                            const uint32_t lo = w4[e] & 0xffffu, hi = w4[e] >> 16;
-                            if (!(lo != 0u && lo < 0x8000u)) f[8 * j + 2 * e] = 0.f;
-                            if (!(hi != 0u && hi < 0x8000u)) f[8 * j + 2 * e + 1] = 0.f;
-                        }
-                    }
-                }
-                if (row_ok) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (col0 + 8 * j < P.N) {
-                            uint4 o;
-                            o.x = pack_bf16(f[8 * j], f[8 * j + 1]);
-                            o.y = pack_bf16(f[8 * j + 2], f[8 * j + 3]);
-                            o.z = pack_bf16(f[8 * j + 4], f[8 * j + 5]);
-                            o.w = pack_bf16(f[8 * j + 6], f[8 * j + 7]);
-                            *reinterpret_cast<uint4*>(crow + col0 + 8 * j) = o;
-                        }
-                    }
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[as]);
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tc_fence_after();
-        tmem_dealloc(tmem_base, 2 * BN);
-    }
-}
+enum { EPI_NONE = 0, EPI_BIAS_RELU = 1, EPI_BIAS = 3, EPI_RELU_BITS = 4 };
 
 // ------------------------------------------------------------------------------------------------------------------
 // forward / dgrad GEMM on CTA pairs.  The single-CTA kernel above moves 48 KB from L2 per 128 x 256 x 64 block of MMA work
@@ -398,8 +210,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 //   empty[s] / acc_full[a] in both CTAs (multicast tcgen05.commit from the leader), acc_empty[a] in the leader (16 epilogue
 //   warps arrive, the peer's remotely).
 // ------------------------------------------------------------------------------------------------------------------
-enum { EPI_RELU_BITS = 4 };
-
 struct PairParams {
     int M, N, K;
     const float* bias;              // [N] fp32 (EPI_BIAS_RELU / EPI_BIAS)
@@ -920,18 +730,6 @@ static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int64_t c
 }
 
 template <int BN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& P, cudaStream_t st) {
-    using S = GemmSmem<BN>;
-    static DeviceOnce once;
-    if (once.first())
-        cudaFuncSetAttribute(gemm_bf16_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kBytes);
-    const int tiles = (int)(ceil_div(P.M, BM) * ceil_div(P.N, BN));
-    const int grid = tiles < kSMs ? tiles : kSMs;
-    gemm_bf16_kernel<BN, B_MN><<<grid, kThreads, S::kBytes, st>>>(ma, mb, P);
-    return check_launch("gemm_bf16");
-}
-
-template <int BN, bool B_MN>
 static int launch_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const PairParams& P, cudaStream_t st) {
     using S = PairSmem<BN>;
     static DeviceOnce once;
@@ -956,11 +754,10 @@ int dlrmx_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int 
     DLRMX_REQUIRE(M >= 0 && N > 0 && K > 0 && N % 8 == 0 && K % 8 == 0, "gemm_bf16: need N %% 8 == 0 and K %% 8 == 0 (M=%d N=%d K=%d)", M, N, K);
     DLRMX_REQUIRE(A != nullptr && B != nullptr && C != nullptr && ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0,
                   "gemm_bf16: C must be 16-byte aligned with ldc %% 8 == 0");
-    DLRMX_REQUIRE(epilogue >= EPI_NONE && epilogue <= EPI_RELU_BITS, "gemm_bf16: bad epilogue %d", epilogue);
+    DLRMX_REQUIRE(epilogue == EPI_NONE || epilogue == EPI_BIAS_RELU || epilogue == EPI_BIAS || epilogue == EPI_RELU_BITS,
+                  "gemm_bf16: bad epilogue %d (0 none, 1 bias + ReLU, 3 bias, 4 ReLU gate bits)", epilogue);
     DLRMX_REQUIRE((epilogue != EPI_BIAS_RELU && epilogue != EPI_BIAS) || (bias != nullptr && (reinterpret_cast<uintptr_t>(bias) & 15) == 0),
                   "gemm_bf16: the bias epilogues need a 16-byte aligned bias");
-    DLRMX_REQUIRE(epilogue != EPI_RELU_MASK || (relu_mask != nullptr && ld_mask % 8 == 0 && (reinterpret_cast<uintptr_t>(relu_mask) & 15) == 0),
-                  "gemm_bf16: the ReLU-mask epilogue needs a 16-byte aligned mask with ld_mask %% 8 == 0");
     DLRMX_REQUIRE(epilogue != EPI_RELU_BITS || (relu_mask != nullptr && ld_mask >= (N + 31) / 32 && (reinterpret_cast<uintptr_t>(relu_mask) & 3) == 0),
                   "gemm_bf16: the ReLU-bits epilogue needs the gate words with ld_mask >= ceil(N / 32)");
     DLRMX_REQUIRE(relu_bits_out == nullptr || (epilogue == EPI_BIAS_RELU && ld_mask >= (N + 31) / 32),
@@ -969,26 +766,6 @@ int dlrmx_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int 
     cudaStream_t st = (cudaStream_t)stream;
     CUtensorMap ma, mb;
     if (!make_map(&ma, A, M, K, lda, BK, BM)) return DLRMX_E_ARG;
-    if (epilogue == EPI_RELU_MASK) {
-        // bf16 mask matrix: the single-CTA kernel
-        const int BN = N > 128 ? 256 : (N > 64 ? 128 : 64);
-        if (b_is_kn) {
-            if (!make_map(&mb, B, K, N, ldb, 64, BK)) return DLRMX_E_ARG;          // [K, N]: blocks of 64 k-rows x 64 n
-        } else {
-            if (!make_map(&mb, B, N, K, ldb, BK, BN)) return DLRMX_E_ARG;          // [N, K]: BN rows x 64 k
-        }
-        GemmParams P;
-        P.M = M; P.N = N; P.K = K; P.C = (__nv_bfloat16*)C; P.ldc = ldc; P.bias = bias;
-        P.mask = (const __nv_bfloat16*)relu_mask; P.ld_mask = ld_mask; P.epilogue = epilogue;
-        if (b_is_kn) {
-            if (BN == 256) return launch_gemm<256, true>(ma, mb, P, st);
-            if (BN == 128) return launch_gemm<128, true>(ma, mb, P, st);
-            return launch_gemm<64, true>(ma, mb, P, st);
-        }
-        if (BN == 256) return launch_gemm<256, false>(ma, mb, P, st);
-        if (BN == 128) return launch_gemm<128, false>(ma, mb, P, st);
-        return launch_gemm<64, false>(ma, mb, P, st);
-    }
     // CTA-pair kernel.  An MN-major B half must cover whole 64-column blocks: BN >= 128 there (columns past N are zero-filled)
     const int BN = N > 128 ? 256 : ((N > 64 || b_is_kn) ? 128 : 64);
     CUtensorMap mc;

@@ -429,7 +429,7 @@ def relu_bwd_bias_grad(dy, y, relu=True, chunks=None, db=None):
     return dz, part
 
 
-EPI_NONE, EPI_BIAS_RELU, EPI_RELU_MASK, EPI_BIAS, EPI_RELU_BITS = 0, 1, 2, 3, 4
+EPI_NONE, EPI_BIAS_RELU, EPI_BIAS, EPI_RELU_BITS = 0, 1, 3, 4
 
 
 def relu_bits_empty(M, N, device):
@@ -439,9 +439,8 @@ def relu_bits_empty(M, N, device):
 
 def gemm_bf16(a, b, b_is_kn=False, epilogue=EPI_NONE, bias=None, relu_mask=None, out=None, relu_bits_out=None):
     """Tensor-core GEMM (tcgen05 / TMEM / TMA): out [M, N] bf16 = epilogue(a [M, K] . op(b)); b is [N, K] (y = x W^t) or,
-    with b_is_kn, [K, N] (dx = dz W).  Row-major bf16 operands with unit column stride.  relu_mask: bf16 [M, N]
-    (EPI_RELU_MASK) or the int32 gate bits of relu_bits_empty (EPI_RELU_BITS); relu_bits_out: such a bit matrix, written by
-    the EPI_BIAS_RELU epilogue."""
+    with b_is_kn, [K, N] (dx = dz W).  Row-major bf16 operands with unit column stride.  relu_mask: the int32 gate bits of
+    relu_bits_empty (EPI_RELU_BITS); relu_bits_out: such a bit matrix, written by the EPI_BIAS_RELU epilogue."""
     _need_cuda(a, b, bias, relu_mask, out, relu_bits_out)
     if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.stride(1) != 1 or b.stride(1) != 1:
         raise _lib.DlrmxError("gemm_bf16: bf16 row-major operands with unit column stride")
@@ -454,11 +453,7 @@ def gemm_bf16(a, b, b_is_kn=False, epilogue=EPI_NONE, bias=None, relu_mask=None,
     bits = relu_mask if epilogue == EPI_RELU_BITS else relu_bits_out
     if bits is not None and (bits.dtype != torch.int32 or bits.stride(1) != 1 or bits.shape[0] != M):
         raise _lib.DlrmxError("gemm_bf16: gate bits are int32 [M, ceil(N / 32)] (ops.relu_bits_empty)")
-    ld_mask = 0
-    if epilogue == EPI_RELU_MASK:
-        ld_mask = relu_mask.stride(0)
-    elif bits is not None:
-        ld_mask = bits.stride(0)
+    ld_mask = bits.stride(0) if bits is not None else 0
     with _timed("gemm_bf16"):
         rc = _lib.load().dlrmx_gemm_bf16(a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), int(b_is_kn), out.data_ptr(),
                                          out.stride(0), M, N, K, int(epilogue), _ptr(bias), _ptr(relu_mask), ld_mask,

@@ -243,9 +243,8 @@ int dlrmx_relu_bwd_bias_grad_noalloc(const void* dy_bf16, const void* y_bf16, vo
  *   epilogue 0: none;  1: + bias[N] (fp32), ReLU -- with relu_bits_out the gates (Y > 0) are also written as one bit per
  *   element, word [m, n >> 5] bit (n & 31), row pitch ld_mask words;  3: + bias;
  *   4: C = acc where the gate bit of relu_mask (such a bit matrix, pitch ld_mask words) is set, else 0 -- the ReLU backward
- *   of the layer that produced this GEMM's output gradient, so the result is that layer's dz;
- *   2: the same with relu_mask a bf16 matrix [M, N] (pitch ld_mask elements), gate = mask > 0.
- *   Epilogues 0, 1, 3, 4 run on CTA pairs (tcgen05.mma.cta_group::2, M = 256 per MMA, TMA-store epilogue); 2 on single CTAs.
+ *   of the layer that produced this GEMM's output gradient, so the result is that layer's dz.
+ *   All run on CTA pairs (tcgen05.mma.cta_group::2, M = 256 per MMA, TMA-store epilogue).
  *   N % 8 == 0, K % 8 == 0, all pointers 16-byte aligned, pitches multiples of 8 elements.
  * gemm_wgrad_bf16: for every layer l of a tower, in ONE launch:  dW[l] [N_l, K_l] (fp32, pitch ld_dw) = dZ[l]^t X[l]  and
  *   db[l] [N_l] = column sums of dZ[l]  (dZ[l] [M, N_l], X[l] [M, K_l] bf16 row-major).  The batch range of every
