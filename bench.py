@@ -45,6 +45,9 @@ def parse():
                     help="1: the top tower's weight-gradient launch moves to the end of the backward pass, beside the sparse update")
     ap.add_argument("--trace", default="", help="after the timed regions: CUPTI kernel timeline (torch.profiler) of 3 more steps, "
                     "written as text (start / duration / stream / kernel) for the LAST of them; every rank writes <trace>.rank<r>")
+    ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "bf16"],
+                    help="row storage of the embedding tables (bf16: widened on load, fp32 sums / updates, rounded on store); "
+                         "the headline stays fp32")
     ap.add_argument("--mlp", default="fused-bf16", choices=["fused-bf16", "tf32", "fp32", "bf16"],
                     help="fused-bf16: FusedMLP (bf16 tensor-core GEMMs, fused epilogues/optimizer); others: torch towers")
     ap.add_argument("--sharder", default="traffic")
@@ -180,11 +183,11 @@ def make_batches(cfg, B_global, local_tables, rep_tables, lb_slice, n, seed, dis
     return out
 
 
-def algorithmic_bytes(N, TB, D, U, ib=4):
+def algorithmic_bytes(N, TB, D, U, ib=4, tb=4):
     """forward = rows + indices + offsets + pooled rows; backward+row-wise Adagrad = pooled-row
-    gradients + (key, bag) + read/write of the U distinct rows and their accumulators."""
-    fwd = N * D * 4 + N * ib + TB * ib + TB * D * 4
-    bwd = TB * D * 4 + N * 8 + 2 * U * D * 4 + 2 * U * 4
+    gradients + (key, bag) + read/write of the U distinct rows and their accumulators.  tb: bytes per table element."""
+    fwd = N * D * tb + N * ib + TB * ib + TB * D * 4
+    bwd = TB * D * 4 + N * 8 + 2 * U * D * tb + 2 * U * 4
     return fwd, bwd
 
 
@@ -203,7 +206,7 @@ def build_model(args, cfg, W, exchange=None):
     torch.manual_seed(123)
     m = dlrm_net.DLRM_Net(D, np.array(cfg["rows"]), ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
                           sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True, sharder=args.sharder,
-                          emb_optimizer=kind, emb_learning_rate=lr, emb_init="device",
+                          emb_optimizer=kind, emb_learning_rate=lr, emb_init="device", emb_weights_precision=args.table_dtype,
                           replicate_rows_below=(args.replicate_below if W > 1 else 0)).cuda()
     m.sync_replicas()
     if W > 1 and exchange == "peer":
@@ -750,14 +753,35 @@ def embbag_c3_probe(peak, iters=20):
     ms_u = timed(upd)
     fb = N * D * 4 + N * 4 + T * B * 4 + T * B * D * 4
     ub = T * B * D * 4 + N * 8 + 2 * U * D * 4
-    res = {"workload": "dlrm_s_benchmark.sh shape: 8 tables x 1M rows, dim 64, 100 indices/lookup, batch 2048, SGD",
+    # the same launches over bf16 table rows (weights_precision="bf16"): table bytes halve, everything else stays fp32
+    ts16 = ops.TableSet([w.to(torch.bfloat16) for w in tw])
+
+    def fwd16():
+        idx, off = batches[it[0] % 4]
+        it[0] += 1
+        ops.embbag_forward(ts16, idx, off, B, out=out, stride_b=T * D, stride_t=D, validate=False)
+    ms_f16 = timed(fwd16)
+
+    def upd16():
+        sk, sb = srt[it[0] % 4]
+        it[0] += 1
+        ops.bwd_update(ts16, _lib.OPT_SGD, grad, T * D, D, B, sk, sb, 0.01, 0.0)
+    ms_u16 = timed(upd16)
+    fb16 = N * D * 2 + N * 4 + T * B * 4 + T * B * D * 4
+    ub16 = T * B * D * 4 + N * 8 + 2 * U * D * 2
+    res = {"bf16_table_rows": {
+               "embbag_fwd": {"ms": round(ms_f16, 4), "algorithmic_MB": round(fb16 / 1e6, 1), "GBps": round(fb16 / ms_f16 / 1e6, 1),
+                              "frac": round(fb16 / ms_f16 / 1e6 / peak, 4)},
+               "bwd_update": {"ms": round(ms_u16, 4), "algorithmic_MB": round(ub16 / 1e6, 1), "GBps": round(ub16 / ms_u16 / 1e6, 1),
+                              "frac": round(ub16 / ms_u16 / 1e6 / peak, 4)}},
+           "workload": "dlrm_s_benchmark.sh shape: 8 tables x 1M rows, dim 64, 100 indices/lookup, batch 2048, SGD",
            "embbag_fwd": {"ms": round(ms_f, 4), "algorithmic_MB": round(fb / 1e6, 1), "GBps": round(fb / ms_f / 1e6, 1),
                           "frac": round(fb / ms_f / 1e6 / peak, 4)},
            "bwd_sort": {"ms": round(ms_s, 4)},
            "bwd_update": {"ms": round(ms_u, 4), "algorithmic_MB": round(ub / 1e6, 1), "GBps": round(ub / ms_u / 1e6, 1),
                           "frac": round(ub / ms_u / 1e6 / peak, 4), "unique_rows": int(U)}}
     res["clocks"] = sampler.stop()
-    del tw, ts, batches, srt, out, grad
+    del tw, ts, ts16, batches, srt, out, grad
     return res
 
 
@@ -822,7 +846,7 @@ def main():
     if Tl > 0:
         skey, _ = ops.bwd_sort(emb.table_set(), r["devb"][0][1], r["devb"][0][2], Bg)
         U = int(ops.bwd_segments(skey)[2].item())
-    fwd_b, bwd_b = algorithmic_bytes(Nl, Tl * Bg, D, U)
+    fwd_b, bwd_b = algorithmic_bytes(Nl, Tl * Bg, D, U, tb=2 if args.table_dtype == "bf16" else 4)
     kern = {}
     for name, nbytes in (("embbag_fwd", fwd_b), ("bwd_update", bwd_b)):
         if name in r["prof"]:
@@ -848,8 +872,9 @@ def main():
         "metric": "DLRM train samples/sec", "value": Bg * K / (r["ms_dev"] / 1e3), "unit": "samples/s",
         "n_gpus": W, "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / K,
         "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
-        "dtype": "fp32 embedding tables, pooled rows, gradients and sparse optimizer; interaction: %s; MLP GEMMs: %s"
-                 % (ix_txt, mlp_txt), "data": "synthetic",
+        "dtype": "%s embedding tables, fp32 pooled rows, gradients and sparse optimizer; interaction: %s; MLP GEMMs: %s"
+                 % ("bf16-row (widened on load, rounded to nearest on store)" if args.table_dtype == "bf16" else "fp32", ix_txt, mlp_txt),
+        "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, W, Bg), "global_batch": Bg, "per_gpu_batch": lb,
                    "index_distribution": args.index_dist,
                    "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder) for the %d tables "
@@ -859,7 +884,8 @@ def main():
                        "exchange fused into the lookup / gradient kernels over NVLink peer memory"
                        if args.exchange == "peer" else "NCCL all-to-all"),
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"
-                         % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * 4 / 1e9, args.nbatches),
+                         % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * (2 if args.table_dtype == "bf16" else 4) / 1e9,
+                            args.nbatches),
                    "rows_cap": args.rows_cap or None},
         "e2e": {"value": Bg * K / (r["wall_e2e"] / 1e3), "unit": "samples/s", "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": 4, "ms_per_step": r["wall_e2e"] / K},

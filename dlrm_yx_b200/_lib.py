@@ -29,6 +29,10 @@ SIGNATURES = {
     "dlrmx_embbag_fwd_scatter_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                              c_int64, c_void_p, c_void_p, c_int, c_int64, c_int64,
                                              c_void_p, c_void_p]),
+    "dlrmx_embbag_fwd_bf16_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,
+                                          c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "dlrmx_embbag_fwd_bf16_i64": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,
+                                          c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "dlrmx_bwd_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "dlrmx_bwd_sort_i32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p,
                                    c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
@@ -41,6 +45,9 @@ SIGNATURES = {
     "dlrmx_bwd_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_int64,
                                  c_int64, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_size_t,
                                  c_void_p]),
+    "dlrmx_bwd_update_bf16": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_int64,
+                                      c_int64, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_size_t,
+                                      c_void_p]),
     "dlrmx_bwd_coalesce": (c_int, [c_int, c_int, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_void_p, c_void_p]),
     "dlrmx_rows_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float,

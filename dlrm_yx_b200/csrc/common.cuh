@@ -1,5 +1,6 @@
 // Shared helpers for libdlrmx (sm_100a only).
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -69,6 +70,23 @@ struct RowVec<4> {
                      : "l"(p));
     }
     __device__ __forceinline__ void load(const float* p) { v = *reinterpret_cast<const float4*>(p); }
+    // bf16 table rows (fp32 everywhere else): 4 elements = one 8-byte access, widened exactly / rounded to nearest even
+    __device__ __forceinline__ void widen(uint2 r) {
+        v.x = __uint_as_float(r.x << 16); v.y = __uint_as_float(r.x & 0xffff0000u);
+        v.z = __uint_as_float(r.y << 16); v.w = __uint_as_float(r.y & 0xffff0000u);
+    }
+    __device__ __forceinline__ void load_stream(const __nv_bfloat16* p) {
+        uint2 r;
+        asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+        widen(r);
+    }
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) { widen(*reinterpret_cast<const uint2*>(p)); }
+    __device__ __forceinline__ void store(__nv_bfloat16* p) const {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 r;
+        r.x = *reinterpret_cast<uint32_t*>(&lo); r.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(p) = r;
+    }
     __device__ __forceinline__ void load_ro(const float* p) { v = __ldg(reinterpret_cast<const float4*>(p)); }
     __device__ __forceinline__ void load_unaligned(const float* p) { v = make_float4(p[0], p[1], p[2], p[3]); }
     __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = v; }
@@ -96,6 +114,9 @@ struct RowVec<1> {
     __device__ __forceinline__ void zero() { v = 0.f; }
     __device__ __forceinline__ void load_stream(const float* p) { v = __ldg(p); }
     __device__ __forceinline__ void load(const float* p) { v = *p; }
+    __device__ __forceinline__ void load_stream(const __nv_bfloat16* p) { v = __bfloat162float(*p); }
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) { v = __bfloat162float(*p); }
+    __device__ __forceinline__ void store(__nv_bfloat16* p) const { *p = __float2bfloat16_rn(v); }
     __device__ __forceinline__ void load_ro(const float* p) { v = __ldg(p); }
     __device__ __forceinline__ void load_unaligned(const float* p) { v = *p; }
     __device__ __forceinline__ void store(float* p) const { *p = v; }

@@ -95,10 +95,10 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
                         if (EXACT || col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
                 }
                 if (l[j]) {
-                    wp[j] = bshfl64<float*, G>(gmask, wptr, jj & (G - 1)) + col0;
+                    wp[j] = tab_off(P, bshfl64<float*, G>(gmask, wptr, jj & (G - 1)), col0);
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (EXACT || col0 + c * G * VEC < P.D) w[j][c].load(wp[j] + c * G * VEC);
+                        if (EXACT || col0 + c * G * VEC < P.D) load_row<VEC>(P, w[j][c], tab_off(P, wp[j], c * G * VEC));
                     if (P.optimizer == DLRMX_OPT_RWSADAGRAD) {
                         mp[j] = bshfl64<float*, G>(gmask, mptr, jj & (G - 1));
                         mo[j] = *mp[j];
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
                         for (int c = 0; c < CH; ++c)
                             if (EXACT || col0 + c * G * VEC < P.D) {
                                 w[j][c].map(g[j][c], [aj](float wv, float gv) { return __fmaf_rn(aj, gv, wv); });
-                                w[j][c].store(wp[j] + c * G * VEC);
+                                store_row<VEC>(P, w[j][c], tab_off(P, wp[j], c * G * VEC));
                             }
                         if (P.optimizer == DLRMX_OPT_RWSADAGRAD && gl == 0) *mp[j] = mnew[j];
                     } else {
@@ -208,11 +208,11 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
             float* wp;
             float* mp;
             run_target(P, skey[p1 - 1], sbag[p1 - 1], wp, mp);
-            wp += col0;
+            wp = tab_off(P, wp, col0);
             RowVec<VEC> w[CH];
 #pragma unroll
             for (int c = 0; c < CH; ++c)
-                if (EXACT || col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
+                if (EXACT || col0 + c * G * VEC < P.D) load_row<VEC>(P, w[c], tab_off(P, wp, c * G * VEC));
             const float mo = (P.optimizer == DLRMX_OPT_RWSADAGRAD) ? *mp : 0.f;
             apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
         } else {                                   // the run leaves the CTA: one tail partial per CTA
@@ -312,11 +312,11 @@ __global__ void __launch_bounds__(256) bwd_fixup_kernel(const BwdParams P) {
     float* wp;
     float* mp;
     run_target(P, key, P.sbag[p1 - 1], wp, mp);
-    wp += col0;
+    wp = tab_off(P, wp, col0);
     RowVec<VEC> w[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c)
-        if (col0 + c * G * VEC < P.D) w[c].load(wp + c * G * VEC);
+        if (col0 + c * G * VEC < P.D) load_row<VEC>(P, w[c], tab_off(P, wp, c * G * VEC));
     const float mo = (P.optimizer == DLRMX_OPT_RWSADAGRAD) ? *mp : 0.f;
     apply_row<VEC, G, CH>(P, wp, mp, mo, w, acc, col0);
 }
@@ -370,7 +370,7 @@ template <int VEC, int G, int CH>
 __global__ void __launch_bounds__(256)
 rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom,
                    const int64_t* __restrict__ rows, const float* __restrict__ gsum, int64_t U, int D,
-                   float lr, float eps) {
+                   float lr, float eps, int tab_bf16) {
     const int gl = threadIdx.x & (G - 1);
     const int64_t u = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
     if (u >= U) return;
@@ -378,15 +378,15 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
     const int64_t row = rows[u];
     BwdParams P;
     P.optimizer = optimizer; P.D = D; P.ld = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
-    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr;
+    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr; P.tab_bf16 = tab_bf16;
     RowVec<VEC> g[CH], w[CH];
-    float* wp = W + row * D + col0;
+    float* wp = tab_off(P, W, row * D + col0);
     const float* gp = gsum + u * D + col0;
 #pragma unroll
     for (int c = 0; c < CH; ++c)
         if (col0 + c * G * VEC < D) {
             g[c].load_ro(gp + c * G * VEC);
-            w[c].load(wp + c * G * VEC);
+            load_row<VEC>(P, w[c], tab_off(P, wp, c * G * VEC));
         } else {
             g[c].zero();
         }
@@ -407,13 +407,13 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
 template <int VEC, int G, int CH>
 __global__ void __launch_bounds__(256)
 dense_rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom, float* __restrict__ gsum,
-                         int64_t rows, int D, int64_t ld, float lr, float eps) {
+                         int64_t rows, int D, int64_t ld, float lr, float eps, int tab_bf16) {
     const int gl = threadIdx.x & (G - 1);
     const unsigned gmask = group_mask<G>();
     const int col0 = gl * VEC;
     BwdParams P;
     P.optimizer = optimizer; P.D = D; P.ld = ld; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
-    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr;
+    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr; P.tab_bf16 = tab_bf16;
     const int64_t ngroups = ((int64_t)gridDim.x * blockDim.x) / G;
     for (int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; r < rows; r += ngroups) {
         RowVec<VEC> g[CH], w[CH];
@@ -428,10 +428,10 @@ dense_rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict
             }
         }
         if (__ballot_sync(gmask, nz) == 0u) continue;           // group-uniform: the whole row is zero
-        float* wp = W + r * ld + col0;
+        float* wp = tab_off(P, W, r * ld + col0);
 #pragma unroll
         for (int c = 0; c < CH; ++c)
-            if (col0 + c * G * VEC < D) w[c].load(wp + c * G * VEC);
+            if (col0 + c * G * VEC < D) load_row<VEC>(P, w[c], tab_off(P, wp, c * G * VEC));
         float* mp = nullptr;
         float mo = 0.f;
         if (optimizer == DLRMX_OPT_RWSADAGRAD) {
@@ -452,7 +452,7 @@ static int launch_dense_rows_update(int optimizer, float* W, float* mom, float* 
                                     float lr, float eps, cudaStream_t st) {
     int64_t blocks = ceil_div(rows * G, 256);
     if (blocks > (int64_t)kSMs * 8) blocks = (int64_t)kSMs * 8;
-    dense_rows_update_kernel<VEC, G, CH><<<(unsigned)blocks, 256, 0, st>>>(optimizer, W, mom, gsum, rows, D, ld, lr, eps);
+    dense_rows_update_kernel<VEC, G, CH><<<(unsigned)blocks, 256, 0, st>>>(optimizer, W, mom, gsum, rows, D, ld, lr, eps, 0);
     return check_launch("dense_rows_update");
 }
 
@@ -460,7 +460,7 @@ template <int VEC, int G, int CH>
 static int launch_rows_update(int optimizer, float* W, float* mom, const int64_t* rows, const float* gsum,
                               int64_t U, int D, float lr, float eps, cudaStream_t st) {
     const unsigned blocks = (unsigned)ceil_div(U * G, 256);
-    rows_update_kernel<VEC, G, CH><<<blocks, 256, 0, st>>>(optimizer, W, mom, rows, gsum, U, D, lr, eps);
+    rows_update_kernel<VEC, G, CH><<<blocks, 256, 0, st>>>(optimizer, W, mom, rows, gsum, U, D, lr, eps, 0);
     return check_launch("rows_update");
 }
 
@@ -531,16 +531,13 @@ static size_t update_workspace_bytes(int64_t N, int D) {
     return align_up((size_t)nseg * D * 4, 256) * 2 + align_up((size_t)(D + 4) * 4, 256);   // + the scratch row
 }
 
-}  // namespace dlrmx
-
-extern "C" {
-size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D) { return dlrmx::update_workspace_bytes(N, D); }
-
-int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, const int64_t* table_row_base,
-                     int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
-                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
-                     float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+static int bwd_update_impl(int optimizer, int tab_bf16, float* const* tables, float* const* moms, const int64_t* table_row_base,
+                           int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
+                           const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
+                           float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
     using namespace dlrmx;
+    DLRMX_REQUIRE(!tab_bf16 || optimizer == DLRMX_OPT_SGD || moms != nullptr,
+                  "bwd_update_bf16: rwsadagrad needs separate fp32 accumulators (moms)");
     DLRMX_REQUIRE(optimizer == DLRMX_OPT_SGD || optimizer == DLRMX_OPT_RWSADAGRAD, "bwd_update: bad optimizer %d", optimizer);
     const int64_t ld = table_ld > 0 ? table_ld : D;
     DLRMX_REQUIRE(ld >= D, "bwd_update: table_ld must be >= D");
@@ -558,7 +555,7 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
         return DLRMX_E_WORKSPACE;
     }
     BwdParams P;
-    P.optimizer = optimizer; P.tables = tables; P.moms = moms; P.row_base = table_row_base;
+    P.optimizer = optimizer; P.tab_bf16 = tab_bf16; P.tables = tables; P.moms = moms; P.row_base = table_row_base;
     P.B = B; P.D = D; P.ld = ld; P.grad = grad; P.stride_b = stride_b; P.stride_t = stride_t;
     P.skey = sorted_key; P.sbag = sorted_bag; P.N = N; P.seg_len = seg_len_for(N, optimizer); P.nseg = ceil_div(N, (int64_t)P.seg_len);
     P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
@@ -579,6 +576,28 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
     DLRMX_GEOM_DISPATCH(g, DLRMX_CALL_UPDATE);
     set_error("bwd_update: no kernel for D=%d", D);
     return DLRMX_E_ARG;
+}
+
+}  // namespace dlrmx
+
+extern "C" {
+size_t dlrmx_bwd_update_workspace_bytes(int64_t N, int D) { return dlrmx::update_workspace_bytes(N, D); }
+
+int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, const int64_t* table_row_base,
+                     int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
+                     const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
+                     float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+    return dlrmx::bwd_update_impl(optimizer, 0, tables, moms, table_row_base, T, B, D, table_ld, grad, stride_b, stride_t,
+                                  sorted_key, sorted_bag, N, total_rows, lr, eps, workspace, workspace_bytes, stream);
+}
+
+int dlrmx_bwd_update_bf16(int optimizer, void* const* tables_bf16, float* const* moms, const int64_t* table_row_base,
+                          int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
+                          const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
+                          float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+    return dlrmx::bwd_update_impl(optimizer, 1, reinterpret_cast<float* const*>(tables_bf16), moms, table_row_base, T, B, D,
+                                  table_ld, grad, stride_b, stride_t, sorted_key, sorted_bag, N, total_rows, lr, eps, workspace,
+                                  workspace_bytes, stream);
 }
 
 int dlrmx_bwd_coalesce(int B, int D, const float* grad, int64_t stride_b, int64_t stride_t,

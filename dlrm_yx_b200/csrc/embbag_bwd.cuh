@@ -27,6 +27,8 @@ constexpr int kSeg = 32;  // sorted positions per group
 
 struct BwdParams {
     int optimizer;
+    int tab_bf16;         // 1: the table rows are bf16 (row pointers below still travel as float*, see tab_off): a row is
+                          // widened to fp32 when it is read, updated in fp32 and rounded to nearest even when it is written
     float* const* tables;
     float* const* moms;
     const int64_t* row_base;
@@ -47,6 +49,21 @@ struct BwdParams {
     float* scratch_row;   // is "applied" to this scratch row [D + 1] instead of a table row -- no branch in the hot loop
 };
 
+// Element arithmetic on a table-row pointer: fp32 rows advance 4 bytes per element, bf16 rows 2.
+__device__ __forceinline__ float* tab_off(const BwdParams& P, float* p, int64_t elems) {
+    return P.tab_bf16 ? reinterpret_cast<float*>(reinterpret_cast<__nv_bfloat16*>(p) + elems) : p + elems;
+}
+template <int VEC>
+__device__ __forceinline__ void load_row(const BwdParams& P, RowVec<VEC>& w, const float* p) {
+    if (P.tab_bf16) w.load(reinterpret_cast<const __nv_bfloat16*>(p));
+    else w.load(p);
+}
+template <int VEC>
+__device__ __forceinline__ void store_row(const BwdParams& P, const RowVec<VEC>& w, float* p) {
+    if (P.tab_bf16) w.store(reinterpret_cast<__nv_bfloat16*>(p));
+    else w.store(p);
+}
+
 // Where the run of `key` (looked up through bag `bag`) lives: table row and, for row-wise Adagrad, its accumulator.
 __device__ __forceinline__ void run_target(const BwdParams& P, uint32_t key, int bag, float*& wp, float*& mp) {
     if (key == P.invalid_key) {
@@ -56,7 +73,7 @@ __device__ __forceinline__ void run_target(const BwdParams& P, uint32_t key, int
     }
     const int t = bag / P.B;
     const int64_t row = (int64_t)key - P.row_base[t];
-    wp = P.tables[t] + row * P.ld;
+    wp = tab_off(P, P.tables[t], row * P.ld);
     mp = nullptr;
     if (P.optimizer == DLRMX_OPT_RWSADAGRAD) mp = P.moms != nullptr ? P.moms[t] + row : wp + P.D;
 }
@@ -92,7 +109,7 @@ __device__ __forceinline__ void apply_row(const BwdParams& P, float* wp, float* 
         for (int c = 0; c < CH; ++c)
             if (col0 + c * G * VEC < P.D) {
                 w[c].map(acc[c], [a](float wv, float gv) { return __fmaf_rn(a, gv, wv); });
-                w[c].store(wp + c * G * VEC);
+                store_row<VEC>(P, w[c], tab_off(P, wp, c * G * VEC));
             }
     } else {
         float ss = 0.f;
@@ -111,7 +128,7 @@ __device__ __forceinline__ void apply_row(const BwdParams& P, float* wp, float* 
         for (int c = 0; c < CH; ++c)
             if (col0 + c * G * VEC < P.D) {
                 w[c].map(acc[c], [a](float wv, float gv) { return __fmaf_rn(a, gv, wv); });
-                w[c].store(wp + c * G * VEC);
+                store_row<VEC>(P, w[c], tab_off(P, wp, c * G * VEC));
             }
         if ((threadIdx.x & (G - 1)) == 0) *mp = mom;
     }

@@ -53,10 +53,11 @@ __device__ __forceinline__ int32_t shfl_idx(unsigned mask, int32_t v, int src, i
 // EXACT: D == VEC*G*CH, every lane owns columns of the row (no per-lane guard).
 // THREADS: CTA size (224 x 4 CTAs per SM = 28 warps at up to 72 registers: between the 24 warps of 256 x 3 and the 64-register
 // budget of 256 x 4).
+// TabT: element type of the table rows (float, or __nv_bfloat16 widened on load; sums, outputs and weights stay fp32).
 template <int VEC, int G, int CH, int K, int U, bool FULL, bool SCATTER, typename IdxT, int OCC = 0, bool EXACT = false,
-          int THREADS = 256>
+          int THREADS = 256, typename TabT = float>
 __global__ void __launch_bounds__(THREADS, OCC > 0 ? OCC : ((K * U * CH <= 4) ? 4 : ((K * U * CH <= 8) ? 3 : 2)))
-embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
+embbag_fwd_kernel(const TabT* const* __restrict__ tables, const int64_t* __restrict__ table_rows,
                   const IdxT* __restrict__ indices, const IdxT* __restrict__ offsets, int64_t N,
                   int B, int D, int64_t ld, int64_t total_bags, const float* __restrict__ psw,
                   float* __restrict__ out, int64_t stride_b, int64_t stride_t, int* err_flag,
@@ -72,7 +73,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     // ---- lane-parallel metadata of the tile: lane i (< TILE) describes bag tile_bag0 + i ---------------
     IdxT my_s = 0, my_ix = -1;
     int my_len = 0;
-    const float* my_base = nullptr;
+    const TabT* my_base = nullptr;
     int64_t my_rows = 0;
     {
         const int64_t q = tile_bag0 + gl;
@@ -94,7 +95,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
         if (tile_bag0 + b0 >= total_bags) break;
         IdxT start[KB], ix[KB][U];
         int len[KB];
-        const float* base[KB];
+        const TabT* base[KB];
         int64_t nrows[KB];
         int maxlen = 0;
 #pragma unroll
@@ -102,7 +103,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
             start[k] = shfl_idx(gmask, my_s, b0 + k, G);
             ix[k][0] = shfl_idx(gmask, my_ix, b0 + k, G);
             len[k] = __shfl_sync(gmask, my_len, b0 + k, G);
-            base[k] = shfl64<const float*>(gmask, my_base, b0 + k, G);
+            base[k] = shfl64<const TabT*>(gmask, my_base, b0 + k, G);
             nrows[k] = shfl64<int64_t>(gmask, my_rows, b0 + k, G);
             maxlen = max(maxlen, len[k]);
         }
@@ -130,7 +131,7 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
                         live[k][u] = false;
                     }
                     if (live[k][u]) {
-                        const float* p = base[k] + (int64_t)ix[k][u] * ld + col0;
+                        const TabT* p = base[k] + (int64_t)ix[k][u] * ld + col0;
 #pragma unroll
                         for (int c = 0; c < CH; ++c)
                             if (EXACT || col0 + c * G * VEC < D) row[k][u][c].load_stream(p + c * G * VEC);
@@ -184,8 +185,8 @@ embbag_fwd_kernel(const float* const* __restrict__ tables, const int64_t* __rest
     }
 }
 
-template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0, int THREADS = 256>
-static int launch_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
+template <int VEC, int G, int CH, int K, int U, bool FULL, typename IdxT, int OCC = 0, int THREADS = 256, typename TabT = float>
+static int launch_fwd(const TabT* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, int64_t ld, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
                       cudaStream_t st) {
@@ -196,7 +197,7 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     const int64_t blocks = ceil_div(groups * G, threads);
     if (blocks == 0) return DLRMX_OK;
 #define DLRMX_FWD_LAUNCH(SC, EX, ...) \
-    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, SC, IdxT, OCC, EX, THREADS><<<(unsigned)blocks, threads, 0, st>>>(__VA_ARGS__)
+    embbag_fwd_kernel<VEC, G, CH, K, U, FULL, SC, IdxT, OCC, EX, THREADS, TabT><<<(unsigned)blocks, threads, 0, st>>>(__VA_ARGS__)
     const bool exact = D == VEC * G * CH;
     if (out_peers != nullptr) {
         if (exact) DLRMX_FWD_LAUNCH(true, true, tables, table_rows, indices, offsets, N, B, D, ld, total_bags, psw, out, stride_b, stride_t, err_flag, out_peers, lb);
@@ -209,8 +210,8 @@ static int launch_fwd(const float* const* tables, const int64_t* table_rows, con
     return check_launch("embbag_fwd");
 }
 
-template <typename IdxT>
-static int embbag_fwd(const float* const* tables, const int64_t* table_rows, const IdxT* indices,
+template <typename IdxT, typename TabT = float>
+static int embbag_fwd(const TabT* const* tables, const int64_t* table_rows, const IdxT* indices,
                       const IdxT* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw, float* out,
                       int64_t stride_b, int64_t stride_t, int* err_flag, float* const* out_peers, int lb,
                       dlrmx_stream_t stream) {
@@ -237,9 +238,9 @@ static int embbag_fwd(const float* const* tables, const int64_t* table_rows, con
     tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                       \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                        \
-        if (short_bags) return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT>(DLRMX_FWD_ARGS);  \
-        if constexpr (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224>(DLRMX_FWD_ARGS); \
-        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3>(DLRMX_FWD_ARGS);           \
+        if (short_bags) return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT, 0, 256, TabT>(DLRMX_FWD_ARGS);  \
+        if constexpr (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224, TabT>(DLRMX_FWD_ARGS); \
+        return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3, 256, TabT>(DLRMX_FWD_ARGS);           \
     }
     DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
     DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)

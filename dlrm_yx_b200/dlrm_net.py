@@ -304,7 +304,7 @@ class DLRM_Net(nn.Module):
         self.Es = Es[self.local_emb_indices] if ext_dist.my_size > 1 else Es
         T = len(self.Es)
         kw = dict(optimizer=self.emb_optimizer, learning_rate=learning_rate, eps=self.emb_eps, stochastic_rounding=False,
-                  init=self.emb_init)
+                  init=self.emb_init, weights_precision=self.emb_weights_precision)
         self.emb_rep = None
         if ext_dist.my_size > 1 and len(self.replicated_emb_indices) > 0:
             rows = Es[self.replicated_emb_indices]
@@ -318,7 +318,7 @@ class DLRM_Net(nn.Module):
                  qr_flag=False, qr_operation="mult", qr_collisions=0, qr_threshold=200, md_flag=False, md_threshold=200,
                  # additions (keyword-only in spirit): the fused optimizer of the batched module
                  emb_optimizer=embedding.Optimizer.SGD, emb_learning_rate=0.1, emb_eps=None, emb_init="auto",
-                 fuse_sparse_arch=False, replicate_rows_below=0):
+                 fuse_sparse_arch=False, replicate_rows_below=0, emb_weights_precision="fp32"):
         super().__init__()
         if any(a is None for a in (m_spa, ln_emb, ln_bot, ln_top, arch_interaction_op)):
             return
@@ -341,6 +341,7 @@ class DLRM_Net(nn.Module):
             raise _lib.DlrmxError("QR / mixed-dimension embeddings use the per-table path (batched_emb=False), as in the reference")
         self.sharder = sharder
         self.emb_optimizer, self.emb_eps, self.emb_init = emb_optimizer, emb_eps, emb_init
+        self.emb_weights_precision = emb_weights_precision      # "bf16": 16-bit row storage of the batched module
         self.fuse_sparse_arch = bool(fuse_sparse_arch)
         if self.fuse_sparse_arch and not (batched_emb and arch_interaction_op == "dot"):
             raise ValueError("fuse_sparse_arch needs batched_emb=True and arch_interaction_op='dot'")

@@ -77,10 +77,17 @@ class TableBatchedEmbeddingBags(nn.Module):
 
     def __init__(self, num_tables, num_embeddings, embedding_dim, optimizer=Optimizer.SGD, learning_rate=0.01,
                  eps=None, stochastic_rounding=False, lr_decay=0.0, initial_accumulator_value=0.0,
-                 init="auto", device=None):
+                 init="auto", device=None, weights_precision="fp32"):
+        """weights_precision: "fp32" (the reference's batched module) or "bf16" -- 16-bit row storage as the `weights_precision`
+        argument of the reference's fbgemm slot offers (dlrm_s_pytorch.py:350-366): rows are widened to fp32 when read, pooled
+        and updated in fp32 (fp32 row-wise accumulators), and rounded to nearest even when written (stochastic_rounding=False,
+        dlrm_s_pytorch.py:333).  Half the table bytes per lookup and per update."""
         super().__init__()
         if stochastic_rounding:
-            raise _lib.DlrmxError("stochastic_rounding applies to fp16 tables; tables here are fp32")
+            raise _lib.DlrmxError("stochastic_rounding is not implemented (bf16 rows are rounded to nearest even)")
+        if weights_precision not in ("fp32", "bf16"):
+            raise ValueError("weights_precision must be 'fp32' or 'bf16'")
+        self.weights_precision = weights_precision
         if isinstance(num_embeddings, (int, np.integer)):
             rows = [int(num_embeddings)] * int(num_tables)
         else:
@@ -109,6 +116,8 @@ class TableBatchedEmbeddingBags(nn.Module):
             elif init != "empty":
                 raise ValueError("init must be auto|numpy|device|empty")
             base += r
+        if weights_precision == "bf16":
+            flat = flat.to(torch.bfloat16)          # the fp32 draw rounded once: the same initial values on a bf16 grid
         self.embedding_weights = nn.Parameter(flat)
         if optimizer in _ROWWISE:
             self.register_buffer("row_momentum", torch.full((total,), float(initial_accumulator_value),

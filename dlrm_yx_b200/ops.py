@@ -83,10 +83,13 @@ class TableSet:
         _need_cuda(*ws)
         D = ws[0].shape[1]
         ld = ws[0].stride(0) if ws[0].shape[0] > 1 else D
+        self.bf16 = ws[0].dtype == torch.bfloat16      # bf16 row storage: widened on load, fp32 sums / updates, rounded on store
         for w in ws:
-            if w.dtype != torch.float32 or w.dim() != 2 or w.shape[1] != D or w.stride(1) != 1 or \
-                    (w.shape[0] > 1 and w.stride(0) != ld):
-                raise _lib.DlrmxError("tables must be row-major fp32 [rows, D] with a common D and a common row pitch")
+            if w.dtype != ws[0].dtype or w.dtype not in (torch.float32, torch.bfloat16) or w.dim() != 2 or w.shape[1] != D or \
+                    w.stride(1) != 1 or (w.shape[0] > 1 and w.stride(0) != ld):
+                raise _lib.DlrmxError("tables must be row-major fp32 (or all bf16) [rows, D] with a common D and a common row pitch")
+        if self.bf16 and self.acc_in_row:
+            raise _lib.DlrmxError("bf16 tables keep their row-wise accumulators in a separate fp32 array (no acc_in_row)")
         if ld < D or (self.acc_in_row and ld <= D):
             raise _lib.DlrmxError("bad table row pitch %d for D=%d (acc_in_row needs padded rows)" % (ld, D))
         self.ld = int(ld)
@@ -159,7 +162,7 @@ def embbag_forward(tables, indices, offsets, B, out=None, stride_b=None, stride_
     if out is None:
         out = torch.empty((B, T, D), dtype=torch.float32, device=tables.device)
         stride_b, stride_t = T * D, D
-    fn = getattr(_lib.load(), "dlrmx_embbag_fwd_" + _idx_suffix(indices, offsets))
+    fn = getattr(_lib.load(), "dlrmx_embbag_fwd_" + ("bf16_" if tables.bf16 else "") + _idx_suffix(indices, offsets))
     if err_flag is None and validate:
         err_flag = globals()["err_flag"](tables.device)
     with _timed("embbag_fwd"):
@@ -182,6 +185,8 @@ def embbag_forward_scatter(tables, indices, offsets, B, out_peers, lb, stride_b,
         raise _lib.DlrmxError("offsets has %d entries, need at least T*B = %d" % (offsets.numel(), T * B))
     if out_peers.dtype != torch.int64 or out_peers.numel() * lb != B:
         raise _lib.DlrmxError("out_peers must hold B / lb int64 pointers")
+    if tables.bf16:
+        raise _lib.DlrmxError("the NVLink scatter lookup takes fp32 tables (bf16 row storage: single-device / NCCL paths)")
     fn = getattr(_lib.load(), "dlrmx_embbag_fwd_scatter_" + _idx_suffix(indices, offsets))
     with _timed("embbag_fwd"):
         rc = fn(tables.table_ptrs.data_ptr(), tables.table_rows.data_ptr() if validate else 0, indices.data_ptr(),
@@ -242,11 +247,12 @@ def bwd_update(tables, optimizer, grad, stride_b, stride_t, B, skey, sbag, lr, e
     wsb = lib.dlrmx_bwd_update_workspace_bytes(N, tables.D)
     ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=tables.device)
     with _timed("bwd_update"):
-        rc = lib.dlrmx_bwd_update(optimizer, tables.table_ptrs.data_ptr(),
-                                  0 if tables.acc_in_row else _ptr(tables.mom_ptrs),
-                                  tables.row_base.data_ptr(), tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b,
-                                  stride_t, skey.data_ptr(), sbag.data_ptr(), N, tables.total_rows, float(lr), float(eps),
-                                  ws.data_ptr(), wsb, _stream())
+        fn = lib.dlrmx_bwd_update_bf16 if tables.bf16 else lib.dlrmx_bwd_update
+        rc = fn(optimizer, tables.table_ptrs.data_ptr(),
+                0 if tables.acc_in_row else _ptr(tables.mom_ptrs),
+                tables.row_base.data_ptr(), tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b,
+                stride_t, skey.data_ptr(), sbag.data_ptr(), N, tables.total_rows, float(lr), float(eps),
+                ws.data_ptr(), wsb, _stream())
         _lib.check(rc, "dlrmx_bwd_update")
 
 

@@ -83,6 +83,18 @@ int dlrmx_embbag_fwd_i64(const float* const* tables, const int64_t* table_rows,
                          float* out, int64_t stride_b, int64_t stride_t,
                          int* err_flag, dlrmx_stream_t stream);
 
+/* The same lookup over bf16 TABLE ROWS (fp16/bf16 row storage of the table-batched module, the `weights_precision` knob of
+ * the reference's fbgemm slot, dlrm_s_pytorch.py:350-366): tables_bf16 [T] device array of row-major bf16 table base
+ * pointers (8-byte aligned when D % 4 == 0), table_ld in ELEMENTS.  Rows are widened exactly to fp32 when they are read and
+ * summed in fp32 in index order; pooled rows, per-sample weights and everything downstream stay fp32.  Half the table bytes
+ * of the fp32 entry points, bit-identical to them on a table holding the widened values. */
+int dlrmx_embbag_fwd_bf16_i32(const void* const* tables_bf16, const int64_t* table_rows, const int32_t* indices,
+                              const int32_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
+                              float* out, int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
+int dlrmx_embbag_fwd_bf16_i64(const void* const* tables_bf16, const int64_t* table_rows, const int64_t* indices,
+                              const int64_t* offsets, int64_t N, int T, int B, int D, int64_t table_ld, const float* psw,
+                              float* out, int64_t stride_b, int64_t stride_t, int* err_flag, dlrmx_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Backward, step 1: sort the looked-up rows.
  * Replaces what EmbeddingBag backward + grad.coalesce() do implicitly (sparse COO gradient with
@@ -144,6 +156,16 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms,
                      const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows,
                      float lr, float eps,
                      void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+/* The fused update on bf16 table rows: every touched row is widened to fp32, updated in fp32 exactly as above and rounded to
+ * nearest even when it is written back (stochastic_rounding=False of the reference's call, dlrm_s_pytorch.py:333); the
+ * row-wise Adagrad accumulators stay fp32 in `moms` (required).  The result equals rounding the fp32 entry point's result
+ * on a table holding the widened rows. */
+int dlrmx_bwd_update_bf16(int optimizer, void* const* tables_bf16, float* const* moms,
+                          const int64_t* table_row_base, int T, int B, int D, int64_t table_ld,
+                          const float* grad, int64_t stride_b, int64_t stride_t,
+                          const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows,
+                          float lr, float eps,
+                          void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
 
 /* Non-fused variant: emits the coalesced gradient rows  gsum[u,:] = sum over run u  ([num_unique, D],
  * row stride D) so that the reference's own optimizers can consume a coalesced sparse COO gradient

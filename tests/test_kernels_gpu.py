@@ -455,3 +455,43 @@ def test_a2a_layout_roundtrip(D):
     assert np.array_equal(pitched.cpu().numpy()[:, 1:, :], ref)
     send2 = ops.a2a_pack_grad(pitched, 1, tpr, lb, D)
     assert np.array_equal(send2.cpu().numpy(), recv.cpu().numpy())
+
+
+@pytest.mark.parametrize("D,L,opt", [(128, 1, "rwsadagrad"), (64, 7, "sgd"), (96, 3, "rwsadagrad"), (6, 2, "sgd")])
+def test_bf16_table_rows_match_the_fp32_path_on_widened_tables(D, L, opt):
+    """bf16 row storage (weights_precision="bf16"): the lookup over bf16 rows must equal, bit for bit, the fp32 lookup over a
+    table holding the widened rows (and with it the numpy oracle's sequential fp32 sums); the fused update must equal the
+    fp32 fused update of the widened table ROUNDED to bf16 (round to nearest even), accumulators bit-identical -- hot rows
+    (3-row table with hundreds of duplicates) and untouched rows included."""
+    from dlrm_yx_b200 import _lib, ops
+    dev = cuda()
+    rng = np.random.default_rng(17)
+    rows, B = [3, 700, 5000], 257
+    Wb = [torch.from_numpy(rng.uniform(-1, 1, size=(r, D)).astype(np.float32)).to(dev).to(torch.bfloat16) for r in rows]
+    Wf = [w.float() for w in Wb]
+    idx = np.concatenate([rng.integers(0, r, size=B * L) for r in rows]).astype(np.int32)
+    off = (np.arange(len(rows) * B + 1) * L).astype(np.int32)
+    idx_t, off_t = torch.from_numpy(idx).to(dev), torch.from_numpy(off).to(dev)
+    kind = _lib.OPT_RWSADAGRAD if opt == "rwsadagrad" else _lib.OPT_SGD
+    mom_b = [torch.full((r,), 0.01, device=dev) for r in rows] if opt == "rwsadagrad" else None
+    mom_f = [m.clone() for m in mom_b] if mom_b is not None else None
+    ts_b, ts_f = ops.TableSet(Wb, mom_b), ops.TableSet(Wf, mom_f)
+    assert ts_b.bf16 and not ts_f.bf16
+    out_b = ops.embbag_forward(ts_b, idx_t, off_t, B)
+    out_f = ops.embbag_forward(ts_f, idx_t, off_t, B)
+    assert torch.equal(out_b, out_f)
+    ref = O.embbag_fwd_batched([w.cpu().numpy() for w in Wf], idx, off, B)
+    assert np.array_equal(out_b.cpu().numpy(), ref)
+    grad = torch.from_numpy(rng.normal(size=(B, len(rows), D)).astype(np.float32)).to(dev)
+    skey, sbag = ops.bwd_sort(ts_f, idx_t, off_t, B)
+    before = [w.clone() for w in Wb]
+    ops.bwd_update(ts_b, kind, grad, len(rows) * D, D, B, skey, sbag, 0.05, 1e-8)
+    ops.bwd_update(ts_f, kind, grad, len(rows) * D, D, B, skey, sbag, 0.05, 1e-8)
+    for k in range(len(rows)):
+        assert torch.equal(Wb[k].view(torch.int16), Wf[k].to(torch.bfloat16).view(torch.int16)), "table %d" % k
+        if mom_b is not None:
+            assert torch.equal(mom_b[k], mom_f[k])
+        touched = torch.zeros(rows[k], dtype=torch.bool, device=dev)
+        touched[torch.from_numpy(idx[k * B * L:(k + 1) * B * L].astype(np.int64)).to(dev)] = True
+        assert torch.equal(Wb[k][~touched], before[k][~touched])
+    ops.check_index_errors()

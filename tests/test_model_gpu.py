@@ -412,3 +412,48 @@ def test_model_with_qr_and_md_tables_trains():
         loss.backward()
         assert np.isfinite(loss.item())
         assert all(p.grad is not None for p in net.emb_l.parameters())
+
+
+def test_bf16_row_storage_two_train_steps_match_the_widened_fp32_model():
+    """TableBatchedEmbeddingBags(weights_precision="bf16") inside the fused sparse arch: two training steps against the same
+    model with fp32 tables initialised to the widened bf16 rows.  Step 1's loss is bit-identical (the lookup widens exactly);
+    after each step the bf16 rows equal the fp32 model's rows rounded to bf16 only while the two models see the same
+    pre-update rows, i.e. after step 1 -- checked bit for bit; step 2's loss then differs by the rounding of the rows
+    (|diff| <= 2e-3 relative)."""
+    from dlrm_yx_b200 import dlrm_net, embedding, ops
+    np.random.seed(5)
+    rows, D, B = [3000, 39, 17, 7, 20, 3, 700, 150], 64, 256
+    ln_bot, ln_top = np.array([13, 32, D]), np.array([data.num_interactions(len(rows), D), 32, 1])
+
+    def build(prec):
+        np.random.seed(11)
+        return dlrm_net.DLRM_Net(D, np.array(rows), ln_bot, ln_top, arch_interaction_op="dot", sigmoid_bot=-1,
+                                 sigmoid_top=ln_top.size - 2, batched_emb=True, fuse_sparse_arch=True,
+                                 emb_optimizer=embedding.Optimizer.EXACT_ROWWISE_ADAGRAD, emb_learning_rate=0.1,
+                                 emb_weights_precision=prec).cuda()
+    mb, mf = build("bf16"), build("fp32")
+    assert mb._batched_module().embedding_weights.dtype == torch.bfloat16
+    with torch.no_grad():
+        mf._batched_module().embedding_weights.copy_(mb._batched_module().embedding_weights.float())
+    opts = [torch.optim.SGD(list(m.bot_l.parameters()) + list(m.top_l.parameters()), lr=0.1) for m in (mb, mf)]
+    rng = np.random.default_rng(5)
+    losses = []
+    for step in range(2):
+        X, lS_o, lS_i, tgt = data.random_batch(rows, B, 2, 13, fixed=True, rng=rng)
+        idx, off = data.pack(lS_o, lS_i)
+        ls = []
+        for m, opt in zip((mb, mf), opts):
+            loss = m.loss_fn(m(X.cuda(), off.cuda(), idx.cuda()), tgt.cuda())
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            ls.append(loss.item())
+        losses.append(ls)
+        if step == 0:
+            assert ls[0] == ls[1]
+            torch.cuda.synchronize()
+            for wb, wf in zip(mb._batched_module().split_weights(), mf._batched_module().split_weights()):
+                assert torch.equal(wb.view(torch.int16), wf.to(torch.bfloat16).view(torch.int16))
+            assert torch.equal(mb._batched_module().row_momentum, mf._batched_module().row_momentum)
+    assert abs(losses[1][0] - losses[1][1]) <= 2e-3 * abs(losses[1][1])
+    ops.check_index_errors()
