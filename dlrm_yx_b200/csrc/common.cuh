@@ -108,6 +108,76 @@ struct RowVec<4> {
     }
 };
 
+// 8 bf16 elements as loaded (4 registers): rows in flight stay packed and are widened when they are added
+struct PackedRow8 {
+    uint4 r;
+    __device__ __forceinline__ void load_stream(const __nv_bfloat16* p) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    }
+};
+
+// 8 elements per lane: the lane geometry of bf16 table rows (one 16-byte access = 8 bf16), fp32 everywhere else (two
+// 16-byte accesses).  Same arithmetic as RowVec<4>, element by element.
+template <>
+struct RowVec<8> {
+    float4 a, b;
+    __device__ __forceinline__ void zero() { a = make_float4(0.f, 0.f, 0.f, 0.f); b = a; }
+    __device__ __forceinline__ void widen(uint4 r) {
+        a.x = __uint_as_float(r.x << 16); a.y = __uint_as_float(r.x & 0xffff0000u);
+        a.z = __uint_as_float(r.y << 16); a.w = __uint_as_float(r.y & 0xffff0000u);
+        b.x = __uint_as_float(r.z << 16); b.y = __uint_as_float(r.z & 0xffff0000u);
+        b.z = __uint_as_float(r.w << 16); b.w = __uint_as_float(r.w & 0xffff0000u);
+    }
+    __device__ __forceinline__ void load_stream(const __nv_bfloat16* p) {
+        uint4 r;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+        widen(r);
+    }
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) { widen(*reinterpret_cast<const uint4*>(p)); }
+    __device__ __forceinline__ void store(__nv_bfloat16* p) const {
+        __nv_bfloat162 q0 = __floats2bfloat162_rn(a.x, a.y), q1 = __floats2bfloat162_rn(a.z, a.w);
+        __nv_bfloat162 q2 = __floats2bfloat162_rn(b.x, b.y), q3 = __floats2bfloat162_rn(b.z, b.w);
+        uint4 r;
+        r.x = *reinterpret_cast<uint32_t*>(&q0); r.y = *reinterpret_cast<uint32_t*>(&q1);
+        r.z = *reinterpret_cast<uint32_t*>(&q2); r.w = *reinterpret_cast<uint32_t*>(&q3);
+        *reinterpret_cast<uint4*>(p) = r;
+    }
+    __device__ __forceinline__ void load_stream(const float* p) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(p));
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p + 4));
+    }
+    __device__ __forceinline__ void load(const float* p) {
+        a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 4);
+    }
+    __device__ __forceinline__ void load_ro(const float* p) {
+        a = __ldg(reinterpret_cast<const float4*>(p)); b = __ldg(reinterpret_cast<const float4*>(p + 4));
+    }
+    __device__ __forceinline__ void store(float* p) const {
+        *reinterpret_cast<float4*>(p) = a; *reinterpret_cast<float4*>(p + 4) = b;
+    }
+    __device__ __forceinline__ void add(const RowVec& o) {
+        a.x = __fadd_rn(a.x, o.a.x); a.y = __fadd_rn(a.y, o.a.y); a.z = __fadd_rn(a.z, o.a.z); a.w = __fadd_rn(a.w, o.a.w);
+        b.x = __fadd_rn(b.x, o.b.x); b.y = __fadd_rn(b.y, o.b.y); b.z = __fadd_rn(b.z, o.b.z); b.w = __fadd_rn(b.w, o.b.w);
+    }
+    __device__ __forceinline__ void add_scaled(const RowVec& o, float w) {  // acc + (row*w), two roundings
+        a.x = __fadd_rn(a.x, __fmul_rn(o.a.x, w)); a.y = __fadd_rn(a.y, __fmul_rn(o.a.y, w));
+        a.z = __fadd_rn(a.z, __fmul_rn(o.a.z, w)); a.w = __fadd_rn(a.w, __fmul_rn(o.a.w, w));
+        b.x = __fadd_rn(b.x, __fmul_rn(o.b.x, w)); b.y = __fadd_rn(b.y, __fmul_rn(o.b.y, w));
+        b.z = __fadd_rn(b.z, __fmul_rn(o.b.z, w)); b.w = __fadd_rn(b.w, __fmul_rn(o.b.w, w));
+    }
+    __device__ __forceinline__ float sumsq() const {
+        return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(a.x, a.x), __fmul_rn(a.y, a.y)), __fadd_rn(__fmul_rn(a.z, a.z), __fmul_rn(a.w, a.w))),
+                         __fadd_rn(__fadd_rn(__fmul_rn(b.x, b.x), __fmul_rn(b.y, b.y)), __fadd_rn(__fmul_rn(b.z, b.z), __fmul_rn(b.w, b.w))));
+    }
+    template <typename F>
+    __device__ __forceinline__ void map(const RowVec& g, F f) {  // v = f(v, g) elementwise
+        a.x = f(a.x, g.a.x); a.y = f(a.y, g.a.y); a.z = f(a.z, g.a.z); a.w = f(a.w, g.a.w);
+        b.x = f(b.x, g.b.x); b.y = f(b.y, g.b.y); b.z = f(b.z, g.b.z); b.w = f(b.w, g.b.w);
+    }
+    __device__ __forceinline__ void add(const PackedRow8& o) { RowVec t; t.widen(o.r); add(t); }
+    __device__ __forceinline__ void add_scaled(const PackedRow8& o, float w) { RowVec t; t.widen(o.r); add_scaled(t, w); }
+};
+
 template <>
 struct RowVec<1> {
     float v;
@@ -132,9 +202,10 @@ struct RowVec<1> {
 struct RowGeom {
     int vec, g, ch;
 };
-inline bool row_geometry(int D, RowGeom* out) {
+// max_vec: 4 (fp32 rows: 16 bytes per lane) or 8 (bf16 rows: 16 bytes per lane as well)
+inline bool row_geometry(int D, RowGeom* out, int max_vec = 4) {
     if (D <= 0) return false;
-    int vec = (D % 4 == 0) ? 4 : 1;
+    int vec = (max_vec == 8 && D % 8 == 0) ? 8 : ((D % 4 == 0 && max_vec != 8) ? 4 : 1);
     int nv = D / vec;
     int g = 1;
     while (g < nv && g < 32) g <<= 1;

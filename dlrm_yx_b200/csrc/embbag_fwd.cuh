@@ -17,6 +17,7 @@
 //     [B, 1+T, D] interaction input (no torch.cat afterwards).
 // HBM-bound: algorithmic bytes = N*D*4 (rows) + N*ib + T*B*ob + T*B*D*4 (pooled rows).
 #pragma once
+#include <type_traits>
 #include "common.cuh"
 
 namespace dlrmx {
@@ -119,7 +120,8 @@ embbag_fwd_kernel(const TabT* const* __restrict__ tables, const int64_t* __restr
             for (int c = 0; c < CH; ++c) acc[k][c].zero();
 
         for (int r = 0; r < maxlen; r += U) {
-            RowVec<VEC> row[KB][U][CH];
+            // rows in flight: bf16 rows of the 8-element lane geometry stay packed (4 registers, widened when added)
+            typename std::conditional<(VEC == 8 && sizeof(TabT) == 2), PackedRow8, RowVec<VEC>>::type row[KB][U][CH];
             bool live[KB][U];
 #pragma unroll
             for (int u = 0; u < U; ++u)
@@ -219,10 +221,11 @@ static int embbag_fwd(const TabT* const* tables, const int64_t* table_rows, cons
     DLRMX_REQUIRE(out_peers == nullptr || (lb > 0 && B % lb == 0), "embbag_fwd_scatter: B must be a multiple of lb > 0");
     DLRMX_REQUIRE((int64_t)T * B < (1ll << 31), "embbag_fwd: T*B must be < 2^31");
     RowGeom g;
-    DLRMX_REQUIRE(row_geometry(D, &g), "embbag_fwd: unsupported D=%d (need D<=512 if D%%4==0, else D<=128)", D);
+    constexpr bool kBf16 = sizeof(TabT) == 2;     // bf16 rows: 8 elements (16 bytes) per lane when D % 8 == 0, else one
+    DLRMX_REQUIRE(row_geometry(D, &g, kBf16 ? 8 : 4), "embbag_fwd: unsupported D=%d (need D<=512 if D%%4==0, else D<=128)", D);
     const int64_t ld = table_ld > 0 ? table_ld : D;      // row pitch of the tables in floats
-    DLRMX_REQUIRE(ld >= D && (g.vec != 4 || ld % 4 == 0), "embbag_fwd: table_ld must be >= D (and a multiple of 4 when D%%4==0)");
-    if (g.vec == 4)
+    DLRMX_REQUIRE(ld >= D && (g.vec == 1 || ld % g.vec == 0), "embbag_fwd: table_ld must be >= D (and a multiple of the lane width %d)", g.vec);
+    if (g.vec >= 4)
         DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && (out_peers != nullptr || ((uintptr_t)out & 15) == 0),
                       "embbag_fwd: out must be 16-B aligned with strides multiple of 4 when D%%4==0");
     if ((int64_t)T * B == 0) return DLRMX_OK;
@@ -238,12 +241,17 @@ static int embbag_fwd(const TabT* const* tables, const int64_t* table_rows, cons
     tables, table_rows, indices, offsets, N, T, B, D, ld, psw, out, stride_b, stride_t, err_flag, out_peers, lb, st
 #define DLRMX_FWD_CASE(VEC_, G_, CH_)                                                                       \
     if (g.vec == VEC_ && g.g == G_ && g.ch == CH_) {                                                        \
-        if (short_bags) return launch_fwd<VEC_, G_, CH_, (CH_ == 1 ? 4 : 2), 1, true, IdxT, 0, 256, TabT>(DLRMX_FWD_ARGS);  \
+        if (short_bags) return launch_fwd<VEC_, G_, CH_, ((CH_ == 1 && VEC_ != 8) ? 4 : 2), 1, true, IdxT, 0, 256, TabT>(DLRMX_FWD_ARGS);  \
         if constexpr (CH_ == 1) return launch_fwd<VEC_, G_, CH_, 1, 8, false, IdxT, 4, 224, TabT>(DLRMX_FWD_ARGS); \
         return launch_fwd<VEC_, G_, CH_, 1, (CH_ == 2 ? 4 : 2), false, IdxT, 3, 256, TabT>(DLRMX_FWD_ARGS);           \
     }
-    DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
-    DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)
+    if constexpr (kBf16) {
+        DLRMX_FWD_CASE(8, 1, 1) DLRMX_FWD_CASE(8, 2, 1) DLRMX_FWD_CASE(8, 4, 1) DLRMX_FWD_CASE(8, 8, 1)
+        DLRMX_FWD_CASE(8, 16, 1) DLRMX_FWD_CASE(8, 32, 1) DLRMX_FWD_CASE(8, 32, 2)
+    } else {
+        DLRMX_FWD_CASE(4, 1, 1) DLRMX_FWD_CASE(4, 2, 1) DLRMX_FWD_CASE(4, 4, 1) DLRMX_FWD_CASE(4, 8, 1)
+        DLRMX_FWD_CASE(4, 16, 1) DLRMX_FWD_CASE(4, 32, 1) DLRMX_FWD_CASE(4, 32, 2) DLRMX_FWD_CASE(4, 32, 4)
+    }
     DLRMX_FWD_CASE(1, 1, 1) DLRMX_FWD_CASE(1, 2, 1) DLRMX_FWD_CASE(1, 4, 1) DLRMX_FWD_CASE(1, 8, 1)
     DLRMX_FWD_CASE(1, 16, 1) DLRMX_FWD_CASE(1, 32, 1) DLRMX_FWD_CASE(1, 32, 2) DLRMX_FWD_CASE(1, 32, 4)
 #undef DLRMX_FWD_CASE
