@@ -29,7 +29,7 @@ print("%-66s %5s %9s %7s" % ("kernel", "calls", "us", "share"))
 for n, (c, v) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print("%-66s %5d %9.1f %6.1f%%" % (n, c, v, 100 * v / tot))
 lib = lambda n: "nvjet" in n or "cublas" in n.lower() or "cutlass" in n.lower()          # noqa: E731  library GEMMs
-other = lambda n: n.startswith("at::") or "at::native" in n or "nccl" in n.lower() or "c10d" in n   # noqa: E731  torch / NCCL
+other = lambda n: "at::" in n or "nccl" in n.lower() or "c10d" in n   # noqa: E731  torch / NCCL
 ours = sum(v for n, v in step if not lib(n) and not other(n))
 print("this repo's kernels (libdlrmx: dlrmx:: and dlrmx::tc::): %.1f us (%.1f%% of the step); library GEMMs (nvjet / cuBLASLt): "
       "%.1f us; other torch kernels (fills, copies): %.1f us"
