@@ -42,7 +42,8 @@ def parse():
                     help="fused-bf16 towers: tc = the repo's tcgen05/TMEM/TMA GEMM kernels; cublas = cuBLASLt through torch, "
                          "the measured comparator (never a fallback)")
     ap.add_argument("--defer-wgrad", type=int, default=1,
-                    help="1: the top tower's weight-gradient launch moves to the end of the backward pass, beside the sparse update")
+                    help="1: the top tower's weight-gradient launch moves to the end of the backward pass, beside the sparse update; "
+                         "2: right behind the interaction backward instead (measured alternative)")
     ap.add_argument("--trace", default="", help="after the timed regions: CUPTI kernel timeline (torch.profiler) of 3 more steps, "
                     "written as text (start / duration / stream / kernel) for the LAST of them; every rank writes <trace>.rank<r>")
     ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "bf16"],
@@ -215,6 +216,9 @@ def build_model(args, cfg, W, exchange=None):
     if args.mlp == "fused-bf16":
         m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm)
         m.top_l.defer_wgrad = bool(m.top_l.defer_wgrad and args.defer_wgrad)
+        dlrm_net.FLUSH_EARLY = args.defer_wgrad == 2
+        if W == 1 and args.defer_wgrad == 1:
+            m.bot_l.defer_wgrad = True
         return m, None
     dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
     if W > 1:

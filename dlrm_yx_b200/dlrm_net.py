@@ -33,6 +33,7 @@ from . import extend_distributed as ext_dist
 # loss.backward() is ordered after the update.  Works eagerly and under CUDA-graph capture (fork / join pattern).
 _SIDE = {}
 OVERLAP_STREAMS = True        # False: everything on the caller's stream (per-kernel timing wants kernels alone)
+FLUSH_EARLY = False           # single-GPU path: True launches the top tower's deferred wgrad right behind the interaction backward
 
 
 def _side_stream(device):
@@ -169,8 +170,26 @@ class _SparseArchLocalMixed(torch.autograd.Function):
         feat, x, indices, offsets = ctx.saved_tensors
         B, F, D = feat.shape
         dfeat, dx = ops.interact_dot_bwd_mixed(feat, x, dR.contiguous(), ctx.itself, relu_x=ctx.relu_x)
-        done = _flush_deferred_wgrads()
-        _update_on_side(ctx.emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, ctx.presorted, keep=(dfeat,), after=done)
+        emb, presorted = ctx.emb, ctx.presorted
+        if FLUSH_EARLY:
+            # the top tower's deferred weight-gradient kernel right behind the interaction backward, the sparse update forked
+            # from before it (1.198 ms at the Terabyte shape: the bottom tower's dgrad GEMMs -- one 34 K-register CTA per SM --
+            # then wait ~35 us for the update's CTAs to retire and run at half speed beside it)
+            done = _flush_deferred_wgrads()
+            _update_on_side(emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, presorted, keep=(dfeat,), after=done)
+        else:
+            # the sparse update is launched when the backward pass ends: the bottom tower's dgrad GEMMs run alone (they are the
+            # only kernels here that cannot share an SM with the update's CTAs), then the weight-gradient kernels of both
+            # towers (15 K registers per SM) go out FIRST and the update fills the SMs beside them
+            from . import mlp
+            mlp._HOLD[0] = True           # the towers' own end-of-pass flush stands back: tail() decides the order
+
+            def tail():
+                mlp._HOLD[0] = False
+                done = torch.cuda.current_stream().record_event()       # the update forks from here, not from behind the wgrads
+                mlp.flush_deferred()
+                _update_on_side(emb, dfeat[:, 1:, :], indices, offsets, B, F * D, D, presorted, keep=(dfeat,), after=done)
+            torch.autograd.Variable._execution_engine.queue_callback(tail)
         ctx.presorted = None
         return dx, None, None, None, None, None, None, None
 

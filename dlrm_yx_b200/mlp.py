@@ -95,12 +95,21 @@ class _LinearAct(torch.autograd.Function):
 # with equal-priority main / side streams 1.196 ms -- the bottom tower's GEMMs starve behind the update's grid; the same
 # with a high-priority main stream 1.240 ms -- the update starves while two high-priority grids share the SMs.)
 _DEFERRED = []
+_HOLD = [False]      # set by a consumer that will flush itself, at a point of its choosing (dlrm_net's sparse arch)
 
 
-def flush_deferred():
-    for launch in _DEFERRED:
-        launch()
+def flush_deferred(force=False):
+    """Launches the deferred weight-gradient jobs, one split-K launch per tower.  (Both towers merged into ONE launch was
+    measured at the Terabyte shape: 39 tiles split 7 ways instead of 34 x 2 + 5 x 14 write 70 MB of partials beside the
+    HBM-bound sparse update -- step 1.189 -> 1.240 ms.)"""
+    if _HOLD[0] and not force:
+        return
+    jobs = list(_DEFERRED)
     _DEFERRED.clear()
+    for mlp, i0, dzs, xs, dws, dbs in jobs:
+        ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, mlp._wgrad_workspace(i0, i0 + len(dzs), dzs[0].shape[0]))
+        if i0 == 0:                    # the tower's first layers come last in the backward: its gradients are complete
+            mlp._start_allreduce()
 
 
 class _Tower(torch.autograd.Function):
@@ -152,17 +161,15 @@ class _Tower(torch.autograd.Function):
             if ctx.in_cols != layers[0].K_pad:       # the caller's input was unpadded
                 dx = dx[:, :layers[0].K]
         xs, dws, ws = list(acts[:-1]), [L.gW for L in layers], mlp._wgrad_workspace(i0, i1, dyb.shape[0])
-        def launch():
-            ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws)
-            if i0 == 0:                # the tower's first layers come last in the backward: its gradients are complete
-                mlp._start_allreduce()
         if mlp.defer_wgrad:
             # the weight gradients are needed only by step(): their launch waits for flush_deferred() -- called by the sparse
             # arch right after the interaction backward, or at the end of the pass (see there)
-            _DEFERRED.append(launch)
+            _DEFERRED.append((mlp, i0, dzs, xs, dws, dbs))
             torch.autograd.Variable._execution_engine.queue_callback(flush_deferred)
         else:
-            launch()
+            ops.gemm_wgrad_bf16(dzs, xs, dws, dbs, ws)
+            if i0 == 0:                # the tower's first layers come last in the backward: its gradients are complete
+                mlp._start_allreduce()
         return dx, None, None, None, None
 
 
