@@ -24,6 +24,9 @@
 // columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
+
+#include <utility>
 
 #include "common.cuh"
 
@@ -153,6 +156,13 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void*
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                  ::"l"(map), "r"(saddr(src)), "r"(c0), "r"(c1) : "memory");
 }
+// Programmatic dependent launch: the kernels of a tower run back to back on one stream.  Each lets the next one be launched
+// as soon as all its CTAs have got past their prologue (launch_dependents) and itself waits -- after ITS prologue: barrier
+// init, TMEM allocation, cluster sync, tensor-map prefetch, none of which touch global memory -- until the grid before it has
+// completed and flushed (grid_dependency_wait).  The launch latency and the prologue of kernel i+1 overlap the tail of
+// kernel i.  Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
@@ -270,6 +280,8 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     cluster_sync_all();            // the peer's barriers are initialised before anything arrives on them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    grid_launch_dependents();
+    grid_dependency_wait();        // everything below reads or writes global memory
 
     if (warp == 0) {
         // ===== TMA producer (both CTAs: own A rows, own half of B) =====
@@ -535,6 +547,8 @@ wgrad_splitk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P)
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    grid_launch_dependents();
+    grid_dependency_wait();
 
     if (warp == 0) {
         // ===== TMA producer (both CTAs) =====
@@ -654,6 +668,8 @@ wgrad_splitk_kernel(const __grid_constant__ WgradMaps maps, const WgradParams P)
 constexpr int kReduceRows = 8;
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const WgradParams P) {
+    grid_launch_dependents();
+    grid_dependency_wait();
     const int tile = blockIdx.x / (WM / kReduceRows);
     const int r0 = (blockIdx.x % (WM / kReduceRows)) * kReduceRows;
     const int nsegs = P.split;
@@ -729,6 +745,31 @@ static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int64_t c
     return true;
 }
 
+// Launch with programmatic stream serialization allowed (see grid_dependency_wait) when the launch is SHORT: at most
+// kPdlMaxRows batch rows.  Measured inside the whole step (profiles/r02_pdl.txt): the 2048-row step gains 5% and the 128-row
+// step 5%, because the next kernel's prologue (barrier init, TMEM allocation, descriptor prefetch) hides behind the
+// previous kernel; the 32768-row step LOSES 2%, because the early-resident CTAs of the dependent spin in
+// griddepcontrol.wait on the SMs whose tile queue ran dry, where the side stream's sparse-update CTAs used to run.
+// DLRMX_NO_PDL=1 in the environment turns it off everywhere.
+constexpr long long kPdlMaxRows = 8192;
+template <typename... KArgs, typename... Args>
+static void launch_pdl(bool allow, void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st,
+                       Args&&... args) {
+    static const bool env_off = getenv("DLRMX_NO_PDL") != nullptr && getenv("DLRMX_NO_PDL")[0] == '1';
+    const bool off = env_off || !allow;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = off ? 0 : 1;
+    cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 template <int BN, bool B_MN>
 static int launch_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const PairParams& P, cudaStream_t st) {
     using S = PairSmem<BN>;
@@ -737,7 +778,7 @@ static int launch_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUten
         cudaFuncSetAttribute(gemm_pair_kernel<BN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kBytes);
     const int tiles = (int)(ceil_div(P.M, 2 * BM) * ceil_div(P.N, BN));
     const int pairs = tiles < kSMs / 2 ? tiles : kSMs / 2;
-    gemm_pair_kernel<BN, B_MN><<<2 * pairs, kPairThreads, S::kBytes, st>>>(ma, mb, mc, P);
+    launch_pdl(P.M <= kPdlMaxRows, gemm_pair_kernel<BN, B_MN>, 2 * pairs, kPairThreads, S::kBytes, st, ma, mb, mc, P);
     return check_launch("gemm_bf16");
 }
 
@@ -849,10 +890,10 @@ int dlrmx_gemm_wgrad_bf16(int n_layers, const void* const* dZ, const int64_t* ld
         cudaFuncSetAttribute(wgrad_splitk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WgradSmem::kBytes);
     const int units = tiles * P.split;
     const int G = units < kSMs / 2 ? units : kSMs / 2;      // CTA pairs
-    wgrad_splitk_kernel<<<2 * G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream>>>(maps, P);
+    launch_pdl(M <= kPdlMaxRows, wgrad_splitk_kernel, 2 * G, kThreads, WgradSmem::kBytes, (cudaStream_t)stream, maps, P);
     if (int rc = check_launch("gemm_wgrad")) return rc;
     if (P.split > 1) {
-        wgrad_reduce_kernel<<<tiles * (WM / kReduceRows), 256, 0, (cudaStream_t)stream>>>(P);
+        launch_pdl(M <= kPdlMaxRows, wgrad_reduce_kernel, tiles * (WM / kReduceRows), 256, 0, (cudaStream_t)stream, P);
         return check_launch("gemm_wgrad_reduce");
     }
     return DLRMX_OK;
