@@ -74,6 +74,8 @@ def parse():
     ap.add_argument("--cpu-warmup", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c3-probe", action="store_true", help="skip the C3-shape embedding-bag kernel lines")
+    ap.add_argument("--tunable", action="append", default=[], metavar="K=V",
+                    help="experiments: dlrmx_set_tunable(K, V) before anything runs (include/dlrmx.h); recorded in config")
     return ap.parse_args()
 
 
@@ -834,6 +836,11 @@ def main():
         _emit(line)
         return
 
+    if args.tunable:
+        from dlrm_yx_b200 import _lib
+        for kv in args.tunable:
+            k, v = kv.split("=")
+            _lib.set_tunable(int(k), int(v))
     r = run_ours(args)
     if r["rank"] != 0:
         return
@@ -890,7 +897,7 @@ def main():
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"
                          % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * (2 if args.table_dtype == "bf16" else 4) / 1e9,
                             args.nbatches),
-                   "rows_cap": args.rows_cap or None},
+                   "rows_cap": args.rows_cap or None, **({"tunables": args.tunable} if args.tunable else {})},
         "e2e": {"value": Bg * K / (r["wall_e2e"] / 1e3), "unit": "samples/s", "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": 4, "ms_per_step": r["wall_e2e"] / K},
         "gpu_launches": r["launches"],

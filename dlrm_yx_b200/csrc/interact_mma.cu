@@ -280,6 +280,170 @@ interact_fwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int64_t fst
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// forward, bf16-facing, bulk-staged input: the kernel the training step runs.  Same arithmetic as
+// interact_fwd_mma_kernel<true, true> (bit-identical results: same k-steps per warp, same MMA order per tile, same
+// order of the four partial sums) with a third of the issued instructions.  The ncu source view of that kernel
+// (profiles/r02_ncu_full_step_summary.txt: 78.7 M warp instructions per launch = 600 per warp and sample, 4 % of
+// them MMAs) put 43 % of the instructions into the k-loop's address arithmetic and scalar fragment loads and 35 % into the
+// predicated scatter of the accumulators into the lower-triangle vector.  Here
+//   * fragments come from `ldmatrix.x4` (an 8 x 8 b16 matrix row = four fp32 of one feature row: lane (g, t) receives
+//     T[8r + g][k0 + 4h + t], which is the m16n8k8 TF32 A fragment AND, for the transposed product, the B fragment):
+//     two instructions per k-step instead of eight loads, per-lane row addresses computed once per kernel;
+//   * the bf16 x row is widened into row 0 of the tile by the warp that contracts those columns (one load, one shift, one
+//     store per lane) instead of a select inside the loop;
+//   * accumulators leave as 12 64-bit stores at constant offsets into a [tile][16][8] partial buffer; which slot of it
+//     an output element sums is computed once per thread, not per sample.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_tf32_r(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+constexpr int kFwdTileFloats = 16 * 8;                    // one m16n8 accumulator tile
+constexpr int kFwdPartFloats = 6 * kFwdTileFloats;        // lower-triangle tiles: (m0: n0 n1) (m1: n0 n1 n2 n3)
+constexpr int kFwdMaxIt = 3;                              // output pairs per thread: (out_stride - D) / 2 <= 3 * 128
+
+template <int NST>      // stages: NST - 1 samples are in flight beside the one being contracted
+__global__ void __launch_bounds__(kMmaWarps * 32, NST == 2 ? 5 : 4)
+interact_fwd_bulk_kernel(const float* __restrict__ feat, int64_t fsb, int B, int F, int D, int itself,
+                         __nv_bfloat16* __restrict__ out, int64_t ostride, const __nv_bfloat16* __restrict__ xb) {
+    extern __shared__ __align__(16) float smem[];
+    __shared__ uint64_t mbar[NST];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int DS = D + 8;                                 // the input's own row pitch (see interact_fwd_mma_kernel)
+    const int tile_floats = F * DS;
+    const int nk = D >> 5;                                // k-steps per warp: warp w contracts columns 8w + 32i .. + 7
+    const bool two_m = F > 16;
+    float* zpart = smem + NST * tile_floats;                // [kMmaWarps][kFwdPartFloats]
+    __nv_bfloat16* xs_base = reinterpret_cast<__nv_bfloat16*>(zpart + kMmaWarps * kFwdPartFloats);
+    const int nz = tri_count_mma(F, itself);
+
+    // ldmatrix row addresses (bytes from the start of a tile buffer): lane l supplies row l % 8 of matrix l / 8; matrix
+    // (r, h) = rows 8r .. 8r+7, columns k0 + 4h .. + 3; instruction p loads (2p, 0) (2p+1, 0) (2p, 1) (2p+1, 1) = the A
+    // fragment of row block p.  Rows >= F only feed discarded outputs: they alias row F - 1.
+    uint32_t ldoff[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int mi = lane >> 3, r = 2 * p + (mi & 1), h = mi >> 1;
+        ldoff[p] = (uint32_t)((min(8 * r + (lane & 7), F - 1) * DS + 4 * h + 8 * warp) * 4);
+    }
+    // which slot of a partial buffer each of this thread's output elements sums (-1: zero padding of the row)
+    int zsrc[kFwdMaxIt][2];
+#pragma unroll
+    for (int itn = 0; itn < kFwdMaxIt; ++itn)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int q = 2 * ((int)threadIdx.x + itn * kMmaWarps * 32) + e;
+            int off = -1;
+            if (q < nz) {
+                int i = itself ? 0 : 1;
+                while (tri_count_mma(i + 1, itself) <= q) ++i;           // row of the lower triangle holding element q
+                const int j = q - tri_count_mma(i, itself);
+                const int tile = (i >> 4) == 0 ? (j >> 3) : 2 + (j >> 3);
+                off = tile * kFwdTileFloats + (i & 15) * 8 + (j & 7);
+            }
+            zsrc[itn][e] = off;
+        }
+    const int npair = (int)((ostride - D) >> 1);
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < NST; ++i) mbar_init(&mbar[i], 1);
+        mbar_init_fence();
+    }
+    __syncthreads();
+    auto stage = [&](int64_t bb, int which) {             // one thread: rows 1 .. F-1 are one contiguous block
+        const uint32_t nb_rows = (uint32_t)((F - 1) * DS * 4);
+        mbar_expect_tx(&mbar[which], nb_rows + (uint32_t)(D * 2));
+        bulk_g2s(smem + which * tile_floats + DS, feat + bb * fsb + DS, nb_rows, &mbar[which]);
+        bulk_g2s(xs_base + which * D, xb + bb * D, (uint32_t)(D * 2), &mbar[which]);
+    };
+    const uint32_t smem_base = smem_u32(smem);
+    float* zp = zpart + warp * kFwdPartFloats + g * 8 + 2 * t;
+    int buf = 0;
+    uint32_t phase = 0;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < NST - 1; ++i)
+            if ((int64_t)blockIdx.x + (int64_t)i * gridDim.x < B) stage((int64_t)blockIdx.x + (int64_t)i * gridDim.x, i);
+    }
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+        // the buffer consumed last: its readers (ldmatrix, the x copy) all finished before the previous sample's barriers
+        if (threadIdx.x == 0 && b + (int64_t)(NST - 1) * gridDim.x < B)
+            stage(b + (int64_t)(NST - 1) * gridDim.x, buf == 0 ? NST - 1 : buf - 1);
+        mbar_wait(&mbar[buf], phase);
+        float* tile = smem + buf * tile_floats;
+        const __nv_bfloat16* xs = xs_base + buf * D;
+        __nv_bfloat16* ob = out + b * ostride;
+        for (int k = threadIdx.x; k < (D >> 1); k += kMmaWarps * 32)          // R[:, 0:D] = x
+            reinterpret_cast<__nv_bfloat162*>(ob)[k] = reinterpret_cast<const __nv_bfloat162*>(xs)[k];
+        // feature 0 arrives as bf16: this warp's columns of it -> fp32 row 0 of the tile
+        for (int idx = lane; idx < 8 * nk; idx += 32) {
+            const int k = 32 * (idx >> 3) + 8 * warp + (idx & 7);
+            tile[k] = __uint_as_float((uint32_t)reinterpret_cast<const unsigned short*>(xs)[k] << 16);
+        }
+        __syncwarp();
+
+        float c[6][4];
+#pragma unroll
+        for (int n = 0; n < 6; ++n)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) c[n][q] = 0.f;
+        const uint32_t tb = smem_base + (uint32_t)(buf * tile_floats * 4);
+        uint32_t ad0 = tb + ldoff[0], ad1 = tb + ldoff[1];
+#pragma unroll 4
+        for (int i = 0; i < nk; ++i, ad0 += 128, ad1 += 128) {
+            uint32_t a0[4], a1[4];
+            ldsm_x4(ad0, a0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) a0[q] += 0x1000u;             // round to nearest TF32 (low 13 bits are ignored)
+            mma_tf32_r(c[0], a0, a0[0], a0[2]);
+            mma_tf32_r(c[1], a0, a0[1], a0[3]);
+            if (two_m) {
+                ldsm_x4(ad1, a1);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) a1[q] += 0x1000u;
+                mma_tf32_r(c[2], a1, a0[0], a0[2]);
+                mma_tf32_r(c[3], a1, a0[1], a0[3]);
+                mma_tf32_r(c[4], a1, a1[0], a1[2]);
+                mma_tf32_r(c[5], a1, a1[1], a1[3]);
+            }
+        }
+        __syncthreads();            // the previous sample's partials have been summed by every thread
+#pragma unroll
+        for (int n = 0; n < 6; ++n) {
+            if (n >= 2 && !two_m) break;
+            *reinterpret_cast<float2*>(zp + n * kFwdTileFloats) = make_float2(c[n][0], c[n][1]);
+            *reinterpret_cast<float2*>(zp + n * kFwdTileFloats + 64) = make_float2(c[n][2], c[n][3]);
+        }
+        __syncthreads();
+        // bf16 pairs; the tail of the row up to ostride (the top MLP's padded K) is zero-filled
+#pragma unroll
+        for (int itn = 0; itn < kFwdMaxIt; ++itn) {
+            const int q2 = (int)threadIdx.x + itn * kMmaWarps * 32;
+            if (q2 >= npair) break;
+            float v[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int o = zsrc[itn][e];
+                v[e] = o >= 0 ? __fadd_rn(__fadd_rn(zpart[o], zpart[kFwdPartFloats + o]),
+                                          __fadd_rn(zpart[2 * kFwdPartFloats + o], zpart[3 * kFwdPartFloats + o]))
+                              : 0.f;
+            }
+            reinterpret_cast<__nv_bfloat162*>(ob + D)[q2] = __floats2bfloat162_rn(v[0], v[1]);
+        }
+        if (++buf == NST) { buf = 0; phase ^= 1u; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // backward:  dfeat[b, i, :] = sum_j S[i][j] * feat[b, j, :]  (+ dR[b, :D] on i = 0),  S = dZ + dZ^t
 // One CTA per sample; the D output columns are split across the 4 warps in 8-column tiles.
 // ---------------------------------------------------------------------------------------------------------
@@ -499,12 +663,25 @@ interact_bwd_mma_kernel(const float* __restrict__ feat, int64_t fsb, int64_t fst
 }
 
 // tunable 10 = 1: per-thread cp.async staging instead of TMA bulk copies; tunable 11: CTAs per SM of the persistent grid
-enum { DLRMX_TUNE_IX_STAGE = 10, DLRMX_TUNE_IX_GRID = 11 };
+// tunable 12 = 1: the bulk-staged forward runs interact_fwd_mma_kernel<true, true> instead of interact_fwd_bulk_kernel (tests
+// compare); 2: interact_fwd_bulk_kernel with two stages even where three fit
+enum { DLRMX_TUNE_IX_STAGE = 10, DLRMX_TUNE_IX_GRID = 11, DLRMX_TUNE_IX_FWD = 12 };
 static bool use_bulk() { return get_tunable(DLRMX_TUNE_IX_STAGE) != 1; }
 
 static int mma_grid(int B) {
     const int per_sm = get_tunable(DLRMX_TUNE_IX_GRID) > 0 ? get_tunable(DLRMX_TUNE_IX_GRID) : 12;
     const int64_t cap = (int64_t)kSMs * per_sm;  // persistent: a few CTAs per SM, each loops over samples
+    return (int)(B < cap ? B : cap);
+}
+
+// interact_fwd_bulk_kernel: persistent, as many CTAs as stay resident (5 per SM at the Terabyte shape's 42 KB)
+static int fwd_bulk_grid(int B, size_t smem, int max_per_sm) {
+    int per_sm = get_tunable(DLRMX_TUNE_IX_GRID);
+    if (per_sm <= 0) {
+        per_sm = (int)((size_t)228 * 1024 / (smem + 1024 + 64));
+        per_sm = per_sm < 1 ? 1 : (per_sm > max_per_sm ? max_per_sm : per_sm);
+    }
+    const int64_t cap = (int64_t)kSMs * per_sm;
     return (int)(B < cap ? B : cap);
 }
 
@@ -568,6 +745,28 @@ int interact_fwd_mixed(const float* feat, int64_t fsb, int64_t fst, const void* 
     if (once.first()) {
         cudaFuncSetAttribute(interact_fwd_mma_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         cudaFuncSetAttribute(interact_fwd_mma_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    }
+    if (padded && get_tunable(DLRMX_TUNE_IX_FWD) != 1 && (ostride - D) / 2 <= kFwdMaxIt * kMmaWarps * 32) {
+        // three stages (two samples in flight per CTA) where four such CTAs fit an SM, else two
+        const size_t per_stage = (size_t)F * (D + 8) * 4 + (size_t)D * 2;
+        const size_t fixed = (size_t)kMmaWarps * kFwdPartFloats * 4;
+        const bool three = get_tunable(DLRMX_TUNE_IX_FWD) != 2 && 4 * (3 * per_stage + fixed + 1024 + 64) <= (size_t)228 * 1024;
+        const size_t smem2 = (three ? 3 : 2) * per_stage + fixed;
+        static DeviceOnce once2;
+        if (once2.first()) {
+            cudaFuncSetAttribute(interact_fwd_bulk_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            cudaFuncSetAttribute(interact_fwd_bulk_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        }
+        if (smem2 <= 200 * 1024) {
+            const int grid = fwd_bulk_grid(B, smem2, three ? 4 : 5);
+            if (three)
+                interact_fwd_bulk_kernel<3><<<grid, kMmaWarps * 32, smem2, st>>>(
+                    feat, fsb, B, F, D, itself, (__nv_bfloat16*)out_bf16, ostride, (const __nv_bfloat16*)x_bf16);
+            else
+                interact_fwd_bulk_kernel<2><<<grid, kMmaWarps * 32, smem2, st>>>(
+                    feat, fsb, B, F, D, itself, (__nv_bfloat16*)out_bf16, ostride, (const __nv_bfloat16*)x_bf16);
+            return check_launch("interact_dot_fwd_mixed");
+        }
     }
     if (padded)
         interact_fwd_mma_kernel<true, true><<<mma_grid(B), kMmaWarps * 32, smem, st>>>(
