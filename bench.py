@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU mini-batch (default: the config's)")
     ap.add_argument("--global-batch", type=int, default=0, help="fix the GLOBAL batch (strong scaling)")
     ap.add_argument("--rows-cap", type=int, default=0, help="cap rows per table (debug only; marks the run)")
+    ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"],
+                    help="data-parallel gradient sums (towers, replicated tables) at N > 1: the repo's kernel over NVLink peer "
+                         "memory (csrc/peer_allreduce.cu) or NCCL (comparator)")
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"],
                     help="fused-bf16 towers: tc = the repo's tcgen05/TMEM/TMA GEMM kernels; cublas = cuBLASLt through torch, "
                          "the measured comparator (never a fallback)")
@@ -216,7 +219,7 @@ def build_model(args, cfg, W, exchange=None):
         lb = cfg["B"] if not args.global_batch else args.global_batch // W
         m.enable_peer_exchange(lb, mixed=(args.mlp == "fused-bf16"))
     if args.mlp == "fused-bf16":
-        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm)
+        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm, allreduce=args.allreduce)
         m.top_l.defer_wgrad = bool(m.top_l.defer_wgrad and args.defer_wgrad)
         dlrm_net.FLUSH_EARLY = args.defer_wgrad == 2
         if W == 1 and args.defer_wgrad == 1:
@@ -890,8 +893,10 @@ def main():
                    "index_distribution": args.index_dist,
                    "parallelism": "single GPU" if W == 1 else "table-wise model parallel x%d (%s sharder) for the %d tables "
                    "with >= %d rows, the other %d replicated on every rank (local lookups, dense-gradient all-reduce); "
-                   "data-parallel MLPs (flat-gradient all-reduce); %s" % (
+                   "data-parallel MLPs (flat-gradient all-reduce); all-reduces: %s; %s" % (
                        W, args.sharder, len(cfg["rows"]) - len(r["rep_tables"]), args.replicate_below, len(r["rep_tables"]),
+                       ("own two-shot kernel over NVLink peer memory" if (args.allreduce == "peer" and args.mlp == "fused-bf16")
+                        else "NCCL"),
                        "exchange fused into the lookup / gradient kernels over NVLink peer memory"
                        if args.exchange == "peer" else "NCCL all-to-all"),
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"

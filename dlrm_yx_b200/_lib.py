@@ -84,6 +84,7 @@ SIGNATURES = {
                                     c_void_p, c_void_p]),
     "dlrmx_a2a_push_grad": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     ctypes.POINTER(c_void_p), c_void_p]),
+    "dlrmx_peer_allreduce": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, c_int64, c_int, c_void_p]),
     "dlrmx_bce_mean_workspace_bytes": (c_size_t, [c_int64]),
     "dlrmx_bce_mean_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dlrmx_bce_mean_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),

@@ -18,7 +18,7 @@ CSRC = os.path.join(PKG, "csrc")
 OBJ = os.path.join(ROOT, "build", "obj")
 LIB = os.path.join(PKG, "libdlrmx.so")
 SOURCES = ["api.cu", "embbag_fwd_i32.cu", "embbag_fwd_i64.cu", "embbag_fwd_bf16_i32.cu", "embbag_fwd_bf16_i64.cu", "radix_sort.cu", "segments.cu", "embbag_bwd.cu", "interact.cu", "interact_mma.cu", "mlp_fused.cu", "gemm_tc.cu",
-           "a2a_layout.cu", "criteo_bin.cu", "embbag_psw.cu", "loss.cu"]
+           "a2a_layout.cu", "peer_allreduce.cu", "criteo_bin.cu", "embbag_psw.cu", "loss.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

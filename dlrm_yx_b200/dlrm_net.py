@@ -421,7 +421,7 @@ class DLRM_Net(nn.Module):
     def apply_mlp(self, x, layers):
         return layers(x)
 
-    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10, gemm="tc"):
+    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10, gemm="tc", allreduce="peer"):
         """Replaces the two nn.Sequential towers by FusedMLP (bf16 tensor-core GEMMs with fused epilogues, flat
         parameter buffers, one-kernel optimizer step).  After this, call `step_mlps()` instead of putting the tower
         parameters into an outer optimizer."""
@@ -443,6 +443,17 @@ class DLRM_Net(nn.Module):
             self.bot_l.dp_world = self.top_l.dp_world = ext_dist.my_size
         if self.emb_rep is not None and self._mixed:
             self.emb_rep.wire_bf16 = True              # mixed-precision mode: the replicated tables' gradients cross NVLink as bf16
+        if allreduce not in ("peer", "nccl"):
+            raise ValueError("allreduce must be 'peer' (own kernel over NVLink peer memory) or 'nccl'")
+        if allreduce == "peer" and ext_dist.my_size > 1:
+            # the three data-parallel sums of a step (two towers, replicated tables) leave NCCL: gradient buffers in
+            # symmetric memory, ext_dist.PeerAllReduce
+            dev = self.bot_l.master.device
+            self.bot_l.use_peer_allreduce(ext_dist.PeerAllReduce(self.bot_l.numel, torch.float32, dev))
+            self.top_l.use_peer_allreduce(ext_dist.PeerAllReduce(self.top_l.numel, torch.float32, dev))
+            if self.emb_rep is not None:
+                self.emb_rep.peer_ar = ext_dist.PeerAllReduce(
+                    self.emb_rep.grad_sum.numel(), torch.bfloat16 if self.emb_rep.wire_bf16 else torch.float32, dev)
         return self
 
     def step_mlps(self):

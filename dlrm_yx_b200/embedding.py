@@ -187,6 +187,7 @@ class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
         self.register_buffer("grad_sum", torch.zeros_like(self.embedding_weights.data), persistent=False)
         self._gts = None
         self.wire_bf16 = False      # True: the gradient all-reduce moves bf16 (set with the bf16 towers, DLRM_Net.fuse_mlps)
+        self.peer_ar = None         # ext_dist.PeerAllReduce over grad_sum.numel() elements (bf16 iff wire_bf16): own kernel, no NCCL
 
     def _grad_table_set(self):
         if self._gts is None or self._gts_key != self.grad_sum.data_ptr():
@@ -225,7 +226,14 @@ class ReplicatedTableBatchedEmbeddingBags(TableBatchedEmbeddingBags):
             comm_stream.wait_stream(cur)
         with torch.cuda.stream(comm_stream):
             if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-                if self.wire_bf16:
+                if self.peer_ar is not None:
+                    # the repo's own two-shot sum over NVLink peer memory (csrc/peer_allreduce.cu): the partial sums go into
+                    # the symmetric buffer (rounded to bf16 in the mixed-precision mode: half the bytes), are added in fp32
+                    # in rank order and rounded once; every replica receives the same bits
+                    self.peer_ar.buf.copy_(self.grad_sum)
+                    self.peer_ar.allreduce()
+                    self.grad_sum.copy_(self.peer_ar.buf)
+                elif self.wire_bf16:
                     # bf16 on the wire (the towers' mixed-precision mode only): every rank's partial sums are rounded to
                     # bf16 before they are added, the sum is widened back -- half the NVLink bytes of the one collective
                     # that is as large as the tables themselves; replicas stay bit-identical (NCCL's result is)

@@ -290,6 +290,43 @@ class PeerExchange(object):
         return self.grad
 
 
+class PeerAllReduce(object):
+    """Sum of one flat buffer over the data-parallel replicas WITHOUT a collective library: the buffer lives in
+    peer-mapped (symmetric) memory, rank r adds slice r of every rank's buffer in rank order and stores the sum into
+    every rank's buffer (csrc/peer_allreduce.cu), between two device barriers.  Stands where DistributedDataParallel's
+    all-reduce stands for the reference's towers (dlrm_s_pytorch.py:1606-1613).  In place on `self.buf` ([numel], fp32
+    or bf16): producers write their operand there, `allreduce()` is stream-ordered, every rank ends with the same bits.
+    One instance per buffer; allocate once (symmetric allocations are collective)."""
+
+    def __init__(self, numel, dtype, device, group=None):
+        if dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("PeerAllReduce: fp32 or bf16 buffers")
+        self.W, self.rank = max(my_size, 1), max(my_rank, 0)
+        per16 = 8 if dtype == torch.bfloat16 else 4
+        self.numel = int(numel)
+        n = (self.numel + per16 - 1) // per16 * per16
+        if self.W > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.group = dist.group.WORLD if group is None else group
+            self._flat = symm_mem.empty(n, dtype=dtype, device=device)
+            self._flat.zero_()
+            self.h = symm_mem.rendezvous(self._flat, self.group)
+            self.ptrs = [int(q) for q in self.h.buffer_ptrs]
+        else:
+            self._flat, self.h = torch.zeros(n, dtype=dtype, device=device), None
+            self.ptrs = [self._flat.data_ptr()]
+        self.buf = self._flat[:self.numel]
+
+    def allreduce(self):
+        with record_function("DLRM peer_allreduce"):
+            if self.h is not None:
+                self.h.barrier()               # every rank's operand is complete; nobody still reads the previous sum
+            ops.peer_allreduce(self.ptrs, self.rank, self._flat.numel(), self._flat.dtype == torch.bfloat16)
+            if self.h is not None:
+                self.h.barrier()               # every remote store has landed
+        return self.buf
+
+
 def all_gather(input, lengths=None, dim=0):
     """Concatenation of every rank's tensor along `dim` (extend_distributed.py:642-645); `lengths[p]` gives
     rank p's extent when they differ."""

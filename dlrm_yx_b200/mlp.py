@@ -218,6 +218,7 @@ class FusedMLP(nn.Module):
         self.defer_wgrad = False    # True: the wgrad launch waits for flush_deferred() (see there)
         self.dp_world = 1           # > 1: data-parallel replicas; the backward pass starts the gradient all-reduce itself
         self._ar_stream = None
+        self.peer_ar = None         # ext_dist.PeerAllReduce: the gradient buffer lives in peer-mapped memory (use_peer_allreduce)
         self._ws = {}
         mods = list(sequential)
         if len(mods) % 2 or not all(isinstance(m, nn.Linear) for m in mods[0::2]):
@@ -314,6 +315,25 @@ class FusedMLP(nn.Module):
             i += 1
         return h if (h.dtype == torch.float32 or self.out_bf16) else h.float()
 
+    def use_peer_allreduce(self, par):
+        """The flat gradient buffer moves into `par` (ext_dist.PeerAllReduce, fp32, numel = self.numel): the weight-gradient
+        kernels write there and the data-parallel sum is the repo's own kernel over NVLink peer memory instead of NCCL.
+        (.to() / .cuda() afterwards would move the gradients back into ordinary memory: call this last.)"""
+        if par.buf.dtype != torch.float32 or par.buf.numel() != self.numel:
+            raise _lib.DlrmxError("use_peer_allreduce: needs an fp32 buffer of %d elements" % self.numel)
+        par.buf.copy_(self.grad)
+        self.grad = par.buf
+        self.peer_ar = par
+        self._ws = {}
+        self._bind()
+        return self
+
+    def _allreduce_grad(self):
+        if self.peer_ar is not None:
+            self.peer_ar.allreduce()
+        else:
+            dist.all_reduce(self.grad)
+
     def _start_allreduce(self):
         """Data-parallel replicas (dp_world > 1): the all-reduce of the flat gradient buffer starts as soon as the tower's
         backward has written it, on a communication stream beside the rest of the backward pass; step() joins it."""
@@ -325,7 +345,7 @@ class FusedMLP(nn.Module):
         if comm != cur:
             comm.wait_stream(cur)
         with torch.cuda.stream(comm):
-            dist.all_reduce(self.grad)
+            self._allreduce_grad()
         self._ar_stream = comm
 
     @torch.no_grad()
@@ -338,7 +358,7 @@ class FusedMLP(nn.Module):
                 torch.cuda.current_stream().wait_stream(self._ar_stream)
                 self._ar_stream = None
             else:
-                dist.all_reduce(self.grad)
+                self._allreduce_grad()
             scale = 1.0 / world_size          # DDP averages the replicas' gradients
         ops.dense_opt(self.mode, self.master.data, self.acc if self.mode == 1 else None, self.grad, self.shadow,
                       self.lr, self.eps, scale)

@@ -362,6 +362,17 @@ def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases):
         _lib.check(rc, "dlrmx_a2a_push_grad")
 
 
+def peer_allreduce(peer_ptrs, rank, numel, is_bf16):
+    """In-place sum over the ranks' peer-mapped buffers (peer_ptrs[p] = rank p's buffer); the caller brackets the call with
+    device barriers (extend_distributed.PeerAllReduce does)."""
+    if not torch.cuda.is_available():
+        raise _lib.DlrmxError("peer_allreduce needs CUDA (no CPU fallback)")
+    ptrs = (ctypes.c_void_p * len(peer_ptrs))(*[int(b) for b in peer_ptrs])
+    with _timed("peer_allreduce"):
+        rc = _lib.load().dlrmx_peer_allreduce(ptrs, len(peer_ptrs), int(rank), int(numel), 1 if is_bf16 else 0, _stream())
+        _lib.check(rc, "dlrmx_peer_allreduce")
+
+
 def a2a_unpack(recv, tables_per_rank, lb, D, dst, feat_off):
     """recv = concat_p [lb, T_p, D]  ->  dst[:, feat_off + t, :] (rank-major table order)."""
     _need_cuda(recv, dst)

@@ -340,6 +340,22 @@ int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfea
                         float* const* host_peer_chunk_bases, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Data-parallel gradient all-reduce over NVLink peer memory (csrc/peer_allreduce.cu).  Replaces the
+ * all-reduce DistributedDataParallel runs for the reference's replicated MLP towers
+ * (dlrm_s_pytorch.py:1606-1613, DDP(bot_l) / DDP(top_l); extend_distributed.py:110-166 sets the
+ * process group up) -- and serves the replicated small tables' dense row gradients of this repo.
+ * host_peer_buffers = HOST array [W] of peer-mapped device pointers, entry p = rank p's buffer
+ * (entry `rank` = the caller's own), all of `numel` elements (fp32, or bf16 when is_bf16), 16-byte
+ * aligned, numel a multiple of 4 (fp32) / 8 (bf16).  In place: on return (stream-ordered, and after
+ * the caller's closing barrier) every buffer holds the element-wise sum, added in rank order
+ * 0 .. W-1 in fp32 (bf16: widened, added, rounded once) -- bit-identical on every rank.
+ * The caller brackets the call with device barriers over the W ranks on the same stream: BEFORE
+ * (every rank's operand is complete) and AFTER (every remote store has landed).  W = 1: no-op sum.
+ * ------------------------------------------------------------------------------------------- */
+int dlrmx_peer_allreduce(void* const* host_peer_buffers, int W, int rank, int64_t numel, int is_bf16,
+                         dlrmx_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Loss: binary cross-entropy, mean reduction.  Replaces dlrm.loss_fn = torch.nn.BCELoss(reduction="mean")
  * (dlrm_s_pytorch.py:505-507, called through loss_fn_wrap 170-173) and its backward: one kernel each way instead of
  * five element-wise / reduce launches, same arithmetic as ATen (log clamped at -100, gradient denominator at 1e-12).

@@ -495,3 +495,30 @@ def test_bf16_table_rows_match_the_fp32_path_on_widened_tables(D, L, opt):
         touched[torch.from_numpy(idx[k * B * L:(k + 1) * B * L].astype(np.int64)).to(dev)] = True
         assert torch.equal(Wb[k][~touched], before[k][~touched])
     ops.check_index_errors()
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 8])
+@pytest.mark.parametrize("dtype,numel", [("fp32", 4 * 100003), ("fp32", 8), ("bf16", 8 * 50021), ("bf16", 8)])
+def test_peer_allreduce_rank_order_sum_on_one_device(W, dtype, numel):
+    """dlrmx_peer_allreduce with W buffers of ONE device standing in for the peers (the kernel only sees pointers; the
+    slices the ranks own are disjoint, so running the W "ranks" one after the other is the same computation): every
+    buffer must end up with the fp32 sum in rank order 0 .. W-1 (bf16: widened, added, rounded once) -- bit for bit,
+    including slices shorter than a rank's share (numel = 8) and -0."""
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    td = torch.float32 if dtype == "fp32" else torch.bfloat16
+    g = torch.Generator(device=dev).manual_seed(W * 7 + numel)
+    bufs = [(torch.randn(numel, device=dev, generator=g) * 3).to(td) for _ in range(W)]
+    for b in bufs:
+        b[3] = -0.0
+    acc = bufs[0].float()
+    for b in bufs[1:]:
+        acc = acc + b.float()
+    ref = acc.to(td)
+    ptrs = [b.data_ptr() for b in bufs]
+    for r in range(W):
+        ops.peer_allreduce(ptrs, r, numel, td == torch.bfloat16)
+    torch.cuda.synchronize()
+    view = torch.int32 if td == torch.float32 else torch.int16
+    for b in bufs:
+        assert torch.equal(b.view(view), ref.view(view))

@@ -35,3 +35,17 @@ def test_exchange_paths_match_each_other_and_the_reference(name, sharders):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("exchange parity OK") == W
+
+
+def test_peer_allreduce_matches_the_rank_order_sum():
+    """ext_dist.PeerAllReduce (own two-shot kernel over NVLink peer memory) on every GPU of the box: bit-equal to the
+    rank-order fp32 sum of the operands, eager and as a replayed graph, NCCL's result within rounding (tools/check_allreduce.py)."""
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    W = 8 if n >= 8 else (4 if n >= 4 else 2)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(W), "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tools", "check_allreduce.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("allreduce parity OK") == W

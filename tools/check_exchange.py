@@ -68,6 +68,7 @@ class Case(object):
         assert self.B % self.W == 0, "fixture batch %d not divisible by %d ranks" % (self.B, self.W)
         self.lb = self.B // self.W
         self.tower_gemm = "tc"
+        self.allreduce = "peer"
 
     def build(self, sharder, exchange, bf16, replicate_below):
         g, dev = self.g, self.dev
@@ -97,7 +98,7 @@ class Case(object):
             m.enable_peer_exchange(self.lb, mixed=bool(bf16))
         opt = None
         if bf16:
-            m.fuse_mlps(self.lr, "sgd" if self.sgd else "adagrad", gemm=self.tower_gemm)
+            m.fuse_mlps(self.lr, "sgd" if self.sgd else "adagrad", gemm=self.tower_gemm, allreduce=self.allreduce)
         else:
             dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
             m.bot_l = ext.DDP(m.bot_l, device_ids=[dev.index])
@@ -198,6 +199,7 @@ def main():
     ap.add_argument("--replicate-below", type=int, default=100)
     ap.add_argument("--out", default="")
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"], help="GEMMs of the fused bf16 towers (cublas: comparator)")
+    ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"], help="gradient sums of the fused towers / replicated tables")
     ap.add_argument("--losses-only", action="store_true", help="debug: print the bf16 variants' losses instead of asserting")
     args = ap.parse_args()
     ext.init_distributed(use_gpu=True, backend="nccl")
@@ -206,6 +208,7 @@ def main():
     torch.backends.cuda.matmul.allow_tf32 = False
     c = Case(args.case, dev)
     c.tower_gemm = args.tower_gemm
+    c.allreduce = args.allreduce
     report = {"case": args.case, "world_size": W, "steps": args.steps, "checks": []}
 
     def note(msg):
