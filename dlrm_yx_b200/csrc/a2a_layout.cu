@@ -122,8 +122,11 @@ int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfea
     const int T = rs.first_table[W];
     if (lb == 0 || T == 0) return DLRMX_OK;
     const int64_t total = (int64_t)lb * T * (vec ? D / 4 : D);
+    // many short-lived CTAs (one or two elements per thread) rather than a persistent grid: the gradient all-reduces run
+    // beside this kernel at a higher stream priority and get an SM slot whenever one of these CTAs retires (with 16 CTAs
+    // per SM looping, the all-reduce kernel waited ~0.1 ms for its first slot: profiles/r02_timeline_n8_peer_ar_rank0.txt)
     int64_t nblk = ceil_div(total, 256);
-    if (nblk > (int64_t)kSMs * 16) nblk = (int64_t)kSMs * 16;
+    if (nblk > (int64_t)kSMs * 512) nblk = (int64_t)kSMs * 512;
     cudaStream_t st = (cudaStream_t)stream;
     if (vec) a2a_push_kernel<4><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
     else     a2a_push_kernel<1><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);

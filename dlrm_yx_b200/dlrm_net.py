@@ -48,13 +48,16 @@ def _side_stream(device):
 _COMM = {}
 
 
-def _comm_stream(device):
-    """Stream of the collectives that run beside compute (gradient all-reduces)."""
+def _comm_stream(device, which=0):
+    """Streams of the gradient all-reduces that run beside compute: 0 = the towers', 1 = the replicated tables' (each
+    chain is barrier -> sum -> barrier -> consumer, and the two do not depend on each other).  High priority: their
+    kernels are small and latency-bound (device barriers, NVLink round trips) and must not queue behind the grids of the
+    gradient push / sparse update they run beside."""
     if not OVERLAP_STREAMS:
         return torch.cuda.current_stream()
-    s = _COMM.get(device)
+    s = _COMM.get((device, which))
     if s is None:
-        s = _COMM[device] = torch.cuda.Stream(device=device)
+        s = _COMM[(device, which)] = torch.cuda.Stream(device=device, priority=-1)
     return s
 
 
@@ -250,7 +253,7 @@ class _DistInteract(torch.autograd.Function):
 
         def sparse_updates():                 # on the side stream
             cur = torch.cuda.current_stream()
-            comm = _comm_stream(dfeat.device)
+            comm = _comm_stream(dfeat.device, 1)
             if step.rep is not None:
                 # replicated tables first: their gradient all-reduce (62 MB at the Terabyte shape, ~0.26 ms on 8 GPUs) and
                 # row update go to the communication stream and run beside the push / update of the sharded tables
