@@ -48,6 +48,9 @@ SIGNATURES = {
     "dlrmx_bwd_update_bf16": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p, c_int64,
                                       c_int64, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float, c_void_p, c_size_t,
                                       c_void_p]),
+    "dlrmx_bwd_update_ex": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p,
+                                    c_int64, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_float, c_float, c_void_p,
+                                    c_size_t, c_void_p]),
     "dlrmx_bwd_coalesce": (c_int, [c_int, c_int, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_void_p, c_void_p]),
     "dlrmx_rows_update": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_float,
@@ -84,6 +87,8 @@ SIGNATURES = {
                                     c_void_p, c_void_p]),
     "dlrmx_a2a_push_grad": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
                                     ctypes.POINTER(c_void_p), c_void_p]),
+    "dlrmx_a2a_push_grad_bf16": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, ctypes.POINTER(c_int), c_int, c_int,
+                                         ctypes.POINTER(c_void_p), c_void_p]),
     "dlrmx_peer_allreduce": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, c_int64, c_int, c_void_p]),
     "dlrmx_bce_mean_workspace_bytes": (c_size_t, [c_int64]),
     "dlrmx_bce_mean_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -7,6 +7,8 @@
 // side is one pass that drops every source rank's [lb, T_p, D] chunk into its feature slots of the
 // [lb, 1+T, D] interaction input (rank-major table order, as the reference's cat produces), and the
 // backward is the mirror image.  Pure copy: 2 * lb*T*D*4 bytes of HBM traffic.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace dlrmx {
@@ -50,7 +52,9 @@ struct PeerBases {
     float* base[kMaxRanks];      // where this rank's [lb, T_p, D] chunk starts inside rank p's buffer
 };
 
-template <int VEC>
+// OUT_BF16: the rows cross NVLink as bf16 (rounded to nearest even here, widened exactly by the update kernel that reads
+// them: dlrmx_bwd_update_ex, grad_is_bf16) -- half the bytes of the one transfer the backward pass waits for.
+template <int VEC, bool OUT_BF16 = false>
 __global__ void __launch_bounds__(256)
 a2a_push_kernel(const float* __restrict__ block, int64_t bsb, int64_t bsf, int feat_off, RankSplit rs, PeerBases pb, int lb,
                 int D) {
@@ -66,11 +70,12 @@ a2a_push_kernel(const float* __restrict__ block, int64_t bsb, int64_t bsf, int f
         int p = 0;
         while (t >= rs.first_table[p + 1]) ++p;
         const int tp = rs.first_table[p + 1] - rs.first_table[p];
-        float* c = pb.base[p] + ((int64_t)b * tp + (t - rs.first_table[p])) * D + d * VEC;
+        const int64_t coff = ((int64_t)b * tp + (t - rs.first_table[p])) * D + d * VEC;
         const float* f = block + (int64_t)b * bsb + (int64_t)(feat_off + t) * bsf + d * VEC;
         RowVec<VEC> v;
         v.load_stream(f);
-        v.store(c);
+        if (OUT_BF16) v.store(reinterpret_cast<__nv_bfloat16*>(pb.base[p]) + coff);
+        else v.store(pb.base[p] + coff);
     }
 }
 
@@ -101,9 +106,9 @@ static int a2a_layout(float* chunks, float* block, int64_t bsb, int64_t bsf, int
 }  // namespace dlrmx
 
 extern "C" {
-int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
-                        const int* host_tables_per_rank, int lb, int D, float* const* host_peer_chunk_bases,
-                        dlrmx_stream_t stream) {
+static int a2a_push_impl(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
+                         const int* host_tables_per_rank, int lb, int D, float* const* host_peer_chunk_bases, bool out_bf16,
+                         dlrmx_stream_t stream) {
     using namespace dlrmx;
     DLRMX_REQUIRE(W >= 1 && W <= kMaxRanks, "a2a_push_grad: W=%d out of range", W);
     DLRMX_REQUIRE(lb >= 0 && D >= 1 && dfeat_stride_f >= D && host_peer_chunk_bases != nullptr, "a2a_push_grad: bad arguments");
@@ -128,9 +133,30 @@ int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfea
     int64_t nblk = ceil_div(total, 256);
     if (nblk > (int64_t)kSMs * 512) nblk = (int64_t)kSMs * 512;
     cudaStream_t st = (cudaStream_t)stream;
+    if (out_bf16) {
+        DLRMX_REQUIRE(vec && D % 8 == 0, "a2a_push_grad_bf16: needs D %% 8 == 0 and 16-byte aligned buffers and strides");
+        const int64_t total8 = (int64_t)lb * T * (D / 8);
+        int64_t nb8 = ceil_div(total8, 256);
+        if (nb8 > (int64_t)kSMs * 512) nb8 = (int64_t)kSMs * 512;
+        a2a_push_kernel<8, true><<<(unsigned)nb8, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
+        return check_launch("a2a_push_grad_bf16");
+    }
     if (vec) a2a_push_kernel<4><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
     else     a2a_push_kernel<1><<<(unsigned)nblk, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
     return check_launch("a2a_push_grad");
+}
+
+int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
+                        const int* host_tables_per_rank, int lb, int D, float* const* host_peer_chunk_bases,
+                        dlrmx_stream_t stream) {
+    return a2a_push_impl(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, W, host_tables_per_rank, lb, D, host_peer_chunk_bases,
+                         false, stream);
+}
+int dlrmx_a2a_push_grad_bf16(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
+                             const int* host_tables_per_rank, int lb, int D, void* const* host_peer_chunk_bases_bf16,
+                             dlrmx_stream_t stream) {
+    return a2a_push_impl(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, W, host_tables_per_rank, lb, D,
+                         reinterpret_cast<float* const*>(host_peer_chunk_bases_bf16), true, stream);
 }
 
 int dlrmx_a2a_unpack(const float* recv, int W, const int* host_tables_per_rank, int lb, int D, float* dst,

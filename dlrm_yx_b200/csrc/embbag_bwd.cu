@@ -25,7 +25,7 @@ __device__ __forceinline__ T bshfl64(unsigned mask, T v, int src) {
 enum { kHasHead = 1, kHeadClosed = 2, kHasTail = 4, kActive = 8 };
 
 // EXACT: D == VEC*G*CH, every lane owns columns of the row (no per-lane guard in the loop).
-template <int VEC, int G, int CH, int K, int OCC = 0, bool EXACT = false>
+template <int VEC, int G, int CH, int K, int OCC = 0, bool EXACT = false, bool GBF = false>
 __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) bwd_update_kernel(const BwdParams P) {
     constexpr int GPC = 256 / G;             // groups (= segments) per CTA
     extern __shared__ __align__(16) float sh_part[];     // [2][GPC][D]: head partials, tail partials
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
             last = knext != key;
             const int t = bag / P.B;
             const int b = bag - t * P.B;
-            gptr = P.grad + (int64_t)b * P.stride_b + (int64_t)t * P.stride_t;    // row start; col0 added after broadcast
+            gptr = grad_off<GBF>(P.grad, (int64_t)b * P.stride_b + (int64_t)t * P.stride_t);    // row start; col0 added after broadcast
             if (last) run_target(P, key, bag, wptr, mptr);
         }
         const unsigned lastmask = (__ballot_sync(gmask, last) >> gshift);
@@ -88,11 +88,11 @@ __global__ void __launch_bounds__(256, OCC > 0 ? OCC : ((K * CH <= 4) ? 3 : 2)) 
                 wp[j] = nullptr;
                 mp[j] = nullptr;
                 mo[j] = 0.f;
-                const float* gp = bshfl64<const float*, G>(gmask, gptr, jj & (G - 1)) + col0;
+                const float* gp = grad_off<GBF>(bshfl64<const float*, G>(gmask, gptr, jj & (G - 1)), col0);
                 if (v[j]) {
 #pragma unroll
                     for (int c = 0; c < CH; ++c)
-                        if (EXACT || col0 + c * G * VEC < P.D) g[j][c].load_ro(gp + c * G * VEC);
+                        if (EXACT || col0 + c * G * VEC < P.D) load_grad<GBF, VEC>(g[j][c], grad_off<GBF>(gp, c * G * VEC));
                 }
                 if (l[j]) {
                     wp[j] = tab_off(P, bshfl64<float*, G>(gmask, wptr, jj & (G - 1)), col0);
@@ -378,7 +378,7 @@ rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict__ mom
     const int64_t row = rows[u];
     BwdParams P;
     P.optimizer = optimizer; P.D = D; P.ld = D; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
-    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr; P.tab_bf16 = tab_bf16;
+    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr; P.tab_bf16 = tab_bf16; P.grad_bf16 = 0;
     RowVec<VEC> g[CH], w[CH];
     float* wp = tab_off(P, W, row * D + col0);
     const float* gp = gsum + u * D + col0;
@@ -413,7 +413,7 @@ dense_rows_update_kernel(int optimizer, float* __restrict__ W, float* __restrict
     const int col0 = gl * VEC;
     BwdParams P;
     P.optimizer = optimizer; P.D = D; P.ld = ld; P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
-    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr; P.tab_bf16 = tab_bf16;
+    P.invalid_key = 0xffffffffu; P.scratch_row = nullptr; P.tab_bf16 = tab_bf16; P.grad_bf16 = 0;
     const int64_t ngroups = ((int64_t)gridDim.x * blockDim.x) / G;
     for (int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; r < rows; r += ngroups) {
         RowVec<VEC> g[CH], w[CH];
@@ -470,8 +470,14 @@ static int launch_update(const BwdParams& P, cudaStream_t st) {
     constexpr int GPC = 256 / G;
     const unsigned blocks = (unsigned)ceil_div(P.nseg, (int64_t)GPC);
     const size_t smem = (size_t)2 * GPC * P.D * sizeof(float);
-    if (P.D == VEC * G * CH) bwd_update_kernel<VEC, G, CH, K, OCC, true><<<blocks, threads, smem, st>>>(P);
-    else bwd_update_kernel<VEC, G, CH, K, OCC, false><<<blocks, threads, smem, st>>>(P);
+    const bool exact = P.D == VEC * G * CH;
+    if (P.grad_bf16) {
+        if (exact) bwd_update_kernel<VEC, G, CH, K, OCC, true, true><<<blocks, threads, smem, st>>>(P);
+        else bwd_update_kernel<VEC, G, CH, K, OCC, false, true><<<blocks, threads, smem, st>>>(P);
+    } else {
+        if (exact) bwd_update_kernel<VEC, G, CH, K, OCC, true, false><<<blocks, threads, smem, st>>>(P);
+        else bwd_update_kernel<VEC, G, CH, K, OCC, false, false><<<blocks, threads, smem, st>>>(P);
+    }
     int rc = check_launch("bwd_update");
     if (rc) return rc;
     // the fix-up works on CTA tiles: GPC segments each, one head / tail partial per tile
@@ -531,7 +537,7 @@ static size_t update_workspace_bytes(int64_t N, int D) {
     return align_up((size_t)nseg * D * 4, 256) * 2 + align_up((size_t)(D + 4) * 4, 256);   // + the scratch row
 }
 
-static int bwd_update_impl(int optimizer, int tab_bf16, float* const* tables, float* const* moms, const int64_t* table_row_base,
+static int bwd_update_impl(int optimizer, int tab_bf16, int grad_bf16, float* const* tables, float* const* moms, const int64_t* table_row_base,
                            int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
                            const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
                            float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
@@ -551,15 +557,15 @@ static int bwd_update_impl(int optimizer, int tab_bf16, float* const* tables, fl
     // cost more than the halved row bytes return.
     DLRMX_REQUIRE(row_geometry(D, &g), "bwd_update: unsupported D=%d", D);
     if (g.vec >= 4)
-        DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && ((uintptr_t)grad & 15) == 0 && ld % g.vec == 0,
-                      "bwd_update: grad must be 16-B aligned with strides (and table_ld) multiple of the lane width");
+        DLRMX_REQUIRE(stride_b % 4 == 0 && stride_t % 4 == 0 && ((uintptr_t)grad & (grad_bf16 ? 7 : 15)) == 0 && ld % g.vec == 0,
+                      "bwd_update: grad must be 16-B aligned (bf16: 8-B) with strides (and table_ld) multiple of the lane width");
     if (N == 0) return DLRMX_OK;
     if (workspace_bytes < update_workspace_bytes(N, D)) {
         set_error("bwd_update: workspace %zu < %zu", workspace_bytes, update_workspace_bytes(N, D));
         return DLRMX_E_WORKSPACE;
     }
     BwdParams P;
-    P.optimizer = optimizer; P.tab_bf16 = tab_bf16; P.tables = tables; P.moms = moms; P.row_base = table_row_base;
+    P.optimizer = optimizer; P.tab_bf16 = tab_bf16; P.grad_bf16 = grad_bf16; P.tables = tables; P.moms = moms; P.row_base = table_row_base;
     P.B = B; P.D = D; P.ld = ld; P.grad = grad; P.stride_b = stride_b; P.stride_t = stride_t;
     P.skey = sorted_key; P.sbag = sorted_bag; P.N = N; P.seg_len = seg_len_for(N, optimizer); P.nseg = ceil_div(N, (int64_t)P.seg_len);
     P.lr = lr; P.eps = eps; P.inv_D = (D & (D - 1)) == 0 ? 1.0f / (float)D : 0.f;
@@ -591,7 +597,7 @@ int dlrmx_bwd_update(int optimizer, float* const* tables, float* const* moms, co
                      int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
                      const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
                      float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
-    return dlrmx::bwd_update_impl(optimizer, 0, tables, moms, table_row_base, T, B, D, table_ld, grad, stride_b, stride_t,
+    return dlrmx::bwd_update_impl(optimizer, 0, 0, tables, moms, table_row_base, T, B, D, table_ld, grad, stride_b, stride_t,
                                   sorted_key, sorted_bag, N, total_rows, lr, eps, workspace, workspace_bytes, stream);
 }
 
@@ -599,9 +605,18 @@ int dlrmx_bwd_update_bf16(int optimizer, void* const* tables_bf16, float* const*
                           int T, int B, int D, int64_t table_ld, const float* grad, int64_t stride_b, int64_t stride_t,
                           const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows, float lr,
                           float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
-    return dlrmx::bwd_update_impl(optimizer, 1, reinterpret_cast<float* const*>(tables_bf16), moms, table_row_base, T, B, D,
+    return dlrmx::bwd_update_impl(optimizer, 1, 0, reinterpret_cast<float* const*>(tables_bf16), moms, table_row_base, T, B, D,
                                   table_ld, grad, stride_b, stride_t, sorted_key, sorted_bag, N, total_rows, lr, eps, workspace,
                                   workspace_bytes, stream);
+}
+
+int dlrmx_bwd_update_ex(int optimizer, int tables_are_bf16, int grad_is_bf16, void* const* tables, float* const* moms,
+                        const int64_t* table_row_base, int T, int B, int D, int64_t table_ld, const void* grad, int64_t stride_b,
+                        int64_t stride_t, const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows,
+                        float lr, float eps, void* workspace, size_t workspace_bytes, dlrmx_stream_t stream) {
+    return dlrmx::bwd_update_impl(optimizer, tables_are_bf16 ? 1 : 0, grad_is_bf16 ? 1 : 0, reinterpret_cast<float* const*>(tables),
+                                  moms, table_row_base, T, B, D, table_ld, reinterpret_cast<const float*>(grad), stride_b, stride_t,
+                                  sorted_key, sorted_bag, N, total_rows, lr, eps, workspace, workspace_bytes, stream);
 }
 
 int dlrmx_bwd_coalesce(int B, int D, const float* grad, int64_t stride_b, int64_t stride_t,

@@ -36,6 +36,8 @@ struct BwdParams {
     int64_t ld;           // row pitch of the tables in floats (>= D); the row-wise accumulator of a row may live in its
                           // padding (moms == nullptr: column D of the row), i.e. in the DRAM page the update opens anyway
     const float* grad;
+    int grad_bf16;        // 1: the pooled-row gradients are bf16 (the pointer still travels as float*, see grad_off; strides in
+                          // elements): the multi-GPU exchange moved them over NVLink in half the bytes; widened exactly when read
     int64_t stride_b, stride_t;
     const uint32_t* skey;
     const int32_t* sbag;
@@ -62,6 +64,19 @@ template <int VEC>
 __device__ __forceinline__ void store_row(const BwdParams& P, const RowVec<VEC>& w, float* p) {
     if (P.tab_bf16) w.store(reinterpret_cast<__nv_bfloat16*>(p));
     else w.store(p);
+}
+
+// The same for the pooled-row gradients (read-only for the kernel's lifetime: non-coherent loads).
+// GBF is a template flag of the update kernel (BwdParams::grad_bf16 selects the instantiation): as a run-time flag it
+// cost the row-wise Adagrad kernel of 512-byte rows its spill-free 64 registers.
+template <bool GBF>
+__device__ __forceinline__ const float* grad_off(const float* p, int64_t elems) {
+    return GBF ? reinterpret_cast<const float*>(reinterpret_cast<const __nv_bfloat16*>(p) + elems) : p + elems;
+}
+template <bool GBF, int VEC>
+__device__ __forceinline__ void load_grad(RowVec<VEC>& g, const float* p) {
+    if (GBF) g.load_stream(reinterpret_cast<const __nv_bfloat16*>(p));
+    else g.load_ro(p);
 }
 
 // Where the run of `key` (looked up through bag `bag`) lives: table row and, for row-wise Adagrad, its accumulator.

@@ -249,7 +249,8 @@ class _DistInteract(torch.autograd.Function):
         T_s = F - 1 - (step.rep.T if step.rep is not None else 0)
         send = None
         if peer is None:      # NCCL: pack + start the transposed all-to-all; _A2AReq.backward completes it and the batched
-            send = ext_dist.start_backward_from(step.info, dfeat, 1)      # lookup's own backward runs the fused update
+            send = ext_dist.start_backward_from(step.info, dfeat, 1,     # lookup's own backward runs the fused update
+                                                wire_bf16=getattr(step.model, "_grad_wire_bf16", False))
 
         def sparse_updates():                 # on the side stream
             cur = torch.cuda.current_stream()
@@ -446,6 +447,14 @@ class DLRM_Net(nn.Module):
             self.bot_l.dp_world = self.top_l.dp_world = ext_dist.my_size
         if self.emb_rep is not None and self._mixed:
             self.emb_rep.wire_bf16 = True              # mixed-precision mode: the replicated tables' gradients cross NVLink as bf16
+        if ext_dist.my_size > 1 and self.fuse_sparse_arch:
+            # bf16 on the wire for the pooled-row gradients of the sharded tables, peer-memory and NCCL exchange alike
+            wire = bool(self._mixed and D % 8 == 0)
+            peer = getattr(self, "_peer", None)
+            if peer is not None and peer.grad_bf16 != wire:
+                raise _lib.DlrmxError("enable_peer_exchange(mixed=%s) does not match the fused towers (mixed=%s)"
+                                      % (peer.grad_bf16, wire))
+            self._grad_wire_bf16 = wire
         if allreduce not in ("peer", "nccl"):
             raise ValueError("allreduce must be 'peer' (own kernel over NVLink peer memory) or 'nccl'")
         if allreduce == "peer" and ext_dist.my_size > 1:
@@ -560,9 +569,12 @@ class DLRM_Net(nn.Module):
         D = int(self.ln_bot[-1])
         n_rep = len(self.replicated_emb_indices)
         F = 1 + int(sum(self.n_emb_per_rank)) + n_rep
-        pitch = ops.interact_feature_pitch(F, D) if (getattr(self, "_mixed", False) if mixed is None else mixed) else D
+        mixed = bool(getattr(self, "_mixed", False) if mixed is None else mixed)
+        pitch = ops.interact_feature_pitch(F, D) if mixed else D
+        # mixed-precision mode: the pooled-row gradients cross NVLink as bf16 (D % 8 == 0: one 16-byte store per 8 elements)
+        self._grad_wire_bf16 = mixed and D % 8 == 0
         self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, D, dev, feature_pitch=pitch,
-                                           extra_features=n_rep)
+                                           extra_features=n_rep, grad_bf16=self._grad_wire_bf16)
         return self
 
     def sync_replicas(self):

@@ -146,6 +146,8 @@ class _A2AReq(Function):
             myreq.req = None
             g = myreq.tensor
             myreq.tensor = None
+        if g.dtype != torch.float32:           # bf16 on the wire (start_backward_from): exact widening
+            g = g.float()
         if info.batched_emb:
             grads = [g.view(info.batch_size, -1, info.emb_dim)]
         else:
@@ -197,10 +199,14 @@ def complete_into(recv, feat, feat_off=1):
     return info
 
 
-def start_backward_from(info, dfeat, feat_off=1):
+def start_backward_from(info, dfeat, feat_off=1, wire_bf16=False):
     """Packs dfeat[:, feat_off:, :] into per-destination chunks (one kernel) and starts the transposed
-    exchange; `_A2AReq.backward` completes it.  Returns the send buffer (kept alive by the caller)."""
+    exchange; `_A2AReq.backward` completes it.  Returns the send buffer (kept alive by the caller).
+    wire_bf16: the chunks cross as bf16 (rounded to nearest even) and are widened on arrival -- the same values the
+    peer-memory path's dlrmx_a2a_push_grad_bf16 delivers."""
     send = ops.a2a_pack_grad(dfeat, feat_off, info.tables_per_rank, info.local_batch_num, info.emb_dim)
+    if wire_bf16:
+        send = send.to(torch.bfloat16)
     _issue_backward(info, send)
     return send
 
@@ -237,7 +243,8 @@ class PeerExchange(object):
     tables_per_rank[p] = SHARDED tables held by rank p (rank-major order, as the reference's cat produces);
     extra_features = feature slots behind them that every rank fills locally (replicated tables)."""
 
-    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, feature_pitch=None, extra_features=0):
+    def __init__(self, tables_per_rank, local_batch, emb_dim, device, group=None, feature_pitch=None, extra_features=0,
+                 grad_bf16=False):
         import torch.distributed._symmetric_memory as symm_mem
         self.group = dist.group.WORLD if group is None else group
         self.W, self.rank = my_size, my_rank
@@ -253,7 +260,11 @@ class PeerExchange(object):
         n_feat = self.lb * F * P
         n_grad = self.W * self.lb * max(max(self.tpr), 1) * self.D     # symmetric: same size on every rank
         self._feat_flat = symm_mem.empty(n_feat, dtype=torch.float32, device=device)
-        self._grad_flat = symm_mem.empty(n_grad, dtype=torch.float32, device=device)
+        # grad_bf16 (the towers' mixed-precision mode): the pooled-row gradients cross NVLink and are stored as bf16 --
+        # half the bytes of the transfer the sparse update waits for; the update kernel widens them exactly
+        self.grad_bf16 = bool(grad_bf16)
+        gsize = 2 if self.grad_bf16 else 4
+        self._grad_flat = symm_mem.empty(n_grad, dtype=torch.bfloat16 if self.grad_bf16 else torch.float32, device=device)
         self.h_feat = symm_mem.rendezvous(self._feat_flat, self.group)
         self.h_grad = symm_mem.rendezvous(self._grad_flat, self.group)
         self.feat = self._feat_flat.view(self.lb, F, P)[:, :, :self.D]               # my interaction input
@@ -262,7 +273,7 @@ class PeerExchange(object):
         fptr = [int(q) + (1 + self.first[self.rank]) * P * 4 for q in self.h_feat.buffer_ptrs]
         self.out_peers = torch.tensor(fptr, dtype=torch.int64, device=device)
         # backward: where MY local batch's chunk starts inside owner p's gradient buffer [W*lb, T_p, D]
-        self.push_bases = [int(q) + self.rank * self.lb * self.tpr[p] * self.D * 4
+        self.push_bases = [int(q) + self.rank * self.lb * self.tpr[p] * self.D * gsize
                            for p, q in enumerate(self.h_grad.buffer_ptrs)]
         self.stride_b, self.stride_t = F * P, P
 
@@ -284,7 +295,7 @@ class PeerExchange(object):
         [W*lb, T_r, D] once every peer's slices have landed (stream-ordered)."""
         with record_function("DLRM alltoall_wait_bwd_single"):       # the reference's names: issue = wait_bwd ...
             self.h_grad.barrier()                  # owners are done with the previous step's gradients
-            ops.a2a_push_grad(dfeat, 1, self.tpr, dfeat.shape[0], self.D, self.push_bases)
+            ops.a2a_push_grad(dfeat, 1, self.tpr, dfeat.shape[0], self.D, self.push_bases, bf16=self.grad_bf16)
         with record_function("DLRM alltoall_req_bwd_single"):        # ... completion = req_bwd (extend_distributed.py:449, 492)
             self.h_grad.barrier()
         return self.grad

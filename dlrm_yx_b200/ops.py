@@ -246,13 +246,22 @@ def bwd_update(tables, optimizer, grad, stride_b, stride_t, B, skey, sbag, lr, e
         raise _lib.DlrmxError("RWSAdagrad update needs row-wise accumulators (TableSet(moms=...) or acc_in_row)")
     wsb = lib.dlrmx_bwd_update_workspace_bytes(N, tables.D)
     ws = torch.empty(max(wsb, 1), dtype=torch.uint8, device=tables.device)
+    if grad.dtype not in (torch.float32, torch.bfloat16):
+        raise _lib.DlrmxError("bwd_update: pooled-row gradients must be fp32 or bf16, got %s" % grad.dtype)
     with _timed("bwd_update"):
-        fn = lib.dlrmx_bwd_update_bf16 if tables.bf16 else lib.dlrmx_bwd_update
-        rc = fn(optimizer, tables.table_ptrs.data_ptr(),
-                0 if tables.acc_in_row else _ptr(tables.mom_ptrs),
-                tables.row_base.data_ptr(), tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b,
-                stride_t, skey.data_ptr(), sbag.data_ptr(), N, tables.total_rows, float(lr), float(eps),
-                ws.data_ptr(), wsb, _stream())
+        if grad.dtype == torch.bfloat16:        # what the bf16 gradient push / all-to-all delivers (strides in elements)
+            rc = lib.dlrmx_bwd_update_ex(optimizer, 1 if tables.bf16 else 0, 1, tables.table_ptrs.data_ptr(),
+                                         0 if tables.acc_in_row else _ptr(tables.mom_ptrs), tables.row_base.data_ptr(),
+                                         tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b, stride_t,
+                                         skey.data_ptr(), sbag.data_ptr(), N, tables.total_rows, float(lr), float(eps),
+                                         ws.data_ptr(), wsb, _stream())
+        else:
+            fn = lib.dlrmx_bwd_update_bf16 if tables.bf16 else lib.dlrmx_bwd_update
+            rc = fn(optimizer, tables.table_ptrs.data_ptr(),
+                    0 if tables.acc_in_row else _ptr(tables.mom_ptrs),
+                    tables.row_base.data_ptr(), tables.T, B, tables.D, tables.ld, grad.data_ptr(), stride_b,
+                    stride_t, skey.data_ptr(), sbag.data_ptr(), N, tables.total_rows, float(lr), float(eps),
+                    ws.data_ptr(), wsb, _stream())
         _lib.check(rc, "dlrmx_bwd_update")
 
 
@@ -352,13 +361,15 @@ def _int_array(values):
     return (ctypes.c_int * len(values))(*[int(v) for v in values])
 
 
-def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases):
-    """dfeat[:, feat_off + t, :] -> rank p's chunk [lb, T_p, D] at peer_chunk_bases[p] (peer-mapped addresses)."""
+def a2a_push_grad(dfeat, feat_off, tables_per_rank, lb, D, peer_chunk_bases, bf16=False):
+    """dfeat[:, feat_off + t, :] -> rank p's chunk [lb, T_p, D] at peer_chunk_bases[p] (peer-mapped addresses); bf16: the
+    owners' buffers are bf16 and the rows are rounded to nearest even on the way."""
     _need_cuda(dfeat)
     bases = (ctypes.c_void_p * len(peer_chunk_bases))(*[int(b) for b in peer_chunk_bases])
     with _timed("a2a_push_grad"):
-        rc = _lib.load().dlrmx_a2a_push_grad(dfeat.data_ptr(), dfeat.stride(0), dfeat.stride(1), feat_off, len(tables_per_rank),
-                                             _int_array(tables_per_rank), lb, D, bases, _stream())
+        fn = _lib.load().dlrmx_a2a_push_grad_bf16 if bf16 else _lib.load().dlrmx_a2a_push_grad
+        rc = fn(dfeat.data_ptr(), dfeat.stride(0), dfeat.stride(1), feat_off, len(tables_per_rank),
+                _int_array(tables_per_rank), lb, D, bases, _stream())
         _lib.check(rc, "dlrmx_a2a_push_grad")
 
 

@@ -167,6 +167,16 @@ int dlrmx_bwd_update_bf16(int optimizer, void* const* tables_bf16, float* const*
                           float lr, float eps,
                           void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
 
+/* The same kernel with the row types as flags: tables fp32 / bf16 (as dlrmx_bwd_update_bf16) and, when grad_is_bf16, pooled-row
+ * gradients stored as bf16 (strides in elements; 8-byte aligned rows): what dlrmx_a2a_push_grad_bf16 delivers.  A bf16
+ * gradient is widened exactly, so the result equals dlrmx_bwd_update's on an fp32 buffer holding the same values. */
+int dlrmx_bwd_update_ex(int optimizer, int tables_are_bf16, int grad_is_bf16, void* const* tables, float* const* moms,
+                        const int64_t* table_row_base, int T, int B, int D, int64_t table_ld,
+                        const void* grad, int64_t stride_b, int64_t stride_t,
+                        const uint32_t* sorted_key, const int32_t* sorted_bag, int64_t N, int64_t total_rows,
+                        float lr, float eps,
+                        void* workspace, size_t workspace_bytes, dlrmx_stream_t stream);
+
 /* Non-fused variant: emits the coalesced gradient rows  gsum[u,:] = sum over run u  ([num_unique, D],
  * row stride D) so that the reference's own optimizers can consume a coalesced sparse COO gradient
  * ("parity seam").  Needs run_off/num_unique from dlrmx_bwd_segments. */
@@ -338,6 +348,11 @@ int dlrmx_embbag_fwd_scatter_i64(const float* const* tables, const int64_t* tabl
 int dlrmx_a2a_push_grad(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
                         const int* host_tables_per_rank, int lb, int D,
                         float* const* host_peer_chunk_bases, dlrmx_stream_t stream);
+/* bf16 on the wire (the mixed-precision mode of the towers): the same slices, rounded to nearest even, into bf16 gradient
+ * buffers [W*lb, T_p, D] of the owners; dlrmx_bwd_update_ex(grad_is_bf16 = 1) reads them.  D % 8 == 0. */
+int dlrmx_a2a_push_grad_bf16(const float* dfeat, int64_t dfeat_stride_b, int64_t dfeat_stride_f, int feat_off, int W,
+                             const int* host_tables_per_rank, int lb, int D,
+                             void* const* host_peer_chunk_bases_bf16, dlrmx_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Data-parallel gradient all-reduce over NVLink peer memory (csrc/peer_allreduce.cu).  Replaces the

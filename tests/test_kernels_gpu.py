@@ -522,3 +522,66 @@ def test_peer_allreduce_rank_order_sum_on_one_device(W, dtype, numel):
     view = torch.int32 if td == torch.float32 else torch.int16
     for b in bufs:
         assert torch.equal(b.view(view), ref.view(view))
+
+
+@pytest.mark.parametrize("D,L,opt,tab", [(128, 1, "rwsadagrad", "fp32"), (64, 7, "sgd", "fp32"), (96, 3, "rwsadagrad", "bf16"),
+                                         (6, 2, "sgd", "fp32"), (16, 1, "rwsadagrad", "fp32")])
+def test_bf16_gradient_rows_match_the_fp32_path_on_widened_gradients(D, L, opt, tab):
+    """Pooled-row gradients stored as bf16 (what the bf16 gradient push delivers, dlrmx_bwd_update_ex): widening is exact,
+    so tables and accumulators must equal, bit for bit, the fused update fed with an fp32 buffer of the same values --
+    strided gradient layout, hot rows, both optimizers, fp32 and bf16 table rows."""
+    from dlrm_yx_b200 import _lib, ops
+    dev = cuda()
+    rng = np.random.default_rng(23)
+    rows, B = [3, 700, 5000], 257
+    tdt = torch.bfloat16 if tab == "bf16" else torch.float32
+    W1 = [torch.from_numpy(rng.uniform(-1, 1, size=(r, D)).astype(np.float32)).to(dev).to(tdt) for r in rows]
+    W2 = [w.clone() for w in W1]
+    idx = np.concatenate([rng.integers(0, r, size=B * L) for r in rows]).astype(np.int32)
+    off = (np.arange(len(rows) * B + 1) * L).astype(np.int32)
+    idx_t, off_t = torch.from_numpy(idx).to(dev), torch.from_numpy(off).to(dev)
+    kind = _lib.OPT_RWSADAGRAD if opt == "rwsadagrad" else _lib.OPT_SGD
+    m1 = [torch.full((r,), 0.01, device=dev) for r in rows] if opt == "rwsadagrad" else None
+    m2 = [m.clone() for m in m1] if m1 is not None else None
+    ts1, ts2 = ops.TableSet(W1, m1), ops.TableSet(W2, m2)
+    T = len(rows)
+    pitch = D + 8 if D % 8 == 0 else D                      # a feature pitch wider than the row, as the exchange buffers may have
+    gb = torch.zeros(B, T + 1, pitch, device=dev, dtype=torch.bfloat16)
+    gb[:, 1:, :D] = torch.from_numpy(rng.normal(size=(B, T, D)).astype(np.float32)).to(dev).to(torch.bfloat16)
+    gf = gb.float()
+    skey, sbag = ops.bwd_sort(ts1, idx_t, off_t, B)
+    ops.bwd_update(ts1, kind, gb[:, 1:, :], gb.stride(0), gb.stride(1), B, skey, sbag, 0.05, 1e-8)
+    ops.bwd_update(ts2, kind, gf[:, 1:, :], gf.stride(0), gf.stride(1), B, skey, sbag, 0.05, 1e-8)
+    view = torch.int16 if tab == "bf16" else torch.int32
+    for k in range(T):
+        assert torch.equal(W1[k].view(view), W2[k].view(view)), "table %d" % k
+        if m1 is not None:
+            assert torch.equal(m1[k], m2[k])
+    ops.check_index_errors()
+
+
+@pytest.mark.parametrize("D", [128, 16])
+def test_gradient_push_bf16_on_one_device(D):
+    """dlrmx_a2a_push_grad_bf16 with buffers of ONE device standing in for the owners: every owner's chunk [lb, T_p, D] must
+    hold the bf16 rounding (nearest even) of the slices the fp32 push stores, from a pitched feature-block gradient."""
+    from dlrm_yx_b200 import ops
+    dev = cuda()
+    tpr, lb, rank, Wn = [2, 0, 3, 1], 37, 1, 4
+    T = sum(tpr)
+    g = torch.Generator(device=dev).manual_seed(5)
+    dfeat = torch.randn(lb, 1 + T + 2, D + 8, device=dev, generator=g)[:, :, :D]      # slot 0 = dense, 2 replicated slots behind
+    bufs_f = [torch.full((Wn * lb, max(t, 1), D), float("nan"), device=dev) for t in tpr]
+    bufs_b = [torch.full((Wn * lb, max(t, 1), D), float("nan"), device=dev, dtype=torch.bfloat16) for t in tpr]
+    bases_f = [b.data_ptr() + rank * lb * t * D * 4 for b, t in zip(bufs_f, tpr)]
+    bases_b = [b.data_ptr() + rank * lb * t * D * 2 for b, t in zip(bufs_b, tpr)]
+    ops.a2a_push_grad(dfeat, 1, tpr, lb, D, bases_f)
+    ops.a2a_push_grad(dfeat, 1, tpr, lb, D, bases_b, bf16=True)
+    first = 0
+    for p, t in enumerate(tpr):
+        if t == 0:
+            continue
+        cf = bufs_f[p].view(-1)[rank * lb * t * D:(rank + 1) * lb * t * D].view(lb, t, D)
+        cb = bufs_b[p].view(-1)[rank * lb * t * D:(rank + 1) * lb * t * D].view(lb, t, D)
+        assert torch.equal(cf, dfeat[:, 1 + first:1 + first + t, :])
+        assert torch.equal(cb.view(torch.int16), cf.to(torch.bfloat16).view(torch.int16))
+        first += t
