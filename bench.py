@@ -886,8 +886,11 @@ def main():
         "metric": "DLRM train samples/sec", "value": Bg * K / (r["ms_dev"] / 1e3), "unit": "samples/s",
         "n_gpus": W, "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_dev"] / K,
         "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
-        "dtype": "%s embedding tables, fp32 pooled rows, gradients and sparse optimizer; interaction: %s; MLP GEMMs: %s"
-                 % ("bf16-row (widened on load, rounded to nearest on store)" if args.table_dtype == "bf16" else "fp32", ix_txt, mlp_txt),
+        "dtype": "%s embedding tables, fp32 pooled rows, gradients and sparse optimizer%s; interaction: %s; MLP GEMMs: %s"
+                 % ("bf16-row (widened on load, rounded to nearest on store)" if args.table_dtype == "bf16" else "fp32",
+                    " (between GPUs the pooled-row gradients of the sharded tables and the replicated tables' gradient sums "
+                    "cross NVLink rounded to bf16, accumulated in fp32)" if (W > 1 and args.mlp == "fused-bf16") else "",
+                    ix_txt, mlp_txt),
         "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, W, Bg), "global_batch": Bg, "per_gpu_batch": lb,
                    "index_distribution": args.index_dist,

@@ -595,13 +595,15 @@ class DLRM_Net(nn.Module):
 
     def _replicated_lookup(self, step, feat, T_s, off, idx):
         """Pooled rows of the replicated tables for the LOCAL batch, straight into their feature slots; the sort for
-        their backward is issued right behind (side stream)."""
+        their backward is issued behind it on the side stream."""
         rep = self.emb_rep
         step.rep, step.rep_indices, step.rep_offsets = rep, idx, off
         ops.embbag_forward(rep.table_set(), idx, off, step.lb, out=feat[:, 1 + T_s:, :], stride_b=feat.stride(0),
                            stride_t=feat.stride(1))
         if torch.is_grad_enabled():
-            step.rep_sorted = rep.sort_lookups(idx, off, step.lb)
+            # on the side stream, where the backward consumes it: on the main stream its eight launches (~80 us at the
+            # Terabyte shape) sat between this lookup and the interaction (profiles/r02_timeline_n8_peer_ar_rank0.txt)
+            step.rep_sorted = _sort_on_side(rep, idx, off, step.lb)
 
     def _peer_forward(self, dense_x, lS_o, lS_i):
         peer = self._peer

@@ -118,11 +118,11 @@ class _Tower(torch.autograd.Function):
     @staticmethod
     def forward(ctx, h, anchor, mlp, i0, i1):
         first = mlp.layers[i0]
-        hb = h if h.dtype == torch.bfloat16 else h.to(torch.bfloat16)
-        if hb.shape[1] != first.K_pad:
-            padded = hb.new_zeros((hb.shape[0], first.K_pad))
-            padded[:, :first.K].copy_(hb)
-            hb = padded
+        if h.shape[1] != first.K_pad:           # cast and pad in one copy (the copy kernel rounds to nearest even, as .to() does)
+            hb = torch.zeros((h.shape[0], first.K_pad), dtype=torch.bfloat16, device=h.device)
+            hb[:, :first.K].copy_(h)
+        else:
+            hb = h if h.dtype == torch.bfloat16 else h.to(torch.bfloat16)
         acts, gates = [hb.contiguous()], []
         for li in range(i0, i1):
             L = mlp.layers[li]
