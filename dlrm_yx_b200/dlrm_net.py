@@ -622,14 +622,23 @@ class DLRM_Net(nn.Module):
                 arrived = side.record_event()
                 if torch.is_grad_enabled() and emb.T > 0:
                     step.presorted = emb.sort_lookups(idx, off, peer.W * lb)
+        rep_done = None
+        if self.emb_rep is not None:
+            # local rows of the replicated tables: HBM work on a third stream, beside the NVLink-bound scatter AND the bottom
+            # tower (behind the tower on the main stream it was the last thing the interaction waited for)
+            rs = _comm_stream(dense_x.device, 1)
+            if rs != main:
+                rs.wait_stream(main)
+            with record_function("module::forward_pass::embedding_lookup"), torch.cuda.stream(rs):
+                self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
+                rep_done = rs.record_event() if rs != main else None
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
-        if self.emb_rep is not None:            # local rows of the replicated tables: HBM work beside the NVLink-bound scatter
-            with record_function("module::forward_pass::embedding_lookup"):
-                self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
         cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
         with record_function("module::forward_pass::interaction"):
             main.wait_event(arrived)
+            if rep_done is not None:
+                main.wait_event(rep_done)
             z = _DistInteract.apply(x, None, step, self.arch_interaction_itself, cols,
                                     cols > 0 and self._take_over_bottom_relu())
         with record_function("module::forward_pass::top_mlp"):
