@@ -41,6 +41,11 @@ def parse():
     ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"],
                     help="data-parallel gradient sums (towers, replicated tables) at N > 1: the repo's kernel over NVLink peer "
                          "memory (csrc/peer_allreduce.cu) or NCCL (comparator)")
+    ap.add_argument("--mgpu-overlap", type=int, default=0, choices=[0, 1],
+                    help="N > 1 schedule (dlrm_net.MGPU_OVERLAP): 0 = the one measured on 2 / 4 / 8 GPUs; 1 = separate high-priority "
+                         "all-reduce streams, replicated lookup on a third stream, short-lived push CTAs (measured on 2 GPUs only)")
+    ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"],
+                    help="N > 1, bf16 towers: pooled-row gradients of the sharded tables cross NVLink as fp32 or rounded to bf16")
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"],
                     help="fused-bf16 towers: tc = the repo's tcgen05/TMEM/TMA GEMM kernels; cublas = cuBLASLt through torch, "
                          "the measured comparator (never a fallback)")
@@ -217,9 +222,10 @@ def build_model(args, cfg, W, exchange=None):
     m.sync_replicas()
     if W > 1 and exchange == "peer":
         lb = cfg["B"] if not args.global_batch else args.global_batch // W
-        m.enable_peer_exchange(lb, mixed=(args.mlp == "fused-bf16"))
+        m.enable_peer_exchange(lb, mixed=(args.mlp == "fused-bf16"), grad_wire_bf16=(args.grad_wire == "bf16"))
     if args.mlp == "fused-bf16":
-        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm, allreduce=args.allreduce)
+        m.fuse_mlps(lr, "adagrad" if args.optimizer == "rwsadagrad" else "sgd", gemm=args.tower_gemm, allreduce=args.allreduce,
+                    grad_wire_bf16=(args.grad_wire == "bf16"))
         m.top_l.defer_wgrad = bool(m.top_l.defer_wgrad and args.defer_wgrad)
         dlrm_net.FLUSH_EARLY = args.defer_wgrad == 2
         if W == 1 and args.defer_wgrad == 1:
@@ -839,6 +845,11 @@ def main():
         _emit(line)
         return
 
+    if args.mgpu_overlap:
+        # one hardware queue per stream: the schedule has three chains of device barriers in flight at once
+        os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+        from dlrm_yx_b200 import dlrm_net as _dn
+        _dn.set_mgpu_overlap(args.mgpu_overlap)
     if args.tunable:
         from dlrm_yx_b200 import _lib
         for kv in args.tunable:
@@ -888,8 +899,9 @@ def main():
         "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
         "dtype": "%s embedding tables, fp32 pooled rows, gradients and sparse optimizer%s; interaction: %s; MLP GEMMs: %s"
                  % ("bf16-row (widened on load, rounded to nearest on store)" if args.table_dtype == "bf16" else "fp32",
-                    " (between GPUs the pooled-row gradients of the sharded tables and the replicated tables' gradient sums "
-                    "cross NVLink rounded to bf16, accumulated in fp32)" if (W > 1 and args.mlp == "fused-bf16") else "",
+                    " (between GPUs the replicated tables' gradient sums%s cross NVLink rounded to bf16, accumulated in fp32)"
+                    % (" and the pooled-row gradients of the sharded tables" if args.grad_wire == "bf16" else "")
+                    if (W > 1 and args.mlp == "fused-bf16") else "",
                     ix_txt, mlp_txt),
         "data": "synthetic",
         "config": {"workload": workload_name(args, cfg, W, Bg), "global_batch": Bg, "per_gpu_batch": lb,
@@ -905,7 +917,8 @@ def main():
                    "l2": "tables (%.1f GB on rank 0) and %d rotating batches exceed L2; no flush needed"
                          % (sum(cfg["rows"][t] for t in r["local_tables"]) * D * (2 if args.table_dtype == "bf16" else 4) / 1e9,
                             args.nbatches),
-                   "rows_cap": args.rows_cap or None, **({"tunables": args.tunable} if args.tunable else {})},
+                   "rows_cap": args.rows_cap or None, **({"tunables": args.tunable} if args.tunable else {}),
+                   **({"mgpu_overlap": args.mgpu_overlap, "grad_wire": args.grad_wire} if W > 1 else {})},
         "e2e": {"value": Bg * K / (r["wall_e2e"] / 1e3), "unit": "samples/s", "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": 4, "ms_per_step": r["wall_e2e"] / K},
         "gpu_launches": r["launches"],

@@ -14,6 +14,7 @@
 namespace dlrmx {
 
 constexpr int kMaxRanks = 64;
+enum { DLRMX_TUNE_PUSH_GRID = 13 };
 struct RankSplit {
     int W;
     int first_table[kMaxRanks + 1];  // exclusive prefix of tables per rank
@@ -127,17 +128,19 @@ static int a2a_push_impl(const float* dfeat, int64_t dfeat_stride_b, int64_t dfe
     const int T = rs.first_table[W];
     if (lb == 0 || T == 0) return DLRMX_OK;
     const int64_t total = (int64_t)lb * T * (vec ? D / 4 : D);
-    // many short-lived CTAs (one or two elements per thread) rather than a persistent grid: the gradient all-reduces run
-    // beside this kernel at a higher stream priority and get an SM slot whenever one of these CTAs retires (with 16 CTAs
-    // per SM looping, the all-reduce kernel waited ~0.1 ms for its first slot: profiles/r02_timeline_n8_peer_ar_rank0.txt)
+    // tunable 13 = 1 (dlrm_net.set_mgpu_overlap): many short-lived CTAs (one or two elements per thread) rather than a looping
+    // grid: the gradient all-reduces then run beside this kernel at a higher stream priority and get an SM slot whenever one
+    // of these CTAs retires (with 16 CTAs per SM looping, the all-reduce kernel waited ~0.1 ms for its first slot:
+    // profiles/r02_timeline_n8_peer_ar_rank0.txt).  Default: the looping grid every multi-GPU run so far was measured with.
+    const int64_t cap = (int64_t)kSMs * (get_tunable(DLRMX_TUNE_PUSH_GRID) == 1 ? 512 : 16);
     int64_t nblk = ceil_div(total, 256);
-    if (nblk > (int64_t)kSMs * 512) nblk = (int64_t)kSMs * 512;
+    if (nblk > cap) nblk = cap;
     cudaStream_t st = (cudaStream_t)stream;
     if (out_bf16) {
         DLRMX_REQUIRE(vec && D % 8 == 0, "a2a_push_grad_bf16: needs D %% 8 == 0 and 16-byte aligned buffers and strides");
         const int64_t total8 = (int64_t)lb * T * (D / 8);
         int64_t nb8 = ceil_div(total8, 256);
-        if (nb8 > (int64_t)kSMs * 512) nb8 = (int64_t)kSMs * 512;
+        if (nb8 > cap) nb8 = cap;
         a2a_push_kernel<8, true><<<(unsigned)nb8, 256, 0, st>>>(dfeat, dfeat_stride_b, dfeat_stride_f, feat_off, rs, pb, lb, D);
         return check_launch("a2a_push_grad_bf16");
     }

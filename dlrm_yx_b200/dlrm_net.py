@@ -47,17 +47,35 @@ def _side_stream(device):
 
 _COMM = {}
 
+# Scheduling of the multi-process step around the exchange.
+#   0 (default): the schedule that has run on 2, 4 and 8 GPUs -- ONE communication stream of default priority for every
+#      gradient all-reduce chain, the replicated tables' lookup and sort on the main stream behind the bottom tower, the
+#      gradient push as a looping grid of 16 CTAs per SM.
+#   1: every all-reduce chain on its own HIGH-priority stream, the replicated tables' lookup on a third stream beside the
+#      scatter and the bottom tower, their sort on the side stream, the gradient push as short-lived CTAs.  Measured on 2
+#      GPUs (1.498 -> 1.418 ms per step, parity checks green); the one 8-GPU run of it did NOT finish within its time limit
+#      (no error, no output: see DESIGN.md section 5) and there was no GPU time left to find out why, so it is opt-in.
+MGPU_OVERLAP = 0
+
+
+def set_mgpu_overlap(level):
+    """Selects the schedule above (before the first step / graph capture) and the matching gradient-push grid."""
+    global MGPU_OVERLAP
+    MGPU_OVERLAP = 1 if int(level) else 0
+    _lib.set_tunable(13, MGPU_OVERLAP)          # DLRMX_TUNE_PUSH_GRID (csrc/a2a_layout.cu)
+
 
 def _comm_stream(device, which=0):
-    """Streams of the gradient all-reduces that run beside compute: 0 = the towers', 1 = the replicated tables' (each
-    chain is barrier -> sum -> barrier -> consumer, and the two do not depend on each other).  High priority: their
-    kernels are small and latency-bound (device barriers, NVLink round trips) and must not queue behind the grids of the
-    gradient push / sparse update they run beside."""
+    """Stream(s) of the gradient all-reduces that run beside compute.  MGPU_OVERLAP = 1: 0 = the towers', 1 = the replicated
+    tables' (each chain is barrier -> sum -> barrier -> consumer, and the two do not depend on each other), both HIGH
+    priority: their kernels are small and latency-bound (device barriers, NVLink round trips) and must not queue behind the
+    grids of the gradient push / sparse update they run beside."""
     if not OVERLAP_STREAMS:
         return torch.cuda.current_stream()
-    s = _COMM.get((device, which))
+    key = (device, which, 1) if MGPU_OVERLAP else (device, 0, 0)
+    s = _COMM.get(key)
     if s is None:
-        s = _COMM[(device, which)] = torch.cuda.Stream(device=device, priority=-1)
+        s = _COMM[key] = torch.cuda.Stream(device=device, priority=-1 if MGPU_OVERLAP else 0)
     return s
 
 
@@ -425,7 +443,7 @@ class DLRM_Net(nn.Module):
     def apply_mlp(self, x, layers):
         return layers(x)
 
-    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10, gemm="tc", allreduce="peer"):
+    def fuse_mlps(self, lr, optimizer="adagrad", eps=1e-10, gemm="tc", allreduce="peer", grad_wire_bf16=False):
         """Replaces the two nn.Sequential towers by FusedMLP (bf16 tensor-core GEMMs with fused epilogues, flat
         parameter buffers, one-kernel optimizer step).  After this, call `step_mlps()` instead of putting the tower
         parameters into an outer optimizer."""
@@ -448,11 +466,12 @@ class DLRM_Net(nn.Module):
         if self.emb_rep is not None and self._mixed:
             self.emb_rep.wire_bf16 = True              # mixed-precision mode: the replicated tables' gradients cross NVLink as bf16
         if ext_dist.my_size > 1 and self.fuse_sparse_arch:
-            # bf16 on the wire for the pooled-row gradients of the sharded tables, peer-memory and NCCL exchange alike
-            wire = bool(self._mixed and D % 8 == 0)
+            # grad_wire_bf16 (opt-in, mixed-precision mode only): the pooled-row gradients of the sharded tables cross NVLink
+            # rounded to bf16, peer-memory and NCCL exchange alike (the same values either way)
+            wire = bool(grad_wire_bf16 and self._mixed and D % 8 == 0)
             peer = getattr(self, "_peer", None)
             if peer is not None and peer.grad_bf16 != wire:
-                raise _lib.DlrmxError("enable_peer_exchange(mixed=%s) does not match the fused towers (mixed=%s)"
+                raise _lib.DlrmxError("enable_peer_exchange(grad_wire_bf16=%s) does not match fuse_mlps (grad_wire_bf16=%s)"
                                       % (peer.grad_bf16, wire))
             self._grad_wire_bf16 = wire
         if allreduce not in ("peer", "nccl"):
@@ -558,7 +577,7 @@ class DLRM_Net(nn.Module):
             p = self.apply_mlp(z, self.top_l)
         return self._clamp(p)
 
-    def enable_peer_exchange(self, local_batch, mixed=None):
+    def enable_peer_exchange(self, local_batch, mixed=None, grad_wire_bf16=False):
         """Replaces the NCCL all-to-all of distributed_forward by kernels that store straight into the peers'
         memory over NVLink (ext_dist.PeerExchange).  Needs fuse_sparse_arch + batched_emb and a fixed local batch.
         mixed=True (bf16 towers will be fused in: fuse_mlps) lays the interaction input out with the row pitch the
@@ -571,8 +590,9 @@ class DLRM_Net(nn.Module):
         F = 1 + int(sum(self.n_emb_per_rank)) + n_rep
         mixed = bool(getattr(self, "_mixed", False) if mixed is None else mixed)
         pitch = ops.interact_feature_pitch(F, D) if mixed else D
-        # mixed-precision mode: the pooled-row gradients cross NVLink as bf16 (D % 8 == 0: one 16-byte store per 8 elements)
-        self._grad_wire_bf16 = mixed and D % 8 == 0
+        # opt-in with the mixed-precision mode: the pooled-row gradients cross NVLink as bf16 (D % 8 == 0: one 16-byte store
+        # per 8 elements); pass the same flag to fuse_mlps
+        self._grad_wire_bf16 = bool(grad_wire_bf16) and mixed and D % 8 == 0
         self._peer = ext_dist.PeerExchange(self.n_emb_per_rank, local_batch, D, dev, feature_pitch=pitch,
                                            extra_features=n_rep, grad_bf16=self._grad_wire_bf16)
         return self
@@ -595,15 +615,18 @@ class DLRM_Net(nn.Module):
 
     def _replicated_lookup(self, step, feat, T_s, off, idx):
         """Pooled rows of the replicated tables for the LOCAL batch, straight into their feature slots; the sort for
-        their backward is issued behind it on the side stream."""
+        their backward is issued right behind (MGPU_OVERLAP: on the side stream)."""
         rep = self.emb_rep
         step.rep, step.rep_indices, step.rep_offsets = rep, idx, off
         ops.embbag_forward(rep.table_set(), idx, off, step.lb, out=feat[:, 1 + T_s:, :], stride_b=feat.stride(0),
                            stride_t=feat.stride(1))
         if torch.is_grad_enabled():
-            # on the side stream, where the backward consumes it: on the main stream its eight launches (~80 us at the
-            # Terabyte shape) sat between this lookup and the interaction (profiles/r02_timeline_n8_peer_ar_rank0.txt)
-            step.rep_sorted = _sort_on_side(rep, idx, off, step.lb)
+            if MGPU_OVERLAP:
+                # on the side stream, where the backward consumes it: on the main stream its eight launches (~80 us at the
+                # Terabyte shape) sit between this lookup and the interaction (profiles/r02_timeline_n8_peer_ar_rank0.txt)
+                step.rep_sorted = _sort_on_side(rep, idx, off, step.lb)
+            else:
+                step.rep_sorted = rep.sort_lookups(idx, off, step.lb)
 
     def _peer_forward(self, dense_x, lS_o, lS_i):
         peer = self._peer
@@ -623,7 +646,7 @@ class DLRM_Net(nn.Module):
                 if torch.is_grad_enabled() and emb.T > 0:
                     step.presorted = emb.sort_lookups(idx, off, peer.W * lb)
         rep_done = None
-        if self.emb_rep is not None:
+        if self.emb_rep is not None and MGPU_OVERLAP:
             # local rows of the replicated tables: HBM work on a third stream, beside the NVLink-bound scatter AND the bottom
             # tower (behind the tower on the main stream it was the last thing the interaction waited for)
             rs = _comm_stream(dense_x.device, 1)
@@ -634,6 +657,9 @@ class DLRM_Net(nn.Module):
                 rep_done = rs.record_event() if rs != main else None
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
+        if self.emb_rep is not None and not MGPU_OVERLAP:      # local rows of the replicated tables: HBM work beside the
+            with record_function("module::forward_pass::embedding_lookup"):       # NVLink-bound scatter
+                self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
         cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0
         with record_function("module::forward_pass::interaction"):
             main.wait_event(arrived)

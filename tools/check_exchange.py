@@ -69,6 +69,7 @@ class Case(object):
         self.lb = self.B // self.W
         self.tower_gemm = "tc"
         self.allreduce = "peer"
+        self.grad_wire = "fp32"
 
     def build(self, sharder, exchange, bf16, replicate_below):
         g, dev = self.g, self.dev
@@ -95,10 +96,11 @@ class Case(object):
                     l.bias.copy_(torch.from_numpy(g["%s_b_%d" % (pre, j)]))
         m.sync_replicas()
         if exchange == "peer":
-            m.enable_peer_exchange(self.lb, mixed=bool(bf16))
+            m.enable_peer_exchange(self.lb, mixed=bool(bf16), grad_wire_bf16=bool(bf16) and self.grad_wire == "bf16")
         opt = None
         if bf16:
-            m.fuse_mlps(self.lr, "sgd" if self.sgd else "adagrad", gemm=self.tower_gemm, allreduce=self.allreduce)
+            m.fuse_mlps(self.lr, "sgd" if self.sgd else "adagrad", gemm=self.tower_gemm, allreduce=self.allreduce,
+                        grad_wire_bf16=self.grad_wire == "bf16")
         else:
             dense = list(m.bot_l.parameters()) + list(m.top_l.parameters())
             m.bot_l = ext.DDP(m.bot_l, device_ids=[dev.index])
@@ -200,6 +202,8 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"], help="GEMMs of the fused bf16 towers (cublas: comparator)")
     ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"], help="gradient sums of the fused towers / replicated tables")
+    ap.add_argument("--mgpu-overlap", type=int, default=0, choices=[0, 1], help="dlrm_net.MGPU_OVERLAP (see there)")
+    ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"], help="pooled-row gradients between GPUs (bf16 towers)")
     ap.add_argument("--losses-only", action="store_true", help="debug: print the bf16 variants' losses instead of asserting")
     args = ap.parse_args()
     ext.init_distributed(use_gpu=True, backend="nccl")
@@ -209,6 +213,9 @@ def main():
     c = Case(args.case, dev)
     c.tower_gemm = args.tower_gemm
     c.allreduce = args.allreduce
+    c.grad_wire = args.grad_wire
+    if args.mgpu_overlap:
+        dlrm_net.set_mgpu_overlap(args.mgpu_overlap)
     report = {"case": args.case, "world_size": W, "steps": args.steps, "checks": []}
 
     def note(msg):
