@@ -13,9 +13,9 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "build", "obj")
 KEYS = ["UTCHMMA", "UTCQMMA", "UTCBAR", "UTCATOMSWS", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMACCTL", "UBLKCP", "SYNCS", "HMMA",
-        "LDG.E.128", "LDG.E.64", "STG.E.128", "STG.E.64", "LDGSTS", "UCGABAR", "MEMBAR", "ATOMG", "RED.E", "REDG"]
+        "LDSM", "LDG.E.128", "LDG.E.64", "STG.E.128", "STG.E.64", "LDGSTS", "UCGABAR", "MEMBAR", "ATOMG", "RED.E", "REDG"]
 WANT = re.compile(r"gemm_pair_kernel|wgrad_splitk|wgrad_reduce|embbag_fwd_kernel|bwd_update_kernel|interact_fwd_mma|interact_bwd_mma|"
-                  r"radix_scatter|build_keys|a2a_push|head_bwd|relu_bwd_bias")
+                  r"radix_scatter|build_keys|a2a_push|head_bwd|relu_bwd_bias|interact_fwd_bulk|peer_allreduce_kernel")
 
 
 def main():
@@ -41,7 +41,7 @@ def main():
             op = ins.split()[1] if ins.startswith("@") and len(ins.split()) > 1 else ins.split()[0]
             for k in KEYS:
                 if op.startswith(k):
-                    full = op if k in ("UTCHMMA", "UTMALDG", "UTCBAR", "SYNCS", "HMMA", "UBLKCP", "LDTM") else k
+                    full = op if k in ("UTCHMMA", "UTMALDG", "UTCBAR", "SYNCS", "HMMA", "UBLKCP", "LDTM", "LDSM") else k
                     counts[full] += 1
                     first.setdefault(full, ins[:110])
         if name:
