@@ -209,3 +209,23 @@ def test_installed_module_has_the_surface_the_reference_imports():
     for kw in ("optimizer", "learning_rate", "eps", "stochastic_rounding"):
         assert kw in sig.parameters
     assert list(inspect.signature(mod.TableBatchedEmbeddingBags.forward).parameters)[1:] == ["indices", "offsets"]
+
+
+def test_multi_gpu_defaults_are_the_schedule_measured_on_eight_gpus(monkeypatch):
+    """The opt-in multi-GPU schedule (dlrm_net.MGPU_OVERLAP = 1) and the bf16 gradient wire have only been measured on two
+    GPUs: nothing may switch them on by default -- not the module, not bench.py's or
+    tools/check_exchange.py's arguments, not the model's entry points."""
+    import inspect
+    import sys
+    from dlrm_yx_b200 import dlrm_net, extend_distributed
+    assert dlrm_net.MGPU_OVERLAP == 0
+    assert inspect.signature(dlrm_net.DLRM_Net.enable_peer_exchange).parameters["grad_wire_bf16"].default is False
+    assert inspect.signature(dlrm_net.DLRM_Net.fuse_mlps).parameters["grad_wire_bf16"].default is False
+    assert inspect.signature(dlrm_net.DLRM_Net.fuse_mlps).parameters["allreduce"].default == "peer"
+    assert inspect.signature(extend_distributed.PeerExchange.__init__).parameters["grad_bf16"].default is False
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import bench
+    monkeypatch.setattr(sys, "argv", ["bench.py"])
+    args = bench.parse()
+    assert args.mgpu_overlap == 0 and args.grad_wire == "fp32" and args.allreduce == "peer"
