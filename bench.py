@@ -41,6 +41,9 @@ def parse():
     ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"],
                     help="data-parallel gradient sums (towers, replicated tables) at N > 1: the repo's kernel over NVLink peer "
                          "memory (csrc/peer_allreduce.cu) or NCCL (comparator)")
+    ap.add_argument("--watchdog-s", type=float, default=900.0,
+                    help="N > 1: a rank that has not finished after this many seconds says so on stderr and exits 124 instead of "
+                         "spinning in a device barrier until an outer limit kills the box (0 = off)")
     ap.add_argument("--mgpu-overlap", type=int, default=0, choices=[0, 1],
                     help="N > 1 schedule (dlrm_net.MGPU_OVERLAP): 0 = the one measured on 2 / 4 / 8 GPUs; 1 = separate high-priority "
                          "all-reduce streams, replicated lookup on a third stream, short-lived push CTAs (measured on 2 GPUs only)")
@@ -363,6 +366,16 @@ def run_ours(args):
     ext.init_distributed(use_gpu=True, backend="nccl")
     rank = max(ext.my_rank, 0)
     dev = torch.device("cuda", torch.cuda.current_device())
+    if W > 1 and args.watchdog_s > 0:
+        # cross-rank device barriers spin on the GPU: if one rank never arrives the others would wait for ever
+        def _expired():
+            sys.stderr.write("bench.py: rank %d not finished after %.0f s (a cross-rank wait that never completed?) -- giving up\n"
+                             % (rank, args.watchdog_s))
+            sys.stderr.flush()
+            os._exit(124)
+        wd = threading.Timer(args.watchdog_s, _expired)
+        wd.daemon = True
+        wd.start()
     if args.mlp == "tf32":
         torch.backends.cuda.matmul.allow_tf32 = True
         torch.backends.cudnn.allow_tf32 = True
