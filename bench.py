@@ -44,9 +44,10 @@ def parse():
     ap.add_argument("--watchdog-s", type=float, default=900.0,
                     help="N > 1: a rank that has not finished after this many seconds says so on stderr and exits 124 instead of "
                          "spinning in a device barrier until an outer limit kills the box (0 = off)")
-    ap.add_argument("--mgpu-overlap", type=int, default=0, choices=[0, 1],
-                    help="N > 1 schedule (dlrm_net.MGPU_OVERLAP): 0 = the one measured on 2 / 4 / 8 GPUs; 1 = separate high-priority "
-                         "all-reduce streams, replicated lookup on a third stream, short-lived push CTAs (measured on 2 GPUs only)")
+    ap.add_argument("--mgpu-overlap", type=int, default=0,
+                    help="N > 1 schedule, bit mask (dlrm_net.MGPU_OVERLAP): 0 = the one measured on 2 / 4 / 8 GPUs; 1 separate "
+                         "high-priority all-reduce streams, 2 short-lived push CTAs, 4 replicated sort on the side stream, 8 "
+                         "replicated lookup on a third stream; 15 = all (measured on 2 GPUs only)")
     ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"],
                     help="N > 1, bf16 towers: pooled-row gradients of the sharded tables cross NVLink as fp32 or rounded to bf16")
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"],

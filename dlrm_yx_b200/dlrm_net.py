@@ -47,35 +47,38 @@ def _side_stream(device):
 
 _COMM = {}
 
-# Scheduling of the multi-process step around the exchange.
+# Scheduling of the multi-process step around the exchange: a bit mask.
 #   0 (default): the schedule that has run on 2, 4 and 8 GPUs -- ONE communication stream of default priority for every
 #      gradient all-reduce chain, the replicated tables' lookup and sort on the main stream behind the bottom tower, the
 #      gradient push as a looping grid of 16 CTAs per SM.
-#   1: every all-reduce chain on its own HIGH-priority stream, the replicated tables' lookup on a third stream beside the
-#      scatter and the bottom tower, their sort on the side stream, the gradient push as short-lived CTAs.  Measured on 2
-#      GPUs (1.498 -> 1.418 ms per step, parity checks green); the one 8-GPU run of it did NOT finish within its time limit
-#      (no error, no output: see DESIGN.md section 5) and there was no GPU time left to find out why, so it is opt-in.
+#   1: every all-reduce chain on its own HIGH-priority stream;  2: the gradient push as short-lived CTAs;
+#   4: the replicated tables' sort on the side stream;  8: their lookup on a third stream beside the scatter and the
+#      bottom tower.  15 = all four, measured on 2 GPUs (1.498 -> 1.418 ms per step with the bf16 gradient wire, parity
+#      checks green); the one 8-GPU run of it did NOT finish within its time limit (no error, no output: see DESIGN.md
+#      section 5) and there was no GPU time left to find out why -- hence opt-in, and hence separate bits, to bisect.
 MGPU_OVERLAP = 0
+MGPU_COMM_STREAMS, MGPU_SHORT_PUSH, MGPU_REP_SORT_SIDE, MGPU_REP_LOOKUP_STREAM = 1, 2, 4, 8
 
 
-def set_mgpu_overlap(level):
+def set_mgpu_overlap(mask):
     """Selects the schedule above (before the first step / graph capture) and the matching gradient-push grid."""
     global MGPU_OVERLAP
-    MGPU_OVERLAP = 1 if int(level) else 0
-    _lib.set_tunable(13, MGPU_OVERLAP)          # DLRMX_TUNE_PUSH_GRID (csrc/a2a_layout.cu)
+    MGPU_OVERLAP = int(mask) & 15
+    _lib.set_tunable(13, 1 if MGPU_OVERLAP & MGPU_SHORT_PUSH else 0)          # DLRMX_TUNE_PUSH_GRID (csrc/a2a_layout.cu)
 
 
 def _comm_stream(device, which=0):
-    """Stream(s) of the gradient all-reduces that run beside compute.  MGPU_OVERLAP = 1: 0 = the towers', 1 = the replicated
+    """Stream(s) of the gradient all-reduces that run beside compute.  MGPU_COMM_STREAMS: 0 = the towers', 1 = the replicated
     tables' (each chain is barrier -> sum -> barrier -> consumer, and the two do not depend on each other), both HIGH
     priority: their kernels are small and latency-bound (device barriers, NVLink round trips) and must not queue behind the
     grids of the gradient push / sparse update they run beside."""
     if not OVERLAP_STREAMS:
         return torch.cuda.current_stream()
-    key = (device, which, 1) if MGPU_OVERLAP else (device, 0, 0)
+    split = bool(MGPU_OVERLAP & MGPU_COMM_STREAMS)
+    key = (device, which, 1) if split else (device, 0, 0)
     s = _COMM.get(key)
     if s is None:
-        s = _COMM[key] = torch.cuda.Stream(device=device, priority=-1 if MGPU_OVERLAP else 0)
+        s = _COMM[key] = torch.cuda.Stream(device=device, priority=-1 if split else 0)
     return s
 
 
@@ -615,13 +618,13 @@ class DLRM_Net(nn.Module):
 
     def _replicated_lookup(self, step, feat, T_s, off, idx):
         """Pooled rows of the replicated tables for the LOCAL batch, straight into their feature slots; the sort for
-        their backward is issued right behind (MGPU_OVERLAP: on the side stream)."""
+        their backward is issued right behind (MGPU_REP_SORT_SIDE: on the side stream)."""
         rep = self.emb_rep
         step.rep, step.rep_indices, step.rep_offsets = rep, idx, off
         ops.embbag_forward(rep.table_set(), idx, off, step.lb, out=feat[:, 1 + T_s:, :], stride_b=feat.stride(0),
                            stride_t=feat.stride(1))
         if torch.is_grad_enabled():
-            if MGPU_OVERLAP:
+            if MGPU_OVERLAP & MGPU_REP_SORT_SIDE:
                 # on the side stream, where the backward consumes it: on the main stream its eight launches (~80 us at the
                 # Terabyte shape) sit between this lookup and the interaction (profiles/r02_timeline_n8_peer_ar_rank0.txt)
                 step.rep_sorted = _sort_on_side(rep, idx, off, step.lb)
@@ -646,7 +649,7 @@ class DLRM_Net(nn.Module):
                 if torch.is_grad_enabled() and emb.T > 0:
                     step.presorted = emb.sort_lookups(idx, off, peer.W * lb)
         rep_done = None
-        if self.emb_rep is not None and MGPU_OVERLAP:
+        if self.emb_rep is not None and (MGPU_OVERLAP & MGPU_REP_LOOKUP_STREAM):
             # local rows of the replicated tables: HBM work on a third stream, beside the NVLink-bound scatter AND the bottom
             # tower (behind the tower on the main stream it was the last thing the interaction waited for)
             rs = _comm_stream(dense_x.device, 1)
@@ -657,7 +660,7 @@ class DLRM_Net(nn.Module):
                 rep_done = rs.record_event() if rs != main else None
         with record_function("module::forward_pass::bottom_mlp"):
             x = self.apply_mlp(dense_x, self.bot_l)
-        if self.emb_rep is not None and not MGPU_OVERLAP:      # local rows of the replicated tables: HBM work beside the
+        if self.emb_rep is not None and not (MGPU_OVERLAP & MGPU_REP_LOOKUP_STREAM):      # local rows of the replicated tables: HBM work beside the
             with record_function("module::forward_pass::embedding_lookup"):       # NVLink-bound scatter
                 self._replicated_lookup(step, peer.feat, T_s, roff, ridx)
         cols = self.top_l.layers[0].K_pad if getattr(self, "_mixed", False) else 0

@@ -212,7 +212,7 @@ def test_installed_module_has_the_surface_the_reference_imports():
 
 
 def test_multi_gpu_defaults_are_the_schedule_measured_on_eight_gpus(monkeypatch):
-    """The opt-in multi-GPU schedule (dlrm_net.MGPU_OVERLAP = 1) and the bf16 gradient wire have only been measured on two
+    """The opt-in multi-GPU schedule (dlrm_net.MGPU_OVERLAP != 0) and the bf16 gradient wire have only been measured on two
     GPUs: nothing may switch them on by default -- not the module, not bench.py's or
     tools/check_exchange.py's arguments, not the model's entry points."""
     import inspect

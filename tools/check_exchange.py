@@ -202,7 +202,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--tower-gemm", default="tc", choices=["tc", "cublas"], help="GEMMs of the fused bf16 towers (cublas: comparator)")
     ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"], help="gradient sums of the fused towers / replicated tables")
-    ap.add_argument("--mgpu-overlap", type=int, default=0, choices=[0, 1], help="dlrm_net.MGPU_OVERLAP (see there)")
+    ap.add_argument("--mgpu-overlap", type=int, default=0, help="dlrm_net.MGPU_OVERLAP bit mask (see there; 15 = all)")
     ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"], help="pooled-row gradients between GPUs (bf16 towers)")
     ap.add_argument("--losses-only", action="store_true", help="debug: print the bf16 variants' losses instead of asserting")
     args = ap.parse_args()
