@@ -18,6 +18,9 @@
 //             fragments to global memory (full 32-byte sectors), with the pass-through dR[:, :D] added to feature 0.
 // HBM traffic is the algorithmic minimum: B*F*D*4 in + B*(D+nz)*4 out (forward).
 //
+// interact_fwd_bulk_kernel (below the generic forward) is the forward kernel of the training step: same arithmetic as
+// interact_fwd_mma_kernel<true, true>, a third of its instructions (ldmatrix fragment loads, constant-offset epilogue).
+//
 // MIXED variants (template flag) serve the bf16 MLP towers: feature 0 (the bottom-MLP output) is read as bf16, the
 // result [x | tril] is written as bf16 with its row padded with zeros to the top MLP's K (a multiple of 8), dR is read
 // as bf16 and the feature-0 gradient is written as bf16; pooled embeddings and their gradients stay fp32.  Since the
@@ -298,13 +301,6 @@ __device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
-__device__ __forceinline__ void mma_tf32_r(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-
 constexpr int kFwdTileFloats = 16 * 8;                    // one m16n8 accumulator tile
 constexpr int kFwdPartFloats = 6 * kFwdTileFloats;        // lower-triangle tiles: (m0: n0 n1) (m1: n0 n1 n2 n3)
 constexpr int kFwdMaxIt = 3;                              // output pairs per thread: (out_stride - D) / 2 <= 3 * 128
@@ -404,16 +400,16 @@ interact_fwd_bulk_kernel(const float* __restrict__ feat, int64_t fsb, int B, int
             ldsm_x4(ad0, a0);
 #pragma unroll
             for (int q = 0; q < 4; ++q) a0[q] += 0x1000u;             // round to nearest TF32 (low 13 bits are ignored)
-            mma_tf32_r(c[0], a0, a0[0], a0[2]);
-            mma_tf32_r(c[1], a0, a0[1], a0[3]);
+            mma_tf32(c[0], a0, a0[0], a0[2]);
+            mma_tf32(c[1], a0, a0[1], a0[3]);
             if (two_m) {
                 ldsm_x4(ad1, a1);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) a1[q] += 0x1000u;
-                mma_tf32_r(c[2], a1, a0[0], a0[2]);
-                mma_tf32_r(c[3], a1, a0[1], a0[3]);
-                mma_tf32_r(c[4], a1, a1[0], a1[2]);
-                mma_tf32_r(c[5], a1, a1[1], a1[3]);
+                mma_tf32(c[2], a1, a0[0], a0[2]);
+                mma_tf32(c[3], a1, a0[1], a0[3]);
+                mma_tf32(c[4], a1, a1[0], a1[2]);
+                mma_tf32(c[5], a1, a1[1], a1[3]);
             }
         }
         __syncthreads();            // the previous sample's partials have been summed by every thread
